@@ -1,0 +1,149 @@
+"""Pins the CPU oracle against the reference's literal known answer, Spark's documented
+hash answers, SURVEY.md Appendix A.6 and the quick-start fixture (CPU only)."""
+import json
+import os
+
+import numpy as np
+import pyarrow as pa
+import pytest
+
+from fixtures import departments_table, employees_table, sample_table
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+TYPES = {"int32": pa.int32(), "int64": pa.int64(), "string": pa.string()}
+
+
+def _cols(spec):
+    return [pa.array(c["values"], type=TYPES[c["type"]]) for c in spec]
+
+
+def _vectors():
+    with open(os.path.join(HERE, "golden", "murmur3_vectors.json")) as f:
+        g = json.load(f)
+    return [(k, i, v) for k in ("pinned", "derived") for i, v in enumerate(g[k])]
+
+
+@pytest.mark.parametrize("kind,i,vec", _vectors())
+def test_murmur3_known_answers(oracle, kind, i, vec):
+    cols = _cols(vec["cols"])
+    if "hash" in vec:
+        assert oracle.hash_rows(cols).tolist() == vec["hash"]
+    if "bucket" in vec:
+        assert oracle.bucket_ids(cols, vec["num_buckets"]).tolist() == vec["bucket"]
+
+
+def test_pmod_is_never_negative(oracle):
+    rng = np.random.default_rng(1)
+    k = pa.array(rng.integers(-2**62, 2**62, size=10000))
+    for nb in (1, 3, 200, 8192):
+        b = oracle.bucket_ids([k], nb)
+        assert b.min() >= 0 and b.max() < nb
+
+
+def test_null_key_leaves_seed(oracle):
+    # A.2: nulls skip, so an all-null key hashes to the seed 42
+    k1 = pa.array([None, 5, None], type=pa.int32())
+    k2 = pa.array([None, None, 7], type=pa.int64())
+    h = oracle.hash_rows([k1, k2])
+    assert h[0] == 42
+    assert h[1] == oracle.hash_rows([pa.array([5], pa.int32())])[0]
+    assert h[2] == oracle.hash_rows([pa.array([7], pa.int64())])[0]
+
+
+def test_float_hash_canonicalises_nan_not_negzero(oracle):
+    a = pa.array([float("nan"), np.float64(np.frombuffer(b"\x01\x00\x00\x00\x00\x00\xf8\xff", dtype=np.float64)[0]), 0.0, -0.0])
+    h = oracle.hash_rows([a])
+    assert h[0] == h[1]
+    assert h[2] != h[3]
+
+
+def test_quickstart_index_layout(oracle):
+    # deptIndex has buckets 53 [20, 40], 122 [10], 181 [30]
+    d = departments_table()
+    cols = [d["deptId"], d["deptName"]]
+    perm, off = oracle.build_index(cols, 1, 200)
+    ids = d["deptId"].to_numpy()[perm]
+    nonempty = {b: ids[off[b]:off[b + 1]].tolist() for b in range(200) if off[b + 1] > off[b]}
+    assert nonempty == {53: [20, 40], 122: [10], 181: [30]}
+    e = employees_table()
+    perm, off = oracle.build_index([e["deptId"], e["empName"]], 1, 200)
+    names = np.array(e["empName"].to_pylist())[perm]
+    got = {b: sorted(names[off[b]:off[b + 1]].tolist()) for b in range(200) if off[b + 1] > off[b]}
+    assert got == {53: sorted(["SMITH", "JONES", "SCOTT", "ADAMS", "FORD"]),
+                   122: sorted(["CLARK", "KING", "MILLER"]),
+                   181: sorted(["ALLEN", "WARD", "BLAKE", "TURNER", "JAMES", "MARTIN"])}
+
+
+def test_quickstart_join_and_filter(oracle):
+    d, e = departments_table(), employees_table()
+    dcols, ecols = [d["deptId"], d["deptName"]], [e["deptId"], e["empName"]]
+    dperm, doff = oracle.build_index(dcols, 1, 200)
+    eperm, eoff = oracle.build_index(ecols, 1, 200)
+    di, ei = oracle.take(dcols, dperm), oracle.take(ecols, eperm)
+    li, ri, ooff = oracle.join(ei, di, 1, eoff, doff)
+    rows = sorted(zip(ei[1].take(pa.array(li)).to_pylist(), di[1].take(pa.array(ri)).to_pylist()))
+    dept = {10: "Accounting", 20: "Research", 30: "Sales"}
+    want = sorted((n, dept[k]) for _, n, k in __import__("fixtures").EMPLOYEES)
+    assert rows == want and len(rows) == 14
+    # filter deptId = 20 -> deptName (App.scala:91)
+    idx = oracle.filter_rows(di, [("eq", 0, 20)])
+    assert di[1].take(pa.array(idx)).to_pylist() == ["Research"]
+
+
+def test_sample_data_bucketing_invariant(oracle):
+    # DataFrameWriterExtensionsTest.scala:93-158: bucket of every row in a "file" == recomputed
+    # bucket, rows sorted inside a bucket, multiset preserved (n=3, string and int+string keys)
+    t = sample_table()
+    for keycols in (["Query"], ["imprs", "Query"]):
+        cols = [t[c] for c in keycols] + [t["clicks"]]
+        nk = len(keycols)
+        perm, off = oracle.build_index(cols, nk, 3)
+        assert sorted(perm.tolist()) == list(range(10))
+        out = oracle.take(cols, perm)
+        b = oracle.bucket_ids(out[:nk], 3)
+        for k in range(3):
+            assert (b[off[k]:off[k + 1]] == k).all()
+            keys = list(zip(*[c.to_pylist() for c in out[:nk]]))[off[k]:off[k + 1]]
+            assert keys == sorted(keys)
+
+
+def test_sort_order_nulls_first_nan_last_strings_bytewise(oracle):
+    a = pa.array([3.0, None, float("nan"), -0.0, 0.0, -1.5, None])
+    perm = oracle.sort_segments([a], 1, [0, 7])
+    vals = [a[int(i)].as_py() for i in perm]
+    assert vals[0] is None and vals[1] is None
+    assert vals[2] == -1.5 and vals[5] == 3.0 and vals[6] != vals[6]
+    assert perm.tolist()[3:5] == [3, 4]  # -0.0 == 0.0, stable
+    s = pa.array(["b", "ab", "a", "", "é", "a\x00", "abc", None])
+    perm = oracle.sort_segments([s], 1, [0, 8])
+    assert [s[int(i)].as_py() for i in perm] == [None, "", "a", "a\x00", "ab", "abc", "b", "é"]
+
+
+def test_radix_fast_path_equals_merge_sort(oracle):
+    rng = np.random.default_rng(7)
+    k = pa.array(rng.integers(-1000, 1000, size=50000))
+    v = pa.array(np.arange(50000))
+    p1, o1 = oracle.build_index([k, v], 1, 7, use_radix=True)
+    p2, o2 = oracle.build_index([k, v], 1, 7, use_radix=False)
+    assert (p1 == p2).all() and (o1 == o2).all()
+
+
+def test_join_null_keys_never_match_and_cross_product(oracle):
+    l = [pa.array([None, 1, 1, 2, 5], type=pa.int64())]
+    r = [pa.array([None, 1, 1, 1, 3, 5], type=pa.int64())]
+    li, ri, off = oracle.join(l, r, 1, [0, 5], [0, 6])
+    assert len(li) == 2 * 3 + 1
+    assert sorted(zip(li.tolist(), ri.tolist())) == sorted([(1, 1), (1, 2), (1, 3), (2, 1), (2, 2), (2, 3), (4, 5)])
+
+
+def test_filter_three_valued_logic(oracle):
+    a = pa.array([1, None, 3, 4], type=pa.int32())
+    b = pa.array(["x", "y", None, "x"])
+    # a > 1 OR b = 'x'
+    idx = oracle.filter_rows([a, b], [("gt", 0, 1), ("eq", 1, "x"), ("or",)])
+    assert idx.tolist() == [0, 2, 3]
+    # NOT (a > 1): row with NULL stays unknown -> dropped
+    idx = oracle.filter_rows([a, b], [("gt", 0, 1), ("not",)])
+    assert idx.tolist() == [0]
+    idx = oracle.filter_rows([a, b], [("is_null", 0), ("is_not_null", 1), ("and",)])
+    assert idx.tolist() == [1]
