@@ -1,0 +1,308 @@
+// hs_api.cu — context lifecycle, column staging, result tables (C ABI glue).
+#include "hs_common.cuh"
+
+struct TableImpl {
+  std::vector<void*> dev;     // device buffers owned by the table
+  std::vector<void*> pinned;  // pinned host buffers owned by the table
+  std::vector<hs_column> cols;
+  std::vector<int64_t> boff;
+};
+
+void hs_sync(hs_ctx* c) { CK(cudaStreamSynchronize(c->stream)); }
+
+static cudaEvent_t get_event(hs_ctx* c) {
+  if (!c->ev_free.empty()) {
+    cudaEvent_t e = c->ev_free.back();
+    c->ev_free.pop_back();
+    return e;
+  }
+  cudaEvent_t e;
+  CK(cudaEventCreate(&e));
+  return e;
+}
+
+void hs_stages_reset(hs_ctx* c) {
+  for (auto& s : c->stages) {
+    c->ev_free.push_back(s.e0);
+    c->ev_free.push_back(s.e1);
+  }
+  c->stages.clear();
+  c->cur_stage = -1;
+}
+
+void hs_stage_begin(hs_ctx* c, const char* name) {
+  if (!c->timing) return;
+  StageRec r;
+  memset(&r, 0, sizeof r);
+  strncpy(r.name, name, sizeof(r.name) - 1);
+  r.e0 = get_event(c);
+  r.e1 = get_event(c);
+  r.launches = 0;
+  CK(cudaEventRecord(r.e0, c->stream));
+  c->stages.push_back(r);
+  c->cur_stage = (int)c->stages.size() - 1;
+}
+
+void hs_stage_end(hs_ctx* c) {
+  if (!c->timing || c->cur_stage < 0) return;
+  cudaEventRecord(c->stages[c->cur_stage].e1, c->stream);
+  c->cur_stage = -1;
+}
+
+bool hs_is_device_ptr(const void* p) {
+  if (!p) return false;
+  cudaPointerAttributes a;
+  cudaError_t e = cudaPointerGetAttributes(&a, p);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+static const void* to_device(hs_ctx* c, const void* p, size_t bytes, DevCol& out) {
+  if (!p || bytes == 0) return p && hs_is_device_ptr(p) ? p : nullptr;
+  if (hs_is_device_ptr(p)) return p;
+  out.owned.emplace_back(c, bytes);
+  CK(cudaMemcpyAsync(out.owned.back().p, p, bytes, cudaMemcpyHostToDevice, c->stream));
+  return out.owned.back().p;
+}
+
+void hs_stage_column(hs_ctx* c, const hs_column& in, DevCol& out) {
+  if (!hs_type_ok(in.type)) HS_THROW(HS_EUNSUPPORTED, "unsupported column type %d", in.type);
+  if (in.length < 0) HS_THROW(HS_EINVAL, "negative column length");
+  if (in.length >= (int64_t)0xFFFFFFF0ll) HS_THROW(HS_EUNSUPPORTED, "more than 2^32-16 rows in one call");
+  out.type = in.type;
+  out.length = in.length;
+  out.null_count = in.validity ? in.null_count : 0;
+  int64_t n = in.length;
+  out.validity = nullptr;
+  if (in.validity && in.null_count != 0)
+    out.validity = (const uint8_t*)to_device(c, in.validity, (size_t)((n + 7) / 8), out);
+  if (hs_is_varlen(in.type)) {
+    if (!in.offsets) HS_THROW(HS_EINVAL, "UTF8/BINARY column without offsets");
+    int32_t last = 0, first = 0;
+    if (hs_is_device_ptr(in.offsets)) {
+      CK(cudaMemcpyAsync(&last, in.offsets + n, 4, cudaMemcpyDeviceToHost, c->stream));
+      CK(cudaMemcpyAsync(&first, in.offsets, 4, cudaMemcpyDeviceToHost, c->stream));
+      hs_sync(c);
+    } else {
+      last = in.offsets[n];
+      first = in.offsets[0];
+    }
+    if (first != 0) HS_THROW(HS_EINVAL, "offsets[0] must be 0 (pass an unsliced array)");
+    out.offsets = (const int32_t*)to_device(c, in.offsets, (size_t)(n + 1) * 4, out);
+    out.data_bytes = last;
+    out.data = to_device(c, in.data, (size_t)last, out);
+  } else if (in.type == HS_BOOL) {
+    out.data_bytes = (n + 7) / 8;
+    out.data = to_device(c, in.data, (size_t)out.data_bytes, out);
+  } else {
+    out.data_bytes = n * hs_fixed_width(in.type);
+    out.data = to_device(c, in.data, (size_t)out.data_bytes, out);
+  }
+  if (n > 0 && !hs_is_varlen(in.type) && !out.data) HS_THROW(HS_EINVAL, "column without data buffer");
+}
+
+void hs_stage_columns(hs_ctx* c, const hs_column* in, int n, std::vector<DevCol>& out) {
+  out.resize(n);
+  for (int i = 0; i < n; i++) {
+    hs_stage_column(c, in[i], out[i]);
+    if (in[i].length != in[0].length) HS_THROW(HS_EINVAL, "columns differ in length");
+  }
+}
+
+KCol hs_kcol(const DevCol& d) {
+  KCol k;
+  k.type = d.type;
+  k.has_nulls = d.validity != nullptr;
+  k.validity = d.validity;
+  k.offsets = d.offsets;
+  k.data = d.data;
+  return k;
+}
+
+void* hs_pinned_alloc(hs_ctx* c, size_t bytes) {
+  if (bytes == 0) bytes = 16;
+  size_t cap = 256;
+  while (cap < bytes) cap <<= 1;
+  if (bytes > (size_t(1) << 26)) cap = (bytes + (size_t(1) << 24) - 1) & ~((size_t(1) << 24) - 1);
+  auto it = c->pinned_free.lower_bound(cap);
+  if (it != c->pinned_free.end() && it->first <= cap * 2) {
+    void* p = it->second;
+    c->pinned_free.erase(it);
+    return p;
+  }
+  void* p = nullptr;
+  CK(cudaMallocHost(&p, cap));
+  c->pinned_size[p] = cap;
+  return p;
+}
+
+void hs_pinned_free(hs_ctx* c, void* p) {
+  if (!p) return;
+  auto it = c->pinned_size.find(p);
+  if (it == c->pinned_size.end()) return;
+  c->pinned_free.insert({it->second, p});
+}
+
+hs_table* hs_finish_table(hs_ctx* c, std::vector<OutCol>& cols, int64_t nrows, int32_t num_buckets,
+                          const std::vector<int64_t>* boff) {
+  TableImpl* ti = new TableImpl();
+  hs_table* t = new hs_table();
+  memset(t, 0, sizeof *t);
+  t->impl = ti;
+  try {
+    ti->cols.resize(cols.size());
+    bool host = c->out_loc == HS_MEM_HOST;
+    auto place = [&](DBuf& b, size_t bytes) -> void* {
+      if (!b.p) return nullptr;
+      if (!host) {
+        void* p = b.detach();
+        ti->dev.push_back(p);
+        return p;
+      }
+      void* h = hs_pinned_alloc(c, bytes);
+      ti->pinned.push_back(h);
+      if (bytes) CK(cudaMemcpyAsync(h, b.p, bytes, cudaMemcpyDeviceToHost, c->stream));
+      return h;
+    };
+    for (size_t i = 0; i < cols.size(); i++) {
+      OutCol& o = cols[i];
+      hs_column& hc = ti->cols[i];
+      memset(&hc, 0, sizeof hc);
+      hc.type = o.type;
+      hc.length = o.length;
+      hc.null_count = o.null_count;
+      hc.validity = (const uint8_t*)place(o.validity, (size_t)((o.length + 7) / 8));
+      hc.offsets = (const int32_t*)place(o.offsets, (size_t)(o.length + 1) * 4);
+      hc.data = place(o.data, (size_t)o.data_bytes);
+      if (!hc.validity) hc.null_count = 0;
+    }
+    hs_sync(c);
+    cols.clear();  // frees the device copies in host mode
+    t->ncols = (int32_t)ti->cols.size();
+    t->location = host ? HS_MEM_HOST : HS_MEM_DEVICE;
+    t->nrows = nrows;
+    t->cols = ti->cols.data();
+    if (boff) {
+      ti->boff = *boff;
+      t->num_buckets = num_buckets;
+      t->bucket_offsets = ti->boff.data();
+    }
+  } catch (...) {
+    for (void* p : ti->dev) cudaFreeAsync(p, c->stream);
+    for (void* p : ti->pinned) hs_pinned_free(c, p);
+    delete ti;
+    delete t;
+    throw;
+  }
+  return t;
+}
+
+extern "C" {
+
+const char* hs_version(void) { return "hsgpu 0.1 (sm_100a)"; }
+
+int32_t hs_ctx_create(int32_t device, hs_ctx** out) {
+  if (!out) return HS_EINVAL;
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    return HS_ECUDA;  // no CPU fallback: without a CUDA device there is no context
+  }
+  if (device < 0 || device >= ndev) return HS_EINVAL;
+  hs_ctx* c = new hs_ctx();
+  c->device = device;
+  if (cudaSetDevice(device) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    cudaGetLastError();
+    delete c;
+    return HS_ECUDA;
+  }
+  // keep freed blocks in the stream-ordered pool: repeated builds reuse them without cudaMalloc
+  cudaMemPool_t pool;
+  if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+    uint64_t thr = UINT64_MAX;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+  }
+  *out = c;
+  return HS_OK;
+}
+
+int32_t hs_comm_destroy(hs_ctx* ctx);
+
+int32_t hs_ctx_destroy(hs_ctx* c) {
+  if (!c) return HS_EINVAL;
+  cudaSetDevice(c->device);
+  hs_comm_destroy(c);
+  cudaStreamSynchronize(c->stream);
+  for (auto& s : c->stages) { cudaEventDestroy(s.e0); cudaEventDestroy(s.e1); }
+  for (auto e : c->ev_free) cudaEventDestroy(e);
+  for (auto& kv : c->pinned_size) cudaFreeHost(kv.first);
+  cudaStreamDestroy(c->stream);
+  delete c;
+  return HS_OK;
+}
+
+const char* hs_last_error(hs_ctx* c) { return c ? c->err.c_str() : "null context"; }
+
+int32_t hs_ctx_set_output_location(hs_ctx* c, int32_t loc) {
+  if (!c || (loc != HS_MEM_HOST && loc != HS_MEM_DEVICE)) return HS_EINVAL;
+  c->out_loc = loc;
+  return HS_OK;
+}
+
+int32_t hs_ctx_get_stream(hs_ctx* c, void** s) {
+  if (!c || !s) return HS_EINVAL;
+  *s = (void*)c->stream;
+  return HS_OK;
+}
+
+int32_t hs_ctx_enable_timing(hs_ctx* c, int32_t on) {
+  if (!c) return HS_EINVAL;
+  c->timing = on != 0;
+  return HS_OK;
+}
+
+int32_t hs_ctx_last_timings(hs_ctx* c, hs_stage_timing* out, int32_t cap, int32_t* n) {
+  if (!c || !n) return HS_EINVAL;
+  API_BEGIN(c)
+  hs_sync(c);
+  int m = 0;
+  for (auto& s : c->stages) {
+    if (m >= cap || !out) break;
+    memset(&out[m], 0, sizeof out[m]);
+    strncpy(out[m].name, s.name, sizeof(out[m].name) - 1);
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, s.e0, s.e1) != cudaSuccess) { cudaGetLastError(); ms = -1.f; }
+    out[m].ms = ms;
+    out[m].launches = s.launches;
+    m++;
+  }
+  *n = out ? m : (int32_t)c->stages.size();
+  API_END(c)
+}
+
+int32_t hs_ctx_launch_count(hs_ctx* c, int64_t* out) {
+  if (!c || !out) return HS_EINVAL;
+  *out = c->launches;
+  return HS_OK;
+}
+
+int32_t hs_table_free(hs_ctx* c, hs_table* t) {
+  if (!c) return HS_EINVAL;
+  if (!t) return HS_OK;
+  cudaSetDevice(c->device);
+  TableImpl* ti = (TableImpl*)t->impl;
+  if (ti) {
+    for (void* p : ti->dev) cudaFreeAsync(p, c->stream);
+    for (void* p : ti->pinned) hs_pinned_free(c, p);
+    delete ti;
+  }
+  delete t;
+  return HS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,118 @@
+// hs_block.cuh — CTA-level building blocks of the row mover: stable digit ranking with
+// warp-private counters (no atomics), block scans, min/max reductions.
+#pragma once
+#include "hs_common.cuh"
+
+#define PT_THREADS 256
+#define PT_WARPS 8
+#define PT_ITEMS 16
+#define PT_TILE (PT_THREADS * PT_ITEMS)  // 4096 rows per tile
+
+__device__ __forceinline__ uint32_t warp_incl_scan_u32(uint32_t v) {
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    uint32_t t = __shfl_up_sync(0xffffffffu, v, d);
+    if (lane_id() >= (uint32_t)d) v += t;
+  }
+  return v;
+}
+
+// exclusive scan of one value per thread over PT_THREADS threads; `scratch` >= PT_WARPS+1 words
+__device__ __forceinline__ uint32_t block_excl_scan_u32(uint32_t v, uint32_t* scratch, uint32_t* total) {
+  uint32_t inc = warp_incl_scan_u32(v);
+  int w = threadIdx.x >> 5;
+  __syncthreads();
+  if (lane_id() == 31) scratch[w] = inc;
+  __syncthreads();
+  if (w == 0) {
+    uint32_t s = lane_id() < PT_WARPS ? scratch[lane_id()] : 0;
+    uint32_t si = warp_incl_scan_u32(s);
+    if (lane_id() < PT_WARPS) scratch[lane_id()] = si - s;
+    if (lane_id() == PT_WARPS - 1) scratch[PT_WARPS] = si;
+  }
+  __syncthreads();
+  if (total) *total = scratch[PT_WARPS];
+  return inc - v + scratch[w];
+}
+
+// Stable ranking of a tile by digit. Item k of lane l in warp w is tile element
+// w*chunk + k*32 + l (warp-striped), so (warp, k, lane) order == element order.
+//   digit[k], valid bit k of vmask : inputs
+//   cnt  : PT_WARPS * radix_pad words   tot, loc : radix_pad words   scratch : PT_WARPS+1 words
+// On return pos[k] = position of the item in the digit-sorted tile, tot[d] = items with digit d,
+// loc[d] = first position of digit d.
+template <int ITEMS>
+__device__ __forceinline__ void tile_rank(const uint32_t (&digit)[ITEMS], uint32_t vmask, int items, int bits,
+                                          int radix_pad, uint32_t* cnt, uint32_t* tot, uint32_t* loc,
+                                          uint32_t* scratch, uint32_t (&pos)[ITEMS]) {
+  const int w = threadIdx.x >> 5;
+  const uint32_t lt = (1u << lane_id()) - 1u;
+  for (int i = threadIdx.x; i < PT_WARPS * radix_pad; i += PT_THREADS) cnt[i] = 0;
+  __syncthreads();
+  uint32_t* mycnt = cnt + w * radix_pad;
+#pragma unroll
+  for (int k = 0; k < ITEMS; k++) {
+    if (k < items) {
+      bool v = (vmask >> k) & 1u;
+      uint32_t d = digit[k];
+      uint32_t m = __ballot_sync(0xffffffffu, v);
+      for (int b = 0; b < bits; b++) {
+        bool bit = (d >> b) & 1u;
+        uint32_t bal = __ballot_sync(0xffffffffu, bit);
+        m &= bit ? bal : ~bal;
+      }
+      uint32_t r = __popc(m & lt);
+      uint32_t pre = v ? mycnt[d] : 0;
+      __syncwarp();
+      if (v && r == 0) mycnt[d] = pre + __popc(m);
+      __syncwarp();
+      pos[k] = pre + r;
+    }
+  }
+  __syncthreads();
+  for (int d = threadIdx.x; d < radix_pad; d += PT_THREADS) {
+    uint32_t run = 0;
+#pragma unroll
+    for (int ww = 0; ww < PT_WARPS; ww++) {
+      uint32_t c = cnt[ww * radix_pad + d];
+      cnt[ww * radix_pad + d] = run;
+      run += c;
+    }
+    tot[d] = run;
+  }
+  __syncthreads();
+  // exclusive scan of tot over digits: each thread owns radix_pad/PT_THREADS consecutive digits
+  const int per = radix_pad / PT_THREADS;
+  uint32_t s = 0;
+  for (int j = 0; j < per; j++) s += tot[threadIdx.x * per + j];
+  uint32_t ex = block_excl_scan_u32(s, scratch, nullptr);
+  for (int j = 0; j < per; j++) {
+    loc[threadIdx.x * per + j] = ex;
+    ex += tot[threadIdx.x * per + j];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < ITEMS; k++) {
+    if (k < items && ((vmask >> k) & 1u)) {
+      uint32_t d = digit[k];
+      pos[k] += loc[d] + mycnt[d];
+    }
+  }
+}
+
+__device__ __forceinline__ uint64_t warp_min_u64(uint64_t v) {
+#pragma unroll
+  for (int d = 16; d; d >>= 1) {
+    uint64_t o = __shfl_xor_sync(0xffffffffu, v, d);
+    v = o < v ? o : v;
+  }
+  return v;
+}
+__device__ __forceinline__ uint64_t warp_max_u64(uint64_t v) {
+#pragma unroll
+  for (int d = 16; d; d >>= 1) {
+    uint64_t o = __shfl_xor_sync(0xffffffffu, v, d);
+    v = o > v ? o : v;
+  }
+  return v;
+}

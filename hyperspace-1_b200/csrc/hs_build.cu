@@ -1,0 +1,534 @@
+// hs_build.cu — the index build behind hs_build_index / hs_merge_runs.
+// Orchestrates K1 (hash + histogram), K2 (bucket scatter) and K3 (per-bucket sort) for the body of
+// CreateActionBase.write (HS/actions/CreateActionBase.scala:122-140):
+//   repartition(numBuckets, indexedCols)  ->  saveWithBuckets(BucketSpec(n, cols, cols))
+// Data layout in HBM: every fixed-width column is its own array (SoA). Validity bitmaps and boolean
+// columns travel as one byte per row and are re-packed at the end; string columns do not travel —
+// a 32-bit source-row column does, and the bytes are gathered once at the end.
+#include "hs_keys.cuh"
+#include "hs_kernels.h"
+
+// ------------------------------------------------------------------ small kernels
+__global__ void __launch_bounds__(256) k_bits_to_bytes(const uint8_t* __restrict__ bits, int64_t n,
+                                                       uint8_t* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) out[i] = (bits[i >> 3] >> (i & 7)) & 1;
+}
+__global__ void __launch_bounds__(256) k_bytes_to_bits(const uint8_t* __restrict__ in, int64_t n,
+                                                       uint8_t* __restrict__ bits) {
+  int64_t nb = (n + 7) >> 3;
+  int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; b < nb; b += stride) {
+    unsigned v = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      int64_t i = b * 8 + k;
+      if (i < n && in[i]) v |= 1u << k;
+    }
+    bits[b] = (uint8_t)v;
+  }
+}
+__global__ void __launch_bounds__(256) k_iota_u32(uint32_t* out, int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) out[i] = (uint32_t)i;
+}
+// chunk d of the normalised key of the rows rows[i] (or i when rows == NULL)
+__global__ void __launch_bounds__(256) k_build_nkey(KeyLayout L, KeySpec ks, int64_t n, int d,
+                                                    const uint32_t* __restrict__ rows,
+                                                    const uint8_t* __restrict__ flag,
+                                                    uint64_t* __restrict__ nkey, uint8_t* __restrict__ more) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    if (flag) {  // refinement: only rows inside a tie group of two or more rows
+      bool single = flag[i] && (i + 1 == n || flag[i + 1]);
+      if (single) continue;
+    }
+    bool m = false;
+    uint64_t v = nkey_chunk(L, ks, rows ? rows[i] : i, d, &m);
+    nkey[i] = v;
+    if (more) more[i] = m ? 1 : 0;
+  }
+}
+__global__ void __launch_bounds__(256) k_mark_starts(const uint32_t* __restrict__ seg_off, int64_t nseg,
+                                                     uint8_t* __restrict__ flag, uint32_t n) {
+  int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < nseg) {
+    uint32_t a = seg_off[s];
+    if (a < n) flag[a] = 1;
+  }
+}
+// a row starts a new group when its chunk differs from the previous row's, or the key is complete
+__global__ void __launch_bounds__(256) k_tie_flags(const uint64_t* __restrict__ nkey, const uint8_t* __restrict__ more,
+                                                   int64_t n, uint8_t* __restrict__ flag) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    uint8_t f = flag[i];
+    if (!f) {
+      if (i == 0 || nkey[i] != nkey[i - 1] || !more[i]) f = 1;
+      flag[i] = f;
+    }
+  }
+}
+__global__ void __launch_bounds__(256) k_head_positions(const uint8_t* __restrict__ flag, const uint32_t* __restrict__ rank,
+                                                        int64_t n, uint32_t* __restrict__ head_pos) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride)
+    if (flag[i]) head_pos[rank[i]] = (uint32_t)i;
+}
+__global__ void __launch_bounds__(256) k_group_segments(const uint32_t* __restrict__ head_pos, const uint64_t* ngroups,
+                                                        uint32_t n, uint32_t* __restrict__ gstart,
+                                                        uint32_t* __restrict__ glen, uint32_t* counter) {
+  int64_t G = (int64_t)*ngroups;
+  int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; g < G; g += stride) {
+    uint32_t a = head_pos[g];
+    uint32_t b = g + 1 < G ? head_pos[g + 1] : n;
+    if (b - a >= 2) {
+      uint32_t k = atomicAdd(counter, 1u);
+      gstart[k] = a;
+      glen[k] = b - a;
+    }
+  }
+}
+
+static unsigned grid1d(int64_t n) {
+  int64_t g = (n + 255) / 256;
+  int64_t cap = (int64_t)HS_NUM_SMS * 16;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (unsigned)g;
+}
+
+static int bitlen64(uint64_t v) {
+  int b = 0;
+  while (v) { b++; v >>= 1; }
+  return b;
+}
+
+// ------------------------------------------------------------------ key layout (host)
+// Packs the fixed-width key columns into static chunks (MSB first, right aligned); see hs_keys.cuh.
+static KeyLayout make_layout(const std::vector<DevCol>& cols, int nk, const uint64_t* minmax) {
+  KeyLayout L;
+  memset(&L, 0, sizeof L);
+  L.nkeys = nk;
+  int run = -1;
+  bool prev_fixed = false;
+  bool any_string = false;
+  struct Item { int col; int bits; bool is_flag; int chunk; };
+  std::vector<std::vector<Item>> runs;
+  for (int k = 0; k < nk; k++) {
+    NGroup& g = L.g[k];
+    g.flag_shift = -1;
+    g.flag_chunk = -1;
+    g.chunk = -1;
+    if (hs_is_varlen(cols[k].type)) {
+      g.is_string = 1;
+      prev_fixed = false;
+      any_string = true;
+      continue;
+    }
+    if (!prev_fixed) { run++; runs.emplace_back(); }
+    prev_fixed = true;
+    g.run_id = run;
+    uint64_t mn = minmax[2 * k], mx = minmax[2 * k + 1];
+    int width = mn <= mx ? bitlen64(mx - mn) : 0;
+    g.min = mn <= mx ? mn : 0;
+    if (cols[k].validity) runs[run].push_back({k, 1, true, 0});
+    if (width > 0) runs[run].push_back({k, width, false, 0});
+  }
+  L.nruns = run + 1;
+  int total_static_chunks = 0;
+  for (int r = 0; r <= run; r++) {
+    auto& items = runs[r];
+    int chunk = 0, used = 0;
+    for (auto& it : items) {
+      if (used + it.bits > 64) { chunk++; used = 0; }
+      it.chunk = chunk;
+      used += it.bits;
+    }
+    int nch = items.empty() ? 1 : chunk + 1;
+    L.run_chunks[r] = nch;
+    total_static_chunks += nch;
+    // shifts: right aligned inside each chunk
+    for (int ch = 0; ch < nch; ch++) {
+      int tot = 0;
+      for (auto& it : items) if (it.chunk == ch) tot += it.bits;
+      int consumed = 0;
+      for (auto& it : items) {
+        if (it.chunk != ch) continue;
+        consumed += it.bits;
+        int shift = tot - consumed;
+        if (it.is_flag) { L.g[it.col].flag_shift = shift; L.g[it.col].flag_chunk = ch; }
+        else { L.g[it.col].shift = shift; L.g[it.col].chunk = ch; }
+      }
+      if (r == 0 && ch == 0) L.bits0 = tot;
+    }
+  }
+  L.single_chunk = (!any_string && total_static_chunks <= 1) ? 1 : 0;
+  if (!L.single_chunk) L.bits0 = 64;
+  return L;
+}
+
+struct MovedCol {
+  int user_col;     // index of the user column, or -1 for internal columns
+  int role;         // 0 data, 1 validity bytes, 2 bool bytes, 3 nkey, 4 more, 5 srcrow
+  int esize;
+  const void* src;  // device source in input row order
+  DBuf a, b, tmp;   // tmp: expanded bits / generated columns (input order)
+};
+
+// The build over staged device columns; shared by hs_build_index, hs_merge_runs and the multi-GPU build.
+void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t nb, int32_t blo, int32_t nbl,
+                   std::vector<OutCol>& out, std::vector<int64_t>& boff) {
+  const int ncols = (int)cols.size();
+  const int64_t n = cols[0].length;
+  boff.assign((size_t)nb + 1, 0);
+  out.resize(ncols);
+  if (n == 0) {
+    for (int i = 0; i < ncols; i++) hs_copy_column(c, cols[i], out[i]);
+    return;
+  }
+  KeySpec ks = hs_make_keyspec(cols, n_indexed);
+
+  // ---- K1: bucket ids, histogram, key ranges
+  DBuf bucket(c, (size_t)n * 2 + 16), hist(c, (size_t)nbl * 4), minmax(c, (2 * HS_MAX_KEYS + 1) * 8);
+  {
+    Stage s(c, "hash_hist");
+    hs_hash_bucket_hist(c, ks, cols, n, nb, blo, nbl, bucket.as<uint16_t>(), hist.as<uint32_t>(),
+                        minmax.as<uint64_t>());
+  }
+  std::vector<uint32_t> h_hist((size_t)nbl);
+  uint64_t h_minmax[2 * HS_MAX_KEYS + 1];
+  CK(cudaMemcpyAsync(h_hist.data(), hist.p, (size_t)nbl * 4, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(h_minmax, minmax.p, sizeof h_minmax, cudaMemcpyDeviceToHost, c->stream));
+  hs_sync(c);
+  if (h_minmax[2 * HS_MAX_KEYS] != 0)
+    HS_THROW(HS_EINVAL, "%llu rows hash outside this rank's bucket range", (unsigned long long)h_minmax[2 * HS_MAX_KEYS]);
+  // local offsets (device, u32) drive the kernels; the global table has empty ranges outside [blo, blo+nbl)
+  std::vector<uint32_t> off32((size_t)nbl + 1, 0);
+  for (int b = 0; b < nbl; b++) off32[b + 1] = off32[b] + h_hist[b];
+  for (int b = 0; b < nb; b++) {
+    int lb = b - blo;
+    boff[b + 1] = boff[b] + ((lb >= 0 && lb < nbl) ? (int64_t)h_hist[lb] : 0);
+  }
+  DBuf d_off(c, ((size_t)nbl + 1) * 4);
+  CK(cudaMemcpyAsync(d_off.p, off32.data(), ((size_t)nbl + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+
+  // ---- key layout and the set of travelling columns
+  KeyLayout L = make_layout(cols, n_indexed, h_minmax);
+  bool fast_key = n_indexed == 1 && !cols[0].validity && (cols[0].type == HS_INT64 || cols[0].type == HS_INT32);
+  bool any_varlen = false;
+  for (auto& dc : cols) any_varlen |= hs_is_varlen(dc.type);
+  bool need_srcrow = any_varlen || !L.single_chunk;
+
+  std::vector<MovedCol> mv;
+  mv.reserve(HS_MAX_MOVE);
+  auto add = [&](int user, int role, int esize, const void* src) -> MovedCol& {
+    if ((int)mv.size() >= HS_MAX_MOVE) HS_THROW(HS_EUNSUPPORTED, "too many columns in one index (limit %d moved arrays)", HS_MAX_MOVE);
+    mv.emplace_back();
+    MovedCol& m = mv.back();
+    m.user_col = user; m.role = role; m.esize = esize; m.src = src;
+    return m;
+  };
+  {
+    Stage s(c, "prepare");
+    for (int i = 0; i < ncols; i++) {
+      DevCol& dc = cols[i];
+      if (dc.validity) {
+        MovedCol& m = add(i, 1, 1, nullptr);
+        m.tmp.alloc(c, (size_t)n);
+        LAUNCH(c, k_bits_to_bytes, grid1d(n), 256, 0, dc.validity, n, m.tmp.as<uint8_t>());
+        m.src = m.tmp.p;
+      }
+      if (hs_is_varlen(dc.type)) continue;
+      if (dc.type == HS_BOOL) {
+        MovedCol& m = add(i, 2, 1, nullptr);
+        m.tmp.alloc(c, (size_t)n);
+        LAUNCH(c, k_bits_to_bytes, grid1d(n), 256, 0, (const uint8_t*)dc.data, n, m.tmp.as<uint8_t>());
+        m.src = m.tmp.p;
+      } else {
+        add(i, 0, hs_fixed_width(dc.type), dc.data);
+      }
+    }
+    if (!fast_key) {
+      MovedCol& m = add(-1, 3, 8, nullptr);
+      m.tmp.alloc(c, (size_t)n * 8);
+      MovedCol* mm = nullptr;
+      if (!L.single_chunk) {
+        mm = &add(-1, 4, 1, nullptr);
+        mm->tmp.alloc(c, (size_t)n);
+        mm->src = mm->tmp.p;
+      }
+      MovedCol& nk = mv[mv.size() - (mm ? 2 : 1)];
+      nk.src = nk.tmp.p;
+      LAUNCH(c, k_build_nkey, grid1d(n), 256, 0, L, ks, n, 0, (const uint32_t*)nullptr, (const uint8_t*)nullptr,
+             nk.tmp.as<uint64_t>(), mm ? mm->tmp.as<uint8_t>() : (uint8_t*)nullptr);
+    }
+    if (need_srcrow) {
+      MovedCol& m = add(-1, 5, 4, nullptr);
+      m.tmp.alloc(c, (size_t)n * 4);
+      LAUNCH(c, k_iota_u32, grid1d(n), 256, 0, m.tmp.as<uint32_t>(), n);
+      m.src = m.tmp.p;
+    }
+  }
+  MoveSet ms;
+  memset(&ms, 0, sizeof ms);
+  ms.n = (int)mv.size();
+  std::vector<const void*> srcs(mv.size());
+  int key_mv = -1, more_mv = -1, srcrow_mv = -1;
+  for (size_t i = 0; i < mv.size(); i++) {
+    mv[i].a.alloc(c, (size_t)n * mv[i].esize);
+    mv[i].b.alloc(c, (size_t)n * mv[i].esize);
+    ms.esize[i] = mv[i].esize;
+    ms.a[i] = mv[i].a.p;
+    ms.b[i] = mv[i].b.p;
+    srcs[i] = mv[i].src;
+    if (mv[i].role == 3) key_mv = (int)i;
+    if (mv[i].role == 4) more_mv = (int)i;
+    if (mv[i].role == 5) srcrow_mv = (int)i;
+    if (fast_key && mv[i].role == 0 && mv[i].user_col == 0) key_mv = (int)i;
+  }
+  KeySrc key;
+  memset(&key, 0, sizeof key);
+  key.col = key_mv;
+  int key_bits;
+  if (fast_key) {
+    key.mode = cols[0].type == HS_INT64 ? KS_I64 : KS_I32;
+    key.min = h_minmax[0];
+    key_bits = bitlen64(h_minmax[1] - h_minmax[0]);
+  } else {
+    key.mode = KS_U64;
+    key.min = 0;
+    key_bits = L.bits0;
+  }
+
+  // ---- K2: rows -> bucket-contiguous layout
+  {
+    Stage s(c, "bucket_scatter");
+    hs_bucket_scatter(c, srcs.data(), ms, bucket.as<uint16_t>(), n, nbl, d_off.as<uint32_t>());
+  }
+  for (auto& m : mv) m.tmp.release();
+  bucket.release();
+
+  // ---- K3: every bucket sorted on the key
+  {
+    Stage s(c, "bucket_sort");
+    hs_segmented_sort(c, ms, key, key_bits, d_off.as<uint32_t>(), nbl, n);
+  }
+
+  // ---- keys wider than one chunk (strings, wide composites): refine tie groups chunk by chunk
+  if (!L.single_chunk) {
+    Stage s(c, "tie_refine");
+    DBuf flag(c, (size_t)n), rank(c, (size_t)n * 4), head_pos(c, (size_t)n * 4), total(c, 8);
+    DBuf gstart(c, (size_t)(n / 2 + 1) * 4), glen(c, (size_t)(n / 2 + 1) * 4), counter(c, 4);
+    flag.zero();
+    LAUNCH(c, k_mark_starts, grid1d(nbl + 1), 256, 0, d_off.as<uint32_t>(), (int64_t)nbl, flag.as<uint8_t>(), (uint32_t)n);
+    uint64_t* nkey = (uint64_t*)ms.a[key_mv];
+    uint8_t* more = (uint8_t*)ms.a[more_mv];
+    const uint32_t* srcrow = (const uint32_t*)ms.a[srcrow_mv];
+    for (int d = 0; d < 1 << 20; d++) {
+      LAUNCH(c, k_tie_flags, grid1d(n), 256, 0, nkey, more, n, flag.as<uint8_t>());
+      hs_exclusive_scan_flags(c, flag.as<uint8_t>(), rank.as<uint32_t>(), n, total.as<uint64_t>());
+      LAUNCH(c, k_head_positions, grid1d(n), 256, 0, flag.as<uint8_t>(), rank.as<uint32_t>(), n, head_pos.as<uint32_t>());
+      counter.zero();
+      LAUNCH(c, k_group_segments, grid1d(n), 256, 0, head_pos.as<uint32_t>(), total.as<uint64_t>(), (uint32_t)n,
+             gstart.as<uint32_t>(), glen.as<uint32_t>(), counter.as<uint32_t>());
+      uint32_t ngroups = 0;
+      CK(cudaMemcpyAsync(&ngroups, counter.p, 4, cudaMemcpyDeviceToHost, c->stream));
+      hs_sync(c);
+      if (ngroups == 0) break;
+      LAUNCH(c, k_build_nkey, grid1d(n), 256, 0, L, ks, n, d + 1, srcrow, (const uint8_t*)flag.p, nkey, more);
+      hs_segmented_sort_list(c, ms, key, 64, gstart.as<uint32_t>(), glen.as<uint32_t>(), ngroups, n);
+    }
+  }
+
+  // ---- assemble the result (buffer A of every user column becomes the output buffer)
+  {
+    Stage s(c, "finalize");
+    for (auto& m : mv) m.b.release();
+    for (int i = 0; i < ncols; i++) {
+      out[i].type = cols[i].type;
+      out[i].length = n;
+      out[i].null_count = cols[i].validity ? cols[i].null_count : 0;
+    }
+    for (auto& m : mv) {
+      if (m.user_col < 0) continue;
+      OutCol& o = out[m.user_col];
+      if (m.role == 0) {
+        o.data_bytes = n * m.esize;
+        o.data = std::move(m.a);
+      } else {
+        DBuf bits(c, (size_t)((n + 7) / 8));
+        LAUNCH(c, k_bytes_to_bits, grid1d((n + 7) / 8), 256, 0, m.a.as<uint8_t>(), n, bits.as<uint8_t>());
+        if (m.role == 1) o.validity = std::move(bits);
+        else { o.data_bytes = (n + 7) / 8; o.data = std::move(bits); }
+      }
+    }
+    for (int i = 0; i < ncols; i++) {
+      if (!hs_is_varlen(cols[i].type)) continue;
+      OutCol g;
+      DevCol nov;  // values only: validity already travelled as bytes
+      nov.type = cols[i].type; nov.length = n; nov.offsets = cols[i].offsets; nov.data = cols[i].data;
+      nov.data_bytes = cols[i].data_bytes;
+      hs_gather_column(c, nov, (const uint32_t*)ms.a[srcrow_mv], n, g);
+      out[i].offsets = std::move(g.offsets);
+      out[i].data = std::move(g.data);
+      out[i].data_bytes = g.data_bytes;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ concatenation of runs (merge)
+__global__ void __launch_bounds__(256) k_concat_validity(const uint8_t* __restrict__ v, int64_t len, int64_t dst0,
+                                                         uint8_t* __restrict__ out_bytes) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < len; i += stride) out_bytes[dst0 + i] = v ? ((v[i >> 3] >> (i & 7)) & 1) : 1;
+}
+__global__ void __launch_bounds__(256) k_rebase_offsets(const int32_t* __restrict__ off, int64_t len, int32_t add,
+                                                        int32_t* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i <= len; i += stride) out[i] = off[i] + add;
+}
+
+static void concat_runs(hs_ctx* c, std::vector<std::vector<DevCol>>& runs, std::vector<DevCol>& out) {
+  int ncols = (int)runs[0].size();
+  int64_t n = 0;
+  for (auto& r : runs) n += r[0].length;
+  out.resize(ncols);
+  for (int i = 0; i < ncols; i++) {
+    DevCol& o = out[i];
+    o.type = runs[0][i].type;
+    o.length = n;
+    bool any_null = false;
+    int64_t bytes = 0, nulls = 0;
+    for (auto& r : runs) {
+      if (r[i].type != o.type) HS_THROW(HS_EINVAL, "runs differ in schema");
+      any_null |= r[i].validity != nullptr;
+      bytes += r[i].data_bytes;
+      nulls += r[i].validity ? r[i].null_count : 0;
+    }
+    if (hs_is_varlen(o.type) && bytes > 0x7fffffffll) HS_THROW(HS_EUNSUPPORTED, "string column exceeds 2 GiB");
+    if (any_null) {
+      DBuf vb(c, (size_t)(n > 0 ? n : 1));
+      int64_t at = 0;
+      for (auto& r : runs) {
+        if (r[i].length) LAUNCH(c, k_concat_validity, grid1d(r[i].length), 256, 0, r[i].validity, r[i].length, at, vb.as<uint8_t>());
+        at += r[i].length;
+      }
+      o.owned.emplace_back(c, (size_t)((n + 7) / 8));
+      LAUNCH(c, k_bytes_to_bits, grid1d((n + 7) / 8), 256, 0, vb.as<uint8_t>(), n, o.owned.back().as<uint8_t>());
+      o.validity = o.owned.back().as<uint8_t>();
+      o.null_count = nulls;
+    }
+    if (hs_is_varlen(o.type)) {
+      o.owned.emplace_back(c, (size_t)(n + 1) * 4);
+      int32_t* offs = o.owned.back().as<int32_t>();
+      o.owned.emplace_back(c, (size_t)bytes);
+      uint8_t* data = o.owned.back().as<uint8_t>();
+      int64_t at = 0, bat = 0;
+      for (auto& r : runs) {
+        LAUNCH(c, k_rebase_offsets, grid1d(r[i].length + 1), 256, 0, r[i].offsets, r[i].length, (int32_t)bat, offs + at);
+        if (r[i].data_bytes)
+          CK(cudaMemcpyAsync(data + bat, r[i].data, (size_t)r[i].data_bytes, cudaMemcpyDeviceToDevice, c->stream));
+        at += r[i].length;
+        bat += r[i].data_bytes;
+      }
+      o.offsets = offs;
+      o.data = data;
+      o.data_bytes = bytes;
+    } else if (o.type == HS_BOOL) {
+      DBuf vb(c, (size_t)(n > 0 ? n : 1));
+      int64_t at = 0;
+      for (auto& r : runs) {
+        if (r[i].length) LAUNCH(c, k_bits_to_bytes, grid1d(r[i].length), 256, 0, (const uint8_t*)r[i].data, r[i].length, vb.as<uint8_t>() + at);
+        at += r[i].length;
+      }
+      o.owned.emplace_back(c, (size_t)((n + 7) / 8));
+      LAUNCH(c, k_bytes_to_bits, grid1d((n + 7) / 8), 256, 0, vb.as<uint8_t>(), n, o.owned.back().as<uint8_t>());
+      o.data = o.owned.back().p;
+      o.data_bytes = (n + 7) / 8;
+    } else {
+      o.owned.emplace_back(c, (size_t)bytes);
+      uint8_t* data = o.owned.back().as<uint8_t>();
+      int64_t bat = 0;
+      for (auto& r : runs) {
+        if (r[i].data_bytes)
+          CK(cudaMemcpyAsync(data + bat, r[i].data, (size_t)r[i].data_bytes, cudaMemcpyDeviceToDevice, c->stream));
+        bat += r[i].data_bytes;
+      }
+      o.data = data;
+      o.data_bytes = bytes;
+    }
+  }
+}
+
+static void check_build_args(const hs_column* cols, int32_t ncols, int32_t n_indexed, int32_t nb) {
+  if (!cols || ncols <= 0) HS_THROW(HS_EINVAL, "no columns");
+  if (n_indexed <= 0 || n_indexed > ncols) HS_THROW(HS_EINVAL, "n_indexed must be in [1, ncols]");
+  if (n_indexed > HS_MAX_KEYS) HS_THROW(HS_EUNSUPPORTED, "more than %d indexed columns", HS_MAX_KEYS);
+  if (nb <= 0) HS_THROW(HS_EINVAL, "num_buckets must be positive");
+}
+
+extern "C" {
+
+int32_t hs_build_index(hs_ctx* ctx, const hs_column* cols, int32_t ncols, int32_t n_indexed, int32_t num_buckets,
+                       hs_table** out) {
+  API_BEGIN(ctx)
+  if (!out) HS_THROW(HS_EINVAL, "null out");
+  *out = nullptr;
+  check_build_args(cols, ncols, n_indexed, num_buckets);
+  hs_stages_reset(ctx);
+  std::vector<DevCol> dcols;
+  {
+    Stage s(ctx, "h2d");
+    hs_stage_columns(ctx, cols, ncols, dcols);
+  }
+  std::vector<OutCol> ocols;
+  std::vector<int64_t> boff;
+  hs_build_core(ctx, dcols, n_indexed, num_buckets, 0, num_buckets, ocols, boff);
+  Stage s(ctx, "d2h");
+  *out = hs_finish_table(ctx, ocols, dcols[0].length, num_buckets, &boff);
+  API_END(ctx)
+}
+
+int32_t hs_merge_runs(hs_ctx* ctx, const hs_index_view* runs, int32_t nruns, hs_table** out) {
+  API_BEGIN(ctx)
+  if (!out || !runs || nruns <= 0) HS_THROW(HS_EINVAL, "bad arguments");
+  *out = nullptr;
+  hs_stages_reset(ctx);
+  for (int r = 0; r < nruns; r++) {
+    check_build_args(runs[r].cols, runs[r].ncols, runs[r].n_indexed, runs[r].num_buckets);
+    if (runs[r].ncols != runs[0].ncols || runs[r].n_indexed != runs[0].n_indexed ||
+        runs[r].num_buckets != runs[0].num_buckets)
+      HS_THROW(HS_EINVAL, "runs differ in schema or bucket count");
+  }
+  std::vector<std::vector<DevCol>> staged((size_t)nruns);
+  {
+    Stage s(ctx, "h2d");
+    for (int r = 0; r < nruns; r++) hs_stage_columns(ctx, runs[r].cols, runs[r].ncols, staged[r]);
+  }
+  std::vector<DevCol> all;
+  {
+    Stage s(ctx, "concat");
+    concat_runs(ctx, staged, all);
+  }
+  std::vector<OutCol> ocols;
+  std::vector<int64_t> boff;
+  // Re-bucketing the concatenation gives every row the bucket it already had (same hash, same n),
+  // and the per-bucket sort merges the runs: exactly what Spark's repartition + sort does here.
+  hs_build_core(ctx, all, runs[0].n_indexed, runs[0].num_buckets, 0, runs[0].num_buckets, ocols, boff);
+  Stage s(ctx, "d2h");
+  *out = hs_finish_table(ctx, ocols, all[0].length, runs[0].num_buckets, &boff);
+  API_END(ctx)
+}
+
+}  // extern "C"

@@ -1,0 +1,207 @@
+// hs_common.cuh — context, error plumbing, device buffers, column staging.
+// Internal to libhsgpu; the public surface is include/hsgpu.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/hsgpu.h"
+
+#define HS_MAX_KEYS 8
+#define HS_MAX_MOVE 40
+#define HS_NUM_SMS 148  // B200: grids are sized in multiples of this
+
+struct HsError {
+  int32_t status;
+  std::string msg;
+};
+
+#define HS_THROW(st, ...)                                   \
+  do {                                                      \
+    char _b[512];                                           \
+    snprintf(_b, sizeof _b, __VA_ARGS__);                   \
+    throw HsError{(int32_t)(st), std::string(_b)};          \
+  } while (0)
+
+#define CK(call)                                                                          \
+  do {                                                                                    \
+    cudaError_t _e = (call);                                                              \
+    if (_e != cudaSuccess)                                                                \
+      HS_THROW(_e == cudaErrorMemoryAllocation ? HS_ENOMEM : HS_ECUDA, "%s:%d %s: %s",    \
+               __FILE__, __LINE__, #call, cudaGetErrorString(_e));                        \
+  } while (0)
+
+struct StageRec {
+  char name[32];
+  cudaEvent_t e0, e1;
+  int launches;
+};
+
+struct hs_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  int out_loc = HS_MEM_HOST;
+  bool timing = false;
+  std::vector<StageRec> stages;      // of the last call
+  std::vector<cudaEvent_t> ev_free;  // recycled events
+  int cur_stage = -1;
+  int64_t launches = 0;
+  std::multimap<size_t, void*> pinned_free;  // cached pinned host blocks by size
+  std::map<void*, size_t> pinned_size;
+  // multi-GPU (hs_dist.cu)
+  void* nccl_lib = nullptr;
+  void* comm = nullptr;
+  int rank = 0, nranks = 1;
+  int64_t last_xchg_bytes = 0;
+  float last_xchg_ms = 0.f;
+};
+
+// counts a kernel launch (for gpu_launches in bench.py and the per-stage table)
+static inline void hs_count_launch(hs_ctx* c) {
+  c->launches++;
+  if (c->cur_stage >= 0) c->stages[c->cur_stage].launches++;
+}
+#define LAUNCH(ctx, kern, grid, block, smem, ...)                       \
+  do {                                                                  \
+    kern<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);      \
+    hs_count_launch(ctx);                                               \
+    CK(cudaGetLastError());                                             \
+  } while (0)
+
+void hs_stage_begin(hs_ctx* c, const char* name);
+void hs_stage_end(hs_ctx* c);
+void hs_stages_reset(hs_ctx* c);
+struct Stage {
+  hs_ctx* c;
+  Stage(hs_ctx* c_, const char* n) : c(c_) { hs_stage_begin(c, n); }
+  ~Stage() { hs_stage_end(c); }
+};
+
+// stream-ordered device buffer
+struct DBuf {
+  hs_ctx* c = nullptr;
+  void* p = nullptr;
+  size_t bytes = 0;
+  DBuf() {}
+  DBuf(hs_ctx* c_, size_t n) { alloc(c_, n); }
+  DBuf(const DBuf&) = delete;
+  DBuf& operator=(const DBuf&) = delete;
+  DBuf(DBuf&& o) noexcept : c(o.c), p(o.p), bytes(o.bytes) { o.p = nullptr; o.bytes = 0; }
+  DBuf& operator=(DBuf&& o) noexcept {
+    if (this != &o) { release(); c = o.c; p = o.p; bytes = o.bytes; o.p = nullptr; o.bytes = 0; }
+    return *this;
+  }
+  void alloc(hs_ctx* c_, size_t n) {
+    release();
+    c = c_;
+    bytes = n;
+    if (n == 0) n = 16;
+    CK(cudaMallocAsync(&p, n, c->stream));
+  }
+  void zero() { if (p) CK(cudaMemsetAsync(p, 0, bytes ? bytes : 16, c->stream)); }
+  void release() {
+    if (p) cudaFreeAsync(p, c->stream);
+    p = nullptr;
+    bytes = 0;
+  }
+  void* detach() { void* r = p; p = nullptr; bytes = 0; return r; }
+  template <typename T> T* as() const { return (T*)p; }
+  ~DBuf() { release(); }
+};
+
+// A column whose buffers are on the device (borrowed from the caller or staged).
+struct DevCol {
+  int32_t type = 0;
+  int64_t length = 0;
+  int64_t null_count = 0;
+  const uint8_t* validity = nullptr;
+  const int32_t* offsets = nullptr;
+  const void* data = nullptr;
+  int64_t data_bytes = 0;
+  std::vector<DBuf> owned;  // staging copies of host inputs
+  DevCol() {}
+  DevCol(DevCol&&) = default;
+  DevCol& operator=(DevCol&&) = default;
+};
+
+// kernel-side view of a column
+struct KCol {
+  int32_t type;
+  int32_t has_nulls;
+  const uint8_t* validity;
+  const int32_t* offsets;
+  const void* data;
+};
+
+// an output column under construction (device buffers)
+struct OutCol {
+  int32_t type = 0;
+  int64_t length = 0;
+  int64_t null_count = 0;
+  DBuf validity, offsets, data;
+  int64_t data_bytes = 0;
+  OutCol() {}
+  OutCol(OutCol&&) = default;
+  OutCol& operator=(OutCol&&) = default;
+};
+
+static inline int hs_fixed_width(int32_t t) {
+  switch (t) {
+    case HS_INT8: return 1;
+    case HS_INT16: return 2;
+    case HS_INT32: case HS_FLOAT32: return 4;
+    case HS_INT64: case HS_FLOAT64: return 8;
+    default: return 0;
+  }
+}
+static inline bool hs_is_varlen(int32_t t) { return t == HS_UTF8 || t == HS_BINARY; }
+static inline bool hs_type_ok(int32_t t) { return t >= HS_BOOL && t <= HS_BINARY; }
+
+bool hs_is_device_ptr(const void* p);
+void hs_stage_column(hs_ctx* c, const hs_column& in, DevCol& out);
+void hs_stage_columns(hs_ctx* c, const hs_column* in, int n, std::vector<DevCol>& out);
+KCol hs_kcol(const DevCol& d);
+void* hs_pinned_alloc(hs_ctx* c, size_t bytes);
+void hs_pinned_free(hs_ctx* c, void* p);
+hs_table* hs_finish_table(hs_ctx* c, std::vector<OutCol>& cols, int64_t nrows, int32_t num_buckets,
+                          const std::vector<int64_t>* boff);
+void hs_sync(hs_ctx* c);
+
+#define API_BEGIN(ctx)                      \
+  if (!(ctx)) return HS_EINVAL;             \
+  try {                                     \
+    CK(cudaSetDevice((ctx)->device));
+
+#define API_END(ctx)                        \
+  }                                         \
+  catch (const HsError& e) {                \
+    (ctx)->err = e.msg;                     \
+    cudaStreamSynchronize((ctx)->stream);   \
+    cudaGetLastError();                     \
+    return e.status;                        \
+  }                                         \
+  catch (const std::exception& e) {         \
+    (ctx)->err = e.what();                  \
+    return HS_ENOMEM;                       \
+  }                                         \
+  return HS_OK;
+
+// ---- shared device helpers -------------------------------------------------
+__device__ __forceinline__ bool kvalid(const uint8_t* v, int64_t i) {
+  return v == nullptr || ((v[i >> 3] >> (i & 7)) & 1);
+}
+__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
+
+// primitives implemented in hs_scan.cu / hs_gather.cu
+// out[i] = sum_{j<i} in[j] (out may alias in); returns nothing, total written to *d_total (device, u64) if non-null
+void hs_exclusive_scan_u32(hs_ctx* c, const uint32_t* in, uint32_t* out, int64_t n, uint64_t* d_total);
+void hs_exclusive_scan_flags(hs_ctx* c, const uint8_t* flags, uint32_t* out, int64_t n, uint64_t* d_total);
+// gather rows idx[0..m) of `src` into a new column
+void hs_gather_column(hs_ctx* c, const DevCol& src, const uint32_t* idx, int64_t m, OutCol& out);
+void hs_copy_column(hs_ctx* c, const DevCol& src, OutCol& out);

@@ -1,0 +1,253 @@
+// hs_filter.cu — K7: predicate-evaluating scan over an index.
+// Executes the plan FilterIndexRule.apply produces (HS/index/rules/FilterIndexRule.scala:43-85): rows of the
+// index for which the predicate is TRUE (SQL three-valued logic), projected to the requested columns.
+// `first indexed column = literal` on a single-column index prunes the scan to the literal's bucket.
+#include "hs_keys.cuh"
+#include "hs_kernels.h"
+
+#define HS_MAX_TERMS 32
+
+struct KTerm {
+  int32_t op, col;
+  int64_t lit_i64;
+  double lit_f64;
+  int32_t lit_off, lit_len;  // into the literal byte pool
+};
+struct KPred {
+  int32_t nterms;
+  KTerm t[HS_MAX_TERMS];
+  const uint8_t* pool;
+};
+struct KCols {
+  KCol c[HS_MAX_MOVE];
+};
+
+__device__ __forceinline__ int cmp_f64_total(double a, double b) {
+  bool an = a != a, bn = b != b;
+  if (an || bn) return (int)an - (int)bn;
+  return (a > b) - (a < b);
+}
+
+__device__ __forceinline__ void eval_leaf(const KCol& c, int64_t i, const KTerm& t, const uint8_t* pool, bool* known,
+                                          bool* val) {
+  bool valid = !c.has_nulls || kvalid(c.validity, i);
+  if (t.op == HS_PRED_IS_NULL) { *known = true; *val = !valid; return; }
+  if (t.op == HS_PRED_IS_NOT_NULL) { *known = true; *val = valid; return; }
+  if (!valid) { *known = false; *val = false; return; }
+  int cmp = 0;
+  switch (c.type) {
+    case HS_BOOL: { int64_t x = (((const uint8_t*)c.data)[i >> 3] >> (i & 7)) & 1; cmp = (x > t.lit_i64) - (x < t.lit_i64); break; }
+    case HS_INT8: { int64_t x = ((const int8_t*)c.data)[i]; cmp = (x > t.lit_i64) - (x < t.lit_i64); break; }
+    case HS_INT16: { int64_t x = ((const int16_t*)c.data)[i]; cmp = (x > t.lit_i64) - (x < t.lit_i64); break; }
+    case HS_INT32: { int64_t x = ((const int32_t*)c.data)[i]; cmp = (x > t.lit_i64) - (x < t.lit_i64); break; }
+    case HS_INT64: { int64_t x = ((const int64_t*)c.data)[i]; cmp = (x > t.lit_i64) - (x < t.lit_i64); break; }
+    case HS_FLOAT32: cmp = cmp_f64_total((double)((const float*)c.data)[i], t.lit_f64); break;
+    case HS_FLOAT64: cmp = cmp_f64_total(((const double*)c.data)[i], t.lit_f64); break;
+    case HS_UTF8:
+    case HS_BINARY: {
+      int s = c.offsets[i];
+      cmp = cmp_u8str((const uint8_t*)c.data + s, c.offsets[i + 1] - s, pool + t.lit_off, t.lit_len);
+      break;
+    }
+  }
+  *known = true;
+  switch (t.op) {
+    case HS_PRED_EQ: *val = cmp == 0; break;
+    case HS_PRED_NE: *val = cmp != 0; break;
+    case HS_PRED_LT: *val = cmp < 0; break;
+    case HS_PRED_LE: *val = cmp <= 0; break;
+    case HS_PRED_GT: *val = cmp > 0; break;
+    case HS_PRED_GE: *val = cmp >= 0; break;
+    default: *val = false; break;
+  }
+}
+
+// rows [row0, row0 + n): flag[i - row0] = predicate is TRUE. The stack is two 32-bit masks.
+__global__ void __launch_bounds__(256) k_filter_eval(const __grid_constant__ KCols cols,
+                                                     const __grid_constant__ KPred pred, int64_t row0, int64_t n,
+                                                     uint8_t* __restrict__ flag) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    uint32_t kn = 0, vl = 0;
+    int sp = 0;
+    for (int t = 0; t < pred.nterms; t++) {
+      const KTerm& tm = pred.t[t];
+      if (tm.op == HS_PRED_AND || tm.op == HS_PRED_OR) {
+        bool kb = (kn >> (sp - 1)) & 1, vb = (vl >> (sp - 1)) & 1;
+        bool ka = (kn >> (sp - 2)) & 1, va = (vl >> (sp - 2)) & 1;
+        bool k, v;
+        if (tm.op == HS_PRED_AND) {
+          if ((ka && !va) || (kb && !vb)) { k = true; v = false; }
+          else if (ka && kb) { k = true; v = true; }
+          else { k = false; v = false; }
+        } else {
+          if ((ka && va) || (kb && vb)) { k = true; v = true; }
+          else if (ka && kb) { k = true; v = false; }
+          else { k = false; v = false; }
+        }
+        sp -= 2;
+        kn = (kn & ~(3u << sp)) | ((uint32_t)k << sp);
+        vl = (vl & ~(3u << sp)) | ((uint32_t)v << sp);
+        sp++;
+      } else if (tm.op == HS_PRED_NOT) {
+        if ((kn >> (sp - 1)) & 1) vl ^= 1u << (sp - 1);
+      } else {
+        bool k, v;
+        eval_leaf(cols.c[tm.col], row0 + i, tm, pred.pool, &k, &v);
+        kn = (kn & ~(1u << sp)) | ((uint32_t)k << sp);
+        vl = (vl & ~(1u << sp)) | ((uint32_t)v << sp);
+        sp++;
+      }
+    }
+    flag[i] = (kn & 1u) && (vl & 1u);
+  }
+}
+
+__global__ void __launch_bounds__(256) k_filter_compact(const uint8_t* __restrict__ flag, const uint32_t* __restrict__ pos,
+                                                        int64_t row0, int64_t n, uint32_t* __restrict__ idx) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride)
+    if (flag[i]) idx[pos[i]] = (uint32_t)(row0 + i);
+}
+
+// host copy of the Murmur3 of hs_keys.cuh for one literal (bucket pruning only)
+static uint32_t h_rotl(uint32_t x, int r) { return (x << r) | (x >> (32 - r)); }
+static uint32_t h_k1(uint32_t k) { k *= 0xcc9e2d51u; k = h_rotl(k, 15); k *= 0x1b873593u; return k; }
+static uint32_t h_h1(uint32_t h, uint32_t k) { h ^= k; h = h_rotl(h, 13); return h * 5u + 0xe6546b64u; }
+static uint32_t h_fmix(uint32_t h, uint32_t len) {
+  h ^= len; h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16; return h;
+}
+static bool literal_bucket(int32_t type, const hs_pred_term& t, int32_t nb, int32_t* bucket) {
+  uint32_t h;
+  switch (type) {
+    case HS_INT8: case HS_INT16: case HS_INT32: {
+      int64_t lo = type == HS_INT8 ? -128 : type == HS_INT16 ? -32768 : -2147483648ll;
+      int64_t hi = type == HS_INT8 ? 127 : type == HS_INT16 ? 32767 : 2147483647ll;
+      if (t.lit_i64 < lo || t.lit_i64 > hi) return false;
+      h = h_fmix(h_h1(42u, h_k1((uint32_t)(int32_t)t.lit_i64)), 4);
+      break;
+    }
+    case HS_INT64: {
+      uint64_t v = (uint64_t)t.lit_i64;
+      h = h_h1(42u, h_k1((uint32_t)v));
+      h = h_fmix(h_h1(h, h_k1((uint32_t)(v >> 32))), 8);
+      break;
+    }
+    case HS_UTF8: case HS_BINARY: {
+      if (!t.lit_bytes && t.lit_len) return false;
+      h = 42u;
+      int n = t.lit_len, nw = n & ~3;
+      for (int i = 0; i < nw; i += 4) { uint32_t w; memcpy(&w, t.lit_bytes + i, 4); h = h_h1(h, h_k1(w)); }
+      for (int i = nw; i < n; i++) h = h_h1(h, h_k1((uint32_t)(int32_t)(int8_t)t.lit_bytes[i]));
+      h = h_fmix(h, (uint32_t)n);
+      break;
+    }
+    default: return false;
+  }
+  int32_t r = (int32_t)h % nb;
+  *bucket = r < 0 ? r + nb : r;
+  return true;
+}
+
+static unsigned fgrid(int64_t n) {
+  int64_t g = (n + 255) / 256, cap = (int64_t)HS_NUM_SMS * 16;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (unsigned)g;
+}
+
+extern "C" int32_t hs_filter_scan(hs_ctx* ctx, const hs_index_view* index, const hs_predicate* pred,
+                                  const int32_t* out_cols, int32_t n_out, hs_table** out) {
+  API_BEGIN(ctx)
+  if (!out) HS_THROW(HS_EINVAL, "null out");
+  *out = nullptr;
+  if (!index || !index->cols || index->ncols <= 0) HS_THROW(HS_EINVAL, "malformed index view");
+  if (index->ncols > HS_MAX_MOVE) HS_THROW(HS_EUNSUPPORTED, "more than %d columns", HS_MAX_MOVE);
+  if (!pred || !pred->terms || pred->nterms <= 0 || pred->nterms > HS_MAX_TERMS)
+    HS_THROW(HS_EINVAL, "predicate must have 1..%d terms", HS_MAX_TERMS);
+  if (n_out <= 0 || !out_cols) HS_THROW(HS_EINVAL, "no output columns");
+  for (int i = 0; i < n_out; i++)
+    if (out_cols[i] < 0 || out_cols[i] >= index->ncols) HS_THROW(HS_EINVAL, "output column out of range");
+  // validate the postfix program
+  int depth = 0;
+  size_t pool_bytes = 0;
+  for (int t = 0; t < pred->nterms; t++) {
+    const hs_pred_term& tm = pred->terms[t];
+    if (tm.op == HS_PRED_AND || tm.op == HS_PRED_OR) { if (depth < 2) HS_THROW(HS_EINVAL, "malformed predicate"); depth--; }
+    else if (tm.op == HS_PRED_NOT) { if (depth < 1) HS_THROW(HS_EINVAL, "malformed predicate"); }
+    else if (tm.op >= HS_PRED_EQ && tm.op <= HS_PRED_IS_NOT_NULL) {
+      if (tm.col < 0 || tm.col >= index->ncols) HS_THROW(HS_EINVAL, "predicate column out of range");
+      if (++depth > 16) HS_THROW(HS_EINVAL, "predicate too deep");
+      if (hs_is_varlen(index->cols[tm.col].type) && tm.op <= HS_PRED_GE) {
+        if (tm.lit_len < 0 || (tm.lit_len > 0 && !tm.lit_bytes)) HS_THROW(HS_EINVAL, "string literal missing");
+        pool_bytes += (size_t)tm.lit_len;
+      }
+    } else HS_THROW(HS_EINVAL, "unknown predicate op %d", tm.op);
+  }
+  if (depth != 1) HS_THROW(HS_EINVAL, "malformed predicate");
+  hs_stages_reset(ctx);
+  std::vector<DevCol> cols;
+  {
+    Stage s(ctx, "h2d");
+    hs_stage_columns(ctx, index->cols, index->ncols, cols);
+  }
+  const int64_t nrows = cols[0].length;
+  KCols kc;
+  memset(&kc, 0, sizeof kc);
+  for (int i = 0; i < index->ncols; i++) kc.c[i] = hs_kcol(cols[i]);
+  KPred kp;
+  memset(&kp, 0, sizeof kp);
+  kp.nterms = pred->nterms;
+  std::vector<uint8_t> pool(pool_bytes + 1);
+  size_t at = 0;
+  for (int t = 0; t < pred->nterms; t++) {
+    const hs_pred_term& tm = pred->terms[t];
+    kp.t[t].op = tm.op;
+    kp.t[t].col = tm.col;
+    kp.t[t].lit_i64 = tm.lit_i64;
+    kp.t[t].lit_f64 = tm.lit_f64;
+    if (tm.op <= HS_PRED_GE && hs_is_varlen(index->cols[tm.col].type)) {
+      kp.t[t].lit_off = (int32_t)at;
+      kp.t[t].lit_len = tm.lit_len;
+      if (tm.lit_len) memcpy(pool.data() + at, tm.lit_bytes, (size_t)tm.lit_len);
+      at += (size_t)tm.lit_len;
+    }
+  }
+  DBuf dpool(ctx, pool.size());
+  CK(cudaMemcpyAsync(dpool.p, pool.data(), pool.size(), cudaMemcpyHostToDevice, ctx->stream));
+  kp.pool = dpool.as<uint8_t>();
+
+  // bucket pruning: key = literal on a single-column index scans one bucket only
+  int64_t row0 = 0, n = nrows;
+  if (pred->nterms == 1 && pred->terms[0].op == HS_PRED_EQ && pred->terms[0].col == 0 && index->n_indexed == 1 &&
+      index->num_buckets > 0 && index->bucket_offsets) {
+    int32_t b;
+    if (literal_bucket(index->cols[0].type, pred->terms[0], index->num_buckets, &b)) {
+      row0 = index->bucket_offsets[b];
+      n = index->bucket_offsets[b + 1] - row0;
+      if (row0 < 0 || n < 0 || row0 + n > nrows) HS_THROW(HS_EINVAL, "bad bucket_offsets");
+    }
+  }
+  DBuf flag(ctx, (size_t)n), pos(ctx, (size_t)n * 4), total(ctx, 8);
+  uint64_t h_total = 0;
+  {
+    Stage s(ctx, "filter_eval");
+    if (n > 0) LAUNCH(ctx, k_filter_eval, fgrid(n), 256, 0, kc, kp, row0, n, flag.as<uint8_t>());
+    hs_exclusive_scan_flags(ctx, flag.as<uint8_t>(), pos.as<uint32_t>(), n, total.as<uint64_t>());
+    CK(cudaMemcpyAsync(&h_total, total.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    hs_sync(ctx);
+  }
+  const int64_t m = (int64_t)h_total;
+  DBuf idx(ctx, (size_t)m * 4);
+  std::vector<OutCol> ocols((size_t)n_out);
+  {
+    Stage s(ctx, "filter_gather");
+    if (n > 0 && m > 0) LAUNCH(ctx, k_filter_compact, fgrid(n), 256, 0, flag.as<uint8_t>(), pos.as<uint32_t>(), row0, n, idx.as<uint32_t>());
+    for (int i = 0; i < n_out; i++) hs_gather_column(ctx, cols[out_cols[i]], idx.as<uint32_t>(), m, ocols[i]);
+  }
+  Stage s(ctx, "d2h");
+  *out = hs_finish_table(ctx, ocols, m, 0, nullptr);
+  API_END(ctx)
+}

@@ -1,0 +1,230 @@
+// hs_hash.cu — K1: Spark-compatible Murmur3 bucket ids, the per-bucket histogram
+// (warp-aggregated shared-memory atomics) and the per-column key ranges the sort uses.
+// Stands in for HashPartitioning.partitionIdExpression = Pmod(Murmur3Hash(cols, 42), n)
+// reached from df.repartition(numBuckets, indexedCols) at
+// HS/actions/CreateActionBase.scala:129-130.
+#include "hs_keys.cuh"
+#include "hs_kernels.h"
+
+#define HASH_THREADS 256
+
+__device__ __forceinline__ void hist_add(uint32_t* hist, uint32_t b, bool valid) {
+  unsigned active = __ballot_sync(0xffffffffu, valid);
+  if (!valid) return;
+  unsigned peers = __match_any_sync(active, b);
+  if ((int)lane_id() == __ffs(peers) - 1) atomicAdd(&hist[b], (uint32_t)__popc(peers));
+}
+
+__device__ __forceinline__ void minmax_flush(uint64_t mn, uint64_t mx, uint64_t* g) {
+#pragma unroll
+  for (int d = 16; d; d >>= 1) {
+    uint64_t a = __shfl_xor_sync(0xffffffffu, mn, d), b = __shfl_xor_sync(0xffffffffu, mx, d);
+    mn = a < mn ? a : mn;
+    mx = b > mx ? b : mx;
+  }
+  if (lane_id() == 0 && mn <= mx) {
+    atomicMin((unsigned long long*)&g[0], (unsigned long long)mn);
+    atomicMax((unsigned long long*)&g[1], (unsigned long long)mx);
+  }
+}
+
+// MODE 0: out32 = raw hash; 1: out32 = bucket; 2: out16 = bucket, hist[nb] += 1, minmax per fixed key
+template <int MODE>
+__global__ void __launch_bounds__(HASH_THREADS) k_hash_generic(KeySpec ks, int64_t n, int32_t nb, int32_t blo,
+                                                               int32_t nbl, int32_t* __restrict__ out32,
+                                                               uint16_t* __restrict__ out16,
+                                                               uint32_t* __restrict__ g_hist, int smem_hist,
+                                                               uint64_t* __restrict__ g_minmax) {
+  extern __shared__ uint32_t s_hist[];
+  uint32_t* hist = g_hist;
+  if (MODE == 2 && smem_hist) {
+    for (int b = threadIdx.x; b < nbl; b += HASH_THREADS) s_hist[b] = 0;
+    __syncthreads();
+    hist = s_hist;
+  }
+  uint64_t mn[HS_MAX_KEYS], mx[HS_MAX_KEYS];
+  if (MODE == 2) {
+#pragma unroll
+    for (int k = 0; k < HS_MAX_KEYS; k++) { mn[k] = ~0ull; mx[k] = 0; }
+  }
+  int64_t stride = (int64_t)gridDim.x * HASH_THREADS;
+  for (int64_t base = (int64_t)blockIdx.x * HASH_THREADS; base < n; base += stride) {
+    int64_t i = base + threadIdx.x;
+    bool valid = i < n;
+    uint32_t h = valid ? mm_hash_row(ks, i) : 0;
+    if (MODE == 0) {
+      if (valid) out32[i] = (int32_t)h;
+    } else {
+      int32_t b = pmod_i32((int32_t)h, nb);
+      if (MODE == 1) {
+        if (valid) out32[i] = b;
+      } else {
+        b -= blo;
+        if (valid && (b < 0 || b >= nbl)) {  // a row that does not belong to this rank's bucket range
+          atomicAdd((unsigned long long*)&g_minmax[2 * HS_MAX_KEYS], 1ull);
+          b = 0;
+        }
+        if (valid) out16[i] = (uint16_t)b;
+        hist_add(hist, (uint32_t)b, valid);
+        if (valid) {
+#pragma unroll
+          for (int k = 0; k < HS_MAX_KEYS; k++) {
+            if (k < ks.nkeys) {
+              const KCol& c = ks.k[k];
+              if (c.type != HS_UTF8 && c.type != HS_BINARY && (!c.has_nulls || kvalid(c.validity, i))) {
+                uint64_t m = omap_cell(c, i);
+                mn[k] = m < mn[k] ? m : mn[k];
+                mx[k] = m > mx[k] ? m : mx[k];
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+  if (MODE == 2) {
+#pragma unroll
+    for (int k = 0; k < HS_MAX_KEYS; k++)
+      if (k < ks.nkeys) minmax_flush(mn[k], mx[k], g_minmax + 2 * k);
+    if (smem_hist) {
+      __syncthreads();
+      for (int b = threadIdx.x; b < nbl; b += HASH_THREADS) {
+        uint32_t v = s_hist[b];
+        if (v) atomicAdd(&g_hist[b], v);
+      }
+    }
+  }
+}
+
+// Fast path: one non-null INT64 key. Each thread hashes two rows from one 128-bit load and
+// stores both 16-bit bucket ids with one 32-bit store.
+__global__ void __launch_bounds__(HASH_THREADS) k_hash_i64x2(const uint64_t* __restrict__ keys, int64_t n,
+                                                             int32_t nb, uint16_t* __restrict__ out16,
+                                                             uint32_t* __restrict__ g_hist,
+                                                             uint64_t* __restrict__ g_minmax) {
+  extern __shared__ uint32_t s_hist[];
+  for (int b = threadIdx.x; b < nb; b += HASH_THREADS) s_hist[b] = 0;
+  __syncthreads();
+  uint64_t mn = ~0ull, mx = 0;
+  int64_t npairs = n >> 1;
+  int64_t stride = (int64_t)gridDim.x * HASH_THREADS;
+  const ulonglong2* k2 = (const ulonglong2*)keys;
+  for (int64_t base = (int64_t)blockIdx.x * HASH_THREADS; base < npairs; base += stride) {
+    int64_t p = base + threadIdx.x;
+    bool valid = p < npairs;
+    uint32_t b0 = 0, b1 = 0;
+    if (valid) {
+      ulonglong2 v;
+      asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(k2 + p));
+      b0 = (uint32_t)pmod_i32((int32_t)mm_hash_long(v.x, 42u), nb);
+      b1 = (uint32_t)pmod_i32((int32_t)mm_hash_long(v.y, 42u), nb);
+      ((uint32_t*)out16)[p] = b0 | (b1 << 16);
+      uint64_t m0 = v.x ^ 0x8000000000000000ull, m1 = v.y ^ 0x8000000000000000ull;
+      uint64_t lo = m0 < m1 ? m0 : m1, hi = m0 < m1 ? m1 : m0;
+      mn = lo < mn ? lo : mn;
+      mx = hi > mx ? hi : mx;
+    }
+    hist_add(s_hist, b0, valid);
+    hist_add(s_hist, b1, valid);
+  }
+  if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+    uint64_t v = keys[n - 1];
+    uint32_t b = (uint32_t)pmod_i32((int32_t)mm_hash_long(v, 42u), nb);
+    out16[n - 1] = (uint16_t)b;
+    atomicAdd(&s_hist[b], 1u);
+    uint64_t m = v ^ 0x8000000000000000ull;
+    mn = m < mn ? m : mn;
+    mx = m > mx ? m : mx;
+  }
+  minmax_flush(mn, mx, g_minmax);
+  __syncthreads();
+  for (int b = threadIdx.x; b < nb; b += HASH_THREADS) {
+    uint32_t v = s_hist[b];
+    if (v) atomicAdd(&g_hist[b], v);
+  }
+}
+
+static unsigned hash_grid(int64_t n) {
+  int64_t g = (n + HASH_THREADS - 1) / HASH_THREADS;
+  int64_t cap = (int64_t)HS_NUM_SMS * 8;  // 8 resident CTAs of 256 threads per SM
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (unsigned)g;
+}
+
+KeySpec hs_make_keyspec(const std::vector<DevCol>& cols, int nkeys) {
+  if (nkeys <= 0 || nkeys > HS_MAX_KEYS) HS_THROW(HS_EINVAL, "between 1 and %d key columns are supported", HS_MAX_KEYS);
+  KeySpec ks;
+  memset(&ks, 0, sizeof ks);
+  ks.nkeys = nkeys;
+  for (int k = 0; k < nkeys; k++) ks.k[k] = hs_kcol(cols[k]);
+  return ks;
+}
+
+void hs_hash_to_i32(hs_ctx* c, const KeySpec& ks, int64_t n, int32_t nb, int32_t* d_out) {
+  if (n == 0) return;
+  if (nb <= 0) LAUNCH(c, k_hash_generic<0>, hash_grid(n), HASH_THREADS, 0, ks, n, 1, 0, 1, d_out, (uint16_t*)nullptr,
+                      (uint32_t*)nullptr, 0, (uint64_t*)nullptr);
+  else LAUNCH(c, k_hash_generic<1>, hash_grid(n), HASH_THREADS, 0, ks, n, nb, 0, nb, d_out, (uint16_t*)nullptr,
+              (uint32_t*)nullptr, 0, (uint64_t*)nullptr);
+}
+
+// Local bucket ids (bucket - blo, u16) + histogram over the nbl buckets [blo, blo + nbl) + min/max of
+// every fixed-width key column. d_hist: nbl u32 (zeroed here); d_minmax: 2*HS_MAX_KEYS + 1 u64
+// (initialised here; the last word counts rows outside the bucket range).
+void hs_hash_bucket_hist(hs_ctx* c, const KeySpec& ks, const std::vector<DevCol>& cols, int64_t n, int32_t nb,
+                         int32_t blo, int32_t nbl, uint16_t* d_bucket, uint32_t* d_hist, uint64_t* d_minmax) {
+  if (nbl > 65536) HS_THROW(HS_EUNSUPPORTED, "more than 65536 buckets on one GPU");
+  CK(cudaMemsetAsync(d_hist, 0, (size_t)nbl * 4, c->stream));
+  uint64_t init[2 * HS_MAX_KEYS + 1];
+  init[2 * HS_MAX_KEYS] = 0;
+  for (int k = 0; k < HS_MAX_KEYS; k++) { init[2 * k] = ~0ull; init[2 * k + 1] = 0; }
+  CK(cudaMemcpyAsync(d_minmax, init, sizeof init, cudaMemcpyHostToDevice, c->stream));
+  if (n == 0) return;
+  size_t smem = (size_t)nbl * 4;
+  bool fast = blo == 0 && nbl == nb && ks.nkeys == 1 && ks.k[0].type == HS_INT64 && !ks.k[0].has_nulls &&
+              (((uintptr_t)ks.k[0].data) & 15) == 0 && (((uintptr_t)d_bucket) & 3) == 0 && smem <= 48 * 1024;
+  if (fast) {
+    LAUNCH(c, k_hash_i64x2, hash_grid((n + 1) / 2), HASH_THREADS, smem, (const uint64_t*)ks.k[0].data, n, nb,
+           d_bucket, d_hist, d_minmax);
+    return;
+  }
+  int smem_hist = smem <= 160 * 1024;
+  if (smem_hist && smem > 48 * 1024)
+    CK(cudaFuncSetAttribute(k_hash_generic<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  LAUNCH(c, k_hash_generic<2>, hash_grid(n), HASH_THREADS, smem_hist ? smem : 0, ks, n, nb, blo, nbl, (int32_t*)nullptr,
+         d_bucket, d_hist, smem_hist, d_minmax);
+}
+
+extern "C" {
+
+static int32_t hash_api(hs_ctx* ctx, const hs_column* keys, int32_t nkeys, int32_t nb, int32_t* out) {
+  API_BEGIN(ctx)
+  if (!keys || !out) HS_THROW(HS_EINVAL, "null argument");
+  hs_stages_reset(ctx);
+  std::vector<DevCol> cols;
+  hs_stage_columns(ctx, keys, nkeys, cols);
+  KeySpec ks = hs_make_keyspec(cols, nkeys);
+  int64_t n = cols[0].length;
+  bool dev_out = hs_is_device_ptr(out);
+  DBuf tmp;
+  int32_t* d_out = out;
+  if (!dev_out) { tmp.alloc(ctx, (size_t)n * 4); d_out = tmp.as<int32_t>(); }
+  {
+    Stage s(ctx, "hash");
+    hs_hash_to_i32(ctx, ks, n, nb, d_out);
+  }
+  if (!dev_out && n) CK(cudaMemcpyAsync(out, d_out, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  hs_sync(ctx);
+  API_END(ctx)
+}
+
+int32_t hs_hash_bucket(hs_ctx* ctx, const hs_column* keys, int32_t nkeys, int32_t num_buckets, int32_t* out) {
+  if (ctx && num_buckets <= 0) { ctx->err = "num_buckets must be positive"; return HS_EINVAL; }
+  return hash_api(ctx, keys, nkeys, num_buckets, out);
+}
+int32_t hs_hash_rows(hs_ctx* ctx, const hs_column* keys, int32_t nkeys, int32_t* out) {
+  return hash_api(ctx, keys, nkeys, 0, out);
+}
+
+}  // extern "C"

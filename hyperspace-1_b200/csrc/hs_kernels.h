@@ -1,0 +1,44 @@
+// hs_kernels.h — internal entry points between the translation units of libhsgpu.
+#pragma once
+#include "hs_common.cuh"
+
+struct KeySpec;
+struct KeyLayout;
+
+KeySpec hs_make_keyspec(const std::vector<DevCol>& cols, int nkeys);
+void hs_hash_to_i32(hs_ctx* c, const KeySpec& ks, int64_t n, int32_t nb, int32_t* d_out);
+void hs_hash_bucket_hist(hs_ctx* c, const KeySpec& ks, const std::vector<DevCol>& cols, int64_t n, int32_t nb,
+                         int32_t blo, int32_t nbl, uint16_t* d_bucket, uint32_t* d_hist, uint64_t* d_minmax);
+// the build over staged device columns; rows must hash into buckets [blo, blo + nbl)
+void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t nb, int32_t blo, int32_t nbl,
+                   std::vector<OutCol>& out, std::vector<int64_t>& boff);
+void hs_offsets_to_device(hs_ctx* c, const int64_t* boff, int32_t nb, int64_t nrows, DBuf& out);
+
+// ---- the row mover / segmented sort (hs_sort.cu) ----
+struct MoveSet {           // the columns that travel together; all fixed width
+  int32_t n;
+  int32_t esize[HS_MAX_MOVE];
+  void* a[HS_MAX_MOVE];    // buffer A (holds the result at the end)
+  void* b[HS_MAX_MOVE];    // buffer B (ping-pong)
+};
+// how kernels read the 64-bit sort key of a row out of the moved columns
+struct KeySrc {
+  int32_t col;             // index into MoveSet
+  int32_t mode;            // 0: u64 as is, 1: int64 (sign flip, minus min), 2: int32 (sign extend, flip, minus min)
+  uint64_t min;
+};
+#define KS_U64 0
+#define KS_I64 1
+#define KS_I32 2
+
+// Scatter rows from the caller's column buffers (src[i], element sizes as in ms) into bucket-contiguous
+// order in ms.a, given u16 bucket ids and host-known bucket offsets.
+void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, const uint16_t* d_bucket, int64_t n,
+                       int32_t nb, const uint32_t* d_bucket_off);
+// Sort every segment [seg_off[s], seg_off[s+1]) of ms.a by the key; result in ms.a. key_bits = significant
+// low bits of the key. d_seg_off: device u32[nseg+1].
+void hs_segmented_sort(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_seg_off,
+                       int64_t nseg, int64_t n);
+// Same, for an explicit device list of segments (start,len), all with the same key_bits.
+void hs_segmented_sort_list(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_start,
+                            const uint32_t* d_len, int64_t nseg, int64_t n);

@@ -1,0 +1,145 @@
+"""K5-K7 parity: join and filter results equal the oracle's row multiset (the reference's verifyIndexUsage
+invariant, E2EHyperspaceRulesTest.scala:1004-1019: indexed result == un-indexed result)."""
+import numpy as np
+import pyarrow as pa
+import pytest
+
+import parity
+from fixtures import EMPLOYEES, departments_table, employees_table, lineitem, orders, string_keys
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx(hs):
+    c = hs.Context(0)
+    yield c
+    c.close()
+
+
+def _oracle_join(oracle, lcols, loff, rcols, roff, nk, lout, rout):
+    li, ri, woff = oracle.join(lcols, rcols, nk, loff, roff)
+    want = [lcols[i].take(pa.array(li)) for i in lout] + [rcols[i].take(pa.array(ri)) for i in rout]
+    return want, woff
+
+
+def test_quickstart_join_and_filter(ctx):
+    d, e = departments_table(), employees_table()
+    dg, doff = ctx.build_index([d["deptId"], d["deptName"]], 1, 200)
+    eg, eoff = ctx.build_index([e["deptId"], e["empName"]], 1, 200)
+    jg, joff = ctx.join(eg, eoff, dg, doff, 1, [1], [1])
+    dept = {10: "Accounting", 20: "Research", 30: "Sales"}
+    assert sorted(zip(jg[0].to_pylist(), jg[1].to_pylist())) == sorted((n, dept[k]) for _, n, k in EMPLOYEES)
+    assert joff[-1] == 14
+    fg = ctx.filter_scan(dg, 1, doff, [("eq", 0, 20)], [1])
+    assert fg[0].to_pylist() == ["Research"]
+
+
+@pytest.mark.parametrize("n_orders,nb", [(2000, 200), (60000, 200), (60000, 3)])
+def test_lineitem_orders_join(ctx, oracle, n_orders, nb):
+    lcols, keys = lineitem(n_orders)
+    ocols = orders(keys)
+    lg, loff = ctx.build_index(lcols, 1, nb)
+    og, ooff = ctx.build_index(ocols, 1, nb)
+    jg, joff = ctx.join(lg, loff, og, ooff, 1, [0, 1, 2], [1])
+    assert len(jg[0]) == len(lcols[0])  # every lineitem row has exactly one order
+    want, woff = _oracle_join(oracle, lg, loff, og, ooff, 1, [0, 1, 2], [1])
+    parity.assert_same_multiset(jg, want, joff, woff, "lineitem x orders")
+
+
+def test_join_many_to_many_nulls_and_misses(ctx, oracle):
+    rng = np.random.default_rng(21)
+    nl, nr = 40000, 30000
+    lk = pa.array(rng.integers(0, 5000, size=nl), mask=rng.random(nl) < 0.05)
+    rk = pa.array(rng.integers(2500, 7500, size=nr), mask=rng.random(nr) < 0.05)
+    lcols, rcols = [lk, pa.array(np.arange(nl))], [rk, pa.array(np.arange(nr) * 1.5)]
+    lg, loff = ctx.build_index(lcols, 1, 16)
+    rg, roff = ctx.build_index(rcols, 1, 16)
+    jg, joff = ctx.join(lg, loff, rg, roff, 1, [0, 1], [0, 1])
+    want, woff = _oracle_join(oracle, lg, loff, rg, roff, 1, [0, 1], [0, 1])
+    assert len(want[0]) > nl  # really many-to-many
+    parity.assert_same_multiset(jg, want, joff, woff, "many-to-many")
+
+
+def test_join_on_string_and_composite_keys(ctx, oracle):
+    s, v = string_keys(5000)
+    idx = np.random.default_rng(1).integers(0, 5000, size=12000)
+    ls = s.take(pa.array(idx))
+    lg, loff = ctx.build_index([ls, pa.array(np.arange(12000))], 1, 8)
+    rg, roff = ctx.build_index([s, v], 1, 8)
+    jg, joff = ctx.join(lg, loff, rg, roff, 1, [0, 1], [1])
+    want, woff = _oracle_join(oracle, lg, loff, rg, roff, 1, [0, 1], [1])
+    parity.assert_same_multiset(jg, want, joff, woff, "string join")
+    rng = np.random.default_rng(2)
+    mk = lambda n: [pa.array(rng.integers(0, 30, size=n).astype(np.int32)), pa.array(rng.integers(0, 40, size=n)),
+                    pa.array(rng.random(n))]
+    l, r = mk(20000), mk(3000)
+    lg, loff = ctx.build_index(l, 2, 32)
+    rg, roff = ctx.build_index(r, 2, 32)
+    jg, joff = ctx.join(lg, loff, rg, roff, 2, [0, 1, 2], [2])
+    want, woff = _oracle_join(oracle, lg, loff, rg, roff, 2, [0, 1, 2], [2])
+    parity.assert_same_multiset(jg, want, joff, woff, "composite join")
+
+
+def test_join_after_incremental_refresh_two_runs_per_bucket(ctx, oracle):
+    lcols, keys = lineitem(20000)
+    n = len(lcols[0])
+    a = [c.slice(0, n * 9 // 10) for c in lcols]
+    b = [c.slice(n * 9 // 10) for c in lcols]
+    ga, oa = ctx.build_index(a, 1, 40)
+    gb, ob = ctx.build_index(b, 1, 40)
+    lg, loff = ctx.merge_runs([(ga, 1, oa), (gb, 1, ob)])
+    og, ooff = ctx.build_index(orders(keys), 1, 40)
+    jg, joff = ctx.join(lg, loff, og, ooff, 1, [0, 1, 2], [1])
+    full, foff = ctx.build_index(lcols, 1, 40)
+    want, woff = _oracle_join(oracle, full, foff, og, ooff, 1, [0, 1, 2], [1])
+    parity.assert_same_multiset(jg, want, joff, woff, "join over merged runs")
+
+
+def test_join_mismatched_bucket_counts_is_unsupported(ctx, hs):
+    a, ao = ctx.build_index([pa.array([1, 2, 3])], 1, 4)
+    b, bo = ctx.build_index([pa.array([1, 2, 3])], 1, 8)
+    with pytest.raises(hs.HyperspaceException):
+        ctx.join(a, ao, b, bo, 1, [0], [0])
+
+
+def test_filter_predicates(ctx, oracle):
+    rng = np.random.default_rng(31)
+    cols, keys = lineitem(30000, null_frac=0.02)
+    s, _ = string_keys(len(cols[0]), seed=8)
+    cols = cols + [pa.array(s.to_pylist(), mask=rng.random(len(s)) < 0.1)]
+    got, boff = ctx.build_index(cols, 1, 64)
+    k = int(keys[100])
+    probe = s[17].as_py()
+    preds = [
+        [("eq", 0, k)],
+        [("eq", 0, -5)],
+        [("gt", 0, k), ("lt", 1, 50000.0), ("and",)],
+        [("le", 0, k), ("ge", 2, 0.05), ("or",)],
+        [("is_null", 0)],
+        [("is_null", 0), ("not",)],
+        [("gt", 0, k), ("not",)],
+        [("eq", 3, probe)],
+        [("ge", 3, "m"), ("is_not_null", 0), ("and",), ("lt", 2, 0.03), ("or",)],
+        [("ne", 2, 0.05), ("is_null", 3), ("and",)],
+    ]
+    for p in preds:
+        fg = ctx.filter_scan(got, 1, boff, p, [0, 1, 3])
+        idx = pa.array(oracle.filter_rows(got, p))
+        want = [got[0].take(idx), got[1].take(idx), got[3].take(idx)]
+        parity.assert_same_multiset(fg, want, what=f"filter {p}")
+
+
+def test_filter_bucket_pruning_matches_full_scan(ctx, oracle):
+    s, v = string_keys(8000)
+    got, boff = ctx.build_index([s, v], 1, 100)
+    for probe in (s[5].as_py(), s[4000].as_py(), "no such key", ""):
+        fg = ctx.filter_scan(got, 1, boff, [("eq", 0, probe)], [0, 1])
+        idx = pa.array(oracle.filter_rows(got, [("eq", 0, probe)]))
+        parity.assert_same_multiset(fg, [got[0].take(idx), got[1].take(idx)], what=f"pruned {probe!r}")
+    k32 = pa.array(np.arange(-500, 500, dtype=np.int32))
+    got, boff = ctx.build_index([k32, pa.array(np.arange(1000))], 1, 200)
+    for lit in (-500, 0, 499, 1000, 2**40):
+        fg = ctx.filter_scan(got, 1, boff, [("eq", 0, lit)], [1])
+        idx = pa.array(oracle.filter_rows(got, [("eq", 0, lit)]))
+        parity.assert_same_multiset(fg, [got[1].take(idx)], what=f"pruned int {lit}")
