@@ -1,0 +1,406 @@
+#!/usr/bin/env python
+"""bench.py — index-build throughput (rows/s) of the covering-index hot path on B200.
+
+One step = one pass of the build (K1 hash+histogram, K2 bucket scatter, K3 per-bucket sort) over one
+batch of synthetic rows. Workload at N=1: BASELINE.json configs[1]: 100 M rows of
+TPC-H-shaped lineitem {l_orderkey:int64, l_extendedprice:float64, l_discount:float64}, CoveringIndex on
+l_orderkey, 200 buckets. N>1: every rank builds its own 100 M rows (weak scaling) and rows reach the GPU
+that owns their bucket through the NCCL all-to-all inside hs_build_index_dist.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--rows R]
+
+Prints ONE JSON line (see README / DESIGN.md for the keys).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NUM_BUCKETS = 200
+ROW_BYTES = 24          # R: int64 key + two float64
+KEY_BYTES = 8           # Kb
+ALGO_BYTES_PER_ROW = KEY_BYTES + 4 * ROW_BYTES   # hash Kb + scatter 2R + sort 2R = 104
+METRIC = "index_build_rows_per_s"
+UNIT = "rows/s"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def gen_lineitem_device(torch, n_rows, seed, device):
+    """cfg2-shaped rows generated on the device: sparse TPC-H order keys repeated 1..7 times (mean 4),
+    shuffled; prices U[900,105000) to 2 dp; discounts in {0.00..0.10}."""
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    n_orders = n_rows // 4
+    o = torch.arange(n_orders, dtype=torch.int64, device=device)
+    keys = (o // 8) * 32 + o % 8 + 1
+    reps = torch.randint(1, 8, (n_orders,), generator=g, device=device)
+    # adjust the counts so that the total is exactly n_rows
+    diff = int(n_rows - int(reps.sum().item()))
+    step = 1 if diff > 0 else -1
+    i = 0
+    while diff != 0:
+        lo, hi = (1, 6) if step > 0 else (2, 7)
+        cand = ((reps >= lo) & (reps <= hi)).nonzero().flatten()
+        take = min(abs(diff), int(cand.numel()))
+        reps[cand[:take]] += step
+        diff -= step * take
+        i += 1
+        assert i < 16
+    l_orderkey = torch.repeat_interleave(keys, reps)
+    del reps, o
+    perm = torch.randperm(n_rows, generator=g, device=device)
+    l_orderkey = l_orderkey[perm].contiguous()
+    del perm
+    price = torch.round((900.0 + torch.rand(n_rows, generator=g, device=device, dtype=torch.float64) * 104100.0) * 100) / 100
+    disc = torch.randint(0, 11, (n_rows,), generator=g, device=device).to(torch.float64) / 100.0
+    return l_orderkey, price, disc, keys
+
+
+def reference_arm(args):
+    """--impl reference: the reference's CPU path for this metric on the host cores. The reference is
+    Scala on Spark 2.4.2 and cannot run here (no JVM/Spark in the image), so the timed code is the
+    oracle port of that path (oracle/hs_oracle.c) with every host thread, on a bounded sample."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import numpy as np
+    import pyarrow as pa
+    from oracle import oracle
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import fixtures
+    n_orders = max(1, args.ref_rows // 4)
+    cols, _ = fixtures.lineitem(n_orders)
+    n = len(cols[0])
+    for _ in range(max(0, min(args.warmup, 1))):
+        oracle.build_index(cols, 1, NUM_BUCKETS)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        perm, off = oracle.build_index(cols, 1, NUM_BUCKETS)
+        # the build also materialises the index columns in their new order
+        for c in cols:
+            np.take(c.to_numpy(zero_copy_only=False), perm)
+    dt = time.perf_counter() - t0
+    v = n * args.steps / dt
+    cores = oracle.num_threads()
+    line = {"metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic", "impl": "reference",
+            "config": {"workload": "cfg2 lineitem shape, int64 key + 2 float64, 200 buckets", "rows_per_step": n,
+                       "num_buckets": NUM_BUCKETS},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": f"{n} rows of the cfg2 workload per step (hash, bucket, per-bucket sort, take)"},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "reference Spark local[*]: unavailable on this box (no JVM/Spark); timed = oracle port"}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native")
+    ap.add_argument("--rows", type=int, default=100_000_000, help="rows per GPU per step")
+    ap.add_argument("--ref-rows", type=int, default=10_000_000, help="rows per step of the CPU arms")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--no-join", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+    if args.impl == "reference":
+        reference_arm(args)
+        return
+
+    import numpy as np
+    import torch
+    from hyperspace_1_b200 import abi, native
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    ctx = native.Context(local)
+    if world > 1:
+        uid = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            uid = torch.frombuffer(bytearray(ctx.comm_unique_id()), dtype=torch.uint8).to(dev)
+        dist.broadcast(uid, 0)
+        ctx.comm_init(rank, world, bytes(uid.cpu().numpy().tobytes()))
+
+    n = args.rows
+    key, price, disc, okeys = gen_lineitem_device(torch, n, 20240601 + rank, dev)
+    torch.cuda.synchronize()
+
+    def dev_cols():
+        return abi.DeviceColumnSet([
+            {"type": abi.HS_INT64, "length": n, "data": key.data_ptr()},
+            {"type": abi.HS_FLOAT64, "length": n, "data": price.data_ptr()},
+            {"type": abi.HS_FLOAT64, "length": n, "data": disc.data_ptr()}])
+
+    cs = dev_cols()
+    use_dist = world > 1
+    ctx.set_output_location(abi.HS_MEM_DEVICE)
+    stream = torch.cuda.ExternalStream(ctx.stream(), device=dev)
+
+    def step():
+        t = ctx.build_index_table(cs, 1, NUM_BUCKETS, dist=use_dist)
+        return t
+
+    for _ in range(max(args.warmup, 3) if args.warmup > 0 else 0):
+        step().free()
+    # ---- timed region: device-resident in -> device-resident out
+    ctx.enable_timing(True)
+    sampler = ClockSampler(local)
+    sampler.start()
+    barrier()
+    l0 = ctx.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stage_ms = {}
+    xchg = []
+    e0.record(stream)
+    for _ in range(args.steps):
+        t = step()
+        for name, ms, launches in ctx.last_timings():
+            a = stage_ms.setdefault(name, [0.0, 0])
+            a[0] += ms
+            a[1] += launches
+        if use_dist:
+            xchg.append(ctx.comm_last_exchange())
+        t.free()
+    e1.record(stream)
+    barrier()
+    launches = ctx.launch_count() - l0
+    clocks = sampler.stop()
+    ms_total = e0.elapsed_time(e1)
+    ctx.enable_timing(False)
+    if dist is not None:
+        tt = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_total = float(tt.item())
+    ms_step = ms_total / args.steps
+    value = n * world / (ms_step * 1e-3)
+
+    # ---- dominant kernel and its roofline (device time of its launches inside the timed region)
+    peak, peak_kind = peaks()
+    algo = {"hash_hist": KEY_BYTES, "bucket_scatter": 2 * ROW_BYTES, "msd_scatter": 2 * ROW_BYTES,
+            "leaf_sort": 2 * ROW_BYTES, "msd_hist": KEY_BYTES}
+    kernel_of = {"hash_hist": "k_hash_i64x2", "bucket_scatter": "k_partition<0>", "msd_scatter": "k_partition<1>",
+                 "leaf_sort": "k_leaf_sort", "msd_hist": "k_msd_hist"}
+    per_stage = {k: {"ms_per_step": v[0] / args.steps, "launches_per_step": v[1] / args.steps}
+                 for k, v in stage_ms.items()}
+    dom = max((k for k in per_stage if k in algo), key=lambda k: per_stage[k]["ms_per_step"])
+    dom_ms = per_stage[dom]["ms_per_step"]
+    achieved = algo[dom] * n / (dom_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": kernel_of[dom], "stage": dom, "achieved": achieved, "peak": peak,
+                "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})", "unit": "GB/s", "frac": achieved / peak,
+                "algorithmic_bytes_per_row": algo[dom], "rows_per_launch": n, "ms_per_launch": dom_ms,
+                "traffic": None}
+    tr_path = os.path.join(ROOT, "profiles", "dominant_kernel_traffic.json")
+    if os.path.exists(tr_path):
+        try:
+            tr = json.load(open(tr_path))
+            if tr.get("kernel") == kernel_of[dom] and tr.get("rows") == n:
+                roofline["traffic"] = tr["dram_bytes_per_launch"]
+        except Exception:
+            pass
+    build_gbs = ALGO_BYTES_PER_ROW * n / (ms_step * 1e-3) / 1e9
+    build_roofline = {"algorithmic_bytes_per_row": ALGO_BYTES_PER_ROW, "achieved": build_gbs, "unit": "GB/s",
+                      "frac_of_measured_peak": build_gbs / peak, "frac_of_8TBs": build_gbs / 8000.0}
+
+    # ---- e2e: the same build through the C ABI with HOST buffers (pinned in, pinned out)
+    e2e = None
+    if args.e2e_steps > 0:
+        hk, hp, hd = key.cpu().pin_memory(), price.cpu().pin_memory(), disc.cpu().pin_memory()
+        hcs = abi.DeviceColumnSet([
+            {"type": abi.HS_INT64, "length": n, "data": hk.data_ptr()},
+            {"type": abi.HS_FLOAT64, "length": n, "data": hp.data_ptr()},
+            {"type": abi.HS_FLOAT64, "length": n, "data": hd.data_ptr()}])
+        ctx.set_output_location(abi.HS_MEM_HOST)
+        ctx.build_index_table(hcs, 1, NUM_BUCKETS, dist=use_dist).free()   # warm the pinned pool
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.e2e_steps):
+            t = ctx.build_index_table(hcs, 1, NUM_BUCKETS, dist=use_dist)
+            first_key = C.c_int64.from_address(t.column(0).data).value if t.nrows else 0  # read the result
+            t.free()
+        barrier()
+        dt = (time.perf_counter() - t0) / args.e2e_steps
+        if dist is not None:
+            tt = torch.tensor([dt], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            dt = float(tt.item())
+        e2e = {"value": n * world / dt, "unit": UNIT, "h2d_bytes_per_step": n * ROW_BYTES,
+               "d2h_bytes_per_step": n * ROW_BYTES, "ms_per_step": dt * 1e3, "steps": args.e2e_steps,
+               "first_key": int(first_key)}
+        del hk, hp, hd
+        ctx.set_output_location(abi.HS_MEM_DEVICE)
+
+    # ---- indexed join (cfg3): lineitem x orders over two indexes, bucket-local, no communication
+    join = None
+    if not args.no_join and world == 1:
+        try:
+            g = torch.Generator(device=dev)
+            g.manual_seed(20240602)
+            n_o = int(okeys.numel())
+            ok = okeys[torch.randperm(n_o, generator=g, device=dev)].contiguous()
+            ototal = 850.0 + torch.rand(n_o, generator=g, device=dev, dtype=torch.float64) * 559150.0
+            torch.cuda.synchronize()   # the library has its own stream: torch's writes must have landed
+            ocs = abi.DeviceColumnSet([{"type": abi.HS_INT64, "length": n_o, "data": ok.data_ptr()},
+                                       {"type": abi.HS_FLOAT64, "length": n_o, "data": ototal.data_ptr()}])
+            lt = ctx.build_index_table(cs, 1, NUM_BUCKETS)
+            ot = ctx.build_index_table(ocs, 1, NUM_BUCKETS)
+
+            def view(tbl, ncols):
+                arr = (abi.hs_column * ncols)(*[tbl.column(i) for i in range(ncols)])
+                dcs = abi.DeviceColumnSet([])
+                dcs.c, dcs.n = arr, ncols
+                return native.IndexView(dcs, 1, tbl.bucket_offsets())
+            lv, ov = view(lt, 3), view(ot, 2)
+            for _ in range(2):
+                ctx.join_table(lv, ov, [0, 1, 2], [1]).free()
+            torch.cuda.synchronize()
+            j0, j1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            jl0 = ctx.launch_count()
+            j0.record(stream)
+            jsteps = max(1, min(args.steps, 5))
+            for _ in range(jsteps):
+                jt = ctx.join_table(lv, ov, [0, 1, 2], [1])
+                n_out = jt.nrows
+                jt.free()
+            j1.record(stream)
+            torch.cuda.synchronize()
+            jms = j0.elapsed_time(j1) / jsteps
+            jbytes = n * ROW_BYTES + n_o * 16 + n_out * 32
+            join = {"metric": "indexed_join_output_rows_per_s", "value": n_out / (jms * 1e-3), "unit": UNIT,
+                    "ms_per_step": jms, "output_rows": int(n_out), "left_rows": n, "right_rows": n_o,
+                    "algorithmic_bytes": jbytes, "achieved_GBps": jbytes / (jms * 1e-3) / 1e9,
+                    "frac_of_measured_peak": jbytes / (jms * 1e-3) / 1e9 / peak,
+                    "gpu_launches": ctx.launch_count() - jl0}
+            lt.free()
+            ot.free()
+            del ok, ototal
+        except Exception as ex:  # the join line is extra; the build line must still print
+            join = {"error": str(ex)[:200]}
+
+    # ---- CPU baseline beside it: the oracle port on a bounded sample (rank 0, N=1 only)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        import pyarrow as pa
+        from oracle import oracle
+        m = min(args.ref_rows, n)
+        sample = [pa.array(key[:m].cpu().numpy()), pa.array(price[:m].cpu().numpy()), pa.array(disc[:m].cpu().numpy())]
+        t0 = time.perf_counter()
+        perm, _ = oracle.build_index(sample, 1, NUM_BUCKETS)
+        for c in sample:
+            np.take(c.to_numpy(zero_copy_only=False), perm)
+        dt = time.perf_counter() - t0
+        cpu = {"value": m / dt, "unit": UNIT, "cores": oracle.num_threads(), "kind": "port",
+               "sample": f"first {m} rows of the same workload, one pass (hash, bucket, per-bucket sort, take)",
+               "seconds": dt}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+                "config": {"workload": "cfg2: TPC-H-shaped lineitem, CoveringIndex on int64 l_orderkey including "
+                                       "l_extendedprice,l_discount, 200 buckets",
+                           "rows_per_gpu": n, "num_buckets": NUM_BUCKETS, "row_bytes": ROW_BYTES,
+                           "l2_policy": "inputs (2.4 GB per step) are larger than L2; no flush needed",
+                           "parallelism": f"buckets sharded over {world} GPU(s), NCCL all-to-all in the build"
+                           if world > 1 else "single GPU"},
+                "roofline": roofline, "build_roofline": build_roofline, "stages": per_stage,
+                "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "join": join}
+        if use_dist and xchg:
+            b = sum(x[0] for x in xchg) / len(xchg)
+            ms = sum(x[1] for x in xchg) / len(xchg)
+            line["all_to_all"] = {"bytes_sent_per_gpu": b, "ms": ms, "bus_GBps": b / (ms * 1e-3) / 1e9 if ms else None,
+                                  "frac_of_900": (b / (ms * 1e-3) / 1e9 / 900.0) if ms else None}
+        print(json.dumps(line), flush=True)
+    ctx.comm_destroy()
+    ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

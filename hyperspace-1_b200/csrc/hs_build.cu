@@ -318,14 +318,10 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
   bucket.release();
 
   // ---- K3: every bucket sorted on the key
-  {
-    Stage s(c, "bucket_sort");
-    hs_segmented_sort(c, ms, key, key_bits, d_off.as<uint32_t>(), nbl, n);
-  }
+  hs_segmented_sort(c, ms, key, key_bits, d_off.as<uint32_t>(), nbl, n);
 
   // ---- keys wider than one chunk (strings, wide composites): refine tie groups chunk by chunk
   if (!L.single_chunk) {
-    Stage s(c, "tie_refine");
     DBuf flag(c, (size_t)n), rank(c, (size_t)n * 4), head_pos(c, (size_t)n * 4), total(c, 8);
     DBuf gstart(c, (size_t)(n / 2 + 1) * 4), glen(c, (size_t)(n / 2 + 1) * 4), counter(c, 4);
     flag.zero();

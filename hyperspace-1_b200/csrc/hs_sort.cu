@@ -449,10 +449,12 @@ static void run_leaf_and_copy(hs_ctx* c, MoveSet& ms, const KeySrc& key, bool sr
     lp.in_place = src_is_a ? 1 : 0;
     size_t smem = leaf_smem_bytes();
     CK(cudaFuncSetAttribute(k_leaf_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    Stage st(c, "leaf_sort");
     LAUNCH(c, k_leaf_sort, n_leaf, PT_THREADS, smem, lp);
   }
   if (n_copy && !src_is_a) {
     MoveArgs mv = make_move(ms, false, true);
+    Stage st(c, "copy_segments");
     LAUNCH(c, k_copy_segments, n_copy, 256, 0, mv, copy.view());
   }
 }
@@ -469,11 +471,13 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
   DBuf counters(c, 8 * 4);
   counters.zero();
   PlanOut po{leaf.view(), large.view(), copy.view(), counters.as<uint32_t>()};
+  hs_stage_begin(c, "sort_plan");
   LAUNCH(c, k_classify, (unsigned)((nseg + 255) / 256), 256, 0, d_seg_off, d_start, d_len, nseg, (uint32_t)key_bits, po);
   DBuf tile_prefix(c, (cap_large + 1) * 4);
   LAUNCH(c, k_tile_prefix, 1, 1024, 0, large.view(), counters.as<uint32_t>(), tile_prefix.as<uint32_t>());
   uint32_t h[4];
   CK(cudaMemcpyAsync(h, counters.p, 16, cudaMemcpyDeviceToHost, c->stream));
+  hs_stage_end(c);
   hs_sync(c);
   bool src_is_a = true;
   run_leaf_and_copy(c, ms, key, src_is_a, leaf, h[0], copy, h[2]);
@@ -495,7 +499,9 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     p.segs = large.view();
     p.tile_prefix = tile_prefix.as<uint32_t>();
     p.nseg = n_large;
+    hs_stage_begin(c, "msd_hist");
     LAUNCH(c, k_msd_hist, n_tiles, PT_THREADS, 0, p);
+    hs_stage_end(c);
     ListBufs nleaf, nlarge, ncopy;
     size_t children = (size_t)n_large * MSD_RADIX;
     nleaf.alloc(c, children);
@@ -504,13 +510,19 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     DBuf ncounters(c, 8 * 4);
     ncounters.zero();
     PlanOut npo{nleaf.view(), nlarge.view(), ncopy.view(), ncounters.as<uint32_t>()};
+    hs_stage_begin(c, "msd_plan");
     LAUNCH(c, k_msd_plan, n_large, MSD_RADIX, 0, large.view(), cursor.as<uint32_t>(), npo);
+    hs_stage_end(c);
     size_t smem = tile_smem_bytes(MSD_RADIX);
     CK(cudaFuncSetAttribute(k_partition<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    hs_stage_begin(c, "msd_scatter");
     LAUNCH(c, k_partition<1>, n_tiles, PT_THREADS, smem, p);
+    hs_stage_end(c);
     DBuf ntile_prefix(c, (cap_large + 1) * 4);
+    hs_stage_begin(c, "msd_plan");
     LAUNCH(c, k_tile_prefix, 1, 1024, 0, nlarge.view(), ncounters.as<uint32_t>(), ntile_prefix.as<uint32_t>());
     CK(cudaMemcpyAsync(h, ncounters.p, 16, cudaMemcpyDeviceToHost, c->stream));
+    hs_stage_end(c);
     hs_sync(c);
     src_is_a = !src_is_a;
     run_leaf_and_copy(c, ms, key, src_is_a, nleaf, h[0], ncopy, h[2]);

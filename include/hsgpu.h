@@ -20,7 +20,9 @@
  *  - outputs are hs_table objects owned by the library and released with
  *    hs_table_free(); their buffers are pinned host memory or device memory,
  *    selected by hs_ctx_set_output_location().
- *  - calls are synchronous: the context's stream is drained before returning.
+ *  - calls are synchronous: the context's stream is drained before returning. The context
+ *    launches on its OWN stream: device inputs must be complete before the call (synchronise
+ *    the stream that produced them first).
  *  - a context is bound to one device and is not thread-safe; different
  *    contexts may be used concurrently from different threads.
  *  - there is no CPU fallback: unsupported inputs return HS_EUNSUPPORTED.
