@@ -17,7 +17,7 @@ EXPORTS = [
     "hs_ctx_create", "hs_ctx_destroy", "hs_last_error", "hs_ctx_set_output_location", "hs_ctx_get_stream",
     "hs_ctx_enable_timing", "hs_ctx_last_timings", "hs_ctx_launch_count", "hs_table_free", "hs_version",
     "hs_hash_bucket", "hs_hash_rows", "hs_build_index", "hs_merge_runs", "hs_join_bucketed", "hs_filter_scan",
-    "hs_comm_unique_id", "hs_comm_init", "hs_comm_destroy", "hs_build_index_dist", "hs_comm_last_exchange",
+    "hs_bucket_histogram_noalloc", "hs_comm_unique_id", "hs_comm_init", "hs_comm_destroy", "hs_build_index_dist", "hs_comm_last_exchange",
 ]
 
 
@@ -183,6 +183,13 @@ class Context:
         self._check(self._lib.hs_hash_rows(self._h, cs.ptr(), C.c_int32(cs.n), out.ctypes.data_as(C.c_void_p)),
                     "hs_hash_rows")
         return out
+
+    def bucket_histogram_noalloc(self, keys, num_buckets, out_ids_ptr, out_counts_ptr):
+        """hs_bucket_histogram_noalloc: `keys` is a DeviceColumnSet, the outputs are raw addresses
+        (int32 ids in device memory; uint32 counts in host or device memory). Allocates nothing."""
+        self._check(self._lib.hs_bucket_histogram_noalloc(self._h, keys.ptr(), C.c_int32(keys.n),
+                                                          C.c_int32(num_buckets), C.c_void_p(out_ids_ptr),
+                                                          C.c_void_p(out_counts_ptr)), "hs_bucket_histogram_noalloc")
 
     # ---- build
     def build_index_table(self, cols, n_indexed, num_buckets, dist=False):

@@ -164,6 +164,21 @@ int32_t hs_hash_bucket(hs_ctx* ctx, const hs_column* keys, int32_t nkeys,
 int32_t hs_hash_rows(hs_ctx* ctx, const hs_column* keys, int32_t nkeys,
                      int32_t* out_hashes);
 
+/* Bucket ids and per-bucket row counts for callers that cannot allocate GPU memory.
+ * No counterpart in the reference (it never touches a GPU); it exists for hosts where cudaMalloc is
+ * not an option: an executor whose device memory is wholly reserved by another pool (an arena /
+ * RMM-style allocator sized to the GPU), or a thread that may not trigger the device-wide
+ * synchronisation cudaMalloc/cudaFree imply. The histogram counters live in a fixed 32 KiB array
+ * inside the library image, so num_buckets is limited to HS_NOALLOC_MAX_BUCKETS = 8192 (larger
+ * values return HS_EINVAL). Key buffers and out_bucket_ids (int32 per row) must be device memory;
+ * out_counts (num_buckets uint32) may be host or device memory. All calls on a GPU share the
+ * array: do not let two of them overlap. The first call on a device resolves the array's device
+ * address; make that call outside of stream capture. Same bucket ids as hs_hash_bucket. */
+#define HS_NOALLOC_MAX_BUCKETS 8192
+int32_t hs_bucket_histogram_noalloc(hs_ctx* ctx, const hs_column* keys, int32_t nkeys,
+                                    int32_t num_buckets, int32_t* out_bucket_ids,
+                                    uint32_t* out_counts);
+
 /* ---- K1+K2+K3: the index build --------------------------------------------
  * Replaces the body of CreateActionBase.write (HS/actions/CreateActionBase.scala:122-140):
  * repartition(numBuckets, indexedCols) followed by saveWithBuckets with
