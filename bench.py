@@ -53,7 +53,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE,
+                                          "-lms", "20", "-i", str(self.gpu)], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -62,12 +62,18 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.perf_counter(), line.strip()))
 
-    def stop(self):
+    def wait_first_sample(self, timeout=5.0):
+        # nvidia-smi takes the driver lock while it starts: let it settle before anything is timed
+        t0 = time.perf_counter()
+        while self.proc and not self.lines and time.perf_counter() - t0 < timeout:
+            time.sleep(0.02)
+
+    def stop(self, t_begin=None, t_end=None):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.05)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=2)
@@ -75,7 +81,15 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        lines = self.lines
+        window = "timed region"
+        if t_begin is not None:
+            inside = [x for x in lines if t_begin <= x[0] <= t_end + 0.05]
+            if inside:
+                lines = inside
+            else:
+                window = "warm-up + timed region (timed region shorter than the sampling period)"
+        for _, ln in lines:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
                 continue
@@ -89,7 +103,7 @@ class ClockSampler:
                     reasons.add(nm)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "window": window, "reasons": sorted(reasons)}
 
 
 def gen_lineitem_device(torch, n_rows, seed, device):
@@ -226,13 +240,15 @@ def main():
         t = ctx.build_index_table(cs, 1, NUM_BUCKETS, dist=use_dist)
         return t
 
+    sampler = ClockSampler(local)
+    sampler.start()
+    sampler.wait_first_sample()
     for _ in range(max(args.warmup, 3) if args.warmup > 0 else 0):
         step().free()
     # ---- timed region: device-resident in -> device-resident out
     ctx.enable_timing(True)
-    sampler = ClockSampler(local)
-    sampler.start()
     barrier()
+    t_begin = time.perf_counter()
     l0 = ctx.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     stage_ms = {}
@@ -250,7 +266,7 @@ def main():
     e1.record(stream)
     barrier()
     launches = ctx.launch_count() - l0
-    clocks = sampler.stop()
+    clocks = sampler.stop(t_begin, time.perf_counter())
     ms_total = e0.elapsed_time(e1)
     ctx.enable_timing(False)
     if dist is not None:

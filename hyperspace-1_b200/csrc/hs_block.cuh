@@ -100,6 +100,123 @@ __device__ __forceinline__ void tile_rank(const uint32_t (&digit)[ITEMS], uint32
   }
 }
 
+// Unstable ranking of a tile by digit with shared-memory atomics (B200: ~11 ATOMS lanes/clk/SM on random
+// addresses, an order of magnitude cheaper than the ballot match above). Use wherever the order of rows
+// with equal digits does not matter: the bucket scatter, MSD levels, the first pass of an LSD sort.
+//   cnt : radix_pad words; on return cnt[d] = first position of digit d (exclusive scan, in place),
+//   tot : radix_pad words = items per digit (may be nullptr when the caller does not need it).
+// On return pos[k] = position of item k in the digit-grouped tile, rnk[k] = its rank inside its digit.
+template <int ITEMS>
+__device__ __forceinline__ void tile_rank_atomic(const uint32_t (&digit)[ITEMS], uint32_t vmask, int items,
+                                                 int radix_pad, uint32_t* cnt, uint32_t* tot, uint32_t* scratch,
+                                                 uint32_t (&pos)[ITEMS]) {
+  for (int i = threadIdx.x; i < radix_pad; i += PT_THREADS) cnt[i] = 0;
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < ITEMS; k++)
+    if (k < items && ((vmask >> k) & 1u)) pos[k] = atomicAdd(&cnt[digit[k]], 1u);
+  __syncthreads();
+  const int per = radix_pad / PT_THREADS;
+  uint32_t s = 0;
+  for (int j = 0; j < per; j++) s += cnt[threadIdx.x * per + j];
+  uint32_t ex = block_excl_scan_u32(s, scratch, nullptr);
+  for (int j = 0; j < per; j++) {
+    uint32_t c = cnt[threadIdx.x * per + j];
+    if (tot) tot[threadIdx.x * per + j] = c;
+    cnt[threadIdx.x * per + j] = ex;
+    ex += c;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < ITEMS; k++)
+    if (k < items && ((vmask >> k) & 1u)) pos[k] += cnt[digit[k]];
+}
+
+// Variants that take the digit as a bit field of a 32-bit word (no digit array in registers).
+template <int ITEMS>
+__device__ __forceinline__ void tile_rank_atomic_w(const uint32_t (&word)[ITEMS], int shift, uint32_t mask,
+                                                   uint32_t vmask, int items, int radix_pad, uint32_t* cnt,
+                                                   uint32_t* scratch, uint32_t (&pos)[ITEMS]) {
+  for (int i = threadIdx.x; i < radix_pad; i += PT_THREADS) cnt[i] = 0;
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < ITEMS; k++)
+    if (k < items && ((vmask >> k) & 1u)) pos[k] = atomicAdd(&cnt[(word[k] >> shift) & mask], 1u);
+  __syncthreads();
+  const int per = radix_pad / PT_THREADS;
+  uint32_t s = 0;
+  for (int j = 0; j < per; j++) s += cnt[threadIdx.x * per + j];
+  uint32_t ex = block_excl_scan_u32(s, scratch, nullptr);
+  for (int j = 0; j < per; j++) {
+    uint32_t c = cnt[threadIdx.x * per + j];
+    cnt[threadIdx.x * per + j] = ex;
+    ex += c;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < ITEMS; k++)
+    if (k < items && ((vmask >> k) & 1u)) pos[k] += cnt[(word[k] >> shift) & mask];
+}
+
+template <int ITEMS>
+__device__ __forceinline__ void tile_rank_w(const uint32_t (&word)[ITEMS], int shift, uint32_t vmask, int items,
+                                            int bits, int radix_pad, uint32_t* cnt, uint32_t* tot, uint32_t* loc,
+                                            uint32_t* scratch, uint32_t (&pos)[ITEMS]) {
+  const int w = threadIdx.x >> 5;
+  const uint32_t lt = (1u << lane_id()) - 1u;
+  const uint32_t mask = (1u << bits) - 1u;
+  for (int i = threadIdx.x; i < PT_WARPS * radix_pad; i += PT_THREADS) cnt[i] = 0;
+  __syncthreads();
+  uint32_t* mycnt = cnt + w * radix_pad;
+#pragma unroll
+  for (int k = 0; k < ITEMS; k++) {
+    if (k < items) {
+      bool v = (vmask >> k) & 1u;
+      uint32_t d = (word[k] >> shift) & mask;
+      uint32_t m = __ballot_sync(0xffffffffu, v);
+      for (int b = 0; b < bits; b++) {
+        bool bit = (d >> b) & 1u;
+        uint32_t bal = __ballot_sync(0xffffffffu, bit);
+        m &= bit ? bal : ~bal;
+      }
+      uint32_t r = __popc(m & lt);
+      uint32_t pre = v ? mycnt[d] : 0;
+      __syncwarp();
+      if (v && r == 0) mycnt[d] = pre + __popc(m);
+      __syncwarp();
+      pos[k] = pre + r;
+    }
+  }
+  __syncthreads();
+  for (int d = threadIdx.x; d < radix_pad; d += PT_THREADS) {
+    uint32_t run = 0;
+#pragma unroll
+    for (int ww = 0; ww < PT_WARPS; ww++) {
+      uint32_t c = cnt[ww * radix_pad + d];
+      cnt[ww * radix_pad + d] = run;
+      run += c;
+    }
+    tot[d] = run;
+  }
+  __syncthreads();
+  const int per = radix_pad / PT_THREADS;
+  uint32_t s = 0;
+  for (int j = 0; j < per; j++) s += tot[threadIdx.x * per + j];
+  uint32_t ex = block_excl_scan_u32(s, scratch, nullptr);
+  for (int j = 0; j < per; j++) {
+    loc[threadIdx.x * per + j] = ex;
+    ex += tot[threadIdx.x * per + j];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < ITEMS; k++) {
+    if (k < items && ((vmask >> k) & 1u)) {
+      uint32_t d = (word[k] >> shift) & mask;
+      pos[k] += loc[d] + mycnt[d];
+    }
+  }
+}
+
 __device__ __forceinline__ uint64_t warp_min_u64(uint64_t v) {
 #pragma unroll
   for (int d = 16; d; d >>= 1) {

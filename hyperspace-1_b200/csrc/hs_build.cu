@@ -318,7 +318,7 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
   bucket.release();
 
   // ---- K3: every bucket sorted on the key
-  hs_segmented_sort(c, ms, key, key_bits, d_off.as<uint32_t>(), nbl, n);
+  hs_segmented_sort(c, ms, key, key_bits, d_off.as<uint32_t>(), nbl, n, off32.data());
 
   // ---- keys wider than one chunk (strings, wide composites): refine tie groups chunk by chunk
   if (!L.single_chunk) {

@@ -38,7 +38,7 @@ void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, con
 // Sort every segment [seg_off[s], seg_off[s+1]) of ms.a by the key; result in ms.a. key_bits = significant
 // low bits of the key. d_seg_off: device u32[nseg+1].
 void hs_segmented_sort(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_seg_off,
-                       int64_t nseg, int64_t n);
+                       int64_t nseg, int64_t n, const uint32_t* h_seg_off);
 // Same, for an explicit device list of segments (start,len), all with the same key_bits.
 void hs_segmented_sort_list(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_start,
                             const uint32_t* d_len, int64_t nseg, int64_t n);

@@ -34,51 +34,58 @@ __device__ __forceinline__ uint64_t load_key(const MoveArgs& mv, const KeySrc& k
   return ((uint64_t)(int64_t)((const int32_t*)p)[row] ^ 0x8000000000000000ull) - ks.min;
 }
 
-// shared memory carve-up of the tile kernels
+// ---- TMA (bulk async copy) + mbarrier helpers: contiguous column slices global -> shared memory
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+
+// shared memory carve-up of the partition kernel
+#define STAGE_BYTES (PT_TILE * 8 + 128)   // one column slice of a tile + alignment slack
 struct TileSmem {
-  uint32_t* cnt;      // PT_WARPS * radix_pad
-  uint32_t* tot;      // radix_pad
-  uint32_t* loc;      // radix_pad
-  uint32_t* gbase;    // radix_pad
-  uint32_t* scratch;  // 16
-  uint32_t* gdst;     // PT_TILE
-  uint64_t* stage;    // PT_TILE
+  unsigned char* stage[2];  // TMA landing buffers (double buffered over the columns)
+  uint32_t* gdst;           // PT_TILE: global destination row of every tile-sorted position
+  uint16_t* inv;            // PT_TILE: tile row that lands at every tile-sorted position
+  uint32_t* cnt;            // radix_pad: counters, then first position of every digit
+  uint32_t* tot;            // radix_pad: rows per digit
+  uint32_t* gbase;          // radix_pad: reserved global run start per digit
+  uint32_t* scratch;        // 16
+  uint64_t* bar;            // 2 mbarriers
 };
 __device__ __forceinline__ TileSmem carve(unsigned char* base, int radix_pad) {
   TileSmem s;
-  s.stage = (uint64_t*)base;
-  s.gdst = (uint32_t*)(s.stage + PT_TILE);
-  s.cnt = s.gdst + PT_TILE;
-  s.tot = s.cnt + PT_WARPS * radix_pad;
-  s.loc = s.tot + radix_pad;
-  s.gbase = s.loc + radix_pad;
+  s.stage[0] = base;
+  s.stage[1] = base + STAGE_BYTES;
+  s.gdst = (uint32_t*)(base + 2 * STAGE_BYTES);
+  s.inv = (uint16_t*)(s.gdst + PT_TILE);
+  s.cnt = (uint32_t*)(s.inv + PT_TILE);
+  s.tot = s.cnt + radix_pad;
+  s.gbase = s.tot + radix_pad;
   s.scratch = s.gbase + radix_pad;
+  s.bar = (uint64_t*)(s.scratch + 16);
   return s;
 }
 static size_t tile_smem_bytes(int radix_pad) {
-  return (size_t)PT_TILE * 8 + (size_t)PT_TILE * 4 + (size_t)(PT_WARPS + 3) * radix_pad * 4 + 64;
-}
-
-template <typename T>
-__device__ __forceinline__ void move_column(const T* __restrict__ src, T* __restrict__ dst, uint32_t tile_start,
-                                            uint32_t tile_len, const uint32_t (&pos)[PT_ITEMS], uint32_t vmask,
-                                            T* stage, const uint32_t* gdst) {
-  const int w = threadIdx.x >> 5;
-  const uint32_t base = w * (PT_ITEMS * 32) + lane_id();
-  T v[PT_ITEMS];
-#pragma unroll
-  for (int k = 0; k < PT_ITEMS; k++)
-    if ((vmask >> k) & 1u) v[k] = src[tile_start + base + k * 32];
-#pragma unroll
-  for (int k = 0; k < PT_ITEMS; k++)
-    if ((vmask >> k) & 1u) stage[pos[k]] = v[k];
-  __syncthreads();
-#pragma unroll
-  for (int k = 0; k < PT_ITEMS; k++) {
-    uint32_t j = threadIdx.x + k * PT_THREADS;
-    if (j < tile_len) dst[gdst[j]] = stage[j];
-  }
-  __syncthreads();
+  return (size_t)2 * STAGE_BYTES + (size_t)PT_TILE * 4 + (size_t)PT_TILE * 2 + (size_t)3 * radix_pad * 4 + 64 + 16;
 }
 
 struct PartParams {
@@ -104,10 +111,41 @@ __device__ __forceinline__ uint32_t find_segment(const uint32_t* tile_prefix, ui
   return lo;
 }
 
+// one elected thread starts the bulk copy of the tile's slice of column c into a stage buffer.
+// The copy covers whole 16-byte granules around the slice: every granule holds at least one byte of the
+// slice, so it never touches a page the slice does not touch. Returns nothing; *lead = offset of the
+// slice inside the stage buffer.
+__device__ __forceinline__ uint32_t slice_lead(const void* col, int esize, uint32_t tile_start) {
+  return (uint32_t)(((uintptr_t)col + (size_t)tile_start * esize) & 15);
+}
+__device__ __forceinline__ void issue_slice(const void* col, int esize, uint32_t tile_start, uint32_t tile_len,
+                                            unsigned char* stage, uint64_t* bar) {
+  uintptr_t addr = (uintptr_t)col + (size_t)tile_start * esize;
+  uintptr_t a0 = addr & ~(uintptr_t)15;
+  uint32_t bytes = (uint32_t)(((addr + (size_t)tile_len * esize + 15) & ~(uintptr_t)15) - a0);
+  mbar_expect_tx(bar, bytes);
+  tma_load_1d(stage, (const void*)a0, bytes, bar);
+}
+
+template <typename T>
+__device__ __forceinline__ void scatter_column(const unsigned char* stage, uint32_t lead, T* __restrict__ dst,
+                                               uint32_t tile_len, const uint16_t* inv, const uint32_t* gdst) {
+  const T* col = (const T*)(stage + lead);
+#pragma unroll 4
+  for (int k = 0; k < PT_ITEMS; k++) {
+    uint32_t j = threadIdx.x + k * PT_THREADS;
+    if (j < tile_len) dst[gdst[j]] = col[inv[j]];
+  }
+}
+
 // MODE 0: scatter by bucket id.  MODE 1: one MSD level inside large segments.
+// Column slices of the tile arrive in shared memory by TMA bulk copies (double buffered, one mbarrier
+// per buffer); rows are ranked by digit with shared-memory atomics; one global atomicAdd per (tile, digit)
+// reserves the output run; every column is then read through the tile permutation and written as
+// contiguous runs per digit.
 template <int MODE>
 __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_constant__ PartParams p) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+  extern __shared__ __align__(128) unsigned char smem_raw[];
   TileSmem sm = carve(smem_raw, p.radix_pad);
   uint32_t tile_start, tile_len, shift = 0;
   int bits = p.bits;
@@ -128,37 +166,76 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
     shift = sh - bits;
     cursor = p.cursor + (size_t)s * MSD_RADIX;
   }
-  const int w = threadIdx.x >> 5;
-  const uint32_t base = w * (PT_ITEMS * 32) + lane_id();
+  const int ncols = p.mv.n;
+  // column order: in MODE 1 the key column goes first (its slice also feeds the digits)
+  const int first = MODE == 1 ? p.key.col : 0;
+  auto col_at = [&](int i) { return i == 0 ? first : (i <= first ? i - 1 : i); };
+  if (threadIdx.x == 0) {
+    mbar_init(&sm.bar[0], 1);
+    mbar_init(&sm.bar[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int c0 = col_at(0);
+    issue_slice(p.mv.src[c0], p.mv.esize[c0], tile_start, tile_len, sm.stage[0], &sm.bar[0]);
+    if (ncols > 1) {
+      int c1 = col_at(1);
+      issue_slice(p.mv.src[c1], p.mv.esize[c1], tile_start, tile_len, sm.stage[1], &sm.bar[1]);
+    }
+  }
   uint32_t digit[PT_ITEMS], pos[PT_ITEMS];
   uint32_t vmask = 0;
+  if (MODE == 1) mbar_wait(&sm.bar[0], 0);
 #pragma unroll
   for (int k = 0; k < PT_ITEMS; k++) {
-    uint32_t idx = base + k * 32;
+    uint32_t idx = threadIdx.x + k * PT_THREADS;
     bool v = idx < tile_len;
     vmask |= (uint32_t)v << k;
     digit[k] = 0;
     if (v) {
-      if (MODE == 0) digit[k] = p.bucket[tile_start + idx];
-      else digit[k] = (uint32_t)(load_key(p.mv, p.key, tile_start + idx) >> shift) & ((1u << bits) - 1u);
+      if (MODE == 0) {
+        digit[k] = p.bucket[tile_start + idx];
+      } else {
+        const unsigned char* ks = sm.stage[0] + slice_lead(p.mv.src[first], p.mv.esize[first], tile_start);
+        uint64_t key;
+        if (p.key.mode == KS_U64) key = ((const uint64_t*)ks)[idx];
+        else if (p.key.mode == KS_I64) key = (((const uint64_t*)ks)[idx] ^ 0x8000000000000000ull) - p.key.min;
+        else key = ((uint64_t)(int64_t)((const int32_t*)ks)[idx] ^ 0x8000000000000000ull) - p.key.min;
+        digit[k] = (uint32_t)(key >> shift) & ((1u << bits) - 1u);
+      }
     }
   }
-  tile_rank<PT_ITEMS>(digit, vmask, PT_ITEMS, bits, p.radix_pad, sm.cnt, sm.tot, sm.loc, sm.scratch, pos);
+  // the order of rows inside a digit is irrelevant here (the sort below fixes it): rank with atomics
+  tile_rank_atomic<PT_ITEMS>(digit, vmask, PT_ITEMS, p.radix_pad, sm.cnt, sm.tot, sm.scratch, pos);
   for (int d = threadIdx.x; d < p.radix_pad; d += PT_THREADS) {
     uint32_t t = sm.tot[d];
     sm.gbase[d] = t ? atomicAdd(&cursor[d], t) : 0;
   }
   __syncthreads();
 #pragma unroll
-  for (int k = 0; k < PT_ITEMS; k++)
-    if ((vmask >> k) & 1u) sm.gdst[pos[k]] = sm.gbase[digit[k]] + pos[k] - sm.loc[digit[k]];
+  for (int k = 0; k < PT_ITEMS; k++) {
+    if ((vmask >> k) & 1u) {
+      sm.gdst[pos[k]] = sm.gbase[digit[k]] + pos[k] - sm.cnt[digit[k]];
+      sm.inv[pos[k]] = (uint16_t)(threadIdx.x + k * PT_THREADS);
+    }
+  }
   __syncthreads();
-  for (int c = 0; c < p.mv.n; c++) {
-    switch (p.mv.esize[c]) {
-      case 8: move_column<uint64_t>((const uint64_t*)p.mv.src[c], (uint64_t*)p.mv.dst[c], tile_start, tile_len, pos, vmask, sm.stage, sm.gdst); break;
-      case 4: move_column<uint32_t>((const uint32_t*)p.mv.src[c], (uint32_t*)p.mv.dst[c], tile_start, tile_len, pos, vmask, (uint32_t*)sm.stage, sm.gdst); break;
-      case 2: move_column<uint16_t>((const uint16_t*)p.mv.src[c], (uint16_t*)p.mv.dst[c], tile_start, tile_len, pos, vmask, (uint16_t*)sm.stage, sm.gdst); break;
-      default: move_column<uint8_t>((const uint8_t*)p.mv.src[c], (uint8_t*)p.mv.dst[c], tile_start, tile_len, pos, vmask, (uint8_t*)sm.stage, sm.gdst); break;
+  for (int i = 0; i < ncols; i++) {
+    const int c = col_at(i), b = i & 1, es = p.mv.esize[c];
+    mbar_wait(&sm.bar[b], (uint32_t)(i >> 1) & 1u);
+    const uint32_t lead = slice_lead(p.mv.src[c], es, tile_start);
+    switch (es) {
+      case 8: scatter_column<uint64_t>(sm.stage[b], lead, (uint64_t*)p.mv.dst[c], tile_len, sm.inv, sm.gdst); break;
+      case 4: scatter_column<uint32_t>(sm.stage[b], lead, (uint32_t*)p.mv.dst[c], tile_len, sm.inv, sm.gdst); break;
+      case 2: scatter_column<uint16_t>(sm.stage[b], lead, (uint16_t*)p.mv.dst[c], tile_len, sm.inv, sm.gdst); break;
+      default: scatter_column<uint8_t>(sm.stage[b], lead, (uint8_t*)p.mv.dst[c], tile_len, sm.inv, sm.gdst); break;
+    }
+    __syncthreads();  // everyone is done with stage[b]: it can be refilled
+    if (threadIdx.x == 0 && i + 2 < ncols) {
+      int cn = col_at(i + 2);
+      issue_slice(p.mv.src[cn], p.mv.esize[cn], tile_start, tile_len, sm.stage[b], &sm.bar[b]);
     }
   }
 }
@@ -265,12 +342,14 @@ struct LeafParams {
   KeySrc key;
   SegList segs;
   int32_t in_place;   // src == dst
+  uint8_t* wide;      // per segment: 1 = key range needs the 64-bit kernel (written by k_leaf_sort32)
+  const uint32_t* count;  // device: number of segments in the list (the grid is an upper bound)
 };
 
 // Sort one segment of at most LEAF_MAX rows entirely in shared memory: LSD radix over the bits that
 // vary inside the segment (min/max of its keys), 8 bits per pass, stable; then move every column.
 __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort(const __grid_constant__ LeafParams p) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+  extern __shared__ __align__(128) unsigned char smem_raw[];
   uint64_t* skey = (uint64_t*)smem_raw;                 // LEAF_MAX
   uint16_t* sidx = (uint16_t*)(skey + LEAF_MAX);        // LEAF_MAX
   uint32_t* cnt = (uint32_t*)(sidx + LEAF_MAX);         // PT_WARPS * 256
@@ -280,6 +359,8 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort(const __grid_consta
   uint64_t* red = (uint64_t*)(scratch + 16);            // 2 * PT_WARPS + 2
 
   const uint32_t s = blockIdx.x;
+  if (s >= *p.count) return;
+  if (p.wide && !p.wide[s]) return;  // already sorted by the packed 32-bit kernel
   const uint32_t start = p.segs.start[s], len = p.segs.len[s];
   const int w = threadIdx.x >> 5;
   const uint32_t chunk = ((len + PT_THREADS - 1) / PT_THREADS) * 32;  // elements per warp, multiple of 32
@@ -371,14 +452,149 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort(const __grid_consta
     }
   }
 }
+
+#define L32_IDX_BITS 12
+#define L32_MAX_KEY_BITS 20
+#define L32_ATOMIC_BITS 11
+
+template <typename T>
+__device__ __forceinline__ void leaf_move_column(const T* __restrict__ src, T* __restrict__ dst, uint32_t start,
+                                                 uint32_t len, const uint32_t* sdata) {
+  T v[PT_ITEMS];
+#pragma unroll
+  for (int k = 0; k < PT_ITEMS; k++) {
+    uint32_t j = threadIdx.x + k * PT_THREADS;
+    if (j < len) v[k] = src[start + (sdata[j] & ((1u << L32_IDX_BITS) - 1u))];
+  }
+  __syncthreads();  // every read of the segment precedes every write: src == dst is safe
+#pragma unroll
+  for (int k = 0; k < PT_ITEMS; k++) {
+    uint32_t j = threadIdx.x + k * PT_THREADS;
+    if (j < len) dst[start + j] = v[k];
+  }
+}
+
+// The leaf sort for segments whose keys span at most 2^20 values (the common case after one MSD level):
+// key - min and the row's position are packed into one 32-bit word, the first LSD pass (up to 11 bits)
+// ranks with shared-memory atomics (no stability needed), the remaining <= 9 bits take one stable
+// ballot-ranked pass. Segments with a wider key range are flagged for k_leaf_sort.
+__global__ void __launch_bounds__(PT_THREADS, 3) k_leaf_sort32(const __grid_constant__ LeafParams p) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  uint32_t* sdata = (uint32_t*)smem_raw;            // LEAF_MAX packed words
+  uint32_t* cnt = sdata + LEAF_MAX;                 // 4096 words: 2048 atomic counters or 8 x 512 warp counters
+  uint32_t* tot = cnt + 4096;                       // 512
+  uint32_t* loc = tot + 512;                        // 512
+  uint32_t* scratch = loc + 512;                    // 16
+  uint64_t* red = (uint64_t*)(scratch + 16);        // 2 * PT_WARPS + 2
+
+  const uint32_t s = blockIdx.x;
+  if (s >= *p.count) return;
+  const uint32_t start = p.segs.start[s], len = p.segs.len[s];
+  const int w = threadIdx.x >> 5;
+  const int items = (int)((len + PT_THREADS - 1) / PT_THREADS);
+
+  // ---- load keys (coalesced), segment min/max
+  uint64_t key[PT_ITEMS];
+  uint32_t vmask = 0;
+  uint64_t mn = ~0ull, mx = 0;
+#pragma unroll
+  for (int k = 0; k < PT_ITEMS; k++) {
+    uint32_t idx = threadIdx.x + k * PT_THREADS;
+    bool v = idx < len;
+    vmask |= (uint32_t)v << k;
+    key[k] = 0;
+    if (v) {
+      key[k] = load_key(p.mv, p.key, start + idx);
+      mn = key[k] < mn ? key[k] : mn;
+      mx = key[k] > mx ? key[k] : mx;
+    }
+  }
+  mn = warp_min_u64(mn);
+  mx = warp_max_u64(mx);
+  if (lane_id() == 0) { red[w] = mn; red[PT_WARPS + w] = mx; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint64_t a = red[0], b = red[PT_WARPS];
+    for (int i = 1; i < PT_WARPS; i++) {
+      a = red[i] < a ? red[i] : a;
+      b = red[PT_WARPS + i] > b ? red[PT_WARPS + i] : b;
+    }
+    red[2 * PT_WARPS] = a;
+    red[2 * PT_WARPS + 1] = b;
+  }
+  __syncthreads();
+  const uint64_t kmin = red[2 * PT_WARPS];
+  const uint64_t range = red[2 * PT_WARPS + 1] - kmin;
+  const int nbits = range ? 64 - __clzll((long long)range) : 0;
+  if (nbits > L32_MAX_KEY_BITS) {
+    if (threadIdx.x == 0) p.wide[s] = 1;
+    return;
+  }
+  if (threadIdx.x == 0) p.wide[s] = 0;
+  if (nbits == 0 && p.in_place) return;  // all keys equal and the rows are already where they belong
+
+  uint32_t word[PT_ITEMS], pos[PT_ITEMS];
+#pragma unroll
+  for (int k = 0; k < PT_ITEMS; k++)
+    word[k] = ((uint32_t)(key[k] - kmin) << L32_IDX_BITS) | (threadIdx.x + k * PT_THREADS);
+
+  if (nbits == 0) {
+#pragma unroll
+    for (int k = 0; k < PT_ITEMS; k++)
+      if ((vmask >> k) & 1u) sdata[threadIdx.x + k * PT_THREADS] = word[k];
+    __syncthreads();
+  } else {
+    // ---- pass A: low bits, atomic ranks
+    const int ba = nbits < L32_ATOMIC_BITS ? nbits : L32_ATOMIC_BITS;
+    const int radix_a = (1 << ba) < PT_THREADS ? PT_THREADS : (1 << ba);
+    tile_rank_atomic_w<PT_ITEMS>(word, L32_IDX_BITS, (1u << ba) - 1u, vmask, items, radix_a, cnt, scratch, pos);
+#pragma unroll
+    for (int k = 0; k < PT_ITEMS; k++)
+      if ((vmask >> k) & 1u) sdata[pos[k]] = word[k];
+    __syncthreads();
+    // ---- pass B: the remaining high bits, stable
+    const int bb = nbits - ba;
+    if (bb > 0) {
+      const uint32_t chunk = (uint32_t)items * 32;
+      const uint32_t base = w * chunk + lane_id();
+      uint32_t vm2 = 0;
+#pragma unroll
+      for (int k = 0; k < PT_ITEMS; k++) {
+        uint32_t idx = base + k * 32;
+        bool v = k < items && idx < len;
+        vm2 |= (uint32_t)v << k;
+        word[k] = v ? sdata[idx] : 0;
+      }
+      const int radix_b = bb <= 8 ? 256 : 512;
+      tile_rank_w<PT_ITEMS>(word, L32_IDX_BITS + ba, vm2, items, bb, radix_b, cnt, tot, loc, scratch, pos);
+#pragma unroll
+      for (int k = 0; k < PT_ITEMS; k++)
+        if ((vm2 >> k) & 1u) sdata[pos[k]] = word[k];
+      __syncthreads();
+    }
+  }
+  // ---- move every column through the sorted positions
+  for (int c = 0; c < p.mv.n; c++) {
+    switch (p.mv.esize[c]) {
+      case 8: leaf_move_column<uint64_t>((const uint64_t*)p.mv.src[c], (uint64_t*)p.mv.dst[c], start, len, sdata); break;
+      case 4: leaf_move_column<uint32_t>((const uint32_t*)p.mv.src[c], (uint32_t*)p.mv.dst[c], start, len, sdata); break;
+      case 2: leaf_move_column<uint16_t>((const uint16_t*)p.mv.src[c], (uint16_t*)p.mv.dst[c], start, len, sdata); break;
+      default: leaf_move_column<uint8_t>((const uint8_t*)p.mv.src[c], (uint8_t*)p.mv.dst[c], start, len, sdata); break;
+    }
+    __syncthreads();
+  }
+}
+static size_t leaf32_smem_bytes() { return (size_t)LEAF_MAX * 4 + 4096 * 4 + 1024 * 4 + 64 + (2 * PT_WARPS + 2) * 8; }
+
 static size_t leaf_smem_bytes() {
   return (size_t)LEAF_MAX * 8 + (size_t)LEAF_MAX * 2 + (size_t)(PT_WARPS + 2) * MSD_RADIX * 4 + 64 +
          (2 * PT_WARPS + 2) * 8;
 }
 
 // segments whose keys are all equal but that are larger than a leaf: plain copy src -> dst
-__global__ void __launch_bounds__(256) k_copy_segments(MoveArgs mv, SegList segs) {
+__global__ void __launch_bounds__(256) k_copy_segments(MoveArgs mv, SegList segs, const uint32_t* count) {
   uint32_t s = blockIdx.x;
+  if (s >= *count) return;
   uint32_t start = segs.start[s], len = segs.len[s];
   for (int c = 0; c < mv.n; c++) {
     const int es = mv.esize[c];
@@ -411,7 +627,7 @@ static int ilog2_ceil(uint32_t v) {
 void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, const uint16_t* d_bucket, int64_t n,
                        int32_t nb, const uint32_t* d_bucket_off) {
   if (n == 0) return;
-  if (nb > 2048) HS_THROW(HS_EUNSUPPORTED, "single-pass bucket scatter supports at most 2048 buckets per GPU");
+  if (nb > 8192) HS_THROW(HS_EUNSUPPORTED, "the bucket scatter supports at most 8192 buckets per GPU");
   PartParams p;
   memset(&p, 0, sizeof p);
   p.mv.n = ms.n;
@@ -425,7 +641,14 @@ void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, con
   CK(cudaMemcpyAsync(cursor.p, d_bucket_off, (size_t)nb * 4, cudaMemcpyDeviceToDevice, c->stream));
   p.cursor = cursor.as<uint32_t>();
   size_t smem = tile_smem_bytes(p.radix_pad);
-  CK(cudaFuncSetAttribute(k_partition<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  static size_t attr_set_dev[64] = {0};
+  int dev = 0;
+  CK(cudaGetDevice(&dev));
+  size_t& attr_set = attr_set_dev[dev & 63];
+  if (smem > attr_set) {
+    CK(cudaFuncSetAttribute(k_partition<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = smem;
+  }
   unsigned tiles = (unsigned)((n + PT_TILE - 1) / PT_TILE);
   LAUNCH(c, k_partition<0>, tiles, PT_THREADS, smem, p);
 }
@@ -438,49 +661,105 @@ struct ListBufs {
   SegList view() const { return SegList{start.as<uint32_t>(), len.as<uint32_t>(), shift.as<uint32_t>()}; }
 };
 
+static void set_smem_attrs_once() {
+  static bool done_dev[64] = {false};
+  int dev = 0;
+  CK(cudaGetDevice(&dev));
+  bool& done = done_dev[dev & 63];
+  if (done) return;
+  CK(cudaFuncSetAttribute(k_leaf_sort32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)leaf32_smem_bytes()));
+  CK(cudaFuncSetAttribute(k_leaf_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)leaf_smem_bytes()));
+  CK(cudaFuncSetAttribute(k_partition<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes(MSD_RADIX)));
+  done = true;
+}
+
+// Launch the leaf and copy kernels over device-resident lists. The grids are upper bounds: the kernels
+// read the real list lengths from `counters` ([0] leaves, [2] copies), so the host does not have to wait
+// for them before launching.
 static void run_leaf_and_copy(hs_ctx* c, MoveSet& ms, const KeySrc& key, bool src_is_a, const ListBufs& leaf,
-                              uint32_t n_leaf, const ListBufs& copy, uint32_t n_copy) {
-  if (n_leaf) {
+                              uint32_t max_leaf, const ListBufs& copy, uint32_t max_copy, const uint32_t* counters) {
+  if (max_leaf) {
     LeafParams lp;
     memset(&lp, 0, sizeof lp);
     lp.mv = make_move(ms, src_is_a, true);
     lp.key = key;
     lp.segs = leaf.view();
     lp.in_place = src_is_a ? 1 : 0;
-    size_t smem = leaf_smem_bytes();
-    CK(cudaFuncSetAttribute(k_leaf_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    Stage st(c, "leaf_sort");
-    LAUNCH(c, k_leaf_sort, n_leaf, PT_THREADS, smem, lp);
+    lp.count = counters;
+    DBuf wide(c, max_leaf);
+    lp.wide = wide.as<uint8_t>();
+    {
+      Stage st(c, "leaf_sort");
+      LAUNCH(c, k_leaf_sort32, max_leaf, PT_THREADS, leaf32_smem_bytes(), lp);
+    }
+    Stage st(c, "leaf_sort_wide");
+    LAUNCH(c, k_leaf_sort, max_leaf, PT_THREADS, leaf_smem_bytes(), lp);  // only segments flagged as wide do work
   }
-  if (n_copy && !src_is_a) {
+  if (max_copy && !src_is_a) {
     MoveArgs mv = make_move(ms, false, true);
     Stage st(c, "copy_segments");
-    LAUNCH(c, k_copy_segments, n_copy, 256, 0, mv, copy.view());
+    LAUNCH(c, k_copy_segments, max_copy, 256, 0, mv, copy.view(), counters + 2);
   }
 }
 
+// h_seg_off (optional): the segment boundaries on the host. With them level 0 is classified on the host
+// and the sort starts without a device round trip.
 static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_seg_off,
-                         const uint32_t* d_start, const uint32_t* d_len, int64_t nseg, int64_t n) {
+                         const uint32_t* d_start, const uint32_t* d_len, int64_t nseg, int64_t n,
+                         const uint32_t* h_seg_off) {
   if (n == 0 || nseg == 0) return;
-  // level 0 lists
+  set_smem_attrs_once();
   size_t cap_leaf = (size_t)nseg, cap_large = (size_t)(n / LEAF_MAX + 1);
   ListBufs leaf, large, copy;
-  leaf.alloc(c, cap_leaf);
-  large.alloc(c, cap_large);
-  copy.alloc(c, cap_large);
-  DBuf counters(c, 8 * 4);
-  counters.zero();
-  PlanOut po{leaf.view(), large.view(), copy.view(), counters.as<uint32_t>()};
-  hs_stage_begin(c, "sort_plan");
-  LAUNCH(c, k_classify, (unsigned)((nseg + 255) / 256), 256, 0, d_seg_off, d_start, d_len, nseg, (uint32_t)key_bits, po);
-  DBuf tile_prefix(c, (cap_large + 1) * 4);
-  LAUNCH(c, k_tile_prefix, 1, 1024, 0, large.view(), counters.as<uint32_t>(), tile_prefix.as<uint32_t>());
-  uint32_t h[4];
-  CK(cudaMemcpyAsync(h, counters.p, 16, cudaMemcpyDeviceToHost, c->stream));
-  hs_stage_end(c);
-  hs_sync(c);
+  DBuf counters(c, 8 * 4), tile_prefix(c, (cap_large + 1) * 4);
+  uint32_t h[4] = {0, 0, 0, 0};
   bool src_is_a = true;
-  run_leaf_and_copy(c, ms, key, src_is_a, leaf, h[0], copy, h[2]);
+  if (h_seg_off) {
+    // ---- level 0 on the host
+    std::vector<uint32_t> lf, lg, cp, tp;  // packed as start[], len[], shift[]
+    std::vector<uint32_t> lf_s, lf_l, lg_s, lg_l;
+    tp.push_back(0);
+    for (int64_t sidx = 0; sidx < nseg; sidx++) {
+      uint32_t st = h_seg_off[sidx], len = h_seg_off[sidx + 1] - st;
+      if (len < 2) continue;
+      if (len <= LEAF_MAX) { lf_s.push_back(st); lf_l.push_back(len); }
+      else if (key_bits > 0) { lg_s.push_back(st); lg_l.push_back(len); tp.push_back(tp.back() + (len + PT_TILE - 1) / PT_TILE); }
+      // larger than a leaf with no key bits: all keys equal, already in place at level 0
+    }
+    h[0] = (uint32_t)lf_s.size();
+    h[1] = (uint32_t)lg_s.size();
+    h[3] = tp.back();
+    auto upload = [&](ListBufs& lb, const std::vector<uint32_t>& st, const std::vector<uint32_t>& ln) {
+      size_t m = st.size();
+      lb.alloc(c, m ? m : 1);
+      if (!m) return;
+      std::vector<uint32_t> sh(m, (uint32_t)key_bits);
+      CK(cudaMemcpyAsync(lb.start.p, st.data(), m * 4, cudaMemcpyHostToDevice, c->stream));
+      CK(cudaMemcpyAsync(lb.len.p, ln.data(), m * 4, cudaMemcpyHostToDevice, c->stream));
+      CK(cudaMemcpyAsync(lb.shift.p, sh.data(), m * 4, cudaMemcpyHostToDevice, c->stream));
+    };
+    upload(leaf, lf_s, lf_l);
+    upload(large, lg_s, lg_l);
+    copy.alloc(c, 1);
+    CK(cudaMemcpyAsync(counters.p, h, 16, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(tile_prefix.p, tp.data(), tp.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    run_leaf_and_copy(c, ms, key, true, leaf, h[0], copy, 0, counters.as<uint32_t>());
+  } else {
+    leaf.alloc(c, cap_leaf);
+    large.alloc(c, cap_large);
+    copy.alloc(c, cap_large);
+    counters.zero();
+    PlanOut po{leaf.view(), large.view(), copy.view(), counters.as<uint32_t>()};
+    hs_stage_begin(c, "sort_plan");
+    LAUNCH(c, k_classify, (unsigned)((nseg + 255) / 256), 256, 0, d_seg_off, d_start, d_len, nseg, (uint32_t)key_bits, po);
+    LAUNCH(c, k_tile_prefix, 1, 1024, 0, large.view(), counters.as<uint32_t>(), tile_prefix.as<uint32_t>());
+    hs_stage_end(c);
+    // leaves first (the grid is an upper bound), then wait for the counts: the wait overlaps the leaf sort
+    run_leaf_and_copy(c, ms, key, true, leaf, (uint32_t)(nseg > 0x7fffffff ? 0x7fffffff : nseg), copy, 0,
+                      counters.as<uint32_t>());
+    CK(cudaMemcpyAsync(h, counters.p, 16, cudaMemcpyDeviceToHost, c->stream));
+    hs_sync(c);
+  }
   uint32_t n_large = h[1], n_tiles = h[3];
   int level = 0;
   while (n_large > 0) {
@@ -513,21 +792,19 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     hs_stage_begin(c, "msd_plan");
     LAUNCH(c, k_msd_plan, n_large, MSD_RADIX, 0, large.view(), cursor.as<uint32_t>(), npo);
     hs_stage_end(c);
-    size_t smem = tile_smem_bytes(MSD_RADIX);
-    CK(cudaFuncSetAttribute(k_partition<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     hs_stage_begin(c, "msd_scatter");
-    LAUNCH(c, k_partition<1>, n_tiles, PT_THREADS, smem, p);
+    LAUNCH(c, k_partition<1>, n_tiles, PT_THREADS, tile_smem_bytes(MSD_RADIX), p);
     hs_stage_end(c);
     DBuf ntile_prefix(c, (cap_large + 1) * 4);
     hs_stage_begin(c, "msd_plan");
     LAUNCH(c, k_tile_prefix, 1, 1024, 0, nlarge.view(), ncounters.as<uint32_t>(), ntile_prefix.as<uint32_t>());
-    CK(cudaMemcpyAsync(h, ncounters.p, 16, cudaMemcpyDeviceToHost, c->stream));
     hs_stage_end(c);
-    hs_sync(c);
     src_is_a = !src_is_a;
-    run_leaf_and_copy(c, ms, key, src_is_a, nleaf, h[0], ncopy, h[2]);
-    // the lists of this level stay alive until the kernels above are queued; stream order makes the
-    // frees below safe
+    // children that fit a leaf are sorted now; the host learns the counts while they run
+    run_leaf_and_copy(c, ms, key, src_is_a, nleaf, (uint32_t)children, ncopy, (uint32_t)cap_large,
+                      ncounters.as<uint32_t>());
+    CK(cudaMemcpyAsync(h, ncounters.p, 16, cudaMemcpyDeviceToHost, c->stream));
+    hs_sync(c);
     large = std::move(nlarge);
     leaf = std::move(nleaf);
     copy = std::move(ncopy);
@@ -538,10 +815,10 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
 }
 
 void hs_segmented_sort(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_seg_off,
-                       int64_t nseg, int64_t n) {
-  segsort_impl(c, ms, key, key_bits, d_seg_off, nullptr, nullptr, nseg, n);
+                       int64_t nseg, int64_t n, const uint32_t* h_seg_off) {
+  segsort_impl(c, ms, key, key_bits, d_seg_off, nullptr, nullptr, nseg, n, h_seg_off);
 }
 void hs_segmented_sort_list(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_start,
                             const uint32_t* d_len, int64_t nseg, int64_t n) {
-  segsort_impl(c, ms, key, key_bits, nullptr, d_start, d_len, nseg, n);
+  segsort_impl(c, ms, key, key_bits, nullptr, d_start, d_len, nseg, n, nullptr);
 }
