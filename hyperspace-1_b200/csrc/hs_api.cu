@@ -1,5 +1,6 @@
 // hs_api.cu — context lifecycle, column staging, result tables (C ABI glue).
 #include "hs_common.cuh"
+#include <stdlib.h>
 
 struct TableImpl {
   std::vector<void*> dev;     // device buffers owned by the table
@@ -30,7 +31,13 @@ void hs_stages_reset(hs_ctx* c) {
   c->cur_stage = -1;
 }
 
+#include <chrono>
+static double host_now_ms() {
+  return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
 void hs_stage_begin(hs_ctx* c, const char* name) {
+  static int trace = getenv("HSGPU_TRACE") ? 1 : 0;
+  if (trace) fprintf(stderr, "[hsgpu] %10.3f ms  %s\n", host_now_ms(), name);
   if (!c->timing) return;
   StageRec r;
   memset(&r, 0, sizeof r);
@@ -122,6 +129,54 @@ KCol hs_kcol(const DevCol& d) {
   return k;
 }
 
+#define HS_DEV_CACHE_MIN (size_t(1) << 20)
+
+void hs_dev_cache_flush(hs_ctx* c) {
+  for (auto& kv : c->dev_free) cudaFreeAsync(kv.second, c->stream);
+  for (auto& kv : c->dev_free) c->dev_size.erase(kv.second);
+  c->dev_free.clear();
+  c->dev_cached_bytes = 0;
+}
+
+void* hs_dev_alloc(hs_ctx* c, size_t bytes) {
+  if (bytes == 0) bytes = 16;
+  if (bytes >= HS_DEV_CACHE_MIN) {
+    auto it = c->dev_free.lower_bound(bytes);
+    if (it != c->dev_free.end() && it->first <= bytes + bytes / 4) {
+      void* p = it->second;
+      c->dev_cached_bytes -= it->first;
+      c->dev_free.erase(it);
+      return p;
+    }
+  }
+  void* p = nullptr;
+  cudaError_t e = cudaMallocAsync(&p, bytes, c->stream);
+  if (e == cudaErrorMemoryAllocation && !c->dev_free.empty()) {
+    cudaGetLastError();
+    hs_dev_cache_flush(c);
+    cudaStreamSynchronize(c->stream);
+    e = cudaMallocAsync(&p, bytes, c->stream);
+  }
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    HS_THROW(e == cudaErrorMemoryAllocation ? HS_ENOMEM : HS_ECUDA, "cudaMallocAsync(%zu bytes): %s", bytes,
+             cudaGetErrorString(e));
+  }
+  if (bytes >= HS_DEV_CACHE_MIN) c->dev_size[p] = bytes;
+  return p;
+}
+
+void hs_dev_free(hs_ctx* c, void* p) {
+  if (!p) return;
+  auto it = c->dev_size.find(p);
+  if (it == c->dev_size.end()) {
+    cudaFreeAsync(p, c->stream);
+    return;
+  }
+  c->dev_free.insert({it->second, p});
+  c->dev_cached_bytes += it->second;
+}
+
 void* hs_pinned_alloc(hs_ctx* c, size_t bytes) {
   if (bytes == 0) bytes = 16;
   size_t cap = 256;
@@ -191,7 +246,7 @@ hs_table* hs_finish_table(hs_ctx* c, std::vector<OutCol>& cols, int64_t nrows, i
       t->bucket_offsets = ti->boff.data();
     }
   } catch (...) {
-    for (void* p : ti->dev) cudaFreeAsync(p, c->stream);
+    for (void* p : ti->dev) hs_dev_free(c, p);
     for (void* p : ti->pinned) hs_pinned_free(c, p);
     delete ti;
     delete t;
@@ -237,6 +292,7 @@ int32_t hs_ctx_destroy(hs_ctx* c) {
   if (!c) return HS_EINVAL;
   cudaSetDevice(c->device);
   hs_comm_destroy(c);
+  hs_dev_cache_flush(c);
   cudaStreamSynchronize(c->stream);
   for (auto& s : c->stages) { cudaEventDestroy(s.e0); cudaEventDestroy(s.e1); }
   for (auto e : c->ev_free) cudaEventDestroy(e);
@@ -297,7 +353,7 @@ int32_t hs_table_free(hs_ctx* c, hs_table* t) {
   cudaSetDevice(c->device);
   TableImpl* ti = (TableImpl*)t->impl;
   if (ti) {
-    for (void* p : ti->dev) cudaFreeAsync(p, c->stream);
+    for (void* p : ti->dev) hs_dev_free(c, p);
     for (void* p : ti->pinned) hs_pinned_free(c, p);
     delete ti;
   }

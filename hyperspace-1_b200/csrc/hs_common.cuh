@@ -54,6 +54,12 @@ struct hs_ctx {
   int64_t launches = 0;
   std::multimap<size_t, void*> pinned_free;  // cached pinned host blocks by size
   std::map<void*, size_t> pinned_size;
+  // large device blocks are recycled inside the context (all work is ordered on one stream, so a block
+  // freed by one call can be handed to the next without touching the allocator: cudaMallocAsync of
+  // ~GB blocks was measured to cost up to 3 ms per build)
+  std::multimap<size_t, void*> dev_free;
+  std::map<void*, size_t> dev_size;
+  size_t dev_cached_bytes = 0;
   // multi-GPU (hs_dist.cu)
   void* nccl_lib = nullptr;
   void* comm = nullptr;
@@ -83,6 +89,10 @@ struct Stage {
   ~Stage() { hs_stage_end(c); }
 };
 
+void* hs_dev_alloc(hs_ctx* c, size_t bytes);
+void hs_dev_free(hs_ctx* c, void* p);
+void hs_dev_cache_flush(hs_ctx* c);
+
 // stream-ordered device buffer
 struct DBuf {
   hs_ctx* c = nullptr;
@@ -101,12 +111,11 @@ struct DBuf {
     release();
     c = c_;
     bytes = n;
-    if (n == 0) n = 16;
-    CK(cudaMallocAsync(&p, n, c->stream));
+    p = hs_dev_alloc(c, n);
   }
   void zero() { if (p) CK(cudaMemsetAsync(p, 0, bytes ? bytes : 16, c->stream)); }
   void release() {
-    if (p) cudaFreeAsync(p, c->stream);
+    if (p) hs_dev_free(c, p);
     p = nullptr;
     bytes = 0;
   }
