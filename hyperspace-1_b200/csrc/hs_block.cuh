@@ -3,10 +3,11 @@
 #pragma once
 #include "hs_common.cuh"
 
-#define PT_THREADS 256
-#define PT_WARPS 8
-#define PT_ITEMS 16
+#define PT_THREADS 512
+#define PT_WARPS 16
+#define PT_ITEMS 8
 #define PT_TILE (PT_THREADS * PT_ITEMS)  // 4096 rows per tile
+#define PT_SCRATCH 32                    // words of scan scratch (>= PT_WARPS + 1)
 
 __device__ __forceinline__ uint32_t warp_incl_scan_u32(uint32_t v) {
 #pragma unroll
@@ -32,6 +33,22 @@ __device__ __forceinline__ uint32_t block_excl_scan_u32(uint32_t v, uint32_t* sc
   }
   __syncthreads();
   if (total) *total = scratch[PT_WARPS];
+  return inc - v + scratch[w];
+}
+
+// the same scan for a CTA of exactly 256 threads (k_msd_plan: one thread per digit)
+__device__ __forceinline__ uint32_t block256_excl_scan_u32(uint32_t v, uint32_t* scratch) {
+  uint32_t inc = warp_incl_scan_u32(v);
+  int w = threadIdx.x >> 5;
+  __syncthreads();
+  if (lane_id() == 31) scratch[w] = inc;
+  __syncthreads();
+  if (w == 0) {
+    uint32_t s = lane_id() < 8 ? scratch[lane_id()] : 0;
+    uint32_t si = warp_incl_scan_u32(s);
+    if (lane_id() < 8) scratch[lane_id()] = si - s;
+  }
+  __syncthreads();
   return inc - v + scratch[w];
 }
 
@@ -81,14 +98,15 @@ __device__ __forceinline__ void tile_rank(const uint32_t (&digit)[ITEMS], uint32
     tot[d] = run;
   }
   __syncthreads();
-  // exclusive scan of tot over digits: each thread owns radix_pad/PT_THREADS consecutive digits
-  const int per = radix_pad / PT_THREADS;
+  // exclusive scan of tot over digits: each thread owns `per` consecutive digits
+  const int per = (radix_pad + PT_THREADS - 1) / PT_THREADS;
+  const int d0 = threadIdx.x * per, d1 = d0 + per < radix_pad ? d0 + per : radix_pad;
   uint32_t s = 0;
-  for (int j = 0; j < per; j++) s += tot[threadIdx.x * per + j];
+  for (int j = d0; j < d1; j++) s += tot[j];
   uint32_t ex = block_excl_scan_u32(s, scratch, nullptr);
-  for (int j = 0; j < per; j++) {
-    loc[threadIdx.x * per + j] = ex;
-    ex += tot[threadIdx.x * per + j];
+  for (int j = d0; j < d1; j++) {
+    loc[j] = ex;
+    ex += tot[j];
   }
   __syncthreads();
 #pragma unroll
@@ -116,14 +134,15 @@ __device__ __forceinline__ void tile_rank_atomic(const uint32_t (&digit)[ITEMS],
   for (int k = 0; k < ITEMS; k++)
     if (k < items && ((vmask >> k) & 1u)) pos[k] = atomicAdd(&cnt[digit[k]], 1u);
   __syncthreads();
-  const int per = radix_pad / PT_THREADS;
+  const int per = (radix_pad + PT_THREADS - 1) / PT_THREADS;
+  const int d0 = threadIdx.x * per, d1 = d0 + per < radix_pad ? d0 + per : radix_pad;
   uint32_t s = 0;
-  for (int j = 0; j < per; j++) s += cnt[threadIdx.x * per + j];
+  for (int j = d0; j < d1; j++) s += cnt[j];
   uint32_t ex = block_excl_scan_u32(s, scratch, nullptr);
-  for (int j = 0; j < per; j++) {
-    uint32_t c = cnt[threadIdx.x * per + j];
-    if (tot) tot[threadIdx.x * per + j] = c;
-    cnt[threadIdx.x * per + j] = ex;
+  for (int j = d0; j < d1; j++) {
+    uint32_t c = cnt[j];
+    if (tot) tot[j] = c;
+    cnt[j] = ex;
     ex += c;
   }
   __syncthreads();
@@ -143,13 +162,14 @@ __device__ __forceinline__ void tile_rank_atomic_w(const uint32_t (&word)[ITEMS]
   for (int k = 0; k < ITEMS; k++)
     if (k < items && ((vmask >> k) & 1u)) pos[k] = atomicAdd(&cnt[(word[k] >> shift) & mask], 1u);
   __syncthreads();
-  const int per = radix_pad / PT_THREADS;
+  const int per = (radix_pad + PT_THREADS - 1) / PT_THREADS;
+  const int d0 = threadIdx.x * per, d1 = d0 + per < radix_pad ? d0 + per : radix_pad;
   uint32_t s = 0;
-  for (int j = 0; j < per; j++) s += cnt[threadIdx.x * per + j];
+  for (int j = d0; j < d1; j++) s += cnt[j];
   uint32_t ex = block_excl_scan_u32(s, scratch, nullptr);
-  for (int j = 0; j < per; j++) {
-    uint32_t c = cnt[threadIdx.x * per + j];
-    cnt[threadIdx.x * per + j] = ex;
+  for (int j = d0; j < d1; j++) {
+    uint32_t c = cnt[j];
+    cnt[j] = ex;
     ex += c;
   }
   __syncthreads();
@@ -199,13 +219,14 @@ __device__ __forceinline__ void tile_rank_w(const uint32_t (&word)[ITEMS], int s
     tot[d] = run;
   }
   __syncthreads();
-  const int per = radix_pad / PT_THREADS;
+  const int per = (radix_pad + PT_THREADS - 1) / PT_THREADS;
+  const int d0 = threadIdx.x * per, d1 = d0 + per < radix_pad ? d0 + per : radix_pad;
   uint32_t s = 0;
-  for (int j = 0; j < per; j++) s += tot[threadIdx.x * per + j];
+  for (int j = d0; j < d1; j++) s += tot[j];
   uint32_t ex = block_excl_scan_u32(s, scratch, nullptr);
-  for (int j = 0; j < per; j++) {
-    loc[threadIdx.x * per + j] = ex;
-    ex += tot[threadIdx.x * per + j];
+  for (int j = d0; j < d1; j++) {
+    loc[j] = ex;
+    ex += tot[j];
   }
   __syncthreads();
 #pragma unroll

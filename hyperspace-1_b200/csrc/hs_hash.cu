@@ -37,8 +37,9 @@ __device__ __forceinline__ void minmax_flush(uint64_t mn, uint64_t mx, uint64_t*
 
 // MODE 0: out32 = raw hash; 1: out32 = bucket; 2: out16 = bucket, hist[nb] += 1, minmax per fixed key
 template <int MODE>
-__global__ void __launch_bounds__(HASH_THREADS) k_hash_generic(KeySpec ks, int64_t n, int32_t nb, int32_t blo,
-                                                               int32_t nbl, int32_t* __restrict__ out32,
+__global__ void __launch_bounds__(HASH_THREADS) k_hash_generic(KeySpec ks, int64_t n, int32_t nb, FastPmod fm,
+                                                               int32_t blo, int32_t nbl,
+                                                               int32_t* __restrict__ out32,
                                                                uint16_t* __restrict__ out16,
                                                                uint32_t* __restrict__ g_hist, int smem_hist,
                                                                uint64_t* __restrict__ g_minmax) {
@@ -62,7 +63,7 @@ __global__ void __launch_bounds__(HASH_THREADS) k_hash_generic(KeySpec ks, int64
     if (MODE == 0) {
       if (valid) out32[i] = (int32_t)h;
     } else {
-      int32_t b = pmod_i32((int32_t)h, nb);
+      int32_t b = (int32_t)fast_pmod(h, fm);
       if (MODE == 1) {
         if (valid) out32[i] = b;
       } else {
@@ -106,7 +107,7 @@ __global__ void __launch_bounds__(HASH_THREADS) k_hash_generic(KeySpec ks, int64
 // Fast path: one non-null INT64 key. Each thread hashes two rows from one 128-bit load and
 // stores both 16-bit bucket ids with one 32-bit store.
 __global__ void __launch_bounds__(HASH_THREADS) k_hash_i64x2(const uint64_t* __restrict__ keys, int64_t n,
-                                                             int32_t nb, uint16_t* __restrict__ out16,
+                                                             int32_t nb, FastPmod fm, uint16_t* __restrict__ out16,
                                                              uint32_t* __restrict__ g_hist,
                                                              uint64_t* __restrict__ g_minmax) {
   extern __shared__ uint32_t s_hist[];
@@ -123,8 +124,8 @@ __global__ void __launch_bounds__(HASH_THREADS) k_hash_i64x2(const uint64_t* __r
     if (valid) {
       ulonglong2 v;
       asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(k2 + p));
-      b0 = (uint32_t)pmod_i32((int32_t)mm_hash_long(v.x, 42u), nb);
-      b1 = (uint32_t)pmod_i32((int32_t)mm_hash_long(v.y, 42u), nb);
+      b0 = fast_pmod(mm_hash_long(v.x, 42u), fm);
+      b1 = fast_pmod(mm_hash_long(v.y, 42u), fm);
       ((uint32_t*)out16)[p] = b0 | (b1 << 16);
       uint64_t m0 = v.x ^ 0x8000000000000000ull, m1 = v.y ^ 0x8000000000000000ull;
       uint64_t lo = m0 < m1 ? m0 : m1, hi = m0 < m1 ? m1 : m0;
@@ -136,7 +137,7 @@ __global__ void __launch_bounds__(HASH_THREADS) k_hash_i64x2(const uint64_t* __r
   }
   if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
     uint64_t v = keys[n - 1];
-    uint32_t b = (uint32_t)pmod_i32((int32_t)mm_hash_long(v, 42u), nb);
+    uint32_t b = fast_pmod(mm_hash_long(v, 42u), fm);
     out16[n - 1] = (uint16_t)b;
     atomicAdd(&s_hist[b], 1u);
     uint64_t m = v ^ 0x8000000000000000ull;
@@ -170,9 +171,9 @@ KeySpec hs_make_keyspec(const std::vector<DevCol>& cols, int nkeys) {
 
 void hs_hash_to_i32(hs_ctx* c, const KeySpec& ks, int64_t n, int32_t nb, int32_t* d_out) {
   if (n == 0) return;
-  if (nb <= 0) LAUNCH(c, k_hash_generic<0>, hash_grid(n), HASH_THREADS, 0, ks, n, 1, 0, 1, d_out, (uint16_t*)nullptr,
+  if (nb <= 0) LAUNCH(c, k_hash_generic<0>, hash_grid(n), HASH_THREADS, 0, ks, n, 1, make_fastpmod(1), 0, 1, d_out, (uint16_t*)nullptr,
                       (uint32_t*)nullptr, 0, (uint64_t*)nullptr);
-  else LAUNCH(c, k_hash_generic<1>, hash_grid(n), HASH_THREADS, 0, ks, n, nb, 0, nb, d_out, (uint16_t*)nullptr,
+  else LAUNCH(c, k_hash_generic<1>, hash_grid(n), HASH_THREADS, 0, ks, n, nb, make_fastpmod(nb), 0, nb, d_out, (uint16_t*)nullptr,
               (uint32_t*)nullptr, 0, (uint64_t*)nullptr);
 }
 
@@ -193,13 +194,14 @@ void hs_hash_bucket_hist(hs_ctx* c, const KeySpec& ks, const std::vector<DevCol>
               (((uintptr_t)ks.k[0].data) & 15) == 0 && (((uintptr_t)d_bucket) & 3) == 0 && smem <= 48 * 1024;
   if (fast) {
     LAUNCH(c, k_hash_i64x2, hash_grid((n + 1) / 2), HASH_THREADS, smem, (const uint64_t*)ks.k[0].data, n, nb,
-           d_bucket, d_hist, d_minmax);
+           make_fastpmod(nb), d_bucket, d_hist, d_minmax);
     return;
   }
   int smem_hist = smem <= 160 * 1024;
   if (smem_hist && smem > 48 * 1024)
     CK(cudaFuncSetAttribute(k_hash_generic<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  LAUNCH(c, k_hash_generic<2>, hash_grid(n), HASH_THREADS, smem_hist ? smem : 0, ks, n, nb, blo, nbl, (int32_t*)nullptr,
+  LAUNCH(c, k_hash_generic<2>, hash_grid(n), HASH_THREADS, smem_hist ? smem : 0, ks, n, nb, make_fastpmod(nb), blo, nbl,
+         (int32_t*)nullptr,
          d_bucket, d_hist, smem_hist, d_minmax);
 }
 

@@ -99,6 +99,25 @@ __device__ __forceinline__ int32_t pmod_i32(int32_t h, int32_t n) {
   return r < 0 ? r + n : r;
 }
 
+// pmod with a precomputed reciprocal (Lemire's fastmod): exact for every 32-bit input, ~10 instructions
+// instead of the ~35 of a runtime-divisor `%`. c = 2^32 mod n folds the sign of the Java remainder in.
+struct FastPmod {
+  uint64_t M;
+  uint32_t n, c;
+};
+static inline FastPmod make_fastpmod(int32_t n) {
+  FastPmod f;
+  f.n = (uint32_t)n;
+  f.M = 0xFFFFFFFFFFFFFFFFull / (uint32_t)n + 1;
+  f.c = (uint32_t)((1ull << 32) % (uint32_t)n);
+  return f;
+}
+__device__ __forceinline__ uint32_t fast_pmod(uint32_t h, const FastPmod& f) {
+  uint32_t a = (uint32_t)__umul64hi(f.M * h, (uint64_t)f.n);  // h mod n, h read as unsigned
+  if ((int32_t)h < 0) a = a >= f.c ? a - f.c : a + f.n - f.c;  // h = u - 2^32
+  return a;
+}
+
 // ---------------------------------------------------------------- order-preserving maps
 __device__ __forceinline__ uint64_t omap_i64(int64_t v) { return (uint64_t)v ^ 0x8000000000000000ull; }
 __device__ __forceinline__ uint64_t omap_f64(double f) {

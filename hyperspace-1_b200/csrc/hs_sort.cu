@@ -68,7 +68,7 @@ struct TileSmem {
   uint32_t* cnt;            // radix_pad: counters, then first position of every digit
   uint32_t* tot;            // radix_pad: rows per digit
   uint32_t* gbase;          // radix_pad: reserved global run start per digit
-  uint32_t* scratch;        // 16
+  uint32_t* scratch;        // PT_SCRATCH
   uint64_t* bar;            // 2 mbarriers
 };
 __device__ __forceinline__ TileSmem carve(unsigned char* base, int radix_pad) {
@@ -81,11 +81,12 @@ __device__ __forceinline__ TileSmem carve(unsigned char* base, int radix_pad) {
   s.tot = s.cnt + radix_pad;
   s.gbase = s.tot + radix_pad;
   s.scratch = s.gbase + radix_pad;
-  s.bar = (uint64_t*)(s.scratch + 16);
+  s.bar = (uint64_t*)(s.scratch + PT_SCRATCH);
   return s;
 }
 static size_t tile_smem_bytes(int radix_pad) {
-  return (size_t)2 * STAGE_BYTES + (size_t)PT_TILE * 4 + (size_t)PT_TILE * 2 + (size_t)3 * radix_pad * 4 + 64 + 16;
+  return (size_t)2 * STAGE_BYTES + (size_t)PT_TILE * 4 + (size_t)PT_TILE * 2 + (size_t)3 * radix_pad * 4 +
+         PT_SCRATCH * 4 + 16;
 }
 
 struct PartParams {
@@ -252,15 +253,17 @@ __global__ void __launch_bounds__(PT_THREADS) k_msd_hist(const __grid_constant__
   uint32_t sh = p.segs.shift[s];
   int bits = sh < MSD_BITS ? (int)sh : MSD_BITS;
   uint32_t shift = sh - bits;
-  hist[threadIdx.x] = 0;
+  if (threadIdx.x < MSD_RADIX) hist[threadIdx.x] = 0;
   __syncthreads();
   for (uint32_t j = threadIdx.x; j < tile_len; j += PT_THREADS) {
     uint32_t d = (uint32_t)(load_key(p.mv, p.key, tile_start + j) >> shift) & ((1u << bits) - 1u);
     atomicAdd(&hist[d], 1u);
   }
   __syncthreads();
-  uint32_t v = hist[threadIdx.x];
-  if (v) atomicAdd(&p.cursor[(size_t)s * MSD_RADIX + threadIdx.x], v);
+  if (threadIdx.x < MSD_RADIX) {
+    uint32_t v = hist[threadIdx.x];
+    if (v) atomicAdd(&p.cursor[(size_t)s * MSD_RADIX + threadIdx.x], v);
+  }
 }
 
 struct PlanOut {
@@ -285,10 +288,10 @@ __device__ __forceinline__ void classify_push(const PlanOut& o, uint32_t start, 
 
 // turn the histograms of one level into write cursors and child segments
 __global__ void __launch_bounds__(MSD_RADIX) k_msd_plan(SegList segs, uint32_t* cursor, PlanOut out) {
-  __shared__ uint32_t scratch[PT_WARPS + 1];
+  __shared__ uint32_t scratch[16];
   uint32_t s = blockIdx.x;
   uint32_t h = cursor[(size_t)s * MSD_RADIX + threadIdx.x];
-  uint32_t ex = block_excl_scan_u32(h, scratch, nullptr);
+  uint32_t ex = block256_excl_scan_u32(h, scratch);
   uint32_t start = segs.start[s] + ex;
   cursor[(size_t)s * MSD_RADIX + threadIdx.x] = start;
   uint32_t sh = segs.shift[s];
@@ -344,6 +347,7 @@ struct LeafParams {
   int32_t in_place;   // src == dst
   uint8_t* wide;      // per segment: 1 = key range needs the 64-bit kernel (written by k_leaf_sort32)
   const uint32_t* count;  // device: number of segments in the list (the grid is an upper bound)
+  uint32_t* n_wide;       // device: how many segments were flagged wide
 };
 
 // Sort one segment of at most LEAF_MAX rows entirely in shared memory: LSD radix over the bits that
@@ -355,8 +359,8 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort(const __grid_consta
   uint32_t* cnt = (uint32_t*)(sidx + LEAF_MAX);         // PT_WARPS * 256
   uint32_t* tot = cnt + PT_WARPS * MSD_RADIX;
   uint32_t* loc = tot + MSD_RADIX;
-  uint32_t* scratch = loc + MSD_RADIX;                  // 16
-  uint64_t* red = (uint64_t*)(scratch + 16);            // 2 * PT_WARPS + 2
+  uint32_t* scratch = loc + MSD_RADIX;                  // PT_SCRATCH
+  uint64_t* red = (uint64_t*)(scratch + PT_SCRATCH);    // 2 * PT_WARPS + 2
 
   const uint32_t s = blockIdx.x;
   if (s >= *p.count) return;
@@ -455,7 +459,7 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort(const __grid_consta
 
 #define L32_IDX_BITS 12
 #define L32_MAX_KEY_BITS 20
-#define L32_ATOMIC_BITS 11
+#define L32_ATOMIC_BITS 11   // the atomic pass takes min(nbits, 11) bits, or 12 when 20 bits vary
 
 template <typename T>
 __device__ __forceinline__ void leaf_move_column(const T* __restrict__ src, T* __restrict__ dst, uint32_t start,
@@ -478,14 +482,15 @@ __device__ __forceinline__ void leaf_move_column(const T* __restrict__ src, T* _
 // key - min and the row's position are packed into one 32-bit word, the first LSD pass (up to 11 bits)
 // ranks with shared-memory atomics (no stability needed), the remaining <= 9 bits take one stable
 // ballot-ranked pass. Segments with a wider key range are flagged for k_leaf_sort.
-__global__ void __launch_bounds__(PT_THREADS, 3) k_leaf_sort32(const __grid_constant__ LeafParams p) {
+template <int KMODE>
+__global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort32(const __grid_constant__ LeafParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   uint32_t* sdata = (uint32_t*)smem_raw;            // LEAF_MAX packed words
-  uint32_t* cnt = sdata + LEAF_MAX;                 // 4096 words: 2048 atomic counters or 8 x 512 warp counters
-  uint32_t* tot = cnt + 4096;                       // 512
-  uint32_t* loc = tot + 512;                        // 512
-  uint32_t* scratch = loc + 512;                    // 16
-  uint64_t* red = (uint64_t*)(scratch + 16);        // 2 * PT_WARPS + 2
+  uint32_t* cnt = sdata + LEAF_MAX;                 // 4096 words: atomic counters or PT_WARPS x 256 warp counters
+  uint32_t* tot = cnt + 4096;                       // 256
+  uint32_t* loc = tot + 256;                        // 256
+  uint32_t* scratch = loc + 256;                    // PT_SCRATCH
+  uint64_t* red = (uint64_t*)(scratch + PT_SCRATCH);  // 2 * PT_WARPS + 2
 
   const uint32_t s = blockIdx.x;
   if (s >= *p.count) return;
@@ -504,7 +509,10 @@ __global__ void __launch_bounds__(PT_THREADS, 3) k_leaf_sort32(const __grid_cons
     vmask |= (uint32_t)v << k;
     key[k] = 0;
     if (v) {
-      key[k] = load_key(p.mv, p.key, start + idx);
+      const void* kp = p.mv.src[p.key.col];
+      if (KMODE == KS_U64) key[k] = ((const uint64_t*)kp)[start + idx];
+      else if (KMODE == KS_I64) key[k] = (((const uint64_t*)kp)[start + idx] ^ 0x8000000000000000ull) - p.key.min;
+      else key[k] = ((uint64_t)(int64_t)((const int32_t*)kp)[start + idx] ^ 0x8000000000000000ull) - p.key.min;
       mn = key[k] < mn ? key[k] : mn;
       mx = key[k] > mx ? key[k] : mx;
     }
@@ -513,21 +521,19 @@ __global__ void __launch_bounds__(PT_THREADS, 3) k_leaf_sort32(const __grid_cons
   mx = warp_max_u64(mx);
   if (lane_id() == 0) { red[w] = mn; red[PT_WARPS + w] = mx; }
   __syncthreads();
-  if (threadIdx.x == 0) {
-    uint64_t a = red[0], b = red[PT_WARPS];
-    for (int i = 1; i < PT_WARPS; i++) {
-      a = red[i] < a ? red[i] : a;
-      b = red[PT_WARPS + i] > b ? red[PT_WARPS + i] : b;
-    }
-    red[2 * PT_WARPS] = a;
-    red[2 * PT_WARPS + 1] = b;
+  if (w == 0) {
+    uint64_t a = lane_id() < PT_WARPS ? red[lane_id()] : ~0ull;
+    uint64_t b = lane_id() < PT_WARPS ? red[PT_WARPS + lane_id()] : 0;
+    a = warp_min_u64(a);
+    b = warp_max_u64(b);
+    if (lane_id() == 0) { red[2 * PT_WARPS] = a; red[2 * PT_WARPS + 1] = b; }
   }
   __syncthreads();
   const uint64_t kmin = red[2 * PT_WARPS];
   const uint64_t range = red[2 * PT_WARPS + 1] - kmin;
   const int nbits = range ? 64 - __clzll((long long)range) : 0;
   if (nbits > L32_MAX_KEY_BITS) {
-    if (threadIdx.x == 0) p.wide[s] = 1;
+    if (threadIdx.x == 0) { p.wide[s] = 1; atomicAdd(p.n_wide, 1u); }
     return;
   }
   if (threadIdx.x == 0) p.wide[s] = 0;
@@ -545,8 +551,9 @@ __global__ void __launch_bounds__(PT_THREADS, 3) k_leaf_sort32(const __grid_cons
     __syncthreads();
   } else {
     // ---- pass A: low bits, atomic ranks
-    const int ba = nbits < L32_ATOMIC_BITS ? nbits : L32_ATOMIC_BITS;
-    const int radix_a = (1 << ba) < PT_THREADS ? PT_THREADS : (1 << ba);
+    int ba = nbits < L32_ATOMIC_BITS ? nbits : L32_ATOMIC_BITS;
+    if (nbits - ba > 8) ba = nbits - 8;  // the stable pass handles at most 8 bits
+    const int radix_a = 1 << ba;
     tile_rank_atomic_w<PT_ITEMS>(word, L32_IDX_BITS, (1u << ba) - 1u, vmask, items, radix_a, cnt, scratch, pos);
 #pragma unroll
     for (int k = 0; k < PT_ITEMS; k++)
@@ -565,7 +572,7 @@ __global__ void __launch_bounds__(PT_THREADS, 3) k_leaf_sort32(const __grid_cons
         vm2 |= (uint32_t)v << k;
         word[k] = v ? sdata[idx] : 0;
       }
-      const int radix_b = bb <= 8 ? 256 : 512;
+      const int radix_b = 256;
       tile_rank_w<PT_ITEMS>(word, L32_IDX_BITS + ba, vm2, items, bb, radix_b, cnt, tot, loc, scratch, pos);
 #pragma unroll
       for (int k = 0; k < PT_ITEMS; k++)
@@ -584,10 +591,12 @@ __global__ void __launch_bounds__(PT_THREADS, 3) k_leaf_sort32(const __grid_cons
     __syncthreads();
   }
 }
-static size_t leaf32_smem_bytes() { return (size_t)LEAF_MAX * 4 + 4096 * 4 + 1024 * 4 + 64 + (2 * PT_WARPS + 2) * 8; }
+static size_t leaf32_smem_bytes() {
+  return (size_t)LEAF_MAX * 4 + 4096 * 4 + 512 * 4 + PT_SCRATCH * 4 + (2 * PT_WARPS + 2) * 8;
+}
 
 static size_t leaf_smem_bytes() {
-  return (size_t)LEAF_MAX * 8 + (size_t)LEAF_MAX * 2 + (size_t)(PT_WARPS + 2) * MSD_RADIX * 4 + 64 +
+  return (size_t)LEAF_MAX * 8 + (size_t)LEAF_MAX * 2 + (size_t)(PT_WARPS + 2) * MSD_RADIX * 4 + PT_SCRATCH * 4 +
          (2 * PT_WARPS + 2) * 8;
 }
 
@@ -667,39 +676,53 @@ static void set_smem_attrs_once() {
   CK(cudaGetDevice(&dev));
   bool& done = done_dev[dev & 63];
   if (done) return;
-  CK(cudaFuncSetAttribute(k_leaf_sort32, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)leaf32_smem_bytes()));
+  CK(cudaFuncSetAttribute(k_leaf_sort32<KS_U64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)leaf32_smem_bytes()));
+  CK(cudaFuncSetAttribute(k_leaf_sort32<KS_I64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)leaf32_smem_bytes()));
+  CK(cudaFuncSetAttribute(k_leaf_sort32<KS_I32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)leaf32_smem_bytes()));
   CK(cudaFuncSetAttribute(k_leaf_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)leaf_smem_bytes()));
   CK(cudaFuncSetAttribute(k_partition<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes(MSD_RADIX)));
   done = true;
 }
 
 // Launch the leaf and copy kernels over device-resident lists. The grids are upper bounds: the kernels
-// read the real list lengths from `counters` ([0] leaves, [2] copies), so the host does not have to wait
-// for them before launching.
+// read the real list lengths from `counters` ([0] leaves, [2] copies, [4] receives the number of segments
+// the packed kernel could not take), so the host does not have to wait for them before launching.
+struct LeafLaunch {
+  DBuf wide;
+  LeafParams lp;
+  uint32_t max_leaf = 0;
+};
 static void run_leaf_and_copy(hs_ctx* c, MoveSet& ms, const KeySrc& key, bool src_is_a, const ListBufs& leaf,
-                              uint32_t max_leaf, const ListBufs& copy, uint32_t max_copy, const uint32_t* counters) {
+                              uint32_t max_leaf, const ListBufs& copy, uint32_t max_copy, uint32_t* counters,
+                              LeafLaunch& ll) {
+  ll.max_leaf = max_leaf;
   if (max_leaf) {
-    LeafParams lp;
+    LeafParams& lp = ll.lp;
     memset(&lp, 0, sizeof lp);
     lp.mv = make_move(ms, src_is_a, true);
     lp.key = key;
     lp.segs = leaf.view();
     lp.in_place = src_is_a ? 1 : 0;
     lp.count = counters;
-    DBuf wide(c, max_leaf);
-    lp.wide = wide.as<uint8_t>();
-    {
-      Stage st(c, "leaf_sort");
-      LAUNCH(c, k_leaf_sort32, max_leaf, PT_THREADS, leaf32_smem_bytes(), lp);
-    }
-    Stage st(c, "leaf_sort_wide");
-    LAUNCH(c, k_leaf_sort, max_leaf, PT_THREADS, leaf_smem_bytes(), lp);  // only segments flagged as wide do work
+    lp.n_wide = counters + 4;
+    ll.wide.alloc(c, max_leaf);
+    lp.wide = ll.wide.as<uint8_t>();
+    Stage st(c, "leaf_sort");
+    if (key.mode == KS_U64) LAUNCH(c, k_leaf_sort32<KS_U64>, max_leaf, PT_THREADS, leaf32_smem_bytes(), lp);
+    else if (key.mode == KS_I64) LAUNCH(c, k_leaf_sort32<KS_I64>, max_leaf, PT_THREADS, leaf32_smem_bytes(), lp);
+    else LAUNCH(c, k_leaf_sort32<KS_I32>, max_leaf, PT_THREADS, leaf32_smem_bytes(), lp);
   }
   if (max_copy && !src_is_a) {
     MoveArgs mv = make_move(ms, false, true);
     Stage st(c, "copy_segments");
     LAUNCH(c, k_copy_segments, max_copy, 256, 0, mv, copy.view(), counters + 2);
   }
+}
+// after the counters have been read back: the 64-bit kernel, only if some segment needs it
+static void run_wide_leaves(hs_ctx* c, LeafLaunch& ll, uint32_t n_wide) {
+  if (!n_wide || !ll.max_leaf) return;
+  Stage st(c, "leaf_sort_wide");
+  LAUNCH(c, k_leaf_sort, ll.max_leaf, PT_THREADS, leaf_smem_bytes(), ll.lp);
 }
 
 // h_seg_off (optional): the segment boundaries on the host. With them level 0 is classified on the host
@@ -712,8 +735,9 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
   size_t cap_leaf = (size_t)nseg, cap_large = (size_t)(n / LEAF_MAX + 1);
   ListBufs leaf, large, copy;
   DBuf counters(c, 8 * 4), tile_prefix(c, (cap_large + 1) * 4);
-  uint32_t h[4] = {0, 0, 0, 0};
+  uint32_t h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   bool src_is_a = true;
+  LeafLaunch ll0;
   if (h_seg_off) {
     // ---- level 0 on the host
     std::vector<uint32_t> lf, lg, cp, tp;  // packed as start[], len[], shift[]
@@ -741,9 +765,15 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     upload(leaf, lf_s, lf_l);
     upload(large, lg_s, lg_l);
     copy.alloc(c, 1);
-    CK(cudaMemcpyAsync(counters.p, h, 16, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(counters.p, h, 32, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemcpyAsync(tile_prefix.p, tp.data(), tp.size() * 4, cudaMemcpyHostToDevice, c->stream));
-    run_leaf_and_copy(c, ms, key, true, leaf, h[0], copy, 0, counters.as<uint32_t>());
+    run_leaf_and_copy(c, ms, key, true, leaf, h[0], copy, 0, counters.as<uint32_t>(), ll0);
+    if (h[0]) {
+      uint32_t nw = 0;
+      CK(cudaMemcpyAsync(&nw, counters.as<uint32_t>() + 4, 4, cudaMemcpyDeviceToHost, c->stream));
+      hs_sync(c);
+      run_wide_leaves(c, ll0, nw);
+    }
   } else {
     leaf.alloc(c, cap_leaf);
     large.alloc(c, cap_large);
@@ -756,9 +786,10 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     hs_stage_end(c);
     // leaves first (the grid is an upper bound), then wait for the counts: the wait overlaps the leaf sort
     run_leaf_and_copy(c, ms, key, true, leaf, (uint32_t)(nseg > 0x7fffffff ? 0x7fffffff : nseg), copy, 0,
-                      counters.as<uint32_t>());
-    CK(cudaMemcpyAsync(h, counters.p, 16, cudaMemcpyDeviceToHost, c->stream));
+                      counters.as<uint32_t>(), ll0);
+    CK(cudaMemcpyAsync(h, counters.p, 32, cudaMemcpyDeviceToHost, c->stream));
     hs_sync(c);
+    run_wide_leaves(c, ll0, h[4]);
   }
   uint32_t n_large = h[1], n_tiles = h[3];
   int level = 0;
@@ -772,7 +803,7 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     p.mv = make_move(ms, src_is_a, !src_is_a);
     p.key = key;
     p.radix = MSD_RADIX;
-    p.radix_pad = MSD_RADIX;
+    p.radix_pad = MSD_RADIX;  // digits of an MSD level
     p.bits = MSD_BITS;
     p.cursor = cursor.as<uint32_t>();
     p.segs = large.view();
@@ -801,10 +832,12 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     hs_stage_end(c);
     src_is_a = !src_is_a;
     // children that fit a leaf are sorted now; the host learns the counts while they run
+    LeafLaunch ll;
     run_leaf_and_copy(c, ms, key, src_is_a, nleaf, (uint32_t)children, ncopy, (uint32_t)cap_large,
-                      ncounters.as<uint32_t>());
-    CK(cudaMemcpyAsync(h, ncounters.p, 16, cudaMemcpyDeviceToHost, c->stream));
+                      ncounters.as<uint32_t>(), ll);
+    CK(cudaMemcpyAsync(h, ncounters.p, 32, cudaMemcpyDeviceToHost, c->stream));
     hs_sync(c);
+    run_wide_leaves(c, ll, h[4]);
     large = std::move(nlarge);
     leaf = std::move(nleaf);
     copy = std::move(ncopy);
