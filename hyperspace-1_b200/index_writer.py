@@ -1,0 +1,78 @@
+"""GpuIndexWriter — the replacement of CreateActionBase.write (HS/actions/CreateActionBase.scala:122-140):
+select(indexed ++ included) -> hs_build_index (hash-partition + per-bucket sort on the GPU) -> one Parquet file
+per non-empty bucket, named as Spark's bucketed writer names them, so that
+BucketingUtils.getBucketId recovers the bucket from the file name. Parquet encode/decode is host work
+(pyarrow) and is timed separately from the kernels."""
+import os
+import time
+import uuid
+
+import numpy as np
+import pyarrow as pa
+import pyarrow.parquet as pq
+
+from . import log_entry as le
+
+
+def write_buckets(columns, names, bucket_offsets, out_dir, task_of_bucket=None, append=False):
+    """Write rows [off[b], off[b+1]) of every non-empty bucket b to
+    part-<task%05d>-<uuid>_<bucket%05d>.c000.snappy.parquet. Returns (files, seconds spent encoding)."""
+    os.makedirs(out_dir, exist_ok=True)
+    job = uuid.uuid4()
+    table = pa.table(columns, names=names)
+    files = []
+    t0 = time.perf_counter()
+    off = np.asarray(bucket_offsets, dtype=np.int64)
+    for b in range(len(off) - 1):
+        n = int(off[b + 1] - off[b])
+        if n == 0:
+            continue      # empty buckets produce no file
+        task = b if task_of_bucket is None else task_of_bucket(b)
+        path = os.path.join(out_dir, f"part-{task:05d}-{job}_{b:05d}.c000.snappy.parquet")
+        pq.write_table(table.slice(int(off[b]), n), path, compression="snappy", version="1.0",
+                       data_page_version="1.0", use_dictionary=True)
+        files.append(path)
+    return files, time.perf_counter() - t0
+
+
+def build_and_write(session, table, indexed, included, num_buckets, out_dir):
+    """table: pyarrow.Table holding at least indexed ++ included (resolved spellings)."""
+    names = list(indexed) + list(included)
+    cols = [table[c].combine_chunks() if isinstance(table[c], pa.ChunkedArray) else table[c] for c in names]
+    arrays, boff = session.ctx.build_index(cols, len(indexed), num_buckets)
+    files, enc_s = write_buckets(arrays, names, boff, out_dir)
+    return files, {"rows": len(cols[0]) if cols else 0, "parquet_encode_s": enc_s,
+                   "gpu_stages": session.ctx.last_timings()}
+
+
+def read_index(entry, columns=None, files=None):
+    """Read the files of an index entry grouped by bucket. Returns (runs, names) where every run is
+    (arrays, bucket_offsets): run k holds the k-th file of every bucket, so an index with one file per bucket
+    is one run and an incrementally refreshed index is several."""
+    props = entry["derivedDataset"]["properties"]
+    nb = props["numBuckets"]
+    names = list(props["columns"]["indexed"]) + list(props["columns"]["included"])
+    want = names if columns is None else [n for n in names if n in columns]
+    infos = le.content_files(entry["content"]) if files is None else files
+    per_bucket = {}
+    for fi in sorted(infos, key=lambda f: f["name"]):
+        b = le.bucket_id_of(fi["name"])
+        per_bucket.setdefault(b, []).append(le.from_uri(fi["name"]))
+    nruns = max((len(v) for v in per_bucket.values()), default=0)
+    runs = []
+    t0 = time.perf_counter()
+    for k in range(max(nruns, 1)):
+        pieces, off = [], [0]
+        for b in range(nb):
+            fl = per_bucket.get(b, [])
+            if k < len(fl):
+                t = pq.read_table(fl[k], columns=want)
+                pieces.append(t)
+                off.append(off[-1] + t.num_rows)
+            else:
+                off.append(off[-1])
+        if not pieces:
+            continue
+        t = pa.concat_tables(pieces)
+        runs.append(([t[c].combine_chunks() for c in want], np.asarray(off, dtype=np.int64)))
+    return runs, want, time.perf_counter() - t0

@@ -6,3 +6,7 @@ _real = _os.path.join(_os.path.dirname(_os.path.dirname(_os.path.abspath(__file_
 __path__.insert(0, _real)
 
 from . import abi  # noqa: E402,F401
+
+from .index_config import IndexConfig, IllegalArgumentException  # noqa: E402,F401
+from .dataframe import Session, Col  # noqa: E402,F401
+from .hyperspace import Hyperspace, HyperspaceException, NoChangesException  # noqa: E402,F401

@@ -1,0 +1,179 @@
+"""End to end through the reference-shaped API on the GPU: quick start (examples/scala/src/main/scala/App.scala),
+the verifyIndexUsage invariant (HT/index/E2EHyperspaceRulesTest.scala:1004-1019: result with indexes == result
+without), incremental refresh leaving several files per bucket (:411-480), optimize, and the lifecycle states."""
+import os
+
+import numpy as np
+import pyarrow as pa
+import pyarrow.parquet as pq
+import pytest
+
+from fixtures import EMPLOYEES, departments_table, employees_table, lineitem, orders, sample_table
+
+pytestmark = pytest.mark.gpu
+
+
+def _rows(t):
+    return sorted(zip(*[t[c].to_pylist() for c in t.column_names]), key=lambda r: tuple((x is None, x) for x in r))
+
+
+def _verify_index_usage(session, df, expect_indexes):
+    session.disable_hyperspace()
+    base = df.collect()
+    assert "IndexScan" not in df.explain_string()
+    session.enable_hyperspace()
+    plan = df.explain_string()
+    for name in expect_indexes:
+        assert f"Name: {name}," in plan, plan
+    got = df.collect()
+    assert got.column_names == base.column_names
+    assert _rows(got) == _rows(base)
+    return got
+
+
+@pytest.fixture()
+def env(tmp_path, hs):
+    from hyperspace_1_b200 import Session
+    s = Session(system_path=str(tmp_path / "indexes"))
+    yield s, tmp_path
+    if s._ctx is not None:
+        s._ctx.close()
+
+
+def test_quick_start(env):
+    from hyperspace_1_b200 import Hyperspace, IndexConfig, log_entry as le
+    s, tmp = env
+    os.makedirs(tmp / "departments")
+    os.makedirs(tmp / "employees")
+    pq.write_table(departments_table(), tmp / "departments" / "part-0.parquet")
+    pq.write_table(employees_table(), tmp / "employees" / "part-0.parquet")
+    dept, emp = s.read_parquet(str(tmp / "departments")), s.read_parquet(str(tmp / "employees"))
+    hs = Hyperspace(s)
+    hs.createIndex(dept, IndexConfig("deptIndex", ["deptId"], ["deptName"]))
+    hs.createIndex(emp, IndexConfig("empIndex", ["deptId"], ["empName"]))
+    # on-disk layout: log 0 = CREATING, 1 = ACTIVE, latestStable, v__=0 with 3 bucket files
+    d = tmp / "indexes" / "deptIndex"
+    lm = le.IndexLogManager(str(d))
+    assert lm.get_log(0)["state"] == "CREATING" and lm.get_log(1)["state"] == "ACTIVE"
+    assert os.path.exists(d / "_hyperspace_log" / "latestStable")
+    names = sorted(os.listdir(d / "v__=0"))
+    assert [n[:10] for n in names] == ["part-00053", "part-00122", "part-00181"]
+    assert all(n.endswith(".c000.snappy.parquet") for n in names)
+    b53 = pq.read_table(d / "v__=0" / names[0])
+    assert b53.column_names == ["deptId", "deptName"] and b53["deptId"].to_pylist() == [20, 40]
+    listed = [os.path.basename(f["name"]) for f in le.content_files(lm.get_log(1)["content"])]
+    assert sorted(listed) == names
+    assert sorted(hs.indexes()["name"].to_pylist()) == ["deptIndex", "empIndex"]
+    with pytest.raises(Exception):
+        hs.createIndex(dept, IndexConfig("DEPTINDEX", ["deptId"], []))   # names are case-insensitive
+    # filter and join of the quick start
+    f = _verify_index_usage(s, dept.filter("deptId = 20").select("deptName"), ["deptIndex"])
+    assert f["deptName"].to_pylist() == ["Research"]
+    j = emp.join(dept, emp["deptId"] == dept["deptId"]).select(emp["empName"], dept["deptName"])
+    got = _verify_index_usage(s, j, ["empIndex", "deptIndex"])
+    deptname = {10: "Accounting", 20: "Research", 30: "Sales"}
+    assert _rows(got) == sorted((n, deptname[k]) for _, n, k in EMPLOYEES)
+    out = []
+    hs.explain(j, redirectFunc=out.append)
+    assert "GpuBucketedSortMergeJoin" in out[0] and "Plan without indexes" in out[0]
+
+
+def test_string_and_composite_indexes_through_the_api(env):
+    from hyperspace_1_b200 import Hyperspace, IndexConfig
+    s, tmp = env
+    os.makedirs(tmp / "sample")
+    pq.write_table(sample_table(), tmp / "sample" / "part-0.parquet")
+    df = s.read_parquet(str(tmp / "sample"))
+    s.conf["spark.hyperspace.index.numBuckets"] = "5"       # python/hyperspace/testing/utils.py:15
+    hs = Hyperspace(s)
+    hs.createIndex(df, IndexConfig("qIndex", ["Query"], ["clicks", "imprs"]))
+    hs.createIndex(df, IndexConfig("ciIndex", ["clicks", "Query"], ["Date"]))
+    _verify_index_usage(s, df.filter("Query = 'facebook'").select("clicks", "Query"), ["qIndex"])
+    _verify_index_usage(s, df.filter("clicks >= 3000 AND Query = 'ibraco'").select("Date", "Query"), ["ciIndex"])
+    # column names resolve case-insensitively to the source spelling (CreateIndexTest.scala:99-111)
+    hs.createIndex(df, IndexConfig("caseIndex", ["rguid"], ["DATE"]))
+    e = hs.index("caseIndex")
+    assert e["derivedDataset"]["properties"]["columns"] == {"indexed": ["RGUID"], "included": ["Date"]}
+
+
+def test_incremental_refresh_then_join_then_optimize(env):
+    from hyperspace_1_b200 import Hyperspace, IndexConfig, log_entry as le
+    s, tmp = env
+    s.conf["spark.hyperspace.index.numBuckets"] = "16"
+    lcols, keys = lineitem(6000)
+    lt = pa.table(lcols, names=["l_orderkey", "l_extendedprice", "l_discount"])
+    n = lt.num_rows
+    os.makedirs(tmp / "lineitem")
+    os.makedirs(tmp / "orders")
+    pq.write_table(lt.slice(0, n * 9 // 10), tmp / "lineitem" / "part-0.parquet")
+    pq.write_table(pa.table(orders(keys), names=["o_orderkey", "o_totalprice"]), tmp / "orders" / "part-0.parquet")
+    hs = Hyperspace(s)
+    li = s.read_parquet(str(tmp / "lineitem"))
+    od = s.read_parquet(str(tmp / "orders"))
+    hs.createIndex(li, IndexConfig("liIndex", ["l_orderkey"], ["l_extendedprice", "l_discount"]))
+    hs.createIndex(od, IndexConfig("oIndex", ["o_orderkey"], ["o_totalprice"]))
+    q = lambda a, b: a.join(b, a["l_orderkey"] == b["o_orderkey"]).select("l_orderkey", "l_extendedprice", "o_totalprice")
+    _verify_index_usage(s, q(li, od), ["liIndex", "oIndex"])
+    # append 10 % (BASELINE config 5 shape): the old index no longer matches, incremental refresh indexes the delta
+    pq.write_table(lt.slice(n * 9 // 10), tmp / "lineitem" / "part-1.parquet")
+    li2 = s.read_parquet(str(tmp / "lineitem"))
+    s.enable_hyperspace()
+    assert "liIndex" not in q(li2, od).explain_string()
+    hs.refreshIndex("liIndex", "incremental")
+    d = tmp / "indexes" / "liIndex"
+    assert sorted(os.listdir(d)) == ["_hyperspace_log", "v__=0", "v__=1"]
+    e = hs.index("liIndex")
+    files = le.content_files(e["content"])
+    assert {os.path.basename(os.path.dirname(f["name"])) for f in files} == {"v__=0", "v__=1"}
+    assert e["state"] == "ACTIVE" and e["id"] == 3
+    assert sum(pq.read_metadata(le.from_uri(f["name"])).num_rows for f in files) == n
+    got = _verify_index_usage(s, q(li2, od), ["liIndex", "oIndex"])     # two runs per bucket merged on the GPU
+    assert got.num_rows == n
+    assert hs.refreshIndex("liIndex", "incremental") is not None       # nothing changed: logged no-op
+    assert hs.index("liIndex")["id"] == 3
+    # optimize: one file per bucket again, same answers
+    hs.optimizeIndex("liIndex", "full")
+    e = hs.index("liIndex")
+    files = le.content_files(e["content"])
+    per_bucket = {}
+    for f in files:
+        per_bucket.setdefault(le.bucket_id_of(f["name"]), []).append(f)
+    assert all(len(v) == 1 for v in per_bucket.values())
+    assert {os.path.basename(os.path.dirname(f["name"])) for f in files} == {"v__=2"}
+    _verify_index_usage(s, q(li2, od), ["liIndex", "oIndex"])
+    for f in files:   # every file sorted on the key, every row in the bucket its name says
+        k = pq.read_table(le.from_uri(f["name"]))["l_orderkey"].to_numpy()
+        assert (np.diff(k) >= 0).all()
+    # full refresh after a delete in the source
+    os.remove(tmp / "lineitem" / "part-1.parquet")
+    with pytest.raises(Exception):
+        hs.refreshIndex("liIndex", "incremental")     # deletes need lineage
+    hs.cancel("liIndex") if hs.index("liIndex")["state"] != "ACTIVE" else None
+    hs.refreshIndex("liIndex", "full")
+    li3 = s.read_parquet(str(tmp / "lineitem"))
+    assert _verify_index_usage(s, q(li3, od), ["liIndex", "oIndex"]).num_rows == n * 9 // 10
+
+
+def test_lifecycle_states(env):
+    from hyperspace_1_b200 import Hyperspace, HyperspaceException, IndexConfig
+    s, tmp = env
+    os.makedirs(tmp / "departments")
+    pq.write_table(departments_table(), tmp / "departments" / "part-0.parquet")
+    dept = s.read_parquet(str(tmp / "departments"))
+    hs = Hyperspace(s)
+    hs.createIndex(dept, IndexConfig("deptIndex", ["deptId"], ["deptName"]))
+    q = dept.filter("deptId = 30").select("deptName")
+    s.enable_hyperspace()
+    assert "deptIndex" in q.explain_string()
+    hs.deleteIndex("deptIndex")
+    assert hs.index("deptIndex")["state"] == "DELETED" and "deptIndex" not in q.explain_string()
+    with pytest.raises(HyperspaceException):
+        hs.refreshIndex("deptIndex", "full")
+    hs.restoreIndex("deptIndex")
+    assert hs.index("deptIndex")["state"] == "ACTIVE" and "deptIndex" in q.explain_string()
+    hs.deleteIndex("deptIndex")
+    hs.vacuumIndex("deptIndex")
+    assert hs.index("deptIndex")["state"] == "DOESNOTEXIST"
+    assert not os.path.exists(tmp / "indexes" / "deptIndex" / "v__=0")
+    hs.createIndex(dept, IndexConfig("deptIndex", ["deptId"], ["deptName"]))   # the name is free again
+    assert q.collect()["deptName"].to_pylist() == ["Sales"]
