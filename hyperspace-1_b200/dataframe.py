@@ -148,7 +148,7 @@ class Relation:
         files = self.files if files is None else files
         if not files:
             return self.schema.empty_table() if columns is None else self.schema.empty_table().select(columns)
-        return pa.concat_tables([pq.read_table(f, columns=columns) for f in files])
+        return pa.concat_tables([pq.ParquetFile(f).read(columns=columns) for f in files])
 
 
 class Scan:

@@ -66,7 +66,7 @@ def read_index(entry, columns=None, files=None):
         for b in range(nb):
             fl = per_bucket.get(b, [])
             if k < len(fl):
-                t = pq.read_table(fl[k], columns=want)
+                t = pq.ParquetFile(fl[k]).read(columns=want)
                 pieces.append(t)
                 off.append(off[-1] + t.num_rows)
             else:

@@ -59,7 +59,7 @@ def test_quick_start(env):
     names = sorted(os.listdir(d / "v__=0"))
     assert [n[:10] for n in names] == ["part-00053", "part-00122", "part-00181"]
     assert all(n.endswith(".c000.snappy.parquet") for n in names)
-    b53 = pq.read_table(d / "v__=0" / names[0])
+    b53 = pq.ParquetFile(d / "v__=0" / names[0]).read()
     assert b53.column_names == ["deptId", "deptName"] and b53["deptId"].to_pylist() == [20, 40]
     listed = [os.path.basename(f["name"]) for f in le.content_files(lm.get_log(1)["content"])]
     assert sorted(listed) == names
@@ -142,7 +142,7 @@ def test_incremental_refresh_then_join_then_optimize(env):
     assert {os.path.basename(os.path.dirname(f["name"])) for f in files} == {"v__=2"}
     _verify_index_usage(s, q(li2, od), ["liIndex", "oIndex"])
     for f in files:   # every file sorted on the key, every row in the bucket its name says
-        k = pq.read_table(le.from_uri(f["name"]))["l_orderkey"].to_numpy()
+        k = pq.ParquetFile(le.from_uri(f["name"])).read()["l_orderkey"].to_numpy()
         assert (np.diff(k) >= 0).all()
     # full refresh after a delete in the source
     os.remove(tmp / "lineitem" / "part-1.parquet")
