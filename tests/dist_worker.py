@@ -1,0 +1,87 @@
+"""Worker for the multi-rank tests, launched by torch.distributed.run (one process per rank).
+  mode gloo : host-side sharding logic on CPU; the per-rank compute is the ORACLE (test infrastructure)
+  mode nccl : hs_build_index_dist on one GPU per rank, checked against the oracle"""
+import os
+import sys
+
+import numpy as np
+import pyarrow as pa
+import torch
+import torch.distributed as dist
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+sys.path.insert(0, HERE)
+
+from hyperspace_1_b200 import dist as hsdist  # noqa: E402
+from oracle import oracle  # noqa: E402
+import parity  # noqa: E402
+
+NB = 64
+
+
+def shard(rank, world, n=30000):
+    rng = np.random.default_rng(100 + rank)
+    k1 = rng.integers(0, 1 << 12, size=n).astype(np.int32)
+    k2 = rng.integers(0, 1 << 30, size=n)
+    v = rng.random(n)
+    mask = rng.random(n) < 0.03
+    return [pa.array(k1), pa.array(k2, mask=mask), pa.array(v)]
+
+
+def gather_all(cols):
+    world = dist.get_world_size()
+    out = [None] * world
+    dist.all_gather_object(out, [c.to_pylist() for c in cols])
+    return [pa.array(sum((o[i] for o in out), []), type=cols[i].type) for i in range(len(cols))]
+
+
+def main():
+    mode = sys.argv[1]
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    if mode == "nccl":
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", rank)))
+        dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ.get("LOCAL_RANK", rank))))
+    else:
+        dist.init_process_group("gloo")
+    cols = shard(rank, world)
+    allcols = gather_all(cols)
+    perm, woff = oracle.build_index(allcols, 2, NB)
+    want = oracle.take(allcols, perm)
+    lo, hi = hsdist.bucket_range(rank, world, NB)
+    assert all(hsdist.owner_of(b, world, NB) == rank for b in range(lo, hi))
+    if mode == "gloo":
+        # the exchange the GPU path performs, spelled out on the host: rows grouped by owner, all-to-all
+        b = oracle.bucket_ids(cols[:2], NB)
+        own = b.astype(np.int64) * world // NB
+        pieces = [[c.take(pa.array(np.nonzero(own == r)[0])).to_pylist() for c in cols] for r in range(world)]
+        recv = [None] * world
+        dist.all_gather_object(recv, pieces)
+        mine = [pa.array(sum((recv[src][rank][i] for src in range(world)), []), type=cols[i].type) for i in range(3)]
+        p2, o2 = oracle.build_index(mine, 2, NB)
+        got = oracle.take(mine, p2)
+        goff = o2
+    else:
+        from hyperspace_1_b200 import native
+        ctx = native.Context(int(os.environ.get("LOCAL_RANK", rank)))
+        hsdist.init_comm(ctx, torch.device("cuda", int(os.environ.get("LOCAL_RANK", rank))))
+        got, goff = hsdist.build_index_dist(ctx, cols, 2, NB)
+        sent, ms = ctx.comm_last_exchange()
+        assert sent > 0 and ms > 0
+        ctx.comm_destroy()
+        ctx.close()
+    # this rank must hold exactly the global index restricted to its bucket range
+    assert (np.diff(goff)[:lo] == 0).all() and (np.diff(goff)[hi:] == 0).all()
+    assert np.array_equal(np.diff(goff)[lo:hi], np.diff(woff)[lo:hi])
+    a, b_ = int(woff[lo]), int(woff[hi])
+    want_mine = [c.slice(a, b_ - a) for c in want]
+    parity.assert_keys_identical(got, want_mine, 2, f"rank {rank}")
+    parity.assert_same_multiset(got, want_mine, goff - goff[lo] * 0, np.concatenate([np.zeros(lo, np.int64), woff[lo:hi + 1] - woff[lo], np.full(NB - hi, woff[hi] - woff[lo])]), f"rank {rank}")
+    dist.barrier()
+    if rank == 0:
+        print(f"DIST_OK mode={mode} world={world}")
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

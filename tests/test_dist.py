@@ -1,0 +1,49 @@
+"""The N > 1 path: bucket ownership and the row exchange, world_size 2 on CPU (gloo, oracle compute) and, where
+two GPUs are present, hs_build_index_dist over NCCL."""
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _run(mode, world):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), os.path.join(HERE, "dist_worker.py"), mode]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert f"DIST_OK mode={mode} world={world}" in r.stdout
+
+
+def test_owner_map():
+    from hyperspace_1_b200 import dist as d
+    for nb, n in ((200, 8), (8192, 8), (1000, 4), (200, 1), (7, 3)):
+        owners = [d.owner_of(b, n, nb) for b in range(nb)]
+        assert owners == sorted(owners) and set(owners) == set(range(n))     # contiguous, every rank owns some
+        for r in range(n):
+            lo, hi = d.bucket_range(r, n, nb)
+            assert owners[lo:hi] == [r] * (hi - lo) and owners.count(r) == hi - lo
+    assert d.bucket_range(3, 8, 200) == (75, 100)      # 200 / 8 = 25 buckets per GPU
+
+
+def test_sharded_build_world2_gloo():
+    _run("gloo", 2)
+
+
+@pytest.mark.gpu
+def test_sharded_build_world2_nccl():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    _run("nccl", 2)
