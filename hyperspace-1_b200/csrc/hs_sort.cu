@@ -7,17 +7,31 @@
 // stage each column through shared memory in digit order, write runs out coalesced. The sort is an MSD
 // radix partition (8 bits per level, only segments larger than a tile) finished by an in-shared-memory
 // LSD radix sort of each leaf segment over the bits that actually vary inside it.
+#include <algorithm>
+
 #include "hs_block.cuh"
 #include "hs_kernels.h"
 
 #define LEAF_MAX PT_TILE
 #define MSD_BITS 8
 #define MSD_RADIX 256
+#define MSD_TARGET_ROWS 2800   // aimed-at child size of an MSD level (a leaf holds at most 4096 rows)
+
+// Digit width of the MSD level that splits a segment of `len` rows whose keys still differ in their low
+// `r` bits: as many bits (at most 8) as keep the expected child, len / 2^bits, near MSD_TARGET_ROWS. A huge
+// segment takes all 8 bits; a segment just above a leaf is only halved, so its children stay full leaves
+// instead of 256 crumbs. Every kernel of a level derives the same value from (len, r).
+__host__ __device__ __forceinline__ int msd_bits(uint32_t len, uint32_t r) {
+  int b = 1;
+  while (b < MSD_BITS && ((uint64_t)len >> b) > MSD_TARGET_ROWS) b++;
+  return b < (int)r ? b : (int)r;
+}
 
 struct SegList {           // device arrays
   uint32_t* start;
   uint32_t* len;
-  uint32_t* shift;         // unsorted low key bits of the segment
+  uint32_t* shift;         // unsorted low bits of (key - base) inside the segment
+  uint64_t* base;          // subtracted from the key before digits are taken (0 until a level re-ranges)
 };
 
 struct MoveArgs {
@@ -149,6 +163,7 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
   extern __shared__ __align__(128) unsigned char smem_raw[];
   TileSmem sm = carve(smem_raw, p.radix_pad);
   uint32_t tile_start, tile_len, shift = 0;
+  uint64_t seg_base = 0;
   int bits = p.bits;
   uint32_t* cursor = p.cursor;
   if (MODE == 0) {
@@ -163,8 +178,9 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
     uint32_t left = slen - t * PT_TILE;
     tile_len = left < PT_TILE ? left : PT_TILE;
     uint32_t sh = p.segs.shift[s];
-    bits = sh < MSD_BITS ? (int)sh : MSD_BITS;
+    bits = msd_bits(slen, sh);
     shift = sh - bits;
+    seg_base = p.segs.base[s];
     cursor = p.cursor + (size_t)s * MSD_RADIX;
   }
   const int ncols = p.mv.n;
@@ -204,7 +220,7 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
         if (p.key.mode == KS_U64) key = ((const uint64_t*)ks)[idx];
         else if (p.key.mode == KS_I64) key = (((const uint64_t*)ks)[idx] ^ 0x8000000000000000ull) - p.key.min;
         else key = ((uint64_t)(int64_t)((const int32_t*)ks)[idx] ^ 0x8000000000000000ull) - p.key.min;
-        digit[k] = (uint32_t)(key >> shift) & ((1u << bits) - 1u);
+        digit[k] = (uint32_t)((key - seg_base) >> shift) & ((1u << bits) - 1u);
       }
     }
   }
@@ -251,12 +267,13 @@ __global__ void __launch_bounds__(PT_THREADS) k_msd_hist(const __grid_constant__
   uint32_t left = slen - t * PT_TILE;
   uint32_t tile_len = left < PT_TILE ? left : PT_TILE;
   uint32_t sh = p.segs.shift[s];
-  int bits = sh < MSD_BITS ? (int)sh : MSD_BITS;
+  int bits = msd_bits(slen, sh);
   uint32_t shift = sh - bits;
+  const uint64_t seg_base = p.segs.base[s];
   if (threadIdx.x < MSD_RADIX) hist[threadIdx.x] = 0;
   __syncthreads();
   for (uint32_t j = threadIdx.x; j < tile_len; j += PT_THREADS) {
-    uint32_t d = (uint32_t)(load_key(p.mv, p.key, tile_start + j) >> shift) & ((1u << bits) - 1u);
+    uint32_t d = (uint32_t)((load_key(p.mv, p.key, tile_start + j) - seg_base) >> shift) & ((1u << bits) - 1u);
     atomicAdd(&hist[d], 1u);
   }
   __syncthreads();
@@ -266,14 +283,19 @@ __global__ void __launch_bounds__(PT_THREADS) k_msd_hist(const __grid_constant__
   }
 }
 
+#define SMALL_MAX 64   // segments up to this many rows are sorted by one warp each (k_leaf_small)
 struct PlanOut {
-  SegList leaf, large, copy;
-  uint32_t* counters;  // [0] leaf, [1] large, [2] copy, [3] tiles of large
+  SegList leaf, large, copy, small;
+  uint32_t* counters;  // [0] leaf, [1] large, [2] copy, [3] tiles of large, [4] wide leaves, [5] small
 };
 
-__device__ __forceinline__ void classify_push(const PlanOut& o, uint32_t start, uint32_t len, uint32_t shift) {
+__device__ __forceinline__ void classify_push(const PlanOut& o, uint32_t start, uint32_t len, uint32_t shift,
+                                              uint64_t base) {
   if (len == 0) return;
-  if (len <= LEAF_MAX) {
+  if (len <= SMALL_MAX) {
+    uint32_t i = atomicAdd(&o.counters[5], 1u);
+    o.small.start[i] = start; o.small.len[i] = len; o.small.shift[i] = shift;
+  } else if (len <= LEAF_MAX) {
     uint32_t i = atomicAdd(&o.counters[0], 1u);
     o.leaf.start[i] = start; o.leaf.len[i] = len; o.leaf.shift[i] = shift;
   } else if (shift == 0) {
@@ -281,7 +303,7 @@ __device__ __forceinline__ void classify_push(const PlanOut& o, uint32_t start, 
     o.copy.start[i] = start; o.copy.len[i] = len; o.copy.shift[i] = 0;
   } else {
     uint32_t i = atomicAdd(&o.counters[1], 1u);
-    o.large.start[i] = start; o.large.len[i] = len; o.large.shift[i] = shift;
+    o.large.start[i] = start; o.large.len[i] = len; o.large.shift[i] = shift; o.large.base[i] = base;
     atomicAdd(&o.counters[3], (len + PT_TILE - 1) / PT_TILE);
   }
 }
@@ -295,8 +317,8 @@ __global__ void __launch_bounds__(MSD_RADIX) k_msd_plan(SegList segs, uint32_t* 
   uint32_t start = segs.start[s] + ex;
   cursor[(size_t)s * MSD_RADIX + threadIdx.x] = start;
   uint32_t sh = segs.shift[s];
-  uint32_t bits = sh < MSD_BITS ? sh : MSD_BITS;
-  classify_push(out, start, h, sh - bits);
+  uint32_t bits = (uint32_t)msd_bits(segs.len[s], sh);
+  classify_push(out, start, h, sh - bits, segs.base[s]);
 }
 
 // level 0: classify the caller's segments
@@ -308,7 +330,40 @@ __global__ void __launch_bounds__(256) k_classify(const uint32_t* seg_off, const
   if (seg_off) { start = seg_off[s]; len = seg_off[s + 1] - start; }
   else { start = lstart[s]; len = llen[s]; }
   if (len < 2) return;  // nothing to sort; level 0 runs in place (src == dst == buffer A)
-  classify_push(out, start, len, key_bits);
+  classify_push(out, start, len, key_bits, 0);
+}
+
+// Deeper levels only see segments that one level could not break up (skewed or duplicate-heavy keys): measure
+// the real key range of each, so that the next digit is taken from bits that actually vary.
+__global__ void __launch_bounds__(PT_THREADS) k_seg_range(const __grid_constant__ PartParams p, uint64_t* rmin,
+                                                          uint64_t* rmax) {
+  uint32_t s = find_segment(p.tile_prefix, p.nseg, blockIdx.x);
+  uint32_t t = blockIdx.x - p.tile_prefix[s];
+  uint32_t slen = p.segs.len[s];
+  uint32_t tile_start = p.segs.start[s] + t * PT_TILE;
+  uint32_t left = slen - t * PT_TILE;
+  uint32_t tile_len = left < PT_TILE ? left : PT_TILE;
+  uint64_t mn = ~0ull, mx = 0;
+  for (uint32_t j = threadIdx.x; j < tile_len; j += PT_THREADS) {
+    uint64_t k = load_key(p.mv, p.key, tile_start + j);
+    mn = k < mn ? k : mn;
+    mx = k > mx ? k : mx;
+  }
+  mn = warp_min_u64(mn);
+  mx = warp_max_u64(mx);
+  if (lane_id() == 0 && mn <= mx) {
+    atomicMin((unsigned long long*)&rmin[s], (unsigned long long)mn);
+    atomicMax((unsigned long long*)&rmax[s], (unsigned long long)mx);
+  }
+}
+__global__ void __launch_bounds__(256) k_seg_rerange(SegList segs, uint32_t nseg, const uint64_t* rmin,
+                                                     const uint64_t* rmax) {
+  uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= nseg) return;
+  uint64_t mn = rmin[s], mx = rmax[s];
+  uint64_t range = mx >= mn ? mx - mn : 0;
+  segs.base[s] = mn;
+  segs.shift[s] = range ? 64 - __clzll((long long)range) : 0;
 }
 
 // exclusive prefix of tiles over the large list (single CTA; the list is short)
@@ -600,6 +655,36 @@ static size_t leaf_smem_bytes() {
          (2 * PT_WARPS + 2) * 8;
 }
 
+// Tiny segments (tie groups of a string sort, buckets of a small table): one warp sorts one segment of at
+// most SMALL_MAX rows by counting, for every row, the rows that precede it (key, then position).
+__global__ void __launch_bounds__(PT_THREADS) k_leaf_small(const __grid_constant__ LeafParams p) {
+  const uint32_t s = blockIdx.x * PT_WARPS + (threadIdx.x >> 5);
+  if (s >= *p.count) return;
+  const uint32_t start = p.segs.start[s], len = p.segs.len[s];
+  const uint32_t lane = lane_id();
+  const uint32_t i0 = lane, i1 = lane + 32;
+  uint64_t k0 = i0 < len ? load_key(p.mv, p.key, start + i0) : ~0ull;
+  uint64_t k1 = i1 < len ? load_key(p.mv, p.key, start + i1) : ~0ull;
+  uint32_t r0 = 0, r1 = 0;
+  for (uint32_t j = 0; j < len; j++) {
+    uint64_t kj = __shfl_sync(0xffffffffu, j < 32 ? k0 : k1, j & 31);
+    r0 += (kj < k0) || (kj == k0 && j < i0);
+    r1 += (kj < k1) || (kj == k1 && j < i1);
+  }
+  for (int c = 0; c < p.mv.n; c++) {
+    const int es = p.mv.esize[c];
+    const unsigned char* src = (const unsigned char*)p.mv.src[c] + (size_t)start * es;
+    unsigned char* dst = (unsigned char*)p.mv.dst[c] + (size_t)start * es;
+    uint64_t v0 = 0, v1 = 0;
+    if (i0 < len) memcpy(&v0, src + (size_t)i0 * es, es);
+    if (i1 < len) memcpy(&v1, src + (size_t)i1 * es, es);
+    __syncwarp();  // all reads before any write: src == dst is safe
+    if (i0 < len) memcpy(dst + (size_t)r0 * es, &v0, es);
+    if (i1 < len) memcpy(dst + (size_t)r1 * es, &v1, es);
+    __syncwarp();
+  }
+}
+
 // segments whose keys are all equal but that are larger than a leaf: plain copy src -> dst
 __global__ void __launch_bounds__(256) k_copy_segments(MoveArgs mv, SegList segs, const uint32_t* count) {
   uint32_t s = blockIdx.x;
@@ -663,11 +748,14 @@ void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, con
 }
 
 struct ListBufs {
-  DBuf start, len, shift;
-  void alloc(hs_ctx* c, size_t cap) {
+  DBuf start, len, shift, base;
+  void alloc(hs_ctx* c, size_t cap, bool with_base = false) {
     start.alloc(c, cap * 4); len.alloc(c, cap * 4); shift.alloc(c, cap * 4);
+    if (with_base) { base.alloc(c, cap * 8); base.zero(); }
   }
-  SegList view() const { return SegList{start.as<uint32_t>(), len.as<uint32_t>(), shift.as<uint32_t>()}; }
+  SegList view() const {
+    return SegList{start.as<uint32_t>(), len.as<uint32_t>(), shift.as<uint32_t>(), base.as<uint64_t>()};
+  }
 };
 
 static void set_smem_attrs_once() {
@@ -694,8 +782,19 @@ struct LeafLaunch {
 };
 static void run_leaf_and_copy(hs_ctx* c, MoveSet& ms, const KeySrc& key, bool src_is_a, const ListBufs& leaf,
                               uint32_t max_leaf, const ListBufs& copy, uint32_t max_copy, uint32_t* counters,
-                              LeafLaunch& ll) {
+                              LeafLaunch& ll, const ListBufs* small = nullptr, uint32_t max_small = 0) {
   ll.max_leaf = max_leaf;
+  if (small && max_small) {
+    LeafParams sp;
+    memset(&sp, 0, sizeof sp);
+    sp.mv = make_move(ms, src_is_a, true);
+    sp.key = key;
+    sp.segs = small->view();
+    sp.in_place = src_is_a ? 1 : 0;
+    sp.count = counters + 5;
+    Stage st(c, "leaf_small");
+    LAUNCH(c, k_leaf_small, (max_small + PT_WARPS - 1) / PT_WARPS, PT_THREADS, 0, sp);
+  }
   if (max_leaf) {
     LeafParams& lp = ll.lp;
     memset(&lp, 0, sizeof lp);
@@ -733,7 +832,7 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
   if (n == 0 || nseg == 0) return;
   set_smem_attrs_once();
   size_t cap_leaf = (size_t)nseg, cap_large = (size_t)(n / LEAF_MAX + 1);
-  ListBufs leaf, large, copy;
+  ListBufs leaf, large, copy, small;
   DBuf counters(c, 8 * 4), tile_prefix(c, (cap_large + 1) * 4);
   uint32_t h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   bool src_is_a = true;
@@ -741,18 +840,20 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
   if (h_seg_off) {
     // ---- level 0 on the host
     std::vector<uint32_t> lf, lg, cp, tp;  // packed as start[], len[], shift[]
-    std::vector<uint32_t> lf_s, lf_l, lg_s, lg_l;
+    std::vector<uint32_t> lf_s, lf_l, lg_s, lg_l, sm_s, sm_l;
     tp.push_back(0);
     for (int64_t sidx = 0; sidx < nseg; sidx++) {
       uint32_t st = h_seg_off[sidx], len = h_seg_off[sidx + 1] - st;
       if (len < 2) continue;
-      if (len <= LEAF_MAX) { lf_s.push_back(st); lf_l.push_back(len); }
+      if (len <= SMALL_MAX) { sm_s.push_back(st); sm_l.push_back(len); }
+      else if (len <= LEAF_MAX) { lf_s.push_back(st); lf_l.push_back(len); }
       else if (key_bits > 0) { lg_s.push_back(st); lg_l.push_back(len); tp.push_back(tp.back() + (len + PT_TILE - 1) / PT_TILE); }
       // larger than a leaf with no key bits: all keys equal, already in place at level 0
     }
     h[0] = (uint32_t)lf_s.size();
     h[1] = (uint32_t)lg_s.size();
     h[3] = tp.back();
+    h[5] = (uint32_t)sm_s.size();
     auto upload = [&](ListBufs& lb, const std::vector<uint32_t>& st, const std::vector<uint32_t>& ln) {
       size_t m = st.size();
       lb.alloc(c, m ? m : 1);
@@ -764,10 +865,13 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     };
     upload(leaf, lf_s, lf_l);
     upload(large, lg_s, lg_l);
+    large.base.alloc(c, (lg_s.size() ? lg_s.size() : 1) * 8);
+    large.base.zero();
+    upload(small, sm_s, sm_l);
     copy.alloc(c, 1);
     CK(cudaMemcpyAsync(counters.p, h, 32, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemcpyAsync(tile_prefix.p, tp.data(), tp.size() * 4, cudaMemcpyHostToDevice, c->stream));
-    run_leaf_and_copy(c, ms, key, true, leaf, h[0], copy, 0, counters.as<uint32_t>(), ll0);
+    run_leaf_and_copy(c, ms, key, true, leaf, h[0], copy, 0, counters.as<uint32_t>(), ll0, &small, h[5]);
     if (h[0]) {
       uint32_t nw = 0;
       CK(cudaMemcpyAsync(&nw, counters.as<uint32_t>() + 4, 4, cudaMemcpyDeviceToHost, c->stream));
@@ -776,17 +880,20 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     }
   } else {
     leaf.alloc(c, cap_leaf);
-    large.alloc(c, cap_large);
+    large.alloc(c, cap_large, true);
     copy.alloc(c, cap_large);
+    small.alloc(c, cap_leaf);
     counters.zero();
-    PlanOut po{leaf.view(), large.view(), copy.view(), counters.as<uint32_t>()};
+    PlanOut po{leaf.view(), large.view(), copy.view(), small.view(), counters.as<uint32_t>()};
     hs_stage_begin(c, "sort_plan");
     LAUNCH(c, k_classify, (unsigned)((nseg + 255) / 256), 256, 0, d_seg_off, d_start, d_len, nseg, (uint32_t)key_bits, po);
     LAUNCH(c, k_tile_prefix, 1, 1024, 0, large.view(), counters.as<uint32_t>(), tile_prefix.as<uint32_t>());
     hs_stage_end(c);
     // leaves first (the grid is an upper bound), then wait for the counts: the wait overlaps the leaf sort
-    run_leaf_and_copy(c, ms, key, true, leaf, (uint32_t)(nseg > 0x7fffffff ? 0x7fffffff : nseg), copy, 0,
-                      counters.as<uint32_t>(), ll0);
+    // sizes are not known on the host yet: the leaf grid is bounded by the rows (a leaf has > SMALL_MAX rows)
+    uint32_t max_leaf0 = (uint32_t)std::min<int64_t>(nseg, n / SMALL_MAX + 1);
+    run_leaf_and_copy(c, ms, key, true, leaf, max_leaf0, copy, 0, counters.as<uint32_t>(), ll0, &small,
+                      (uint32_t)std::min<int64_t>(nseg, 0x7fffffff));
     CK(cudaMemcpyAsync(h, counters.p, 32, cudaMemcpyDeviceToHost, c->stream));
     hs_sync(c);
     run_wide_leaves(c, ll0, h[4]);
@@ -794,7 +901,7 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
   uint32_t n_large = h[1], n_tiles = h[3];
   int level = 0;
   while (n_large > 0) {
-    if (++level > 10) HS_THROW(HS_ECUDA, "segmented sort did not converge");
+    if (++level > 80) HS_THROW(HS_ECUDA, "segmented sort did not converge");
     // histograms -> cursors + child lists
     DBuf cursor(c, (size_t)n_large * MSD_RADIX * 4);
     cursor.zero();
@@ -809,17 +916,29 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     p.segs = large.view();
     p.tile_prefix = tile_prefix.as<uint32_t>();
     p.nseg = n_large;
+    if (level >= 2) {
+      // what is still large after a level is skewed: take the next digit from its real key range
+      DBuf rmin(c, (size_t)n_large * 8), rmax(c, (size_t)n_large * 8);
+      CK(cudaMemsetAsync(rmin.p, 0xFF, (size_t)n_large * 8, c->stream));
+      rmax.zero();
+      hs_stage_begin(c, "msd_range");
+      LAUNCH(c, k_seg_range, n_tiles, PT_THREADS, 0, p, rmin.as<uint64_t>(), rmax.as<uint64_t>());
+      LAUNCH(c, k_seg_rerange, (n_large + 255) / 256, 256, 0, large.view(), n_large, rmin.as<uint64_t>(),
+             rmax.as<uint64_t>());
+      hs_stage_end(c);
+    }
     hs_stage_begin(c, "msd_hist");
     LAUNCH(c, k_msd_hist, n_tiles, PT_THREADS, 0, p);
     hs_stage_end(c);
-    ListBufs nleaf, nlarge, ncopy;
+    ListBufs nleaf, nlarge, ncopy, nsmall;
     size_t children = (size_t)n_large * MSD_RADIX;
     nleaf.alloc(c, children);
-    nlarge.alloc(c, cap_large);
+    nlarge.alloc(c, cap_large, true);
     ncopy.alloc(c, cap_large);
+    nsmall.alloc(c, children);
     DBuf ncounters(c, 8 * 4);
     ncounters.zero();
-    PlanOut npo{nleaf.view(), nlarge.view(), ncopy.view(), ncounters.as<uint32_t>()};
+    PlanOut npo{nleaf.view(), nlarge.view(), ncopy.view(), nsmall.view(), ncounters.as<uint32_t>()};
     hs_stage_begin(c, "msd_plan");
     LAUNCH(c, k_msd_plan, n_large, MSD_RADIX, 0, large.view(), cursor.as<uint32_t>(), npo);
     hs_stage_end(c);
@@ -833,14 +952,15 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     src_is_a = !src_is_a;
     // children that fit a leaf are sorted now; the host learns the counts while they run
     LeafLaunch ll;
-    run_leaf_and_copy(c, ms, key, src_is_a, nleaf, (uint32_t)children, ncopy, (uint32_t)cap_large,
-                      ncounters.as<uint32_t>(), ll);
+    run_leaf_and_copy(c, ms, key, src_is_a, nleaf, (uint32_t)std::min<size_t>(children, n / SMALL_MAX + 1), ncopy,
+                      (uint32_t)cap_large, ncounters.as<uint32_t>(), ll, &nsmall, (uint32_t)children);
     CK(cudaMemcpyAsync(h, ncounters.p, 32, cudaMemcpyDeviceToHost, c->stream));
     hs_sync(c);
     run_wide_leaves(c, ll, h[4]);
     large = std::move(nlarge);
     leaf = std::move(nleaf);
     copy = std::move(ncopy);
+    small = std::move(nsmall);
     tile_prefix = std::move(ntile_prefix);
     n_large = h[1];
     n_tiles = h[3];
