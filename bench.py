@@ -137,7 +137,7 @@ def gen_lineitem_device(torch, n_rows, seed, device):
     return l_orderkey, price, disc, keys
 
 
-def reference_arm(args):
+def reference_arm(args, out):
     """--impl reference: the reference's CPU path for this metric on the host cores. The reference is
     Scala on Spark 2.4.2 and cannot run here (no JVM/Spark in the image), so the timed code is the
     oracle port of that path (oracle/hs_oracle.c) with every host thread, on a bounded sample."""
@@ -172,10 +172,20 @@ def reference_arm(args):
                              "sample": f"{n} rows of the cfg2 workload per step (hash, bucket, per-bucket sort, take)"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "note": "reference Spark local[*]: unavailable on this box (no JVM/Spark); timed = oracle port"}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=out, flush=True)
+
+
+def _claim_stdout():
+    """Libraries (NCCL prints its version banner) write to fd 1; the contract is ONE JSON line there. Send fd 1
+    to stderr for the run and keep the real stdout for the result line."""
+    real = os.fdopen(os.dup(1), "w")
+    sys.stdout.flush()
+    os.dup2(2, 1)
+    return real
 
 
 def main():
+    real_stdout = _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
@@ -189,7 +199,7 @@ def main():
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
-        reference_arm(args)
+        reference_arm(args, real_stdout)
         return
 
     import numpy as np
@@ -281,7 +291,7 @@ def main():
     algo = {"hash_hist": KEY_BYTES, "bucket_scatter": 2 * ROW_BYTES, "msd_scatter": 2 * ROW_BYTES,
             "leaf_sort": 2 * ROW_BYTES, "msd_hist": KEY_BYTES}
     kernel_of = {"hash_hist": "k_hash_i64x2", "bucket_scatter": "k_partition<0>", "msd_scatter": "k_partition<1>",
-                 "leaf_sort": "k_leaf_sort", "msd_hist": "k_msd_hist"}
+                 "leaf_sort": "k_leaf_sort32<KS_I64>", "msd_hist": "k_msd_hist"}
     per_stage = {k: {"ms_per_step": v[0] / args.steps, "launches_per_step": v[1] / args.steps}
                  for k, v in stage_ms.items()}
     dom = max((k for k in per_stage if k in algo), key=lambda k: per_stage[k]["ms_per_step"])
@@ -411,7 +421,7 @@ def main():
             ms = sum(x[1] for x in xchg) / len(xchg)
             line["all_to_all"] = {"bytes_sent_per_gpu": b, "ms": ms, "bus_GBps": b / (ms * 1e-3) / 1e9 if ms else None,
                                   "frac_of_900": (b / (ms * 1e-3) / 1e9 / 900.0) if ms else None}
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=real_stdout, flush=True)
     ctx.comm_destroy()
     ctx.close()
     if dist is not None:

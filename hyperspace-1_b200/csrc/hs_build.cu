@@ -5,6 +5,8 @@
 // Data layout in HBM: every fixed-width column is its own array (SoA). Validity bitmaps and boolean
 // columns travel as one byte per row and are re-packed at the end; string columns do not travel —
 // a 32-bit source-row column does, and the bytes are gathered once at the end.
+#include <algorithm>
+
 #include "hs_keys.cuh"
 #include "hs_kernels.h"
 
@@ -29,6 +31,24 @@ __global__ void __launch_bounds__(256) k_bytes_to_bits(const uint8_t* __restrict
     }
     bits[b] = (uint8_t)v;
   }
+}
+// same, also counting the zero bytes (= NULL rows) into *zeros
+__global__ void __launch_bounds__(256) k_bytes_to_bits_count(const uint8_t* __restrict__ in, int64_t n,
+                                                             uint8_t* __restrict__ bits, unsigned long long* zeros) {
+  int64_t nb = (n + 7) >> 3;
+  int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  unsigned z = 0;
+  for (; b < nb; b += stride) {
+    unsigned v = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+      int64_t i = b * 8 + k;
+      if (i < n) { if (in[i]) v |= 1u << k; else z++; }
+    }
+    bits[b] = (uint8_t)v;
+  }
+  if (z) atomicAdd(zeros, (unsigned long long)z);
 }
 __global__ void __launch_bounds__(256) k_iota_u32(uint32_t* out, int64_t n) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -114,7 +134,8 @@ static int bitlen64(uint64_t v) {
 
 // ------------------------------------------------------------------ key layout (host)
 // Packs the fixed-width key columns into static chunks (MSB first, right aligned); see hs_keys.cuh.
-static KeyLayout make_layout(const std::vector<DevCol>& cols, int nk, const uint64_t* minmax) {
+static KeyLayout make_layout(const std::vector<DevCol>& cols, int nk, const uint64_t* minmax,
+                             const std::vector<uint8_t>& has_nulls) {
   KeyLayout L;
   memset(&L, 0, sizeof L);
   L.nkeys = nk;
@@ -140,7 +161,7 @@ static KeyLayout make_layout(const std::vector<DevCol>& cols, int nk, const uint
     uint64_t mn = minmax[2 * k], mx = minmax[2 * k + 1];
     int width = mn <= mx ? bitlen64(mx - mn) : 0;
     g.min = mn <= mx ? mn : 0;
-    if (cols[k].validity) runs[run].push_back({k, 1, true, 0});
+    if (has_nulls[k]) runs[run].push_back({k, 1, true, 0});
     if (width > 0) runs[run].push_back({k, width, false, 0});
   }
   L.nruns = run + 1;
@@ -186,16 +207,17 @@ struct MovedCol {
 
 // The build over staged device columns; shared by hs_build_index, hs_merge_runs and the multi-GPU build.
 void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t nb, int32_t blo, int32_t nbl,
-                   std::vector<OutCol>& out, std::vector<int64_t>& boff) {
+                   std::vector<OutCol>& out, std::vector<int64_t>& boff, BuildExchange* xchg) {
   const int ncols = (int)cols.size();
-  const int64_t n = cols[0].length;
+  int64_t n = cols[0].length;
   boff.assign((size_t)nb + 1, 0);
   out.resize(ncols);
-  if (n == 0) {
+  if (n == 0 && !xchg) {
     for (int i = 0; i < ncols; i++) hs_copy_column(c, cols[i], out[i]);
     return;
   }
   KeySpec ks = hs_make_keyspec(cols, n_indexed);
+  if (xchg) { blo = 0; nbl = nb; }   // the local phase sees every bucket; ownership is applied by the exchange
 
   // ---- K1: bucket ids, histogram, key ranges
   DBuf bucket(c, (size_t)n * 2 + 16), hist(c, (size_t)nbl * 4), minmax(c, (2 * HS_MAX_KEYS + 1) * 8);
@@ -211,6 +233,10 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
   hs_sync(c);
   if (h_minmax[2 * HS_MAX_KEYS] != 0)
     HS_THROW(HS_EINVAL, "%llu rows hash outside this rank's bucket range", (unsigned long long)h_minmax[2 * HS_MAX_KEYS]);
+  std::vector<uint8_t> has_nulls((size_t)ncols);
+  for (int i = 0; i < ncols; i++) has_nulls[i] = cols[i].validity != nullptr;
+  // key ranges and NULL presence become global: every rank builds the same nkey and moves the same columns
+  if (xchg) xchg->share_stats(c, h_hist, h_minmax, has_nulls);
   // local offsets (device, u32) drive the kernels; the global table has empty ranges outside [blo, blo+nbl)
   std::vector<uint32_t> off32((size_t)nbl + 1, 0);
   for (int b = 0; b < nbl; b++) off32[b + 1] = off32[b] + h_hist[b];
@@ -222,11 +248,13 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
   CK(cudaMemcpyAsync(d_off.p, off32.data(), ((size_t)nbl + 1) * 4, cudaMemcpyHostToDevice, c->stream));
 
   // ---- key layout and the set of travelling columns
-  KeyLayout L = make_layout(cols, n_indexed, h_minmax);
-  bool fast_key = n_indexed == 1 && !cols[0].validity && (cols[0].type == HS_INT64 || cols[0].type == HS_INT32);
+  KeyLayout L = make_layout(cols, n_indexed, h_minmax, has_nulls);
+  bool fast_key = n_indexed == 1 && !has_nulls[0] && (cols[0].type == HS_INT64 || cols[0].type == HS_INT32);
   bool any_varlen = false;
   for (auto& dc : cols) any_varlen |= hs_is_varlen(dc.type);
   bool need_srcrow = any_varlen || !L.single_chunk;
+  if (xchg && need_srcrow)
+    HS_THROW(HS_EUNSUPPORTED, "string columns and keys wider than 64 bits are not supported in the multi-GPU build");
 
   std::vector<MovedCol> mv;
   mv.reserve(HS_MAX_MOVE);
@@ -241,10 +269,11 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
     Stage s(c, "prepare");
     for (int i = 0; i < ncols; i++) {
       DevCol& dc = cols[i];
-      if (dc.validity) {
+      if (has_nulls[i]) {
         MovedCol& m = add(i, 1, 1, nullptr);
         m.tmp.alloc(c, (size_t)n);
-        LAUNCH(c, k_bits_to_bytes, grid1d(n), 256, 0, dc.validity, n, m.tmp.as<uint8_t>());
+        if (dc.validity) LAUNCH(c, k_bits_to_bytes, grid1d(n), 256, 0, dc.validity, n, m.tmp.as<uint8_t>());
+        else CK(cudaMemsetAsync(m.tmp.p, 1, (size_t)(n ? n : 1), c->stream));   // NULLs only on other ranks
         m.src = m.tmp.p;
       }
       if (hs_is_varlen(dc.type)) continue;
@@ -284,11 +313,10 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
   std::vector<const void*> srcs(mv.size());
   int key_mv = -1, more_mv = -1, srcrow_mv = -1;
   for (size_t i = 0; i < mv.size(); i++) {
-    mv[i].a.alloc(c, (size_t)n * mv[i].esize);
-    mv[i].b.alloc(c, (size_t)n * mv[i].esize);
+    mv[i].a.alloc(c, (size_t)n * mv[i].esize + 16);
     ms.esize[i] = mv[i].esize;
     ms.a[i] = mv[i].a.p;
-    ms.b[i] = mv[i].b.p;
+    ms.b[i] = nullptr;
     srcs[i] = mv[i].src;
     if (mv[i].role == 3) key_mv = (int)i;
     if (mv[i].role == 4) more_mv = (int)i;
@@ -316,6 +344,30 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
   }
   for (auto& m : mv) m.tmp.release();
   bucket.release();
+
+  // ---- multi-GPU: bucket runs travel to the GPU that owns the bucket and land at their final place
+  if (xchg) {
+    std::vector<DBuf*> bufs;
+    std::vector<int> es;
+    for (auto& m : mv) { bufs.push_back(&m.a); es.push_back(m.esize); }
+    std::vector<uint32_t> seg_off;
+    n = xchg->exchange(c, bufs, es, off32, seg_off);
+    blo = xchg->blo;
+    nbl = xchg->nbl;
+    off32 = seg_off;
+    for (size_t i = 0; i < mv.size(); i++) ms.a[i] = mv[i].a.p;
+    std::fill(boff.begin(), boff.end(), 0);
+    for (int b = 0; b < nb; b++) {
+      int lb = b - blo;
+      boff[b + 1] = boff[b] + ((lb >= 0 && lb < nbl) ? (int64_t)(off32[lb + 1] - off32[lb]) : 0);
+    }
+    d_off.alloc(c, ((size_t)nbl + 1) * 4);
+    CK(cudaMemcpyAsync(d_off.p, off32.data(), ((size_t)nbl + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+  }
+  for (size_t i = 0; i < mv.size(); i++) {
+    mv[i].b.alloc(c, (size_t)n * mv[i].esize + 16);
+    ms.b[i] = mv[i].b.p;
+  }
 
   // ---- K3: every bucket sorted on the key
   hs_segmented_sort(c, ms, key, key_bits, d_off.as<uint32_t>(), nbl, n, off32.data());
@@ -352,7 +404,7 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
     for (int i = 0; i < ncols; i++) {
       out[i].type = cols[i].type;
       out[i].length = n;
-      out[i].null_count = cols[i].validity ? cols[i].null_count : 0;
+      out[i].null_count = cols[i].validity ? cols[i].null_count : 0;  // recounted below after an exchange
     }
     for (auto& m : mv) {
       if (m.user_col < 0) continue;
@@ -360,6 +412,17 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
       if (m.role == 0) {
         o.data_bytes = n * m.esize;
         o.data = std::move(m.a);
+      } else if (m.role == 1 && xchg) {
+        // the rows of this table came from every rank: count its NULLs afresh
+        DBuf bits(c, (size_t)((n + 7) / 8)), zeros(c, 8);
+        zeros.zero();
+        LAUNCH(c, k_bytes_to_bits_count, grid1d((n + 7) / 8), 256, 0, m.a.as<uint8_t>(), n, bits.as<uint8_t>(),
+               zeros.as<unsigned long long>());
+        unsigned long long z = 0;
+        CK(cudaMemcpyAsync(&z, zeros.p, 8, cudaMemcpyDeviceToHost, c->stream));
+        hs_sync(c);
+        o.null_count = (int64_t)z;
+        if (z) o.validity = std::move(bits);
       } else {
         DBuf bits(c, (size_t)((n + 7) / 8));
         LAUNCH(c, k_bytes_to_bits, grid1d((n + 7) / 8), 256, 0, m.a.as<uint8_t>(), n, bits.as<uint8_t>());
@@ -490,7 +553,7 @@ int32_t hs_build_index(hs_ctx* ctx, const hs_column* cols, int32_t ncols, int32_
   }
   std::vector<OutCol> ocols;
   std::vector<int64_t> boff;
-  hs_build_core(ctx, dcols, n_indexed, num_buckets, 0, num_buckets, ocols, boff);
+  hs_build_core(ctx, dcols, n_indexed, num_buckets, 0, num_buckets, ocols, boff, nullptr);
   Stage s(ctx, "d2h");
   *out = hs_finish_table(ctx, ocols, dcols[0].length, num_buckets, &boff);
   API_END(ctx)
@@ -521,7 +584,7 @@ int32_t hs_merge_runs(hs_ctx* ctx, const hs_index_view* runs, int32_t nruns, hs_
   std::vector<int64_t> boff;
   // Re-bucketing the concatenation gives every row the bucket it already had (same hash, same n),
   // and the per-bucket sort merges the runs: exactly what Spark's repartition + sort does here.
-  hs_build_core(ctx, all, runs[0].n_indexed, runs[0].num_buckets, 0, runs[0].num_buckets, ocols, boff);
+  hs_build_core(ctx, all, runs[0].n_indexed, runs[0].num_buckets, 0, runs[0].num_buckets, ocols, boff, nullptr);
   Stage s(ctx, "d2h");
   *out = hs_finish_table(ctx, ocols, all[0].length, runs[0].num_buckets, &boff);
   API_END(ctx)

@@ -70,42 +70,169 @@ static void nccl_load() {
 // owner(b) = b * N / nb: contiguous bucket ranges, so every GPU writes a contiguous file-id range
 static inline int owner_of(int b, int nranks, int nb) { return (int)((int64_t)b * nranks / nb); }
 
-__global__ void __launch_bounds__(256) k_bucket_to_owner(const uint16_t* __restrict__ bucket, int64_t n, int nranks,
-                                                         int nb, uint16_t* __restrict__ owner) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (; i < n; i += stride) owner[i] = (uint16_t)(((int64_t)bucket[i] * nranks) / nb);
-}
-__global__ void __launch_bounds__(256) k_bits_to_bytes_d(const uint8_t* __restrict__ bits, int64_t n,
-                                                         uint8_t* __restrict__ out) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (; i < n; i += stride) out[i] = (bits[i >> 3] >> (i & 7)) & 1;
-}
-__global__ void __launch_bounds__(256) k_bytes_to_bits_d(const uint8_t* __restrict__ in, int64_t n,
-                                                         uint8_t* __restrict__ bits, unsigned long long* zeros) {
-  int64_t nbytes = (n + 7) >> 3;
-  int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  unsigned z = 0;
-  for (; b < nbytes; b += stride) {
-    unsigned v = 0;
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-      int64_t i = b * 8 + k;
-      if (i < n) { if (in[i]) v |= 1u << k; else z++; }
-    }
-    bits[b] = (uint8_t)v;
+// copies runs of rows: run j = (src row, dst row, rows); 16-byte vector moves where alignment allows
+__global__ void __launch_bounds__(256) k_copy_runs(const unsigned char* __restrict__ src, unsigned char* __restrict__ dst,
+                                                   const uint32_t* __restrict__ runs, int esize) {
+  const uint32_t s0 = runs[3 * blockIdx.x], d0 = runs[3 * blockIdx.x + 1], m = runs[3 * blockIdx.x + 2];
+  const unsigned char* sp = src + (size_t)s0 * esize;
+  unsigned char* dp = dst + (size_t)d0 * esize;
+  size_t bytes = (size_t)m * esize;
+  if ((((uintptr_t)sp | (uintptr_t)dp) & 15) == 0) {
+    size_t nv = bytes >> 4;
+    const uint4* s4 = (const uint4*)sp;
+    uint4* d4 = (uint4*)dp;
+    for (size_t i = threadIdx.x; i < nv; i += blockDim.x) d4[i] = s4[i];
+    for (size_t i = (nv << 4) + threadIdx.x; i < bytes; i += blockDim.x) dp[i] = sp[i];
+  } else if ((((uintptr_t)sp | (uintptr_t)dp) & 7) == 0 && (esize & 7) == 0) {
+    size_t nv = bytes >> 3;
+    const uint64_t* s8 = (const uint64_t*)sp;
+    uint64_t* d8 = (uint64_t*)dp;
+    for (size_t i = threadIdx.x; i < nv; i += blockDim.x) d8[i] = s8[i];
+  } else {
+    for (size_t i = threadIdx.x; i < bytes; i += blockDim.x) dp[i] = sp[i];
   }
-  if (z && zeros) atomicAdd(zeros, (unsigned long long)z);
 }
 
-static unsigned dgrid(int64_t n) {
-  int64_t g = (n + 255) / 256, cap = (int64_t)HS_NUM_SMS * 16;
-  if (g > cap) g = cap;
-  if (g < 1) g = 1;
-  return (unsigned)g;
-}
+// The exchange step of the build. Each rank has scattered its rows by bucket; the run of bucket b goes to
+// owner(b), which places the runs of all senders for that bucket next to each other. The receive therefore
+// finishes the bucket partition: nothing is re-hashed or re-scattered after it.
+struct NcclExchange : BuildExchange {
+  int N, me, nb;
+  std::vector<uint32_t> all_hist;   // [rank][bucket]
+  NcclExchange(hs_ctx* c, int nb_) : N(c->nranks), me(c->rank), nb(nb_) {
+    blo = nb; int bhi = 0;
+    for (int b = 0; b < nb; b++)
+      if (owner_of(b, N, nb) == me) { if (b < blo) blo = b; if (b + 1 > bhi) bhi = b + 1; }
+    nbl = bhi > blo ? bhi - blo : 0;
+    if (nbl == 0) blo = 0;
+  }
+  void share_stats(hs_ctx* c, const std::vector<uint32_t>& local_hist, uint64_t* minmax,
+                   std::vector<uint8_t>& has_nulls) override {
+    Stage s(c, "stats_exchange");
+    // one all-gather carries the histogram, the key ranges and the NULL presence of every rank
+    const size_t ncol = has_nulls.size();
+    const size_t words = (size_t)nb + 4 * HS_MAX_KEYS + ncol;   // hist (u32) + minmax (u64 = 2 words each) + flags
+    std::vector<uint32_t> mine(words), all(words * N);
+    memcpy(mine.data(), local_hist.data(), (size_t)nb * 4);
+    memcpy(mine.data() + nb, minmax, (size_t)2 * HS_MAX_KEYS * 8);
+    for (size_t i = 0; i < ncol; i++) mine[nb + 4 * HS_MAX_KEYS + i] = has_nulls[i];
+    DBuf d_mine(c, words * 4), d_all(c, words * 4 * N);
+    CK(cudaMemcpyAsync(d_mine.p, mine.data(), words * 4, cudaMemcpyHostToDevice, c->stream));
+    NCK(g_nccl.allgather(d_mine.p, d_all.p, words * 4, NCCL_UINT8, (nccl_comm)c->comm, c->stream));
+    CK(cudaMemcpyAsync(all.data(), d_all.p, words * 4 * N, cudaMemcpyDeviceToHost, c->stream));
+    hs_sync(c);
+    all_hist.assign((size_t)N * nb, 0);
+    for (int k = 0; k < HS_MAX_KEYS; k++) { minmax[2 * k] = ~0ull; minmax[2 * k + 1] = 0; }
+    for (int r = 0; r < N; r++) {
+      memcpy(&all_hist[(size_t)r * nb], &all[words * r], (size_t)nb * 4);
+      uint64_t mm[2 * HS_MAX_KEYS];
+      memcpy(mm, &all[words * r + nb], sizeof mm);
+      for (int k = 0; k < HS_MAX_KEYS; k++) {
+        if (mm[2 * k] < minmax[2 * k]) minmax[2 * k] = mm[2 * k];
+        if (mm[2 * k + 1] > minmax[2 * k + 1]) minmax[2 * k + 1] = mm[2 * k + 1];
+      }
+      for (size_t i = 0; i < ncol; i++) has_nulls[i] |= (uint8_t)(all[words * r + nb + 4 * HS_MAX_KEYS + i] != 0);
+    }
+  }
+  int64_t exchange(hs_ctx* c, std::vector<DBuf*>& bufs, const std::vector<int>& esize,
+                   const std::vector<uint32_t>& local_off, std::vector<uint32_t>& seg_off) override {
+    // Wire format: one message per (peer, column) — the runs of a peer's buckets are adjacent in the
+    // bucket-scattered buffer, so they travel as one span (NCCL is slow on hundreds of small messages).
+    // The receiver then holds [sender][bucket] blocks and re-orders them to [bucket][sender] with one
+    // run-copy kernel per column: after that every owned bucket is contiguous.
+    std::vector<uint64_t> recv_cnt(N, 0), recv_off(N + 1, 0), send_cnt(N, 0), send_off(N, 0);
+    for (int r = 0; r < N; r++) {
+      for (int lb = 0; lb < nbl; lb++) recv_cnt[r] += all_hist[(size_t)r * nb + blo + lb];
+      recv_off[r + 1] = recv_off[r] + recv_cnt[r];
+    }
+    for (int b = 0; b < nb; b++) send_cnt[owner_of(b, N, nb)] += all_hist[(size_t)me * nb + b];
+    for (int r = 0, first = 0; r < N; r++) {
+      while (first < nb && owner_of(first, N, nb) < r) first++;
+      send_off[r] = first < nb ? local_off[first] : local_off[nb];
+    }
+    const uint64_t total = recv_off[N];
+    if (total >= 0xFFFFFFF0ull) HS_THROW(HS_EUNSUPPORTED, "more than 2^32-16 rows on one GPU");
+    const int64_t nrecv = (int64_t)total;
+    seg_off.assign((size_t)nbl + 1, 0);
+    // run table: (src row, dst row, rows) for every (sender, owned bucket)
+    std::vector<uint32_t> runs;
+    {
+      uint64_t at = 0;
+      std::vector<uint64_t> src_at(N);
+      for (int r = 0; r < N; r++) src_at[r] = recv_off[r];
+      for (int lb = 0; lb < nbl; lb++) {
+        seg_off[lb] = (uint32_t)at;
+        for (int r = 0; r < N; r++) {
+          uint32_t cnt = all_hist[(size_t)r * nb + blo + lb];
+          // split long runs so that the copy has enough CTAs
+          for (uint32_t done = 0; done < cnt; done += 65536) {
+            uint32_t m = cnt - done < 65536 ? cnt - done : 65536;
+            runs.push_back((uint32_t)(src_at[r] + done));
+            runs.push_back((uint32_t)(at + done));
+            runs.push_back(m);
+          }
+          src_at[r] += cnt;
+          at += cnt;
+        }
+      }
+      seg_off[nbl] = (uint32_t)at;
+    }
+    int64_t bytes_sent = 0;
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    std::vector<DBuf> recv(bufs.size());
+    for (size_t i = 0; i < bufs.size(); i++) recv[i].alloc(c, (size_t)nrecv * esize[i] + 16);
+    {
+      Stage s(c, "all_to_all");
+      CK(cudaEventRecord(e0, c->stream));
+      for (size_t i = 0; i < bufs.size(); i++)
+        if (send_cnt[me])
+          CK(cudaMemcpyAsync((char*)recv[i].p + recv_off[me] * esize[i], (char*)bufs[i]->p + send_off[me] * esize[i],
+                             send_cnt[me] * esize[i], cudaMemcpyDeviceToDevice, c->stream));
+      NCK(g_nccl.group_start());
+      for (size_t i = 0; i < bufs.size(); i++) {
+        for (int r = 0; r < N; r++) {
+          if (r == me) continue;
+          if (send_cnt[r]) {
+            NCK(g_nccl.send((char*)bufs[i]->p + send_off[r] * esize[i], send_cnt[r] * esize[i], NCCL_UINT8, r,
+                            (nccl_comm)c->comm, c->stream));
+            bytes_sent += (int64_t)(send_cnt[r] * esize[i]);
+          }
+          if (recv_cnt[r])
+            NCK(g_nccl.recv((char*)recv[i].p + recv_off[r] * esize[i], recv_cnt[r] * esize[i], NCCL_UINT8, r,
+                            (nccl_comm)c->comm, c->stream));
+        }
+      }
+      NCK(g_nccl.group_end());
+      CK(cudaEventRecord(e1, c->stream));
+    }
+    {
+      // [sender][bucket] -> [bucket][sender]; the send buffers are reused as destination when they are
+      // large enough, else fresh buffers are taken
+      Stage s(c, "run_transpose");
+      DBuf d_runs(c, runs.size() * 4 + 16);
+      if (!runs.empty())
+        CK(cudaMemcpyAsync(d_runs.p, runs.data(), runs.size() * 4, cudaMemcpyHostToDevice, c->stream));
+      for (size_t i = 0; i < bufs.size(); i++) {
+        DBuf dst(c, (size_t)nrecv * esize[i] + 16);
+        if (!runs.empty())
+          LAUNCH(c, k_copy_runs, (unsigned)(runs.size() / 3), 256, 0, (const unsigned char*)recv[i].p,
+                 (unsigned char*)dst.p, d_runs.as<uint32_t>(), esize[i]);
+        *bufs[i] = std::move(dst);
+        recv[i].release();
+      }
+    }
+    hs_sync(c);
+    float ms_x = 0.f;
+    cudaEventElapsedTime(&ms_x, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    c->last_xchg_bytes = bytes_sent;
+    c->last_xchg_ms = ms_x;
+    return nrecv;
+  }
+};
 
 extern "C" {
 
@@ -163,7 +290,7 @@ int32_t hs_build_index_dist(hs_ctx* ctx, const hs_column* cols, int32_t ncols, i
   *out = nullptr;
   if (!cols || ncols <= 0 || n_indexed <= 0 || n_indexed > ncols || num_buckets <= 0)
     HS_THROW(HS_EINVAL, "bad arguments");
-  const int N = ctx->nranks, me = ctx->rank, nb = num_buckets;
+  const int N = ctx->nranks, nb = num_buckets;
   if (N > 1 && !ctx->comm) HS_THROW(HS_EINVAL, "hs_comm_init has not been called");
   if (nb < N) HS_THROW(HS_EINVAL, "num_buckets must be >= number of ranks");
   hs_stages_reset(ctx);
@@ -174,175 +301,18 @@ int32_t hs_build_index_dist(hs_ctx* ctx, const hs_column* cols, int32_t ncols, i
     Stage s(ctx, "h2d");
     hs_stage_columns(ctx, cols, ncols, dcols);
   }
-  // bucket range of this rank
-  int blo = 0, bhi = nb;
-  if (N > 1) {
-    blo = nb; bhi = 0;
-    for (int b = 0; b < nb; b++)
-      if (owner_of(b, N, nb) == me) { if (b < blo) blo = b; if (b + 1 > bhi) bhi = b + 1; }
-  }
   std::vector<OutCol> ocols;
   std::vector<int64_t> boff;
   if (N == 1) {
-    hs_build_core(ctx, dcols, n_indexed, nb, 0, nb, ocols, boff);
+    hs_build_core(ctx, dcols, n_indexed, nb, 0, nb, ocols, boff, nullptr);
     Stage s(ctx, "d2h");
     *out = hs_finish_table(ctx, ocols, dcols[0].length, nb, &boff);
     return HS_OK;
   }
-  for (auto& dc : dcols)
-    if (hs_is_varlen(dc.type)) HS_THROW(HS_EUNSUPPORTED, "string columns in the multi-GPU build");
-  const int64_t n = dcols[0].length;
-
-  // ---- local hash -> owner of every row, rows grouped by owner
-  KeySpec ks = hs_make_keyspec(dcols, n_indexed);
-  DBuf bucket(ctx, (size_t)n * 2 + 16), hist(ctx, (size_t)nb * 4), minmax(ctx, (2 * HS_MAX_KEYS + 1) * 8);
-  std::vector<uint32_t> h_hist((size_t)nb);
-  {
-    Stage s(ctx, "hash_hist");
-    hs_hash_bucket_hist(ctx, ks, dcols, n, nb, 0, nb, bucket.as<uint16_t>(), hist.as<uint32_t>(), minmax.as<uint64_t>());
-    CK(cudaMemcpyAsync(h_hist.data(), hist.p, (size_t)nb * 4, cudaMemcpyDeviceToHost, ctx->stream));
-    hs_sync(ctx);
-  }
-  std::vector<uint64_t> send_cnt((size_t)N, 0);
-  for (int b = 0; b < nb; b++) send_cnt[owner_of(b, N, nb)] += h_hist[b];
-  std::vector<uint32_t> send_off((size_t)N + 1, 0);
-  for (int r = 0; r < N; r++) send_off[r + 1] = send_off[r] + (uint32_t)send_cnt[r];
-
-  // travelling arrays: values, validity bytes, boolean bytes
-  struct Trav { int col; int role; int esize; const void* src; DBuf tmp, sendbuf, recvbuf; };
-  std::vector<Trav> tv;
-  tv.reserve(2 * (size_t)ncols);
-  {
-    Stage s(ctx, "prepare");
-    for (int i = 0; i < ncols; i++) {
-      DevCol& dc = dcols[i];
-      if (dc.validity) {
-        tv.emplace_back();
-        Trav& t = tv.back();
-        t.col = i; t.role = 1; t.esize = 1;
-        t.tmp.alloc(ctx, (size_t)(n ? n : 1));
-        if (n) LAUNCH(ctx, k_bits_to_bytes_d, dgrid(n), 256, 0, dc.validity, n, t.tmp.as<uint8_t>());
-        t.src = t.tmp.p;
-      }
-      tv.emplace_back();
-      Trav& t = tv.back();
-      t.col = i;
-      if (dc.type == HS_BOOL) {
-        t.role = 2; t.esize = 1;
-        t.tmp.alloc(ctx, (size_t)(n ? n : 1));
-        if (n) LAUNCH(ctx, k_bits_to_bytes_d, dgrid(n), 256, 0, (const uint8_t*)dc.data, n, t.tmp.as<uint8_t>());
-        t.src = t.tmp.p;
-      } else {
-        t.role = 0; t.esize = hs_fixed_width(dc.type); t.src = dc.data;
-      }
-    }
-    if ((int)tv.size() > HS_MAX_MOVE) HS_THROW(HS_EUNSUPPORTED, "too many columns");
-  }
-  MoveSet ms;
-  memset(&ms, 0, sizeof ms);
-  ms.n = (int)tv.size();
-  std::vector<const void*> srcs(tv.size());
-  for (size_t i = 0; i < tv.size(); i++) {
-    tv[i].sendbuf.alloc(ctx, (size_t)n * tv[i].esize);
-    ms.esize[i] = tv[i].esize;
-    ms.a[i] = tv[i].sendbuf.p;
-    ms.b[i] = nullptr;
-    srcs[i] = tv[i].src;
-  }
-  {
-    Stage s(ctx, "owner_scatter");
-    DBuf owner(ctx, (size_t)n * 2 + 16), d_soff(ctx, ((size_t)N + 1) * 4);
-    if (n) LAUNCH(ctx, k_bucket_to_owner, dgrid(n), 256, 0, bucket.as<uint16_t>(), n, N, nb, owner.as<uint16_t>());
-    CK(cudaMemcpyAsync(d_soff.p, send_off.data(), ((size_t)N + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
-    hs_bucket_scatter(ctx, srcs.data(), ms, owner.as<uint16_t>(), n, N, d_soff.as<uint32_t>());
-    hs_sync(ctx);
-  }
-  bucket.release();
-  for (auto& t : tv) t.tmp.release();
-
-  // ---- counts, then the all-to-all
-  std::vector<uint64_t> all_cnt((size_t)N * N, 0);
-  {
-    Stage s(ctx, "count_exchange");
-    DBuf d_send(ctx, (size_t)N * 8), d_all(ctx, (size_t)N * N * 8);
-    CK(cudaMemcpyAsync(d_send.p, send_cnt.data(), (size_t)N * 8, cudaMemcpyHostToDevice, ctx->stream));
-    NCK(g_nccl.allgather(d_send.p, d_all.p, (size_t)N, NCCL_UINT64, (nccl_comm)ctx->comm, ctx->stream));
-    CK(cudaMemcpyAsync(all_cnt.data(), d_all.p, (size_t)N * N * 8, cudaMemcpyDeviceToHost, ctx->stream));
-    hs_sync(ctx);
-  }
-  std::vector<uint64_t> recv_off((size_t)N + 1, 0);
-  for (int r = 0; r < N; r++) recv_off[r + 1] = recv_off[r] + all_cnt[(size_t)r * N + me];
-  const int64_t nrecv = (int64_t)recv_off[N];
-  if (nrecv >= (int64_t)0xFFFFFFF0ll) HS_THROW(HS_EUNSUPPORTED, "more than 2^32-16 rows on one GPU");
-  int64_t bytes_sent = 0;
-  {
-    cudaEvent_t e0, e1;
-    CK(cudaEventCreate(&e0));
-    CK(cudaEventCreate(&e1));
-    Stage s(ctx, "all_to_all");
-    for (auto& t : tv) t.recvbuf.alloc(ctx, (size_t)nrecv * t.esize);
-    CK(cudaEventRecord(e0, ctx->stream));
-    NCK(g_nccl.group_start());
-    for (auto& t : tv) {
-      for (int r = 0; r < N; r++) {
-        size_t sb = (size_t)send_cnt[r] * t.esize, rb = (size_t)all_cnt[(size_t)r * N + me] * t.esize;
-        if (r == me) {
-          if (sb) CK(cudaMemcpyAsync((char*)t.recvbuf.p + recv_off[r] * t.esize, (char*)t.sendbuf.p + (size_t)send_off[r] * t.esize,
-                                     sb, cudaMemcpyDeviceToDevice, ctx->stream));
-          continue;
-        }
-        if (sb) { NCK(g_nccl.send((char*)t.sendbuf.p + (size_t)send_off[r] * t.esize, sb, NCCL_UINT8, r, (nccl_comm)ctx->comm, ctx->stream)); bytes_sent += (int64_t)sb; }
-        if (rb) NCK(g_nccl.recv((char*)t.recvbuf.p + recv_off[r] * t.esize, rb, NCCL_UINT8, r, (nccl_comm)ctx->comm, ctx->stream));
-      }
-    }
-    NCK(g_nccl.group_end());
-    CK(cudaEventRecord(e1, ctx->stream));
-    hs_sync(ctx);
-    float ms_x = 0.f;
-    cudaEventElapsedTime(&ms_x, e0, e1);
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
-    ctx->last_xchg_bytes = bytes_sent;
-    ctx->last_xchg_ms = ms_x;
-    for (auto& t : tv) t.sendbuf.release();
-  }
-
-  // ---- bucket-local build on the received rows
-  std::vector<DevCol> rcols((size_t)ncols);
-  {
-    Stage s(ctx, "repack");
-    for (int i = 0; i < ncols; i++) {
-      rcols[i].type = dcols[i].type;
-      rcols[i].length = nrecv;
-    }
-    for (auto& t : tv) {
-      DevCol& rc = rcols[t.col];
-      if (t.role == 0) {
-        rc.data = t.recvbuf.p;
-        rc.data_bytes = nrecv * t.esize;
-        rc.owned.push_back(std::move(t.recvbuf));
-      } else {
-        DBuf bits(ctx, (size_t)((nrecv + 7) / 8)), zeros(ctx, 8);
-        zeros.zero();
-        LAUNCH(ctx, k_bytes_to_bits_d, dgrid((nrecv + 7) / 8), 256, 0, t.recvbuf.as<uint8_t>(), nrecv, bits.as<uint8_t>(),
-               t.role == 1 ? zeros.as<unsigned long long>() : (unsigned long long*)nullptr);
-        if (t.role == 1) {
-          unsigned long long z = 0;
-          CK(cudaMemcpyAsync(&z, zeros.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
-          hs_sync(ctx);
-          if (z) { rc.validity = bits.as<uint8_t>(); rc.null_count = (int64_t)z; rc.owned.push_back(std::move(bits)); }
-        } else {
-          rc.data = bits.p;
-          rc.data_bytes = (nrecv + 7) / 8;
-          rc.owned.push_back(std::move(bits));
-        }
-      }
-    }
-  }
-  dcols.clear();
-  hs_build_core(ctx, rcols, n_indexed, nb, blo, bhi - blo, ocols, boff);
+  NcclExchange xchg(ctx, nb);
+  hs_build_core(ctx, dcols, n_indexed, nb, 0, nb, ocols, boff, &xchg);
   Stage s(ctx, "d2h");
-  *out = hs_finish_table(ctx, ocols, nrecv, nb, &boff);
+  *out = hs_finish_table(ctx, ocols, boff[nb], nb, &boff);
   API_END(ctx)
 }
 

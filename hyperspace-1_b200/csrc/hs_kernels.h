@@ -10,8 +10,22 @@ void hs_hash_to_i32(hs_ctx* c, const KeySpec& ks, int64_t n, int32_t nb, int32_t
 void hs_hash_bucket_hist(hs_ctx* c, const KeySpec& ks, const std::vector<DevCol>& cols, int64_t n, int32_t nb,
                          int32_t blo, int32_t nbl, uint16_t* d_bucket, uint32_t* d_hist, uint64_t* d_minmax);
 // the build over staged device columns; rows must hash into buckets [blo, blo + nbl)
+// Multi-GPU hook of the build (implemented over NCCL in hs_dist.cu).
+struct BuildExchange {
+  int blo = 0, nbl = 0;   // the bucket range this rank owns
+  virtual ~BuildExchange() {}
+  // in: this rank's histogram over all buckets, its key min/max and which columns hold NULLs here;
+  // out: minmax and has_nulls replaced by their global values
+  virtual void share_stats(hs_ctx* c, const std::vector<uint32_t>& local_hist, uint64_t* minmax,
+                           std::vector<uint8_t>& has_nulls) = 0;
+  // in: bufs[i] holds the local rows bucket-contiguously (local_off, nb+1 entries). Every bucket run goes to the
+  // bucket's owner; bufs[i] is replaced by a buffer holding this rank's buckets, each contiguous. Returns the
+  // rows received; seg_off (nbl+1 entries) are the local offsets of the owned buckets.
+  virtual int64_t exchange(hs_ctx* c, std::vector<DBuf*>& bufs, const std::vector<int>& esize,
+                           const std::vector<uint32_t>& local_off, std::vector<uint32_t>& seg_off) = 0;
+};
 void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t nb, int32_t blo, int32_t nbl,
-                   std::vector<OutCol>& out, std::vector<int64_t>& boff);
+                   std::vector<OutCol>& out, std::vector<int64_t>& boff, BuildExchange* xchg);
 void hs_offsets_to_device(hs_ctx* c, const int64_t* boff, int32_t nb, int64_t nrows, DBuf& out);
 
 // ---- the row mover / segmented sort (hs_sort.cu) ----

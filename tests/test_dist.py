@@ -22,7 +22,7 @@ def _run(mode, world):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()), os.path.join(HERE, "dist_worker.py"), mode]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert r.returncode == 0, "\n".join(l for l in (r.stdout + r.stderr).splitlines() if "Error" in l or "error" in l or "assert" in l.lower() or "HS_" in l)[-3000:]
     assert f"DIST_OK mode={mode} world={world}" in r.stdout
 
 
