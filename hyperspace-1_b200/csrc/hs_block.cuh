@@ -194,10 +194,13 @@ __device__ __forceinline__ void tile_rank_w(const uint32_t (&word)[ITEMS], int s
       bool v = (vmask >> k) & 1u;
       uint32_t d = (word[k] >> shift) & mask;
       uint32_t m = __ballot_sync(0xffffffffu, v);
-      for (int b = 0; b < bits; b++) {
-        bool bit = (d >> b) & 1u;
-        uint32_t bal = __ballot_sync(0xffffffffu, bit);
-        m &= bit ? bal : ~bal;
+#pragma unroll
+      for (int b = 0; b < 8; b++) {   // bits <= 8; unrolled so that every bit test has a constant mask
+        if (b < bits) {
+          const bool bit = (d & (1u << b)) != 0;
+          const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+          m &= bal ^ ((uint32_t)bit - 1u);   // bit ? bal : ~bal
+        }
       }
       uint32_t r = __popc(m & lt);
       uint32_t pre = v ? mycnt[d] : 0;

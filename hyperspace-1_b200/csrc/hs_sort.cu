@@ -297,7 +297,7 @@ __device__ __forceinline__ void classify_push(const PlanOut& o, uint32_t start, 
     o.small.start[i] = start; o.small.len[i] = len; o.small.shift[i] = shift;
   } else if (len <= LEAF_MAX) {
     uint32_t i = atomicAdd(&o.counters[0], 1u);
-    o.leaf.start[i] = start; o.leaf.len[i] = len; o.leaf.shift[i] = shift;
+    o.leaf.start[i] = start; o.leaf.len[i] = len; o.leaf.shift[i] = shift; o.leaf.base[i] = base;
   } else if (shift == 0) {
     uint32_t i = atomicAdd(&o.counters[2], 1u);
     o.copy.start[i] = start; o.copy.len[i] = len; o.copy.shift[i] = 0;
@@ -537,23 +537,69 @@ __device__ __forceinline__ void leaf_move_column(const T* __restrict__ src, T* _
 // key - min and the row's position are packed into one 32-bit word, the first LSD pass (up to 11 bits)
 // ranks with shared-memory atomics (no stability needed), the remaining <= 9 bits take one stable
 // ballot-ranked pass. Segments with a wider key range are flagged for k_leaf_sort.
+template <typename T>
+__device__ __forceinline__ void leaf_permute_column(const unsigned char* stage, uint32_t lead, T* __restrict__ dst,
+                                                    uint32_t start, uint32_t len, const uint32_t* sdata) {
+  const T* col = (const T*)(stage + lead);
+#pragma unroll 4
+  for (int k = 0; k < PT_ITEMS; k++) {
+    uint32_t j = threadIdx.x + k * PT_THREADS;
+    if (j < len) dst[start + j] = col[sdata[j] & ((1u << L32_IDX_BITS) - 1u)];
+  }
+}
+
+// The leaf sort for segments whose keys span at most 2^20 values (the common case after one MSD level).
+// Every column slice of the segment arrives in shared memory through a TMA bulk copy (double buffered, the
+// key column first); key - min and the row's position are packed into one 32-bit word; the first LSD pass
+// (up to 11-12 bits) ranks with shared-memory atomics (no stability needed), the remaining <= 8 bits take
+// one stable ballot-ranked pass; each column is then read through the permutation from shared memory and
+// written out coalesced. Because a slice is completely in shared memory before the first row of that
+// column is written, sorting in place (src == dst) is safe. Segments with a wider key range are flagged
+// for k_leaf_sort.
 template <int KMODE>
 __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort32(const __grid_constant__ LeafParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  uint32_t* sdata = (uint32_t*)smem_raw;            // LEAF_MAX packed words
+  unsigned char* stage0 = smem_raw;
+  unsigned char* stage1 = smem_raw + STAGE_BYTES;
+  uint32_t* sdata = (uint32_t*)(smem_raw + 2 * STAGE_BYTES);  // LEAF_MAX packed words
   uint32_t* cnt = sdata + LEAF_MAX;                 // 4096 words: atomic counters or PT_WARPS x 256 warp counters
   uint32_t* tot = cnt + 4096;                       // 256
   uint32_t* loc = tot + 256;                        // 256
   uint32_t* scratch = loc + 256;                    // PT_SCRATCH
   uint64_t* red = (uint64_t*)(scratch + PT_SCRATCH);  // 2 * PT_WARPS + 2
+  uint64_t* bar = red + 2 * PT_WARPS + 2;           // 2 mbarriers
 
   const uint32_t s = blockIdx.x;
   if (s >= *p.count) return;
   const uint32_t start = p.segs.start[s], len = p.segs.len[s];
   const int w = threadIdx.x >> 5;
   const int items = (int)((len + PT_THREADS - 1) / PT_THREADS);
+  const int ncols = p.mv.n;
+  const int first = p.key.col;
+  auto col_at = [&](int i) { return i == 0 ? first : (i <= first ? i - 1 : i); };
 
-  // ---- load keys (coalesced), segment min/max
+  if (threadIdx.x == 0) {
+    mbar_init(&bar[0], 1);
+    mbar_init(&bar[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    issue_slice(p.mv.src[first], p.mv.esize[first], start, len, stage0, &bar[0]);
+    if (ncols > 1) {
+      int c1 = col_at(1);
+      issue_slice(p.mv.src[c1], p.mv.esize[c1], start, len, stage1, &bar[1]);
+    }
+  }
+  // ---- keys from the staged slice. The segment descriptor says how many low bits of (key - base) can still
+  // differ inside the segment; when that fits the packed word no min/max pass is needed at all.
+  const uint32_t seg_bits = p.segs.shift[s];
+  const uint64_t seg_base = p.segs.base[s];
+  const bool known = seg_bits <= L32_MAX_KEY_BITS;
+  const uint64_t seg_mask = known ? ((1ull << seg_bits) - 1ull) : ~0ull;
+  mbar_wait(&bar[0], 0);
+  const unsigned char* ks = stage0 + slice_lead(p.mv.src[first], p.mv.esize[first], start);
   uint64_t key[PT_ITEMS];
   uint32_t vmask = 0;
   uint64_t mn = ~0ull, mx = 0;
@@ -564,35 +610,46 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort32(const __grid_cons
     vmask |= (uint32_t)v << k;
     key[k] = 0;
     if (v) {
-      const void* kp = p.mv.src[p.key.col];
-      if (KMODE == KS_U64) key[k] = ((const uint64_t*)kp)[start + idx];
-      else if (KMODE == KS_I64) key[k] = (((const uint64_t*)kp)[start + idx] ^ 0x8000000000000000ull) - p.key.min;
-      else key[k] = ((uint64_t)(int64_t)((const int32_t*)kp)[start + idx] ^ 0x8000000000000000ull) - p.key.min;
-      mn = key[k] < mn ? key[k] : mn;
-      mx = key[k] > mx ? key[k] : mx;
+      if (KMODE == KS_U64) key[k] = ((const uint64_t*)ks)[idx];
+      else if (KMODE == KS_I64) key[k] = (((const uint64_t*)ks)[idx] ^ 0x8000000000000000ull) - p.key.min;
+      else key[k] = ((uint64_t)(int64_t)((const int32_t*)ks)[idx] ^ 0x8000000000000000ull) - p.key.min;
+      key[k] = (key[k] - seg_base) & seg_mask;
+      if (!known) {
+        mn = key[k] < mn ? key[k] : mn;
+        mx = key[k] > mx ? key[k] : mx;
+      }
     }
   }
-  mn = warp_min_u64(mn);
-  mx = warp_max_u64(mx);
-  if (lane_id() == 0) { red[w] = mn; red[PT_WARPS + w] = mx; }
-  __syncthreads();
-  if (w == 0) {
-    uint64_t a = lane_id() < PT_WARPS ? red[lane_id()] : ~0ull;
-    uint64_t b = lane_id() < PT_WARPS ? red[PT_WARPS + lane_id()] : 0;
-    a = warp_min_u64(a);
-    b = warp_max_u64(b);
-    if (lane_id() == 0) { red[2 * PT_WARPS] = a; red[2 * PT_WARPS + 1] = b; }
+  uint64_t kmin = 0;
+  int nbits = (int)seg_bits;
+  if (!known) {
+    mn = warp_min_u64(mn);
+    mx = warp_max_u64(mx);
+    if (lane_id() == 0) { red[w] = mn; red[PT_WARPS + w] = mx; }
+    __syncthreads();
+    if (w == 0) {
+      uint64_t a = lane_id() < PT_WARPS ? red[lane_id()] : ~0ull;
+      uint64_t b = lane_id() < PT_WARPS ? red[PT_WARPS + lane_id()] : 0;
+      a = warp_min_u64(a);
+      b = warp_max_u64(b);
+      if (lane_id() == 0) { red[2 * PT_WARPS] = a; red[2 * PT_WARPS + 1] = b; }
+    }
+    __syncthreads();
+    kmin = red[2 * PT_WARPS];
+    const uint64_t range = red[2 * PT_WARPS + 1] - kmin;
+    nbits = range ? 64 - __clzll((long long)range) : 0;
   }
-  __syncthreads();
-  const uint64_t kmin = red[2 * PT_WARPS];
-  const uint64_t range = red[2 * PT_WARPS + 1] - kmin;
-  const int nbits = range ? 64 - __clzll((long long)range) : 0;
-  if (nbits > L32_MAX_KEY_BITS) {
-    if (threadIdx.x == 0) { p.wide[s] = 1; atomicAdd(p.n_wide, 1u); }
+  const bool wide = nbits > L32_MAX_KEY_BITS;
+  if (threadIdx.x == 0) {
+    p.wide[s] = wide ? 1 : 0;
+    if (wide) atomicAdd(p.n_wide, 1u);
+  }
+  if (wide || (nbits == 0 && p.in_place)) {
+    // nothing to do here (the 64-bit kernel takes it, or all keys are equal and the rows are in place);
+    // a CTA must not retire with a bulk copy in flight
+    if (ncols > 1) mbar_wait(&bar[1], 0);
     return;
   }
-  if (threadIdx.x == 0) p.wide[s] = 0;
-  if (nbits == 0 && p.in_place) return;  // all keys equal and the rows are already where they belong
 
   uint32_t word[PT_ITEMS], pos[PT_ITEMS];
 #pragma unroll
@@ -627,27 +684,35 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort32(const __grid_cons
         vm2 |= (uint32_t)v << k;
         word[k] = v ? sdata[idx] : 0;
       }
-      const int radix_b = 256;
-      tile_rank_w<PT_ITEMS>(word, L32_IDX_BITS + ba, vm2, items, bb, radix_b, cnt, tot, loc, scratch, pos);
+      tile_rank_w<PT_ITEMS>(word, L32_IDX_BITS + ba, vm2, items, bb, 256, cnt, tot, loc, scratch, pos);
 #pragma unroll
       for (int k = 0; k < PT_ITEMS; k++)
         if ((vm2 >> k) & 1u) sdata[pos[k]] = word[k];
       __syncthreads();
     }
   }
-  // ---- move every column through the sorted positions
-  for (int c = 0; c < p.mv.n; c++) {
-    switch (p.mv.esize[c]) {
-      case 8: leaf_move_column<uint64_t>((const uint64_t*)p.mv.src[c], (uint64_t*)p.mv.dst[c], start, len, sdata); break;
-      case 4: leaf_move_column<uint32_t>((const uint32_t*)p.mv.src[c], (uint32_t*)p.mv.dst[c], start, len, sdata); break;
-      case 2: leaf_move_column<uint16_t>((const uint16_t*)p.mv.src[c], (uint16_t*)p.mv.dst[c], start, len, sdata); break;
-      default: leaf_move_column<uint8_t>((const uint8_t*)p.mv.src[c], (uint8_t*)p.mv.dst[c], start, len, sdata); break;
+  // ---- every column: staged slice -> permutation -> coalesced store
+  for (int i = 0; i < ncols; i++) {
+    const int c = col_at(i), b = i & 1, es = p.mv.esize[c];
+    unsigned char* stage = b ? stage1 : stage0;
+    mbar_wait(&bar[b], (uint32_t)(i >> 1) & 1u);
+    const uint32_t lead = slice_lead(p.mv.src[c], es, start);
+    switch (es) {
+      case 8: leaf_permute_column<uint64_t>(stage, lead, (uint64_t*)p.mv.dst[c], start, len, sdata); break;
+      case 4: leaf_permute_column<uint32_t>(stage, lead, (uint32_t*)p.mv.dst[c], start, len, sdata); break;
+      case 2: leaf_permute_column<uint16_t>(stage, lead, (uint16_t*)p.mv.dst[c], start, len, sdata); break;
+      default: leaf_permute_column<uint8_t>(stage, lead, (uint8_t*)p.mv.dst[c], start, len, sdata); break;
     }
-    __syncthreads();
+    __syncthreads();  // stage[b] is free again
+    if (threadIdx.x == 0 && i + 2 < ncols) {
+      int cn = col_at(i + 2);
+      issue_slice(p.mv.src[cn], p.mv.esize[cn], start, len, stage, &bar[b]);
+    }
   }
 }
 static size_t leaf32_smem_bytes() {
-  return (size_t)LEAF_MAX * 4 + 4096 * 4 + 512 * 4 + PT_SCRATCH * 4 + (2 * PT_WARPS + 2) * 8;
+  return (size_t)2 * STAGE_BYTES + (size_t)LEAF_MAX * 4 + 4096 * 4 + 512 * 4 + PT_SCRATCH * 4 +
+         (2 * PT_WARPS + 2) * 8 + 16;
 }
 
 static size_t leaf_smem_bytes() {
@@ -867,6 +932,8 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     upload(large, lg_s, lg_l);
     large.base.alloc(c, (lg_s.size() ? lg_s.size() : 1) * 8);
     large.base.zero();
+    leaf.base.alloc(c, (lf_s.size() ? lf_s.size() : 1) * 8);
+    leaf.base.zero();
     upload(small, sm_s, sm_l);
     copy.alloc(c, 1);
     CK(cudaMemcpyAsync(counters.p, h, 32, cudaMemcpyHostToDevice, c->stream));
@@ -879,7 +946,7 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
       run_wide_leaves(c, ll0, nw);
     }
   } else {
-    leaf.alloc(c, cap_leaf);
+    leaf.alloc(c, cap_leaf, true);
     large.alloc(c, cap_large, true);
     copy.alloc(c, cap_large);
     small.alloc(c, cap_leaf);
@@ -932,7 +999,7 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     hs_stage_end(c);
     ListBufs nleaf, nlarge, ncopy, nsmall;
     size_t children = (size_t)n_large * MSD_RADIX;
-    nleaf.alloc(c, children);
+    nleaf.alloc(c, children, true);
     nlarge.alloc(c, cap_large, true);
     ncopy.alloc(c, cap_large);
     nsmall.alloc(c, children);
