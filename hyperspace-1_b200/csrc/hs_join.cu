@@ -6,6 +6,8 @@
 // Both sides are sorted per bucket, so neighbouring left rows probe neighbouring right rows: each left
 // row binary-searches its bucket of the right run (the probes of a warp share cache lines), a scan turns
 // match counts into output offsets, and the pairs are expanded and gathered.
+#include <algorithm>
+
 #include "hs_keys.cuh"
 #include "hs_kernels.h"
 
@@ -98,6 +100,280 @@ __global__ void __launch_bounds__(256) k_join_bucket_offsets(const uint32_t* __r
   out[b] = r < nl ? off[r] : *total;
 }
 
+// ------------------------------------------------------------------ fast path: merge-path tiles
+// One signed-integer key without NULLs on both sides and fixed-width, NULL-free output columns (the
+// lineitem x orders shape). Left rows are cut into tiles of JT rows that never cross a bucket; because both
+// runs are sorted, a tile's matches lie in one narrow window of the right run: the window is located with
+// two warp-wide searches, its keys are staged in shared memory, every left row finds [lower, upper) there.
+// Pass 1 counts matches per tile, a scan turns the counts into output offsets, pass 2 repeats the search,
+// expands the pairs in shared memory and writes every output column directly (no index arrays in HBM).
+#define JT 2048          // left rows per tile
+#define JR 6144          // right keys staged per tile (falls back to global probes when the window is larger)
+#define JTHREADS 256
+
+struct JoinFast {
+  const void* lkey; const void* rkey;     // key columns
+  const uint32_t* roff;                   // right bucket offsets (device)
+  const uint32_t* tile_bucket;            // per tile
+  const uint32_t* tile_start;             // first left row of the tile
+  const uint32_t* tile_len;
+  uint32_t ntiles;
+  uint32_t* tile_win;                     // [2 * ntiles]: window [lo, hi) of the right run per tile
+  uint32_t* tile_cnt;                     // pass 1 out / pass 2 in: matches per tile, then exclusive offsets
+  int32_t n_lout, n_rout;
+  const void* lsrc[16]; const void* rsrc[16];
+  void* ldst[16]; void* rdst[16];
+  int32_t les[16], res[16];
+};
+
+template <typename K>
+__device__ __forceinline__ uint32_t warp_lower_bound(const K* a, uint32_t lo, uint32_t hi, K key, bool upper) {
+  // first index in [lo, hi) with a[i] >= key (upper: > key); 32-ary search by one warp
+  while (hi - lo > 32) {
+    uint32_t step = (hi - lo + 31) / 32;
+    uint32_t idx = lo + lane_id() * step;
+    bool before = idx < hi && (upper ? a[idx] <= key : a[idx] < key);
+    uint32_t m = __ballot_sync(0xffffffffu, before);
+    uint32_t k = __popc(m);                      // probes 0..k-1 are before the answer
+    uint32_t nlo = k ? lo + (k - 1) * step + 1 : lo;
+    uint32_t nhi = k < 32 ? lo + k * step : hi;
+    lo = nlo;
+    hi = nhi < hi ? nhi : hi;
+    if (lo > hi) lo = hi;
+  }
+  uint32_t idx = lo + lane_id();
+  bool before = idx < hi && (upper ? a[idx] <= key : a[idx] < key);
+  return lo + __popc(__ballot_sync(0xffffffffu, before));
+}
+
+#define JPER (JT / JTHREADS)   // consecutive left rows owned by one thread
+
+// one warp per tile: the window of the right run that can hold matches for the tile's left rows
+template <typename K>
+__global__ void __launch_bounds__(256) k_join_windows(const __grid_constant__ JoinFast p) {
+  const uint32_t t = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (t >= p.ntiles) return;
+  const uint32_t b = p.tile_bucket[t], l0 = p.tile_start[t], ln = p.tile_len[t];
+  const K* lk = (const K*)p.lkey + l0;
+  const K* rk = (const K*)p.rkey;
+  const uint32_t r0 = p.roff[b], r1 = p.roff[b + 1];
+  uint32_t lo = warp_lower_bound<K>(rk, r0, r1, lk[0], false);
+  uint32_t hi = warp_lower_bound<K>(rk, lo, r1, lk[ln - 1], true);
+  if (lane_id() == 0) { p.tile_win[2 * t] = lo; p.tile_win[2 * t + 1] = hi; }
+}
+
+// first position >= pos in the staged window whose key is >= key (short forward scan, binary search for
+// long gaps)
+template <typename K>
+__device__ __forceinline__ uint32_t window_advance(const K* sR, uint32_t pos, uint32_t wn, K key) {
+  if (pos + 8 < wn && sR[pos + 8] < key) {
+    uint32_t a = pos + 9, e = wn;
+    while (a < e) { uint32_t m = (a + e) >> 1; if (sR[m] < key) a = m + 1; else e = m; }
+    return a;
+  }
+  while (pos < wn && sR[pos] < key) pos++;
+  return pos;
+}
+
+template <typename K, bool WRITE>
+__global__ void __launch_bounds__(JTHREADS) k_join_tiles(const __grid_constant__ JoinFast p) {
+  extern __shared__ __align__(16) unsigned char jsm[];
+  K* sR = (K*)jsm;                                   // JR staged right keys
+  uint32_t* slb = (uint32_t*)(sR + JR);              // JT  (absolute right row of the first match)
+  uint32_t* scn = slb + JT;                          // JT + 1 (exclusive scan of the match counts)
+  __shared__ uint32_t s_red[JTHREADS / 32 + 1];
+  const uint32_t t = blockIdx.x;
+  const uint32_t l0 = p.tile_start[t], ln = p.tile_len[t];
+  const K* lk = (const K*)p.lkey + l0;
+  const K* rk = (const K*)p.rkey;
+  // each thread owns JPER consecutive left rows: sorted keys straight from global memory (the warp reads one
+  // contiguous span), merged against the staged window of the right run
+  const uint32_t i0 = threadIdx.x * JPER;
+  K key[JPER];
+#pragma unroll
+  for (int j = 0; j < JPER; j++) key[j] = i0 + j < ln ? lk[i0 + j] : (K)0;
+  const uint32_t wlo = p.tile_win[2 * t], whi = p.tile_win[2 * t + 1], wn = whi - wlo;
+  const bool staged = wn <= JR;
+  if (staged)
+    for (uint32_t i = threadIdx.x; i < wn; i += JTHREADS) sR[i] = rk[wlo + i];
+  __syncthreads();
+  uint32_t lb[JPER], cnt[JPER];
+  uint32_t mysum = 0;
+  if (staged) {
+    uint32_t pos = 0;
+    if (i0 < ln) {
+      uint32_t a = 0, e = wn;
+      while (a < e) { uint32_t m = (a + e) >> 1; if (sR[m] < key[0]) a = m + 1; else e = m; }
+      pos = a;
+    }
+#pragma unroll
+    for (int j = 0; j < JPER; j++) {
+      lb[j] = 0; cnt[j] = 0;
+      if (i0 + j < ln) {
+        pos = window_advance<K>(sR, pos, wn, key[j]);
+        uint32_t e = pos;
+        while (e < wn && sR[e] == key[j]) e++;
+        lb[j] = wlo + pos;
+        cnt[j] = e - pos;
+        mysum += cnt[j];
+      }
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < JPER; j++) {
+      lb[j] = 0; cnt[j] = 0;
+      if (i0 + j < ln) {
+        uint32_t a = wlo, e = whi;
+        while (a < e) { uint32_t m = (a + e) >> 1; if (rk[m] < key[j]) a = m + 1; else e = m; }
+        uint32_t f = a;
+        e = whi;
+        while (a < e) { uint32_t m = (a + e) >> 1; if (rk[m] <= key[j]) a = m + 1; else e = m; }
+        lb[j] = f;
+        cnt[j] = a - f;
+        mysum += cnt[j];
+      }
+    }
+  }
+  // block exclusive scan of the per-thread sums
+  uint32_t inc = mysum;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+    if (lane_id() >= (uint32_t)d) inc += o;
+  }
+  if (lane_id() == 31) s_red[threadIdx.x >> 5] = inc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t run = 0;
+    for (int w = 0; w < JTHREADS / 32; w++) { uint32_t v = s_red[w]; s_red[w] = run; run += v; }
+    s_red[JTHREADS / 32] = run;
+  }
+  __syncthreads();
+  const uint32_t total = s_red[JTHREADS / 32];
+  if (!WRITE) {
+    if (threadIdx.x == 0) p.tile_cnt[t] = total;
+    return;
+  }
+  uint32_t ex = inc - mysum + s_red[threadIdx.x >> 5];
+  const uint32_t obase = p.tile_cnt[t];   // exclusive offset of this tile in the output
+  // warp-level view of the outputs: a warp whose rows produce at most 256 outputs transposes them through
+  // shared memory (the slb/scn area is free in this mode) so that global stores are fully coalesced
+  uint32_t winc = mysum;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    uint32_t o = __shfl_up_sync(0xffffffffu, winc, d);
+    if (lane_id() >= (uint32_t)d) winc += o;
+  }
+  const uint32_t wtotal = __shfl_sync(0xffffffffu, winc, 31);
+  const uint32_t wex = winc - mysum;                                   // this thread's offset inside the warp
+  const uint32_t wbase = obase + (ex - wex);                           // first output row of the warp
+  const bool all_warps_small = __syncthreads_and(wtotal <= 256);
+  if (total <= 4 * ln && all_warps_small) {
+    uint64_t* wst = (uint64_t*)slb + (threadIdx.x >> 5) * 256;        // 256 x 8 B per warp
+    for (int c = 0; c < p.n_lout + p.n_rout; c++) {
+      const bool left = c < p.n_lout;
+      const int cc = left ? c : c - p.n_lout;
+      const int es = left ? p.les[cc] : p.res[cc];
+      const void* src = left ? p.lsrc[cc] : p.rsrc[cc];
+      void* dst = left ? p.ldst[cc] : p.rdst[cc];
+      uint32_t o = wex;
+#pragma unroll
+      for (int j = 0; j < JPER; j++) {
+        for (uint32_t q = 0; q < cnt[j]; q++) {
+          uint32_t r = left ? l0 + i0 + j : lb[j] + q;
+          wst[o + q] = es == 8 ? ((const uint64_t*)src)[r] : (uint64_t)((const uint32_t*)src)[r];
+        }
+        o += cnt[j];
+      }
+      __syncwarp();
+      for (uint32_t q = lane_id(); q < wtotal; q += 32) {
+        if (es == 8) ((uint64_t*)dst)[wbase + q] = wst[q];
+        else ((uint32_t*)dst)[wbase + q] = (uint32_t)wst[q];
+      }
+      __syncwarp();
+    }
+    return;
+  }
+  if (total <= 4 * ln) {
+    // every thread writes the matches of its own rows (consecutive outputs per thread)
+    for (int c = 0; c < p.n_lout; c++) {
+      uint32_t o = obase + ex;
+      const int es = p.les[c];
+#pragma unroll
+      for (int j = 0; j < JPER; j++) {
+        if (cnt[j]) {
+          if (es == 8) {
+            uint64_t v = ((const uint64_t*)p.lsrc[c])[l0 + i0 + j];
+            for (uint32_t q = 0; q < cnt[j]; q++) ((uint64_t*)p.ldst[c])[o + q] = v;
+          } else {
+            uint32_t v = ((const uint32_t*)p.lsrc[c])[l0 + i0 + j];
+            for (uint32_t q = 0; q < cnt[j]; q++) ((uint32_t*)p.ldst[c])[o + q] = v;
+          }
+          o += cnt[j];
+        }
+      }
+    }
+    for (int c = 0; c < p.n_rout; c++) {
+      uint32_t o = obase + ex;
+      const int es = p.res[c];
+#pragma unroll
+      for (int j = 0; j < JPER; j++) {
+        for (uint32_t q = 0; q < cnt[j]; q++) {
+          if (es == 8) ((uint64_t*)p.rdst[c])[o + q] = ((const uint64_t*)p.rsrc[c])[lb[j] + q];
+          else ((uint32_t*)p.rdst[c])[o + q] = ((const uint32_t*)p.rsrc[c])[lb[j] + q];
+        }
+        o += cnt[j];
+      }
+    }
+    return;
+  }
+  // expanding case (large cross products): spread the outputs over the whole CTA
+#pragma unroll
+  for (int j = 0; j < JPER; j++) {
+    if (i0 + j < ln) { slb[i0 + j] = lb[j]; scn[i0 + j] = ex; }
+    ex += cnt[j];
+  }
+  if (threadIdx.x == 0) scn[ln] = total;
+  __syncthreads();
+  for (uint32_t chunk = 0; chunk < total; chunk += JTHREADS * 8) {
+    uint32_t li[8], rj[8];
+#pragma unroll
+    for (int q = 0; q < 8; q++) {
+      uint32_t o = chunk + q * JTHREADS + threadIdx.x;
+      li[q] = 0; rj[q] = 0;
+      if (o < total) {
+        uint32_t a = 0, e = ln;   // last row i with scn[i] <= o
+        while (e - a > 1) { uint32_t m = (a + e) >> 1; if (scn[m] <= o) a = m; else e = m; }
+        li[q] = a;
+        rj[q] = slb[a] + (o - scn[a]);
+      }
+    }
+    for (int c = 0; c < p.n_lout; c++) {
+#pragma unroll
+      for (int q = 0; q < 8; q++) {
+        uint32_t o = chunk + q * JTHREADS + threadIdx.x;
+        if (o < total) {
+          if (p.les[c] == 8) ((uint64_t*)p.ldst[c])[obase + o] = ((const uint64_t*)p.lsrc[c])[l0 + li[q]];
+          else ((uint32_t*)p.ldst[c])[obase + o] = ((const uint32_t*)p.lsrc[c])[l0 + li[q]];
+        }
+      }
+    }
+    for (int c = 0; c < p.n_rout; c++) {
+#pragma unroll
+      for (int q = 0; q < 8; q++) {
+        uint32_t o = chunk + q * JTHREADS + threadIdx.x;
+        if (o < total) {
+          if (p.res[c] == 8) ((uint64_t*)p.rdst[c])[obase + o] = ((const uint64_t*)p.rsrc[c])[rj[q]];
+          else ((uint32_t*)p.rdst[c])[obase + o] = ((const uint32_t*)p.rsrc[c])[rj[q]];
+        }
+      }
+    }
+  }
+}
+
+template <typename K>
+static size_t join_smem_bytes() { return (size_t)JR * sizeof(K) + (size_t)(2 * JT + 1) * 4 + 16; }
+
 static void check_view(const hs_index_view* v) {
   if (!v || !v->cols || v->ncols <= 0 || v->n_indexed <= 0 || v->n_indexed > v->ncols || v->num_buckets <= 0 ||
       !v->bucket_offsets)
@@ -150,6 +426,99 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
   hs_offsets_to_device(ctx, right->bucket_offsets, nb, nr, roff);
   JoinSide L{hs_make_keyspec(lc, nk), loff.as<uint32_t>()};
   JoinSide R{hs_make_keyspec(rc, nk), roff.as<uint32_t>()};
+
+  // ---- fast path: one integer key, no NULL keys, fixed-width NULL-free outputs
+  bool fast_join = nk == 1 && (lc[0].type == HS_INT64 || lc[0].type == HS_INT32) && !lc[0].validity && !rc[0].validity &&
+                   n_left_out <= 16 && n_right_out <= 16 && nl > 0 && nr > 0;
+  for (int i = 0; i < n_left_out && fast_join; i++) {
+    int w = hs_fixed_width(lc[left_out[i]].type);
+    if ((w != 4 && w != 8) || lc[left_out[i]].validity) fast_join = false;
+  }
+  for (int i = 0; i < n_right_out && fast_join; i++) {
+    int w = hs_fixed_width(rc[right_out[i]].type);
+    if ((w != 4 && w != 8) || rc[right_out[i]].validity) fast_join = false;
+  }
+  if (fast_join) {
+    std::vector<uint32_t> tb, ts, tl, first_tile((size_t)nb + 1);
+    for (int b = 0; b < nb; b++) {
+      first_tile[b] = (uint32_t)tb.size();
+      for (int64_t a = left->bucket_offsets[b]; a < left->bucket_offsets[b + 1]; a += JT) {
+        tb.push_back((uint32_t)b);
+        ts.push_back((uint32_t)a);
+        tl.push_back((uint32_t)std::min<int64_t>(JT, left->bucket_offsets[b + 1] - a));
+      }
+    }
+    first_tile[nb] = (uint32_t)tb.size();
+    const uint32_t ntiles = (uint32_t)tb.size();
+    DBuf d_tb(ctx, (size_t)ntiles * 4), d_ts(ctx, (size_t)ntiles * 4), d_tl(ctx, (size_t)ntiles * 4),
+        d_cnt(ctx, (size_t)ntiles * 4 + 4), d_total(ctx, 8), d_win(ctx, (size_t)ntiles * 8);
+    CK(cudaMemcpyAsync(d_tb.p, tb.data(), (size_t)ntiles * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_ts.p, ts.data(), (size_t)ntiles * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_tl.p, tl.data(), (size_t)ntiles * 4, cudaMemcpyHostToDevice, ctx->stream));
+    JoinFast jf;
+    memset(&jf, 0, sizeof jf);
+    jf.lkey = lc[0].data; jf.rkey = rc[0].data;
+    jf.roff = roff.as<uint32_t>();
+    jf.tile_bucket = d_tb.as<uint32_t>(); jf.tile_start = d_ts.as<uint32_t>(); jf.tile_len = d_tl.as<uint32_t>();
+    jf.ntiles = ntiles;
+    jf.tile_cnt = d_cnt.as<uint32_t>();
+    jf.tile_win = d_win.as<uint32_t>();
+    const bool k64 = lc[0].type == HS_INT64;
+    const size_t smem = k64 ? join_smem_bytes<int64_t>() : join_smem_bytes<int32_t>();
+    static bool attr_done[64] = {false};
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (!attr_done[dev & 63]) {
+      CK(cudaFuncSetAttribute(k_join_tiles<int64_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int64_t>()));
+      CK(cudaFuncSetAttribute(k_join_tiles<int64_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int64_t>()));
+      CK(cudaFuncSetAttribute(k_join_tiles<int32_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int32_t>()));
+      CK(cudaFuncSetAttribute(k_join_tiles<int32_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int32_t>()));
+      attr_done[dev & 63] = true;
+    }
+    uint64_t h_tot = 0;
+    std::vector<uint32_t> h_off((size_t)ntiles);
+    {
+      Stage s(ctx, "join_count");
+      if (k64) LAUNCH(ctx, k_join_windows<int64_t>, (ntiles + 7) / 8, 256, 0, jf);
+      else LAUNCH(ctx, k_join_windows<int32_t>, (ntiles + 7) / 8, 256, 0, jf);
+      if (k64) LAUNCH(ctx, (k_join_tiles<int64_t, false>), ntiles, JTHREADS, smem, jf);
+      else LAUNCH(ctx, (k_join_tiles<int32_t, false>), ntiles, JTHREADS, smem, jf);
+      hs_exclusive_scan_u32(ctx, d_cnt.as<uint32_t>(), d_cnt.as<uint32_t>(), ntiles, d_total.as<uint64_t>());
+      CK(cudaMemcpyAsync(&h_tot, d_total.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+      CK(cudaMemcpyAsync(h_off.data(), d_cnt.p, (size_t)ntiles * 4, cudaMemcpyDeviceToHost, ctx->stream));
+      hs_sync(ctx);
+    }
+    if (h_tot >= 0xFFFFFFF0ull) HS_THROW(HS_EUNSUPPORTED, "join output exceeds 2^32-16 rows in one call");
+    const int64_t m = (int64_t)h_tot;
+    std::vector<OutCol> ocols((size_t)(n_left_out + n_right_out));
+    for (int i = 0; i < n_left_out; i++) {
+      const DevCol& sc = lc[left_out[i]];
+      OutCol& o = ocols[i];
+      o.type = sc.type; o.length = m; o.null_count = 0;
+      o.data_bytes = m * hs_fixed_width(sc.type);
+      o.data.alloc(ctx, (size_t)o.data_bytes);
+      jf.lsrc[i] = sc.data; jf.ldst[i] = o.data.p; jf.les[i] = hs_fixed_width(sc.type);
+    }
+    for (int i = 0; i < n_right_out; i++) {
+      const DevCol& sc = rc[right_out[i]];
+      OutCol& o = ocols[n_left_out + i];
+      o.type = sc.type; o.length = m; o.null_count = 0;
+      o.data_bytes = m * hs_fixed_width(sc.type);
+      o.data.alloc(ctx, (size_t)o.data_bytes);
+      jf.rsrc[i] = sc.data; jf.rdst[i] = o.data.p; jf.res[i] = hs_fixed_width(sc.type);
+    }
+    jf.n_lout = n_left_out; jf.n_rout = n_right_out;
+    {
+      Stage s(ctx, "join_write");
+      if (k64) LAUNCH(ctx, (k_join_tiles<int64_t, true>), ntiles, JTHREADS, smem, jf);
+      else LAUNCH(ctx, (k_join_tiles<int32_t, true>), ntiles, JTHREADS, smem, jf);
+    }
+    std::vector<int64_t> ooff((size_t)nb + 1, 0);
+    for (int b = 0; b <= nb; b++) ooff[b] = first_tile[b] < ntiles ? (int64_t)h_off[first_tile[b]] : m;
+    Stage s(ctx, "d2h");
+    *out = hs_finish_table(ctx, ocols, m, nb, &ooff);
+    return HS_OK;
+  }
 
   DBuf lb(ctx, (size_t)nl * 4), cnt(ctx, (size_t)nl * 4), off(ctx, (size_t)nl * 4), total(ctx, 8);
   uint64_t h_total = 0;

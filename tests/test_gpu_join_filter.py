@@ -61,6 +61,30 @@ def test_join_many_to_many_nulls_and_misses(ctx, oracle):
     parity.assert_same_multiset(jg, want, joff, woff, "many-to-many")
 
 
+@pytest.mark.parametrize("dtype", [np.int64, np.int32])
+def test_fast_join_many_to_many_and_wide_windows(ctx, oracle, dtype):
+    # no NULL keys, fixed-width outputs -> the merge-path tile kernels; heavy right-side duplicates make some
+    # windows larger than the staged chunk (global probes), sparse keys leave tiles without any match
+    rng = np.random.default_rng(77)
+    nl, nr = 120000, 90000
+    lk = rng.integers(0, 3000, size=nl).astype(dtype)
+    rk = np.concatenate([rng.integers(1000, 5000, size=nr - 30000), np.full(30000, 1234)]).astype(dtype)
+    lcols = [pa.array(lk), pa.array(np.arange(nl, dtype=np.int64)), pa.array(rng.random(nl).astype(np.float32))]
+    rcols = [pa.array(rk), pa.array(np.arange(nr) * 0.5)]
+    for nb in (4, 64):
+        lg, loff = ctx.build_index(lcols, 1, nb)
+        rg, roff = ctx.build_index(rcols, 1, nb)
+        jg, joff = ctx.join(lg, loff, rg, roff, 1, [0, 1, 2], [0, 1])
+        want, woff = _oracle_join(oracle, lg, loff, rg, roff, 1, [0, 1, 2], [0, 1])
+        assert len(want[0]) > 2 * nl
+        parity.assert_same_multiset(jg, want, joff, woff, f"fast join {dtype.__name__}/{nb}")
+    # one side empty
+    eg, eoff = ctx.build_index([pa.array(np.zeros(0, dtype=dtype)), pa.array(np.zeros(0))], 1, 4)
+    lg, loff = ctx.build_index(lcols, 1, 4)
+    jg, joff = ctx.join(lg, loff, eg, eoff, 1, [0], [1])
+    assert len(jg[0]) == 0 and joff.tolist() == [0] * 5
+
+
 def test_join_on_string_and_composite_keys(ctx, oracle):
     s, v = string_keys(5000)
     idx = np.random.default_rng(1).integers(0, 5000, size=12000)
