@@ -639,22 +639,21 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort32(const __grid_cons
     const uint64_t range = red[2 * PT_WARPS + 1] - kmin;
     nbits = range ? 64 - __clzll((long long)range) : 0;
   }
-  const bool wide = nbits > L32_MAX_KEY_BITS;
-  if (threadIdx.x == 0) {
-    p.wide[s] = wide ? 1 : 0;
-    if (wide) atomicAdd(p.n_wide, 1u);
-  }
-  if (wide || (nbits == 0 && p.in_place)) {
-    // nothing to do here (the 64-bit kernel takes it, or all keys are equal and the rows are in place);
-    // a CTA must not retire with a bulk copy in flight
+  // A key range wider than the packed field: sort on the top L32_MAX_KEY_BITS bits of (key - kmin) and repair
+  // the (rare) runs of equal prefixes afterwards by comparing full keys (see the fix-up below).
+  const int drop = nbits > L32_MAX_KEY_BITS ? nbits - L32_MAX_KEY_BITS : 0;
+  if (nbits == 0 && p.in_place) {
+    // all keys equal and the rows are in place; a CTA must not retire with a bulk copy in flight
+    if (threadIdx.x == 0) p.wide[s] = 0;
     if (ncols > 1) mbar_wait(&bar[1], 0);
     return;
   }
+  if (drop) nbits = L32_MAX_KEY_BITS;
 
   uint32_t word[PT_ITEMS], pos[PT_ITEMS];
 #pragma unroll
   for (int k = 0; k < PT_ITEMS; k++)
-    word[k] = ((uint32_t)(key[k] - kmin) << L32_IDX_BITS) | (threadIdx.x + k * PT_THREADS);
+    word[k] = ((uint32_t)((key[k] - kmin) >> drop) << L32_IDX_BITS) | (threadIdx.x + k * PT_THREADS);
 
   if (nbits == 0) {
 #pragma unroll
@@ -690,6 +689,65 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort32(const __grid_cons
         if ((vm2 >> k) & 1u) sdata[pos[k]] = word[k];
       __syncthreads();
     }
+  }
+  // ---- prefix ties: rows whose dropped low bits differ may be out of order inside a run of equal prefixes.
+  // Every row of such a run ranks itself inside the run by the full key (the key slice is still staged).
+  // Runs are short for keys that are not clustered; a run longer than 64 rows sends the segment to the
+  // 64-bit kernel instead.
+  bool too_long = false;
+  if (drop) {
+    uint32_t npos[PT_ITEMS];
+#pragma unroll
+    for (int k = 0; k < PT_ITEMS; k++) {
+      const uint32_t j = threadIdx.x + k * PT_THREADS;
+      npos[k] = j;
+      if (j < len) {
+        const uint32_t wj = sdata[j], pj = wj >> L32_IDX_BITS;
+        uint32_t a = j, e = j + 1;
+        while (a > 0 && (sdata[a - 1] >> L32_IDX_BITS) == pj && j - a < 65) a--;
+        while (e < len && (sdata[e] >> L32_IDX_BITS) == pj && e - j < 65) e++;
+        if (e - a > 64) too_long = true;
+        else if (e - a > 1) {
+          auto full = [&](uint32_t w) -> uint64_t {
+            const uint32_t r = w & ((1u << L32_IDX_BITS) - 1u);
+            if (KMODE == KS_U64) return ((const uint64_t*)ks)[r];
+            if (KMODE == KS_I64) return ((const uint64_t*)ks)[r] ^ 0x8000000000000000ull;
+            return (uint64_t)(int64_t)((const int32_t*)ks)[r] ^ 0x8000000000000000ull;
+          };
+          const uint64_t kj = full(wj);
+          uint32_t r = 0;
+          for (uint32_t i = a; i < e; i++) {
+            const uint64_t ki = full(sdata[i]);
+            r += (ki < kj) || (ki == kj && i < j);
+          }
+          npos[k] = a + r;
+        }
+      }
+    }
+    too_long = __syncthreads_or(too_long);
+    if (!too_long) {
+      uint32_t wv[PT_ITEMS];
+#pragma unroll
+      for (int k = 0; k < PT_ITEMS; k++) {
+        const uint32_t j = threadIdx.x + k * PT_THREADS;
+        wv[k] = j < len ? sdata[j] : 0;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int k = 0; k < PT_ITEMS; k++) {
+        const uint32_t j = threadIdx.x + k * PT_THREADS;
+        if (j < len) sdata[npos[k]] = wv[k];
+      }
+      __syncthreads();
+    }
+  }
+  if (threadIdx.x == 0) {
+    p.wide[s] = too_long ? 1 : 0;
+    if (too_long) atomicAdd(p.n_wide, 1u);
+  }
+  if (too_long) {
+    if (ncols > 1) mbar_wait(&bar[1], 0);
+    return;
   }
   // ---- every column: staged slice -> permutation -> coalesced store
   for (int i = 0; i < ncols; i++) {
