@@ -114,6 +114,7 @@ __global__ void __launch_bounds__(HASH_THREADS) k_hash_i64x2(const uint64_t* __r
   for (int b = threadIdx.x; b < nb; b += HASH_THREADS) s_hist[b] = 0;
   __syncthreads();
   uint64_t mn = ~0ull, mx = 0;
+  long long smn = 0x7fffffffffffffffll, smx = -0x7fffffffffffffffll - 1;
   int64_t npairs = n >> 1;
   int64_t stride = (int64_t)gridDim.x * HASH_THREADS;
   const ulonglong2* k2 = (const ulonglong2*)keys;
@@ -127,13 +128,16 @@ __global__ void __launch_bounds__(HASH_THREADS) k_hash_i64x2(const uint64_t* __r
       b0 = fast_pmod(mm_hash_long(v.x, 42u), fm);
       b1 = fast_pmod(mm_hash_long(v.y, 42u), fm);
       ((uint32_t*)out16)[p] = b0 | (b1 << 16);
-      uint64_t m0 = v.x ^ 0x8000000000000000ull, m1 = v.y ^ 0x8000000000000000ull;
-      uint64_t lo = m0 < m1 ? m0 : m1, hi = m0 < m1 ? m1 : m0;
-      mn = lo < mn ? lo : mn;
-      mx = hi > mx ? hi : mx;
+      long long s0 = (long long)v.x, s1 = (long long)v.y;
+      smn = min(smn, min(s0, s1));
+      smx = max(smx, max(s0, s1));
     }
-    hist_add(s_hist, b0, valid);
-    hist_add(s_hist, b1, valid);
+    if (valid) {
+      // plain shared atomics: ~11 lanes/clk/SM on spread buckets; when both rows of a thread share a bucket
+      // (hot key) they collapse to one update
+      if (b0 == b1) atomicAdd(&s_hist[b0], 2u);
+      else { atomicAdd(&s_hist[b0], 1u); atomicAdd(&s_hist[b1], 1u); }
+    }
   }
   if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
     uint64_t v = keys[n - 1];
@@ -143,6 +147,11 @@ __global__ void __launch_bounds__(HASH_THREADS) k_hash_i64x2(const uint64_t* __r
     uint64_t m = v ^ 0x8000000000000000ull;
     mn = m < mn ? m : mn;
     mx = m > mx ? m : mx;
+  }
+  if (smn <= smx) {
+    uint64_t a = (uint64_t)smn ^ 0x8000000000000000ull, b = (uint64_t)smx ^ 0x8000000000000000ull;
+    mn = a < mn ? a : mn;
+    mx = b > mx ? b : mx;
   }
   minmax_flush(mn, mx, g_minmax);
   __syncthreads();
