@@ -312,8 +312,11 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
   ms.n = (int)mv.size();
   std::vector<const void*> srcs(mv.size());
   int key_mv = -1, more_mv = -1, srcrow_mv = -1;
+  std::vector<int> mv_es;
+  for (auto& m : mv) mv_es.push_back(m.esize);
+  const bool fused = xchg && xchg->try_fused(c, mv_es);   // rows go straight to their owners' buffers
   for (size_t i = 0; i < mv.size(); i++) {
-    mv[i].a.alloc(c, (size_t)n * mv[i].esize + 16);
+    if (!fused) mv[i].a.alloc(c, (size_t)n * mv[i].esize + 16);
     ms.esize[i] = mv[i].esize;
     ms.a[i] = mv[i].a.p;
     ms.b[i] = nullptr;
@@ -338,7 +341,27 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
   }
 
   // ---- K2: rows -> bucket-contiguous layout
-  {
+  std::vector<void*> recv_ptrs;
+  if (fused) {
+    // multi-GPU, fused: one kernel scatters by bucket and delivers over NVLink at the same time
+    std::vector<uint32_t> seg_off;
+    n = xchg->scatter_exchange(c, srcs.data(), mv_es, bucket.as<uint16_t>(), n, recv_ptrs, seg_off);
+    blo = xchg->blo;
+    nbl = xchg->nbl;
+    off32 = seg_off;
+    for (size_t i = 0; i < mv.size(); i++) {
+      mv[i].a.alloc(c, (size_t)n * mv[i].esize + 16);
+      ms.a[i] = mv[i].a.p;
+      ms.s0[i] = recv_ptrs[i];
+    }
+    std::fill(boff.begin(), boff.end(), 0);
+    for (int b = 0; b < nb; b++) {
+      int lb = b - blo;
+      boff[b + 1] = boff[b] + ((lb >= 0 && lb < nbl) ? (int64_t)(off32[lb + 1] - off32[lb]) : 0);
+    }
+    d_off.alloc(c, ((size_t)nbl + 1) * 4);
+    CK(cudaMemcpyAsync(d_off.p, off32.data(), ((size_t)nbl + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+  } else {
     Stage s(c, "bucket_scatter");
     hs_bucket_scatter(c, srcs.data(), ms, bucket.as<uint16_t>(), n, nbl, d_off.as<uint32_t>());
   }
@@ -346,7 +369,7 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
   bucket.release();
 
   // ---- multi-GPU: bucket runs travel to the GPU that owns the bucket and land at their final place
-  if (xchg) {
+  if (xchg && !fused) {
     std::vector<DBuf*> bufs;
     std::vector<int> es;
     for (auto& m : mv) { bufs.push_back(&m.a); es.push_back(m.esize); }

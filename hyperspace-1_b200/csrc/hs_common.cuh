@@ -63,6 +63,7 @@ struct hs_ctx {
   // multi-GPU (hs_dist.cu)
   void* nccl_lib = nullptr;
   void* comm = nullptr;
+  void* p2p = nullptr;     // peer-mapped receive buffers of the fused multi-GPU scatter (hs_dist.cu)
   int rank = 0, nranks = 1;
   int64_t last_xchg_bytes = 0;
   float last_xchg_ms = 0.f;

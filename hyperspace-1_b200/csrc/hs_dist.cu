@@ -5,6 +5,9 @@
 // NCCL is bound at run time (dlopen of libnccl.so.2) so that libhsgpu loads on hosts without it.
 #include <dlfcn.h>
 
+#include <map>
+#include <string>
+
 #include "hs_keys.cuh"
 #include "hs_kernels.h"
 
@@ -64,6 +67,8 @@ static void nccl_load() {
       HS_THROW(HS_ENCCL, "%s: %s", #call, g_nccl.errstr ? g_nccl.errstr(_r) : "nccl error"); \
   } while (0)
 
+#define HS_MAX_PEERS_HOST 8
+#define HS_MAX_PEER_COLS_HOST 16
 #define NCCL_UINT8 1
 #define NCCL_UINT64 5
 
@@ -91,6 +96,38 @@ __global__ void __launch_bounds__(256) k_copy_runs(const unsigned char* __restri
   } else {
     for (size_t i = threadIdx.x; i < bytes; i += blockDim.x) dp[i] = sp[i];
   }
+}
+
+// ---- peer-mapped receive buffers (fused path) ---------------------------------------------------------
+// Every rank keeps one receive buffer per travelling column, allocated with cudaMalloc (cudaIpc needs that),
+// grown when a build needs more, and exported to the other processes with cudaIpcGetMemHandle. The buffers
+// are persistent: the sort reads them as its level-0 source and never hands them to the caller.
+struct P2PSlot {
+  void* ptr = nullptr;
+  size_t cap = 0;
+  cudaIpcMemHandle_t handle;
+};
+struct P2PState {
+  std::vector<P2PSlot> slots;
+  std::vector<void*> retired;                         // old buffers, freed once every peer has let go of them
+  std::map<std::string, void*> opened;                // peer handle bytes -> local mapping
+  std::map<int, std::string> current;                 // rank * 64 + slot -> handle currently mapped for it
+  std::vector<void*> peer_ptr;                        // [rank][slot] for the current build
+  bool unusable = false;
+};
+static P2PState* p2p_of(hs_ctx* c) {
+  if (!c->p2p) c->p2p = new P2PState();
+  return (P2PState*)c->p2p;
+}
+static void p2p_destroy(hs_ctx* c) {
+  P2PState* st = (P2PState*)c->p2p;
+  if (!st) return;
+  for (auto& kv : st->opened) cudaIpcCloseMemHandle(kv.second);
+  for (auto& sl : st->slots) if (sl.ptr) cudaFree(sl.ptr);
+  for (void* p : st->retired) cudaFree(p);
+  delete st;
+  c->p2p = nullptr;
+  cudaGetLastError();
 }
 
 // The exchange step of the build. Each rank has scattered its rows by bucket; the run of bucket b goes to
@@ -232,6 +269,144 @@ struct NcclExchange : BuildExchange {
     c->last_xchg_ms = ms_x;
     return nrecv;
   }
+
+  // ---- fused path ------------------------------------------------------------------------------------
+  std::vector<uint64_t> rank_rows;   // rows every rank receives
+
+  bool try_fused(hs_ctx* c, const std::vector<int>& esize) override {
+    const char* off = getenv("HSGPU_NO_P2P");
+    if (off && *off && *off != '0') return false;
+    if (N > HS_MAX_PEERS_HOST || (int)esize.size() > HS_MAX_PEER_COLS_HOST) return false;
+    P2PState* st = p2p_of(c);
+    if (st->unusable) return false;
+    Stage s(c, "p2p_setup");
+    const int ncol = (int)esize.size();
+    rank_rows.assign(N, 0);
+    for (int b = 0; b < nb; b++)
+      for (int r = 0; r < N; r++) rank_rows[owner_of(b, N, nb)] += all_hist[(size_t)r * nb + b];
+    if (rank_rows[me] >= 0xFFFFFFF0ull) HS_THROW(HS_EUNSUPPORTED, "more than 2^32-16 rows on one GPU");
+    // peers have finished with buffers retired one build ago (they passed an all-gather since)
+    for (void* p : st->retired) cudaFree(p);
+    st->retired.clear();
+    bool ok = true;
+    if ((int)st->slots.size() < ncol) st->slots.resize(ncol);
+    for (int i = 0; i < ncol && ok; i++) {
+      size_t need = (size_t)rank_rows[me] * esize[i] + 256;
+      P2PSlot& sl = st->slots[i];
+      if (sl.cap < need) {
+        if (sl.ptr) st->retired.push_back(sl.ptr);
+        sl.ptr = nullptr;
+        size_t cap = need + need / 4;
+        if (cudaMalloc(&sl.ptr, cap) != cudaSuccess) { cudaGetLastError(); sl.ptr = nullptr; sl.cap = 0; ok = false; break; }
+        sl.cap = cap;
+        if (cudaIpcGetMemHandle(&sl.handle, sl.ptr) != cudaSuccess) { cudaGetLastError(); ok = false; }
+      }
+    }
+    // all-gather: [ok flag | handles]; doubles as the barrier that says "nobody still reads the buffers"
+    const size_t rec = 8 + (size_t)ncol * sizeof(cudaIpcMemHandle_t);
+    std::vector<unsigned char> mine(rec, 0), all(rec * N, 0);
+    mine[0] = ok ? 1 : 0;
+    for (int i = 0; i < ncol && ok; i++) memcpy(&mine[8 + i * sizeof(cudaIpcMemHandle_t)], &st->slots[i].handle, sizeof(cudaIpcMemHandle_t));
+    DBuf d_mine(c, rec), d_all(c, rec * N);
+    CK(cudaMemcpyAsync(d_mine.p, mine.data(), rec, cudaMemcpyHostToDevice, c->stream));
+    NCK(g_nccl.allgather(d_mine.p, d_all.p, rec, NCCL_UINT8, (nccl_comm)c->comm, c->stream));
+    CK(cudaMemcpyAsync(all.data(), d_all.p, rec * N, cudaMemcpyDeviceToHost, c->stream));
+    hs_sync(c);
+    for (int r = 0; r < N; r++) ok = ok && all[rec * r] == 1;
+    st->peer_ptr.assign((size_t)N * ncol, nullptr);
+    for (int r = 0; r < N && ok; r++) {
+      for (int i = 0; i < ncol && ok; i++) {
+        if (r == me) { st->peer_ptr[(size_t)r * ncol + i] = st->slots[i].ptr; continue; }
+        std::string key((const char*)&all[rec * r + 8 + i * sizeof(cudaIpcMemHandle_t)], sizeof(cudaIpcMemHandle_t));
+        // a peer that re-allocated a slot published a new handle: let go of the old mapping first, so that
+        // the owner may free the old buffer after the next all-gather
+        auto cur = st->current.find(r * 64 + i);
+        if (cur != st->current.end() && cur->second != key) {
+          auto old = st->opened.find(cur->second);
+          if (old != st->opened.end()) { cudaIpcCloseMemHandle(old->second); st->opened.erase(old); }
+        }
+        st->current[r * 64 + i] = key;
+        auto it = st->opened.find(key);
+        if (it == st->opened.end()) {
+          cudaIpcMemHandle_t h;
+          memcpy(&h, key.data(), sizeof h);
+          void* p = nullptr;
+          if (cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = false; break; }
+          it = st->opened.emplace(key, p).first;
+        }
+        st->peer_ptr[(size_t)r * ncol + i] = it->second;
+      }
+    }
+    // every rank must take the same path
+    unsigned char flag = ok ? 1 : 0;
+    std::vector<unsigned char> flags(N, 0);
+    DBuf d_f(c, 16), d_fa(c, 16 * (size_t)N);
+    CK(cudaMemcpyAsync(d_f.p, &flag, 1, cudaMemcpyHostToDevice, c->stream));
+    NCK(g_nccl.allgather(d_f.p, d_fa.p, 1, NCCL_UINT8, (nccl_comm)c->comm, c->stream));
+    CK(cudaMemcpyAsync(flags.data(), d_fa.p, N, cudaMemcpyDeviceToHost, c->stream));
+    hs_sync(c);
+    for (int r = 0; r < N; r++) ok = ok && flags[r] == 1;
+    if (!ok) st->unusable = true;   // fall back to the NCCL exchange, now and later
+    return ok;
+  }
+
+  int64_t scatter_exchange(hs_ctx* c, const void* const* srcs, const std::vector<int>& esize, const uint16_t* d_bucket,
+                           int64_t n_local, std::vector<void*>& recv, std::vector<uint32_t>& seg_off) override {
+    P2PState* st = p2p_of(c);
+    const int ncol = (int)esize.size();
+    // where this rank's run of every bucket starts inside the owner's buffer
+    std::vector<uint32_t> run_base((size_t)nb, 0);
+    std::vector<uint64_t> at(N, 0);
+    for (int b = 0; b < nb; b++) {
+      const int r = owner_of(b, N, nb);
+      uint64_t before = 0;
+      for (int q = 0; q < me; q++) before += all_hist[(size_t)q * nb + b];
+      run_base[b] = (uint32_t)(at[r] + before);
+      for (int q = 0; q < N; q++) at[r] += all_hist[(size_t)q * nb + b];
+    }
+    seg_off.assign((size_t)nbl + 1, 0);
+    {
+      uint64_t acc = 0;
+      for (int lb = 0; lb < nbl; lb++) {
+        seg_off[lb] = (uint32_t)acc;
+        for (int q = 0; q < N; q++) acc += all_hist[(size_t)q * nb + blo + lb];
+      }
+      seg_off[nbl] = (uint32_t)acc;
+    }
+    int64_t bytes_sent = 0;
+    for (int b = 0; b < nb; b++)
+      if (owner_of(b, N, nb) != me)
+        for (int i = 0; i < ncol; i++) bytes_sent += (int64_t)all_hist[(size_t)me * nb + b] * esize[i];
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    {
+      Stage s(c, "scatter_to_owners");
+      DBuf d_base(c, (size_t)nb * 4);
+      CK(cudaMemcpyAsync(d_base.p, run_base.data(), (size_t)nb * 4, cudaMemcpyHostToDevice, c->stream));
+      CK(cudaEventRecord(e0, c->stream));
+      hs_bucket_scatter_peers(c, srcs, esize.data(), ncol, st->peer_ptr.data(), N, d_bucket, n_local, nb,
+                              d_base.as<uint32_t>());
+      CK(cudaEventRecord(e1, c->stream));
+      hs_sync(c);   // my stores have left this GPU
+    }
+    {
+      // nobody may read its receive buffer before every sender has finished: a tiny all-gather is the barrier
+      Stage s(c, "p2p_barrier");
+      DBuf d_f(c, 16), d_fa(c, 16 * (size_t)N);
+      NCK(g_nccl.allgather(d_f.p, d_fa.p, 1, NCCL_UINT8, (nccl_comm)c->comm, c->stream));
+      hs_sync(c);
+    }
+    float ms_x = 0.f;
+    cudaEventElapsedTime(&ms_x, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    c->last_xchg_bytes = bytes_sent;
+    c->last_xchg_ms = ms_x;
+    recv.resize(ncol);
+    for (int i = 0; i < ncol; i++) recv[i] = st->slots[i].ptr;
+    return (int64_t)rank_rows[me];
+  }
 };
 
 extern "C" {
@@ -266,6 +441,8 @@ int32_t hs_comm_init(hs_ctx* ctx, int32_t rank, int32_t nranks, const void* id12
 
 int32_t hs_comm_destroy(hs_ctx* ctx) {
   if (!ctx) return HS_EINVAL;
+  cudaStreamSynchronize(ctx->stream);
+  p2p_destroy(ctx);
   if (ctx->comm && g_nccl.comm_destroy) {
     cudaStreamSynchronize(ctx->stream);
     g_nccl.comm_destroy((nccl_comm)ctx->comm);

@@ -23,6 +23,14 @@ struct BuildExchange {
   // rows received; seg_off (nbl+1 entries) are the local offsets of the owned buckets.
   virtual int64_t exchange(hs_ctx* c, std::vector<DBuf*>& bufs, const std::vector<int>& esize,
                            const std::vector<uint32_t>& local_off, std::vector<uint32_t>& seg_off) = 0;
+  // Fused path: the bucket scatter kernel itself writes every row into the owner's receive buffer over
+  // peer-mapped memory, so there is no separate all-to-all. try_fused sets up the receive buffers on all ranks
+  // (collective; false on every rank if any rank cannot map its peers). scatter_exchange then takes the rows
+  // in input order; recv[i] is this rank's receive buffer of column i (persistent, owned by the exchange).
+  virtual bool try_fused(hs_ctx* c, const std::vector<int>& esize) { return false; }
+  virtual int64_t scatter_exchange(hs_ctx* c, const void* const* srcs, const std::vector<int>& esize,
+                                   const uint16_t* d_bucket, int64_t n_local, std::vector<void*>& recv,
+                                   std::vector<uint32_t>& seg_off) { return -1; }
 };
 void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t nb, int32_t blo, int32_t nbl,
                    std::vector<OutCol>& out, std::vector<int64_t>& boff, BuildExchange* xchg);
@@ -34,6 +42,8 @@ struct MoveSet {           // the columns that travel together; all fixed width
   int32_t esize[HS_MAX_MOVE];
   void* a[HS_MAX_MOVE];    // buffer A (holds the result at the end)
   void* b[HS_MAX_MOVE];    // buffer B (ping-pong)
+  void* s0[HS_MAX_MOVE];   // optional: where the rows are when the sort starts (else they are in A);
+                           // used by the multi-GPU build, whose receive buffers are persistent peer-mapped memory
 };
 // how kernels read the 64-bit sort key of a row out of the moved columns
 struct KeySrc {
@@ -49,6 +59,8 @@ struct KeySrc {
 // order in ms.a, given u16 bucket ids and host-known bucket offsets.
 void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, const uint16_t* d_bucket, int64_t n,
                        int32_t nb, const uint32_t* d_bucket_off);
+void hs_bucket_scatter_peers(hs_ctx* c, const void* const* src, const int32_t* esize, int ncols, void* const* pdst,
+                             int nranks, const uint16_t* d_bucket, int64_t n, int32_t nb, const uint32_t* d_run_base);
 // Sort every segment [seg_off[s], seg_off[s+1]) of ms.a by the key; result in ms.a. key_bits = significant
 // low bits of the key. d_seg_off: device u32[nseg+1].
 void hs_segmented_sort(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_seg_off,

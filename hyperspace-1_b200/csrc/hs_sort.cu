@@ -34,6 +34,9 @@ struct SegList {           // device arrays
   uint64_t* base;          // subtracted from the key before digits are taken (0 until a level re-ranges)
 };
 
+#define HS_MAX_PEERS 8
+#define HS_MAX_PEER_COLS 16
+
 struct MoveArgs {
   int32_t n;
   int32_t esize[HS_MAX_MOVE];
@@ -115,6 +118,10 @@ struct PartParams {
   SegList segs;             // MODE 1: the large segments of this level
   const uint32_t* tile_prefix;  // MODE 1: [nseg + 1]
   uint32_t nseg;
+  // MODE 2 (multi-GPU): bucket d belongs to rank d * nranks / radix; column c of that rank's receive buffer is
+  // pdst[rank][c] (peer-mapped memory); cursor[d] starts at this sender's run inside the owner's bucket
+  int32_t nranks;
+  void* pdst[HS_MAX_PEERS][HS_MAX_PEER_COLS];
 };
 
 __device__ __forceinline__ uint32_t find_segment(const uint32_t* tile_prefix, uint32_t nseg, uint32_t tile) {
@@ -153,7 +160,23 @@ __device__ __forceinline__ void scatter_column(const unsigned char* stage, uint3
   }
 }
 
+template <typename T>
+__device__ __forceinline__ void scatter_column_peers(const unsigned char* stage, uint32_t lead, void* const (*pdst)[HS_MAX_PEER_COLS],
+                                                     int c, uint32_t tile_len, const uint16_t* inv, const uint32_t* gdst) {
+  const T* col = (const T*)(stage + lead);
+#pragma unroll 4
+  for (int k = 0; k < PT_ITEMS; k++) {
+    uint32_t j = threadIdx.x + k * PT_THREADS;
+    if (j < tile_len) {
+      const uint32_t iv = inv[j];
+      T* dst = (T*)pdst[iv >> 12][c];            // the owner's buffer (local or over NVLink)
+      dst[gdst[j]] = col[iv & 0xFFFu];
+    }
+  }
+}
+
 // MODE 0: scatter by bucket id.  MODE 1: one MSD level inside large segments.
+// MODE 2: scatter by bucket id straight into the receive buffers of the GPUs that own the buckets.
 // Column slices of the tile arrive in shared memory by TMA bulk copies (double buffered, one mbarrier
 // per buffer); rows are ranked by digit with shared-memory atomics; one global atomicAdd per (tile, digit)
 // reserves the output run; every column is then read through the tile permutation and written as
@@ -166,7 +189,7 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
   uint64_t seg_base = 0;
   int bits = p.bits;
   uint32_t* cursor = p.cursor;
-  if (MODE == 0) {
+  if (MODE == 0 || MODE == 2) {
     tile_start = blockIdx.x * (uint32_t)PT_TILE;
     uint32_t left = p.n - tile_start;
     tile_len = left < PT_TILE ? left : PT_TILE;
@@ -212,7 +235,7 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
     vmask |= (uint32_t)v << k;
     digit[k] = 0;
     if (v) {
-      if (MODE == 0) {
+      if (MODE == 0 || MODE == 2) {
         digit[k] = p.bucket[tile_start + idx];
       } else {
         const unsigned char* ks = sm.stage[0] + slice_lead(p.mv.src[first], p.mv.esize[first], tile_start);
@@ -235,7 +258,9 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
   for (int k = 0; k < PT_ITEMS; k++) {
     if ((vmask >> k) & 1u) {
       sm.gdst[pos[k]] = sm.gbase[digit[k]] + pos[k] - sm.cnt[digit[k]];
-      sm.inv[pos[k]] = (uint16_t)(threadIdx.x + k * PT_THREADS);
+      uint32_t iv = threadIdx.x + k * PT_THREADS;
+      if (MODE == 2) iv |= (uint32_t)(((uint64_t)digit[k] * (uint32_t)p.nranks) / (uint32_t)p.radix) << 12;
+      sm.inv[pos[k]] = (uint16_t)iv;
     }
   }
   __syncthreads();
@@ -243,6 +268,14 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
     const int c = col_at(i), b = i & 1, es = p.mv.esize[c];
     mbar_wait(&sm.bar[b], (uint32_t)(i >> 1) & 1u);
     const uint32_t lead = slice_lead(p.mv.src[c], es, tile_start);
+    if (MODE == 2) {
+      switch (es) {
+        case 8: scatter_column_peers<uint64_t>(sm.stage[b], lead, p.pdst, c, tile_len, sm.inv, sm.gdst); break;
+        case 4: scatter_column_peers<uint32_t>(sm.stage[b], lead, p.pdst, c, tile_len, sm.inv, sm.gdst); break;
+        case 2: scatter_column_peers<uint16_t>(sm.stage[b], lead, p.pdst, c, tile_len, sm.inv, sm.gdst); break;
+        default: scatter_column_peers<uint8_t>(sm.stage[b], lead, p.pdst, c, tile_len, sm.inv, sm.gdst); break;
+      }
+    } else
     switch (es) {
       case 8: scatter_column<uint64_t>(sm.stage[b], lead, (uint64_t*)p.mv.dst[c], tile_len, sm.inv, sm.gdst); break;
       case 4: scatter_column<uint32_t>(sm.stage[b], lead, (uint32_t*)p.mv.dst[c], tile_len, sm.inv, sm.gdst); break;
@@ -823,14 +856,19 @@ __global__ void __launch_bounds__(256) k_copy_segments(MoveArgs mv, SegList segs
 }
 
 // ---------------------------------------------------------------- host drivers
-static MoveArgs make_move(const MoveSet& ms, bool src_is_a, bool dst_is_a) {
+#define BUF_A 0
+#define BUF_B 1
+#define BUF_S0 2
+static void* const* buf_of(const MoveSet& ms, int code) { return code == BUF_A ? ms.a : code == BUF_B ? ms.b : ms.s0; }
+static int other_buf(int code) { return code == BUF_B ? BUF_A : BUF_B; }
+static MoveArgs make_move(const MoveSet& ms, int src_code, int dst_code) {
   MoveArgs mv;
   memset(&mv, 0, sizeof mv);
   mv.n = ms.n;
   for (int i = 0; i < ms.n; i++) {
     mv.esize[i] = ms.esize[i];
-    mv.src[i] = src_is_a ? ms.a[i] : ms.b[i];
-    mv.dst[i] = dst_is_a ? ms.a[i] : ms.b[i];
+    mv.src[i] = buf_of(ms, src_code)[i];
+    mv.dst[i] = buf_of(ms, dst_code)[i];
   }
   return mv;
 }
@@ -870,6 +908,41 @@ void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, con
   LAUNCH(c, k_partition<0>, tiles, PT_THREADS, smem, p);
 }
 
+// Multi-GPU variant of the bucket scatter: rows go straight into the owners' receive buffers.
+// d_run_base[b] = first row, inside the owner's buffer, of THIS rank's run for bucket b.
+void hs_bucket_scatter_peers(hs_ctx* c, const void* const* src, const int32_t* esize, int ncols, void* const* pdst,
+                             int nranks, const uint16_t* d_bucket, int64_t n, int32_t nb, const uint32_t* d_run_base) {
+  if (n == 0) return;
+  if (nb > 8192) HS_THROW(HS_EUNSUPPORTED, "the bucket scatter supports at most 8192 buckets");
+  if (ncols > HS_MAX_PEER_COLS || nranks > HS_MAX_PEERS) HS_THROW(HS_EUNSUPPORTED, "too many columns or ranks for the peer scatter");
+  PartParams p;
+  memset(&p, 0, sizeof p);
+  p.mv.n = ncols;
+  for (int i = 0; i < ncols; i++) { p.mv.esize[i] = esize[i]; p.mv.src[i] = src[i]; p.mv.dst[i] = nullptr; }
+  for (int r = 0; r < nranks; r++)
+    for (int i = 0; i < ncols; i++) p.pdst[r][i] = pdst[r * ncols + i];
+  p.nranks = nranks;
+  p.bucket = d_bucket;
+  p.n = (uint32_t)n;
+  p.radix = nb;
+  p.radix_pad = ((nb + PT_THREADS - 1) / PT_THREADS) * PT_THREADS;
+  p.bits = 0;
+  DBuf cursor(c, (size_t)nb * 4);
+  CK(cudaMemcpyAsync(cursor.p, d_run_base, (size_t)nb * 4, cudaMemcpyDeviceToDevice, c->stream));
+  p.cursor = cursor.as<uint32_t>();
+  size_t smem = tile_smem_bytes(p.radix_pad);
+  static size_t attr_set_dev[64] = {0};
+  int dev = 0;
+  CK(cudaGetDevice(&dev));
+  size_t& attr_set = attr_set_dev[dev & 63];
+  if (smem > attr_set) {
+    CK(cudaFuncSetAttribute(k_partition<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = smem;
+  }
+  unsigned tiles = (unsigned)((n + PT_TILE - 1) / PT_TILE);
+  LAUNCH(c, k_partition<2>, tiles, PT_THREADS, smem, p);
+}
+
 struct ListBufs {
   DBuf start, len, shift, base;
   void alloc(hs_ctx* c, size_t cap, bool with_base = false) {
@@ -903,17 +976,17 @@ struct LeafLaunch {
   LeafParams lp;
   uint32_t max_leaf = 0;
 };
-static void run_leaf_and_copy(hs_ctx* c, MoveSet& ms, const KeySrc& key, bool src_is_a, const ListBufs& leaf,
+static void run_leaf_and_copy(hs_ctx* c, MoveSet& ms, const KeySrc& key, int src_code, const ListBufs& leaf,
                               uint32_t max_leaf, const ListBufs& copy, uint32_t max_copy, uint32_t* counters,
                               LeafLaunch& ll, const ListBufs* small = nullptr, uint32_t max_small = 0) {
   ll.max_leaf = max_leaf;
   if (small && max_small) {
     LeafParams sp;
     memset(&sp, 0, sizeof sp);
-    sp.mv = make_move(ms, src_is_a, true);
+    sp.mv = make_move(ms, src_code, BUF_A);
     sp.key = key;
     sp.segs = small->view();
-    sp.in_place = src_is_a ? 1 : 0;
+    sp.in_place = src_code == BUF_A ? 1 : 0;
     sp.count = counters + 5;
     Stage st(c, "leaf_small");
     LAUNCH(c, k_leaf_small, (max_small + PT_WARPS - 1) / PT_WARPS, PT_THREADS, 0, sp);
@@ -921,10 +994,10 @@ static void run_leaf_and_copy(hs_ctx* c, MoveSet& ms, const KeySrc& key, bool sr
   if (max_leaf) {
     LeafParams& lp = ll.lp;
     memset(&lp, 0, sizeof lp);
-    lp.mv = make_move(ms, src_is_a, true);
+    lp.mv = make_move(ms, src_code, BUF_A);
     lp.key = key;
     lp.segs = leaf.view();
-    lp.in_place = src_is_a ? 1 : 0;
+    lp.in_place = src_code == BUF_A ? 1 : 0;
     lp.count = counters;
     lp.n_wide = counters + 4;
     ll.wide.alloc(c, max_leaf);
@@ -934,8 +1007,8 @@ static void run_leaf_and_copy(hs_ctx* c, MoveSet& ms, const KeySrc& key, bool sr
     else if (key.mode == KS_I64) LAUNCH(c, k_leaf_sort32<KS_I64>, max_leaf, PT_THREADS, leaf32_smem_bytes(), lp);
     else LAUNCH(c, k_leaf_sort32<KS_I32>, max_leaf, PT_THREADS, leaf32_smem_bytes(), lp);
   }
-  if (max_copy && !src_is_a) {
-    MoveArgs mv = make_move(ms, false, true);
+  if (max_copy && src_code != BUF_A) {
+    MoveArgs mv = make_move(ms, src_code, BUF_A);
     Stage st(c, "copy_segments");
     LAUNCH(c, k_copy_segments, max_copy, 256, 0, mv, copy.view(), counters + 2);
   }
@@ -958,23 +1031,26 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
   ListBufs leaf, large, copy, small;
   DBuf counters(c, 8 * 4), tile_prefix(c, (cap_large + 1) * 4);
   uint32_t h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  bool src_is_a = true;
+  const bool ext = ms.s0[0] != nullptr;   // the rows start outside buffer A: every row has to be moved
+  int src = ext ? BUF_S0 : BUF_A;
   LeafLaunch ll0;
   if (h_seg_off) {
     // ---- level 0 on the host
-    std::vector<uint32_t> lf, lg, cp, tp;  // packed as start[], len[], shift[]
-    std::vector<uint32_t> lf_s, lf_l, lg_s, lg_l, sm_s, sm_l;
+    std::vector<uint32_t> tp;
+    std::vector<uint32_t> lf_s, lf_l, lg_s, lg_l, sm_s, sm_l, cp_s, cp_l;
     tp.push_back(0);
     for (int64_t sidx = 0; sidx < nseg; sidx++) {
       uint32_t st = h_seg_off[sidx], len = h_seg_off[sidx + 1] - st;
-      if (len < 2) continue;
+      if (len == 0 || (len < 2 && !ext)) continue;
       if (len <= SMALL_MAX) { sm_s.push_back(st); sm_l.push_back(len); }
       else if (len <= LEAF_MAX) { lf_s.push_back(st); lf_l.push_back(len); }
       else if (key_bits > 0) { lg_s.push_back(st); lg_l.push_back(len); tp.push_back(tp.back() + (len + PT_TILE - 1) / PT_TILE); }
-      // larger than a leaf with no key bits: all keys equal, already in place at level 0
+      else if (ext) { cp_s.push_back(st); cp_l.push_back(len); }
+      // larger than a leaf with no key bits: all keys equal; in place when the rows already are in A
     }
     h[0] = (uint32_t)lf_s.size();
     h[1] = (uint32_t)lg_s.size();
+    h[2] = (uint32_t)cp_s.size();
     h[3] = tp.back();
     h[5] = (uint32_t)sm_s.size();
     auto upload = [&](ListBufs& lb, const std::vector<uint32_t>& st, const std::vector<uint32_t>& ln) {
@@ -993,10 +1069,10 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     leaf.base.alloc(c, (lf_s.size() ? lf_s.size() : 1) * 8);
     leaf.base.zero();
     upload(small, sm_s, sm_l);
-    copy.alloc(c, 1);
+    upload(copy, cp_s, cp_l);
     CK(cudaMemcpyAsync(counters.p, h, 32, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemcpyAsync(tile_prefix.p, tp.data(), tp.size() * 4, cudaMemcpyHostToDevice, c->stream));
-    run_leaf_and_copy(c, ms, key, true, leaf, h[0], copy, 0, counters.as<uint32_t>(), ll0, &small, h[5]);
+    run_leaf_and_copy(c, ms, key, src, leaf, h[0], copy, h[2], counters.as<uint32_t>(), ll0, &small, h[5]);
     if (h[0]) {
       uint32_t nw = 0;
       CK(cudaMemcpyAsync(&nw, counters.as<uint32_t>() + 4, 4, cudaMemcpyDeviceToHost, c->stream));
@@ -1016,8 +1092,9 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     hs_stage_end(c);
     // leaves first (the grid is an upper bound), then wait for the counts: the wait overlaps the leaf sort
     // sizes are not known on the host yet: the leaf grid is bounded by the rows (a leaf has > SMALL_MAX rows)
+    if (ext) HS_THROW(HS_EINVAL, "external start buffers need host-known segments");
     uint32_t max_leaf0 = (uint32_t)std::min<int64_t>(nseg, n / SMALL_MAX + 1);
-    run_leaf_and_copy(c, ms, key, true, leaf, max_leaf0, copy, 0, counters.as<uint32_t>(), ll0, &small,
+    run_leaf_and_copy(c, ms, key, BUF_A, leaf, max_leaf0, copy, 0, counters.as<uint32_t>(), ll0, &small,
                       (uint32_t)std::min<int64_t>(nseg, 0x7fffffff));
     CK(cudaMemcpyAsync(h, counters.p, 32, cudaMemcpyDeviceToHost, c->stream));
     hs_sync(c);
@@ -1032,7 +1109,7 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     cursor.zero();
     PartParams p;
     memset(&p, 0, sizeof p);
-    p.mv = make_move(ms, src_is_a, !src_is_a);
+    p.mv = make_move(ms, src, other_buf(src));
     p.key = key;
     p.radix = MSD_RADIX;
     p.radix_pad = MSD_RADIX;  // digits of an MSD level
@@ -1074,10 +1151,10 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     hs_stage_begin(c, "msd_plan");
     LAUNCH(c, k_tile_prefix, 1, 1024, 0, nlarge.view(), ncounters.as<uint32_t>(), ntile_prefix.as<uint32_t>());
     hs_stage_end(c);
-    src_is_a = !src_is_a;
+    src = other_buf(src);
     // children that fit a leaf are sorted now; the host learns the counts while they run
     LeafLaunch ll;
-    run_leaf_and_copy(c, ms, key, src_is_a, nleaf, (uint32_t)std::min<size_t>(children, n / SMALL_MAX + 1), ncopy,
+    run_leaf_and_copy(c, ms, key, src, nleaf, (uint32_t)std::min<size_t>(children, n / SMALL_MAX + 1), ncopy,
                       (uint32_t)cap_large, ncounters.as<uint32_t>(), ll, &nsmall, (uint32_t)children);
     CK(cudaMemcpyAsync(h, ncounters.p, 32, cudaMemcpyDeviceToHost, c->stream));
     hs_sync(c);
