@@ -151,6 +151,51 @@ __device__ __forceinline__ void tile_rank_atomic(const uint32_t (&digit)[ITEMS],
     if (k < items && ((vmask >> k) & 1u)) pos[k] += cnt[digit[k]];
 }
 
+// tile_rank_atomic that also reserves the global output runs: gbase[d] = atomicAdd(&cursor[d], rows of d).
+// The global atomics are issued as soon as the counts are final and their results are only consumed after
+// the block scan, so the ~1 us round trip to L2 hides behind the scan (one digit per thread; wider radixes
+// issue them after the scan).
+template <int ITEMS>
+__device__ __forceinline__ void tile_rank_atomic_reserve(const uint32_t (&digit)[ITEMS], uint32_t vmask, int items,
+                                                         int radix_pad, uint32_t* cnt, uint32_t* tot, uint32_t* gbase,
+                                                         uint32_t* cursor, uint32_t* scratch, uint32_t (&pos)[ITEMS]) {
+  for (int i = threadIdx.x; i < radix_pad; i += PT_THREADS) cnt[i] = 0;
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < ITEMS; k++)
+    if (k < items && ((vmask >> k) & 1u)) pos[k] = atomicAdd(&cnt[digit[k]], 1u);
+  __syncthreads();
+  const bool early = radix_pad <= PT_THREADS;
+  uint32_t my_t = 0, my_g = 0;
+  if (early && (int)threadIdx.x < radix_pad) {
+    my_t = cnt[threadIdx.x];
+    if (my_t) my_g = atomicAdd(&cursor[threadIdx.x], my_t);
+  }
+  const int per = (radix_pad + PT_THREADS - 1) / PT_THREADS;
+  const int d0 = threadIdx.x * per, d1 = d0 + per < radix_pad ? d0 + per : radix_pad;
+  uint32_t s = 0;
+  for (int j = d0; j < d1; j++) s += cnt[j];
+  uint32_t ex = block_excl_scan_u32(s, scratch, nullptr);
+  for (int j = d0; j < d1; j++) {
+    uint32_t c = cnt[j];
+    tot[j] = c;
+    cnt[j] = ex;
+    ex += c;
+  }
+  if (early && (int)threadIdx.x < radix_pad) gbase[threadIdx.x] = my_g;
+  __syncthreads();
+  if (!early) {
+    for (int d = threadIdx.x; d < radix_pad; d += PT_THREADS) {
+      uint32_t t = tot[d];
+      gbase[d] = t ? atomicAdd(&cursor[d], t) : 0;
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int k = 0; k < ITEMS; k++)
+    if (k < items && ((vmask >> k) & 1u)) pos[k] += cnt[digit[k]];
+}
+
 // Variants that take the digit as a bit field of a 32-bit word (no digit array in registers).
 template <int ITEMS>
 __device__ __forceinline__ void tile_rank_atomic_w(const uint32_t (&word)[ITEMS], int shift, uint32_t mask,

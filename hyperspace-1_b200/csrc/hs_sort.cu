@@ -86,7 +86,8 @@ struct TileSmem {
   uint32_t* tot;            // radix_pad: rows per digit
   uint32_t* gbase;          // radix_pad: reserved global run start per digit
   uint32_t* scratch;        // PT_SCRATCH
-  uint64_t* bar;            // 2 mbarriers
+  uint64_t* bar;            // 3 mbarriers
+  unsigned char* bstage;    // TMA landing buffer of the tile's bucket ids (u16)
 };
 __device__ __forceinline__ TileSmem carve(unsigned char* base, int radix_pad) {
   TileSmem s;
@@ -99,11 +100,12 @@ __device__ __forceinline__ TileSmem carve(unsigned char* base, int radix_pad) {
   s.gbase = s.tot + radix_pad;
   s.scratch = s.gbase + radix_pad;
   s.bar = (uint64_t*)(s.scratch + PT_SCRATCH);
+  s.bstage = (unsigned char*)(s.bar + 4);
   return s;
 }
 static size_t tile_smem_bytes(int radix_pad) {
   return (size_t)2 * STAGE_BYTES + (size_t)PT_TILE * 4 + (size_t)PT_TILE * 2 + (size_t)3 * radix_pad * 4 +
-         PT_SCRATCH * 4 + 16;
+         PT_SCRATCH * 4 + 32 + (size_t)PT_TILE * 2 + 32;
 }
 
 struct PartParams {
@@ -213,11 +215,13 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
   if (threadIdx.x == 0) {
     mbar_init(&sm.bar[0], 1);
     mbar_init(&sm.bar[1], 1);
+    mbar_init(&sm.bar[2], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
   __syncthreads();
   if (threadIdx.x == 0) {
+    if (MODE != 1) issue_slice(p.bucket, 2, tile_start, tile_len, sm.bstage, &sm.bar[2]);
     int c0 = col_at(0);
     issue_slice(p.mv.src[c0], p.mv.esize[c0], tile_start, tile_len, sm.stage[0], &sm.bar[0]);
     if (ncols > 1) {
@@ -228,6 +232,8 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
   uint32_t digit[PT_ITEMS], pos[PT_ITEMS];
   uint32_t vmask = 0;
   if (MODE == 1) mbar_wait(&sm.bar[0], 0);
+  else mbar_wait(&sm.bar[2], 0);
+  const uint16_t* sbucket = (const uint16_t*)(sm.bstage + slice_lead(p.bucket, 2, tile_start));
 #pragma unroll
   for (int k = 0; k < PT_ITEMS; k++) {
     uint32_t idx = threadIdx.x + k * PT_THREADS;
@@ -236,7 +242,7 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
     digit[k] = 0;
     if (v) {
       if (MODE == 0 || MODE == 2) {
-        digit[k] = p.bucket[tile_start + idx];
+        digit[k] = sbucket[idx];
       } else {
         const unsigned char* ks = sm.stage[0] + slice_lead(p.mv.src[first], p.mv.esize[first], tile_start);
         uint64_t key;
@@ -248,12 +254,8 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
     }
   }
   // the order of rows inside a digit is irrelevant here (the sort below fixes it): rank with atomics
-  tile_rank_atomic<PT_ITEMS>(digit, vmask, PT_ITEMS, p.radix_pad, sm.cnt, sm.tot, sm.scratch, pos);
-  for (int d = threadIdx.x; d < p.radix_pad; d += PT_THREADS) {
-    uint32_t t = sm.tot[d];
-    sm.gbase[d] = t ? atomicAdd(&cursor[d], t) : 0;
-  }
-  __syncthreads();
+  tile_rank_atomic_reserve<PT_ITEMS>(digit, vmask, PT_ITEMS, p.radix_pad, sm.cnt, sm.tot, sm.gbase, cursor,
+                                     sm.scratch, pos);
 #pragma unroll
   for (int k = 0; k < PT_ITEMS; k++) {
     if ((vmask >> k) & 1u) {
