@@ -7,6 +7,7 @@
 // row binary-searches its bucket of the right run (the probes of a warp share cache lines), a scan turns
 // match counts into output offsets, and the pairs are expanded and gathered.
 #include <algorithm>
+#include <stdlib.h>
 
 #include "hs_keys.cuh"
 #include "hs_kernels.h"
@@ -120,6 +121,11 @@ struct JoinFast {
   uint32_t ntiles;
   uint32_t* tile_win;                     // [2 * ntiles]: window [lo, hi) of the right run per tile
   uint32_t* tile_cnt;                     // pass 1 out / pass 2 in: matches per tile, then exclusive offsets
+  // single-pass mode: chained scan over the tiles (decoupled look-back) instead of a separate count pass
+  unsigned long long* tile_state;         // [ntiles]: (flag << 62) | value; flag 1 = tile total, 2 = inclusive prefix
+  uint32_t* ticket;                       // dynamic tile ids: a tile only ever waits for tiles that already run
+  uint32_t capacity;                      // rows the output buffers can hold
+  uint32_t* overflow;                     // set when the output does not fit: the caller falls back to two passes
   int32_t n_lout, n_rout;
   const void* lsrc[16]; const void* rsrc[16];
   void* ldst[16]; void* rdst[16];
@@ -175,14 +181,21 @@ __device__ __forceinline__ uint32_t window_advance(const K* sR, uint32_t pos, ui
   return pos;
 }
 
-template <typename K, bool WRITE>
+// MODE 0: count matches per tile.  MODE 1: write, offsets from the scanned counts.
+// MODE 2: single pass — the tile's output offset comes from a chained scan over the tiles.
+template <typename K, int MODE>
 __global__ void __launch_bounds__(JTHREADS) k_join_tiles(const __grid_constant__ JoinFast p) {
   extern __shared__ __align__(16) unsigned char jsm[];
   K* sR = (K*)jsm;                                   // JR staged right keys
   uint32_t* slb = (uint32_t*)(sR + JR);              // JT  (absolute right row of the first match)
   uint32_t* scn = slb + JT;                          // JT + 1 (exclusive scan of the match counts)
   __shared__ uint32_t s_red[JTHREADS / 32 + 1];
-  const uint32_t t = blockIdx.x;
+  __shared__ uint32_t s_tile, s_obase;
+  if (MODE == 2) {
+    if (threadIdx.x == 0) s_tile = atomicAdd(p.ticket, 1u);
+    __syncthreads();
+  }
+  const uint32_t t = MODE == 2 ? s_tile : blockIdx.x;
   const uint32_t l0 = p.tile_start[t], ln = p.tile_len[t];
   const K* lk = (const K*)p.lkey + l0;
   const K* rk = (const K*)p.rkey;
@@ -250,12 +263,36 @@ __global__ void __launch_bounds__(JTHREADS) k_join_tiles(const __grid_constant__
   }
   __syncthreads();
   const uint32_t total = s_red[JTHREADS / 32];
-  if (!WRITE) {
+  if (MODE == 0) {
     if (threadIdx.x == 0) p.tile_cnt[t] = total;
     return;
   }
   uint32_t ex = inc - mysum + s_red[threadIdx.x >> 5];
-  const uint32_t obase = p.tile_cnt[t];   // exclusive offset of this tile in the output
+  if (MODE == 2) {
+    if (threadIdx.x == 0) {
+      const unsigned long long FA = 1ull << 62, FP = 2ull << 62, VM = (1ull << 62) - 1;
+      volatile unsigned long long* st = p.tile_state;
+      unsigned long long excl = 0;
+      if (t > 0) {
+        st[t] = FA | total;
+        __threadfence();
+        for (int64_t q = (int64_t)t - 1; q >= 0; q--) {
+          unsigned long long v;
+          do { v = st[q]; } while ((v >> 62) == 0);   // the predecessor has started (ticket order): it will publish
+          excl += v & VM;
+          if ((v >> 62) == 2) break;
+        }
+      }
+      __threadfence();
+      st[t] = FP | (excl + total);
+      s_obase = (uint32_t)excl;
+      p.tile_cnt[t] = (uint32_t)excl;
+      if (excl + total > p.capacity) *p.overflow = 1;
+    }
+    __syncthreads();
+    if ((unsigned long long)s_obase + total > p.capacity) return;   // does not fit: count only
+  }
+  const uint32_t obase = MODE == 2 ? s_obase : p.tile_cnt[t];   // exclusive offset of this tile in the output
   // warp-level view of the outputs: a warp whose rows produce at most 256 outputs transposes them through
   // shared memory (the slb/scn area is free in this mode) so that global stores are fully coalesced
   uint32_t winc = mysum;
@@ -469,20 +506,78 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
     int dev = 0;
     CK(cudaGetDevice(&dev));
     if (!attr_done[dev & 63]) {
-      CK(cudaFuncSetAttribute(k_join_tiles<int64_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int64_t>()));
-      CK(cudaFuncSetAttribute(k_join_tiles<int64_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int64_t>()));
-      CK(cudaFuncSetAttribute(k_join_tiles<int32_t, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int32_t>()));
-      CK(cudaFuncSetAttribute(k_join_tiles<int32_t, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int32_t>()));
+      CK(cudaFuncSetAttribute(k_join_tiles<int64_t, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int64_t>()));
+      CK(cudaFuncSetAttribute(k_join_tiles<int64_t, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int64_t>()));
+      CK(cudaFuncSetAttribute(k_join_tiles<int32_t, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int32_t>()));
+      CK(cudaFuncSetAttribute(k_join_tiles<int32_t, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int32_t>()));
+      CK(cudaFuncSetAttribute(k_join_tiles<int64_t, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int64_t>()));
+      CK(cudaFuncSetAttribute(k_join_tiles<int32_t, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int32_t>()));
       attr_done[dev & 63] = true;
     }
     uint64_t h_tot = 0;
     std::vector<uint32_t> h_off((size_t)ntiles);
+    // ---- single pass first: the output is sized for one match per left row (a key -> unique-key join, the
+    // shape JoinIndexRule mostly produces); tiles learn their output offset from a chained scan. If the matches
+    // do not fit, the pass has only counted and the two-pass path below runs instead.
+    const char* no_single = getenv("HSGPU_JOIN_TWO_PASS");
+    if (!(no_single && *no_single && *no_single != '0')) {
+      const int64_t cap = nl;
+      std::vector<OutCol> ocols((size_t)(n_left_out + n_right_out));
+      auto bind = [&](OutCol& o, const DevCol& sc) {
+        o.type = sc.type; o.length = 0; o.null_count = 0;
+        o.data.alloc(ctx, (size_t)cap * hs_fixed_width(sc.type) + 16);
+      };
+      for (int i = 0; i < n_left_out; i++) {
+        const DevCol& sc = lc[left_out[i]];
+        bind(ocols[i], sc);
+        jf.lsrc[i] = sc.data; jf.ldst[i] = ocols[i].data.p; jf.les[i] = hs_fixed_width(sc.type);
+      }
+      for (int i = 0; i < n_right_out; i++) {
+        const DevCol& sc = rc[right_out[i]];
+        bind(ocols[n_left_out + i], sc);
+        jf.rsrc[i] = sc.data; jf.rdst[i] = ocols[n_left_out + i].data.p; jf.res[i] = hs_fixed_width(sc.type);
+      }
+      jf.n_lout = n_left_out; jf.n_rout = n_right_out;
+      DBuf d_state(ctx, (size_t)ntiles * 8), d_misc(ctx, 16);
+      d_state.zero();
+      d_misc.zero();
+      jf.tile_state = d_state.as<unsigned long long>();
+      jf.ticket = d_misc.as<uint32_t>();
+      jf.overflow = d_misc.as<uint32_t>() + 1;
+      jf.capacity = (uint32_t)cap;
+      uint32_t h_misc[4] = {0, 0, 0, 0};
+      unsigned long long h_last = 0;
+      {
+        Stage s(ctx, "join_fused");
+        if (k64) LAUNCH(ctx, k_join_windows<int64_t>, (ntiles + 7) / 8, 256, 0, jf);
+        else LAUNCH(ctx, k_join_windows<int32_t>, (ntiles + 7) / 8, 256, 0, jf);
+        if (k64) LAUNCH(ctx, (k_join_tiles<int64_t, 2>), ntiles, JTHREADS, smem, jf);
+        else LAUNCH(ctx, (k_join_tiles<int32_t, 2>), ntiles, JTHREADS, smem, jf);
+        CK(cudaMemcpyAsync(h_misc, d_misc.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaMemcpyAsync(&h_last, d_state.as<unsigned long long>() + (ntiles - 1), 8, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaMemcpyAsync(h_off.data(), d_cnt.p, (size_t)ntiles * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        hs_sync(ctx);
+      }
+      if (!h_misc[1]) {
+        const int64_t m = (int64_t)(h_last & ((1ull << 62) - 1));
+        for (size_t i = 0; i < ocols.size(); i++) {
+          ocols[i].length = m;
+          ocols[i].data_bytes = m * hs_fixed_width(ocols[i].type);
+        }
+        std::vector<int64_t> ooff((size_t)nb + 1, 0);
+        for (int b = 0; b <= nb; b++) ooff[b] = first_tile[b] < ntiles ? (int64_t)h_off[first_tile[b]] : m;
+        Stage s(ctx, "d2h");
+        *out = hs_finish_table(ctx, ocols, m, nb, &ooff);
+        return HS_OK;
+      }
+      // more matches than left rows: fall through to the exact two-pass path
+    }
     {
       Stage s(ctx, "join_count");
       if (k64) LAUNCH(ctx, k_join_windows<int64_t>, (ntiles + 7) / 8, 256, 0, jf);
       else LAUNCH(ctx, k_join_windows<int32_t>, (ntiles + 7) / 8, 256, 0, jf);
-      if (k64) LAUNCH(ctx, (k_join_tiles<int64_t, false>), ntiles, JTHREADS, smem, jf);
-      else LAUNCH(ctx, (k_join_tiles<int32_t, false>), ntiles, JTHREADS, smem, jf);
+      if (k64) LAUNCH(ctx, (k_join_tiles<int64_t, 0>), ntiles, JTHREADS, smem, jf);
+      else LAUNCH(ctx, (k_join_tiles<int32_t, 0>), ntiles, JTHREADS, smem, jf);
       hs_exclusive_scan_u32(ctx, d_cnt.as<uint32_t>(), d_cnt.as<uint32_t>(), ntiles, d_total.as<uint64_t>());
       CK(cudaMemcpyAsync(&h_tot, d_total.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
       CK(cudaMemcpyAsync(h_off.data(), d_cnt.p, (size_t)ntiles * 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -510,8 +605,8 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
     jf.n_lout = n_left_out; jf.n_rout = n_right_out;
     {
       Stage s(ctx, "join_write");
-      if (k64) LAUNCH(ctx, (k_join_tiles<int64_t, true>), ntiles, JTHREADS, smem, jf);
-      else LAUNCH(ctx, (k_join_tiles<int32_t, true>), ntiles, JTHREADS, smem, jf);
+      if (k64) LAUNCH(ctx, (k_join_tiles<int64_t, 1>), ntiles, JTHREADS, smem, jf);
+      else LAUNCH(ctx, (k_join_tiles<int32_t, 1>), ntiles, JTHREADS, smem, jf);
     }
     std::vector<int64_t> ooff((size_t)nb + 1, 0);
     for (int b = 0; b <= nb; b++) ooff[b] = first_tile[b] < ntiles ? (int64_t)h_off[first_tile[b]] : m;
