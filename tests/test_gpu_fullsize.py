@@ -95,3 +95,82 @@ def test_cfg2_build_and_cfg3_join_properties(hs):
     ot.free()
     t.free()
     ctx.close()
+
+
+def test_cfg5_shape_composite_key_properties(hs):
+    """cfg5 per-GPU shape at 50 M rows: (k1:int32 < 2^20, k2:int64 < 2^40, v:float64), 1024 buckets —
+    lexicographic order inside every bucket, bucket membership, checksums."""
+    import torch
+    from hyperspace_1_b200 import abi
+    dev = torch.device("cuda", 0)
+    n = int(os.environ.get("HS_CFG5_ROWS", "50000000"))
+    g = torch.Generator(device=dev)
+    g.manual_seed(20240604)
+    k1 = torch.randint(0, 1 << 20, (n,), generator=g, device=dev, dtype=torch.int32)
+    k2 = torch.randint(0, 1 << 40, (n,), generator=g, device=dev, dtype=torch.int64)
+    v = torch.rand(n, generator=g, device=dev, dtype=torch.float64)
+    torch.cuda.synchronize()
+    ctx = hs.Context(0)
+    ctx.set_output_location(abi.HS_MEM_DEVICE)
+    cs = abi.DeviceColumnSet([{"type": abi.HS_INT32, "length": n, "data": k1.data_ptr()},
+                              {"type": abi.HS_INT64, "length": n, "data": k2.data_ptr()},
+                              {"type": abi.HS_FLOAT64, "length": n, "data": v.data_ptr()}])
+    nb = 1024
+    t = ctx.build_index_table(cs, 2, nb)
+    boff = t.bucket_offsets()
+    assert t.nrows == n and boff[-1] == n
+    o1 = _dev_tensor(torch, t.column(0), torch.int32, n)
+    o2 = _dev_tensor(torch, t.column(1), torch.int64, n)
+    ov = _dev_tensor(torch, t.column(2), torch.float64, n)
+    mix_in = (k1.to(torch.int64) * 1000003 + k2 * 7 + v.view(torch.int64)).sum()
+    mix_out = (o1.to(torch.int64) * 1000003 + o2 * 7 + ov.view(torch.int64)).sum()
+    assert int(mix_in) == int(mix_out), "rows were torn apart or lost"
+    bad = ((o1[1:] < o1[:-1]) | ((o1[1:] == o1[:-1]) & (o2[1:] < o2[:-1]))).nonzero().flatten() + 1
+    starts = torch.as_tensor(boff[1:-1], device=dev)
+    assert bool(torch.isin(bad, starts).all()), "a bucket is not sorted on (k1, k2)"
+    bid = torch.empty(n, dtype=torch.int32, device=dev)
+    kcs = abi.DeviceColumnSet([{"type": abi.HS_INT32, "length": n, "data": t.column(0).data},
+                               {"type": abi.HS_INT64, "length": n, "data": t.column(1).data}])
+    assert ctx._lib.hs_hash_bucket(ctx._h, kcs.ptr(), C.c_int32(2), C.c_int32(nb), C.c_void_p(bid.data_ptr())) == 0
+    want = torch.repeat_interleave(torch.arange(nb, dtype=torch.int32, device=dev), torch.as_tensor(np.diff(boff), device=dev))
+    assert bool((bid == want).all()), "a row is in the wrong bucket"
+    t.free()
+    ctx.close()
+
+
+def test_cfg4_shape_string_keys_properties(hs, oracle):
+    """cfg4 shape at 10 M rows (host buffers): variable-length keys from a 64-symbol alphabet, 10 % sharing one of
+    1000 16-byte prefixes, 1000 buckets. Every output row is checked: bucket membership (oracle hash), order
+    inside the bucket, and (key, row id) pairing against the input."""
+    import pyarrow as pa
+    import pyarrow.compute as pc
+    m = int(os.environ.get("HS_CFG4_ROWS", "10000000"))
+    rng = np.random.default_rng(20240603)
+    lens = np.clip(8 + rng.geometric(1 / 17, size=m), 1, 96).astype(np.int32)
+    off = np.zeros(m + 1, dtype=np.int32)
+    np.cumsum(lens, out=off[1:])
+    alphabet = np.frombuffer(b"abcdefghijklmnopqrstuvwxyzABCDEFGHIJKLMNOPQRSTUVWXYZ0123456789-_", dtype=np.uint8)
+    data = alphabet[rng.integers(0, 64, size=int(off[-1]))]
+    pref = alphabet[rng.integers(0, 64, size=(1000, 16))]
+    sel = np.nonzero((rng.random(m) < 0.10) & (lens >= 16))[0]
+    pi = rng.integers(0, 1000, size=len(sel))
+    for j in range(16):
+        data[off[sel] + j] = pref[pi, j]
+    s = pa.Array.from_buffers(pa.string(), m, [None, pa.py_buffer(off.tobytes()), pa.py_buffer(data.tobytes())])
+    rid = pa.array(np.arange(m, dtype=np.int64))
+    ctx = hs.Context(0)
+    nb = 1000
+    got, boff = ctx.build_index([s, rid], 1, nb)
+    ctx.close()
+    assert len(got[0]) == m and boff[-1] == m
+    # pairing: the key that travelled with row id r is the input key of row r; every row id appears once
+    r = got[1].to_numpy()
+    assert np.array_equal(np.sort(r), np.arange(m))
+    assert got[0].equals(s.take(pa.array(r)))
+    # membership: the oracle's bucket of every output key is the bucket the row sits in
+    b = oracle.bucket_ids([got[0]], nb)
+    assert np.array_equal(b, np.repeat(np.arange(nb, dtype=np.int32), np.diff(boff)))
+    # order: inside a bucket keys never decrease (byte-wise)
+    a0, a1 = got[0].slice(0, m - 1).cast(pa.binary()), got[0].slice(1).cast(pa.binary())
+    dec = np.nonzero(pc.greater(a0, a1).to_numpy(zero_copy_only=False))[0] + 1
+    assert np.isin(dec, boff[1:-1]).all(), "a bucket is not sorted"
