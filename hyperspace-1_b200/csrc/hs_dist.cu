@@ -130,6 +130,37 @@ static void p2p_destroy(hs_ctx* c) {
   cudaGetLastError();
 }
 
+// copies runs of rows into the owners' buffers: run j = (src row, dst row, rows, owner); dst[owner] are
+// peer-mapped pointers, so the stores of a warp leave as full 128-byte lines over NVLink
+struct PeerPtrs { unsigned char* p[HS_MAX_PEERS_HOST]; };
+__global__ void __launch_bounds__(256) k_copy_runs_peers(const unsigned char* __restrict__ src, PeerPtrs dst,
+                                                         const uint32_t* __restrict__ runs, int esize) {
+  const uint32_t s0 = runs[4 * blockIdx.x], d0 = runs[4 * blockIdx.x + 1], m = runs[4 * blockIdx.x + 2];
+  const uint32_t owner = runs[4 * blockIdx.x + 3];
+  const unsigned char* sp = src + (size_t)s0 * esize;
+  unsigned char* dp = dst.p[owner] + (size_t)d0 * esize;
+  size_t bytes = (size_t)m * esize;
+  if ((((uintptr_t)sp | (uintptr_t)dp) & 15) == 0) {
+    size_t nv = bytes >> 4;
+    const uint4* s4 = (const uint4*)sp;
+    uint4* d4 = (uint4*)dp;
+    for (size_t i = threadIdx.x; i < nv; i += blockDim.x) d4[i] = s4[i];
+    for (size_t i = (nv << 4) + threadIdx.x; i < bytes; i += blockDim.x) dp[i] = sp[i];
+  } else if ((((uintptr_t)sp | (uintptr_t)dp) & 7) == 0 && (bytes & 7) == 0) {
+    size_t nv = bytes >> 3;
+    const uint64_t* s8 = (const uint64_t*)sp;
+    uint64_t* d8 = (uint64_t*)dp;
+    for (size_t i = threadIdx.x; i < nv; i += blockDim.x) d8[i] = s8[i];
+  } else if ((((uintptr_t)sp | (uintptr_t)dp) & 3) == 0 && (bytes & 3) == 0) {
+    size_t nv = bytes >> 2;
+    const uint32_t* s4 = (const uint32_t*)sp;
+    uint32_t* d4 = (uint32_t*)dp;
+    for (size_t i = threadIdx.x; i < nv; i += blockDim.x) d4[i] = s4[i];
+  } else {
+    for (size_t i = threadIdx.x; i < bytes; i += blockDim.x) dp[i] = sp[i];
+  }
+}
+
 // The exchange step of the build. Each rank has scattered its rows by bucket; the run of bucket b goes to
 // owner(b), which places the runs of all senders for that bucket next to each other. The receive therefore
 // finishes the bucket partition: nothing is re-hashed or re-scattered after it.
@@ -380,13 +411,58 @@ struct NcclExchange : BuildExchange {
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
     CK(cudaEventCreate(&e1));
-    {
+    const char* mode = getenv("HSGPU_P2P_MODE");
+    const bool one_kernel = !(mode && !strcmp(mode, "copy"));   // default: the fused kernel (measured faster)
+    if (one_kernel) {
+      // one kernel: the bucket scatter stores every row at its final place in the owner's memory
       Stage s(c, "scatter_to_owners");
       DBuf d_base(c, (size_t)nb * 4);
       CK(cudaMemcpyAsync(d_base.p, run_base.data(), (size_t)nb * 4, cudaMemcpyHostToDevice, c->stream));
       CK(cudaEventRecord(e0, c->stream));
       hs_bucket_scatter_peers(c, srcs, esize.data(), ncol, st->peer_ptr.data(), N, d_bucket, n_local, nb,
                               d_base.as<uint32_t>());
+      CK(cudaEventRecord(e1, c->stream));
+      hs_sync(c);   // my stores have left this GPU
+    } else {
+      // two kernels (HSGPU_P2P_MODE=copy; 3.6 ms vs 3.06 ms fused at N=2): scatter locally, then push whole
+      // bucket runs to their final place in the owners' memory with full-line peer stores
+      std::vector<uint32_t> local_off((size_t)nb + 1, 0);
+      for (int b = 0; b < nb; b++) local_off[b + 1] = local_off[b] + all_hist[(size_t)me * nb + b];
+      std::vector<DBuf> tmp((size_t)ncol);
+      MoveSet ms;
+      memset(&ms, 0, sizeof ms);
+      ms.n = ncol;
+      for (int i = 0; i < ncol; i++) {
+        tmp[i].alloc(c, (size_t)n_local * esize[i] + 16);
+        ms.esize[i] = esize[i];
+        ms.a[i] = tmp[i].p;
+      }
+      {
+        Stage s(c, "bucket_scatter");
+        DBuf d_loff(c, ((size_t)nb + 1) * 4);
+        CK(cudaMemcpyAsync(d_loff.p, local_off.data(), ((size_t)nb + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+        hs_bucket_scatter(c, srcs, ms, d_bucket, n_local, nb, d_loff.as<uint32_t>());
+      }
+      std::vector<uint32_t> runs;
+      for (int b = 0; b < nb; b++) {
+        uint32_t cnt = all_hist[(size_t)me * nb + b];
+        for (uint32_t done = 0; done < cnt; done += 32768) {
+          runs.push_back(local_off[b] + done);
+          runs.push_back(run_base[b] + done);
+          runs.push_back(cnt - done < 32768 ? cnt - done : 32768);
+          runs.push_back((uint32_t)owner_of(b, N, nb));
+        }
+      }
+      Stage s(c, "runs_to_owners");
+      DBuf d_runs(c, runs.size() * 4 + 16);
+      if (!runs.empty()) CK(cudaMemcpyAsync(d_runs.p, runs.data(), runs.size() * 4, cudaMemcpyHostToDevice, c->stream));
+      CK(cudaEventRecord(e0, c->stream));
+      for (int i = 0; i < ncol && !runs.empty(); i++) {
+        PeerPtrs pp;
+        for (int r = 0; r < N; r++) pp.p[r] = (unsigned char*)st->peer_ptr[(size_t)r * ncol + i];
+        LAUNCH(c, k_copy_runs_peers, (unsigned)(runs.size() / 4), 256, 0, (const unsigned char*)tmp[i].p, pp,
+               d_runs.as<uint32_t>(), esize[i]);
+      }
       CK(cudaEventRecord(e1, c->stream));
       hs_sync(c);   // my stores have left this GPU
     }
