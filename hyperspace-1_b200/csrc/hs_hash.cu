@@ -35,71 +35,62 @@ __device__ __forceinline__ void minmax_flush(uint64_t mn, uint64_t mx, uint64_t*
   }
 }
 
-// MODE 0: out32 = raw hash; 1: out32 = bucket; 2: out16 = bucket, hist[nb] += 1, minmax per fixed key
+// MODE 0: out32 = raw hash; 1: out32 = bucket (any number of key columns)
 template <int MODE>
 __global__ void __launch_bounds__(HASH_THREADS) k_hash_generic(KeySpec ks, int64_t n, int32_t nb, FastPmod fm,
-                                                               int32_t blo, int32_t nbl,
-                                                               int32_t* __restrict__ out32,
-                                                               uint16_t* __restrict__ out16,
-                                                               uint32_t* __restrict__ g_hist, int smem_hist,
-                                                               uint64_t* __restrict__ g_minmax) {
+                                                               int32_t* __restrict__ out32) {
+  int64_t stride = (int64_t)gridDim.x * HASH_THREADS;
+  for (int64_t i = (int64_t)blockIdx.x * HASH_THREADS + threadIdx.x; i < n; i += stride) {
+    uint32_t h = mm_hash_row(ks, i);
+    out32[i] = MODE == 0 ? (int32_t)h : (int32_t)fast_pmod(h, fm);
+  }
+}
+
+// The build's K1 for any key shape: out16 = local bucket id, hist[nbl] += 1, min/max of every fixed-width key
+// column. NK = number of key columns (compile time: the per-column state stays in registers).
+template <int NK>
+__global__ void __launch_bounds__(HASH_THREADS) k_hash_build(KeySpec ks, int64_t n, FastPmod fm, int32_t blo,
+                                                             int32_t nbl, uint16_t* __restrict__ out16,
+                                                             uint32_t* __restrict__ g_hist, int smem_hist,
+                                                             uint64_t* __restrict__ g_minmax) {
   extern __shared__ uint32_t s_hist[];
   uint32_t* hist = g_hist;
-  if (MODE == 2 && smem_hist) {
+  if (smem_hist) {
     for (int b = threadIdx.x; b < nbl; b += HASH_THREADS) s_hist[b] = 0;
     __syncthreads();
     hist = s_hist;
   }
-  uint64_t mn[HS_MAX_KEYS], mx[HS_MAX_KEYS];
-  if (MODE == 2) {
+  uint64_t mn[NK], mx[NK];
 #pragma unroll
-    for (int k = 0; k < HS_MAX_KEYS; k++) { mn[k] = ~0ull; mx[k] = 0; }
-  }
+  for (int k = 0; k < NK; k++) { mn[k] = ~0ull; mx[k] = 0; }
   int64_t stride = (int64_t)gridDim.x * HASH_THREADS;
-  for (int64_t base = (int64_t)blockIdx.x * HASH_THREADS; base < n; base += stride) {
-    int64_t i = base + threadIdx.x;
-    bool valid = i < n;
-    uint32_t h = valid ? mm_hash_row(ks, i) : 0;
-    if (MODE == 0) {
-      if (valid) out32[i] = (int32_t)h;
-    } else {
-      int32_t b = (int32_t)fast_pmod(h, fm);
-      if (MODE == 1) {
-        if (valid) out32[i] = b;
-      } else {
-        b -= blo;
-        if (valid && (b < 0 || b >= nbl)) {  // a row that does not belong to this rank's bucket range
-          atomicAdd((unsigned long long*)&g_minmax[2 * HS_MAX_KEYS], 1ull);
-          b = 0;
-        }
-        if (valid) out16[i] = (uint16_t)b;
-        hist_add(hist, (uint32_t)b, valid);
-        if (valid) {
+  for (int64_t i = (int64_t)blockIdx.x * HASH_THREADS + threadIdx.x; i < n; i += stride) {
+    uint32_t h = 42u;
 #pragma unroll
-          for (int k = 0; k < HS_MAX_KEYS; k++) {
-            if (k < ks.nkeys) {
-              const KCol& c = ks.k[k];
-              if (c.type != HS_UTF8 && c.type != HS_BINARY && (!c.has_nulls || kvalid(c.validity, i))) {
-                uint64_t m = omap_cell(c, i);
-                mn[k] = m < mn[k] ? m : mn[k];
-                mx[k] = m > mx[k] ? m : mx[k];
-              }
-            }
-          }
-        }
+    for (int k = 0; k < NK; k++) {
+      uint64_t m;
+      bool has;
+      h = mm_hash_and_map(ks.k[k], i, h, &m, &has);
+      if (has) {
+        mn[k] = m < mn[k] ? m : mn[k];
+        mx[k] = m > mx[k] ? m : mx[k];
       }
     }
+    int32_t b = (int32_t)fast_pmod(h, fm) - blo;
+    if (b < 0 || b >= nbl) {  // a row that does not belong to this rank's bucket range
+      atomicAdd((unsigned long long*)&g_minmax[2 * HS_MAX_KEYS], 1ull);
+      b = 0;
+    }
+    out16[i] = (uint16_t)b;
+    atomicAdd(&hist[b], 1u);   // shared atomics: ~11 lanes/clk/SM; a hot bucket serialises within the warp only
   }
-  if (MODE == 2) {
 #pragma unroll
-    for (int k = 0; k < HS_MAX_KEYS; k++)
-      if (k < ks.nkeys) minmax_flush(mn[k], mx[k], g_minmax + 2 * k);
-    if (smem_hist) {
-      __syncthreads();
-      for (int b = threadIdx.x; b < nbl; b += HASH_THREADS) {
-        uint32_t v = s_hist[b];
-        if (v) atomicAdd(&g_hist[b], v);
-      }
+  for (int k = 0; k < NK; k++) minmax_flush(mn[k], mx[k], g_minmax + 2 * k);
+  if (smem_hist) {
+    __syncthreads();
+    for (int b = threadIdx.x; b < nbl; b += HASH_THREADS) {
+      uint32_t v = s_hist[b];
+      if (v) atomicAdd(&g_hist[b], v);
     }
   }
 }
@@ -180,10 +171,8 @@ KeySpec hs_make_keyspec(const std::vector<DevCol>& cols, int nkeys) {
 
 void hs_hash_to_i32(hs_ctx* c, const KeySpec& ks, int64_t n, int32_t nb, int32_t* d_out) {
   if (n == 0) return;
-  if (nb <= 0) LAUNCH(c, k_hash_generic<0>, hash_grid(n), HASH_THREADS, 0, ks, n, 1, make_fastpmod(1), 0, 1, d_out, (uint16_t*)nullptr,
-                      (uint32_t*)nullptr, 0, (uint64_t*)nullptr);
-  else LAUNCH(c, k_hash_generic<1>, hash_grid(n), HASH_THREADS, 0, ks, n, nb, make_fastpmod(nb), 0, nb, d_out, (uint16_t*)nullptr,
-              (uint32_t*)nullptr, 0, (uint64_t*)nullptr);
+  if (nb <= 0) LAUNCH(c, k_hash_generic<0>, hash_grid(n), HASH_THREADS, 0, ks, n, 1, make_fastpmod(1), d_out);
+  else LAUNCH(c, k_hash_generic<1>, hash_grid(n), HASH_THREADS, 0, ks, n, nb, make_fastpmod(nb), d_out);
 }
 
 // Local bucket ids (bucket - blo, u16) + histogram over the nbl buckets [blo, blo + nbl) + min/max of
@@ -207,11 +196,25 @@ void hs_hash_bucket_hist(hs_ctx* c, const KeySpec& ks, const std::vector<DevCol>
     return;
   }
   int smem_hist = smem <= 160 * 1024;
-  if (smem_hist && smem > 48 * 1024)
-    CK(cudaFuncSetAttribute(k_hash_generic<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  LAUNCH(c, k_hash_generic<2>, hash_grid(n), HASH_THREADS, smem_hist ? smem : 0, ks, n, nb, make_fastpmod(nb), blo, nbl,
-         (int32_t*)nullptr,
-         d_bucket, d_hist, smem_hist, d_minmax);
+  size_t sm = smem_hist ? smem : 0;
+  FastPmod fm = make_fastpmod(nb);
+#define HS_LAUNCH_BUILD(NK)                                                                                        \
+  do {                                                                                                             \
+    if (sm > 48 * 1024) CK(cudaFuncSetAttribute(k_hash_build<NK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm)); \
+    LAUNCH(c, k_hash_build<NK>, hash_grid(n), HASH_THREADS, sm, ks, n, fm, blo, nbl, d_bucket, d_hist, smem_hist,   \
+           d_minmax);                                                                                              \
+  } while (0)
+  switch (ks.nkeys) {
+    case 1: HS_LAUNCH_BUILD(1); break;
+    case 2: HS_LAUNCH_BUILD(2); break;
+    case 3: HS_LAUNCH_BUILD(3); break;
+    case 4: HS_LAUNCH_BUILD(4); break;
+    case 5: HS_LAUNCH_BUILD(5); break;
+    case 6: HS_LAUNCH_BUILD(6); break;
+    case 7: HS_LAUNCH_BUILD(7); break;
+    default: HS_LAUNCH_BUILD(8); break;
+  }
+#undef HS_LAUNCH_BUILD
 }
 
 extern "C" {

@@ -127,6 +127,27 @@ __device__ __forceinline__ uint64_t omap_f64(double f) {
   uint64_t b = (uint64_t)__double_as_longlong(f);
   return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
 }
+// one cell: contribution to the running hash and, for fixed-width types, the order-preserving image of the
+// value (one load, one type switch for both)
+__device__ __forceinline__ uint32_t mm_hash_and_map(const KCol& c, int64_t i, uint32_t h, uint64_t* mapped, bool* has) {
+  *has = false;
+  if (c.has_nulls && !kvalid(c.validity, i)) return h;
+  switch (c.type) {
+    case HS_BOOL: { uint32_t v = (((const uint8_t*)c.data)[i >> 3] >> (i & 7)) & 1u; *mapped = omap_i64(v); *has = true; return mm_hash_int(v, h); }
+    case HS_INT8: { int32_t v = ((const int8_t*)c.data)[i]; *mapped = omap_i64(v); *has = true; return mm_hash_int((uint32_t)v, h); }
+    case HS_INT16: { int32_t v = ((const int16_t*)c.data)[i]; *mapped = omap_i64(v); *has = true; return mm_hash_int((uint32_t)v, h); }
+    case HS_INT32: { int32_t v = ((const int32_t*)c.data)[i]; *mapped = omap_i64(v); *has = true; return mm_hash_int((uint32_t)v, h); }
+    case HS_INT64: { int64_t v = ((const int64_t*)c.data)[i]; *mapped = omap_i64(v); *has = true; return mm_hash_long((uint64_t)v, h); }
+    case HS_FLOAT32: { float f = ((const float*)c.data)[i]; *mapped = omap_f64((double)f); *has = true; return mm_hash_int(canon_f32_bits(f), h); }
+    case HS_FLOAT64: { double f = ((const double*)c.data)[i]; *mapped = omap_f64(f); *has = true; return mm_hash_long(canon_f64_bits(f), h); }
+    case HS_UTF8:
+    case HS_BINARY: {
+      int32_t s = c.offsets[i], e = c.offsets[i + 1];
+      return mm_hash_bytes((const uint8_t*)c.data + s, e - s, h);
+    }
+  }
+  return h;
+}
 // mapped value of a valid fixed-width cell (callers check validity first)
 __device__ __forceinline__ uint64_t omap_cell(const KCol& c, int64_t i) {
   switch (c.type) {
