@@ -193,8 +193,8 @@ def main():
     ap.add_argument("--impl", default="native")
     ap.add_argument("--rows", type=int, default=100_000_000, help="rows per GPU per step")
     ap.add_argument("--ref-rows", type=int, default=10_000_000, help="rows per step of the CPU arms")
-    ap.add_argument("--e2e-steps", type=int, default=2, help="end-to-end steps per host thread")
-    ap.add_argument("--e2e-threads", type=int, default=2, help="host threads (contexts) of the end-to-end leg at N=1")
+    ap.add_argument("--e2e-steps", type=int, default=3, help="end-to-end steps per host thread")
+    ap.add_argument("--e2e-threads", type=int, default=3, help="host threads (contexts) of the end-to-end leg at N=1")
     ap.add_argument("--no-join", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
@@ -364,8 +364,8 @@ def main():
         e2e = {"value": n * world / dt, "unit": UNIT, "h2d_bytes_per_step": n * ROW_BYTES,
                "d2h_bytes_per_step": n * ROW_BYTES, "ms_per_step": dt * 1e3, "steps": total_steps,
                "host_threads": n_threads,
-               "note": "pinned host buffers in and out through hs_build_index; with 2 host threads (one context "
-                       "each) the upload of one build overlaps the download of the other",
+               "note": "pinned host buffers in and out through hs_build_index; with several host threads (one context "
+                       "each) the uploads of some builds overlap the downloads of others",
                "first_key": int(first_key)}
         del hk, hp, hd
         ctx.set_output_location(abi.HS_MEM_DEVICE)

@@ -10,6 +10,8 @@ import pyarrow as pa
 
 HS_OK, HS_EINVAL, HS_ENOMEM, HS_ECUDA, HS_ENCCL, HS_EUNSUPPORTED = range(6)
 HS_BOOL, HS_INT8, HS_INT16, HS_INT32, HS_INT64, HS_FLOAT32, HS_FLOAT64, HS_UTF8, HS_BINARY = range(1, 10)
+HS_LARGE_UTF8, HS_LARGE_BINARY = 10, 11   # Arrow large_string / large_binary: int64 offsets
+VARLEN = (HS_UTF8, HS_BINARY, HS_LARGE_UTF8, HS_LARGE_BINARY)
 HS_MEM_HOST, HS_MEM_DEVICE = 0, 1
 (HS_PRED_EQ, HS_PRED_NE, HS_PRED_LT, HS_PRED_LE, HS_PRED_GT, HS_PRED_GE,
  HS_PRED_IS_NULL, HS_PRED_IS_NOT_NULL) = range(1, 9)
@@ -77,6 +79,10 @@ def arrow_type_code(t):
         return HS_UTF8
     if pa.types.is_binary(t):
         return HS_BINARY
+    if pa.types.is_large_string(t):
+        return HS_LARGE_UTF8
+    if pa.types.is_large_binary(t):
+        return HS_LARGE_BINARY
     raise TypeError(f"unsupported column type {t}")
 
 
@@ -115,11 +121,11 @@ class ColumnSet:
         col.length = len(a)
         col.null_count = a.null_count
         col.validity = bufs[0].address if (bufs[0] is not None and a.null_count > 0) else None
-        if code in (HS_UTF8, HS_BINARY):
+        if code in VARLEN:
             col.offsets = bufs[1].address if bufs[1] is not None else None
             col.data = bufs[2].address if (len(bufs) > 2 and bufs[2] is not None) else None
             if col.offsets is None:  # zero-length array without buffers
-                z = np.zeros(1, dtype=np.int32)
+                z = np.zeros(1, dtype=np.int64)
                 self._keep.append(z)
                 col.offsets = z.ctypes.data
         else:
@@ -165,11 +171,14 @@ def host_column_to_arrow(col, arrow_type=None):
     validity = None
     if col.validity and col.null_count > 0:
         validity = pa.py_buffer(_np_from_addr(col.validity, (n + 7) // 8).tobytes())
-    if code in (HS_UTF8, HS_BINARY):
-        offs = _np_from_addr(col.offsets, 4 * (n + 1)).view(np.int32).copy()
+    if code in VARLEN:
+        large = code in (HS_LARGE_UTF8, HS_LARGE_BINARY)
+        ow, odt = (8, np.int64) if large else (4, np.int32)
+        offs = _np_from_addr(col.offsets, ow * (n + 1)).view(odt).copy()
         nbytes = int(offs[-1]) if n >= 0 and len(offs) else 0
         data = _np_from_addr(col.data, nbytes).tobytes()
-        t = pa.string() if code == HS_UTF8 else pa.binary()
+        t = {HS_UTF8: pa.string(), HS_BINARY: pa.binary(), HS_LARGE_UTF8: pa.large_string(),
+             HS_LARGE_BINARY: pa.large_binary()}[code]
         arr = pa.Array.from_buffers(t, n, [validity, pa.py_buffer(offs.tobytes()), pa.py_buffer(data)],
                                     null_count=col.null_count if validity is not None else 0)
     elif code == HS_BOOL:
@@ -182,6 +191,10 @@ def host_column_to_arrow(col, arrow_type=None):
         t = pa.from_numpy_dtype(NUMPY_OF[code])
         arr = pa.Array.from_buffers(t, n, [validity, pa.py_buffer(data)],
                                     null_count=col.null_count if validity is not None else 0)
-    if arrow_type is not None and arr.type != arrow_type:
+    if arrow_type is not None and code in VARLEN:
+        # a string column that outgrew int32 offsets comes back as its LARGE twin and stays that way
+        if arr.type != arrow_type and code not in (HS_LARGE_UTF8, HS_LARGE_BINARY):
+            arr = arr.cast(arrow_type)
+    elif arrow_type is not None and arr.type != arrow_type:
         arr = arr.view(arrow_type) if not pa.types.is_date64(arrow_type) else arr.cast(arrow_type)
     return arr

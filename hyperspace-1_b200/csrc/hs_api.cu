@@ -11,6 +11,23 @@ struct TableImpl {
 
 void hs_sync(hs_ctx* c) { CK(cudaStreamSynchronize(c->stream)); }
 
+int hs_read_begin(hs_ctx* c, const void* d_src, size_t bytes) {
+  if (bytes > HS_READ_BYTES) HS_THROW(HS_EINVAL, "hs_read_begin: %zu bytes", bytes);
+  if (!c->rd_pin) {
+    CK(cudaMallocHost(&c->rd_pin, HS_READ_SLOTS * HS_READ_BYTES));
+    for (int i = 0; i < HS_READ_SLOTS; i++) CK(cudaEventCreateWithFlags(&c->rd_ev[i], cudaEventDisableTiming));
+  }
+  int slot = c->rd_next;
+  c->rd_next = (slot + 1) % HS_READ_SLOTS;
+  CK(cudaMemcpyAsync((char*)c->rd_pin + slot * HS_READ_BYTES, d_src, bytes, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaEventRecord(c->rd_ev[slot], c->stream));
+  return slot;
+}
+const void* hs_read_wait(hs_ctx* c, int slot) {
+  CK(cudaEventSynchronize(c->rd_ev[slot]));
+  return (const char*)c->rd_pin + slot * HS_READ_BYTES;
+}
+
 static cudaEvent_t get_event(hs_ctx* c) {
   if (!c->ev_free.empty()) {
     cudaEvent_t e = c->ev_free.back();
@@ -88,17 +105,27 @@ void hs_stage_column(hs_ctx* c, const hs_column& in, DevCol& out) {
     out.validity = (const uint8_t*)to_device(c, in.validity, (size_t)((n + 7) / 8), out);
   if (hs_is_varlen(in.type)) {
     if (!in.offsets) HS_THROW(HS_EINVAL, "UTF8/BINARY column without offsets");
-    int32_t last = 0, first = 0;
+    const size_t ow = hs_offset_width(in.type);
+    int64_t last = 0, first = 0;
+    const char* op = (const char*)in.offsets;
+    auto rd = [&](const void* p) -> int64_t {
+      if (ow == 8) { int64_t v; memcpy(&v, p, 8); return v; }
+      int32_t v; memcpy(&v, p, 4); return v;
+    };
     if (hs_is_device_ptr(in.offsets)) {
-      CK(cudaMemcpyAsync(&last, in.offsets + n, 4, cudaMemcpyDeviceToHost, c->stream));
-      CK(cudaMemcpyAsync(&first, in.offsets, 4, cudaMemcpyDeviceToHost, c->stream));
+      char tmp[16];
+      CK(cudaMemcpyAsync(tmp, op + (size_t)n * ow, ow, cudaMemcpyDeviceToHost, c->stream));
+      CK(cudaMemcpyAsync(tmp + 8, op, ow, cudaMemcpyDeviceToHost, c->stream));
       hs_sync(c);
+      last = rd(tmp);
+      first = rd(tmp + 8);
     } else {
-      last = in.offsets[n];
-      first = in.offsets[0];
+      last = rd(op + (size_t)n * ow);
+      first = rd(op);
     }
     if (first != 0) HS_THROW(HS_EINVAL, "offsets[0] must be 0 (pass an unsliced array)");
-    out.offsets = (const int32_t*)to_device(c, in.offsets, (size_t)(n + 1) * 4, out);
+    if (last < 0) HS_THROW(HS_EINVAL, "negative string offsets");
+    out.offsets = (const int32_t*)to_device(c, in.offsets, (size_t)(n + 1) * ow, out);
     out.data_bytes = last;
     out.data = to_device(c, in.data, (size_t)last, out);
   } else if (in.type == HS_BOOL) {
@@ -230,7 +257,7 @@ hs_table* hs_finish_table(hs_ctx* c, std::vector<OutCol>& cols, int64_t nrows, i
       hc.length = o.length;
       hc.null_count = o.null_count;
       hc.validity = (const uint8_t*)place(o.validity, (size_t)((o.length + 7) / 8));
-      hc.offsets = (const int32_t*)place(o.offsets, (size_t)(o.length + 1) * 4);
+      hc.offsets = (const int32_t*)place(o.offsets, (size_t)(o.length + 1) * hs_offset_width(o.type));
       hc.data = place(o.data, (size_t)o.data_bytes);
       if (!hc.validity) hc.null_count = 0;
     }
@@ -297,6 +324,10 @@ int32_t hs_ctx_destroy(hs_ctx* c) {
   for (auto& s : c->stages) { cudaEventDestroy(s.e0); cudaEventDestroy(s.e1); }
   for (auto e : c->ev_free) cudaEventDestroy(e);
   for (auto& kv : c->pinned_size) cudaFreeHost(kv.first);
+  if (c->rd_pin) {
+    cudaFreeHost(c->rd_pin);
+    for (int i = 0; i < HS_READ_SLOTS; i++) cudaEventDestroy(c->rd_ev[i]);
+  }
   cudaStreamDestroy(c->stream);
   delete c;
   return HS_OK;

@@ -101,8 +101,13 @@ __global__ void __launch_bounds__(256) k_head_positions(const uint8_t* __restric
   for (; i < n; i += stride)
     if (flag[i]) head_pos[rank[i]] = (uint32_t)i;
 }
+// groups of two or more rows: up to TIE_SMALL rows -> the small list (finished in one go by k_tie_finish),
+// longer ones -> the big list (next chunk, another round). counter[0] = small, counter[1] = big.
+#define TIE_SMALL 64
+#define TF_PRE 3
 __global__ void __launch_bounds__(256) k_group_segments(const uint32_t* __restrict__ head_pos, const uint64_t* ngroups,
-                                                        uint32_t n, uint32_t* __restrict__ gstart,
+                                                        uint32_t n, uint32_t* __restrict__ sstart,
+                                                        uint32_t* __restrict__ slen, uint32_t* __restrict__ gstart,
                                                         uint32_t* __restrict__ glen, uint32_t* counter) {
   int64_t G = (int64_t)*ngroups;
   int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -110,12 +115,126 @@ __global__ void __launch_bounds__(256) k_group_segments(const uint32_t* __restri
   for (; g < G; g += stride) {
     uint32_t a = head_pos[g];
     uint32_t b = g + 1 < G ? head_pos[g + 1] : n;
-    if (b - a >= 2) {
-      uint32_t k = atomicAdd(counter, 1u);
+    if (b - a > TIE_SMALL) {
+      uint32_t k = atomicAdd(counter + 1, 1u);
       gstart[k] = a;
       glen[k] = b - a;
+    } else if (b - a >= 2) {
+      // small groups are many (one per shared prefix): one atomic per warp, not per group
+      const uint32_t peers = __activemask();
+      const uint32_t lane = threadIdx.x & 31, leader = __ffs(peers) - 1;
+      uint32_t base = 0;
+      if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(peers));
+      base = __shfl_sync(peers, base, leader);
+      const uint32_t k = base + __popc(peers & ((1u << lane) - 1u));
+      sstart[k] = a;
+      slen[k] = b - a;
     }
   }
+}
+
+struct TieCols {
+  int32_t n, srcrow_col;
+  int32_t esize[HS_MAX_MOVE];
+  void* a[HS_MAX_MOVE];
+};
+// -1 / 0 / +1: rows ra, rb of the SOURCE table compared on key chunks d0, d0+1, ... (equal chunks carry equal
+// "more" flags: the tag byte of a string chunk says whether the string goes on)
+__device__ __forceinline__ int cmp_key_tail(const KeyLayout& L, const KeySpec& ks, uint32_t ra, uint32_t rb, int d0) {
+  for (int d = d0;; d++) {
+    bool ma = false, mb = false;
+    const uint64_t a = nkey_chunk(L, ks, ra, d, &ma);
+    const uint64_t b = nkey_chunk(L, ks, rb, d, &mb);
+    if (a != b) return a < b ? -1 : 1;
+    if (!ma || !mb) return 0;
+  }
+}
+// One warp finishes one small tie group: every row ranks itself inside the group by comparing the rest of its
+// key (chunks d0...) with every other row's, straight from the source columns; the moved columns are permuted in
+// place and the rows are flagged as settled. Most ties of a string key are a handful of rows sharing a prefix:
+// this replaces one full round (flags, scan, group list, next chunk, segmented sort) per 7 more key bytes.
+__global__ void __launch_bounds__(256) k_tie_finish(const __grid_constant__ KeyLayout L, const __grid_constant__ KeySpec ks,
+                                                    const __grid_constant__ TieCols tc,
+                                                    const uint32_t* __restrict__ sstart, const uint32_t* __restrict__ slen,
+                                                    uint32_t ngroups, int d0, uint8_t* __restrict__ flag) {
+  const uint32_t g = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (g >= ngroups) return;
+  const uint32_t start = sstart[g], len = slen[g];
+  const uint32_t lane = lane_id();
+  const uint32_t i0 = lane, i1 = lane + 32;
+  const uint32_t* srcrow = (const uint32_t*)tc.a[tc.srcrow_col];
+  const uint32_t s0 = i0 < len ? srcrow[start + i0] : 0, s1 = i1 < len ? srcrow[start + i1] : 0;
+  // the next TF_PRE chunks of both rows go to registers (independent loads, one round trip); the ranking loop
+  // then runs on shuffles and touches memory only for pairs that still tie after them
+  uint64_t a0[TF_PRE], a1[TF_PRE];
+  bool m0 = i0 < len, m1 = i1 < len;     // "the key goes on" after the chunks read so far
+#pragma unroll
+  for (int t = 0; t < TF_PRE; t++) {
+    a0[t] = a1[t] = 0;
+    if (m0) a0[t] = nkey_chunk(L, ks, s0, d0 + t, &m0);
+    if (m1) a1[t] = nkey_chunk(L, ks, s1, d0 + t, &m1);
+  }
+  uint32_t r0 = 0, r1 = 0;
+  for (uint32_t j = 0; j < len; j++) {
+    const bool hi = j >= 32;
+    const uint32_t sj = __shfl_sync(0xffffffffu, hi ? s1 : s0, j & 31);
+    const bool mj = __shfl_sync(0xffffffffu, (int)(hi ? m1 : m0), j & 31) != 0;
+    int c0 = 0, c1 = 0;
+#pragma unroll
+    for (int t = 0; t < TF_PRE; t++) {
+      const uint64_t b = __shfl_sync(0xffffffffu, hi ? a1[t] : a0[t], j & 31);
+      if (c0 == 0 && b != a0[t]) c0 = b < a0[t] ? -1 : 1;
+      if (c1 == 0 && b != a1[t]) c1 = b < a1[t] ? -1 : 1;
+    }
+    if (i0 < len && j != i0) {
+      if (c0 == 0 && mj && m0) c0 = cmp_key_tail(L, ks, sj, s0, d0 + TF_PRE);
+      r0 += c0 < 0 || (c0 == 0 && j < i0);
+    }
+    if (i1 < len && j != i1) {
+      if (c1 == 0 && mj && m1) c1 = cmp_key_tail(L, ks, sj, s1, d0 + TF_PRE);
+      r1 += c1 < 0 || (c1 == 0 && j < i1);
+    }
+  }
+  auto ld = [](const void* base, size_t i, int es) -> uint64_t {
+    switch (es) {
+      case 8: return ((const uint64_t*)base)[i];
+      case 4: return ((const uint32_t*)base)[i];
+      case 2: return ((const uint16_t*)base)[i];
+      default: return ((const uint8_t*)base)[i];
+    }
+  };
+  auto st = [](void* base, size_t i, int es, uint64_t v) {
+    switch (es) {
+      case 8: ((uint64_t*)base)[i] = v; break;
+      case 4: ((uint32_t*)base)[i] = (uint32_t)v; break;
+      case 2: ((uint16_t*)base)[i] = (uint16_t)v; break;
+      default: ((uint8_t*)base)[i] = (uint8_t)v; break;
+    }
+  };
+  for (int c0 = 0; c0 < tc.n; c0 += 4) {
+    uint64_t v0[4], v1[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int c = c0 + u;
+      v0[u] = v1[u] = 0;
+      if (c < tc.n) {
+        if (i0 < len) v0[u] = ld(tc.a[c], (size_t)start + i0, tc.esize[c]);
+        if (i1 < len) v1[u] = ld(tc.a[c], (size_t)start + i1, tc.esize[c]);
+      }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int c = c0 + u;
+      if (c < tc.n) {
+        if (i0 < len) st(tc.a[c], (size_t)start + r0, tc.esize[c], v0[u]);
+        if (i1 < len) st(tc.a[c], (size_t)start + r1, tc.esize[c], v1[u]);
+      }
+    }
+    __syncwarp();
+  }
+  if (i0 < len) flag[start + i0] = 1;
+  if (i1 < len) flag[start + i1] = 1;
 }
 
 static unsigned grid1d(int64_t n) {
@@ -398,25 +517,43 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
   // ---- keys wider than one chunk (strings, wide composites): refine tie groups chunk by chunk
   if (!L.single_chunk) {
     DBuf flag(c, (size_t)n), rank(c, (size_t)n * 4), head_pos(c, (size_t)n * 4), total(c, 8);
-    DBuf gstart(c, (size_t)(n / 2 + 1) * 4), glen(c, (size_t)(n / 2 + 1) * 4), counter(c, 4);
+    DBuf gstart(c, (size_t)(n / TIE_SMALL + 1) * 4), glen(c, (size_t)(n / TIE_SMALL + 1) * 4), counter(c, 8);
+    DBuf sstart(c, (size_t)(n / 2 + 1) * 4), slen(c, (size_t)(n / 2 + 1) * 4);
     flag.zero();
     LAUNCH(c, k_mark_starts, grid1d(nbl + 1), 256, 0, d_off.as<uint32_t>(), (int64_t)nbl, flag.as<uint8_t>(), (uint32_t)n);
     uint64_t* nkey = (uint64_t*)ms.a[key_mv];
     uint8_t* more = (uint8_t*)ms.a[more_mv];
     const uint32_t* srcrow = (const uint32_t*)ms.a[srcrow_mv];
+    TieCols tc;
+    memset(&tc, 0, sizeof tc);
+    tc.n = ms.n;
+    tc.srcrow_col = srcrow_mv;
+    for (int i = 0; i < ms.n; i++) { tc.esize[i] = ms.esize[i]; tc.a[i] = ms.a[i]; }
     for (int d = 0; d < 1 << 20; d++) {
+      hs_stage_begin(c, "tie_groups");
       LAUNCH(c, k_tie_flags, grid1d(n), 256, 0, nkey, more, n, flag.as<uint8_t>());
       hs_exclusive_scan_flags(c, flag.as<uint8_t>(), rank.as<uint32_t>(), n, total.as<uint64_t>());
       LAUNCH(c, k_head_positions, grid1d(n), 256, 0, flag.as<uint8_t>(), rank.as<uint32_t>(), n, head_pos.as<uint32_t>());
       counter.zero();
       LAUNCH(c, k_group_segments, grid1d(n), 256, 0, head_pos.as<uint32_t>(), total.as<uint64_t>(), (uint32_t)n,
-             gstart.as<uint32_t>(), glen.as<uint32_t>(), counter.as<uint32_t>());
-      uint32_t ngroups = 0;
-      CK(cudaMemcpyAsync(&ngroups, counter.p, 4, cudaMemcpyDeviceToHost, c->stream));
-      hs_sync(c);
-      if (ngroups == 0) break;
-      LAUNCH(c, k_build_nkey, grid1d(n), 256, 0, L, ks, n, d + 1, srcrow, (const uint8_t*)flag.p, nkey, more);
-      hs_segmented_sort_list(c, ms, key, 64, gstart.as<uint32_t>(), glen.as<uint32_t>(), ngroups, n);
+             sstart.as<uint32_t>(), slen.as<uint32_t>(), gstart.as<uint32_t>(), glen.as<uint32_t>(), counter.as<uint32_t>());
+      hs_stage_end(c);
+      uint32_t cnt[2];
+      memcpy(cnt, hs_read_wait(c, hs_read_begin(c, counter.p, 8)), 8);
+      if (getenv("HSGPU_TRACE")) fprintf(stderr, "[hsgpu] tie round %d: %u small groups, %u big groups\n", d, cnt[0], cnt[1]);
+      if (cnt[0]) {
+        // small groups are settled for good, whatever the length of the keys
+        Stage st(c, "tie_finish");
+        LAUNCH(c, k_tie_finish, (cnt[0] + 7) / 8, 256, 0, L, ks, tc, sstart.as<uint32_t>(), slen.as<uint32_t>(), cnt[0],
+               d + 1, flag.as<uint8_t>());
+      }
+      if (cnt[1] == 0) break;
+      // long runs of equal prefixes: next chunk, sorted by the segmented sort, and another look
+      {
+        Stage st(c, "tie_next_chunk");
+        LAUNCH(c, k_build_nkey, grid1d(n), 256, 0, L, ks, n, d + 1, srcrow, (const uint8_t*)flag.p, nkey, more);
+      }
+      hs_segmented_sort_list(c, ms, key, 64, gstart.as<uint32_t>(), glen.as<uint32_t>(), cnt[1], n);
     }
   }
 
@@ -460,6 +597,7 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
       nov.type = cols[i].type; nov.length = n; nov.offsets = cols[i].offsets; nov.data = cols[i].data;
       nov.data_bytes = cols[i].data_bytes;
       hs_gather_column(c, nov, (const uint32_t*)ms.a[srcrow_mv], n, g);
+      out[i].type = g.type;
       out[i].offsets = std::move(g.offsets);
       out[i].data = std::move(g.data);
       out[i].data_bytes = g.data_bytes;
@@ -474,11 +612,12 @@ __global__ void __launch_bounds__(256) k_concat_validity(const uint8_t* __restri
   int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (; i < len; i += stride) out_bytes[dst0 + i] = v ? ((v[i >> 3] >> (i & 7)) & 1) : 1;
 }
-__global__ void __launch_bounds__(256) k_rebase_offsets(const int32_t* __restrict__ off, int64_t len, int32_t add,
-                                                        int32_t* __restrict__ out) {
+template <typename TI, typename TO>
+__global__ void __launch_bounds__(256) k_rebase_offsets(const TI* __restrict__ off, int64_t len, int64_t add,
+                                                        TO* __restrict__ out) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (; i <= len; i += stride) out[i] = off[i] + add;
+  for (; i <= len; i += stride) out[i] = (TO)((int64_t)off[i] + add);
 }
 
 static void concat_runs(hs_ctx* c, std::vector<std::vector<DevCol>>& runs, std::vector<DevCol>& out) {
@@ -498,7 +637,9 @@ static void concat_runs(hs_ctx* c, std::vector<std::vector<DevCol>>& runs, std::
       bytes += r[i].data_bytes;
       nulls += r[i].validity ? r[i].null_count : 0;
     }
-    if (hs_is_varlen(o.type) && bytes > 0x7fffffffll) HS_THROW(HS_EUNSUPPORTED, "string column exceeds 2 GiB");
+    // runs with int32 offsets that together exceed 2 GiB come out with int64 offsets (the LARGE twin of the type)
+    const bool in_large = hs_is_large(o.type);
+    if (hs_is_varlen(o.type) && !in_large && bytes > 0x7fffffffll) o.type = o.type == HS_UTF8 ? HS_LARGE_UTF8 : HS_LARGE_BINARY;
     if (any_null) {
       DBuf vb(c, (size_t)(n > 0 ? n : 1));
       int64_t at = 0;
@@ -512,13 +653,20 @@ static void concat_runs(hs_ctx* c, std::vector<std::vector<DevCol>>& runs, std::
       o.null_count = nulls;
     }
     if (hs_is_varlen(o.type)) {
-      o.owned.emplace_back(c, (size_t)(n + 1) * 4);
+      const bool out_large = hs_is_large(o.type);
+      o.owned.emplace_back(c, (size_t)(n + 1) * (out_large ? 8 : 4));
       int32_t* offs = o.owned.back().as<int32_t>();
       o.owned.emplace_back(c, (size_t)bytes);
       uint8_t* data = o.owned.back().as<uint8_t>();
       int64_t at = 0, bat = 0;
       for (auto& r : runs) {
-        LAUNCH(c, k_rebase_offsets, grid1d(r[i].length + 1), 256, 0, r[i].offsets, r[i].length, (int32_t)bat, offs + at);
+        const unsigned g = grid1d(r[i].length + 1);
+        if (in_large)
+          LAUNCH(c, (k_rebase_offsets<int64_t, int64_t>), g, 256, 0, (const int64_t*)r[i].offsets, r[i].length, bat, (int64_t*)offs + at);
+        else if (out_large)
+          LAUNCH(c, (k_rebase_offsets<int32_t, int64_t>), g, 256, 0, r[i].offsets, r[i].length, bat, (int64_t*)offs + at);
+        else
+          LAUNCH(c, (k_rebase_offsets<int32_t, int32_t>), g, 256, 0, r[i].offsets, r[i].length, bat, offs + at);
         if (r[i].data_bytes)
           CK(cudaMemcpyAsync(data + bat, r[i].data, (size_t)r[i].data_bytes, cudaMemcpyDeviceToDevice, c->stream));
         at += r[i].length;

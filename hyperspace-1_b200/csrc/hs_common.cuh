@@ -67,7 +67,13 @@ struct hs_ctx {
   int rank = 0, nranks = 1;
   int64_t last_xchg_bytes = 0;
   float last_xchg_ms = 0.f;
+  // small device->host reads that must not stall the queue behind them (hs_read_begin / hs_read_wait)
+  void* rd_pin = nullptr;            // pinned, HS_READ_SLOTS x HS_READ_BYTES
+  cudaEvent_t rd_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  int rd_next = 0;
 };
+#define HS_READ_SLOTS 4
+#define HS_READ_BYTES 256
 
 // counts a kernel launch (for gpu_launches in bench.py and the per-stage table)
 static inline void hs_count_launch(hs_ctx* c) {
@@ -170,8 +176,10 @@ static inline int hs_fixed_width(int32_t t) {
     default: return 0;
   }
 }
-static inline bool hs_is_varlen(int32_t t) { return t == HS_UTF8 || t == HS_BINARY; }
-static inline bool hs_type_ok(int32_t t) { return t >= HS_BOOL && t <= HS_BINARY; }
+__host__ __device__ __forceinline__ bool hs_is_large(int32_t t) { return t == HS_LARGE_UTF8 || t == HS_LARGE_BINARY; }
+__host__ __device__ __forceinline__ bool hs_is_varlen(int32_t t) { return t >= HS_UTF8 && t <= HS_LARGE_BINARY; }
+static inline bool hs_type_ok(int32_t t) { return t >= HS_BOOL && t <= HS_LARGE_BINARY; }
+static inline size_t hs_offset_width(int32_t t) { return hs_is_large(t) ? 8 : 4; }
 
 bool hs_is_device_ptr(const void* p);
 void hs_stage_column(hs_ctx* c, const hs_column& in, DevCol& out);
@@ -182,6 +190,10 @@ void hs_pinned_free(hs_ctx* c, void* p);
 hs_table* hs_finish_table(hs_ctx* c, std::vector<OutCol>& cols, int64_t nrows, int32_t num_buckets,
                           const std::vector<int64_t>* boff);
 void hs_sync(hs_ctx* c);
+// Copy up to HS_READ_BYTES from the device into a pinned slot and mark the point with an event; work queued
+// afterwards keeps running while the host waits for just that copy. Returns the slot.
+int hs_read_begin(hs_ctx* c, const void* d_src, size_t bytes);
+const void* hs_read_wait(hs_ctx* c, int slot);
 
 #define API_BEGIN(ctx)                      \
   if (!(ctx)) return HS_EINVAL;             \
@@ -207,11 +219,24 @@ __device__ __forceinline__ bool kvalid(const uint8_t* v, int64_t i) {
   return v == nullptr || ((v[i >> 3] >> (i & 7)) & 1);
 }
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
+// start and length of string cell i (int32 or int64 offsets behind the same pointer)
+__device__ __forceinline__ int64_t kstr_start(const KCol& c, int64_t i, int32_t* len) {
+  if (hs_is_large(c.type)) {
+    const int64_t* o = (const int64_t*)c.offsets;
+    int64_t s = o[i];
+    *len = (int32_t)(o[i + 1] - s);
+    return s;
+  }
+  int32_t s = c.offsets[i];
+  *len = c.offsets[i + 1] - s;
+  return s;
+}
 
 // primitives implemented in hs_scan.cu / hs_gather.cu
 // out[i] = sum_{j<i} in[j] (out may alias in); returns nothing, total written to *d_total (device, u64) if non-null
 void hs_exclusive_scan_u32(hs_ctx* c, const uint32_t* in, uint32_t* out, int64_t n, uint64_t* d_total);
 void hs_exclusive_scan_flags(hs_ctx* c, const uint8_t* flags, uint32_t* out, int64_t n, uint64_t* d_total);
+int64_t hs_offsets_from_lens(hs_ctx* c, const uint32_t* lens, int64_t m, int32_t type, OutCol& out);
 // gather rows idx[0..m) of `src` into a new column
 void hs_gather_column(hs_ctx* c, const DevCol& src, const uint32_t* idx, int64_t m, OutCol& out);
 void hs_copy_column(hs_ctx* c, const DevCol& src, OutCol& out);

@@ -43,10 +43,10 @@ __device__ __forceinline__ void eval_leaf(const KCol& c, int64_t i, const KTerm&
     case HS_INT64: { int64_t x = ((const int64_t*)c.data)[i]; cmp = (x > t.lit_i64) - (x < t.lit_i64); break; }
     case HS_FLOAT32: cmp = cmp_f64_total((double)((const float*)c.data)[i], t.lit_f64); break;
     case HS_FLOAT64: cmp = cmp_f64_total(((const double*)c.data)[i], t.lit_f64); break;
-    case HS_UTF8:
-    case HS_BINARY: {
-      int s = c.offsets[i];
-      cmp = cmp_u8str((const uint8_t*)c.data + s, c.offsets[i + 1] - s, pool + t.lit_off, t.lit_len);
+    case HS_UTF8: case HS_BINARY: case HS_LARGE_UTF8: case HS_LARGE_BINARY: {
+      int32_t len;
+      int64_t s = kstr_start(c, i, &len);
+      cmp = cmp_u8str((const uint8_t*)c.data + s, len, pool + t.lit_off, t.lit_len);
       break;
     }
   }
@@ -135,7 +135,7 @@ static bool literal_bucket(int32_t type, const hs_pred_term& t, int32_t nb, int3
       h = h_fmix(h_h1(h, h_k1((uint32_t)(v >> 32))), 8);
       break;
     }
-    case HS_UTF8: case HS_BINARY: {
+    case HS_UTF8: case HS_BINARY: case HS_LARGE_UTF8: case HS_LARGE_BINARY: {
       if (!t.lit_bytes && t.lit_len) return false;
       h = 42u;
       int n = t.lit_len, nw = n & ~3;

@@ -35,33 +35,103 @@ __global__ void __launch_bounds__(256) k_gather_bits(const uint8_t* __restrict__
   if (lane_id() == 0 && cnt && ones) atomicAdd(ones, (unsigned long long)cnt);
 }
 
-__global__ void __launch_bounds__(256) k_gather_lens(const int32_t* __restrict__ off, const uint32_t* __restrict__ idx,
-                                                     int64_t m, uint32_t* __restrict__ lens) {
+// length and source start of every output row: the one random read of the source offsets; the byte mover below
+// then reads its row table sequentially
+template <typename TO>
+__global__ void __launch_bounds__(256) k_gather_lens(const TO* __restrict__ off, const uint32_t* __restrict__ idx,
+                                                     int64_t m, uint32_t* __restrict__ lens, TO* __restrict__ starts) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (; i < m; i += stride) {
     uint32_t s = idx[i];
-    lens[i] = (uint32_t)(off[s + 1] - off[s]);
+    TO a = off[s], b = off[s + 1];
+    lens[i] = (uint32_t)(b - a);
+    starts[i] = a;
   }
 }
 
-// 8 lanes cooperate on one string: short strings (mean ~24 B) finish in one round of 4-byte moves
-__global__ void __launch_bounds__(256) k_gather_bytes(const int32_t* __restrict__ off, const uint8_t* __restrict__ in,
-                                                      const uint32_t* __restrict__ idx, int64_t m,
-                                                      const int32_t* __restrict__ new_off, uint8_t* __restrict__ out) {
-  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 3;
-  int sub = threadIdx.x & 7;
-  for (int64_t i = t >> 3; i < m; i += stride) {
-    uint32_t s = idx[i];
-    const uint8_t* src = in + off[s];
-    int len = off[s + 1] - off[s];
-    uint8_t* dst = out + new_off[i];
-    for (int b = sub; b < len; b += 8) dst[b] = src[b];
+// String bytes of `rows` consecutive OUTPUT rows are contiguous in the output: a CTA collects them in shared
+// memory and then writes the whole span with 16-byte stores (writing string pieces straight to global memory
+// costs a partial-sector write per piece). Per tile:
+//   1. the row table (source start from k_gather_lens, destination start), one row per thread;
+//   2. 16 lanes fetch one string as aligned 4-byte words (64 bytes per step, four strings in flight per
+//      group) and drop the bytes at their place in the staging buffer (measured: faster than cp.async words
+//      into a raw area + a repack, 6.4 vs 8.4 ms for the whole finalize step of 80 M rows);
+//   3. packed span -> global memory, 16 bytes per store.
+// Tiles whose bytes do not fit (long strings) write the bytes to global memory directly.
+#define GB_MAX_ROWS 256
+#define GB_CAP (24 * 1024)
+#define GB_UNROLL 4
+template <typename TO, typename TN>
+__global__ void __launch_bounds__(256) k_gather_bytes(const TO* __restrict__ starts, const uint8_t* __restrict__ in,
+                                                      int64_t m, int rows,
+                                                      const TN* __restrict__ new_off, uint8_t* __restrict__ out) {
+  __shared__ __align__(16) uint8_t s_buf[GB_CAP + 16];
+  __shared__ int64_t s_src[GB_MAX_ROWS];
+  __shared__ int64_t s_dst[GB_MAX_ROWS + 1];
+  const int sub = threadIdx.x & 15, grp = threadIdx.x >> 4;
+  const int64_t ntiles = (m + rows - 1) / rows;
+  for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t r0 = tile * rows;
+    const int nrows = (int)((r0 + rows < m) ? rows : m - r0);
+    if ((int)threadIdx.x < nrows) {
+      s_src[threadIdx.x] = (int64_t)starts[r0 + threadIdx.x];
+      s_dst[threadIdx.x] = (int64_t)new_off[r0 + threadIdx.x];
+    }
+    if (threadIdx.x == 0) s_dst[nrows] = (int64_t)new_off[r0 + nrows];
+    __syncthreads();
+    const int64_t b0 = s_dst[0], bytes = s_dst[nrows] - b0;
+    const bool staged = bytes <= GB_CAP;
+    const uint32_t pad = (uint32_t)((uintptr_t)(out + b0) & 15);
+    uint8_t* const dbase = staged ? s_buf + pad : out + b0;
+    for (int rb = grp; rb < nrows; rb += 16 * GB_UNROLL) {
+      uint32_t w[GB_UNROLL];
+      int len[GB_UNROLL], k0[GB_UNROLL];   // k0 = row byte index of this lane's first fetched byte (may be < 0)
+      const uint8_t* p[GB_UNROLL];
+#pragma unroll
+      for (int u = 0; u < GB_UNROLL; u++) {
+        const int r = rb + u * 16;
+        len[u] = 0;
+        k0[u] = 0;
+        p[u] = in;
+        w[u] = 0;
+        if (r < nrows) {
+          p[u] = in + s_src[r];
+          len[u] = (int)(s_dst[r + 1] - s_dst[r]);
+          k0[u] = 4 * sub - (int)((uintptr_t)p[u] & 3);
+          if (k0[u] < len[u]) w[u] = *(const uint32_t*)(p[u] + k0[u]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < GB_UNROLL; u++) {
+        const int r = rb + u * 16;
+        if (r >= nrows) continue;
+        uint8_t* d = dbase + (s_dst[r] - b0);
+        int k = k0[u];
+        uint32_t word = w[u];
+        while (k < len[u]) {
+#pragma unroll
+          for (int j = 0; j < 4; j++)
+            if (k + j >= 0 && k + j < len[u]) d[k + j] = (uint8_t)(word >> (8 * j));
+          k += 64;
+          if (k < len[u]) word = *(const uint32_t*)(p[u] + k);
+        }
+      }
+    }
+    if (staged) {
+      __syncthreads();
+      uint8_t* g = out + b0 - pad;                       // 16-byte aligned
+      const uint32_t total = pad + (uint32_t)bytes;
+      for (uint32_t lo = threadIdx.x * 16; lo < total; lo += 256 * 16) {
+        const uint32_t hi = lo + 16;
+        if (lo >= pad && hi <= total) *(uint4*)(g + lo) = *(const uint4*)(s_buf + lo);
+        else
+          for (uint32_t b = lo < pad ? pad : lo; b < (hi < total ? hi : total); b++) g[b] = s_buf[b];
+      }
+    }
+    __syncthreads();
   }
 }
-
-__global__ void k_set_last_offset(int32_t* off, int64_t m, const uint64_t* total) { off[m] = (int32_t)*total; }
 
 static unsigned grid_for(int64_t n, int threads = 256) {
   int64_t g = (n + threads - 1) / threads;
@@ -90,20 +160,33 @@ void hs_gather_column(hs_ctx* c, const DevCol& src, const uint32_t* idx, int64_t
   out.length = m;
   gather_validity(c, src, idx, m, out);
   if (hs_is_varlen(src.type)) {
-    out.offsets.alloc(c, (size_t)(m + 1) * 4);
-    DBuf total(c, 8);
-    if (m > 0) LAUNCH(c, k_gather_lens, grid_for(m), 256, 0, src.offsets, idx, m, out.offsets.as<uint32_t>());
-    hs_exclusive_scan_u32(c, out.offsets.as<uint32_t>(), out.offsets.as<uint32_t>(), m, total.as<uint64_t>());
-    LAUNCH(c, k_set_last_offset, 1, 1, 0, out.offsets.as<int32_t>(), m, total.as<uint64_t>());
-    uint64_t h = 0;
-    CK(cudaMemcpyAsync(&h, total.p, 8, cudaMemcpyDeviceToHost, c->stream));
-    hs_sync(c);
-    if (h > 0x7fffffffull) HS_THROW(HS_EUNSUPPORTED, "string column exceeds 2 GiB (int32 offsets)");
-    out.data_bytes = (int64_t)h;
+    const bool in_large = hs_is_large(src.type);
+    DBuf lens(c, (size_t)(m > 0 ? m : 1) * 4), starts(c, (size_t)(m > 0 ? m : 1) * (in_large ? 8 : 4));
+    if (m > 0) {
+      if (in_large)
+        LAUNCH(c, k_gather_lens<int64_t>, grid_for(m), 256, 0, (const int64_t*)src.offsets, idx, m, lens.as<uint32_t>(), starts.as<int64_t>());
+      else
+        LAUNCH(c, k_gather_lens<int32_t>, grid_for(m), 256, 0, src.offsets, idx, m, lens.as<uint32_t>(), starts.as<int32_t>());
+    }
+    // rows can repeat (join output): the gathered bytes may pass 2 GiB even when the source did not
+    const int64_t h = hs_offsets_from_lens(c, lens.as<uint32_t>(), m, src.type, out);
+    const bool out_large = hs_is_large(out.type);
+    out.data_bytes = h;
     out.data.alloc(c, (size_t)h);
-    if (m > 0 && h > 0)
-      LAUNCH(c, k_gather_bytes, grid_for(m * 8), 256, 0, src.offsets, (const uint8_t*)src.data, idx, m,
-             out.offsets.as<int32_t>(), out.data.as<uint8_t>());
+    if (m > 0 && h > 0) {
+      // rows per tile: as many as keep the expected tile inside the staging buffer (3/4 full on average)
+      int rows = GB_MAX_ROWS;
+      while (rows > 8 && (h / m + 1) * rows > GB_CAP * 3 / 4) rows >>= 1;
+      const unsigned g = (unsigned)std::min<int64_t>((m + rows - 1) / rows, (int64_t)HS_NUM_SMS * 32);
+      const uint8_t* in = (const uint8_t*)src.data;
+      uint8_t* o = out.data.as<uint8_t>();
+      if (in_large)   // a LARGE source always gives a LARGE result
+        LAUNCH(c, (k_gather_bytes<int64_t, int64_t>), g, 256, 0, starts.as<int64_t>(), in, m, rows, out.offsets.as<int64_t>(), o);
+      else if (out_large)
+        LAUNCH(c, (k_gather_bytes<int32_t, int64_t>), g, 256, 0, starts.as<int32_t>(), in, m, rows, out.offsets.as<int64_t>(), o);
+      else
+        LAUNCH(c, (k_gather_bytes<int32_t, int32_t>), g, 256, 0, starts.as<int32_t>(), in, m, rows, out.offsets.as<int32_t>(), o);
+    }
   } else if (src.type == HS_BOOL) {
     out.data_bytes = (m + 7) / 8;
     out.data.alloc(c, (size_t)out.data_bytes);
@@ -136,8 +219,8 @@ void hs_copy_column(hs_ctx* c, const DevCol& src, OutCol& out) {
     CK(cudaMemcpyAsync(out.validity.p, src.validity, (size_t)((n + 7) / 8), cudaMemcpyDeviceToDevice, c->stream));
   }
   if (hs_is_varlen(src.type)) {
-    out.offsets.alloc(c, (size_t)(n + 1) * 4);
-    CK(cudaMemcpyAsync(out.offsets.p, src.offsets, (size_t)(n + 1) * 4, cudaMemcpyDeviceToDevice, c->stream));
+    out.offsets.alloc(c, (size_t)(n + 1) * hs_offset_width(src.type));
+    CK(cudaMemcpyAsync(out.offsets.p, src.offsets, (size_t)(n + 1) * hs_offset_width(src.type), cudaMemcpyDeviceToDevice, c->stream));
   }
   out.data_bytes = src.data_bytes;
   out.data.alloc(c, (size_t)src.data_bytes);

@@ -79,10 +79,10 @@ __device__ __forceinline__ uint32_t mm_hash_value(const KCol& c, int64_t i, uint
     case HS_INT64: return mm_hash_long(((const uint64_t*)c.data)[i], h);
     case HS_FLOAT32: return mm_hash_int(canon_f32_bits(((const float*)c.data)[i]), h);
     case HS_FLOAT64: return mm_hash_long(canon_f64_bits(((const double*)c.data)[i]), h);
-    case HS_UTF8:
-    case HS_BINARY: {
-      int32_t s = c.offsets[i], e = c.offsets[i + 1];
-      return mm_hash_bytes((const uint8_t*)c.data + s, e - s, h);
+    case HS_UTF8: case HS_BINARY: case HS_LARGE_UTF8: case HS_LARGE_BINARY: {
+      int32_t len;
+      int64_t s = kstr_start(c, i, &len);
+      return mm_hash_bytes((const uint8_t*)c.data + s, len, h);
     }
   }
   return h;
@@ -140,10 +140,10 @@ __device__ __forceinline__ uint32_t mm_hash_and_map(const KCol& c, int64_t i, ui
     case HS_INT64: { int64_t v = ((const int64_t*)c.data)[i]; *mapped = omap_i64(v); *has = true; return mm_hash_long((uint64_t)v, h); }
     case HS_FLOAT32: { float f = ((const float*)c.data)[i]; *mapped = omap_f64((double)f); *has = true; return mm_hash_int(canon_f32_bits(f), h); }
     case HS_FLOAT64: { double f = ((const double*)c.data)[i]; *mapped = omap_f64(f); *has = true; return mm_hash_long(canon_f64_bits(f), h); }
-    case HS_UTF8:
-    case HS_BINARY: {
-      int32_t s = c.offsets[i], e = c.offsets[i + 1];
-      return mm_hash_bytes((const uint8_t*)c.data + s, e - s, h);
+    case HS_UTF8: case HS_BINARY: case HS_LARGE_UTF8: case HS_LARGE_BINARY: {
+      int32_t len;
+      int64_t s = kstr_start(c, i, &len);
+      return mm_hash_bytes((const uint8_t*)c.data + s, len, h);
     }
   }
   return h;
@@ -189,6 +189,21 @@ struct KeyLayout {
 __device__ __forceinline__ int nk_string_chunks(int len) { return len <= 7 ? 1 : (len + 6) / 7; }
 
 // chunk d of row i; *more = further chunks can still distinguish rows that tie on chunks 0..d
+// bytes p[0..take) (take <= 7) as the top bytes of a big-endian u64, the rest zero. Two aligned 8-byte loads and
+// a funnel shift instead of a byte loop: the loop's loads each wait for the previous one (the value is used at
+// once), which made every caller latency-bound. An aligned word that holds a valid byte lies in that byte's
+// page, so reading it whole is safe.
+__device__ __forceinline__ uint64_t nk_load_be(const uint8_t* p, int take) {
+  if (take <= 0) return 0;
+  const uintptr_t a = (uintptr_t)p & ~(uintptr_t)7;
+  const int mis = (int)((uintptr_t)p & 7);
+  const uint64_t w0 = *(const uint64_t*)a;
+  const uint64_t w1 = mis + take > 8 ? *(const uint64_t*)(a + 8) : 0;
+  const uint64_t le = mis ? (w0 >> (8 * mis)) | (w1 << (64 - 8 * mis)) : w0;   // p[0] in the low byte
+  const uint32_t lo = (uint32_t)le, hi = (uint32_t)(le >> 32);
+  const uint64_t be = ((uint64_t)__byte_perm(lo, 0, 0x0123) << 32) | __byte_perm(hi, 0, 0x0123);
+  return be & ~((1ull << (64 - 8 * take)) - 1ull);
+}
 __device__ __forceinline__ uint64_t nkey_chunk(const KeyLayout& L, const KeySpec& ks, int64_t i, int d,
                                                bool* more) {
   int base = 0;
@@ -218,8 +233,9 @@ __device__ __forceinline__ uint64_t nkey_chunk(const KeyLayout& L, const KeySpec
     } else {
       const KCol& c = ks.k[k];
       bool valid = !c.has_nulls || kvalid(c.validity, i);
-      int s = 0, len = 0;
-      if (valid) { s = c.offsets[i]; len = c.offsets[i + 1] - s; }
+      int64_t s = 0;
+      int len = 0;
+      if (valid) s = kstr_start(c, i, &len);
       int nch = valid ? nk_string_chunks(len) : 1;
       if (d < base + nch) {
         bool later = k + 1 < L.nkeys;
@@ -227,9 +243,7 @@ __device__ __forceinline__ uint64_t nkey_chunk(const KeyLayout& L, const KeySpec
         int j = d - base;
         int rem = len - 7 * j;
         int take = rem > 7 ? 7 : rem;
-        const uint8_t* p = (const uint8_t*)c.data + s + 7 * j;
-        uint64_t v = 0;
-        for (int b = 0; b < take; b++) v |= (uint64_t)p[b] << (56 - 8 * b);
+        const uint64_t v = nk_load_be(( const uint8_t*)c.data + s + 7 * j, take);
         uint64_t tag = rem > 7 ? 9 : (uint64_t)(1 + rem);
         *more = rem > 7 || later;
         return v | tag;
@@ -253,10 +267,10 @@ __device__ __forceinline__ int cmp_u8str(const uint8_t* a, int la, const uint8_t
 }
 // both cells valid
 __device__ __forceinline__ int cmp_cells(const KCol& a, int64_t i, const KCol& b, int64_t j) {
-  if (a.type == HS_UTF8 || a.type == HS_BINARY) {
-    int sa = a.offsets[i], sb = b.offsets[j];
-    return cmp_u8str((const uint8_t*)a.data + sa, a.offsets[i + 1] - sa, (const uint8_t*)b.data + sb,
-                     b.offsets[j + 1] - sb);
+  if (hs_is_varlen(a.type)) {
+    int32_t la, lb;
+    int64_t sa = kstr_start(a, i, &la), sb = kstr_start(b, j, &lb);
+    return cmp_u8str((const uint8_t*)a.data + sa, la, (const uint8_t*)b.data + sb, lb);
   }
   uint64_t x = omap_cell(a, i), y = omap_cell(b, j);
   return (x > y) - (x < y);

@@ -86,9 +86,9 @@ __global__ void __launch_bounds__(1024) k_scan_sums(uint64_t* sums, int64_t nb, 
   if (threadIdx.x == 0 && total) *total = carry;
 }
 
-template <typename T>
-__global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(const T* in, uint32_t* out, int64_t n,
-                                                              const uint64_t* __restrict__ sums) {
+template <typename T, typename TO>
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(const T* in, TO* out, int64_t n,
+                                                              const uint64_t* __restrict__ sums, int write_total) {
   int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
   uint32_t v[SCAN_ITEMS];
   uint32_t s = 0;
@@ -99,12 +99,13 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(const T* in, uint32
     s += v[k];
   }
   uint32_t tot;
-  uint32_t ex = block_excl_scan(s, &tot) + (uint32_t)sums[blockIdx.x];
+  TO ex = (TO)block_excl_scan(s, &tot) + (TO)sums[blockIdx.x];
 #pragma unroll
   for (int k = 0; k < SCAN_ITEMS; k++) {
     int64_t i = base + k;
     if (i < n) out[i] = ex;
     ex += v[k];
+    if (write_total && i == n - 1) out[n] = ex;   // offsets arrays carry the total as their last entry
   }
 }
 
@@ -118,7 +119,7 @@ static void scan_impl(hs_ctx* c, const T* in, uint32_t* out, int64_t n, uint64_t
   DBuf sums(c, (size_t)nb * 8);
   LAUNCH(c, k_scan_reduce<T>, (unsigned)nb, SCAN_THREADS, 0, in, n, sums.as<uint64_t>());
   LAUNCH(c, k_scan_sums, 1, 1024, 0, sums.as<uint64_t>(), nb, d_total);
-  LAUNCH(c, k_scan_apply<T>, (unsigned)nb, SCAN_THREADS, 0, in, out, n, sums.as<uint64_t>());
+  LAUNCH(c, (k_scan_apply<T, uint32_t>), (unsigned)nb, SCAN_THREADS, 0, in, out, n, sums.as<uint64_t>(), 0);
 }
 
 void hs_exclusive_scan_u32(hs_ctx* c, const uint32_t* in, uint32_t* out, int64_t n, uint64_t* d_total) {
@@ -126,4 +127,36 @@ void hs_exclusive_scan_u32(hs_ctx* c, const uint32_t* in, uint32_t* out, int64_t
 }
 void hs_exclusive_scan_flags(hs_ctx* c, const uint8_t* flags, uint32_t* out, int64_t n, uint64_t* d_total) {
   scan_impl<uint8_t>(c, flags, out, n, d_total);
+}
+
+// lens[0..m) -> Arrow offsets (m+1 entries) in `out`, int32 while the bytes fit 2 GiB, int64 (and the LARGE twin
+// of `type`) beyond that or when `type` is LARGE already. Returns the total number of bytes.
+int64_t hs_offsets_from_lens(hs_ctx* c, const uint32_t* lens, int64_t m, int32_t type, OutCol& out) {
+  bool large = hs_is_large(type);
+  if (m <= 0) {
+    out.type = type;
+    out.offsets.alloc(c, large ? 8 : 4);
+    out.offsets.zero();
+    return 0;
+  }
+  int64_t nb = (m + SCAN_TILE - 1) / SCAN_TILE;
+  DBuf sums(c, (size_t)nb * 8), total(c, 8);
+  LAUNCH(c, k_scan_reduce<uint32_t>, (unsigned)nb, SCAN_THREADS, 0, lens, m, sums.as<uint64_t>());
+  LAUNCH(c, k_scan_sums, 1, 1024, 0, sums.as<uint64_t>(), nb, total.as<uint64_t>());
+  uint64_t h = 0;
+  CK(cudaMemcpyAsync(&h, total.p, 8, cudaMemcpyDeviceToHost, c->stream));
+  hs_sync(c);
+  if (!large && h > 0x7fffffffull) {
+    large = true;
+    type = type == HS_UTF8 ? HS_LARGE_UTF8 : HS_LARGE_BINARY;
+  }
+  out.type = type;
+  out.offsets.alloc(c, (size_t)(m + 1) * (large ? 8 : 4));
+  if (large)
+    LAUNCH(c, (k_scan_apply<uint32_t, int64_t>), (unsigned)nb, SCAN_THREADS, 0, lens, out.offsets.as<int64_t>(), m,
+           sums.as<uint64_t>(), 1);
+  else
+    LAUNCH(c, (k_scan_apply<uint32_t, int32_t>), (unsigned)nb, SCAN_THREADS, 0, lens, out.offsets.as<int32_t>(), m,
+           sums.as<uint64_t>(), 1);
+  return (int64_t)h;
 }

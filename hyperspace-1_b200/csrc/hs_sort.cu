@@ -829,16 +829,44 @@ __global__ void __launch_bounds__(PT_THREADS) k_leaf_small(const __grid_constant
     r0 += (kj < k0) || (kj == k0 && j < i0);
     r1 += (kj < k1) || (kj == k1 && j < i1);
   }
-  for (int c = 0; c < p.mv.n; c++) {
-    const int es = p.mv.esize[c];
-    const unsigned char* src = (const unsigned char*)p.mv.src[c] + (size_t)start * es;
-    unsigned char* dst = (unsigned char*)p.mv.dst[c] + (size_t)start * es;
-    uint64_t v0 = 0, v1 = 0;
-    if (i0 < len) memcpy(&v0, src + (size_t)i0 * es, es);
-    if (i1 < len) memcpy(&v1, src + (size_t)i1 * es, es);
-    __syncwarp();  // all reads before any write: src == dst is safe
-    if (i0 < len) memcpy(dst + (size_t)r0 * es, &v0, es);
-    if (i1 < len) memcpy(dst + (size_t)r1 * es, &v1, es);
+  // four columns at a time: all loads are issued before the first store (one memory round trip per group of
+  // columns instead of one per column; also what makes src == dst safe)
+  auto ld = [](const void* base, size_t i, int es) -> uint64_t {
+    switch (es) {
+      case 8: return ((const uint64_t*)base)[i];
+      case 4: return ((const uint32_t*)base)[i];
+      case 2: return ((const uint16_t*)base)[i];
+      default: return ((const uint8_t*)base)[i];
+    }
+  };
+  auto st = [](void* base, size_t i, int es, uint64_t v) {
+    switch (es) {
+      case 8: ((uint64_t*)base)[i] = v; break;
+      case 4: ((uint32_t*)base)[i] = (uint32_t)v; break;
+      case 2: ((uint16_t*)base)[i] = (uint16_t)v; break;
+      default: ((uint8_t*)base)[i] = (uint8_t)v; break;
+    }
+  };
+  for (int c0 = 0; c0 < p.mv.n; c0 += 4) {
+    uint64_t v0[4], v1[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int c = c0 + u;
+      v0[u] = v1[u] = 0;
+      if (c < p.mv.n) {
+        if (i0 < len) v0[u] = ld(p.mv.src[c], (size_t)start + i0, p.mv.esize[c]);
+        if (i1 < len) v1[u] = ld(p.mv.src[c], (size_t)start + i1, p.mv.esize[c]);
+      }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int c = c0 + u;
+      if (c < p.mv.n) {
+        if (i0 < len) st(p.mv.dst[c], (size_t)start + r0, p.mv.esize[c], v0[u]);
+        if (i1 < len) st(p.mv.dst[c], (size_t)start + r1, p.mv.esize[c], v1[u]);
+      }
+    }
     __syncwarp();
   }
 }
@@ -1022,6 +1050,15 @@ static void run_wide_leaves(hs_ctx* c, LeafLaunch& ll, uint32_t n_wide) {
   LAUNCH(c, k_leaf_sort, ll.max_leaf, PT_THREADS, leaf_smem_bytes(), ll.lp);
 }
 
+// The 64-bit kernel runs only for segments the packed kernel flagged. With few leaves it is cheaper to launch it
+// blind (unflagged CTAs exit at once) than to ask the device how many were flagged.
+static void launch_wide(hs_ctx* c, LeafLaunch& ll, uint32_t* d_counters) {
+  if (!ll.max_leaf) return;
+  uint32_t nw = 1;
+  if (ll.max_leaf > 8192) nw = *(const uint32_t*)hs_read_wait(c, hs_read_begin(c, d_counters + 4, 4));
+  run_wide_leaves(c, ll, nw);
+}
+
 // h_seg_off (optional): the segment boundaries on the host. With them level 0 is classified on the host
 // and the sort starts without a device round trip.
 static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_seg_off,
@@ -1075,12 +1112,7 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     CK(cudaMemcpyAsync(counters.p, h, 32, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemcpyAsync(tile_prefix.p, tp.data(), tp.size() * 4, cudaMemcpyHostToDevice, c->stream));
     run_leaf_and_copy(c, ms, key, src, leaf, h[0], copy, h[2], counters.as<uint32_t>(), ll0, &small, h[5]);
-    if (h[0]) {
-      uint32_t nw = 0;
-      CK(cudaMemcpyAsync(&nw, counters.as<uint32_t>() + 4, 4, cudaMemcpyDeviceToHost, c->stream));
-      hs_sync(c);
-      run_wide_leaves(c, ll0, nw);
-    }
+    launch_wide(c, ll0, counters.as<uint32_t>());
   } else {
     leaf.alloc(c, cap_leaf, true);
     large.alloc(c, cap_large, true);
@@ -1092,15 +1124,12 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     LAUNCH(c, k_classify, (unsigned)((nseg + 255) / 256), 256, 0, d_seg_off, d_start, d_len, nseg, (uint32_t)key_bits, po);
     LAUNCH(c, k_tile_prefix, 1, 1024, 0, large.view(), counters.as<uint32_t>(), tile_prefix.as<uint32_t>());
     hs_stage_end(c);
-    // leaves first (the grid is an upper bound), then wait for the counts: the wait overlaps the leaf sort
-    // sizes are not known on the host yet: the leaf grid is bounded by the rows (a leaf has > SMALL_MAX rows)
+    // the list lengths come back first: grids sized by upper bounds (rows / 64 CTAs) cost more in empty CTAs
+    // than the round trip does
     if (ext) HS_THROW(HS_EINVAL, "external start buffers need host-known segments");
-    uint32_t max_leaf0 = (uint32_t)std::min<int64_t>(nseg, n / SMALL_MAX + 1);
-    run_leaf_and_copy(c, ms, key, BUF_A, leaf, max_leaf0, copy, 0, counters.as<uint32_t>(), ll0, &small,
-                      (uint32_t)std::min<int64_t>(nseg, 0x7fffffff));
-    CK(cudaMemcpyAsync(h, counters.p, 32, cudaMemcpyDeviceToHost, c->stream));
-    hs_sync(c);
-    run_wide_leaves(c, ll0, h[4]);
+    memcpy(h, hs_read_wait(c, hs_read_begin(c, counters.p, 32)), 32);
+    run_leaf_and_copy(c, ms, key, BUF_A, leaf, h[0], copy, 0, counters.as<uint32_t>(), ll0, &small, h[5]);
+    launch_wide(c, ll0, counters.as<uint32_t>());
   }
   uint32_t n_large = h[1], n_tiles = h[3];
   int level = 0;
@@ -1145,22 +1174,19 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     PlanOut npo{nleaf.view(), nlarge.view(), ncopy.view(), nsmall.view(), ncounters.as<uint32_t>()};
     hs_stage_begin(c, "msd_plan");
     LAUNCH(c, k_msd_plan, n_large, MSD_RADIX, 0, large.view(), cursor.as<uint32_t>(), npo);
+    DBuf ntile_prefix(c, (cap_large + 1) * 4);
+    LAUNCH(c, k_tile_prefix, 1, 1024, 0, nlarge.view(), ncounters.as<uint32_t>(), ntile_prefix.as<uint32_t>());
     hs_stage_end(c);
+    // the child counts travel to the host while the scatter runs: the leaf grids below are exact
+    const int slot = hs_read_begin(c, ncounters.p, 32);
     hs_stage_begin(c, "msd_scatter");
     LAUNCH(c, k_partition<1>, n_tiles, PT_THREADS, tile_smem_bytes(MSD_RADIX), p);
     hs_stage_end(c);
-    DBuf ntile_prefix(c, (cap_large + 1) * 4);
-    hs_stage_begin(c, "msd_plan");
-    LAUNCH(c, k_tile_prefix, 1, 1024, 0, nlarge.view(), ncounters.as<uint32_t>(), ntile_prefix.as<uint32_t>());
-    hs_stage_end(c);
     src = other_buf(src);
-    // children that fit a leaf are sorted now; the host learns the counts while they run
+    memcpy(h, hs_read_wait(c, slot), 32);
     LeafLaunch ll;
-    run_leaf_and_copy(c, ms, key, src, nleaf, (uint32_t)std::min<size_t>(children, n / SMALL_MAX + 1), ncopy,
-                      (uint32_t)cap_large, ncounters.as<uint32_t>(), ll, &nsmall, (uint32_t)children);
-    CK(cudaMemcpyAsync(h, ncounters.p, 32, cudaMemcpyDeviceToHost, c->stream));
-    hs_sync(c);
-    run_wide_leaves(c, ll, h[4]);
+    run_leaf_and_copy(c, ms, key, src, nleaf, h[0], ncopy, h[2], ncounters.as<uint32_t>(), ll, &nsmall, h[5]);
+    launch_wide(c, ll, ncounters.as<uint32_t>());
     large = std::move(nlarge);
     leaf = std::move(nleaf);
     copy = std::move(ncopy);

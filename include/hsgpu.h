@@ -56,7 +56,10 @@ typedef enum hs_type {
   HS_FLOAT32 = 6,
   HS_FLOAT64 = 7,
   HS_UTF8 = 8,    /* int32 offsets[length+1] + bytes */
-  HS_BINARY = 9   /* same layout as HS_UTF8 */
+  HS_BINARY = 9,  /* same layout as HS_UTF8 */
+  HS_LARGE_UTF8 = 10,   /* Arrow large_string: `offsets` points at int64 entries (cast the pointer); for columns
+                         * holding more than 2 GiB of bytes. Hashes and orders exactly like HS_UTF8. */
+  HS_LARGE_BINARY = 11  /* same layout as HS_LARGE_UTF8 */
 } hs_type;
 
 typedef enum hs_mem { HS_MEM_HOST = 0, HS_MEM_DEVICE = 1 } hs_mem;
@@ -68,7 +71,8 @@ typedef struct hs_column {
   int64_t length;          /* rows */
   int64_t null_count;      /* 0 when validity == NULL */
   const uint8_t* validity; /* LSB bitmap, bit i set = row i valid; or NULL */
-  const int32_t* offsets;  /* HS_UTF8/HS_BINARY only: length+1 entries */
+  const int32_t* offsets;  /* HS_UTF8/HS_BINARY: length+1 int32 entries; HS_LARGE_*: length+1 int64 entries
+                            * behind the same pointer */
   const void* data;        /* values (fixed width) or bytes (UTF8/BINARY) */
 } hs_column;
 

@@ -1,0 +1,112 @@
+#!/usr/bin/env python
+"""Side measurements for the BASELINE.json configs that are not the bench.py headline line:
+cfg4 (utf8 keys, 1000 buckets) and cfg5 (composite int32+int64 key, 8192 buckets, then a 10 % append =
+refresh-incremental and a join over two runs per bucket). Device-resident in -> device-resident out, CUDA events,
+per-stage times from the library's own stage timers. One JSON line per config on stdout.
+
+    python tools/bench_configs.py --config cfg4 --rows 80000000
+    python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 tools/bench_configs.py --config cfg5
+"""
+import argparse
+import json
+import os
+import sys
+import time
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+
+
+def gen_cfg4_device(torch, m, seed, dev):
+    """cfg4 rows on the device: length ~ 8 + Geometric(1/17) clipped to [1, 96], bytes from a 64-symbol alphabet,
+    10 % of the keys (those of >= 16 bytes) start with one of 1000 fixed 16-byte prefixes; v = row id."""
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed)
+    lens = torch.empty(m, device=dev, dtype=torch.float32).geometric_(1.0 / 17.0, generator=g).to(torch.int64) + 8
+    lens.clamp_(1, 96)
+    off = torch.zeros(m + 1, dtype=torch.int64, device=dev)
+    torch.cumsum(lens, 0, out=off[1:])
+    total = int(off[-1])
+    alphabet = torch.frombuffer(bytearray(b"abcdefghijklmnopqrstuvwxyzABCDEFGHIJKLMNOPQRSTUVWXYZ0123456789-_"),
+                                dtype=torch.uint8).to(dev)
+    data = torch.empty(total, dtype=torch.uint8, device=dev)
+    step = 1 << 28
+    for s in range(0, total, step):
+        e = min(total, s + step)
+        data[s:e] = alphabet[torch.randint(0, 64, (e - s,), generator=g, device=dev)]
+    pref = alphabet[torch.randint(0, 64, (1000, 16), generator=g, device=dev)]
+    sel = ((torch.rand(m, generator=g, device=dev) < 0.10) & (lens >= 16)).nonzero().flatten()
+    pi = torch.randint(0, 1000, (sel.numel(),), generator=g, device=dev)
+    pos = off[sel]
+    for j in range(16):
+        data[pos + j] = pref[pi, j]
+    rid = torch.arange(m, dtype=torch.int64, device=dev)
+    return off, data, rid, total
+
+
+def run_cfg4(args):
+    import torch
+    from hyperspace_1_b200 import abi, native
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    m, nb = args.rows or 80_000_000, 1000
+    off64, data, rid, total = gen_cfg4_device(torch, m, 20240603, dev)
+    wide = total >= (1 << 31) or args.large_offsets
+    off = off64 if wide else off64.to(torch.int32)
+    torch.cuda.synchronize()
+    ctx = native.Context(0)
+    ctx.set_output_location(abi.HS_MEM_DEVICE)
+    cs = abi.DeviceColumnSet([
+        {"type": getattr(abi, "HS_LARGE_UTF8", -1) if wide else abi.HS_UTF8, "length": m, "offsets": off.data_ptr(),
+         "data": data.data_ptr()},
+        {"type": abi.HS_INT64, "length": m, "data": rid.data_ptr()}])
+    stream = torch.cuda.ExternalStream(ctx.stream(), device=dev)
+    for _ in range(args.warmup):
+        ctx.build_index_table(cs, 1, nb).free()
+    ctx.enable_timing(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stage_ms = {}
+    e0.record(stream)
+    for _ in range(args.steps):
+        t = ctx.build_index_table(cs, 1, nb)
+        for name, ms, launches in ctx.last_timings():
+            a = stage_ms.setdefault(name, [0.0, 0])
+            a[0] += ms
+            a[1] += launches
+        t.free()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms_step = e0.elapsed_time(e1) / args.steps
+    row_bytes = total / m + (8 if wide else 4) + 8
+    key_bytes = total / m + (8 if wide else 4)
+    algo = key_bytes + 4 * row_bytes
+    line = {"config": "cfg4", "rows": m, "key_bytes_total": total, "num_buckets": nb, "offsets": "int64" if wide else "int32",
+            "ms_per_step": ms_step, "rows_per_s": m / (ms_step * 1e-3), "algorithmic_bytes_per_row": algo,
+            "achieved_gbs": algo * m / (ms_step * 1e-3) / 1e9,
+            "stages_ms": {k: round(v[0] / args.steps, 3) for k, v in stage_ms.items()},
+            "launches_per_step": sum(v[1] for v in stage_ms.values()) / args.steps}
+    print(json.dumps(line), flush=True)
+    ctx.close()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--config", choices=["cfg4", "cfg5"], required=True)
+    ap.add_argument("--rows", type=int, default=0, help="rows (per GPU for cfg5); default = the config's size that fits")
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=2)
+    ap.add_argument("--large-offsets", action="store_true", help="cfg4: int64 offsets even below 2 GiB of key bytes")
+    args = ap.parse_args()
+    if args.config == "cfg4":
+        run_cfg4(args)
+    else:
+        run_cfg5(args)
+
+
+def run_cfg5(args):
+    raise SystemExit("cfg5: see below")
+
+
+if __name__ == "__main__":
+    t0 = time.time()
+    main()
