@@ -411,8 +411,15 @@ struct NcclExchange : BuildExchange {
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
     CK(cudaEventCreate(&e1));
+    // The fused kernel stores every row straight at its place in the owner's memory: with few buckets a tile
+    // of 4096 rows holds runs of tens of rows per bucket and the stores leave as decent NVLink packets (measured
+    // faster than scatter + copy, 3.06 vs 3.6 ms at N=2, 200 buckets). With thousands of buckets every row is a
+    // packet of its own (measured 3.5 GB/s at 8192 buckets) — then the rows are scattered locally first and whole
+    // bucket runs are pushed. HSGPU_P2P_MODE=fused|copy overrides.
     const char* mode = getenv("HSGPU_P2P_MODE");
-    const bool one_kernel = !(mode && !strcmp(mode, "copy"));   // default: the fused kernel (measured faster)
+    bool one_kernel = nb <= 512;
+    if (mode && !strcmp(mode, "copy")) one_kernel = false;
+    if (mode && !strcmp(mode, "fused")) one_kernel = true;
     if (one_kernel) {
       // one kernel: the bucket scatter stores every row at its final place in the owner's memory
       Stage s(c, "scatter_to_owners");

@@ -430,6 +430,52 @@ void hs_offsets_to_device(hs_ctx* c, const int64_t* boff, int32_t nb, int64_t nr
   hs_sync(c);  // h goes out of scope
 }
 
+// per key column: min and max of the order-preserving image of the (NULL-free) cells
+__global__ void __launch_bounds__(256) k_keys_range(const __grid_constant__ KeySpec ks, int64_t n, uint64_t* __restrict__ mm) {
+  uint64_t mn[HS_MAX_KEYS], mx[HS_MAX_KEYS];
+#pragma unroll
+  for (int k = 0; k < HS_MAX_KEYS; k++) { mn[k] = ~0ull; mx[k] = 0; }
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+#pragma unroll
+    for (int k = 0; k < HS_MAX_KEYS; k++)
+      if (k < ks.nkeys) {
+        const uint64_t v = omap_cell(ks.k[k], i);
+        mn[k] = v < mn[k] ? v : mn[k];
+        mx[k] = v > mx[k] ? v : mx[k];
+      }
+  }
+#pragma unroll
+  for (int k = 0; k < HS_MAX_KEYS; k++)
+    if (k < ks.nkeys) {
+      for (int d = 16; d; d >>= 1) {
+        const uint64_t a = __shfl_xor_sync(0xffffffffu, mn[k], d), b = __shfl_xor_sync(0xffffffffu, mx[k], d);
+        mn[k] = a < mn[k] ? a : mn[k];
+        mx[k] = b > mx[k] ? b : mx[k];
+      }
+      if (lane_id() == 0 && mn[k] <= mx[k]) {
+        atomicMin((unsigned long long*)&mm[2 * k], (unsigned long long)mn[k]);
+        atomicMax((unsigned long long*)&mm[2 * k + 1], (unsigned long long)mx[k]);
+      }
+    }
+}
+struct KeyPack {
+  uint64_t min[HS_MAX_KEYS];
+  int32_t shift[HS_MAX_KEYS];
+};
+// key tuple -> one u64: sum of (cell - min) << shift, first column in the highest bits (lexicographic order kept)
+__global__ void __launch_bounds__(256) k_pack_keys(const __grid_constant__ KeySpec ks, int64_t n,
+                                                   const __grid_constant__ KeyPack kp, uint64_t* __restrict__ out) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    uint64_t v = 0;
+#pragma unroll
+    for (int k = 0; k < HS_MAX_KEYS; k++)
+      if (k < ks.nkeys) v |= (omap_cell(ks.k[k], i) - kp.min[k]) << kp.shift[k];
+    out[i] = v;
+  }
+}
+
 extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, const hs_index_view* right,
                                     int32_t join_type, const int32_t* left_out, int32_t n_left_out,
                                     const int32_t* right_out, int32_t n_right_out, hs_table** out) {
@@ -464,9 +510,12 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
   JoinSide L{hs_make_keyspec(lc, nk), loff.as<uint32_t>()};
   JoinSide R{hs_make_keyspec(rc, nk), roff.as<uint32_t>()};
 
-  // ---- fast path: one integer key, no NULL keys, fixed-width NULL-free outputs
-  bool fast_join = nk == 1 && (lc[0].type == HS_INT64 || lc[0].type == HS_INT32) && !lc[0].validity && !rc[0].validity &&
-                   n_left_out <= 16 && n_right_out <= 16 && nl > 0 && nr > 0;
+  // ---- fast path: the key is one integer column, or any NULL-free fixed-width key tuple whose value ranges
+  // fit 64 bits together (packed below); fixed-width NULL-free outputs
+  const bool int_key = nk == 1 && (lc[0].type == HS_INT64 || lc[0].type == HS_INT32);
+  bool fast_join = n_left_out <= 16 && n_right_out <= 16 && nl > 0 && nr > 0;
+  for (int k = 0; k < nk && fast_join; k++)
+    if (hs_is_varlen(lc[k].type) || lc[k].validity || rc[k].validity) fast_join = false;
   for (int i = 0; i < n_left_out && fast_join; i++) {
     int w = hs_fixed_width(lc[left_out[i]].type);
     if ((w != 4 && w != 8) || lc[left_out[i]].validity) fast_join = false;
@@ -474,6 +523,41 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
   for (int i = 0; i < n_right_out && fast_join; i++) {
     int w = hs_fixed_width(rc[right_out[i]].type);
     if ((w != 4 && w != 8) || rc[right_out[i]].validity) fast_join = false;
+  }
+  // composite (or non-integer) keys: both sides are rewritten as one order-preserving u64 per row, so that the
+  // tile merge below compares plain integers (cfg5's (int32, int64) key: 12 bytes -> 8)
+  bool packed = false;
+  DBuf lpk, rpk;
+  if (fast_join && !int_key) {
+    Stage s(ctx, "join_pack_keys");
+    DBuf mm(ctx, 2 * HS_MAX_KEYS * 8);
+    uint64_t init[2 * HS_MAX_KEYS], h_mm[2 * HS_MAX_KEYS];
+    for (int k = 0; k < HS_MAX_KEYS; k++) { init[2 * k] = ~0ull; init[2 * k + 1] = 0; }
+    CK(cudaMemcpyAsync(mm.p, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+    LAUNCH(ctx, k_keys_range, HS_NUM_SMS * 8, 256, 0, L.ks, nl, mm.as<uint64_t>());
+    LAUNCH(ctx, k_keys_range, HS_NUM_SMS * 8, 256, 0, R.ks, nr, mm.as<uint64_t>());
+    CK(cudaMemcpyAsync(h_mm, mm.p, sizeof h_mm, cudaMemcpyDeviceToHost, ctx->stream));
+    hs_sync(ctx);
+    KeyPack kp;
+    memset(&kp, 0, sizeof kp);
+    int total_bits = 0;
+    for (int k = nk - 1; k >= 0; k--) {
+      uint64_t range = h_mm[2 * k + 1] - h_mm[2 * k];
+      int bits = 0;
+      while (bits < 64 && (range >> bits)) bits++;
+      kp.min[k] = h_mm[2 * k];
+      kp.shift[k] = total_bits;
+      total_bits += bits;
+    }
+    if (total_bits <= 64) {
+      lpk.alloc(ctx, (size_t)nl * 8);
+      rpk.alloc(ctx, (size_t)nr * 8);
+      LAUNCH(ctx, k_pack_keys, HS_NUM_SMS * 16, 256, 0, L.ks, nl, kp, lpk.as<uint64_t>());
+      LAUNCH(ctx, k_pack_keys, HS_NUM_SMS * 16, 256, 0, R.ks, nr, kp, rpk.as<uint64_t>());
+      packed = true;
+    } else {
+      fast_join = false;
+    }
   }
   if (fast_join) {
     std::vector<uint32_t> tb, ts, tl, first_tile((size_t)nb + 1);
@@ -494,14 +578,28 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
     CK(cudaMemcpyAsync(d_tl.p, tl.data(), (size_t)ntiles * 4, cudaMemcpyHostToDevice, ctx->stream));
     JoinFast jf;
     memset(&jf, 0, sizeof jf);
-    jf.lkey = lc[0].data; jf.rkey = rc[0].data;
+    jf.lkey = packed ? lpk.p : lc[0].data;
+    jf.rkey = packed ? rpk.p : rc[0].data;
     jf.roff = roff.as<uint32_t>();
     jf.tile_bucket = d_tb.as<uint32_t>(); jf.tile_start = d_ts.as<uint32_t>(); jf.tile_len = d_tl.as<uint32_t>();
     jf.ntiles = ntiles;
     jf.tile_cnt = d_cnt.as<uint32_t>();
     jf.tile_win = d_win.as<uint32_t>();
-    const bool k64 = lc[0].type == HS_INT64;
-    const size_t smem = k64 ? join_smem_bytes<int64_t>() : join_smem_bytes<int32_t>();
+    // key kind: 0 = int32 column, 1 = int64 column, 2 = packed u64 (built above)
+    const int kkind = packed ? 2 : (lc[0].type == HS_INT64 ? 1 : 0);
+    const size_t smem = kkind ? join_smem_bytes<int64_t>() : join_smem_bytes<int32_t>();
+    auto launch_windows = [&]() {
+      if (kkind == 2) LAUNCH(ctx, k_join_windows<uint64_t>, (ntiles + 7) / 8, 256, 0, jf);
+      else if (kkind == 1) LAUNCH(ctx, k_join_windows<int64_t>, (ntiles + 7) / 8, 256, 0, jf);
+      else LAUNCH(ctx, k_join_windows<int32_t>, (ntiles + 7) / 8, 256, 0, jf);
+    };
+    auto launch_tiles = [&](int mode) {
+#define HS_JT(K, M) LAUNCH(ctx, (k_join_tiles<K, M>), ntiles, JTHREADS, smem, jf)
+      if (kkind == 2) { if (mode == 0) HS_JT(uint64_t, 0); else if (mode == 1) HS_JT(uint64_t, 1); else HS_JT(uint64_t, 2); }
+      else if (kkind == 1) { if (mode == 0) HS_JT(int64_t, 0); else if (mode == 1) HS_JT(int64_t, 1); else HS_JT(int64_t, 2); }
+      else { if (mode == 0) HS_JT(int32_t, 0); else if (mode == 1) HS_JT(int32_t, 1); else HS_JT(int32_t, 2); }
+#undef HS_JT
+    };
     static bool attr_done[64] = {false};
     int dev = 0;
     CK(cudaGetDevice(&dev));
@@ -512,6 +610,9 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
       CK(cudaFuncSetAttribute(k_join_tiles<int32_t, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int32_t>()));
       CK(cudaFuncSetAttribute(k_join_tiles<int64_t, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int64_t>()));
       CK(cudaFuncSetAttribute(k_join_tiles<int32_t, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int32_t>()));
+      CK(cudaFuncSetAttribute(k_join_tiles<uint64_t, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int64_t>()));
+      CK(cudaFuncSetAttribute(k_join_tiles<uint64_t, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int64_t>()));
+      CK(cudaFuncSetAttribute(k_join_tiles<uint64_t, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int64_t>()));
       attr_done[dev & 63] = true;
     }
     uint64_t h_tot = 0;
@@ -549,10 +650,8 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
       unsigned long long h_last = 0;
       {
         Stage s(ctx, "join_fused");
-        if (k64) LAUNCH(ctx, k_join_windows<int64_t>, (ntiles + 7) / 8, 256, 0, jf);
-        else LAUNCH(ctx, k_join_windows<int32_t>, (ntiles + 7) / 8, 256, 0, jf);
-        if (k64) LAUNCH(ctx, (k_join_tiles<int64_t, 2>), ntiles, JTHREADS, smem, jf);
-        else LAUNCH(ctx, (k_join_tiles<int32_t, 2>), ntiles, JTHREADS, smem, jf);
+        launch_windows();
+        launch_tiles(2);
         CK(cudaMemcpyAsync(h_misc, d_misc.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
         CK(cudaMemcpyAsync(&h_last, d_state.as<unsigned long long>() + (ntiles - 1), 8, cudaMemcpyDeviceToHost, ctx->stream));
         CK(cudaMemcpyAsync(h_off.data(), d_cnt.p, (size_t)ntiles * 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -574,10 +673,8 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
     }
     {
       Stage s(ctx, "join_count");
-      if (k64) LAUNCH(ctx, k_join_windows<int64_t>, (ntiles + 7) / 8, 256, 0, jf);
-      else LAUNCH(ctx, k_join_windows<int32_t>, (ntiles + 7) / 8, 256, 0, jf);
-      if (k64) LAUNCH(ctx, (k_join_tiles<int64_t, 0>), ntiles, JTHREADS, smem, jf);
-      else LAUNCH(ctx, (k_join_tiles<int32_t, 0>), ntiles, JTHREADS, smem, jf);
+      launch_windows();
+      launch_tiles(0);
       hs_exclusive_scan_u32(ctx, d_cnt.as<uint32_t>(), d_cnt.as<uint32_t>(), ntiles, d_total.as<uint64_t>());
       CK(cudaMemcpyAsync(&h_tot, d_total.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
       CK(cudaMemcpyAsync(h_off.data(), d_cnt.p, (size_t)ntiles * 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -605,8 +702,7 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
     jf.n_lout = n_left_out; jf.n_rout = n_right_out;
     {
       Stage s(ctx, "join_write");
-      if (k64) LAUNCH(ctx, (k_join_tiles<int64_t, 1>), ntiles, JTHREADS, smem, jf);
-      else LAUNCH(ctx, (k_join_tiles<int32_t, 1>), ntiles, JTHREADS, smem, jf);
+      launch_tiles(1);
     }
     std::vector<int64_t> ooff((size_t)nb + 1, 0);
     for (int b = 0; b <= nb; b++) ooff[b] = first_tile[b] < ntiles ? (int64_t)h_off[first_tile[b]] : m;

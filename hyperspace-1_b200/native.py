@@ -72,6 +72,14 @@ class Table:
             raise HyperspaceException("to_arrow needs a host-resident table")
         return [abi.host_column_to_arrow(t.cols[i], types[i] if types else None) for i in range(t.ncols)]
 
+    def view(self, n_indexed):
+        """IndexView over this table's own buffers (borrowed: keep the table alive while the view is used)."""
+        t = self.t
+        spec = [{"type": t.cols[i].type, "length": t.cols[i].length, "null_count": t.cols[i].null_count,
+                 "validity": t.cols[i].validity, "offsets": t.cols[i].offsets, "data": t.cols[i].data}
+                for i in range(t.ncols)]
+        return IndexView(abi.DeviceColumnSet(spec), n_indexed, self.bucket_offsets())
+
     def free(self):
         if self.ptr is not None:
             self.ctx._lib.hs_table_free(self.ctx._h, self.ptr)
@@ -224,6 +232,13 @@ class Context:
             return t.to_arrow(types), t.bucket_offsets()
         finally:
             t.free()
+
+    def merge_tables(self, views):
+        """hs_merge_runs over IndexViews (host or device buffers) -> Table."""
+        arr = (abi.hs_index_view * len(views))(*[v.c for v in views])
+        out = C.POINTER(abi.hs_table)()
+        self._check(self._lib.hs_merge_runs(self._h, arr, C.c_int32(len(views)), C.byref(out)), "hs_merge_runs")
+        return Table(self, out)
 
     # ---- join / filter
     def join_table(self, left, right, left_out, right_out):

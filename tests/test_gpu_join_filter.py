@@ -105,6 +105,47 @@ def test_join_on_string_and_composite_keys(ctx, oracle):
     parity.assert_same_multiset(jg, want, joff, woff, "composite join")
 
 
+def test_join_packed_key_tuples(ctx, oracle):
+    """NULL-free fixed-width key tuples are packed into one u64 per row and take the tile-merge path: small
+    integer types, floats (NaN, -0.0), booleans, three-column keys; many-to-many matches included."""
+    rng = np.random.default_rng(9)
+
+    def side(n, kinds):
+        cols = []
+        for kind in kinds:
+            if kind == "i8":
+                cols.append(pa.array(rng.integers(-5, 6, size=n).astype(np.int8)))
+            elif kind == "i16":
+                cols.append(pa.array(rng.integers(-300, 300, size=n).astype(np.int16)))
+            elif kind == "i32":
+                cols.append(pa.array(rng.integers(-2**31, 2**31 - 1, size=n).astype(np.int32) // (1 << 22)))
+            elif kind == "i64":
+                cols.append(pa.array(rng.integers(-40, 40, size=n) * (1 << 40)))
+            elif kind == "f32":
+                v = rng.integers(-4, 5, size=n).astype(np.float32) / 2
+                v[rng.random(n) < 0.05] = np.nan
+                v[rng.random(n) < 0.05] = -0.0
+                cols.append(pa.array(v))
+            elif kind == "f64":
+                v = rng.integers(-4, 5, size=n).astype(np.float64) / 4
+                v[rng.random(n) < 0.05] = np.nan
+                v[rng.random(n) < 0.05] = -0.0
+                cols.append(pa.array(v))
+            elif kind == "bool":
+                cols.append(pa.array(rng.random(n) < 0.5))
+        return cols + [pa.array(np.arange(n)), pa.array(rng.random(n).astype(np.float32))]
+
+    for kinds in (["i16"], ["f64"], ["f32", "i8"], ["bool", "i32", "i16"], ["i64", "f64"], ["i8", "i8", "i8"]):
+        nk = len(kinds)
+        l, r = side(6000, kinds), side(900, kinds)
+        lg, loff = ctx.build_index(l, nk, 16)
+        rg, roff = ctx.build_index(r, nk, 16)
+        lout, rout = list(range(nk + 2)), [nk, nk + 1]
+        jg, joff = ctx.join(lg, loff, rg, roff, nk, lout, rout)
+        want, woff = _oracle_join(oracle, lg, loff, rg, roff, nk, lout, rout)
+        parity.assert_same_multiset(jg, want, joff, woff, f"packed-key join {kinds}")
+
+
 def test_join_after_incremental_refresh_two_runs_per_bucket(ctx, oracle):
     lcols, keys = lineitem(20000)
     n = len(lcols[0])

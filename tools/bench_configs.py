@@ -104,7 +104,120 @@ def main():
 
 
 def run_cfg5(args):
-    raise SystemExit("cfg5: see below")
+    """cfg5: (k1:int32 < 2^20, k2:int64 < 2^40, v:float64), 8192 buckets, rows generated on the device per rank;
+    distributed build of the base, distributed build of a 10 % append (refresh-incremental builds the delta only),
+    then on every rank, over its own buckets and without communication: merge of the two runs per bucket and a
+    join of the merged index with the delta index on (k1, k2)."""
+    import torch
+    import torch.distributed as dist
+    from hyperspace_1_b200 import abi, native
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29517")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    ctx = native.Context(local)
+    if world > 1:
+        uid = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            uid = torch.frombuffer(bytearray(ctx.comm_unique_id()), dtype=torch.uint8).to(dev)
+        dist.broadcast(uid, 0)
+        ctx.comm_init(rank, world, bytes(uid.cpu().numpy().tobytes()))
+    n, nb = args.rows or 500_000_000, 8192
+    nd = n // 10
+
+    def gen(m, seed):
+        g = torch.Generator(device=dev)
+        g.manual_seed(seed)
+        k1 = torch.randint(0, 1 << 20, (m,), generator=g, device=dev, dtype=torch.int32)
+        k2 = torch.randint(0, 1 << 40, (m,), generator=g, device=dev, dtype=torch.int64)
+        v = torch.rand(m, generator=g, device=dev, dtype=torch.float64)
+        return k1, k2, v
+
+    def cols(t):
+        return abi.DeviceColumnSet([{"type": abi.HS_INT32, "length": t[0].numel(), "data": t[0].data_ptr()},
+                                    {"type": abi.HS_INT64, "length": t[1].numel(), "data": t[1].data_ptr()},
+                                    {"type": abi.HS_FLOAT64, "length": t[2].numel(), "data": t[2].data_ptr()}])
+
+    base, delta = gen(n, 20240604 + rank), gen(nd, 20240605 + rank)
+    torch.cuda.synchronize()
+    ctx.set_output_location(abi.HS_MEM_DEVICE)
+    stream = torch.cuda.ExternalStream(ctx.stream(), device=dev)
+    use_dist = world > 1
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def timed(fn, steps, warmup, keep_last=False):
+        out = None
+        for _ in range(warmup):
+            fn().free()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for i in range(steps):
+            t = fn()
+            if keep_last and i == steps - 1:
+                out = t
+            else:
+                t.free()
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1) / steps
+        if world > 1:
+            tt = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ms = float(tt.item())
+        return ms, out
+
+    def total(x):
+        if world == 1:
+            return int(x)
+        tt = torch.tensor([x], dtype=torch.int64, device=dev)
+        dist.all_reduce(tt)
+        return int(tt.item())
+
+    cb, cd = cols(base), cols(delta)
+    ms_base, tb = timed(lambda: ctx.build_index_table(cb, 2, nb, dist=use_dist), args.steps, args.warmup, True)
+    xb = ctx.comm_last_exchange() if use_dist else None
+    ctx.enable_timing(True)
+    ctx.build_index_table(cb, 2, nb, dist=use_dist).free()
+    stages = {name: round(ms, 3) for name, ms, _ in ctx.last_timings()}
+    ctx.enable_timing(False)
+    ms_delta, td = timed(lambda: ctx.build_index_table(cd, 2, nb, dist=use_dist), args.steps, args.warmup, True)
+    rows_owned = total(tb.nrows)
+    vb, vd = tb.view(2), td.view(2)
+    ms_merge, tm = timed(lambda: ctx.merge_tables([vb, vd]), args.steps, 1, True)
+    vm = tm.view(2)
+    ms_join, tj = timed(lambda: ctx.join_table(vm, vd, [0, 1, 2], [2]), args.steps, 1, True)
+    out_rows = total(tj.nrows)
+    merged_rows = total(tm.nrows)
+    # sanity: every delta row finds itself in the merged index
+    ok = out_rows >= nd * world and merged_rows == (n + nd) * world and rows_owned == n * world
+    for t in (tj, tm, td, tb):
+        t.free()
+    if rank == 0:
+        row_bytes, key_bytes = 20, 12
+        line = {"config": "cfg5", "n_gpus": world, "rows_per_gpu": n, "delta_rows_per_gpu": nd, "num_buckets": nb,
+                "build_ms": ms_base, "build_rows_per_s": n * world / (ms_base * 1e-3),
+                "build_algorithmic_bytes_per_row": key_bytes + 4 * row_bytes,
+                "build_achieved_gbs_per_gpu": (key_bytes + 4 * row_bytes) * n / (ms_base * 1e-3) / 1e9,
+                "refresh_incremental_ms": ms_delta, "refresh_rows_per_s": nd * world / (ms_delta * 1e-3),
+                "merge_two_runs_ms": ms_merge, "merge_rows_per_s": (n + nd) * world / (ms_merge * 1e-3),
+                "join_merged_x_delta_ms": ms_join, "join_output_rows": out_rows,
+                "join_output_rows_per_s": out_rows / (ms_join * 1e-3), "checks_ok": bool(ok)}
+        line["build_stages_ms_rank0"] = stages
+        if xb:
+            line["exchange_bytes_ms_rank0"] = xb
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
