@@ -132,32 +132,44 @@ static void p2p_destroy(hs_ctx* c) {
 
 // copies runs of rows into the owners' buffers: run j = (src row, dst row, rows, owner); dst[owner] are
 // peer-mapped pointers, so the stores of a warp leave as full 128-byte lines over NVLink
-struct PeerPtrs { unsigned char* p[HS_MAX_PEERS_HOST]; };
-__global__ void __launch_bounds__(256) k_copy_runs_peers(const unsigned char* __restrict__ src, PeerPtrs dst,
-                                                         const uint32_t* __restrict__ runs, int esize) {
-  const uint32_t s0 = runs[4 * blockIdx.x], d0 = runs[4 * blockIdx.x + 1], m = runs[4 * blockIdx.x + 2];
-  const uint32_t owner = runs[4 * blockIdx.x + 3];
-  const unsigned char* sp = src + (size_t)s0 * esize;
-  unsigned char* dp = dst.p[owner] + (size_t)d0 * esize;
-  size_t bytes = (size_t)m * esize;
-  if ((((uintptr_t)sp | (uintptr_t)dp) & 15) == 0) {
-    size_t nv = bytes >> 4;
-    const uint4* s4 = (const uint4*)sp;
-    uint4* d4 = (uint4*)dp;
-    for (size_t i = threadIdx.x; i < nv; i += blockDim.x) d4[i] = s4[i];
-    for (size_t i = (nv << 4) + threadIdx.x; i < bytes; i += blockDim.x) dp[i] = sp[i];
-  } else if ((((uintptr_t)sp | (uintptr_t)dp) & 7) == 0 && (bytes & 7) == 0) {
-    size_t nv = bytes >> 3;
-    const uint64_t* s8 = (const uint64_t*)sp;
-    uint64_t* d8 = (uint64_t*)dp;
-    for (size_t i = threadIdx.x; i < nv; i += blockDim.x) d8[i] = s8[i];
-  } else if ((((uintptr_t)sp | (uintptr_t)dp) & 3) == 0 && (bytes & 3) == 0) {
-    size_t nv = bytes >> 2;
-    const uint32_t* s4 = (const uint32_t*)sp;
-    uint32_t* d4 = (uint32_t*)dp;
-    for (size_t i = threadIdx.x; i < nv; i += blockDim.x) d4[i] = s4[i];
-  } else {
-    for (size_t i = threadIdx.x; i < bytes; i += blockDim.x) dp[i] = sp[i];
+struct PeerCols {
+  int32_t ncol;
+  int32_t esize[HS_MAX_PEER_COLS_HOST];
+  const unsigned char* src[HS_MAX_PEER_COLS_HOST];
+  unsigned char* dst[HS_MAX_PEERS_HOST][HS_MAX_PEER_COLS_HOST];
+};
+template <typename V>
+__device__ __forceinline__ void copy_vec4(const V* __restrict__ s, V* __restrict__ d, size_t nv) {
+  size_t i = threadIdx.x;
+  for (; i + 3 * 256 < nv; i += 4 * 256) {   // four loads in flight per thread before the first remote store
+    const V a = s[i], b = s[i + 256], c = s[i + 512], e = s[i + 768];
+    d[i] = a; d[i + 256] = b; d[i + 512] = c; d[i + 768] = e;
+  }
+  for (; i < nv; i += 256) d[i] = s[i];
+}
+// One CTA takes one run chunk and pushes it column after column (all columns in one launch: no tail per column).
+__global__ void __launch_bounds__(256) k_copy_runs_peers(const __grid_constant__ PeerCols pc,
+                                                         const uint32_t* __restrict__ runs, uint32_t nruns) {
+  for (uint32_t j = blockIdx.x; j < nruns; j += gridDim.x) {
+    const uint32_t s0 = runs[4 * j], d0 = runs[4 * j + 1], m = runs[4 * j + 2], owner = runs[4 * j + 3];
+    for (int col = 0; col < pc.ncol; col++) {
+      const int esize = pc.esize[col];
+      const unsigned char* sp = pc.src[col] + (size_t)s0 * esize;
+      unsigned char* dp = pc.dst[owner][col] + (size_t)d0 * esize;
+      const size_t bytes = (size_t)m * esize;
+      const uintptr_t al = (uintptr_t)sp | (uintptr_t)dp;
+      if ((al & 15) == 0) {
+        const size_t nv = bytes >> 4;
+        copy_vec4<uint4>((const uint4*)sp, (uint4*)dp, nv);
+        for (size_t i = (nv << 4) + threadIdx.x; i < bytes; i += blockDim.x) dp[i] = sp[i];
+      } else if ((al & 7) == 0 && (bytes & 7) == 0) {
+        copy_vec4<uint64_t>((const uint64_t*)sp, (uint64_t*)dp, bytes >> 3);
+      } else if ((al & 3) == 0 && (bytes & 3) == 0) {
+        copy_vec4<uint32_t>((const uint32_t*)sp, (uint32_t*)dp, bytes >> 2);
+      } else {
+        copy_vec4<unsigned char>(sp, dp, bytes);
+      }
+    }
   }
 }
 
@@ -450,13 +462,20 @@ struct NcclExchange : BuildExchange {
         CK(cudaMemcpyAsync(d_loff.p, local_off.data(), ((size_t)nb + 1) * 4, cudaMemcpyHostToDevice, c->stream));
         hs_bucket_scatter(c, srcs, ms, d_bucket, n_local, nb, d_loff.as<uint32_t>());
       }
+      // every sender starts with a different owner (me+1, me+2, ..., me last): if all ranks walked the buckets in
+      // the same order they would all push into the same GPU at the same time (measured: 32 ms of the 8-GPU
+      // cfg5 build waiting at the barrier for the ranks served last)
       std::vector<uint32_t> runs;
-      for (int b = 0; b < nb; b++) {
+      std::vector<int> order;
+      for (int k = 1; k <= N; k++)
+        for (int b = 0; b < nb; b++)
+          if (owner_of(b, N, nb) == (me + k) % N) order.push_back(b);
+      for (int b : order) {
         uint32_t cnt = all_hist[(size_t)me * nb + b];
-        for (uint32_t done = 0; done < cnt; done += 32768) {
+        for (uint32_t done = 0; done < cnt; done += 16384) {
           runs.push_back(local_off[b] + done);
           runs.push_back(run_base[b] + done);
-          runs.push_back(cnt - done < 32768 ? cnt - done : 32768);
+          runs.push_back(cnt - done < 16384 ? cnt - done : 16384);
           runs.push_back((uint32_t)owner_of(b, N, nb));
         }
       }
@@ -464,11 +483,17 @@ struct NcclExchange : BuildExchange {
       DBuf d_runs(c, runs.size() * 4 + 16);
       if (!runs.empty()) CK(cudaMemcpyAsync(d_runs.p, runs.data(), runs.size() * 4, cudaMemcpyHostToDevice, c->stream));
       CK(cudaEventRecord(e0, c->stream));
-      for (int i = 0; i < ncol && !runs.empty(); i++) {
-        PeerPtrs pp;
-        for (int r = 0; r < N; r++) pp.p[r] = (unsigned char*)st->peer_ptr[(size_t)r * ncol + i];
-        LAUNCH(c, k_copy_runs_peers, (unsigned)(runs.size() / 4), 256, 0, (const unsigned char*)tmp[i].p, pp,
-               d_runs.as<uint32_t>(), esize[i]);
+      if (!runs.empty()) {
+        PeerCols pc;
+        memset(&pc, 0, sizeof pc);
+        pc.ncol = ncol;
+        for (int i = 0; i < ncol; i++) {
+          pc.esize[i] = esize[i];
+          pc.src[i] = (const unsigned char*)tmp[i].p;
+          for (int r = 0; r < N; r++) pc.dst[r][i] = (unsigned char*)st->peer_ptr[(size_t)r * ncol + i];
+        }
+        const uint32_t nruns = (uint32_t)(runs.size() / 4);
+        LAUNCH(c, k_copy_runs_peers, std::min<uint32_t>(nruns, HS_NUM_SMS * 8), 256, 0, pc, d_runs.as<uint32_t>(), nruns);
       }
       CK(cudaEventRecord(e1, c->stream));
       hs_sync(c);   // my stores have left this GPU

@@ -98,7 +98,7 @@ def test_cfg2_build_and_cfg3_join_properties(hs):
 
 
 def test_cfg5_shape_composite_key_properties(hs):
-    """cfg5 per-GPU shape at 50 M rows: (k1:int32 < 2^20, k2:int64 < 2^40, v:float64), 1024 buckets —
+    """cfg5 per-GPU shape at 50 M rows: (k1:int32 < 2^20, k2:int64 < 2^40, v:float64), 8192 buckets —
     lexicographic order inside every bucket, bucket membership, checksums."""
     import torch
     from hyperspace_1_b200 import abi
@@ -115,7 +115,7 @@ def test_cfg5_shape_composite_key_properties(hs):
     cs = abi.DeviceColumnSet([{"type": abi.HS_INT32, "length": n, "data": k1.data_ptr()},
                               {"type": abi.HS_INT64, "length": n, "data": k2.data_ptr()},
                               {"type": abi.HS_FLOAT64, "length": n, "data": v.data_ptr()}])
-    nb = 1024
+    nb = 8192   # cfg5's bucket count: more than 2048 buckets take the two-level bucket scatter
     t = ctx.build_index_table(cs, 2, nb)
     boff = t.bucket_offsets()
     assert t.nrows == n and boff[-1] == n

@@ -186,8 +186,9 @@ def run_cfg5(args):
     ms_base, tb = timed(lambda: ctx.build_index_table(cb, 2, nb, dist=use_dist), args.steps, args.warmup, True)
     xb = ctx.comm_last_exchange() if use_dist else None
     ctx.enable_timing(True)
-    ctx.build_index_table(cb, 2, nb, dist=use_dist).free()
-    stages = {name: round(ms, 3) for name, ms, _ in ctx.last_timings()}
+    for _ in range(2):   # the second call's numbers are reported (the first may still grow the block cache)
+        ctx.build_index_table(cb, 2, nb, dist=use_dist).free()
+        stages = {name: round(ms, 3) for name, ms, _ in ctx.last_timings()}
     ctx.enable_timing(False)
     ms_delta, td = timed(lambda: ctx.build_index_table(cd, 2, nb, dist=use_dist), args.steps, args.warmup, True)
     rows_owned = total(tb.nrows)
