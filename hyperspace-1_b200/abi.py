@@ -16,7 +16,9 @@ HS_MEM_HOST, HS_MEM_DEVICE = 0, 1
 (HS_PRED_EQ, HS_PRED_NE, HS_PRED_LT, HS_PRED_LE, HS_PRED_GT, HS_PRED_GE,
  HS_PRED_IS_NULL, HS_PRED_IS_NOT_NULL) = range(1, 9)
 HS_PRED_AND, HS_PRED_OR, HS_PRED_NOT = 16, 17, 18
-HS_JOIN_INNER = 0
+HS_JOIN_INNER, HS_JOIN_LEFT_OUTER, HS_JOIN_RIGHT_OUTER, HS_JOIN_FULL_OUTER, HS_JOIN_LEFT_SEMI, HS_JOIN_LEFT_ANTI = range(6)
+JOIN_TYPES = {"inner": 0, "left_outer": 1, "left": 1, "right_outer": 2, "right": 2, "full_outer": 3, "outer": 3,
+              "full": 3, "left_semi": 4, "semi": 4, "left_anti": 5, "anti": 5}   # Spark's joinType spellings
 
 STATUS_NAMES = {0: "HS_OK", 1: "HS_EINVAL", 2: "HS_ENOMEM", 3: "HS_ECUDA", 4: "HS_ENCCL",
                 5: "HS_EUNSUPPORTED"}

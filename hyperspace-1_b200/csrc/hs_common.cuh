@@ -238,5 +238,7 @@ void hs_exclusive_scan_u32(hs_ctx* c, const uint32_t* in, uint32_t* out, int64_t
 void hs_exclusive_scan_flags(hs_ctx* c, const uint8_t* flags, uint32_t* out, int64_t n, uint64_t* d_total);
 int64_t hs_offsets_from_lens(hs_ctx* c, const uint32_t* lens, int64_t m, int32_t type, OutCol& out);
 // gather rows idx[0..m) of `src` into a new column
-void hs_gather_column(hs_ctx* c, const DevCol& src, const uint32_t* idx, int64_t m, OutCol& out);
+// may_miss: idx may hold HS_MISS for "no source row" (outer joins): those rows come out NULL
+#define HS_MISS 0xFFFFFFFFu
+void hs_gather_column(hs_ctx* c, const DevCol& src, const uint32_t* idx, int64_t m, OutCol& out, bool may_miss = false);
 void hs_copy_column(hs_ctx* c, const DevCol& src, OutCol& out);

@@ -7,7 +7,10 @@ __global__ void __launch_bounds__(256) k_gather_fixed(const T* __restrict__ in, 
                                                       int64_t m, T* __restrict__ out) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (; i < m; i += stride) out[i] = in[idx[i]];
+  for (; i < m; i += stride) {
+    const uint32_t s = idx[i];
+    out[i] = s == HS_MISS ? T(0) : in[s];
+  }
 }
 
 // one thread builds one output byte (8 rows); counts set bits into *ones
@@ -25,7 +28,7 @@ __global__ void __launch_bounds__(256) k_gather_bits(const uint8_t* __restrict__
       int64_t i = b * 8 + k;
       if (i < m) {
         uint32_t s = idx[i];
-        v |= ((in[s >> 3] >> (s & 7)) & 1u) << k;
+        if (s != HS_MISS) v |= (in ? ((in[s >> 3] >> (s & 7)) & 1u) : 1u) << k;   // in == NULL: all rows valid
       }
     }
     out[b] = (uint8_t)v;
@@ -44,7 +47,8 @@ __global__ void __launch_bounds__(256) k_gather_lens(const TO* __restrict__ off,
   int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (; i < m; i += stride) {
     uint32_t s = idx[i];
-    TO a = off[s], b = off[s + 1];
+    TO a = 0, b = 0;
+    if (s != HS_MISS) { a = off[s]; b = off[s + 1]; }
     lens[i] = (uint32_t)(b - a);
     starts[i] = a;
   }
@@ -141,8 +145,8 @@ static unsigned grid_for(int64_t n, int threads = 256) {
   return (unsigned)g;
 }
 
-static void gather_validity(hs_ctx* c, const DevCol& src, const uint32_t* idx, int64_t m, OutCol& out) {
-  if (!src.validity) { out.null_count = 0; return; }
+static void gather_validity(hs_ctx* c, const DevCol& src, const uint32_t* idx, int64_t m, OutCol& out, bool may_miss) {
+  if (!src.validity && !may_miss) { out.null_count = 0; return; }
   out.validity.alloc(c, (size_t)((m + 7) / 8));
   DBuf ones(c, 8);
   ones.zero();
@@ -155,10 +159,10 @@ static void gather_validity(hs_ctx* c, const DevCol& src, const uint32_t* idx, i
   if (out.null_count == 0) out.validity.release();
 }
 
-void hs_gather_column(hs_ctx* c, const DevCol& src, const uint32_t* idx, int64_t m, OutCol& out) {
+void hs_gather_column(hs_ctx* c, const DevCol& src, const uint32_t* idx, int64_t m, OutCol& out, bool may_miss) {
   out.type = src.type;
   out.length = m;
-  gather_validity(c, src, idx, m, out);
+  gather_validity(c, src, idx, m, out, may_miss);
   if (hs_is_varlen(src.type)) {
     const bool in_large = hs_is_large(src.type);
     DBuf lens(c, (size_t)(m > 0 ? m : 1) * 4), starts(c, (size_t)(m > 0 ? m : 1) * (in_large ? 8 : 4));

@@ -101,6 +101,52 @@ __global__ void __launch_bounds__(256) k_join_bucket_offsets(const uint32_t* __r
   out[b] = r < nl ? off[r] : *total;
 }
 
+// join types other than inner: how many rows a left row contributes, given its number of matches
+__global__ void __launch_bounds__(256) k_join_type_counts(const uint32_t* __restrict__ cnt, int64_t nl, int type,
+                                                          uint32_t* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nl) return;
+  const uint32_t c = cnt[i];
+  out[i] = type == HS_JOIN_LEFT_OUTER ? (c ? c : 1u) : type == HS_JOIN_LEFT_SEMI ? (c ? 1u : 0u) : (c ? 0u : 1u);
+}
+// expansion for LEFT_OUTER (a row without a match pairs with HS_MISS), LEFT_SEMI and LEFT_ANTI (left rows only)
+__global__ void __launch_bounds__(256) k_join_expand_typed(const uint32_t* __restrict__ lb, const uint32_t* __restrict__ cnt,
+                                                           const uint32_t* __restrict__ tcnt, const uint32_t* __restrict__ off,
+                                                           int64_t nl, uint32_t* __restrict__ li, uint32_t* __restrict__ ri) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nl) return;
+  const uint32_t c = cnt[i], t = tcnt[i], o = off[i], b = lb[i];
+  for (uint32_t k = 0; k < t; k++) {
+    li[o + k] = (uint32_t)i;
+    if (ri) ri[o + k] = c ? b + k : HS_MISS;
+  }
+}
+// FULL OUTER = the LEFT OUTER pairs plus the right rows without a match; bucket b of the result holds its
+// left-outer pairs first (o1 = their bucket offsets), then its unmatched right rows (o2)
+__global__ void __launch_bounds__(256) k_full_outer_merge(const uint32_t* __restrict__ li1, const uint32_t* __restrict__ ri1,
+                                                          int64_t m1, const uint64_t* __restrict__ o1,
+                                                          const uint32_t* __restrict__ rj, int64_t m2,
+                                                          const uint64_t* __restrict__ o2, int32_t nb,
+                                                          uint32_t* __restrict__ li, uint32_t* __restrict__ ri) {
+  int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= m1 + m2) return;
+  const bool second = t >= m1;
+  const uint64_t q = second ? (uint64_t)(t - m1) : (uint64_t)t;
+  const uint64_t* o = second ? o2 : o1;
+  int lo = 0, hi = nb;            // largest b with o[b] <= q
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (o[mid] <= q) lo = mid; else hi = mid;
+  }
+  if (!second) {
+    const uint64_t d = q + o2[lo];
+    li[d] = li1[q]; ri[d] = ri1[q];
+  } else {
+    const uint64_t d = o1[lo + 1] + q;
+    li[d] = HS_MISS; ri[d] = rj[q];
+  }
+}
+
 // ------------------------------------------------------------------ fast path: merge-path tiles
 // One signed-integer key without NULLs on both sides and fixed-width, NULL-free output columns (the
 // lineitem x orders shape). Left rows are cut into tiles of JT rows that never cross a bucket; because both
@@ -430,6 +476,61 @@ void hs_offsets_to_device(hs_ctx* c, const int64_t* boff, int32_t nb, int64_t nr
   hs_sync(c);  // h goes out of scope
 }
 
+// (left row, right row) pairs of a join driven from side A: for every row of A the matching range of B's run in
+// the same bucket, turned into output counts according to the join type (INNER, LEFT_OUTER, LEFT_SEMI, LEFT_ANTI)
+struct PairList {
+  DBuf li, ri, d_ooff;          // row ids into A and B (ri unset for SEMI/ANTI); bucket offsets of the pairs (u64)
+  int64_t m = 0;
+  std::vector<int64_t> ooff;
+};
+static void probe_join(hs_ctx* ctx, const JoinSide& A, const JoinSide& B, int nk, int64_t na, int32_t nb, const DBuf& aoff,
+                       int type, PairList& out) {
+  DBuf lb(ctx, (size_t)na * 4), cnt(ctx, (size_t)na * 4), tcnt, off(ctx, (size_t)na * 4), total(ctx, 8);
+  uint64_t h_total = 0;
+  const uint32_t* counts = cnt.as<uint32_t>();
+  {
+    Stage s(ctx, "join_probe");
+    const KCol& ak = A.ks.k[0];
+    const KCol& bk = B.ks.k[0];
+    bool fast = nk == 1 && ak.type == HS_INT64 && !ak.has_nulls && !bk.has_nulls;
+    if (na > 0) {
+      unsigned g = (unsigned)((na + 255) / 256);
+      if (fast) LAUNCH(ctx, k_join_probe<true>, g, 256, 0, A, B, na, nb, lb.as<uint32_t>(), cnt.as<uint32_t>());
+      else LAUNCH(ctx, k_join_probe<false>, g, 256, 0, A, B, na, nb, lb.as<uint32_t>(), cnt.as<uint32_t>());
+      if (type != HS_JOIN_INNER) {
+        tcnt.alloc(ctx, (size_t)na * 4);
+        LAUNCH(ctx, k_join_type_counts, g, 256, 0, cnt.as<uint32_t>(), na, type, tcnt.as<uint32_t>());
+        counts = tcnt.as<uint32_t>();
+      }
+    }
+    hs_exclusive_scan_u32(ctx, counts, off.as<uint32_t>(), na, total.as<uint64_t>());
+    CK(cudaMemcpyAsync(&h_total, total.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    hs_sync(ctx);
+  }
+  if (h_total >= 0xFFFFFFF0ull) HS_THROW(HS_EUNSUPPORTED, "join output exceeds 2^32-16 rows in one call");
+  const int64_t m = (int64_t)h_total;
+  const bool pairs = type == HS_JOIN_INNER || type == HS_JOIN_LEFT_OUTER;
+  out.m = m;
+  out.li.alloc(ctx, (size_t)m * 4);
+  if (pairs) out.ri.alloc(ctx, (size_t)m * 4);
+  out.d_ooff.alloc(ctx, ((size_t)nb + 1) * 8);
+  out.ooff.assign((size_t)nb + 1, 0);
+  Stage s(ctx, "join_expand");
+  if (na > 0) {
+    unsigned g = (unsigned)((na + 255) / 256);
+    if (type == HS_JOIN_INNER)
+      LAUNCH(ctx, k_join_expand, g, 256, 0, lb.as<uint32_t>(), cnt.as<uint32_t>(), off.as<uint32_t>(), na,
+             out.li.as<uint32_t>(), out.ri.as<uint32_t>());
+    else
+      LAUNCH(ctx, k_join_expand_typed, g, 256, 0, lb.as<uint32_t>(), cnt.as<uint32_t>(), tcnt.as<uint32_t>(),
+             off.as<uint32_t>(), na, out.li.as<uint32_t>(), pairs ? out.ri.as<uint32_t>() : (uint32_t*)nullptr);
+  }
+  LAUNCH(ctx, k_join_bucket_offsets, (unsigned)((nb + 256) / 256), 256, 0, aoff.as<uint32_t>(), off.as<uint32_t>(),
+         total.as<uint64_t>(), na, nb, out.d_ooff.as<uint64_t>());
+  CK(cudaMemcpyAsync(out.ooff.data(), out.d_ooff.p, ((size_t)nb + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  hs_sync(ctx);
+}
+
 // per key column: min and max of the order-preserving image of the (NULL-free) cells
 __global__ void __launch_bounds__(256) k_keys_range(const __grid_constant__ KeySpec ks, int64_t n, uint64_t* __restrict__ mm) {
   uint64_t mn[HS_MAX_KEYS], mx[HS_MAX_KEYS];
@@ -484,7 +585,9 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
   *out = nullptr;
   check_view(left);
   check_view(right);
-  if (join_type != HS_JOIN_INNER) HS_THROW(HS_EUNSUPPORTED, "only inner joins are implemented");
+  if (join_type < HS_JOIN_INNER || join_type > HS_JOIN_LEFT_ANTI) HS_THROW(HS_EINVAL, "unknown join type %d", join_type);
+  if ((join_type == HS_JOIN_LEFT_SEMI || join_type == HS_JOIN_LEFT_ANTI) && n_right_out != 0)
+    HS_THROW(HS_EINVAL, "semi and anti joins return left columns only");
   if (left->num_buckets != right->num_buckets)
     HS_THROW(HS_EUNSUPPORTED, "indexes with different bucket counts (Spark would re-shuffle one side)");
   if (left->n_indexed != right->n_indexed) HS_THROW(HS_EINVAL, "indexes differ in number of indexed columns");
@@ -513,7 +616,7 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
   // ---- fast path: the key is one integer column, or any NULL-free fixed-width key tuple whose value ranges
   // fit 64 bits together (packed below); fixed-width NULL-free outputs
   const bool int_key = nk == 1 && (lc[0].type == HS_INT64 || lc[0].type == HS_INT32);
-  bool fast_join = n_left_out <= 16 && n_right_out <= 16 && nl > 0 && nr > 0;
+  bool fast_join = join_type == HS_JOIN_INNER && n_left_out <= 16 && n_right_out <= 16 && nl > 0 && nr > 0;
   for (int k = 0; k < nk && fast_join; k++)
     if (hs_is_varlen(lc[k].type) || lc[k].validity || rc[k].validity) fast_join = false;
   for (int i = 0; i < n_left_out && fast_join; i++) {
@@ -711,43 +814,43 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
     return HS_OK;
   }
 
-  DBuf lb(ctx, (size_t)nl * 4), cnt(ctx, (size_t)nl * 4), off(ctx, (size_t)nl * 4), total(ctx, 8);
-  uint64_t h_total = 0;
-  {
-    Stage s(ctx, "join_probe");
-    bool fast = nk == 1 && lc[0].type == HS_INT64 && !lc[0].validity && !rc[0].validity;
-    if (nl > 0) {
-      unsigned g = (unsigned)((nl + 255) / 256);
-      if (fast) LAUNCH(ctx, k_join_probe<true>, g, 256, 0, L, R, nl, nb, lb.as<uint32_t>(), cnt.as<uint32_t>());
-      else LAUNCH(ctx, k_join_probe<false>, g, 256, 0, L, R, nl, nb, lb.as<uint32_t>(), cnt.as<uint32_t>());
+  // ---- general path: per-row search of the other side's run, scan, pair lists, gathers
+  PairList pl;
+  bool miss_left = false, miss_right = false;
+  if (join_type == HS_JOIN_RIGHT_OUTER) {
+    probe_join(ctx, R, L, nk, nr, nb, roff, HS_JOIN_LEFT_OUTER, pl);
+    std::swap(pl.li, pl.ri);
+    miss_left = true;
+  } else if (join_type == HS_JOIN_FULL_OUTER) {
+    PairList a, b;
+    probe_join(ctx, L, R, nk, nl, nb, loff, HS_JOIN_LEFT_OUTER, a);
+    probe_join(ctx, R, L, nk, nr, nb, roff, HS_JOIN_LEFT_ANTI, b);
+    pl.m = a.m + b.m;
+    if ((uint64_t)pl.m >= 0xFFFFFFF0ull) HS_THROW(HS_EUNSUPPORTED, "join output exceeds 2^32-16 rows in one call");
+    pl.li.alloc(ctx, (size_t)pl.m * 4);
+    pl.ri.alloc(ctx, (size_t)pl.m * 4);
+    pl.ooff.resize((size_t)nb + 1);
+    for (int i = 0; i <= nb; i++) pl.ooff[i] = a.ooff[i] + b.ooff[i];
+    if (pl.m > 0) {
+      Stage s(ctx, "join_expand");
+      LAUNCH(ctx, k_full_outer_merge, (unsigned)((pl.m + 255) / 256), 256, 0, a.li.as<uint32_t>(), a.ri.as<uint32_t>(), a.m,
+             a.d_ooff.as<uint64_t>(), b.li.as<uint32_t>(), b.m, b.d_ooff.as<uint64_t>(), nb, pl.li.as<uint32_t>(),
+             pl.ri.as<uint32_t>());
     }
-    hs_exclusive_scan_u32(ctx, cnt.as<uint32_t>(), off.as<uint32_t>(), nl, total.as<uint64_t>());
-    CK(cudaMemcpyAsync(&h_total, total.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    hs_sync(ctx);
+    miss_left = miss_right = true;
+  } else {
+    probe_join(ctx, L, R, nk, nl, nb, loff, join_type, pl);
+    miss_right = join_type == HS_JOIN_LEFT_OUTER;
   }
-  if (h_total >= 0xFFFFFFF0ull) HS_THROW(HS_EUNSUPPORTED, "join output exceeds 2^32-16 rows in one call");
-  const int64_t m = (int64_t)h_total;
-  DBuf li(ctx, (size_t)m * 4), ri(ctx, (size_t)m * 4), d_ooff(ctx, ((size_t)nb + 1) * 8);
-  std::vector<int64_t> ooff((size_t)nb + 1, 0);
-  {
-    Stage s(ctx, "join_expand");
-    if (nl > 0)
-      LAUNCH(ctx, k_join_expand, (unsigned)((nl + 255) / 256), 256, 0, lb.as<uint32_t>(), cnt.as<uint32_t>(),
-             off.as<uint32_t>(), nl, li.as<uint32_t>(), ri.as<uint32_t>());
-    LAUNCH(ctx, k_join_bucket_offsets, (unsigned)((nb + 256) / 256), 256, 0, loff.as<uint32_t>(), off.as<uint32_t>(),
-           total.as<uint64_t>(), nl, nb, d_ooff.as<uint64_t>());
-    CK(cudaMemcpyAsync(ooff.data(), d_ooff.p, ((size_t)nb + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
-    hs_sync(ctx);
-  }
-  lb.release(); cnt.release(); off.release();
+  const int64_t m = pl.m;
   std::vector<OutCol> ocols((size_t)(n_left_out + n_right_out));
   {
     Stage s(ctx, "join_gather");
-    for (int i = 0; i < n_left_out; i++) hs_gather_column(ctx, lc[left_out[i]], li.as<uint32_t>(), m, ocols[i]);
+    for (int i = 0; i < n_left_out; i++) hs_gather_column(ctx, lc[left_out[i]], pl.li.as<uint32_t>(), m, ocols[i], miss_left);
     for (int i = 0; i < n_right_out; i++)
-      hs_gather_column(ctx, rc[right_out[i]], ri.as<uint32_t>(), m, ocols[n_left_out + i]);
+      hs_gather_column(ctx, rc[right_out[i]], pl.ri.as<uint32_t>(), m, ocols[n_left_out + i], miss_right);
   }
   Stage s(ctx, "d2h");
-  *out = hs_finish_table(ctx, ocols, m, nb, &ooff);
+  *out = hs_finish_table(ctx, ocols, m, nb, &pl.ooff);
   API_END(ctx)
 }

@@ -204,12 +204,30 @@ class Project:
 class Join:
     node_name = "Join"
 
-    def __init__(self, left, right, lkeys, rkeys):
+    def __init__(self, left, right, lkeys, rkeys, how="inner"):
         self.left, self.right, self.lkeys, self.rkeys = left, right, list(lkeys), list(rkeys)
+        self.how = normalise_join_type(how)
         self.children = [left, right]
 
     def output(self):
+        if self.how in ("left_semi", "left_anti"):
+            return self.left.output()
         return self.left.output() + self.right.output()
+
+
+_JOIN_TYPES = {"inner": "inner", "left": "left_outer", "leftouter": "left_outer", "left_outer": "left_outer",
+               "right": "right_outer", "rightouter": "right_outer", "right_outer": "right_outer",
+               "outer": "full_outer", "full": "full_outer", "fullouter": "full_outer", "full_outer": "full_outer",
+               "semi": "left_semi", "leftsemi": "left_semi", "left_semi": "left_semi",
+               "anti": "left_anti", "leftanti": "left_anti", "left_anti": "left_anti"}
+
+
+def normalise_join_type(how):
+    """Spark's joinType spellings (Dataset.join(right, joinExprs, joinType)) -> one name per type."""
+    k = how.lower().replace(" ", "")
+    if k not in _JOIN_TYPES:
+        raise ValueError(f"Unsupported join type '{how}'")
+    return _JOIN_TYPES[k]
 
 
 def resolve_name(name, available):
@@ -245,10 +263,11 @@ class DataFrame:
         names = [c.name if isinstance(c, Col) else c for c in cols]
         return DataFrame(self.session, Project(self.plan, names))
 
-    def join(self, other, on):
-        """on: EqCols, a conjunction of EqCols, or a list of column names present on both sides."""
+    def join(self, other, on, how="inner"):
+        """on: EqCols, a conjunction of EqCols, or a list of column names present on both sides;
+        how: Spark's join type names (inner, left_outer, right_outer, full_outer, left_semi, left_anti, ...)."""
         if isinstance(on, (list, tuple)) and all(isinstance(c, str) for c in on):
-            return DataFrame(self.session, Join(self.plan, other.plan, list(on), list(on)))
+            return DataFrame(self.session, Join(self.plan, other.plan, list(on), list(on), how))
         pairs = []
 
         def walk(e):
@@ -266,7 +285,7 @@ class DataFrame:
                 a, b = b, a
             lk.append(a.name)
             rk.append(b.name)
-        return DataFrame(self.session, Join(self.plan, other.plan, lk, rk))
+        return DataFrame(self.session, Join(self.plan, other.plan, lk, rk, how))
 
     def collect(self):
         """-> pyarrow.Table. With Hyperspace enabled the plan goes through the index rules first."""

@@ -241,19 +241,20 @@ class Context:
         return Table(self, out)
 
     # ---- join / filter
-    def join_table(self, left, right, left_out, right_out):
+    def join_table(self, left, right, left_out, right_out, how="inner"):
         lo = (C.c_int32 * max(len(left_out), 1))(*left_out)
         ro = (C.c_int32 * max(len(right_out), 1))(*right_out)
         out = C.POINTER(abi.hs_table)()
-        self._check(self._lib.hs_join_bucketed(self._h, C.byref(left.c), C.byref(right.c), C.c_int32(abi.HS_JOIN_INNER),
+        jt = abi.JOIN_TYPES[how] if isinstance(how, str) else int(how)
+        self._check(self._lib.hs_join_bucketed(self._h, C.byref(left.c), C.byref(right.c), C.c_int32(jt),
                                                lo, C.c_int32(len(left_out)), ro, C.c_int32(len(right_out)),
                                                C.byref(out)), "hs_join_bucketed")
         return Table(self, out)
 
-    def join(self, left_cols, left_off, right_cols, right_off, n_indexed, left_out, right_out):
+    def join(self, left_cols, left_off, right_cols, right_off, n_indexed, left_out, right_out, how="inner"):
         lcs, rcs = abi.ColumnSet(left_cols), abi.ColumnSet(right_cols)
         lv, rv = IndexView(lcs, n_indexed, left_off), IndexView(rcs, n_indexed, right_off)
-        t = self.join_table(lv, rv, left_out, right_out)
+        t = self.join_table(lv, rv, left_out, right_out, how)
         try:
             types = [lcs.arrays[i].type for i in left_out] + [rcs.arrays[i].type for i in right_out]
             return t.to_arrow(types), t.bucket_offsets()

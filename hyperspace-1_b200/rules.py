@@ -129,8 +129,9 @@ def _join_rule(session, plan):
         return None   # Spark would re-shuffle one side; not built
     ai, _ = _index_columns(a)
     lmap = {k.lower(): v for k, v in zip(plan.lkeys, plan.rkeys)}
-    j = Join(IndexScan(a, True), IndexScan(b, True), ai, [resolve_name(lmap[c.lower()], _index_columns(b)[0]) for c in ai])
-    j.left_out, j.right_out = list(lout), list(rout)
+    j = Join(IndexScan(a, True), IndexScan(b, True), ai, [resolve_name(lmap[c.lower()], _index_columns(b)[0]) for c in ai],
+             plan.how)
+    j.left_out, j.right_out = list(lout), ([] if plan.how in ("left_semi", "left_anti") else list(rout))
     return j
 
 
@@ -145,7 +146,7 @@ def prune_columns(plan):
             need = [c for c in have if any(c.lower() == p.lower() for p in plan.cols) or
                     any(c.lower() == k.lower() for k in keys)]
             sides.append(Project(child, need) if len(need) < len(have) and not isinstance(child, Project) else child)
-        return Project(Join(sides[0], sides[1], j.lkeys, j.rkeys), plan.cols)
+        return Project(Join(sides[0], sides[1], j.lkeys, j.rkeys, j.how), plan.cols)
     return plan
 
 
@@ -165,7 +166,7 @@ def apply_rules(session, plan):
         if isinstance(node, Filter):
             return Filter(rewrite(node.child, rule), node.pred)
         if isinstance(node, Join) and not isinstance(node.left, IndexScan):
-            j = Join(rewrite(node.left, rule), rewrite(node.right, rule), node.lkeys, node.rkeys)
+            j = Join(rewrite(node.left, rule), rewrite(node.right, rule), node.lkeys, node.rkeys, node.how)
             return j
         return node
     plan = rewrite(plan, _join_rule)
@@ -234,7 +235,7 @@ def execute(session, plan):
             nk = len(_index_columns(plan.left.entry)[0])
             if la is None or ra is None:
                 return pa.table({})
-            out, _ = session.ctx.join(la, lo, ra, ro, nk, lout, rout)
+            out, _ = session.ctx.join(la, lo, ra, ro, nk, lout, rout, how=plan.how)
             names = _dedupe([ln[i] for i in lout] + [rn[i] for i in rout])
             return pa.table(out, names=names)
         lt, rt = execute(session, plan.left), execute(session, plan.right)
@@ -245,13 +246,13 @@ def execute(session, plan):
         rt2 = rt.rename_columns(names[lt.num_columns:])
         lk2 = [names[lt.column_names.index(k)] for k in lk]
         rk2 = [names[lt.num_columns + rt.column_names.index(k)] for k in rk]
-        # inner equi-join; pyarrow drops NULL keys as SQL does; keep both key columns like Spark
-        rt3 = rt2.append_column("__rk", rt2[rk2[0]]) if len(rk2) == 1 else rt2
-        j = lt2.join(rt3, keys=lk2, right_keys=rk2, join_type="inner", coalesce_keys=True)
-        if len(rk2) == 1:
-            j = j.rename_columns([rk2[0] if c == "__rk" else c for c in j.column_names])
-            return j.select(names)
-        return j
+        # equi-join on the host engine; NULL keys match nothing, both key columns are kept like Spark does
+        pa_how = {"inner": "inner", "left_outer": "left outer", "right_outer": "right outer",
+                  "full_outer": "full outer", "left_semi": "left semi", "left_anti": "left anti"}[plan.how]
+        j = lt2.join(rt2, keys=lk2, right_keys=rk2, join_type=pa_how, coalesce_keys=False)
+        if plan.how in ("left_semi", "left_anti"):
+            return j.select(names[: lt.num_columns])
+        return j.select(names)
     if isinstance(plan, IndexScan):
         arrays, names, _ = _single_run(session, plan.entry)
         return pa.table(arrays, names=names)

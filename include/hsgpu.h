@@ -126,7 +126,18 @@ typedef struct hs_predicate {
   const hs_pred_term* terms; /* postfix order; at most 32 terms, depth 16 */
 } hs_predicate;
 
-typedef enum hs_join_type { HS_JOIN_INNER = 0 } hs_join_type;
+/* JoinIndexRule matches a Join of any type with an equi-condition (HS/index/rules/JoinIndexRule.scala:57-60);
+ * these are the types Spark's SortMergeJoinExec runs over the two bucketed index scans. Rows whose key holds a
+ * NULL match nothing: they appear (padded with NULLs) in the outer joins on their own side and in LEFT_ANTI.
+ * SEMI and ANTI return left columns only (n_right_out must be 0). */
+typedef enum hs_join_type {
+  HS_JOIN_INNER = 0,
+  HS_JOIN_LEFT_OUTER = 1,
+  HS_JOIN_RIGHT_OUTER = 2,
+  HS_JOIN_FULL_OUTER = 3,
+  HS_JOIN_LEFT_SEMI = 4,
+  HS_JOIN_LEFT_ANTI = 5
+} hs_join_type;
 
 /* Per-stage device timings of the last call (CUDA events on the context's
  * stream), filled only while timing is enabled. */
@@ -211,7 +222,9 @@ int32_t hs_merge_runs(hs_ctx* ctx, const hs_index_view* runs, int32_t nruns,
  * index joins bucket i of the right one on the indexed columns; NULL keys never match.
  * Both views must have the same num_buckets and key types (else HS_EUNSUPPORTED).
  * Output columns: left_out[0..n_left_out) of the left view, then right_out[..] of the
- * right view; row order inside a bucket is unspecified (compare as multisets). */
+ * right view; row order inside a bucket is unspecified (compare as multisets). In the outer
+ * joins the columns of the side without a match are NULL for that row (validity bitmaps are
+ * added to the result as needed). join_type: hs_join_type. */
 int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left,
                          const hs_index_view* right, int32_t join_type,
                          const int32_t* left_out, int32_t n_left_out,

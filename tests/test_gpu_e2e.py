@@ -78,6 +78,39 @@ def test_quick_start(env):
     assert "GpuBucketedSortMergeJoin" in out[0] and "Plan without indexes" in out[0]
 
 
+@pytest.mark.parametrize("how", ["left_outer", "right_outer", "full_outer", "left_semi", "left_anti"])
+def test_join_types_through_the_api(env, how):
+    """JoinIndexRule rewrites joins of every type (JoinIndexRule.scala:57-60): indexed result == plain result,
+    with an employee in a department that does not exist, a department without employees and a NULL key."""
+    from hyperspace_1_b200 import Hyperspace, IndexConfig
+    s, tmp = env
+    os.makedirs(tmp / "departments")
+    os.makedirs(tmp / "employees")
+    dept = departments_table()
+    emp = employees_table()
+    emp = pa.concat_tables([emp, pa.table({"empId": pa.array([9001, 9002], type=emp.schema.field("empId").type),
+                                           "empName": ["NOBODY", "NULLKEY"],
+                                           "deptId": pa.array([77, None], type=emp.schema.field("deptId").type)})])
+    pq.write_table(dept, tmp / "departments" / "part-0.parquet")
+    pq.write_table(emp, tmp / "employees" / "part-0.parquet")
+    d, e = s.read_parquet(str(tmp / "departments")), s.read_parquet(str(tmp / "employees"))
+    hs = Hyperspace(s)
+    hs.createIndex(d, IndexConfig("deptIndex", ["deptId"], ["deptName"]))
+    hs.createIndex(e, IndexConfig("empIndex", ["deptId"], ["empName"]))
+    j = e.join(d, e["deptId"] == d["deptId"], how)
+    j = j.select(e["empName"]) if how in ("left_semi", "left_anti") else j.select(e["empName"], d["deptName"])
+    got = _verify_index_usage(s, j, ["empIndex", "deptIndex"])
+    names = got["empName"].to_pylist()
+    if how == "left_anti":
+        assert sorted(names) == ["NOBODY", "NULLKEY"]
+    if how == "left_semi":
+        assert "NOBODY" not in names and len(names) == len(EMPLOYEES)
+    if how in ("right_outer", "full_outer"):
+        assert "Operations" in got["deptName"].to_pylist()      # department 40 has no employees
+    if how in ("left_outer", "full_outer"):
+        assert "NOBODY" in names and "NULLKEY" in names
+
+
 def test_string_and_composite_indexes_through_the_api(env):
     from hyperspace_1_b200 import Hyperspace, IndexConfig
     s, tmp = env

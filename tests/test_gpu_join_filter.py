@@ -146,6 +146,35 @@ def test_join_packed_key_tuples(ctx, oracle):
         parity.assert_same_multiset(jg, want, joff, woff, f"packed-key join {kinds}")
 
 
+@pytest.mark.parametrize("how", ["left_outer", "right_outer", "full_outer", "left_semi", "left_anti"])
+def test_join_types(ctx, oracle, how):
+    """Outer, semi and anti joins over two indexes (JoinIndexRule accepts every join type): NULL keys, keys
+    missing on either side, many-to-many matches, empty buckets, string and composite keys, string payloads."""
+    rng = np.random.default_rng(41)
+
+    def check(l, r, nk, nb, what):
+        lg, loff = ctx.build_index(l, nk, nb)
+        rg, roff = ctx.build_index(r, nk, nb)
+        lout = list(range(len(l)))
+        rout = [] if how in ("left_semi", "left_anti") else list(range(len(r)))
+        jg, joff = ctx.join(lg, loff, rg, roff, nk, lout, rout, how=how)
+        li, ri, woff = oracle.join_typed(lg, rg, nk, loff, roff, how)
+        want = [oracle.take_or_null(lg[i], li) for i in lout] + [oracle.take_or_null(rg[i], ri) for i in rout]
+        parity.assert_same_multiset(jg, want, joff, woff, f"{how} join, {what}")
+
+    mk = lambda n, hi, nullp: [pa.array(rng.integers(0, hi, size=n), mask=rng.random(n) < nullp),
+                               pa.array(rng.random(n)), pa.array([f"s{int(x)}" * int(x % 4) for x in rng.integers(0, 99, size=n)])]
+    check(mk(5000, 900, 0.03), mk(1200, 1100, 0.03), 1, 16, "int keys with NULLs")
+    check(mk(300, 40, 0.0), mk(20, 4000, 0.0), 1, 64, "mostly empty buckets")
+    check(mk(50, 10, 0.0), [c.slice(0, 0) for c in mk(5, 10, 0.0)], 1, 4, "empty right side")
+    s, v = string_keys(3000)
+    ls = s.take(pa.array(rng.integers(0, 3000, size=5000)))
+    check([ls, pa.array(np.arange(5000))], [s.slice(0, 2000), v.slice(0, 2000)], 1, 8, "string keys")
+    comp = lambda n: [pa.array(rng.integers(0, 20, size=n).astype(np.int32)),
+                      pa.array(rng.integers(0, 30, size=n), mask=rng.random(n) < 0.02), pa.array(rng.random(n))]
+    check(comp(4000), comp(700), 2, 32, "composite keys")
+
+
 def test_join_after_incremental_refresh_two_runs_per_bucket(ctx, oracle):
     lcols, keys = lineitem(20000)
     n = len(lcols[0])

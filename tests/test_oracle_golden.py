@@ -147,3 +147,30 @@ def test_filter_three_valued_logic(oracle):
     assert idx.tolist() == [0]
     idx = oracle.filter_rows([a, b], [("is_null", 0), ("is_not_null", 1), ("and",)])
     assert idx.tolist() == [1]
+
+
+def test_join_types_against_pyarrow(oracle):
+    """oracle.join_typed (outer/semi/anti on top of the inner pairs) against pyarrow's hash join on the same
+    rows: an independent implementation with the same NULL-key rule (NULL keys match nothing)."""
+    import numpy as np
+    import pyarrow as pa
+    rng = np.random.default_rng(5)
+    mk = lambda n, hi: [pa.array(rng.integers(0, hi, size=n), mask=rng.random(n) < 0.05), pa.array(np.arange(n))]
+    l, r = mk(400, 60), mk(150, 80)
+    nb = 8
+    lp, loff = oracle.build_index(l, 1, nb)
+    rp, roff = oracle.build_index(r, 1, nb)
+    lg, rg = oracle.take(l, lp), oracle.take(r, rp)
+    lt = pa.table({"k": lg[0], "lv": lg[1]})
+    rt = pa.table({"k": rg[0], "rv": rg[1]})
+    for how, pa_how in (("inner", "inner"), ("left_outer", "left outer"), ("right_outer", "right outer"),
+                        ("full_outer", "full outer"), ("left_semi", "left semi"), ("left_anti", "left anti")):
+        li, ri, ooff = oracle.join_typed(lg, rg, 1, loff, roff, how)
+        got_l = oracle.take_or_null(lg[1], li).to_pylist()
+        got_r = oracle.take_or_null(rg[1], ri).to_pylist() if ri is not None else [None] * len(li)
+        want = lt.join(rt, keys="k", join_type=pa_how)
+        want_l = want["lv"].to_pylist()
+        want_r = want["rv"].to_pylist() if "rv" in want.column_names else [None] * want.num_rows
+        key = lambda p: (-1 if p[0] is None else p[0], -1 if p[1] is None else p[1])
+        assert sorted(zip(got_l, got_r), key=key) == sorted(zip(want_l, want_r), key=key), how
+        assert ooff[-1] == len(li)
