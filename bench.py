@@ -23,7 +23,8 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-NUM_BUCKETS = 200
+BUCKETS_PER_GPU = 200
+NUM_BUCKETS = BUCKETS_PER_GPU
 ROW_BYTES = 24          # R: int64 key + two float64
 KEY_BYTES = 8           # Kb
 ALGO_BYTES_PER_ROW = KEY_BYTES + 4 * ROW_BYTES   # hash Kb + scatter 2R + sort 2R = 104
@@ -195,9 +196,14 @@ def main():
     ap.add_argument("--ref-rows", type=int, default=10_000_000, help="rows per step of the CPU arms")
     ap.add_argument("--e2e-steps", type=int, default=3, help="end-to-end steps per host thread")
     ap.add_argument("--e2e-threads", type=int, default=3, help="host threads (contexts) of the end-to-end leg at N=1")
+    ap.add_argument("--buckets", type=int, default=0,
+                    help="bucket count of the index; default 200 per GPU (the bucket size, i.e. the index file size, "
+                         "stays that of the 1-GPU configuration as rows are added with GPUs)")
     ap.add_argument("--no-join", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
+    global NUM_BUCKETS
+    NUM_BUCKETS = args.buckets if args.buckets > 0 else BUCKETS_PER_GPU * max(1, args.gpus)
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
         reference_arm(args, real_stdout)
@@ -460,10 +466,11 @@ def main():
                 "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "int64", "data": "synthetic",
                 "config": {"workload": "cfg2: TPC-H-shaped lineitem, CoveringIndex on int64 l_orderkey including "
-                                       "l_extendedprice,l_discount, 200 buckets",
+                                       "l_extendedprice,l_discount, 200 buckets per GPU "
+                                       "(100 M rows and 200 buckets are added with every GPU: constant bucket size)",
                            "rows_per_gpu": n, "num_buckets": NUM_BUCKETS, "row_bytes": ROW_BYTES,
                            "l2_policy": "inputs (2.4 GB per step) are larger than L2; no flush needed",
-                           "parallelism": f"buckets sharded over {world} GPU(s), NCCL all-to-all in the build"
+                           "parallelism": f"buckets sharded over {world} GPU(s); rows reach their owners over NVLink peer memory"
                            if world > 1 else "single GPU"},
                 "roofline": roofline, "build_roofline": build_roofline, "stages": per_stage,
                 "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "join": join}
