@@ -378,8 +378,10 @@ def main():
 
     # ---- indexed join (cfg3): lineitem x orders over two indexes, bucket-local, no communication
     join = None
+    filt = None
     if not args.no_join:
         jerr, jlaunches = "", 0
+        flocal = [0.0, 0.0, 0.0, 0.0]
         try:
             g = torch.Generator(device=dev)
             g.manual_seed(20240602 + rank)
@@ -420,6 +422,21 @@ def main():
             torch.cuda.synchronize()
             jlocal = [j0.elapsed_time(j1) / jsteps, float(n_out), float(lt.nrows), float(ot.nrows), 1.0]
             jlaunches = ctx.launch_count() - jl0
+            # ---- filtered index scan over the same lineitem index (FilterIndexRule's plan, K7)
+            thr = int(key[: min(n, 1_000_000)].median().item())
+            probe = int(key[0].item())
+            for terms, slot in (([("ge", 0, thr)], 0), ([("eq", 0, probe)], 1)):
+                ctx.filter_table(lv, terms, [0, 1, 2]).free()
+                torch.cuda.synchronize()
+                f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                f0.record(stream)
+                for _ in range(jsteps):
+                    ft = ctx.filter_table(lv, terms, [0, 1, 2])
+                    flocal[2 * slot + 1] = float(ft.nrows)
+                    ft.free()
+                f1.record(stream)
+                torch.cuda.synchronize()
+                flocal[2 * slot] = f0.elapsed_time(f1) / jsteps
             lt.free()
             ot.free()
             del ok, ototal
@@ -427,6 +444,22 @@ def main():
             jlocal = [0.0, 0.0, 0.0, 0.0, 0.0]
             jerr = str(ex)[:200]
         # every rank reaches the reductions, whether its join worked or not
+        fmx = torch.tensor(flocal, dtype=torch.float64, device=dev)
+        fsum = fmx.clone()
+        if dist is not None:
+            dist.all_reduce(fmx, op=dist.ReduceOp.MAX)
+            dist.all_reduce(fsum, op=dist.ReduceOp.SUM)
+        if float(fmx[0].item()) > 0:
+            rows_all = n * world
+            m_range, m_point = int(fsum[1].item()), int(fsum[3].item())
+            ms_range, ms_point = float(fmx[0].item()), float(fmx[2].item())
+            fbytes = rows_all * KEY_BYTES + 2 * m_range * ROW_BYTES
+            filt = {"range_scan": {"predicate": "l_orderkey >= median", "ms_per_step": ms_range, "rows_scanned": rows_all,
+                                   "rows_out": m_range, "scanned_rows_per_s": rows_all / (ms_range * 1e-3),
+                                   "algorithmic_bytes": fbytes, "achieved_GBps": fbytes / (ms_range * 1e-3) / 1e9,
+                                   "frac_of_measured_peak_per_gpu": fbytes / (ms_range * 1e-3) / 1e9 / peak / world},
+                    "point_lookup": {"predicate": "l_orderkey = literal (one bucket, binary search of the sorted run)",
+                                     "ms_per_step": ms_point, "rows_out": m_point}}
         tot = torch.tensor(jlocal, dtype=torch.float64, device=dev)
         mx = tot.clone()
         if dist is not None:
@@ -473,7 +506,8 @@ def main():
                            "parallelism": f"buckets sharded over {world} GPU(s); rows reach their owners over NVLink peer memory"
                            if world > 1 else "single GPU"},
                 "roofline": roofline, "build_roofline": build_roofline, "stages": per_stage,
-                "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "join": join}
+                "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "join": join,
+                "filter": filt}
         if use_dist and xchg:
             b = sum(x[0] for x in xchg) / len(xchg)
             ms = sum(x[1] for x in xchg) / len(xchg)

@@ -62,45 +62,135 @@ __device__ __forceinline__ void eval_leaf(const KCol& c, int64_t i, const KTerm&
   }
 }
 
-// rows [row0, row0 + n): flag[i - row0] = predicate is TRUE. The stack is two 32-bit masks.
+// the postfix program on one row -> TRUE or not (3-valued logic: kn = "known" bits, vl = value bits; the stack
+// is two 32-bit masks)
+__device__ __forceinline__ bool eval_pred(const KCols& cols, const KPred& pred, int64_t row) {
+  uint32_t kn = 0, vl = 0;
+  int sp = 0;
+  for (int t = 0; t < pred.nterms; t++) {
+    const KTerm& tm = pred.t[t];
+    if (tm.op == HS_PRED_AND || tm.op == HS_PRED_OR) {
+      bool kb = (kn >> (sp - 1)) & 1, vb = (vl >> (sp - 1)) & 1;
+      bool ka = (kn >> (sp - 2)) & 1, va = (vl >> (sp - 2)) & 1;
+      bool k, v;
+      if (tm.op == HS_PRED_AND) {
+        if ((ka && !va) || (kb && !vb)) { k = true; v = false; }
+        else if (ka && kb) { k = true; v = true; }
+        else { k = false; v = false; }
+      } else {
+        if ((ka && va) || (kb && vb)) { k = true; v = true; }
+        else if (ka && kb) { k = true; v = false; }
+        else { k = false; v = false; }
+      }
+      sp -= 2;
+      kn = (kn & ~(3u << sp)) | ((uint32_t)k << sp);
+      vl = (vl & ~(3u << sp)) | ((uint32_t)v << sp);
+      sp++;
+    } else if (tm.op == HS_PRED_NOT) {
+      if ((kn >> (sp - 1)) & 1) vl ^= 1u << (sp - 1);
+    } else {
+      bool k, v;
+      eval_leaf(cols.c[tm.col], row, tm, pred.pool, &k, &v);
+      kn = (kn & ~(1u << sp)) | ((uint32_t)k << sp);
+      vl = (vl & ~(1u << sp)) | ((uint32_t)v << sp);
+      sp++;
+    }
+  }
+  return (kn & 1u) && (vl & 1u);
+}
+
+// rows [row0, row0 + n): flag[i - row0] = predicate is TRUE
 __global__ void __launch_bounds__(256) k_filter_eval(const __grid_constant__ KCols cols,
                                                      const __grid_constant__ KPred pred, int64_t row0, int64_t n,
                                                      uint8_t* __restrict__ flag) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (; i < n; i += stride) {
-    uint32_t kn = 0, vl = 0;
-    int sp = 0;
-    for (int t = 0; t < pred.nterms; t++) {
-      const KTerm& tm = pred.t[t];
-      if (tm.op == HS_PRED_AND || tm.op == HS_PRED_OR) {
-        bool kb = (kn >> (sp - 1)) & 1, vb = (vl >> (sp - 1)) & 1;
-        bool ka = (kn >> (sp - 2)) & 1, va = (vl >> (sp - 2)) & 1;
-        bool k, v;
-        if (tm.op == HS_PRED_AND) {
-          if ((ka && !va) || (kb && !vb)) { k = true; v = false; }
-          else if (ka && kb) { k = true; v = true; }
-          else { k = false; v = false; }
-        } else {
-          if ((ka && va) || (kb && vb)) { k = true; v = true; }
-          else if (ka && kb) { k = true; v = false; }
-          else { k = false; v = false; }
-        }
-        sp -= 2;
-        kn = (kn & ~(3u << sp)) | ((uint32_t)k << sp);
-        vl = (vl & ~(3u << sp)) | ((uint32_t)v << sp);
-        sp++;
-      } else if (tm.op == HS_PRED_NOT) {
-        if ((kn >> (sp - 1)) & 1) vl ^= 1u << (sp - 1);
-      } else {
-        bool k, v;
-        eval_leaf(cols.c[tm.col], row0 + i, tm, pred.pool, &k, &v);
-        kn = (kn & ~(1u << sp)) | ((uint32_t)k << sp);
-        vl = (vl & ~(1u << sp)) | ((uint32_t)v << sp);
-        sp++;
+  for (; i < n; i += stride) flag[i] = eval_pred(cols, pred, row0 + i);
+}
+
+// ---- fixed-width, NULL-free output columns: two streaming passes, no row-id list
+// Pass 1 evaluates the predicate once and keeps one bit per row (a warp's ballot per 32 rows) plus the number of
+// matches per tile of FT_TILE rows. After a scan of the tile counts, pass 2 reads the bits, ranks the matches
+// of a tile with popcounts and copies every output column straight from its source to its packed place — rows
+// keep their order, so a scan of a sorted index stays sorted. Per row: predicate columns once, output columns
+// once, 1/8 byte of bits twice.
+#define FT_TILE 2048
+__global__ void __launch_bounds__(256) k_filter_mask(const __grid_constant__ KCols cols, const __grid_constant__ KPred pred,
+                                                     int64_t row0, int64_t n, uint32_t* __restrict__ mask,
+                                                     uint32_t* __restrict__ tile_cnt) {
+  __shared__ uint32_t s_cnt[8];
+  const int64_t base = (int64_t)blockIdx.x * FT_TILE;
+  uint32_t c = 0;
+#pragma unroll
+  for (int k = 0; k < FT_TILE / 256; k++) {
+    const int64_t i = base + k * 256 + threadIdx.x;
+    const bool f = i < n && eval_pred(cols, pred, row0 + i);
+    const uint32_t b = __ballot_sync(0xffffffffu, f);
+    if (lane_id() == 0) {
+      if (base + k * 256 + (threadIdx.x & ~31) < n) mask[(base + k * 256 + threadIdx.x) >> 5] = b;
+      c += __popc(b);
+    }
+  }
+  if (lane_id() == 0) s_cnt[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+    for (int w = 0; w < 8; w++) t += s_cnt[w];
+    tile_cnt[blockIdx.x] = t;
+  }
+}
+struct FilterOut {
+  int32_t n;
+  int32_t es[HS_MAX_MOVE];
+  const void* src[HS_MAX_MOVE];
+  void* dst[HS_MAX_MOVE];
+};
+__global__ void __launch_bounds__(256) k_filter_write(const __grid_constant__ FilterOut fo, int64_t row0, int64_t n,
+                                                      const uint32_t* __restrict__ mask,
+                                                      const uint32_t* __restrict__ tile_off) {
+  __shared__ uint32_t s_word[FT_TILE / 32], s_pre[FT_TILE / 32];
+  const int64_t base = (int64_t)blockIdx.x * FT_TILE;
+  if (threadIdx.x < FT_TILE / 32) {
+    const int64_t w = (base >> 5) + threadIdx.x;
+    const uint32_t v = (w << 5) < n ? mask[w] : 0u;
+    s_word[threadIdx.x] = v;
+    // exclusive prefix of the popcounts of the tile's 64 words: per warp here, the second warp's words get the
+    // first warp's total (s_half) added where they are used
+    uint32_t inc = __popc(v);
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d);
+      if (lane_id() >= (uint32_t)d) inc += o;
+    }
+    s_pre[threadIdx.x] = inc - __popc(v);
+  }
+  __syncthreads();
+  __shared__ uint32_t s_half;
+  if (threadIdx.x == 31) s_half = s_pre[31] + __popc(s_word[31]);
+  __syncthreads();
+  const uint32_t obase = tile_off[blockIdx.x];
+  uint32_t rank[FT_TILE / 256];
+  uint32_t fl = 0;
+#pragma unroll
+  for (int k = 0; k < FT_TILE / 256; k++) {
+    const uint32_t r = k * 256 + threadIdx.x, w = r >> 5;
+    const uint32_t word = s_word[w];
+    if ((word >> (r & 31)) & 1u) fl |= 1u << k;
+    rank[k] = obase + s_pre[w] + (w >= 32 ? s_half : 0u) + __popc(word & ((1u << (r & 31)) - 1u));
+  }
+  for (int c = 0; c < fo.n; c++) {
+    const int es = fo.es[c];
+#pragma unroll
+    for (int k = 0; k < FT_TILE / 256; k++) {
+      if (!((fl >> k) & 1u)) continue;
+      const int64_t i = row0 + base + k * 256 + threadIdx.x;
+      switch (es) {
+        case 8: ((uint64_t*)fo.dst[c])[rank[k]] = ((const uint64_t*)fo.src[c])[i]; break;
+        case 4: ((uint32_t*)fo.dst[c])[rank[k]] = ((const uint32_t*)fo.src[c])[i]; break;
+        case 2: ((uint16_t*)fo.dst[c])[rank[k]] = ((const uint16_t*)fo.src[c])[i]; break;
+        default: ((uint8_t*)fo.dst[c])[rank[k]] = ((const uint8_t*)fo.src[c])[i]; break;
       }
     }
-    flag[i] = (kn & 1u) && (vl & 1u);
   }
 }
 
@@ -229,6 +319,42 @@ extern "C" int32_t hs_filter_scan(hs_ctx* ctx, const hs_index_view* index, const
       n = index->bucket_offsets[b + 1] - row0;
       if (row0 < 0 || n < 0 || row0 + n > nrows) HS_THROW(HS_EINVAL, "bad bucket_offsets");
     }
+  }
+  bool packed_out = n > 0;
+  for (int i = 0; i < n_out && packed_out; i++) {
+    const DevCol& oc = cols[out_cols[i]];
+    if (hs_fixed_width(oc.type) == 0 || oc.validity) packed_out = false;
+  }
+  if (packed_out) {
+    const uint32_t ntiles = (uint32_t)((n + FT_TILE - 1) / FT_TILE);
+    DBuf mask(ctx, (size_t)ntiles * (FT_TILE / 32) * 4), tcnt(ctx, (size_t)ntiles * 4), total(ctx, 8);
+    uint64_t h_total = 0;
+    {
+      Stage s(ctx, "filter_eval");
+      LAUNCH(ctx, k_filter_mask, ntiles, 256, 0, kc, kp, row0, n, mask.as<uint32_t>(), tcnt.as<uint32_t>());
+      hs_exclusive_scan_u32(ctx, tcnt.as<uint32_t>(), tcnt.as<uint32_t>(), ntiles, total.as<uint64_t>());
+      h_total = *(const uint64_t*)hs_read_wait(ctx, hs_read_begin(ctx, total.p, 8));
+    }
+    const int64_t m = (int64_t)h_total;
+    std::vector<OutCol> ocols((size_t)n_out);
+    FilterOut fo;
+    memset(&fo, 0, sizeof fo);
+    fo.n = n_out;
+    for (int i = 0; i < n_out; i++) {
+      const DevCol& oc = cols[out_cols[i]];
+      OutCol& o = ocols[i];
+      o.type = oc.type; o.length = m; o.null_count = 0;
+      o.data_bytes = m * hs_fixed_width(oc.type);
+      o.data.alloc(ctx, (size_t)o.data_bytes);
+      fo.es[i] = hs_fixed_width(oc.type); fo.src[i] = oc.data; fo.dst[i] = o.data.p;
+    }
+    if (m > 0) {
+      Stage s(ctx, "filter_write");
+      LAUNCH(ctx, k_filter_write, ntiles, 256, 0, fo, row0, n, mask.as<uint32_t>(), tcnt.as<uint32_t>());
+    }
+    Stage s(ctx, "d2h");
+    *out = hs_finish_table(ctx, ocols, m, 0, nullptr);
+    return HS_OK;
   }
   DBuf flag(ctx, (size_t)n), pos(ctx, (size_t)n * 4), total(ctx, 8);
   uint64_t h_total = 0;

@@ -224,6 +224,24 @@ def test_filter_predicates(ctx, oracle):
         parity.assert_same_multiset(fg, want, what=f"filter {p}")
 
 
+def test_filter_packed_outputs_keep_row_order(ctx, oracle):
+    """Fixed-width NULL-free output columns take the two-pass bitmask path: same rows as the oracle, and in
+    the order of the index (a scan of a sorted run stays sorted). Sizes around the 2048-row tile, a pruned
+    bucket (scan starting in the middle of the table), predicates that select nothing and everything."""
+    for n_orders in (300, 5000, 40000):
+        cols, keys = lineitem(n_orders)
+        got, boff = ctx.build_index(cols, 1, 16)
+        k = int(keys[len(keys) // 2])
+        for p in ([("ge", 0, k)], [("eq", 0, k)], [("lt", 1, 30000.0), ("ge", 2, 0.05), ("and",)],
+                  [("lt", 0, -1)], [("ge", 0, -1)], [("eq", 0, k), ("not",)],
+                  [("gt", 2, 0.02), ("le", 0, k), ("or",), ("ne", 1, 0.0), ("and",)]):
+            fg = ctx.filter_scan(got, 1, boff, p, [2, 0, 1])
+            idx = pa.array(oracle.filter_rows(got, p))
+            want = [got[2].take(idx), got[0].take(idx), got[1].take(idx)]
+            for g, w in zip(fg, want):
+                assert g.equals(w), f"filter {p} on {len(got[0])} rows: rows or their order differ"
+
+
 def test_filter_bucket_pruning_matches_full_scan(ctx, oracle):
     s, v = string_keys(8000)
     got, boff = ctx.build_index([s, v], 1, 100)
