@@ -15,6 +15,7 @@ VARLEN = (HS_UTF8, HS_BINARY, HS_LARGE_UTF8, HS_LARGE_BINARY)
 HS_MEM_HOST, HS_MEM_DEVICE = 0, 1
 (HS_PRED_EQ, HS_PRED_NE, HS_PRED_LT, HS_PRED_LE, HS_PRED_GT, HS_PRED_GE,
  HS_PRED_IS_NULL, HS_PRED_IS_NOT_NULL) = range(1, 9)
+HS_PRED_IN = 9
 HS_PRED_AND, HS_PRED_OR, HS_PRED_NOT = 16, 17, 18
 HS_JOIN_INNER, HS_JOIN_LEFT_OUTER, HS_JOIN_RIGHT_OUTER, HS_JOIN_FULL_OUTER, HS_JOIN_LEFT_SEMI, HS_JOIN_LEFT_ANTI = range(6)
 JOIN_TYPES = {"inner": 0, "left_outer": 1, "left": 1, "right_outer": 2, "right": 2, "full_outer": 3, "outer": 3,

@@ -2,6 +2,8 @@
 // Executes the plan FilterIndexRule.apply produces (HS/index/rules/FilterIndexRule.scala:43-85): rows of the
 // index for which the predicate is TRUE (SQL three-valued logic), projected to the requested columns.
 // `first indexed column = literal` on a single-column index prunes the scan to the literal's bucket.
+#include <algorithm>
+
 #include "hs_keys.cuh"
 #include "hs_kernels.h"
 
@@ -34,6 +36,23 @@ __device__ __forceinline__ void eval_leaf(const KCol& c, int64_t i, const KTerm&
   if (t.op == HS_PRED_IS_NULL) { *known = true; *val = !valid; return; }
   if (t.op == HS_PRED_IS_NOT_NULL) { *known = true; *val = valid; return; }
   if (!valid) { *known = false; *val = false; return; }
+  if (t.op == HS_PRED_IN) {
+    // integer cell against a sorted list of int64 in the literal pool (8-byte aligned there)
+    int64_t x = 0;
+    switch (c.type) {
+      case HS_BOOL: x = (((const uint8_t*)c.data)[i >> 3] >> (i & 7)) & 1; break;
+      case HS_INT8: x = ((const int8_t*)c.data)[i]; break;
+      case HS_INT16: x = ((const int16_t*)c.data)[i]; break;
+      case HS_INT32: x = ((const int32_t*)c.data)[i]; break;
+      default: x = ((const int64_t*)c.data)[i]; break;
+    }
+    const int64_t* list = (const int64_t*)(pool + t.lit_off);
+    int lo = 0, hi = t.lit_len;
+    while (lo < hi) { int mid = (lo + hi) >> 1; if (list[mid] < x) lo = mid + 1; else hi = mid; }
+    *known = true;
+    *val = lo < t.lit_len && list[lo] == x;
+    return;
+  }
   int cmp = 0;
   switch (c.type) {
     case HS_BOOL: { int64_t x = (((const uint8_t*)c.data)[i >> 3] >> (i & 7)) & 1; cmp = (x > t.lit_i64) - (x < t.lit_i64); break; }
@@ -267,9 +286,15 @@ extern "C" int32_t hs_filter_scan(hs_ctx* ctx, const hs_index_view* index, const
     const hs_pred_term& tm = pred->terms[t];
     if (tm.op == HS_PRED_AND || tm.op == HS_PRED_OR) { if (depth < 2) HS_THROW(HS_EINVAL, "malformed predicate"); depth--; }
     else if (tm.op == HS_PRED_NOT) { if (depth < 1) HS_THROW(HS_EINVAL, "malformed predicate"); }
-    else if (tm.op >= HS_PRED_EQ && tm.op <= HS_PRED_IS_NOT_NULL) {
+    else if (tm.op >= HS_PRED_EQ && tm.op <= HS_PRED_IN) {
       if (tm.col < 0 || tm.col >= index->ncols) HS_THROW(HS_EINVAL, "predicate column out of range");
       if (++depth > 16) HS_THROW(HS_EINVAL, "predicate too deep");
+      if (tm.op == HS_PRED_IN) {
+        const int32_t ct = index->cols[tm.col].type;
+        if (ct < HS_BOOL || ct > HS_INT64) HS_THROW(HS_EUNSUPPORTED, "IN is implemented for integer columns");
+        if (tm.lit_len < 0 || (tm.lit_len > 0 && !tm.lit_bytes)) HS_THROW(HS_EINVAL, "IN list missing");
+        pool_bytes = ((pool_bytes + 7) & ~(size_t)7) + (size_t)tm.lit_len * 8;
+      }
       if (hs_is_varlen(index->cols[tm.col].type) && tm.op <= HS_PRED_GE) {
         if (tm.lit_len < 0 || (tm.lit_len > 0 && !tm.lit_bytes)) HS_THROW(HS_EINVAL, "string literal missing");
         pool_bytes += (size_t)tm.lit_len;
@@ -290,7 +315,7 @@ extern "C" int32_t hs_filter_scan(hs_ctx* ctx, const hs_index_view* index, const
   KPred kp;
   memset(&kp, 0, sizeof kp);
   kp.nterms = pred->nterms;
-  std::vector<uint8_t> pool(pool_bytes + 1);
+  std::vector<uint8_t> pool(pool_bytes + 16);
   size_t at = 0;
   for (int t = 0; t < pred->nterms; t++) {
     const hs_pred_term& tm = pred->terms[t];
@@ -298,7 +323,17 @@ extern "C" int32_t hs_filter_scan(hs_ctx* ctx, const hs_index_view* index, const
     kp.t[t].col = tm.col;
     kp.t[t].lit_i64 = tm.lit_i64;
     kp.t[t].lit_f64 = tm.lit_f64;
-    if (tm.op <= HS_PRED_GE && hs_is_varlen(index->cols[tm.col].type)) {
+    if (tm.op == HS_PRED_IN) {
+      at = (at + 7) & ~(size_t)7;
+      kp.t[t].lit_off = (int32_t)at;
+      kp.t[t].lit_len = tm.lit_len;
+      if (tm.lit_len) {
+        int64_t* dst = (int64_t*)(pool.data() + at);
+        memcpy(dst, tm.lit_bytes, (size_t)tm.lit_len * 8);
+        std::sort(dst, dst + tm.lit_len);
+      }
+      at += (size_t)tm.lit_len * 8;
+    } else if (tm.op <= HS_PRED_GE && hs_is_varlen(index->cols[tm.col].type)) {
       kp.t[t].lit_off = (int32_t)at;
       kp.t[t].lit_len = tm.lit_len;
       if (tm.lit_len) memcpy(pool.data() + at, tm.lit_bytes, (size_t)tm.lit_len);

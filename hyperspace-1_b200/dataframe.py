@@ -167,8 +167,11 @@ class IndexScan:
     IndexHadoopFsRelation.scala:29-50). use_bucket_spec mirrors RuleUtils.scala:264-292."""
     node_name = "IndexScan"
 
-    def __init__(self, entry, use_bucket_spec):
+    def __init__(self, entry, use_bucket_spec, hybrid=None):
         self.entry, self.use_bucket_spec = entry, use_bucket_spec
+        # hybrid scan (RuleUtils.scala:307-450): source files appended since the index was built are indexed on
+        # the fly and merged in; rows of deleted source files are dropped through the lineage column
+        self.hybrid = hybrid or {}
         self.children = []
 
     def output(self):
@@ -176,7 +179,10 @@ class IndexScan:
         return list(props["indexed"]) + list(props["included"])
 
     def describe(self):
-        return f"Hyperspace(Type: CI, Name: {self.entry['name']}, LogVersion: {self.entry['id']})"
+        h = ""
+        if self.hybrid.get("appended") or self.hybrid.get("deleted_ids"):
+            h = f", HybridScan: +{len(self.hybrid.get('appended', []))} files -{len(self.hybrid.get('deleted_ids', []))} files"
+        return f"Hyperspace(Type: CI, Name: {self.entry['name']}, LogVersion: {self.entry['id']}{h})"
 
 
 class Filter:
@@ -307,6 +313,9 @@ DEFAULT_CONF = {
     "spark.hyperspace.index.numBuckets": "200",        # IndexConstants.scala:29-32
     "spark.hyperspace.index.lineage.enabled": "false",  # IndexConstants.scala:75-76
     "spark.hyperspace.index.optimize.fileSizeThreshold": str(256 * 1024 * 1024),  # IndexConstants.scala:86-87
+    "spark.hyperspace.index.hybridscan.enabled": "false",          # IndexConstants.scala:34-35
+    "spark.hyperspace.index.hybridscan.maxAppendedRatio": "0.3",   # IndexConstants.scala:43-45
+    "spark.hyperspace.index.hybridscan.maxDeletedRatio": "0.2",    # IndexConstants.scala:38-40
 }
 
 

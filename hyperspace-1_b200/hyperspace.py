@@ -7,9 +7,11 @@ latestStable. The compute inside op() is GpuIndexWriter (hs_build_index / hs_mer
 import os
 import shutil
 
+import numpy as np
 import pyarrow as pa
 
 from . import index_writer, log_entry as le
+from .index_writer import LINEAGE_COL
 from .dataframe import DataFrame, Relation, Scan, resolve_name
 from .index_config import IndexConfig
 from .native import HyperspaceException
@@ -79,18 +81,39 @@ class _CreateBase(_Action):
             raise HyperspaceException("Index config is not applicable to dataframe schema.")   # CreateAction.scala:52-54
         return indexed, included
 
-    def _write(self, relation, files, indexed, included, num_buckets, out_dir):
-        table = relation.read(columns=indexed + included, files=files)
-        written, stats = index_writer.build_and_write(self.session, table, indexed, included, num_buckets, out_dir)
+    def _write(self, relation, files, indexed, included, num_buckets, out_dir, lineage_ids=None):
+        """lineage_ids: {source file path: file id} — every row then carries the id of the file it came from in
+        a trailing _data_file_id column (CreateActionBase.scala:171-203: the reference joins input_file_name()
+        with a broadcast (path, id) table; here the id is attached while each file is read)."""
+        if lineage_ids is None:
+            table = relation.read(columns=indexed + included, files=files)
+            inc = list(included)
+        else:
+            parts = []
+            for f in (relation.files if files is None else files):
+                t = relation.read(columns=indexed + included, files=[f])
+                parts.append(t.append_column(LINEAGE_COL, pa.array(np.full(t.num_rows, lineage_ids[f], dtype=np.int64))))
+            table = pa.concat_tables(parts) if parts else relation.read(columns=indexed + included, files=[]).append_column(
+                LINEAGE_COL, pa.array([], type=pa.int64()))
+            inc = list(included) + [LINEAGE_COL]
+        written, stats = index_writer.build_and_write(self.session, table, indexed, inc, num_buckets, out_dir)
         self.stats = stats
         return written
 
     def _entry(self, name, indexed, included, relation, num_buckets, index_files, tracker, properties=None):
-        index_schema = pa.schema([relation.schema.field(c) for c in indexed + included])
+        properties = dict(properties or {})
+        fields = [relation.schema.field(c) for c in indexed + included]
+        if str(properties.get("lineage", "false")).lower() == "true":
+            fields.append(pa.field(LINEAGE_COL, pa.int64(), nullable=False))
+        index_schema = pa.schema(fields)
         src = relation.file_infos(tracker)
         idx = [le.file_info(f, tracker) for f in index_files]
         return le.make_entry(name, indexed, included, index_schema, num_buckets, idx, [relation.root], src,
-                             relation.schema, properties=properties or {})
+                             relation.schema, properties=properties)
+
+
+def _lineage_enabled(session):
+    return str(session.conf.get("spark.hyperspace.index.lineage.enabled", "false")).lower() == "true"
 
 
 class CreateAction(_CreateBase):
@@ -112,19 +135,44 @@ class CreateAction(_CreateBase):
             raise HyperspaceException(f"Another Index with name {self.config.indexName} already exists")
 
     def op(self):
-        self.files = self._write(self.relation, None, self.indexed, self.included, self.session.num_buckets(), self.out_dir)
+        self.tracker = le.FileIdTracker()
+        lineage_ids = None
+        if _lineage_enabled(self.session):
+            # source file ids start at 0 and are the ids the log entry records (IndexLogEntry.scala:617-686)
+            lineage_ids = {le.from_uri(f["name"]): f["id"] for f in self.relation.file_infos(self.tracker)}
+        self.files = self._write(self.relation, None, self.indexed, self.included, self.session.num_buckets(),
+                                 self.out_dir, lineage_ids)
 
     def log_entry(self):
-        tracker = le.FileIdTracker()
+        tracker = getattr(self, "tracker", None) or le.FileIdTracker()
+        props = {"lineage": "true"} if _lineage_enabled(self.session) else {}
         return self._entry(self.config.indexName, self.indexed, self.included, self.relation,
-                           self.session.num_buckets(), self.files, tracker)
+                           self.session.num_buckets(), self.files, tracker, props)
+
+
+def drop_deleted_rows(session, arrays, n_indexed, boff, names, deleted_ids):
+    """Rows of an index run minus those whose _data_file_id is one of deleted_ids: hs_filter_scan with
+    NOT (_data_file_id IN (...)) — rows keep their order, so every bucket stays sorted and only its boundaries
+    move (RefreshIncrementalAction.scala:73-95 writes the result without re-partitioning, for the same reason)."""
+    lin = names.index(LINEAGE_COL)
+    out = session.ctx.filter_scan(arrays, n_indexed, boff, [("in", lin, list(deleted_ids)), ("not",)],
+                                  list(range(len(names))))
+    nb = len(boff) - 1
+    if len(out[0]) == 0:
+        return out, np.zeros(nb + 1, dtype=np.int64)
+    ids = session.ctx.hash_bucket(out[:n_indexed], nb)
+    new_off = np.zeros(nb + 1, dtype=np.int64)
+    np.cumsum(np.bincount(ids, minlength=nb), out=new_off[1:])
+    return out, new_off
 
 
 class RefreshAction(_CreateBase):
-    """mode full: rebuild over the relation as it is now (RefreshAction.scala:41). mode incremental: index only
-    the appended source files into a new version directory and keep the old files, so that buckets end up with
-    several sorted files (RefreshIncrementalAction.scala:53-96, :129-144). Deleted source files need the lineage
-    column, which this build does not write."""
+    """mode full: rebuild over the relation as it is now (RefreshAction.scala:41). mode incremental
+    (RefreshIncrementalAction.scala:53-96, :129-144): appended source files are indexed into a new version
+    directory and the old files are kept, so that buckets end up with several sorted files; if source files were
+    deleted (needs the lineage column) the old index files are rewritten without their rows. mode quick
+    (RefreshQuickAction.scala): nothing is computed — the entry records which files were appended and deleted and
+    queries bridge the gap with hybrid scan."""
     transient, final = le.States.REFRESHING, le.States.ACTIVE
 
     def __init__(self, session, index_path, mode):
@@ -133,6 +181,7 @@ class RefreshAction(_CreateBase):
         self.prev = self.log.get_latest_log()
         self.out_dir = _next_version_dir(self.data)
         self.new_files = []
+        self.rewritten = False
 
     def validate(self):
         if self.prev is None or self.prev["state"] != le.States.ACTIVE:   # RefreshActionBase.scala:97-103
@@ -142,34 +191,75 @@ class RefreshAction(_CreateBase):
         props = self.prev["derivedDataset"]["properties"]
         self.indexed, self.included = list(props["columns"]["indexed"]), list(props["columns"]["included"])
         self.num_buckets = props["numBuckets"]                               # refresh keeps the original count
-        logged = {(f["name"], f["size"], f["modifiedTime"]) for f in le.content_files(rel["data"]["properties"]["content"])}
-        current = {(f["name"], f["size"], f["modifiedTime"]) for f in self.relation.file_infos()}
+        self.lineage = index_writer.has_lineage(self.prev)                   # ... and the lineage flag (:57-65)
+        self.logged = le.content_files(rel["data"]["properties"]["content"])
+        logged = {(f["name"], f["size"], f["modifiedTime"]) for f in self.logged}
+        self.current = self.relation.file_infos()
+        current = {(f["name"], f["size"], f["modifiedTime"]) for f in self.current}
         self.appended = sorted(le.from_uri(n) for n, _, _ in current - logged)   # RefreshActionBase.scala:142-147
         self.deleted = sorted(le.from_uri(n) for n, _, _ in logged - current)    # :112-117
-        if self.mode == "incremental":
-            if not self.appended and not self.deleted:
-                raise NoChangesException("Refresh incremental aborted as no source data change found.")
-            if self.deleted:
-                raise HyperspaceException("Index refresh (to handle deleted source data) is only supported on an "
-                                          "index with lineage.")            # RefreshIncrementalAction.scala:102-115
-        elif self.mode == "full":
-            if not self.appended and not self.deleted:
-                raise NoChangesException("Refresh full aborted as no source data change found.")
+        self.deleted_infos = [f for f in self.logged if (f["name"], f["size"], f["modifiedTime"]) not in current]
+        self.appended_infos = [f for f in self.current if (f["name"], f["size"], f["modifiedTime"]) not in logged]
+        if not self.appended and not self.deleted:
+            raise NoChangesException(f"Refresh {self.mode} aborted as no source data change found.")
+        if self.mode in ("incremental", "quick") and self.deleted and not self.lineage:
+            raise HyperspaceException("Index refresh (to handle deleted source data) is only supported on an "
+                                      "index with lineage.")            # RefreshIncrementalAction.scala:102-115
+
+    def _tracker(self):
+        """File ids survive a refresh: the lineage column refers to them (IndexLogEntry.scala:617-686)."""
+        t = le.FileIdTracker()
+        for f in self.logged:
+            t.add_known(f["name"], f["size"], f["modifiedTime"], f["id"])
+        for f in le.content_files(self.prev["content"]):
+            t.add_known(f["name"], f["size"], f["modifiedTime"], f["id"])
+        return t
 
     def op(self):
-        files = self.appended if self.mode == "incremental" else None
-        self.new_files = self._write(self.relation, files, self.indexed, self.included, self.num_buckets, self.out_dir)
+        self.tracker = self._tracker()
+        if self.mode == "quick":
+            return
+        lineage_ids = None
+        if self.lineage:
+            lineage_ids = {le.from_uri(f["name"]): f["id"] for f in self.relation.file_infos(self.tracker)}
+        if self.mode == "full":
+            self.new_files = self._write(self.relation, None, self.indexed, self.included, self.num_buckets,
+                                         self.out_dir, lineage_ids)
+            return
+        if self.deleted:
+            runs, names, _ = index_writer.read_index(self.prev)
+            ids = [f["id"] for f in self.deleted_infos]
+            for arrays, boff in runs:
+                kept, koff = drop_deleted_rows(self.session, arrays, len(self.indexed), boff, names, ids)
+                files, _ = index_writer.write_buckets(kept, names, koff, self.out_dir)
+                self.new_files += files
+            self.rewritten = True
+        if self.appended:
+            self.new_files += self._write(self.relation, self.appended, self.indexed, self.included, self.num_buckets,
+                                          self.out_dir, lineage_ids)
 
     def log_entry(self):
-        tracker = le.FileIdTracker()
+        tracker = getattr(self, "tracker", None) or self._tracker()
+        props = self.prev["derivedDataset"]["properties"]["properties"]
+        if self.mode == "quick":
+            # same index files; the source relation keeps its logged content and gains the update lists, the
+            # fingerprint becomes that of the files as they are now (RefreshQuickAction.scala: logEntry)
+            e = self._entry(self.prev["name"], self.indexed, self.included, self.relation, self.num_buckets, [],
+                            tracker, props)
+            e["content"] = self.prev["content"]
+            rel = e["source"]["plan"]["properties"]["relations"][0]
+            rel["data"]["properties"]["content"] = self.prev["source"]["plan"]["properties"]["relations"][0]["data"][
+                "properties"]["content"]
+            rel["data"]["properties"]["update"] = {
+                "appendedFiles": le.content_of([dict(f, id=tracker.add_file(f["name"], f["size"], f["modifiedTime"]))
+                                                for f in self.appended_infos]) if self.appended_infos else None,
+                "deletedFiles": le.content_of(self.deleted_infos) if self.deleted_infos else None}
+            return e
         keep = []
-        if self.mode == "incremental":
-            for f in le.content_files(self.prev["content"]):
-                tracker.add_known(f["name"], f["size"], f["modifiedTime"], f["id"])
-                keep.append(le.from_uri(f["name"]))
-        e = self._entry(self.prev["name"], self.indexed, self.included, self.relation, self.num_buckets,
-                        keep + self.new_files, tracker, self.prev["derivedDataset"]["properties"]["properties"])
-        return e
+        if self.mode == "incremental" and not self.rewritten:
+            keep = [le.from_uri(f["name"]) for f in le.content_files(self.prev["content"])]
+        return self._entry(self.prev["name"], self.indexed, self.included, self.relation, self.num_buckets,
+                           keep + self.new_files, tracker, props)
 
 
 class OptimizeAction(_CreateBase):
@@ -274,8 +364,6 @@ class Hyperspace:
     def refreshIndex(self, indexName, mode="full"):
         if mode.lower() not in REFRESH_MODES:
             raise HyperspaceException(f"Unsupported refresh mode '{mode}' found.")
-        if mode.lower() == "quick":
-            raise HyperspaceException("quick refresh relies on hybrid scan, which this build does not have")
         a = RefreshAction(self.session, self._index_path(indexName), mode.lower())
         a.run()
         return a.stats

@@ -13,6 +13,18 @@ import pyarrow.parquet as pq
 
 from . import log_entry as le
 
+LINEAGE_COL = "_data_file_id"      # IndexConstants.scala:73 (DATA_FILE_NAME_ID)
+
+
+def has_lineage(entry):
+    return str(entry["derivedDataset"]["properties"]["properties"].get("lineage", "false")).lower() == "true"
+
+
+def index_column_names(entry):
+    """indexed ++ included (++ _data_file_id when the index carries lineage): the columns of its files."""
+    c = entry["derivedDataset"]["properties"]["columns"]
+    return list(c["indexed"]) + list(c["included"]) + ([LINEAGE_COL] if has_lineage(entry) else [])
+
 
 def write_buckets(columns, names, bucket_offsets, out_dir, task_of_bucket=None, append=False):
     """Write rows [off[b], off[b+1]) of every non-empty bucket b to
@@ -51,7 +63,7 @@ def read_index(entry, columns=None, files=None):
     is one run and an incrementally refreshed index is several."""
     props = entry["derivedDataset"]["properties"]
     nb = props["numBuckets"]
-    names = list(props["columns"]["indexed"]) + list(props["columns"]["included"])
+    names = index_column_names(entry)
     want = names if columns is None else [n for n in names if n in columns]
     infos = le.content_files(entry["content"]) if files is None else files
     per_bucket = {}

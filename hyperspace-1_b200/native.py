@@ -98,7 +98,7 @@ class IndexView:
 
 def make_predicate(terms):
     """postfix list of tuples -> (hs_predicate, keepalive)."""
-    ops = {"eq": 1, "ne": 2, "lt": 3, "le": 4, "gt": 5, "ge": 6, "is_null": 7, "is_not_null": 8,
+    ops = {"eq": 1, "ne": 2, "lt": 3, "le": 4, "gt": 5, "ge": 6, "is_null": 7, "is_not_null": 8, "in": 9,
            "and": 16, "or": 17, "not": 18}
     keep = []
     arr = (abi.hs_pred_term * max(len(terms), 1))()
@@ -108,6 +108,12 @@ def make_predicate(terms):
         tm.col = t[1] if len(t) > 1 else 0
         if len(t) > 2:
             lit = t[2]
+            if t[0] == "in":      # list of integers -> int64 array behind lit_bytes, lit_len = count
+                vals = np.ascontiguousarray(list(lit), dtype=np.int64)
+                keep.append(vals)
+                tm.lit_bytes = C.cast(vals.ctypes.data, C.c_char_p)
+                tm.lit_len = len(vals)
+                continue
             if isinstance(lit, str):
                 lit = lit.encode("utf-8")
             if isinstance(lit, (bytes, bytearray)):

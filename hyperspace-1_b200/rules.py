@@ -29,6 +29,46 @@ def _signature_matches(entry, relation):
     return any(s["provider"] == le.SIGNATURE_PROVIDER and s["value"] == now for s in sigs)
 
 
+def _applicable(session, entry, relation):
+    """None if the index cannot serve the relation as it is now, else the hybrid-scan work it needs
+    ({} = none): {"appended": [paths], "deleted_ids": [file ids]}.
+    * the signature matches (RuleUtils.scala:61-76) -> {}, or, after a quick refresh, the update lists the
+      entry recorded (IndexLogEntry.hasSourceUpdate -> transformPlanToUseHybridScan, RuleUtils.scala:236-262);
+    * otherwise, with spark.hyperspace.index.hybridscan.enabled, the index is a candidate if it shares files
+      with the relation, deleted files are covered by lineage, and the appended / deleted bytes stay below the
+      configured ratios (RuleUtils.scala:84-147)."""
+    rel = entry["source"]["plan"]["properties"]["relations"][0]["data"]["properties"]
+    if _signature_matches(entry, relation):
+        upd = rel.get("update") or {}
+        hybrid = {}
+        if upd.get("appendedFiles"):
+            hybrid["appended"] = [le.from_uri(f["name"]) for f in le.content_files(upd["appendedFiles"])]
+        if upd.get("deletedFiles"):
+            hybrid["deleted_ids"] = [f["id"] for f in le.content_files(upd["deletedFiles"])]
+        return hybrid
+    if str(session.conf.get("spark.hyperspace.index.hybridscan.enabled", "false")).lower() != "true":
+        return None
+    from .index_writer import has_lineage
+    logged = le.content_files(rel["content"])
+    key = lambda f: (f["name"], f["size"], f["modifiedTime"])
+    now = relation.file_infos()
+    lset, nset = {key(f) for f in logged}, {key(f) for f in now}
+    common = lset & nset
+    if not common:
+        return None
+    deleted = [f for f in logged if key(f) not in nset]
+    appended = [f for f in now if key(f) not in lset]
+    if deleted and not has_lineage(entry):
+        return None
+    common_bytes = sum(f["size"] for f in logged if key(f) in common)
+    app_bytes, del_bytes = sum(f["size"] for f in appended), sum(f["size"] for f in deleted)
+    max_app = float(session.conf["spark.hyperspace.index.hybridscan.maxAppendedRatio"])
+    max_del = float(session.conf["spark.hyperspace.index.hybridscan.maxDeletedRatio"])
+    if app_bytes > max_app * (common_bytes + app_bytes) or del_bytes > max_del * (common_bytes + del_bytes):
+        return None
+    return {"appended": [le.from_uri(f["name"]) for f in appended], "deleted_ids": [f["id"] for f in deleted]}
+
+
 def _index_columns(entry):
     c = entry["derivedDataset"]["properties"]["columns"]
     return list(c["indexed"]), list(c["included"])
@@ -71,13 +111,16 @@ def _filter_rule(session, plan):
             continue
         if not needed <= allc:
             continue
-        if not _signature_matches(e, scan.relation):
+        hybrid = _applicable(session, e, scan.relation)
+        if hybrid is None:
             continue
-        cands.append(e)
+        cands.append((e, hybrid))
     if not cands:
         return None
-    best = cands[0]                                                 # FilterIndexRanker.rank(...).head
-    node = Filter(IndexScan(best, use_bucket_spec=False), flt.pred)
+    best, hybrid = cands[0]                                         # FilterIndexRanker.rank(...).head
+    if hybrid:
+        hybrid = dict(hybrid, relation=scan.relation)
+    node = Filter(IndexScan(best, use_bucket_spec=False, hybrid=hybrid), flt.pred)
     return Project(node, out_cols) if proj is not None else Project(node, scan.output())
 
 
@@ -103,8 +146,11 @@ def _join_rule(session, plan):
                 continue
             if not need <= {c.lower() for c in indexed + included}:
                 continue
-            if not _signature_matches(e, scan.relation):
+            hybrid = _applicable(session, e, scan.relation)
+            if hybrid is None:
                 continue
+            e = dict(e)
+            e["__hybrid"] = dict(hybrid, relation=scan.relation) if hybrid else {}
             res.append(e)
         return res
     lc, rc = usable(lscan, plan.lkeys, lout), usable(rscan, plan.rkeys, rout)
@@ -129,8 +175,8 @@ def _join_rule(session, plan):
         return None   # Spark would re-shuffle one side; not built
     ai, _ = _index_columns(a)
     lmap = {k.lower(): v for k, v in zip(plan.lkeys, plan.rkeys)}
-    j = Join(IndexScan(a, True), IndexScan(b, True), ai, [resolve_name(lmap[c.lower()], _index_columns(b)[0]) for c in ai],
-             plan.how)
+    j = Join(IndexScan(a, True, a.get("__hybrid")), IndexScan(b, True, b.get("__hybrid")), ai,
+             [resolve_name(lmap[c.lower()], _index_columns(b)[0]) for c in ai], plan.how)
     j.left_out, j.right_out = list(lout), ([] if plan.how in ("left_semi", "left_anti") else list(rout))
     return j
 
@@ -192,18 +238,40 @@ def plan_string(plan, depth=0):
     return f"{pad}{plan}\n"
 
 
-def _single_run(session, entry, columns=None):
+def _single_run(session, entry, columns=None, hybrid=None):
     """All files of an index as ONE sorted run per bucket; several files per bucket are merged on the GPU
-    (what Spark does with a per-side SortExec, E2EHyperspaceRulesTest.scala:474-478)."""
-    from .index_writer import read_index
+    (what Spark does with a per-side SortExec, E2EHyperspaceRulesTest.scala:474-478). With hybrid scan
+    (RuleUtils.scala:307-450): rows of deleted source files leave through NOT (_data_file_id IN ids), appended
+    source files are indexed on the fly with the index's bucket count (the reference injects a shuffle,
+    RuleUtils.scala:519-578) and merged bucket by bucket (BucketUnionExec.scala:52-121). The lineage column is
+    not part of the result."""
+    from .hyperspace import drop_deleted_rows
+    from .index_writer import LINEAGE_COL, read_index
     indexed, included = _index_columns(entry)
     runs, names, _ = read_index(entry)
     nb = entry["derivedDataset"]["properties"]["numBuckets"]
-    if not runs:
-        return None, names, np.zeros(nb + 1, dtype=np.int64)
-    if len(runs) == 1:
-        return runs[0][0], names, runs[0][1]
-    arrays, boff = session.ctx.merge_runs([(a, len(indexed), off) for a, off in runs if a is not None])
+    nk = len(indexed)
+    hybrid = hybrid or {}
+    if len(runs) > 1:
+        arrays, boff = session.ctx.merge_runs([(a, nk, off) for a, off in runs if a is not None])
+    elif runs:
+        arrays, boff = runs[0]
+    else:
+        arrays, boff = None, np.zeros(nb + 1, dtype=np.int64)
+    if arrays is not None and hybrid.get("deleted_ids"):
+        arrays, boff = drop_deleted_rows(session, arrays, nk, boff, names, hybrid["deleted_ids"])
+    if LINEAGE_COL in names:
+        if arrays is not None:
+            arrays = [a for a, n in zip(arrays, names) if n != LINEAGE_COL]
+        names = [n for n in names if n != LINEAGE_COL]
+    if hybrid.get("appended"):
+        t = hybrid["relation"].read(columns=names, files=hybrid["appended"])
+        cols = [t[c].combine_chunks() for c in names]
+        new, noff = session.ctx.build_index(cols, nk, nb)
+        if arrays is None:
+            arrays, boff = new, noff
+        else:
+            arrays, boff = session.ctx.merge_runs([(arrays, nk, boff), (new, nk, noff)])
     return arrays, names, boff
 
 
@@ -216,7 +284,7 @@ def execute(session, plan):
     if isinstance(plan, Filter):
         if isinstance(plan.child, IndexScan):
             entry = plan.child.entry
-            arrays, names, boff = _single_run(session, entry)
+            arrays, names, boff = _single_run(session, entry, hybrid=plan.child.hybrid)
             if arrays is None:
                 return pa.table({n: pa.array([]) for n in names})
             idx = {n.lower(): i for i, n in enumerate(names)}
@@ -228,8 +296,8 @@ def execute(session, plan):
         return t.filter(expr_to_arrow(plan.pred, lambda n: resolve_name(n, t.column_names)))
     if isinstance(plan, Join):
         if isinstance(plan.left, IndexScan):
-            la, ln, lo = _single_run(session, plan.left.entry)
-            ra, rn, ro = _single_run(session, plan.right.entry)
+            la, ln, lo = _single_run(session, plan.left.entry, hybrid=plan.left.hybrid)
+            ra, rn, ro = _single_run(session, plan.right.entry, hybrid=plan.right.hybrid)
             lout = [ln.index(resolve_name(c, ln)) for c in plan.left_out]
             rout = [rn.index(resolve_name(c, rn)) for c in plan.right_out]
             nk = len(_index_columns(plan.left.entry)[0])
@@ -254,7 +322,7 @@ def execute(session, plan):
             return j.select(names[: lt.num_columns])
         return j.select(names)
     if isinstance(plan, IndexScan):
-        arrays, names, _ = _single_run(session, plan.entry)
+        arrays, names, _ = _single_run(session, plan.entry, hybrid=plan.hybrid)
         return pa.table(arrays, names=names)
     raise TypeError(plan)
 

@@ -107,6 +107,10 @@ typedef enum hs_pred_op {
   HS_PRED_EQ = 1, HS_PRED_NE = 2, HS_PRED_LT = 3, HS_PRED_LE = 4,
   HS_PRED_GT = 5, HS_PRED_GE = 6,          /* column <op> literal          */
   HS_PRED_IS_NULL = 7, HS_PRED_IS_NOT_NULL = 8,
+  HS_PRED_IN = 9,  /* integer column IN (list): lit_bytes points at lit_len int64 values (host memory, any order).
+                    * NOT IN = IN followed by NOT. This is the lineage filter of hybrid scan and of an incremental
+                    * refresh after source files were deleted: NOT (_data_file_id IN (ids of the deleted files)),
+                    * HS/index/rules/RuleUtils.scala:402-425, HS/actions/RefreshIncrementalAction.scala:73-95 */
   HS_PRED_AND = 16, HS_PRED_OR = 17, HS_PRED_NOT = 18 /* pop operands      */
 } hs_pred_op;
 
@@ -115,8 +119,8 @@ typedef struct hs_pred_term {
   int32_t col;           /* column index in the view (leaf ops) */
   int64_t lit_i64;       /* literal for BOOL/INT8..INT64 columns */
   double lit_f64;        /* literal for FLOAT32/FLOAT64 columns */
-  const char* lit_bytes; /* literal for UTF8/BINARY columns (host memory) */
-  int32_t lit_len;
+  const char* lit_bytes; /* literal for UTF8/BINARY columns; the int64 list of HS_PRED_IN (host memory) */
+  int32_t lit_len;       /* bytes of the string literal; number of values of HS_PRED_IN */
   int32_t reserved;
 } hs_pred_term;
 

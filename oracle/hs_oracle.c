@@ -348,6 +348,21 @@ static inline void eval_leaf(const hs_column* c, int64_t i, const hs_pred_term* 
   if (t->op == HS_PRED_IS_NULL) { *known = 1; *val = !is_valid(c, i); return; }
   if (t->op == HS_PRED_IS_NOT_NULL) { *known = 1; *val = is_valid(c, i); return; }
   if (!is_valid(c, i)) { *known = 0; *val = 0; return; }
+  if (t->op == HS_PRED_IN) {   /* SQL IN over a literal list without NULLs: TRUE if any element equals the cell */
+    int64_t x = 0;
+    switch (c->type) {
+      case HS_BOOL: x = (((const uint8_t*)c->data)[i >> 3] >> (i & 7)) & 1; break;
+      case HS_INT8: x = ((const int8_t*)c->data)[i]; break;
+      case HS_INT16: x = ((const int16_t*)c->data)[i]; break;
+      case HS_INT32: x = ((const int32_t*)c->data)[i]; break;
+      default: x = ((const int64_t*)c->data)[i]; break;
+    }
+    const int64_t* list = (const int64_t*)t->lit_bytes;
+    int hit = 0;
+    for (int32_t k = 0; k < t->lit_len && !hit; k++) hit = list[k] == x;
+    *known = 1; *val = hit;
+    return;
+  }
   int cmp = 0;
   switch (c->type) {
     case HS_BOOL: { int64_t x = (((const uint8_t*)c->data)[i >> 3] >> (i & 7)) & 1; cmp = (x > t->lit_i64) - (x < t->lit_i64); break; }

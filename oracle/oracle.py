@@ -145,7 +145,7 @@ def take_or_null(col, idx):
 class Predicate:
     """Builds an hs_predicate from a postfix list of tuples:
     ("eq"|"ne"|"lt"|"le"|"gt"|"ge", col, literal) | ("is_null"|"is_not_null", col) | ("and",)|("or",)|("not",)"""
-    OPS = {"eq": 1, "ne": 2, "lt": 3, "le": 4, "gt": 5, "ge": 6, "is_null": 7, "is_not_null": 8,
+    OPS = {"eq": 1, "ne": 2, "lt": 3, "le": 4, "gt": 5, "ge": 6, "is_null": 7, "is_not_null": 8, "in": 9,
            "and": 16, "or": 17, "not": 18}
 
     def __init__(self, terms):
@@ -158,6 +158,12 @@ class Predicate:
             tm.col = t[1] if len(t) > 1 else 0
             if len(t) > 2:
                 lit = t[2]
+                if t[0] == "in":      # list of integers -> int64 array behind lit_bytes, lit_len = count
+                    vals = np.ascontiguousarray(list(lit), dtype=np.int64)
+                    self._keep.append(vals)
+                    tm.lit_bytes = C.cast(vals.ctypes.data, C.c_char_p)
+                    tm.lit_len = len(vals)
+                    continue
                 if isinstance(lit, str):
                     lit = lit.encode("utf-8")
                 if isinstance(lit, (bytes, bytearray)):

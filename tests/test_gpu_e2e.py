@@ -180,11 +180,114 @@ def test_incremental_refresh_then_join_then_optimize(env):
     # full refresh after a delete in the source
     os.remove(tmp / "lineitem" / "part-1.parquet")
     with pytest.raises(Exception):
-        hs.refreshIndex("liIndex", "incremental")     # deletes need lineage
+        hs.refreshIndex("liIndex", "incremental")     # deletes need lineage (this index was built without)
     hs.cancel("liIndex") if hs.index("liIndex")["state"] != "ACTIVE" else None
     hs.refreshIndex("liIndex", "full")
     li3 = s.read_parquet(str(tmp / "lineitem"))
     assert _verify_index_usage(s, q(li3, od), ["liIndex", "oIndex"]).num_rows == n * 9 // 10
+
+
+def _lineitem_files(tmp, n_orders=4000, parts=4):
+    lcols, keys = lineitem(n_orders)
+    lt = pa.table(lcols, names=["l_orderkey", "l_extendedprice", "l_discount"])
+    os.makedirs(tmp / "lineitem")
+    os.makedirs(tmp / "orders")
+    step = lt.num_rows // parts
+    for i in range(parts):
+        pq.write_table(lt.slice(i * step, step if i < parts - 1 else lt.num_rows - i * step),
+                       tmp / "lineitem" / f"part-{i}.parquet")
+    pq.write_table(pa.table(orders(keys), names=["o_orderkey", "o_totalprice"]), tmp / "orders" / "part-0.parquet")
+    return lt, step
+
+
+def test_lineage_column_and_refresh_after_deletes(env):
+    """spark.hyperspace.index.lineage.enabled: every index row carries the id of its source file
+    (CreateIndexTest.scala:159-243: schema = indexed ++ included ++ _data_file_id, ids from 0); an incremental
+    refresh after a source file was deleted rewrites the index without that file's rows
+    (RefreshIndexTest.scala:58-110) — bucket files stay sorted and in their buckets."""
+    from hyperspace_1_b200 import Hyperspace, IndexConfig, log_entry as le
+    s, tmp = env
+    s.conf["spark.hyperspace.index.numBuckets"] = "8"
+    s.conf["spark.hyperspace.index.lineage.enabled"] = "true"
+    lt, step = _lineitem_files(tmp)
+    hs = Hyperspace(s)
+    li = s.read_parquet(str(tmp / "lineitem"))
+    hs.createIndex(li, IndexConfig("liIndex", ["l_orderkey"], ["l_extendedprice"]))
+    e = hs.index("liIndex")
+    assert e["derivedDataset"]["properties"]["properties"]["lineage"] == "true"
+    assert e["derivedDataset"]["properties"]["columns"] == {"indexed": ["l_orderkey"], "included": ["l_extendedprice"]}
+    src = {os.path.basename(f["name"]): f["id"] for f in
+           le.content_files(e["source"]["plan"]["properties"]["relations"][0]["data"]["properties"]["content"])}
+    assert sorted(src.values()) == [0, 1, 2, 3]
+    files = [le.from_uri(f["name"]) for f in le.content_files(e["content"])]
+    t = pa.concat_tables([pq.ParquetFile(f).read() for f in files])
+    assert t.column_names == ["l_orderkey", "l_extendedprice", "_data_file_id"]
+    for name, fid in src.items():      # the rows tagged with a file id are exactly that file's rows
+        want = pq.ParquetFile(tmp / "lineitem" / name).read()
+        got = t.filter(pa.compute.equal(t["_data_file_id"], fid))
+        assert sorted(got["l_orderkey"].to_pylist()) == sorted(want["l_orderkey"].to_pylist())
+    q = lambda df: df.filter("l_orderkey >= 0").select("l_orderkey", "l_extendedprice")
+    _verify_index_usage(s, q(li), ["liIndex"])
+    # delete one source file, append another: incremental refresh = old rows minus the deleted file + the new rows
+    os.remove(tmp / "lineitem" / "part-1.parquet")
+    extra = lt.slice(0, 500)
+    pq.write_table(extra, tmp / "lineitem" / "part-9.parquet")
+    hs.refreshIndex("liIndex", "incremental")
+    e2 = hs.index("liIndex")
+    files = [le.from_uri(f["name"]) for f in le.content_files(e2["content"])]
+    assert {os.path.basename(os.path.dirname(f)) for f in files} == {"v__=1"}     # old files were rewritten
+    t2 = pa.concat_tables([pq.ParquetFile(f).read() for f in files])
+    assert src["part-1.parquet"] not in set(t2["_data_file_id"].to_pylist())
+    assert t2.num_rows == lt.num_rows - step + 500
+    for f in files:
+        k = pq.ParquetFile(f).read()["l_orderkey"].to_numpy()
+        assert (np.diff(k) >= 0).all()
+    src2 = {os.path.basename(f["name"]): f["id"] for f in
+            le.content_files(e2["source"]["plan"]["properties"]["relations"][0]["data"]["properties"]["content"])}
+    assert all(src2[k] == v for k, v in src.items() if k in src2) and src2["part-9.parquet"] not in src.values()
+    li2 = s.read_parquet(str(tmp / "lineitem"))
+    got = _verify_index_usage(s, q(li2), ["liIndex"])
+    assert got.num_rows == t2.num_rows
+
+
+@pytest.mark.parametrize("mode", ["hybrid_conf", "quick_refresh"])
+def test_hybrid_scan_appended_and_deleted_files(env, mode):
+    """HybridScanSuite.scala:186-307,371-663: with source files appended and deleted after the build, queries
+    still use the index — appended files are bucketed on the fly and merged bucket by bucket, rows of deleted
+    files are filtered through the lineage column — and return what the plain query returns. Reached either
+    through spark.hyperspace.index.hybridscan.enabled or after refreshIndex(name, "quick")."""
+    from hyperspace_1_b200 import Hyperspace, IndexConfig
+    s, tmp = env
+    s.conf["spark.hyperspace.index.numBuckets"] = "8"
+    s.conf["spark.hyperspace.index.lineage.enabled"] = "true"
+    lt, step = _lineitem_files(tmp, parts=8)
+    hs = Hyperspace(s)
+    li, od = s.read_parquet(str(tmp / "lineitem")), s.read_parquet(str(tmp / "orders"))
+    hs.createIndex(li, IndexConfig("liIndex", ["l_orderkey"], ["l_extendedprice", "l_discount"]))
+    hs.createIndex(od, IndexConfig("oIndex", ["o_orderkey"], ["o_totalprice"]))
+    os.remove(tmp / "lineitem" / "part-3.parquet")
+    pq.write_table(lt.slice(10, 700), tmp / "lineitem" / "part-new.parquet")
+    li2 = s.read_parquet(str(tmp / "lineitem"))
+    fq = li2.filter("l_orderkey >= 1000").select("l_orderkey", "l_discount")
+    jq = li2.join(od, li2["l_orderkey"] == od["o_orderkey"]).select("l_orderkey", "l_extendedprice", "o_totalprice")
+    s.enable_hyperspace()
+    assert "liIndex" not in fq.explain_string()          # signature mismatch and no hybrid scan: index unused
+    if mode == "hybrid_conf":
+        s.conf["spark.hyperspace.index.hybridscan.enabled"] = "true"
+    else:
+        hs.refreshIndex("liIndex", "quick")
+        e = hs.index("liIndex")
+        upd = e["source"]["plan"]["properties"]["relations"][0]["data"]["properties"]["update"]
+        assert upd["appendedFiles"] is not None and upd["deletedFiles"] is not None
+        assert sorted(os.listdir(tmp / "indexes" / "liIndex")) == ["_hyperspace_log", "v__=0"]   # no data written
+    assert "HybridScan: +1 files -1 files" in fq.explain_string()
+    got = _verify_index_usage(s, fq, ["liIndex"])
+    assert got.num_rows > 0
+    got = _verify_index_usage(s, jq, ["liIndex", "oIndex"])
+    assert got.num_rows == lt.num_rows - step + 700
+    if mode == "hybrid_conf":        # too much appended data: the index is not a candidate any more
+        s.conf["spark.hyperspace.index.hybridscan.maxAppendedRatio"] = "0.01"
+        assert "liIndex" not in fq.explain_string()
 
 
 def test_lifecycle_states(env):

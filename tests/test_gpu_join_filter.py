@@ -216,6 +216,9 @@ def test_filter_predicates(ctx, oracle):
         [("eq", 3, probe)],
         [("ge", 3, "m"), ("is_not_null", 0), ("and",), ("lt", 2, 0.03), ("or",)],
         [("ne", 2, 0.05), ("is_null", 3), ("and",)],
+        [("in", 0, [k, int(keys[5]), -7, int(keys[200])])],               # IN list (the lineage filter's op)
+        [("in", 0, [k, int(keys[5])]), ("not",)],                           # NOT IN: NULL keys stay out (unknown)
+        [("in", 0, []), ("not",), ("gt", 1, 90000.0), ("and",)],
     ]
     for p in preds:
         fg = ctx.filter_scan(got, 1, boff, p, [0, 1, 3])
@@ -234,6 +237,7 @@ def test_filter_packed_outputs_keep_row_order(ctx, oracle):
         k = int(keys[len(keys) // 2])
         for p in ([("ge", 0, k)], [("eq", 0, k)], [("lt", 1, 30000.0), ("ge", 2, 0.05), ("and",)],
                   [("lt", 0, -1)], [("ge", 0, -1)], [("eq", 0, k), ("not",)],
+                  [("in", 0, [int(x) for x in keys[::7]])], [("in", 0, [int(x) for x in keys[::3]]), ("not",)],
                   [("gt", 2, 0.02), ("le", 0, k), ("or",), ("ne", 1, 0.0), ("and",)]):
             fg = ctx.filter_scan(got, 1, boff, p, [2, 0, 1])
             idx = pa.array(oracle.filter_rows(got, p))
