@@ -588,8 +588,6 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
   if (join_type < HS_JOIN_INNER || join_type > HS_JOIN_LEFT_ANTI) HS_THROW(HS_EINVAL, "unknown join type %d", join_type);
   if ((join_type == HS_JOIN_LEFT_SEMI || join_type == HS_JOIN_LEFT_ANTI) && n_right_out != 0)
     HS_THROW(HS_EINVAL, "semi and anti joins return left columns only");
-  if (left->num_buckets != right->num_buckets)
-    HS_THROW(HS_EUNSUPPORTED, "indexes with different bucket counts (Spark would re-shuffle one side)");
   if (left->n_indexed != right->n_indexed) HS_THROW(HS_EINVAL, "indexes differ in number of indexed columns");
   if (n_left_out < 0 || n_right_out < 0 || n_left_out + n_right_out <= 0) HS_THROW(HS_EINVAL, "no output columns");
   for (int i = 0; i < n_left_out; i++)
@@ -597,7 +595,9 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
   for (int i = 0; i < n_right_out; i++)
     if (right_out[i] < 0 || right_out[i] >= right->ncols) HS_THROW(HS_EINVAL, "right output column out of range");
   hs_stages_reset(ctx);
-  const int nk = left->n_indexed, nb = left->num_buckets;
+  const int nk = left->n_indexed;
+  // the bucket count of the join: when the counts differ, that of the side with more rows (see below)
+  int nb = left->num_buckets;
   std::vector<DevCol> lc, rc;
   {
     Stage s(ctx, "h2d");
@@ -607,9 +607,35 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
   for (int k = 0; k < nk; k++)
     if (lc[k].type != rc[k].type) HS_THROW(HS_EUNSUPPORTED, "join key %d differs in type between the indexes", k);
   const int64_t nl = lc[0].length, nr = rc[0].length;
+  // Different bucket counts (JoinIndexRule accepts such a pair, JoinIndexRule.scala:515-516; Spark then
+  // re-shuffles one side): the side with fewer rows is re-bucketed here to the other side's count — the same
+  // hash + scatter + sort as a build, on the fly — and the join runs bucket by bucket as usual.
+  std::vector<OutCol> rebuilt;
+  std::vector<int64_t> rebuilt_off;
+  const int64_t* lboff = left->bucket_offsets;
+  const int64_t* rboff = right->bucket_offsets;
+  if (left->num_buckets != right->num_buckets) {
+    const bool redo_left = nl < nr;
+    std::vector<DevCol>& side = redo_left ? lc : rc;
+    const int32_t target = redo_left ? right->num_buckets : left->num_buckets;
+    hs_build_core(ctx, side, nk, target, 0, target, rebuilt, rebuilt_off, nullptr);
+    for (size_t i = 0; i < side.size(); i++) {
+      DevCol v;
+      v.type = rebuilt[i].type;
+      v.length = rebuilt[i].length;
+      v.null_count = rebuilt[i].null_count;
+      v.validity = rebuilt[i].validity.p && rebuilt[i].null_count ? rebuilt[i].validity.as<uint8_t>() : nullptr;
+      v.offsets = rebuilt[i].offsets.as<int32_t>();
+      v.data = rebuilt[i].data.p;
+      v.data_bytes = rebuilt[i].data_bytes;
+      side[i] = std::move(v);
+    }
+    (redo_left ? lboff : rboff) = rebuilt_off.data();
+    nb = target;
+  }
   DBuf loff, roff;
-  hs_offsets_to_device(ctx, left->bucket_offsets, nb, nl, loff);
-  hs_offsets_to_device(ctx, right->bucket_offsets, nb, nr, roff);
+  hs_offsets_to_device(ctx, lboff, nb, nl, loff);
+  hs_offsets_to_device(ctx, rboff, nb, nr, roff);
   JoinSide L{hs_make_keyspec(lc, nk), loff.as<uint32_t>()};
   JoinSide R{hs_make_keyspec(rc, nk), roff.as<uint32_t>()};
 
@@ -666,10 +692,10 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
     std::vector<uint32_t> tb, ts, tl, first_tile((size_t)nb + 1);
     for (int b = 0; b < nb; b++) {
       first_tile[b] = (uint32_t)tb.size();
-      for (int64_t a = left->bucket_offsets[b]; a < left->bucket_offsets[b + 1]; a += JT) {
+      for (int64_t a = lboff[b]; a < lboff[b + 1]; a += JT) {
         tb.push_back((uint32_t)b);
         ts.push_back((uint32_t)a);
-        tl.push_back((uint32_t)std::min<int64_t>(JT, left->bucket_offsets[b + 1] - a));
+        tl.push_back((uint32_t)std::min<int64_t>(JT, lboff[b + 1] - a));
       }
     }
     first_tile[nb] = (uint32_t)tb.size();

@@ -171,8 +171,7 @@ def _join_rule(session, plan):
         nb = p[1]["derivedDataset"]["properties"]["numBuckets"]
         return (0 if na == nb else 1, -max(na, nb))
     a, b = sorted(pairs, key=rank)[0]
-    if a["derivedDataset"]["properties"]["numBuckets"] != b["derivedDataset"]["properties"]["numBuckets"]:
-        return None   # Spark would re-shuffle one side; not built
+    # different bucket counts are fine: hs_join_bucketed re-buckets the smaller side (Spark re-shuffles one)
     ai, _ = _index_columns(a)
     lmap = {k.lower(): v for k, v in zip(plan.lkeys, plan.rkeys)}
     j = Join(IndexScan(a, True, a.get("__hybrid")), IndexScan(b, True, b.get("__hybrid")), ai,

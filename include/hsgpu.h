@@ -224,7 +224,9 @@ int32_t hs_merge_runs(hs_ctx* ctx, const hs_index_view* runs, int32_t nruns,
  * over two index relations created by RuleUtils.transformPlanToUseIndexOnlyScan with
  * useBucketSpec = true (HS/index/rules/RuleUtils.scala:264-292): bucket i of the left
  * index joins bucket i of the right one on the indexed columns; NULL keys never match.
- * Both views must have the same num_buckets and key types (else HS_EUNSUPPORTED).
+ * Key types must agree (else HS_EUNSUPPORTED). If the bucket counts differ (the rule tolerates it,
+ * JoinIndexRule.scala:515-516; Spark re-shuffles one side), the side with fewer rows is re-bucketed
+ * on the fly to the other side's count and the result carries that count.
  * Output columns: left_out[0..n_left_out) of the left view, then right_out[..] of the
  * right view; row order inside a bucket is unspecified (compare as multisets). In the outer
  * joins the columns of the side without a match are NULL for that row (validity bitmaps are

@@ -190,11 +190,25 @@ def test_join_after_incremental_refresh_two_runs_per_bucket(ctx, oracle):
     parity.assert_same_multiset(jg, want, joff, woff, "join over merged runs")
 
 
-def test_join_mismatched_bucket_counts_is_unsupported(ctx, hs):
-    a, ao = ctx.build_index([pa.array([1, 2, 3])], 1, 4)
-    b, bo = ctx.build_index([pa.array([1, 2, 3])], 1, 8)
-    with pytest.raises(hs.HyperspaceException):
-        ctx.join(a, ao, b, bo, 1, [0], [0])
+def test_join_with_different_bucket_counts(ctx, oracle):
+    """JoinIndexRule pairs indexes whose bucket counts differ too (JoinIndexRule.scala:515-516; Spark then
+    re-shuffles one side): the side with fewer rows is re-bucketed on the fly to the other side's count, and the
+    rows are those of a join over two indexes built with that count."""
+    lcols, keys = lineitem(8000, null_frac=0.01)
+    lg, loff = ctx.build_index(lcols, 1, 24)
+    og, ooff = ctx.build_index(orders(keys), 1, 7)
+    for how in ("inner", "left_outer", "full_outer"):
+        jg, joff = ctx.join(lg, loff, og, ooff, 1, [0, 1, 2], [0, 1], how=how)
+        assert len(joff) == 25                       # the larger side (lineitem) keeps its 24 buckets
+        og24, ooff24 = ctx.build_index(orders(keys), 1, 24)
+        li, ri, woff = oracle.join_typed(lg, og24, 1, loff, ooff24, how)
+        want = [oracle.take_or_null(lg[i], li) for i in (0, 1, 2)] + [oracle.take_or_null(og24[i], ri) for i in (0, 1)]
+        parity.assert_same_multiset(jg, want, joff, woff, f"{how} join, 24 x 7 buckets")
+    # the other way round: the left side is the small one
+    jg, joff = ctx.join(og, ooff, lg, loff, 1, [1], [0, 2])
+    li, ri, woff = oracle.join(og24, lg, 1, ooff24, loff)
+    want = [og24[1].take(pa.array(li)), lg[0].take(pa.array(ri)), lg[2].take(pa.array(ri))]
+    parity.assert_same_multiset(jg, want, joff, woff, "7 x 24 buckets")
 
 
 def test_filter_predicates(ctx, oracle):
