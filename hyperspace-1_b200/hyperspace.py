@@ -231,7 +231,7 @@ class RefreshAction(_CreateBase):
             ids = [f["id"] for f in self.deleted_infos]
             for arrays, boff in runs:
                 kept, koff = drop_deleted_rows(self.session, arrays, len(self.indexed), boff, names, ids)
-                files, _ = index_writer.write_buckets(kept, names, koff, self.out_dir)
+                files, _ = index_writer.write_index_files(self.session, kept, names, koff, self.out_dir)
                 self.new_files += files
             self.rewritten = True
         if self.appended:
@@ -300,7 +300,7 @@ class OptimizeAction(_CreateBase):
         indexed = list(props["columns"]["indexed"])
         runs, names, _ = index_writer.read_index(self.prev, files=self.to_optimize)
         arrays, boff = self.session.ctx.merge_runs([(a, len(indexed), off) for a, off in runs])
-        self.new_files, _ = index_writer.write_buckets(arrays, names, boff, self.out_dir)
+        self.new_files, _ = index_writer.write_index_files(self.session, arrays, names, boff, self.out_dir)
 
     def log_entry(self):
         tracker = le.FileIdTracker()

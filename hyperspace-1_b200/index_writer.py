@@ -47,12 +47,24 @@ def write_buckets(columns, names, bucket_offsets, out_dir, task_of_bucket=None, 
     return files, time.perf_counter() - t0
 
 
+def write_index_files(session, arrays, names, boff, out_dir):
+    """Parquet files of one index version. hsgpu.index.fileWriter = "pyarrow-snappy" (default: the host library
+    encodes, files are named and compressed as Spark's default writer would) or "gpu-plain" (page bodies encoded
+    on the device by hs_parquet_plain_pages, PLAIN + uncompressed; parquet_plain.py)."""
+    t0 = time.perf_counter()
+    if session.conf.get("hsgpu.index.fileWriter", "pyarrow-snappy") == "gpu-plain":
+        from .parquet_plain import write_buckets_plain
+        files = write_buckets_plain(session.ctx, arrays, names, boff, out_dir)
+        return files, time.perf_counter() - t0
+    return write_buckets(arrays, names, boff, out_dir)
+
+
 def build_and_write(session, table, indexed, included, num_buckets, out_dir):
     """table: pyarrow.Table holding at least indexed ++ included (resolved spellings)."""
     names = list(indexed) + list(included)
     cols = [table[c].combine_chunks() if isinstance(table[c], pa.ChunkedArray) else table[c] for c in names]
     arrays, boff = session.ctx.build_index(cols, len(indexed), num_buckets)
-    files, enc_s = write_buckets(arrays, names, boff, out_dir)
+    files, enc_s = write_index_files(session, arrays, names, boff, out_dir)
     return files, {"rows": len(cols[0]) if cols else 0, "parquet_encode_s": enc_s,
                    "gpu_stages": session.ctx.last_timings()}
 

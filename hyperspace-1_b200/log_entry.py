@@ -116,9 +116,9 @@ def arrow_to_spark_type(t):
         return "float"
     if pa.types.is_float64(t):
         return "double"
-    if pa.types.is_string(t):
+    if pa.types.is_string(t) or pa.types.is_large_string(t):
         return "string"
-    if pa.types.is_binary(t):
+    if pa.types.is_binary(t) or pa.types.is_large_binary(t):
         return "binary"
     if pa.types.is_date32(t):
         return "date"

@@ -16,6 +16,7 @@ _lib = None
 EXPORTS = [
     "hs_ctx_create", "hs_ctx_destroy", "hs_last_error", "hs_ctx_set_output_location", "hs_ctx_get_stream",
     "hs_ctx_enable_timing", "hs_ctx_last_timings", "hs_ctx_launch_count", "hs_table_free", "hs_version",
+    "hs_parquet_plain_pages",
     "hs_hash_bucket", "hs_hash_rows", "hs_build_index", "hs_merge_runs", "hs_join_bucketed", "hs_filter_scan",
     "hs_bucket_histogram_noalloc", "hs_comm_unique_id", "hs_comm_init", "hs_comm_destroy", "hs_build_index_dist", "hs_comm_last_exchange",
 ]
@@ -245,6 +246,21 @@ class Context:
         out = C.POINTER(abi.hs_table)()
         self._check(self._lib.hs_merge_runs(self._h, arr, C.c_int32(len(views)), C.byref(out)), "hs_merge_runs")
         return Table(self, out)
+
+    def parquet_plain_pages(self, array, optional, page_rows):
+        """hs_parquet_plain_pages for one Arrow array -> (list of page bodies as bytes, NULLs per page)."""
+        cs = abi.ColumnSet([array])
+        pr = np.ascontiguousarray(page_rows, dtype=np.int64)
+        out = C.POINTER(abi.hs_table)()
+        self._check(self._lib.hs_parquet_plain_pages(self._h, cs.ptr(), C.c_int32(1 if optional else 0),
+                                                     pr.ctypes.data_as(C.POINTER(C.c_int64)), C.c_int32(len(pr) - 1),
+                                                     C.byref(out)), "hs_parquet_plain_pages")
+        t = Table(self, out)
+        try:
+            bodies, nulls = t.to_arrow()
+            return [b.as_py() for b in bodies], nulls.to_numpy()
+        finally:
+            t.free()
 
     # ---- join / filter
     def join_table(self, left, right, left_out, right_out, how="inner"):

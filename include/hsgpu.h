@@ -237,6 +237,19 @@ int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left,
                          const int32_t* right_out, int32_t n_right_out,
                          hs_table** out);
 
+/* ---- K4: Parquet page bodies (PLAIN) --------------------------------------
+ * What Spark's DynamicPartitionDataWriter + ParquetFileFormat do to every value behind saveWithBuckets
+ * (HS/index/DataFrameWriterExtensions.scala:58-65). One call encodes all data pages (Parquet v1, PLAIN,
+ * uncompressed) of ONE column: page p covers rows [page_rows[p], page_rows[p+1]); page_rows (host memory) has
+ * npages+1 entries, starts at 0 and ends at the column length. Result: column 0 = BINARY with one row per page,
+ * the page body = [definition levels, only if `optional`] ++ [PLAIN values of the non-NULL rows]; column 1 =
+ * INT64 number of NULLs per page. Definition levels: 4-byte LE byte count + RLE/bit-packed hybrid of bit
+ * width 1 (one RLE run for a page without NULLs, bit-packed groups from the validity bitmap otherwise).
+ * Values: fixed width little-endian; BOOL bit-packed LSB first; UTF8/BINARY 4-byte LE length + bytes.
+ * The Thrift page headers and the file footer are framing the host writes. */
+int32_t hs_parquet_plain_pages(hs_ctx* ctx, const hs_column* col, int32_t optional,
+                               const int64_t* page_rows, int32_t npages, hs_table** out);
+
 /* ---- K7: filtered index scan -----------------------------------------------
  * Executes the plan FilterIndexRule.apply produces (HS/index/rules/FilterIndexRule.scala:43-85,
  * useBucketSpec = false at :59-65): rows of the index for which the predicate is TRUE,

@@ -91,7 +91,7 @@ def run_cfg4(args):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--config", choices=["cfg4", "cfg5"], required=True)
+    ap.add_argument("--config", choices=["cfg4", "cfg5", "parquet"], required=True)
     ap.add_argument("--rows", type=int, default=0, help="rows (per GPU for cfg5); default = the config's size that fits")
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=2)
@@ -99,8 +99,53 @@ def main():
     args = ap.parse_args()
     if args.config == "cfg4":
         run_cfg4(args)
+    elif args.config == "parquet":
+        run_parquet(args)
     else:
         run_cfg5(args)
+
+
+def run_parquet(args):
+    """K4 beside the kernels (timed separately): the files of a cfg2-shaped index written by the
+    host library (pyarrow, snappy, what index_writer does by default) and by the device encoder
+    (hs_parquet_plain_pages + parquet_plain.py framing, PLAIN uncompressed), same rows, to a tmpfs directory."""
+    import shutil
+    import tempfile
+    import numpy as np
+    import pyarrow as pa
+    import pyarrow.parquet as pq
+    from hyperspace_1_b200 import index_writer, native, parquet_plain
+    n, nb = args.rows or 20_000_000, 200
+    rng = np.random.default_rng(20240601)
+    cols = [pa.array(rng.integers(1, n, size=n)), pa.array(np.round(rng.random(n) * 104100 + 900, 2)),
+            pa.array(rng.integers(0, 11, size=n) / 100.0)]
+    names = ["l_orderkey", "l_extendedprice", "l_discount"]
+    ctx = native.Context(0)
+    arrays, boff = ctx.build_index(cols, 1, nb)
+    root = tempfile.mkdtemp(dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+    out = {"config": "parquet", "rows": n, "num_buckets": nb, "raw_bytes": n * 24}
+    try:
+        for name, fn in (("pyarrow_snappy", lambda d: index_writer.write_buckets(arrays, names, boff, d)[0]),
+                         ("gpu_plain", lambda d: parquet_plain.write_buckets_plain(ctx, arrays, names, boff, d))):
+            best, files = 1e9, []
+            for rep in range(max(1, args.steps)):
+                d = os.path.join(root, f"{name}_{rep}")
+                t0 = time.perf_counter()
+                files = fn(d)
+                best = min(best, time.perf_counter() - t0)
+                if rep + 1 < max(1, args.steps):
+                    shutil.rmtree(d)
+            size = sum(os.path.getsize(f) for f in files)
+            t0 = time.perf_counter()
+            rows = sum(pq.ParquetFile(f).read().num_rows for f in files)
+            rd = time.perf_counter() - t0
+            assert rows == n
+            out[name] = {"write_s": best, "rows_per_s": n / best, "file_bytes": size, "files": len(files),
+                         "pyarrow_read_back_s": rd}
+    finally:
+        shutil.rmtree(root, ignore_errors=True)
+    print(json.dumps(out), flush=True)
+    ctx.close()
 
 
 def run_cfg5(args):
