@@ -174,3 +174,43 @@ def test_cfg4_shape_string_keys_properties(hs, oracle):
     a0, a1 = got[0].slice(0, m - 1).cast(pa.binary()), got[0].slice(1).cast(pa.binary())
     dec = np.nonzero(pc.greater(a0, a1).to_numpy(zero_copy_only=False))[0] + 1
     assert np.isin(dec, boff[1:-1]).all(), "a bucket is not sorted"
+
+
+def test_skewed_key_distributions(hs):
+    """20 M rows per case (device-resident): constant keys, a handful of distinct keys (whole buckets of equal
+    keys: the copy path of the segmented sort), power-law keys (several MSD levels on few buckets' worth of key
+    range), sorted input, two far-apart clusters, the full signed range. Every case: buckets sorted, every key
+    still paired with its row id, every row id present once."""
+    import torch
+    from hyperspace_1_b200 import abi
+    dev = torch.device("cuda", 0)
+    n = int(os.environ.get("HS_SKEW_ROWS", "20000000"))
+    g = torch.Generator(device=dev)
+    g.manual_seed(1)
+    ctx = hs.Context(0)
+    ctx.set_output_location(abi.HS_MEM_DEVICE)
+    u = lambda hi: torch.randint(0, hi, (n,), generator=g, device=dev)
+    cases = {
+        "all equal": torch.full((n,), 7, device=dev, dtype=torch.int64),
+        "10 distinct": u(10),
+        "1000 distinct": u(1000),
+        "power law": (torch.rand(n, generator=g, device=dev).pow(8) * 1e9).to(torch.int64),
+        "sorted input": torch.arange(n, device=dev, dtype=torch.int64),
+        "two clusters": torch.where(torch.rand(n, generator=g, device=dev) < 0.5, u(1000000), (1 << 62) + u(1000000)),
+        "full signed range": torch.randint(-(1 << 62), 1 << 62, (n,), generator=g, device=dev),
+    }
+    rid = torch.arange(n, device=dev, dtype=torch.int64)
+    for name, key in cases.items():
+        torch.cuda.synchronize()
+        cs = abi.DeviceColumnSet([{"type": abi.HS_INT64, "length": n, "data": key.data_ptr()},
+                                  {"type": abi.HS_INT64, "length": n, "data": rid.data_ptr()}])
+        t = ctx.build_index_table(cs, 1, 200)
+        boff = t.bucket_offsets()
+        ok = _dev_tensor(torch, t.column(0), torch.int64, n)
+        ov = _dev_tensor(torch, t.column(1), torch.int64, n)
+        bad = (ok[1:] < ok[:-1]).nonzero().flatten() + 1
+        assert bool(torch.isin(bad, torch.as_tensor(boff[1:-1], device=dev)).all()), f"{name}: a bucket is not sorted"
+        assert bool((key[ov] == ok).all()), f"{name}: a key lost its row"
+        assert int(ov.sum()) == n * (n - 1) // 2 and int(ov.max()) == n - 1, f"{name}: row ids are not a permutation"
+        t.free()
+    ctx.close()
