@@ -310,9 +310,17 @@ __global__ void __launch_bounds__(PT_THREADS) k_msd_hist(const __grid_constant__
   const uint64_t seg_base = p.segs.base[s];
   if (threadIdx.x < MSD_RADIX) hist[threadIdx.x] = 0;
   __syncthreads();
-  for (uint32_t j = threadIdx.x; j < tile_len; j += PT_THREADS) {
-    uint32_t d = (uint32_t)((load_key(p.mv, p.key, tile_start + j) - seg_base) >> shift) & ((1u << bits) - 1u);
-    atomicAdd(&hist[d], 1u);
+  // all keys of the thread first (independent loads), then the shared-memory updates
+  uint64_t kk[PT_ITEMS];
+#pragma unroll
+  for (int k = 0; k < PT_ITEMS; k++) {
+    const uint32_t j = threadIdx.x + k * PT_THREADS;
+    kk[k] = j < tile_len ? load_key(p.mv, p.key, tile_start + j) : 0;
+  }
+#pragma unroll
+  for (int k = 0; k < PT_ITEMS; k++) {
+    const uint32_t j = threadIdx.x + k * PT_THREADS;
+    if (j < tile_len) atomicAdd(&hist[(uint32_t)((kk[k] - seg_base) >> shift) & ((1u << bits) - 1u)], 1u);
   }
   __syncthreads();
   if (threadIdx.x < MSD_RADIX) {
