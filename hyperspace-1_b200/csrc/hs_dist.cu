@@ -315,6 +315,9 @@ struct NcclExchange : BuildExchange {
 
   // ---- fused path ------------------------------------------------------------------------------------
   std::vector<uint64_t> rank_rows;   // rows every rank receives
+  int xmode = 0;                     // 0 fused, 1 owner, 2 copy (see try_fused)
+  std::vector<int> xes;              // element sizes of the travelling columns (+ the bucket ids in owner mode)
+  std::vector<DBuf> owner_sorted;    // owner mode: the received rows, scattered by bucket (the sort's source)
 
   bool try_fused(hs_ctx* c, const std::vector<int>& esize) override {
     const char* off = getenv("HSGPU_NO_P2P");
@@ -323,7 +326,23 @@ struct NcclExchange : BuildExchange {
     P2PState* st = p2p_of(c);
     if (st->unusable) return false;
     Stage s(c, "p2p_setup");
-    const int ncol = (int)esize.size();
+    // How the rows travel (HSGPU_P2P_MODE=fused|owner|copy overrides):
+    //  fused  the bucket scatter stores every row straight at its place in the owner's bucket. Few buckets:
+    //         a tile of 4096 rows holds runs of tens of rows per bucket, decent NVLink packets.
+    //  owner  thousands of buckets would make every row a packet of its own (measured 3.5 GB/s per GPU at 8192
+    //         buckets). The scatter then groups rows by OWNER only (runs of hundreds of rows per destination),
+    //         the bucket ids travel as one more column, and the owner scatters what it received by bucket.
+    //  copy   scatter by bucket locally, then push whole bucket runs (kept for comparison).
+    const char* mode = getenv("HSGPU_P2P_MODE");
+    xmode = nb <= 256 ? 0 : 1;
+    if (mode && !strcmp(mode, "fused")) xmode = 0;
+    if (mode && !strcmp(mode, "owner")) xmode = 1;
+    if (mode && !strcmp(mode, "copy")) xmode = 2;
+    xes = esize;
+    if (xmode == 1) xes.push_back(2);       // the bucket-id column
+    if ((int)xes.size() > HS_MAX_PEER_COLS_HOST) return false;
+    const int ncol = (int)xes.size();
+    const std::vector<int>& esize_x = xes;
     rank_rows.assign(N, 0);
     for (int b = 0; b < nb; b++)
       for (int r = 0; r < N; r++) rank_rows[owner_of(b, N, nb)] += all_hist[(size_t)r * nb + b];
@@ -334,7 +353,7 @@ struct NcclExchange : BuildExchange {
     bool ok = true;
     if ((int)st->slots.size() < ncol) st->slots.resize(ncol);
     for (int i = 0; i < ncol && ok; i++) {
-      size_t need = (size_t)rank_rows[me] * esize[i] + 256;
+      size_t need = (size_t)rank_rows[me] * esize_x[i] + 256;
       P2PSlot& sl = st->slots[i];
       if (sl.cap < need) {
         if (sl.ptr) st->retired.push_back(sl.ptr);
@@ -423,16 +442,25 @@ struct NcclExchange : BuildExchange {
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
     CK(cudaEventCreate(&e1));
-    // The fused kernel stores every row straight at its place in the owner's memory: with few buckets a tile
-    // of 4096 rows holds runs of tens of rows per bucket and the stores leave as decent NVLink packets (measured
-    // faster than scatter + copy, 3.06 vs 3.6 ms at N=2, 200 buckets). With thousands of buckets every row is a
-    // packet of its own (measured 3.5 GB/s at 8192 buckets) — then the rows are scattered locally first and whole
-    // bucket runs are pushed. HSGPU_P2P_MODE=fused|copy overrides.
-    const char* mode = getenv("HSGPU_P2P_MODE");
-    bool one_kernel = nb <= 512;
-    if (mode && !strcmp(mode, "copy")) one_kernel = false;
-    if (mode && !strcmp(mode, "fused")) one_kernel = true;
-    if (one_kernel) {
+    const bool one_kernel = xmode == 0;
+    if (xmode == 1) {
+      // grouped by owner: my rows for owner o land behind those of the ranks before me
+      Stage s(c, "scatter_to_owners");
+      std::vector<uint32_t> base((size_t)N, 0);
+      for (int o = 0; o < N; o++)
+        for (int q = 0; q < me; q++)
+          for (int b = 0; b < nb; b++)
+            if (owner_of(b, N, nb) == o) base[o] += all_hist[(size_t)q * nb + b];
+      DBuf d_base(c, (size_t)N * 4);
+      CK(cudaMemcpyAsync(d_base.p, base.data(), (size_t)N * 4, cudaMemcpyHostToDevice, c->stream));
+      std::vector<const void*> xsrc(srcs, srcs + ncol);
+      xsrc.push_back(d_bucket);
+      CK(cudaEventRecord(e0, c->stream));
+      hs_bucket_scatter_peers(c, xsrc.data(), xes.data(), ncol + 1, st->peer_ptr.data(), N, d_bucket, n_local, nb,
+                              d_base.as<uint32_t>(), true);
+      CK(cudaEventRecord(e1, c->stream));
+      hs_sync(c);   // my stores have left this GPU
+    } else if (one_kernel) {
       // one kernel: the bucket scatter stores every row at its final place in the owner's memory
       Stage s(c, "scatter_to_owners");
       DBuf d_base(c, (size_t)nb * 4);
@@ -512,6 +540,30 @@ struct NcclExchange : BuildExchange {
     c->last_xchg_bytes = bytes_sent;
     c->last_xchg_ms = ms_x;
     recv.resize(ncol);
+    if (xmode == 1) {
+      // what arrived is grouped by sender only: scatter it by bucket (ids in the last received column, this
+      // rank's buckets start at blo) into buffers that then serve as the sort's source
+      Stage s(c, "bucket_scatter");
+      const int64_t nrecv = (int64_t)rank_rows[me];
+      owner_sorted.clear();
+      owner_sorted.resize((size_t)ncol);
+      MoveSet ms;
+      memset(&ms, 0, sizeof ms);
+      ms.n = ncol;
+      std::vector<const void*> rsrc((size_t)ncol);
+      for (int i = 0; i < ncol; i++) {
+        owner_sorted[i].alloc(c, (size_t)nrecv * esize[i] + 16);
+        ms.esize[i] = esize[i];
+        ms.a[i] = owner_sorted[i].p;
+        rsrc[i] = st->slots[i].ptr;
+        recv[i] = owner_sorted[i].p;
+      }
+      DBuf d_off(c, ((size_t)nbl + 1) * 4);
+      CK(cudaMemcpyAsync(d_off.p, seg_off.data(), ((size_t)nbl + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+      hs_bucket_scatter(c, rsrc.data(), ms, (const uint16_t*)st->slots[ncol].ptr, nrecv, nbl, d_off.as<uint32_t>(), blo);
+      hs_sync(c);   // seg_off is the caller's vector, d_off dies here
+      return nrecv;
+    }
     for (int i = 0; i < ncol; i++) recv[i] = st->slots[i].ptr;
     return (int64_t)rank_rows[me];
   }

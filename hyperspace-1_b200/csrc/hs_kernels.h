@@ -58,9 +58,10 @@ struct KeySrc {
 // Scatter rows from the caller's column buffers (src[i], element sizes as in ms) into bucket-contiguous
 // order in ms.a, given u16 bucket ids and host-known bucket offsets.
 void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, const uint16_t* d_bucket, int64_t n,
-                       int32_t nb, const uint32_t* d_bucket_off);
+                       int32_t nb, const uint32_t* d_bucket_off, int32_t bucket_base = 0);
 void hs_bucket_scatter_peers(hs_ctx* c, const void* const* src, const int32_t* esize, int ncols, void* const* pdst,
-                             int nranks, const uint16_t* d_bucket, int64_t n, int32_t nb, const uint32_t* d_run_base);
+                             int nranks, const uint16_t* d_bucket, int64_t n, int32_t nb, const uint32_t* d_run_base,
+                             bool by_owner = false);
 // Sort every segment [seg_off[s], seg_off[s+1]) of ms.a by the key; result in ms.a. key_bits = significant
 // low bits of the key. d_seg_off: device u32[nseg+1].
 void hs_segmented_sort(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_seg_off,

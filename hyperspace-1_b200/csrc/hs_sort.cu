@@ -117,6 +117,9 @@ struct PartParams {
   int32_t radix_pad;
   int32_t bits;             // MODE 0: bits of a bucket id
   int32_t bucket_shift;     // MODE 0: digit = bucket id >> bucket_shift (coarse pass of the two-level scatter)
+  int32_t bucket_base;      // MODE 0: subtracted from the bucket id first (ids of a rank's own bucket range)
+  int32_t by_owner;         // MODE 2: digit = owner of the bucket (nranks bins) instead of the bucket itself
+  int32_t nb_total;         // MODE 2, by_owner: number of buckets of the index
   uint32_t* cursor;         // MODE 0: [radix]; MODE 1: [nseg * 256]
   SegList segs;             // MODE 1: the large segments of this level
   const uint32_t* tile_prefix;  // MODE 1: [nseg + 1]
@@ -243,9 +246,9 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
     digit[k] = 0;
     if (v) {
       if (MODE == 0) {
-        digit[k] = (uint32_t)sbucket[idx] >> p.bucket_shift;
+        digit[k] = ((uint32_t)sbucket[idx] - (uint32_t)p.bucket_base) >> p.bucket_shift;
       } else if (MODE == 2) {
-        digit[k] = sbucket[idx];
+        digit[k] = p.by_owner ? ((uint32_t)sbucket[idx] * (uint32_t)p.nranks) / (uint32_t)p.nb_total : sbucket[idx];
       } else {
         const unsigned char* ks = sm.stage[0] + slice_lead(p.mv.src[first], p.mv.esize[first], tile_start);
         uint64_t key;
@@ -264,7 +267,8 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
     if ((vmask >> k) & 1u) {
       sm.gdst[pos[k]] = sm.gbase[digit[k]] + pos[k] - sm.cnt[digit[k]];
       uint32_t iv = threadIdx.x + k * PT_THREADS;
-      if (MODE == 2) iv |= (uint32_t)(((uint64_t)digit[k] * (uint32_t)p.nranks) / (uint32_t)p.radix) << 12;
+      if (MODE == 2)
+        iv |= (p.by_owner ? digit[k] : (uint32_t)(((uint64_t)digit[k] * (uint32_t)p.nranks) / (uint32_t)p.radix)) << 12;
       sm.inv[pos[k]] = (uint16_t)iv;
     }
   }
@@ -963,12 +967,13 @@ static void launch_bucket_scatter(hs_ctx* c, const PartParams& p, int64_t n) {
 }
 
 void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, const uint16_t* d_bucket, int64_t n,
-                       int32_t nb, const uint32_t* d_bucket_off) {
+                       int32_t nb, const uint32_t* d_bucket_off, int32_t bucket_base) {
   if (n == 0) return;
   if (nb > 8192) HS_THROW(HS_EUNSUPPORTED, "the bucket scatter supports at most 8192 buckets per GPU");
   PartParams p;
   memset(&p, 0, sizeof p);
   p.n = (uint32_t)n;
+  p.bucket_base = bucket_base;
   DBuf cursor(c, (size_t)nb * 4);
   CK(cudaMemcpyAsync(cursor.p, d_bucket_off, (size_t)nb * 4, cudaMemcpyDeviceToDevice, c->stream));
   const char* one = getenv("HSGPU_ONE_LEVEL_SCATTER");
@@ -1013,7 +1018,8 @@ void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, con
 // Multi-GPU variant of the bucket scatter: rows go straight into the owners' receive buffers.
 // d_run_base[b] = first row, inside the owner's buffer, of THIS rank's run for bucket b.
 void hs_bucket_scatter_peers(hs_ctx* c, const void* const* src, const int32_t* esize, int ncols, void* const* pdst,
-                             int nranks, const uint16_t* d_bucket, int64_t n, int32_t nb, const uint32_t* d_run_base) {
+                             int nranks, const uint16_t* d_bucket, int64_t n, int32_t nb, const uint32_t* d_run_base,
+                             bool by_owner) {
   if (n == 0) return;
   if (nb > 8192) HS_THROW(HS_EUNSUPPORTED, "the bucket scatter supports at most 8192 buckets");
   if (ncols > HS_MAX_PEER_COLS || nranks > HS_MAX_PEERS) HS_THROW(HS_EUNSUPPORTED, "too many columns or ranks for the peer scatter");
@@ -1026,11 +1032,16 @@ void hs_bucket_scatter_peers(hs_ctx* c, const void* const* src, const int32_t* e
   p.nranks = nranks;
   p.bucket = d_bucket;
   p.n = (uint32_t)n;
-  p.radix = nb;
-  p.radix_pad = ((nb + PT_THREADS - 1) / PT_THREADS) * PT_THREADS;
+  // by_owner: rows are only grouped by the GPU that owns their bucket (nranks bins, d_run_base has nranks entries):
+  // a tile then holds runs of hundreds of rows per destination, which is what NVLink stores want
+  p.by_owner = by_owner ? 1 : 0;
+  p.nb_total = nb;
+  const int32_t radix = by_owner ? nranks : nb;
+  p.radix = radix;
+  p.radix_pad = ((radix + PT_THREADS - 1) / PT_THREADS) * PT_THREADS;
   p.bits = 0;
-  DBuf cursor(c, (size_t)nb * 4);
-  CK(cudaMemcpyAsync(cursor.p, d_run_base, (size_t)nb * 4, cudaMemcpyDeviceToDevice, c->stream));
+  DBuf cursor(c, (size_t)radix * 4);
+  CK(cudaMemcpyAsync(cursor.p, d_run_base, (size_t)radix * 4, cudaMemcpyDeviceToDevice, c->stream));
   p.cursor = cursor.as<uint32_t>();
   size_t smem = tile_smem_bytes(p.radix_pad);
   static size_t attr_set_dev[64] = {0};

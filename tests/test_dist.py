@@ -42,8 +42,16 @@ def test_sharded_build_world2_gloo():
 
 
 @pytest.mark.gpu
-def test_sharded_build_world2_nccl():
+@pytest.mark.parametrize("exchange", ["fused", "owner", "copy", "nccl"])
+def test_sharded_build_world2_nccl(exchange, monkeypatch):
+    """hs_build_index_dist on two GPUs against the oracle, once per way the rows can travel: straight into the
+    owner's buckets (fused), grouped by owner with the bucket ids alongside and a bucket scatter at the receiver
+    (owner), whole bucket runs pushed after a local scatter (copy), and the NCCL send/receive fallback."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
+    if exchange == "nccl":
+        monkeypatch.setenv("HSGPU_NO_P2P", "1")
+    else:
+        monkeypatch.setenv("HSGPU_P2P_MODE", exchange)
     _run("nccl", 2)
