@@ -237,6 +237,23 @@ __global__ void __launch_bounds__(256) k_tie_finish(const __grid_constant__ KeyL
   if (i1 < len) flag[start + i1] = 1;
 }
 
+// Integer key columns out of the sorted single-chunk normalised key: the key IS the column values (valid flag,
+// value - minimum), so those columns need not travel through the scatter and sort passes at all.
+template <typename T>
+__global__ void __launch_bounds__(256) k_decode_key(const uint64_t* __restrict__ nkey, int64_t n, NGroup g,
+                                                    T* __restrict__ out, uint8_t* __restrict__ valid_bytes) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const uint64_t mask = g.width >= 64 ? ~0ull : ((1ull << g.width) - 1ull);
+  for (; i < n; i += stride) {
+    const uint64_t k = nkey[i];
+    const bool valid = g.flag_shift < 0 || ((k >> g.flag_shift) & 1ull);
+    const uint64_t mapped = (g.width ? ((k >> g.shift) & mask) : 0ull) + g.min;
+    out[i] = valid ? (T)(int64_t)(mapped ^ 0x8000000000000000ull) : (T)0;
+    if (valid_bytes) valid_bytes[i] = valid;
+  }
+}
+
 static unsigned grid1d(int64_t n) {
   int64_t g = (n + 255) / 256;
   int64_t cap = (int64_t)HS_NUM_SMS * 16;
@@ -280,6 +297,7 @@ static KeyLayout make_layout(const std::vector<DevCol>& cols, int nk, const uint
     uint64_t mn = minmax[2 * k], mx = minmax[2 * k + 1];
     int width = mn <= mx ? bitlen64(mx - mn) : 0;
     g.min = mn <= mx ? mn : 0;
+    g.width = width;
     if (has_nulls[k]) runs[run].push_back({k, 1, true, 0});
     if (width > 0) runs[run].push_back({k, width, false, 0});
   }
@@ -372,6 +390,14 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
   bool any_varlen = false;
   for (auto& dc : cols) any_varlen |= hs_is_varlen(dc.type);
   bool need_srcrow = any_varlen || !L.single_chunk;
+  // composite / small integer keys that fit one chunk: the key columns stay behind, the 8-byte key stands for them
+  bool packed_keys = !fast_key && L.single_chunk;
+  for (int k = 0; k < n_indexed && packed_keys; k++)
+    if (cols[k].type < HS_INT8 || cols[k].type > HS_INT64) packed_keys = false;
+  {
+    const char* off = getenv("HSGPU_MOVE_KEY_COLUMNS");
+    if (off && *off && *off != '0') packed_keys = false;
+  }
   if (xchg && need_srcrow)
     HS_THROW(HS_EUNSUPPORTED, "string columns and keys wider than 64 bits are not supported in the multi-GPU build");
 
@@ -388,6 +414,7 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
     Stage s(c, "prepare");
     for (int i = 0; i < ncols; i++) {
       DevCol& dc = cols[i];
+      if (packed_keys && i < n_indexed) continue;
       if (has_nulls[i]) {
         MovedCol& m = add(i, 1, 1, nullptr);
         m.tmp.alloc(c, (size_t)n);
@@ -588,6 +615,33 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
         LAUNCH(c, k_bytes_to_bits, grid1d((n + 7) / 8), 256, 0, m.a.as<uint8_t>(), n, bits.as<uint8_t>());
         if (m.role == 1) o.validity = std::move(bits);
         else { o.data_bytes = (n + 7) / 8; o.data = std::move(bits); }
+      }
+    }
+    for (int i = 0; packed_keys && i < n_indexed; i++) {
+      OutCol& o = out[i];
+      const int w = hs_fixed_width(cols[i].type);
+      o.data_bytes = n * w;
+      o.data.alloc(c, (size_t)o.data_bytes + 16);
+      DBuf vbytes;
+      if (has_nulls[i]) vbytes.alloc(c, (size_t)(n > 0 ? n : 1));
+      const uint64_t* sorted_key = (const uint64_t*)ms.a[key_mv];
+      uint8_t* vb = has_nulls[i] ? vbytes.as<uint8_t>() : nullptr;
+      if (n > 0) switch (w) {
+        case 1: LAUNCH(c, k_decode_key<int8_t>, grid1d(n), 256, 0, sorted_key, n, L.g[i], o.data.as<int8_t>(), vb); break;
+        case 2: LAUNCH(c, k_decode_key<int16_t>, grid1d(n), 256, 0, sorted_key, n, L.g[i], o.data.as<int16_t>(), vb); break;
+        case 4: LAUNCH(c, k_decode_key<int32_t>, grid1d(n), 256, 0, sorted_key, n, L.g[i], o.data.as<int32_t>(), vb); break;
+        default: LAUNCH(c, k_decode_key<int64_t>, grid1d(n), 256, 0, sorted_key, n, L.g[i], o.data.as<int64_t>(), vb); break;
+      }
+      if (has_nulls[i]) {
+        DBuf bits(c, (size_t)((n + 7) / 8)), zeros(c, 8);
+        zeros.zero();
+        LAUNCH(c, k_bytes_to_bits_count, grid1d((n + 7) / 8), 256, 0, vbytes.as<uint8_t>(), n, bits.as<uint8_t>(),
+               zeros.as<unsigned long long>());
+        unsigned long long z = 0;
+        CK(cudaMemcpyAsync(&z, zeros.p, 8, cudaMemcpyDeviceToHost, c->stream));
+        hs_sync(c);
+        o.null_count = (int64_t)z;
+        if (z) o.validity = std::move(bits);
       }
     }
     for (int i = 0; i < ncols; i++) {

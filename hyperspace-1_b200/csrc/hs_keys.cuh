@@ -175,6 +175,7 @@ struct NGroup {            // one key column
   int32_t flag_shift;      // fixed: position of the valid flag, or -1
   int32_t flag_chunk;      // fixed: chunk that holds the flag (a 65-bit field splits)
   int32_t run_id;          // fixed: which run of consecutive fixed columns
+  int32_t width;           // fixed: bits of the value field (0: all valid cells hold the minimum)
   uint64_t min;            // fixed: mapped minimum over valid cells
 };
 struct KeyLayout {
