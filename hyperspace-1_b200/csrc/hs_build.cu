@@ -800,6 +800,46 @@ int32_t hs_merge_runs(hs_ctx* ctx, const hs_index_view* runs, int32_t nruns, hs_
     Stage s(ctx, "h2d");
     for (int r = 0; r < nruns; r++) hs_stage_columns(ctx, runs[r].cols, runs[r].ncols, staged[r]);
   }
+  // ---- sorted runs merge pairwise along the merge path when the shape allows it (hs_merge.cu)
+  const int32_t nbk = runs[0].num_buckets;
+  bool offsets_ok = true;
+  for (int r = 0; r < nruns && offsets_ok; r++) {
+    const int64_t* o = runs[r].bucket_offsets;
+    offsets_ok = o && o[0] == 0 && o[nbk] == staged[r][0].length;
+    for (int32_t k = 0; k < nbk && offsets_ok; k++) offsets_ok = o[k + 1] >= o[k];
+  }
+  if (offsets_ok && nruns >= 2) {
+    std::vector<OutCol> cur_out;
+    std::vector<int64_t> cur_off(runs[0].bucket_offsets, runs[0].bucket_offsets + nbk + 1);
+    std::vector<DevCol> cur;
+    std::vector<DevCol>* left = &staged[0];
+    bool merged = true;
+    for (int r = 1; r < nruns && merged; r++) {
+      std::vector<OutCol> next_out;
+      std::vector<int64_t> next_off;
+      merged = hs_merge_two_runs(ctx, *left, cur_off.data(), staged[r], runs[r].bucket_offsets, runs[0].n_indexed, nbk,
+                                 next_out, next_off);
+      if (!merged) break;
+      cur_out = std::move(next_out);     // the previous intermediate (if any) is released here, in stream order
+      cur_off = std::move(next_off);
+      cur.clear();
+      cur.resize(cur_out.size());
+      for (size_t i = 0; i < cur_out.size(); i++) {
+        cur[i].type = cur_out[i].type;
+        cur[i].length = cur_out[i].length;
+        cur[i].null_count = cur_out[i].null_count;
+        cur[i].validity = cur_out[i].null_count ? cur_out[i].validity.as<uint8_t>() : nullptr;
+        cur[i].data = cur_out[i].data.p;
+        cur[i].data_bytes = cur_out[i].data_bytes;
+      }
+      left = &cur;
+    }
+    if (merged) {
+      Stage s(ctx, "d2h");
+      *out = hs_finish_table(ctx, cur_out, cur_out[0].length, nbk, &cur_off);
+      return HS_OK;
+    }
+  }
   std::vector<DevCol> all;
   {
     Stage s(ctx, "concat");

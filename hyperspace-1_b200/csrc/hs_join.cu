@@ -577,6 +577,37 @@ __global__ void __launch_bounds__(256) k_pack_keys(const __grid_constant__ KeySp
   }
 }
 
+// Both sides' NULL-free fixed-width key tuples as one order-preserving u64 per row, with a common layout
+// (per-column minimum over both sides, widths from the joint ranges). false if the ranges need more than 64 bits.
+bool hs_pack_key_tuples(hs_ctx* ctx, const KeySpec& a, int64_t na, const KeySpec& b, int64_t nrows_b, int nk, DBuf& pa,
+                        DBuf& pb) {
+  DBuf mm(ctx, 2 * HS_MAX_KEYS * 8);
+  uint64_t init[2 * HS_MAX_KEYS], h_mm[2 * HS_MAX_KEYS];
+  for (int k = 0; k < HS_MAX_KEYS; k++) { init[2 * k] = ~0ull; init[2 * k + 1] = 0; }
+  CK(cudaMemcpyAsync(mm.p, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+  if (na > 0) LAUNCH(ctx, k_keys_range, HS_NUM_SMS * 8, 256, 0, a, na, mm.as<uint64_t>());
+  if (nrows_b > 0) LAUNCH(ctx, k_keys_range, HS_NUM_SMS * 8, 256, 0, b, nrows_b, mm.as<uint64_t>());
+  CK(cudaMemcpyAsync(h_mm, mm.p, sizeof h_mm, cudaMemcpyDeviceToHost, ctx->stream));
+  hs_sync(ctx);
+  KeyPack kp;
+  memset(&kp, 0, sizeof kp);
+  int total_bits = 0;
+  for (int k = nk - 1; k >= 0; k--) {
+    uint64_t range = h_mm[2 * k] <= h_mm[2 * k + 1] ? h_mm[2 * k + 1] - h_mm[2 * k] : 0;
+    int bits = 0;
+    while (bits < 64 && (range >> bits)) bits++;
+    kp.min[k] = h_mm[2 * k] <= h_mm[2 * k + 1] ? h_mm[2 * k] : 0;
+    kp.shift[k] = total_bits;
+    total_bits += bits;
+  }
+  if (total_bits > 64) return false;
+  pa.alloc(ctx, (size_t)(na > 0 ? na : 1) * 8);
+  pb.alloc(ctx, (size_t)(nrows_b > 0 ? nrows_b : 1) * 8);
+  if (na > 0) LAUNCH(ctx, k_pack_keys, HS_NUM_SMS * 16, 256, 0, a, na, kp, pa.as<uint64_t>());
+  if (nrows_b > 0) LAUNCH(ctx, k_pack_keys, HS_NUM_SMS * 16, 256, 0, b, nrows_b, kp, pb.as<uint64_t>());
+  return true;
+}
+
 extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, const hs_index_view* right,
                                     int32_t join_type, const int32_t* left_out, int32_t n_left_out,
                                     const int32_t* right_out, int32_t n_right_out, hs_table** out) {
@@ -659,34 +690,8 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
   DBuf lpk, rpk;
   if (fast_join && !int_key) {
     Stage s(ctx, "join_pack_keys");
-    DBuf mm(ctx, 2 * HS_MAX_KEYS * 8);
-    uint64_t init[2 * HS_MAX_KEYS], h_mm[2 * HS_MAX_KEYS];
-    for (int k = 0; k < HS_MAX_KEYS; k++) { init[2 * k] = ~0ull; init[2 * k + 1] = 0; }
-    CK(cudaMemcpyAsync(mm.p, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
-    LAUNCH(ctx, k_keys_range, HS_NUM_SMS * 8, 256, 0, L.ks, nl, mm.as<uint64_t>());
-    LAUNCH(ctx, k_keys_range, HS_NUM_SMS * 8, 256, 0, R.ks, nr, mm.as<uint64_t>());
-    CK(cudaMemcpyAsync(h_mm, mm.p, sizeof h_mm, cudaMemcpyDeviceToHost, ctx->stream));
-    hs_sync(ctx);
-    KeyPack kp;
-    memset(&kp, 0, sizeof kp);
-    int total_bits = 0;
-    for (int k = nk - 1; k >= 0; k--) {
-      uint64_t range = h_mm[2 * k + 1] - h_mm[2 * k];
-      int bits = 0;
-      while (bits < 64 && (range >> bits)) bits++;
-      kp.min[k] = h_mm[2 * k];
-      kp.shift[k] = total_bits;
-      total_bits += bits;
-    }
-    if (total_bits <= 64) {
-      lpk.alloc(ctx, (size_t)nl * 8);
-      rpk.alloc(ctx, (size_t)nr * 8);
-      LAUNCH(ctx, k_pack_keys, HS_NUM_SMS * 16, 256, 0, L.ks, nl, kp, lpk.as<uint64_t>());
-      LAUNCH(ctx, k_pack_keys, HS_NUM_SMS * 16, 256, 0, R.ks, nr, kp, rpk.as<uint64_t>());
-      packed = true;
-    } else {
-      fast_join = false;
-    }
+    packed = hs_pack_key_tuples(ctx, L.ks, nl, R.ks, nr, nk, lpk, rpk);
+    if (!packed) fast_join = false;
   }
   if (fast_join) {
     std::vector<uint32_t> tb, ts, tl, first_tile((size_t)nb + 1);

@@ -35,6 +35,11 @@ struct BuildExchange {
 void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t nb, int32_t blo, int32_t nbl,
                    std::vector<OutCol>& out, std::vector<int64_t>& boff, BuildExchange* xchg);
 void hs_offsets_to_device(hs_ctx* c, const int64_t* boff, int32_t nb, int64_t nrows, DBuf& out);
+bool hs_pack_key_tuples(hs_ctx* ctx, const KeySpec& a, int64_t na, const KeySpec& b, int64_t nrows_b, int nk, DBuf& pa,
+                        DBuf& pb);
+// two sorted runs per bucket -> one (merge path); false if the shape is not covered (the caller re-sorts instead)
+bool hs_merge_two_runs(hs_ctx* c, std::vector<DevCol>& a, const int64_t* aoff, std::vector<DevCol>& b, const int64_t* boff_b,
+                       int nk, int32_t nb, std::vector<OutCol>& out, std::vector<int64_t>& out_off);
 
 // ---- the row mover / segmented sort (hs_sort.cu) ----
 struct MoveSet {           // the columns that travel together; all fixed width

@@ -215,7 +215,11 @@ int32_t hs_build_index(hs_ctx* ctx, const hs_column* cols, int32_t ncols,
  * (HS/actions/OptimizeAction.scala:85-99) and the per-side SortExec Spark plans
  * when a bucket has more than one file after an incremental refresh
  * (HS/actions/RefreshIncrementalAction.scala:129-144; asserted in
- * src/test/scala/com/microsoft/hyperspace/index/E2EHyperspaceRulesTest.scala:474-478). */
+ * src/test/scala/com/microsoft/hyperspace/index/E2EHyperspaceRulesTest.scala:474-478).
+ * Every run must be what hs_build_index returns for its rows: rows of bucket b at
+ * [bucket_offsets[b], bucket_offsets[b+1]), sorted on the indexed columns. Fixed-width tables
+ * with NULL-free keys are merged along the merge path (no sort); other shapes are
+ * concatenated and sorted. */
 int32_t hs_merge_runs(hs_ctx* ctx, const hs_index_view* runs, int32_t nruns,
                       hs_table** out);
 

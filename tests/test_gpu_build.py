@@ -187,6 +187,46 @@ def test_merge_runs_equals_rebuild(ctx, oracle):
     parity.check_index(oracle, merged, moff, cols, 1, 50, "merge runs")
 
 
+@pytest.mark.parametrize("by_sort", ["0", "1"])
+def test_merge_path_of_sorted_runs(ctx, oracle, monkeypatch, by_sort):
+    """Fixed-width tables merge along the merge path (no re-sort): keys duplicated inside and across runs,
+    NULLs in included columns, three runs, an empty run, buckets present in one run only, composite and small
+    integer keys, float keys; HSGPU_MERGE_BY_SORT=1 forces the concatenate-and-sort path on the same inputs.
+    Both must equal an index built over all rows."""
+    monkeypatch.setenv("HSGPU_MERGE_BY_SORT", by_sort)
+    rng = np.random.default_rng(8)
+
+    def table(n, kinds):
+        cols = []
+        for kind in kinds:
+            if kind == "i64":
+                cols.append(pa.array(rng.integers(0, 400, size=n) * 7))
+            elif kind == "i32":
+                cols.append(pa.array(rng.integers(-50, 50, size=n).astype(np.int32)))
+            elif kind == "i8":
+                cols.append(pa.array(rng.integers(-5, 5, size=n).astype(np.int8)))
+            elif kind == "f64":
+                cols.append(pa.array(rng.integers(-8, 8, size=n) / 4.0))
+        return cols + [pa.array(rng.random(n), mask=rng.random(n) < 0.2), pa.array(np.arange(n).astype(np.int16))]
+
+    for kinds, nb in ((["i64"], 13), (["i32", "i64"], 8), (["i8"], 4), (["f64", "i8"], 5)):
+        nk = len(kinds)
+        parts = [table(n, kinds) for n in (9000, 2500, 0, 4100)]
+        runs = []
+        for p in parts:
+            g, o = ctx.build_index(p, nk, nb)
+            runs.append((g, nk, o))
+        merged, moff = ctx.merge_runs(runs)
+        allcols = [pa.concat_arrays([p[i] for p in parts]) for i in range(len(parts[0]))]
+        parity.check_index(oracle, merged, moff, allcols, nk, nb, f"merge of 4 runs, key {kinds}, by_sort={by_sort}")
+    # one key only in run A, another only in run B
+    a, oa = ctx.build_index([pa.array([5] * 3000), pa.array(np.arange(3000))], 1, 6)
+    b, ob = ctx.build_index([pa.array([6] * 10), pa.array(np.arange(10))], 1, 6)
+    merged, moff = ctx.merge_runs([(a, 1, oa), (b, 1, ob)])
+    parity.check_index(oracle, merged, moff, [pa.array([5] * 3000 + [6] * 10), pa.array(list(range(3000)) + list(range(10)))],
+                       1, 6, "disjoint buckets")
+
+
 def test_unsupported_inputs_fail_loudly(ctx, hs):
     with pytest.raises(hs.HyperspaceException):
         ctx.build_index([pa.array([1, 2, 3])], 1, 0)
