@@ -15,7 +15,7 @@
 #define LEAF_MAX PT_TILE
 #define MSD_BITS 8
 #define MSD_RADIX 256
-#define MSD_TARGET_ROWS 2800   // aimed-at child size of an MSD level (a leaf holds at most 4096 rows)
+#define MSD_TARGET_ROWS 3300   // aimed-at child size of an MSD level (a leaf holds at most 4096 rows)
 
 // Digit width of the MSD level that splits a segment of `len` rows whose keys still differ in their low
 // `r` bits: as many bits (at most 8) as keep the expected child, len / 2^bits, near MSD_TARGET_ROWS. A huge
