@@ -178,3 +178,116 @@ def test_predicate_parser_and_postfix():
         ("eq", 0, 20), ("ne", 1, "x y"), ("and",), ("ge", 2, 1.5), ("and",)]
     e = ~((Col("a") > 1) | Col("b").isNull())
     assert expr_to_postfix(e, {"a": 0, "b": 1}) == [("gt", 0, 1), ("is_null", 1), ("or",), ("not",)]
+
+
+def test_hybrid_scan_candidates_and_quick_refresh_metadata(tmp_path, oracle):
+    """Plan-level behaviour of hybrid scan (RuleUtils.scala:84-147, 236-262) without touching a GPU: an index
+    whose source gained and lost files is a candidate only with the hybrid-scan switch, only below the
+    appended/deleted ratios, and deleted files need lineage; refreshIndex(name, "quick") records the update in
+    the log entry and makes the index applicable again."""
+    from hyperspace_1_b200 import Hyperspace, Session
+    from hyperspace_1_b200.dataframe import IndexScan
+    from hyperspace_1_b200 import log_entry as le
+    os.makedirs(tmp_path / "t")
+    base = pa.table({"k": pa.array(np.arange(4000)), "v": pa.array(np.arange(4000) * 2.0)})
+    for i in range(8):
+        pq.write_table(base.slice(i * 500, 500), tmp_path / "t" / f"part-{i}.parquet")
+    s = Session(system_path=str(tmp_path / "indexes"))
+    df = s.read_parquet(str(tmp_path / "t"))
+    _fabricate_index(oracle, s, "kIndex", df.plan.relation, ["k"], ["v"], 8)
+    s.enable_hyperspace()
+    q = lambda d: d.filter("k >= 10").select("k", "v")
+    assert "kIndex" in q(df).explain_string()
+    pq.write_table(base.slice(0, 300), tmp_path / "t" / "part-new.parquet")
+    df2 = s.read_parquet(str(tmp_path / "t"))
+    assert "kIndex" not in q(df2).explain_string()                        # signature mismatch
+    s.conf["spark.hyperspace.index.hybridscan.enabled"] = "true"
+    plan = q(df2).optimized_plan()
+    scan = plan.child.child
+    assert isinstance(scan, IndexScan) and [os.path.basename(f) for f in scan.hybrid["appended"]] == ["part-new.parquet"]
+    assert scan.hybrid["deleted_ids"] == [] and "HybridScan: +1 files -0 files" in q(df2).explain_string()
+    s.conf["spark.hyperspace.index.hybridscan.maxAppendedRatio"] = "0.01"
+    assert "kIndex" not in q(df2).explain_string()                        # too much appended data
+    s.conf["spark.hyperspace.index.hybridscan.maxAppendedRatio"] = "0.3"
+    os.remove(tmp_path / "t" / "part-3.parquet")
+    df3 = s.read_parquet(str(tmp_path / "t"))
+    assert "kIndex" not in q(df3).explain_string()                        # deleted file, index without lineage
+    hs = Hyperspace(s)
+    with pytest.raises(Exception):
+        hs.refreshIndex("kIndex", "quick")                                # same rule for the quick refresh
+    # an index WITH lineage: deletes are fine, and a quick refresh stores the update lists
+    e = hs.index("kIndex")
+    e = dict(e, id=2)
+    e["derivedDataset"]["properties"]["properties"]["lineage"] = "true"
+    lm = le.IndexLogManager(str(tmp_path / "indexes" / "kIndex"))
+    assert lm.write_log(2, e)
+    lm.delete_latest_stable_log()
+    lm.create_latest_stable_log(2)
+    plan = q(df3).optimized_plan()
+    assert len(plan.child.child.hybrid["deleted_ids"]) == 1
+    s.conf["spark.hyperspace.index.hybridscan.enabled"] = "false"
+    assert "kIndex" not in q(df3).explain_string()
+    hs.refreshIndex("kIndex", "quick")
+    e2 = hs.index("kIndex")
+    assert e2["state"] == "ACTIVE" and e2["id"] == 4
+    upd = e2["source"]["plan"]["properties"]["relations"][0]["data"]["properties"]["update"]
+    assert [os.path.basename(f["name"]) for f in le.content_files(upd["appendedFiles"])] == ["part-new.parquet"]
+    assert [os.path.basename(f["name"]) for f in le.content_files(upd["deletedFiles"])] == ["part-3.parquet"]
+    assert e2["content"] == e["content"]                                   # metadata only: same index files
+    assert "HybridScan: +1 files -1 files" in q(df3).explain_string()      # applicable again, without the switch
+
+
+def test_parquet_framing_reads_back_with_pyarrow(tmp_path):
+    """parquet_plain.py's Thrift framing with page bodies encoded by hand (numpy) instead of by the device:
+    PLAIN int64 / double / byte-array values and RLE or bit-packed definition levels, two pages per column.
+    pyarrow must read back the rows; this pins the container format on the CPU side."""
+    import struct
+    from hyperspace_1_b200 import log_entry as le, parquet_plain as pp
+
+    def def_levels(valid):
+        n = len(valid)
+        if valid.all():
+            body = bytes([n << 1, 1]) if n < 64 else None
+            if body is None:
+                t = pp._Thrift()
+                t._varint(n << 1)
+                body = bytes(t.b) + b"\x01"
+        else:
+            groups = (n + 7) // 8
+            t = pp._Thrift()
+            t._varint((groups << 1) | 1)
+            body = bytes(t.b) + np.packbits(np.pad(valid, (0, groups * 8 - n)), bitorder="little").tobytes()
+        return struct.pack("<I", len(body)) + body
+
+    cols = {"a": pa.array([1, None, 3, 4, 5, None, 7], type=pa.int64()),
+            "b": pa.array([0.5, 1.5, 2.5, 3.5, 4.5, 5.5, 6.5]),
+            "s": pa.array(["x", "", None, "hello", "wörld", "z", None])}
+    names, types = list(cols), [c.type for c in cols.values()]
+    pages = [(0, 4), (4, 7)]
+    path = tmp_path / "t.parquet"
+    with open(path, "wb") as f:
+        f.write(pp.MAGIC)
+        pos, chunks = 4, []
+        for name, arr in cols.items():
+            start = pos
+            for a, e in pages:
+                part = arr.slice(a, e - a)
+                valid = np.array([v is not None for v in part.to_pylist()])
+                vals = [v for v in part.to_pylist() if v is not None]
+                if pa.types.is_int64(arr.type):
+                    values = np.array(vals, dtype="<i8").tobytes()
+                elif pa.types.is_float64(arr.type):
+                    values = np.array(vals, dtype="<f8").tobytes()
+                else:
+                    values = b"".join(struct.pack("<I", len(v.encode())) + v.encode() for v in vals)
+                body = def_levels(valid) + values
+                hdr = pp.page_header(e - a, len(body))
+                f.write(hdr + body)
+                pos += len(hdr) + len(body)
+            chunks.append((start, pos - start, len(arr)))
+        foot = pp.footer(names, types, 7, chunks, le.schema_json(pa.schema([pa.field(n, t) for n, t in zip(names, types)])))
+        f.write(foot + struct.pack("<I", len(foot)) + pp.MAGIC)
+    got = pq.ParquetFile(path).read()
+    assert got.column_names == names
+    for n in names:
+        assert got[n].to_pylist() == cols[n].to_pylist()
