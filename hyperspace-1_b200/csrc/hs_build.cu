@@ -133,6 +133,70 @@ __global__ void __launch_bounds__(256) k_group_segments(const uint32_t* __restri
   }
 }
 
+// ---- rounds after the first work on the rows of the big groups only, through a compact index space:
+// compact row ci of group g = real row gstart[g] + (ci - cstart[g])
+__global__ void __launch_bounds__(256) k_tie_rowmap(const uint32_t* __restrict__ gstart, const uint32_t* __restrict__ cstart,
+                                                    uint32_t ngroups, uint32_t m, uint32_t* __restrict__ rowmap,
+                                                    uint8_t* __restrict__ cflag) {
+  uint32_t ci = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (; ci < m; ci += stride) {
+    uint32_t lo = 0, hi = ngroups;      // largest g with cstart[g] <= ci
+    while (hi - lo > 1) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (cstart[mid] <= ci) lo = mid; else hi = mid;
+    }
+    rowmap[ci] = gstart[lo] + (ci - cstart[lo]);
+    cflag[ci] = ci == cstart[lo];       // a big group starts here: forced head
+  }
+}
+__global__ void __launch_bounds__(256) k_build_nkey_rows(KeyLayout L, KeySpec ks, const uint32_t* __restrict__ rowmap,
+                                                         uint32_t m, int d, const uint32_t* __restrict__ srcrow,
+                                                         uint64_t* __restrict__ nkey, uint8_t* __restrict__ more) {
+  uint32_t ci = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (; ci < m; ci += stride) {
+    const uint32_t i = rowmap[ci];
+    bool mr = false;
+    nkey[i] = nkey_chunk(L, ks, srcrow[i], d, &mr);
+    more[i] = mr ? 1 : 0;
+  }
+}
+__global__ void __launch_bounds__(256) k_tie_flags_rows(const uint64_t* __restrict__ nkey, const uint8_t* __restrict__ more,
+                                                        const uint32_t* __restrict__ rowmap, uint32_t m,
+                                                        uint8_t* __restrict__ cflag) {
+  uint32_t ci = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (; ci < m; ci += stride) {
+    if (cflag[ci]) continue;
+    const uint32_t i = rowmap[ci];      // not a group start: row i - 1 belongs to the same big group
+    if (nkey[i] != nkey[i - 1] || !more[i]) cflag[ci] = 1;
+  }
+}
+// as k_group_segments, heads given in compact positions; the groups go out in real row positions
+__global__ void __launch_bounds__(256) k_group_segments_rows(const uint32_t* __restrict__ head_pos, const uint64_t* ngroups,
+                                                             uint32_t m, const uint32_t* __restrict__ rowmap,
+                                                             uint32_t* __restrict__ sstart, uint32_t* __restrict__ slen,
+                                                             uint32_t* __restrict__ gstart, uint32_t* __restrict__ glen,
+                                                             uint32_t* counter) {
+  int64_t G = (int64_t)*ngroups;
+  int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; g < G; g += stride) {
+    const uint32_t a = head_pos[g];
+    const uint32_t b = g + 1 < G ? head_pos[g + 1] : m;
+    if (b - a > TIE_SMALL) {
+      uint32_t k = atomicAdd(counter + 1, 1u);
+      gstart[k] = rowmap[a];
+      glen[k] = b - a;
+    } else if (b - a >= 2) {
+      uint32_t k = atomicAdd(counter, 1u);
+      sstart[k] = rowmap[a];
+      slen[k] = b - a;
+    }
+  }
+}
+
 struct TieCols {
   int32_t n, srcrow_col;
   int32_t esize[HS_MAX_MOVE];
@@ -556,7 +620,9 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
     tc.n = ms.n;
     tc.srcrow_col = srcrow_mv;
     for (int i = 0; i < ms.n; i++) { tc.esize[i] = ms.esize[i]; tc.a[i] = ms.a[i]; }
-    for (int d = 0; d < 1 << 20; d++) {
+    // round 0: ties of chunk 0 among all rows
+    uint32_t cnt[2];
+    {
       hs_stage_begin(c, "tie_groups");
       LAUNCH(c, k_tie_flags, grid1d(n), 256, 0, nkey, more, n, flag.as<uint8_t>());
       hs_exclusive_scan_flags(c, flag.as<uint8_t>(), rank.as<uint32_t>(), n, total.as<uint64_t>());
@@ -565,22 +631,56 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
       LAUNCH(c, k_group_segments, grid1d(n), 256, 0, head_pos.as<uint32_t>(), total.as<uint64_t>(), (uint32_t)n,
              sstart.as<uint32_t>(), slen.as<uint32_t>(), gstart.as<uint32_t>(), glen.as<uint32_t>(), counter.as<uint32_t>());
       hs_stage_end(c);
-      uint32_t cnt[2];
       memcpy(cnt, hs_read_wait(c, hs_read_begin(c, counter.p, 8)), 8);
-      if (getenv("HSGPU_TRACE")) fprintf(stderr, "[hsgpu] tie round %d: %u small groups, %u big groups\n", d, cnt[0], cnt[1]);
+      if (getenv("HSGPU_TRACE")) fprintf(stderr, "[hsgpu] tie round 0: %u small groups, %u big groups\n", cnt[0], cnt[1]);
       if (cnt[0]) {
         // small groups are settled for good, whatever the length of the keys
+        Stage st(c, "tie_finish");
+        LAUNCH(c, k_tie_finish, (cnt[0] + 7) / 8, 256, 0, L, ks, tc, sstart.as<uint32_t>(), slen.as<uint32_t>(), cnt[0], 1,
+               flag.as<uint8_t>());
+      }
+    }
+    rank.release();
+    head_pos.release();
+    // Long runs of equal prefixes (duplicates, shared path-like prefixes): next chunk, sorted by the segmented
+    // sort, and another look — only over the rows of those runs, addressed through a compact index space.
+    DBuf gstart2(c, gstart.bytes), glen2(c, glen.bytes);
+    DBuf* gs[2] = {&gstart, &gstart2};
+    DBuf* gl[2] = {&glen, &glen2};
+    int cur = 0;
+    for (int d = 1; cnt[1] > 0 && d < 1 << 20; d++) {
+      const uint32_t G = cnt[1];
+      DBuf cstart(c, (size_t)G * 4), mtot(c, 8);
+      hs_stage_begin(c, "tie_groups");
+      hs_exclusive_scan_u32(c, gl[cur]->as<uint32_t>(), cstart.as<uint32_t>(), G, mtot.as<uint64_t>());
+      const uint32_t m = (uint32_t) * (const uint64_t*)hs_read_wait(c, hs_read_begin(c, mtot.p, 8));
+      DBuf rowmap(c, (size_t)m * 4), cflag(c, (size_t)m), crank(c, (size_t)m * 4), chead(c, (size_t)m * 4), ctotal(c, 8);
+      LAUNCH(c, k_tie_rowmap, grid1d(m), 256, 0, gs[cur]->as<uint32_t>(), cstart.as<uint32_t>(), G, m, rowmap.as<uint32_t>(),
+             cflag.as<uint8_t>());
+      hs_stage_end(c);
+      {
+        Stage st(c, "tie_next_chunk");
+        LAUNCH(c, k_build_nkey_rows, grid1d(m), 256, 0, L, ks, rowmap.as<uint32_t>(), m, d, srcrow, nkey, more);
+      }
+      hs_segmented_sort_list(c, ms, key, 64, gs[cur]->as<uint32_t>(), gl[cur]->as<uint32_t>(), G, n);
+      hs_stage_begin(c, "tie_groups");
+      LAUNCH(c, k_tie_flags_rows, grid1d(m), 256, 0, nkey, more, rowmap.as<uint32_t>(), m, cflag.as<uint8_t>());
+      hs_exclusive_scan_flags(c, cflag.as<uint8_t>(), crank.as<uint32_t>(), m, ctotal.as<uint64_t>());
+      LAUNCH(c, k_head_positions, grid1d(m), 256, 0, cflag.as<uint8_t>(), crank.as<uint32_t>(), (int64_t)m, chead.as<uint32_t>());
+      counter.zero();
+      LAUNCH(c, k_group_segments_rows, grid1d(m), 256, 0, chead.as<uint32_t>(), ctotal.as<uint64_t>(), m, rowmap.as<uint32_t>(),
+             sstart.as<uint32_t>(), slen.as<uint32_t>(), gs[cur ^ 1]->as<uint32_t>(), gl[cur ^ 1]->as<uint32_t>(),
+             counter.as<uint32_t>());
+      hs_stage_end(c);
+      memcpy(cnt, hs_read_wait(c, hs_read_begin(c, counter.p, 8)), 8);
+      if (getenv("HSGPU_TRACE"))
+        fprintf(stderr, "[hsgpu] tie round %d: %u rows in %u big groups -> %u small groups, %u big groups\n", d, m, G, cnt[0], cnt[1]);
+      if (cnt[0]) {
         Stage st(c, "tie_finish");
         LAUNCH(c, k_tie_finish, (cnt[0] + 7) / 8, 256, 0, L, ks, tc, sstart.as<uint32_t>(), slen.as<uint32_t>(), cnt[0],
                d + 1, flag.as<uint8_t>());
       }
-      if (cnt[1] == 0) break;
-      // long runs of equal prefixes: next chunk, sorted by the segmented sort, and another look
-      {
-        Stage st(c, "tie_next_chunk");
-        LAUNCH(c, k_build_nkey, grid1d(n), 256, 0, L, ks, n, d + 1, srcrow, (const uint8_t*)flag.p, nkey, more);
-      }
-      hs_segmented_sort_list(c, ms, key, 64, gstart.as<uint32_t>(), glen.as<uint32_t>(), cnt[1], n);
+      cur ^= 1;
     }
   }
 
