@@ -167,7 +167,7 @@ def reference_arm(args, out):
     line = {"metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic", "impl": "reference",
-            "config": {"workload": "cfg2 lineitem shape, int64 key + 2 float64, 200 buckets", "rows_per_step": n,
+            "config": {"workload": "cfg2 lineitem shape, int64 key + 2 float64, 200 buckets per GPU", "rows_per_step": n,
                        "num_buckets": NUM_BUCKETS},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": f"{n} rows of the cfg2 workload per step (hash, bucket, per-bucket sort, take)"},
