@@ -1,5 +1,7 @@
-// hs_dist.cu — multi-GPU index build: one process per GPU, rows travel once to the GPU that owns
-// their bucket through an NCCL all-to-all over NVLink/NVSwitch; everything after is bucket-local.
+// hs_dist.cu — multi-GPU index build: one process per GPU, rows travel once to the GPU that owns their
+// bucket — stored by the scatter kernel itself into the owners' peer-mapped receive buffers over
+// NVLink/NVSwitch (fused / owner / copy modes, see try_fused), or through an NCCL all-to-all when peers
+// cannot be mapped; everything after is bucket-local.
 // Replaces Spark's ShuffleExchangeExec under df.repartition(numBuckets, cols)
 // (HS/actions/CreateActionBase.scala:129-130) for N > 1 executors.
 // NCCL is bound at run time (dlopen of libnccl.so.2) so that libhsgpu loads on hosts without it.

@@ -3,10 +3,11 @@
 //    df.repartition(numBuckets, cols), HS/actions/CreateActionBase.scala:129-130)
 //  * segmented sort: every bucket sorted on the normalised key (stands in for the SortExec that
 //    FileFormatWriter plans for BucketSpec(n, cols, cols), HS/index/DataFrameWriterExtensions.scala:57-66)
-// One tile kernel does both: rank the tile's rows by an up-to-11-bit digit with warp-private counters,
-// stage each column through shared memory in digit order, write runs out coalesced. The sort is an MSD
-// radix partition (8 bits per level, only segments larger than a tile) finished by an in-shared-memory
-// LSD radix sort of each leaf segment over the bits that actually vary inside it.
+// One tile kernel (k_partition) does both movements: the column slices of a 4096-row tile arrive in shared
+// memory by TMA bulk copies, the rows are ranked by digit (bucket id, or the next key bits) with shared-memory
+// atomics, and every column is written out as runs per digit. The sort is an MSD radix partition (up to 8 bits
+// per level, only for segments larger than a leaf) finished by an in-shared-memory LSD radix sort of each leaf
+// segment over the bits that actually vary inside it (k_leaf_sort32 / k_leaf_sort / k_leaf_small).
 #include <algorithm>
 
 #include "hs_block.cuh"
