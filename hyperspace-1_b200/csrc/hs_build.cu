@@ -524,6 +524,12 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
   int key_mv = -1, more_mv = -1, srcrow_mv = -1;
   std::vector<int> mv_es;
   for (auto& m : mv) mv_es.push_back(m.esize);
+  if (xchg && fast_key && cols[0].type == HS_INT64) {
+    for (size_t i = 0; i < mv.size(); i++)
+      if (mv[i].role == 0 && mv[i].user_col == 0) xchg->key_col = (int)i;
+    xchg->key_min = h_minmax[0];
+    xchg->key_span = h_minmax[1] - h_minmax[0];
+  }
   const bool fused = xchg && xchg->try_fused(c, mv_es);   // rows go straight to their owners' buffers
   for (size_t i = 0; i < mv.size(); i++) {
     if (!fused) mv[i].a.alloc(c, (size_t)n * mv[i].esize + 16);

@@ -320,6 +320,7 @@ struct NcclExchange : BuildExchange {
   int xmode = 0;                     // 0 fused, 1 owner, 2 copy (see try_fused)
   std::vector<int> xes;              // element sizes of the travelling columns (+ the bucket ids in owner mode)
   std::vector<DBuf> owner_sorted;    // owner mode: the received rows, scattered by bucket (the sort's source)
+  bool narrow = false;               // owner mode: the INT64 key travels as u32 (value - minimum)
 
   bool try_fused(hs_ctx* c, const std::vector<int>& esize) override {
     const char* off = getenv("HSGPU_NO_P2P");
@@ -341,6 +342,11 @@ struct NcclExchange : BuildExchange {
     if (mode && !strcmp(mode, "owner")) xmode = 1;
     if (mode && !strcmp(mode, "copy")) xmode = 2;
     xes = esize;
+    // owner mode: an INT64 key whose values span less than 2^32 crosses NVLink as 4 bytes (HSGPU_WIDE_KEYS=1: no)
+    const char* wide = getenv("HSGPU_WIDE_KEYS");
+    narrow = xmode == 1 && key_col >= 0 && key_col < (int)esize.size() && esize[key_col] == 8 &&
+             key_span < 0xFFFFFFFFull && nbl <= 2048 && !(wide && *wide && *wide != '0');
+    if (narrow) xes[key_col] = 4;
     if (xmode == 1) xes.push_back(2);       // the bucket-id column
     if ((int)xes.size() > HS_MAX_PEER_COLS_HOST) return false;
     const int ncol = (int)xes.size();
@@ -440,7 +446,7 @@ struct NcclExchange : BuildExchange {
     int64_t bytes_sent = 0;
     for (int b = 0; b < nb; b++)
       if (owner_of(b, N, nb) != me)
-        for (int i = 0; i < ncol; i++) bytes_sent += (int64_t)all_hist[(size_t)me * nb + b] * esize[i];
+        for (size_t i = 0; i < xes.size(); i++) bytes_sent += (int64_t)all_hist[(size_t)me * nb + b] * xes[i];
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
     CK(cudaEventCreate(&e1));
@@ -459,7 +465,7 @@ struct NcclExchange : BuildExchange {
       xsrc.push_back(d_bucket);
       CK(cudaEventRecord(e0, c->stream));
       hs_bucket_scatter_peers(c, xsrc.data(), xes.data(), ncol + 1, st->peer_ptr.data(), N, d_bucket, n_local, nb,
-                              d_base.as<uint32_t>(), true);
+                              d_base.as<uint32_t>(), true, narrow ? key_col : -1, key_min);
       CK(cudaEventRecord(e1, c->stream));
       hs_sync(c);   // my stores have left this GPU
     } else if (one_kernel) {
@@ -562,7 +568,8 @@ struct NcclExchange : BuildExchange {
       }
       DBuf d_off(c, ((size_t)nbl + 1) * 4);
       CK(cudaMemcpyAsync(d_off.p, seg_off.data(), ((size_t)nbl + 1) * 4, cudaMemcpyHostToDevice, c->stream));
-      hs_bucket_scatter(c, rsrc.data(), ms, (const uint16_t*)st->slots[ncol].ptr, nrecv, nbl, d_off.as<uint32_t>(), blo);
+      hs_bucket_scatter(c, rsrc.data(), ms, (const uint16_t*)st->slots[ncol].ptr, nrecv, nbl, d_off.as<uint32_t>(), blo,
+                        narrow ? key_col : -1, key_min);
       hs_sync(c);   // seg_off is the caller's vector, d_off dies here
       return nrecv;
     }

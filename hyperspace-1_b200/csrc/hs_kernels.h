@@ -27,6 +27,11 @@ struct BuildExchange {
   // peer-mapped memory, so there is no separate all-to-all. try_fused sets up the receive buffers on all ranks
   // (collective; false on every rank if any rank cannot map its peers). scatter_exchange then takes the rows
   // in input order; recv[i] is this rank's receive buffer of column i (persistent, owned by the exchange).
+  // set by the build before try_fused when the sort key is one non-null INT64 column: that moved column, the
+  // mapped (sign-flipped) minimum over all ranks and the span max - min. A span below 2^32 lets the key travel as
+  // 4 bytes (value - minimum) and be widened again by the receiver's bucket scatter.
+  int key_col = -1;
+  uint64_t key_min = 0, key_span = ~0ull;
   virtual bool try_fused(hs_ctx* c, const std::vector<int>& esize) { return false; }
   virtual int64_t scatter_exchange(hs_ctx* c, const void* const* srcs, const std::vector<int>& esize,
                                    const uint16_t* d_bucket, int64_t n_local, std::vector<void*>& recv,
@@ -62,11 +67,14 @@ struct KeySrc {
 
 // Scatter rows from the caller's column buffers (src[i], element sizes as in ms) into bucket-contiguous
 // order in ms.a, given u16 bucket ids and host-known bucket offsets.
+// widen_col >= 0: that column arrives as u32 (value - widen_min of the sign-flipped key) and is written as the
+// original int64 again
 void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, const uint16_t* d_bucket, int64_t n,
-                       int32_t nb, const uint32_t* d_bucket_off, int32_t bucket_base = 0);
+                       int32_t nb, const uint32_t* d_bucket_off, int32_t bucket_base = 0, int widen_col = -1,
+                       uint64_t widen_min = 0);
 void hs_bucket_scatter_peers(hs_ctx* c, const void* const* src, const int32_t* esize, int ncols, void* const* pdst,
                              int nranks, const uint16_t* d_bucket, int64_t n, int32_t nb, const uint32_t* d_run_base,
-                             bool by_owner = false);
+                             bool by_owner = false, int narrow_col = -1, uint64_t narrow_min = 0);
 // Sort every segment [seg_off[s], seg_off[s+1]) of ms.a by the key; result in ms.a. key_bits = significant
 // low bits of the key. d_seg_off: device u32[nseg+1].
 void hs_segmented_sort(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_seg_off,

@@ -121,6 +121,9 @@ struct PartParams {
   int32_t bucket_base;      // MODE 0: subtracted from the bucket id first (ids of a rank's own bucket range)
   int32_t by_owner;         // MODE 2: digit = owner of the bucket (nranks bins) instead of the bucket itself
   int32_t nb_total;         // MODE 2, by_owner: number of buckets of the index
+  int32_t conv_col1;        // 1 + the column converted on the way (0 = none): MODE 2 writes int64 as u32
+                            // ((v ^ sign) - conv_min), MODE 0 reads such u32 and writes the int64 back
+  uint64_t conv_min;
   uint32_t* cursor;         // MODE 0: [radix]; MODE 1: [nseg * 256]
   SegList segs;             // MODE 1: the large segments of this level
   const uint32_t* tile_prefix;  // MODE 1: [nseg + 1]
@@ -179,6 +182,31 @@ __device__ __forceinline__ void scatter_column_peers(const unsigned char* stage,
       T* dst = (T*)pdst[iv >> 12][c];            // the owner's buffer (local or over NVLink)
       dst[gdst[j]] = col[iv & 0xFFFu];
     }
+  }
+}
+
+#define HS_SIGN64 0x8000000000000000ull
+__device__ __forceinline__ void scatter_column_peers_narrow(const unsigned char* stage, uint32_t lead,
+                                                            void* const (*pdst)[HS_MAX_PEER_COLS], int c, uint32_t tile_len,
+                                                            const uint16_t* inv, const uint32_t* gdst, uint64_t mn) {
+  const uint64_t* col = (const uint64_t*)(stage + lead);
+#pragma unroll 4
+  for (int k = 0; k < PT_ITEMS; k++) {
+    uint32_t j = threadIdx.x + k * PT_THREADS;
+    if (j < tile_len) {
+      const uint32_t iv = inv[j];
+      ((uint32_t*)pdst[iv >> 12][c])[gdst[j]] = (uint32_t)((col[iv & 0xFFFu] ^ HS_SIGN64) - mn);
+    }
+  }
+}
+__device__ __forceinline__ void scatter_column_widen(const unsigned char* stage, uint32_t lead, uint64_t* __restrict__ dst,
+                                                     uint32_t tile_len, const uint16_t* inv, const uint32_t* gdst,
+                                                     uint64_t mn) {
+  const uint32_t* col = (const uint32_t*)(stage + lead);
+#pragma unroll 4
+  for (int k = 0; k < PT_ITEMS; k++) {
+    uint32_t j = threadIdx.x + k * PT_THREADS;
+    if (j < tile_len) dst[gdst[j]] = ((uint64_t)col[inv[j]] + mn) ^ HS_SIGN64;
   }
 }
 
@@ -278,7 +306,11 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
     const int c = col_at(i), b = i & 1, es = p.mv.esize[c];
     mbar_wait(&sm.bar[b], (uint32_t)(i >> 1) & 1u);
     const uint32_t lead = slice_lead(p.mv.src[c], es, tile_start);
-    if (MODE == 2) {
+    if (MODE == 2 && c + 1 == p.conv_col1) {
+      scatter_column_peers_narrow(sm.stage[b], lead, p.pdst, c, tile_len, sm.inv, sm.gdst, p.conv_min);
+    } else if (MODE == 0 && c + 1 == p.conv_col1) {
+      scatter_column_widen(sm.stage[b], lead, (uint64_t*)p.mv.dst[c], tile_len, sm.inv, sm.gdst, p.conv_min);
+    } else if (MODE == 2) {
       switch (es) {
         case 8: scatter_column_peers<uint64_t>(sm.stage[b], lead, p.pdst, c, tile_len, sm.inv, sm.gdst); break;
         case 4: scatter_column_peers<uint32_t>(sm.stage[b], lead, p.pdst, c, tile_len, sm.inv, sm.gdst); break;
@@ -968,8 +1000,9 @@ static void launch_bucket_scatter(hs_ctx* c, const PartParams& p, int64_t n) {
 }
 
 void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, const uint16_t* d_bucket, int64_t n,
-                       int32_t nb, const uint32_t* d_bucket_off, int32_t bucket_base) {
+                       int32_t nb, const uint32_t* d_bucket_off, int32_t bucket_base, int widen_col, uint64_t widen_min) {
   if (n == 0) return;
+  if (widen_col >= 0 && nb > 2048) HS_THROW(HS_EINVAL, "a narrowed key cannot pass the two-level scatter");
   if (nb > 8192) HS_THROW(HS_EUNSUPPORTED, "the bucket scatter supports at most 8192 buckets per GPU");
   PartParams p;
   memset(&p, 0, sizeof p);
@@ -1007,6 +1040,11 @@ void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, con
   } else {
     p.mv.n = ms.n;
     for (int i = 0; i < ms.n; i++) { p.mv.esize[i] = ms.esize[i]; p.mv.src[i] = src[i]; p.mv.dst[i] = ms.a[i]; }
+    if (widen_col >= 0) {
+      p.mv.esize[widen_col] = 4;          // what the tile stages; the store widens to 8 bytes
+      p.conv_col1 = widen_col + 1;
+      p.conv_min = widen_min;
+    }
     p.bucket = d_bucket;
   }
   p.radix = nb;
@@ -1020,7 +1058,7 @@ void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, con
 // d_run_base[b] = first row, inside the owner's buffer, of THIS rank's run for bucket b.
 void hs_bucket_scatter_peers(hs_ctx* c, const void* const* src, const int32_t* esize, int ncols, void* const* pdst,
                              int nranks, const uint16_t* d_bucket, int64_t n, int32_t nb, const uint32_t* d_run_base,
-                             bool by_owner) {
+                             bool by_owner, int narrow_col, uint64_t narrow_min) {
   if (n == 0) return;
   if (nb > 8192) HS_THROW(HS_EUNSUPPORTED, "the bucket scatter supports at most 8192 buckets");
   if (ncols > HS_MAX_PEER_COLS || nranks > HS_MAX_PEERS) HS_THROW(HS_EUNSUPPORTED, "too many columns or ranks for the peer scatter");
@@ -1037,6 +1075,11 @@ void hs_bucket_scatter_peers(hs_ctx* c, const void* const* src, const int32_t* e
   // a tile then holds runs of hundreds of rows per destination, which is what NVLink stores want
   p.by_owner = by_owner ? 1 : 0;
   p.nb_total = nb;
+  if (narrow_col >= 0) {
+    p.mv.esize[narrow_col] = 8;           // the source is the int64 column; the store narrows it to 4 bytes
+    p.conv_col1 = narrow_col + 1;
+    p.conv_min = narrow_min;
+  }
   const int32_t radix = by_owner ? nranks : nb;
   p.radix = radix;
   p.radix_pad = ((radix + PT_THREADS - 1) / PT_THREADS) * PT_THREADS;

@@ -20,8 +20,18 @@ import parity  # noqa: E402
 NB = 64
 
 
+NKEYS = int(os.environ.get("HS_DIST_NKEYS", "2"))   # 1: a single non-null int64 key (the lineitem shape)
+
+
 def shard(rank, world, n=30000):
     rng = np.random.default_rng(100 + rank)
+    if NKEYS == 1:
+        # negative and positive keys around a large offset: exercises the sign flip and the subtraction of the
+        # minimum when the key crosses NVLink as 4 bytes
+        k = rng.integers(-70000, 2_000_000_000, size=n) - (1 << 40)
+        v = rng.random(n)
+        vmask = rng.random(n) < (0.05 if rank % 2 == 1 else 0.0)
+        return [pa.array(k), pa.array(v, mask=vmask), pa.array(rng.integers(0, 100, size=n).astype(np.int16))]
     k1 = rng.integers(0, 1 << 12, size=n).astype(np.int32)
     k2 = rng.integers(0, 1 << 30, size=n)
     v = rng.random(n)
@@ -48,26 +58,26 @@ def main():
         dist.init_process_group("gloo")
     cols = shard(rank, world)
     allcols = gather_all(cols)
-    perm, woff = oracle.build_index(allcols, 2, NB)
+    perm, woff = oracle.build_index(allcols, NKEYS, NB)
     want = oracle.take(allcols, perm)
     lo, hi = hsdist.bucket_range(rank, world, NB)
     assert all(hsdist.owner_of(b, world, NB) == rank for b in range(lo, hi))
     if mode == "gloo":
         # the exchange the GPU path performs, spelled out on the host: rows grouped by owner, all-to-all
-        b = oracle.bucket_ids(cols[:2], NB)
+        b = oracle.bucket_ids(cols[:NKEYS], NB)
         own = b.astype(np.int64) * world // NB
         pieces = [[c.take(pa.array(np.nonzero(own == r)[0])).to_pylist() for c in cols] for r in range(world)]
         recv = [None] * world
         dist.all_gather_object(recv, pieces)
         mine = [pa.array(sum((recv[src][rank][i] for src in range(world)), []), type=cols[i].type) for i in range(3)]
-        p2, o2 = oracle.build_index(mine, 2, NB)
+        p2, o2 = oracle.build_index(mine, NKEYS, NB)
         got = oracle.take(mine, p2)
         goff = o2
     else:
         from hyperspace_1_b200 import native
         ctx = native.Context(int(os.environ.get("LOCAL_RANK", rank)))
         hsdist.init_comm(ctx, torch.device("cuda", int(os.environ.get("LOCAL_RANK", rank))))
-        got, goff = hsdist.build_index_dist(ctx, cols, 2, NB)
+        got, goff = hsdist.build_index_dist(ctx, cols, NKEYS, NB)
         sent, ms = ctx.comm_last_exchange()
         assert sent > 0 and ms > 0
         ctx.comm_destroy()
@@ -77,7 +87,7 @@ def main():
     assert np.array_equal(np.diff(goff)[lo:hi], np.diff(woff)[lo:hi])
     a, b_ = int(woff[lo]), int(woff[hi])
     want_mine = [c.slice(a, b_ - a) for c in want]
-    parity.assert_keys_identical(got, want_mine, 2, f"rank {rank}")
+    parity.assert_keys_identical(got, want_mine, NKEYS, f"rank {rank}")
     parity.assert_same_multiset(got, want_mine, goff - goff[lo] * 0, np.concatenate([np.zeros(lo, np.int64), woff[lo:hi + 1] - woff[lo], np.full(NB - hi, woff[hi] - woff[lo])]), f"rank {rank}")
     dist.barrier()
     if rank == 0:
