@@ -174,3 +174,81 @@ def test_join_types_against_pyarrow(oracle):
         key = lambda p: (-1 if p[0] is None else p[0], -1 if p[1] is None else p[1])
         assert sorted(zip(got_l, got_r), key=key) == sorted(zip(want_l, want_r), key=key), how
         assert ooff[-1] == len(li)
+
+
+# ---- a second, independent transcription of SURVEY Appendix A.1/A.2 (plain Python integers), used only here
+def _py_hash_row(values, types):
+    import struct
+    M = 0xFFFFFFFF
+    rotl = lambda x, r: ((x << r) | (x >> (32 - r))) & M
+    mix_k1 = lambda k: (rotl((k * 0xCC9E2D51) & M, 15) * 0x1B873593) & M
+    mix_h1 = lambda h, k: (rotl(h ^ k, 13) * 5 + 0xE6546B64) & M
+
+    def fmix(h, n):
+        h ^= n
+        h ^= h >> 16
+        h = (h * 0x85EBCA6B) & M
+        h ^= h >> 13
+        h = (h * 0xC2B2AE35) & M
+        return h ^ (h >> 16)
+    hash_int = lambda v, s: fmix(mix_h1(s, mix_k1(v & M)), 4)
+    hash_long = lambda v, s: fmix(mix_h1(mix_h1(s, mix_k1(v & M)), mix_k1((v >> 32) & M)), 8)
+
+    def hash_bytes(b, s):
+        h, n = s, len(b)
+        for i in range(0, n - n % 4, 4):
+            h = mix_h1(h, mix_k1(int.from_bytes(b[i:i + 4], "little")))
+        for i in range(n - n % 4, n):
+            h = mix_h1(h, mix_k1((b[i] - 256 if b[i] >= 128 else b[i]) & M))
+        return fmix(h, n)
+    h = 42
+    for v, t in zip(values, types):
+        if v is None:
+            continue
+        if t == "bool":
+            h = hash_int(1 if v else 0, h)
+        elif t in ("i8", "i16", "i32"):
+            h = hash_int(v, h)
+        elif t == "i64":
+            h = hash_long(v & 0xFFFFFFFFFFFFFFFF, h)
+        elif t == "f32":
+            bits = 0x7FC00000 if v != v else struct.unpack("<I", struct.pack("<f", v))[0]
+            h = hash_int(bits, h)
+        elif t == "f64":
+            bits = 0x7FF8000000000000 if v != v else struct.unpack("<Q", struct.pack("<d", v))[0]
+            h = hash_long(bits, h)
+        else:
+            h = hash_bytes(v.encode("utf-8") if isinstance(v, str) else bytes(v), h)
+    return h - (1 << 32) if h >= (1 << 31) else h
+
+
+def test_oracle_against_a_second_transcription_on_random_rows(oracle):
+    """The C oracle and a from-the-spec Python transcription of Murmur3Hash(cols, 42) + pmod agree on 3000 random
+    rows of every key type, with NULLs, NaN, -0.0, empty and multi-byte strings, bytes >= 0x80 in every tail
+    position (the signed-byte rule) — two independent restatements of SURVEY Appendix A.1/A.2."""
+    import numpy as np
+    import pyarrow as pa
+    rng = np.random.default_rng(2024)
+    n = 3000
+    null = lambda p: rng.random(n) < p
+    f32 = rng.standard_normal(n).astype(np.float32)
+    f64 = rng.standard_normal(n)
+    f32[:5] = [np.nan, -0.0, 0.0, np.inf, -np.inf]
+    f64[:5] = [np.nan, -0.0, 0.0, np.inf, -np.inf]
+    alphabet = ["a", "Z", "0", "é", "日", "\\x7f", "ÿ", " "]
+    strs = ["".join(rng.choice(alphabet, size=rng.integers(0, 12))) for _ in range(n)]
+    bins = [bytes(rng.integers(0, 256, size=rng.integers(0, 11)).astype(np.uint8)) for _ in range(n)]
+    cols = [pa.array(rng.random(n) < 0.5, mask=null(0.1)), pa.array(rng.integers(-128, 128, size=n).astype(np.int8)),
+            pa.array(rng.integers(-2**15, 2**15, size=n).astype(np.int16), mask=null(0.1)),
+            pa.array(rng.integers(-2**31, 2**31, size=n).astype(np.int32)),
+            pa.array(rng.integers(-2**63, 2**63 - 1, size=n), mask=null(0.1)), pa.array(f32), pa.array(f64, mask=null(0.1)),
+            pa.array(strs, mask=null(0.1)), pa.array(bins, type=pa.binary())]
+    types = ["bool", "i8", "i16", "i32", "i64", "f32", "f64", "str", "bin"]
+    py = [c.to_pylist() for c in cols]
+    for subset in ([0], [1], [2], [3], [4], [5], [6], [7], [8], [3, 7], [7, 4, 6], list(range(9))):
+        want = np.array([_py_hash_row([py[j][i] for j in subset], [types[j] for j in subset]) for i in range(n)], dtype=np.int64)
+        got = oracle.hash_rows([cols[j] for j in subset]).astype(np.int64)
+        assert np.array_equal(got, want), f"hash of columns {subset} differs"
+        for nb in (1, 7, 200, 8192):
+            b = oracle.bucket_ids([cols[j] for j in subset], nb)
+            assert np.array_equal(b, ((want % nb) + nb) % nb), f"bucket ids of columns {subset}, {nb} buckets"
