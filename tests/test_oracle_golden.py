@@ -252,3 +252,41 @@ def test_oracle_against_a_second_transcription_on_random_rows(oracle):
         for nb in (1, 7, 200, 8192):
             b = oracle.bucket_ids([cols[j] for j in subset], nb)
             assert np.array_equal(b, ((want % nb) + nb) % nb), f"bucket ids of columns {subset}, {nb} buckets"
+
+
+def test_oracle_build_against_python_sorted_on_random_rows(oracle):
+    """hso_build_index against bucket + sort done with Python's sorted() over the same rows: bucket of every row
+    from the second Murmur3 transcription, order inside a bucket ASC NULLS FIRST with NaN greatest, -0.0 == 0.0
+    and strings compared as unsigned bytes."""
+    import math
+    import numpy as np
+    import pyarrow as pa
+    rng = np.random.default_rng(77)
+    n, nb = 4000, 13
+    f = rng.integers(-3, 4, size=n) / 2.0
+    f[rng.random(n) < 0.05] = np.nan
+    f[rng.random(n) < 0.05] = -0.0
+    strs = ["".join(rng.choice(["a", "b", "é", "\\x7f", "ÿ"], size=rng.integers(0, 4))) for _ in range(n)]
+    k0 = pa.array(rng.integers(-5, 6, size=n).astype(np.int32), mask=rng.random(n) < 0.1)
+    k1 = pa.array(f, mask=rng.random(n) < 0.1)
+    k2 = pa.array(strs, mask=rng.random(n) < 0.1)
+    rid = pa.array(np.arange(n))
+    types = ["i32", "f64", "str"]
+    py = [k0.to_pylist(), k1.to_pylist(), k2.to_pylist()]
+
+    def cell_key(v, t):
+        if v is None:
+            return (0,)
+        if t == "f64":
+            return (1, 1, 0.0) if math.isnan(v) else (1, 0, v + 0.0)     # NaN greatest; -0.0 + 0.0 == 0.0
+        if t == "str":
+            return (1, v.encode("utf-8"))
+        return (1, v)
+    perm, off = oracle.build_index([k0, k1, k2, rid], 3, nb)
+    h = [_py_hash_row([py[j][i] for j in range(3)], types) for i in range(n)]
+    bucket = [((x % nb) + nb) % nb for x in h]
+    want_rows = sorted(range(n), key=lambda i: (bucket[i], tuple(cell_key(py[j][i], types[j]) for j in range(3))))
+    assert list(np.diff(off)) == [bucket.count(b) for b in range(nb)]
+    key_of = lambda i: tuple(cell_key(py[j][i], types[j]) for j in range(3))
+    assert [key_of(i) for i in perm.tolist()] == [key_of(i) for i in want_rows]
+    assert sorted(perm.tolist()) == list(range(n))
