@@ -291,3 +291,72 @@ def test_parquet_framing_reads_back_with_pyarrow(tmp_path):
     assert got.column_names == names
     for n in names:
         assert got[n].to_pylist() == cols[n].to_pylist()
+
+
+def test_refresh_and_optimize_decisions_without_a_gpu(tmp_path, oracle):
+    """validate() of the refresh and optimize actions (the parts that decide WHAT to compute) on an index
+    fabricated by the oracle: which source files count as appended / deleted (RefreshActionBase.scala:112-147),
+    no-change refreshes are logged no-ops (NoChangesException), deletes need lineage, and optimize picks the
+    files of buckets holding more than one file, below the size threshold in quick mode
+    (OptimizeAction.scala:115-133)."""
+    import shutil
+    from hyperspace_1_b200 import Hyperspace, HyperspaceException, Session, hyperspace as hsmod, index_writer
+    from hyperspace_1_b200 import log_entry as le
+    os.makedirs(tmp_path / "t")
+    base = pa.table({"k": pa.array(np.arange(3000)), "v": pa.array(np.arange(3000) * 1.5)})
+    for i in range(3):
+        pq.write_table(base.slice(i * 1000, 1000), tmp_path / "t" / f"part-{i}.parquet")
+    s = Session(system_path=str(tmp_path / "indexes"))
+    df = s.read_parquet(str(tmp_path / "t"))
+    _fabricate_index(oracle, s, "kIndex", df.plan.relation, ["k"], ["v"], 4)
+    hs = Hyperspace(s)
+    path = hs._index_path("kIndex")
+    # nothing changed: every mode is a no-op that leaves the log where it is
+    for mode in ("full", "incremental", "quick"):
+        a = hsmod.RefreshAction(s, path, mode)
+        with pytest.raises(hsmod.NoChangesException):
+            a.validate()
+        assert hs.refreshIndex("kIndex", mode) is not None and hs.index("kIndex")["id"] == 1
+    with pytest.raises(HyperspaceException):
+        hs.refreshIndex("kIndex", "sideways")
+    # one file appended, one deleted
+    pq.write_table(base.slice(0, 10), tmp_path / "t" / "part-9.parquet")
+    os.remove(tmp_path / "t" / "part-1.parquet")
+    a = hsmod.RefreshAction(s, path, "full")
+    a.validate()
+    assert [os.path.basename(f) for f in a.appended] == ["part-9.parquet"]
+    assert [os.path.basename(f) for f in a.deleted] == ["part-1.parquet"]
+    assert a.num_buckets == 4 and a.indexed == ["k"] and a.included == ["v"] and not a.lineage
+    for mode in ("incremental", "quick"):
+        with pytest.raises(HyperspaceException, match="lineage"):
+            hsmod.RefreshAction(s, path, mode).validate()
+    # optimize: a second file in buckets 0 and 2 (copies of the first), nothing extra in 1 and 3
+    e = hs.index("kIndex")
+    files = sorted(le.from_uri(f["name"]) for f in le.content_files(e["content"]))
+    by_bucket = {le.bucket_id_of(f): f for f in files}
+    extra = []
+    os.makedirs(os.path.join(path, "v__=1"))
+    for b in (0, 2):
+        dst = os.path.join(path, "v__=1", os.path.basename(by_bucket[b]).replace("part-", "part-x"))
+        shutil.copy(by_bucket[b], dst)
+        extra.append(dst)
+    tracker = le.FileIdTracker()
+    e2 = dict(e, id=2)
+    e2["content"] = le.content_of([le.file_info(f, tracker) for f in files + extra])
+    lm = le.IndexLogManager(path)
+    assert lm.write_log(2, e2)
+    lm.delete_latest_stable_log()
+    lm.create_latest_stable_log(2)
+    o = hsmod.OptimizeAction(s, path, "full")
+    o.validate()
+    assert sorted(le.bucket_id_of(f["name"]) for f in o.to_optimize) == [0, 0, 2, 2]
+    assert sorted(le.bucket_id_of(f["name"]) for f in o.to_ignore) == sorted(set(by_bucket) - {0, 2})
+    s.conf["spark.hyperspace.index.optimize.fileSizeThreshold"] = "1"      # every file is "large": nothing to do
+    with pytest.raises(hsmod.NoChangesException):
+        hsmod.OptimizeAction(s, path, "quick").validate()
+    with pytest.raises(HyperspaceException):
+        hsmod.OptimizeAction(s, path, "sometimes").validate()
+    # the files of the fabricated index group into one run; with the copies, two runs for buckets 0 and 2
+    runs, names, _ = index_writer.read_index(e2)
+    assert names == ["k", "v"] and len(runs) == 2
+    assert (np.diff(runs[1][1]) > 0).tolist() == [b in (0, 2) for b in range(4)]
