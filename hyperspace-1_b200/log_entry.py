@@ -135,15 +135,25 @@ def schema_json(schema):
 
 
 def source_signature(source_file_infos, plan_node_names=("LogicalRelation",)):
-    """IndexSignatureProvider (HS/index/IndexSignatureProvider.scala:44-50): md5(fileSig + planSig) with
-    fileSig folded over the files sorted by path (DefaultFileBasedSource.scala:188-210) and planSig folded over
-    the plan's node names bottom-up (PlanSignatureProvider.scala:36-43)."""
-    fsig = ""
+    """The value RuleUtils.getCandidateIndexes compares (HS/index/rules/RuleUtils.scala:61-76):
+        fold  = foldLeft("") over the files sorted by path of md5Hex(acc + len + mtime + path)
+                                                      (sources/default/DefaultFileBasedSource.scala:188-210)
+        f     = md5Hex(fold)                          (FileBasedSignatureProvider.scala:39-40; None when fold is "")
+        p     = fold over the plan's node names bottom-up of md5Hex(acc + nodeName)
+                                                      (PlanSignatureProvider.scala:36-43)
+        value = md5Hex(f + p)                         (IndexSignatureProvider.scala:44-50)
+    Returns None when the relation has no files (the reference then provides no signature)."""
+    fold = ""
     for fi in sorted(source_file_infos, key=lambda f: f["name"]):
-        fsig = md5_hex(fsig + str(fi["size"]) + str(fi["modifiedTime"]) + fi["name"])
+        fold = md5_hex(fold + str(fi["size"]) + str(fi["modifiedTime"]) + fi["name"])
+    if fold == "":
+        return None
+    fsig = md5_hex(fold)
     psig = ""
     for n in plan_node_names:
         psig = md5_hex(psig + n)
+    if psig == "":
+        return None
     return md5_hex(fsig + psig)
 
 

@@ -78,6 +78,81 @@ def test_signature_changes_when_a_file_changes(tmp_path):
     assert le.md5_hex("") == "d41d8cd98f00b204e9800998ecf8427e"   # HashingUtilsTest
 
 
+def test_signature_is_the_three_step_formula_of_the_reference():
+    """md5Hex(md5Hex(fold over files) + fold over plan nodes): FileBasedSignatureProvider.scala:39-40 applies
+    md5Hex once more to the fold of DefaultFileBasedSource.scala:188-210 before IndexSignatureProvider.scala:44-50
+    joins it with PlanSignatureProvider.scala:36-43. Values below were worked out step by step with hashlib."""
+    import hashlib
+    from hyperspace_1_b200 import log_entry as le
+    md5 = lambda t: hashlib.md5(t.encode()).hexdigest()
+    a = [{"name": "file:/d/f2", "size": 7, "modifiedTime": 6, "id": 1}, {"name": "file:/d/f1", "size": 10, "modifiedTime": 5, "id": 0}]
+    fold = md5(md5("" + "10" + "5" + "file:/d/f1") + "7" + "6" + "file:/d/f2")
+    assert fold == "e9837d664321adf6da7a1cba5b74975e"
+    f = md5(fold)
+    assert f == "414c807ad09f419b7dc4d849b3da5a53"
+    p = md5("" + "LogicalRelation")
+    assert p == "9afbc93584b4d85d5bda90a51959f4c8"
+    assert le.source_signature(a) == md5(f + p) == "17c677285177d3645e7a50190eb312c7"
+    # a plan of two nodes folds bottom-up; no files -> no signature at all
+    assert le.source_signature(a, ("LogicalRelation", "Project")) == md5(f + md5(md5("LogicalRelation") + "Project"))
+    assert le.source_signature([]) is None
+
+
+def test_golden_log_entry_of_the_reference_is_read_and_reproduced(tmp_path):
+    """The 'IndexLogEntry spec example' (HT/index/IndexLogEntryTest.scala:83-185) as a fixture: the log manager
+    reads it, the helpers recover what the reference's test asserts, and an entry made here has the same shape."""
+    from hyperspace_1_b200 import log_entry as le
+    import pyarrow as pa
+    gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "index_log_entry_spec.json")))["entry"]
+    # written the way an index directory holds it, read back through the log manager
+    lm = le.IndexLogManager(str(tmp_path / "idx"))
+    os.makedirs(tmp_path / "idx" / "_hyperspace_log")
+    with open(tmp_path / "idx" / "_hyperspace_log" / "0", "w") as fh:
+        fh.write(le.to_json(gold))
+    got = lm.get_log(0)
+    assert got == gold and lm.get_latest_stable_log()["state"] == "ACTIVE"
+    rel = got["source"]["plan"]["properties"]["relations"][0]
+    files = le.content_files(rel["data"]["properties"]["content"])
+    assert [f["name"] for f in files] == ["test/f1", "test/f2"] and [f["id"] for f in files] == [0, 1]
+    assert sum(f["size"] for f in files) == 200                      # sourceFilesSizeInBytes (:184)
+    deleted = le.content_files(rel["data"]["properties"]["update"]["deletedFiles"])
+    assert [(f["size"], f["modifiedTime"], f["id"]) for f in deleted] == [(10, 10, 2)]
+    assert rel["data"]["properties"]["update"]["appendedFiles"] is None
+    assert json.loads(got["derivedDataset"]["properties"]["schemaString"])["fields"][0]["name"] == "RGUID"
+
+    # an entry made here: the same keys, in the same order, with the same JSON types, all the way down
+    schema = pa.schema([("RGUID", pa.string()), ("Date", pa.string())])
+    src = [{"name": "file:/test/f1", "size": 100, "modifiedTime": 100, "id": 0},
+           {"name": "file:/test/f2", "size": 100, "modifiedTime": 200, "id": 1}]
+    mine = le.make_entry("indexName", ["col1"], ["col2", "col3"], schema, 200, [], ["/rootpath"], src, schema)
+    mine["source"]["plan"]["properties"]["relations"][0]["data"]["properties"]["update"] = {
+        "deletedFiles": le.content_of([{"name": "file:/f1", "size": 10, "modifiedTime": 10, "id": 2}]), "appendedFiles": None}
+
+    def shape(x, path=""):
+        if isinstance(x, dict):
+            return {k: shape(v, path + "/" + k) for k, v in x.items()}
+        if isinstance(x, list):
+            return [shape(x[0], path + "[]")] if x else []
+        return type(x).__name__
+    gs, ms = shape(gold), shape(mine)
+    # directory trees differ in depth (ours start at the filesystem root): compare them apart from subDirs
+    def strip(d):
+        if isinstance(d, dict):
+            return {k: strip(v) for k, v in d.items() if k != "subDirs"}
+        if isinstance(d, list):
+            return [strip(v) for v in d]
+        return d
+    gs, ms = strip(gs), strip(ms)
+    ms["content"]["root"]["files"] = gs["content"]["root"]["files"]
+    ms["source"]["plan"]["properties"]["relations"][0]["data"]["properties"]["content"]["root"]["files"] = \
+        gs["source"]["plan"]["properties"]["relations"][0]["data"]["properties"]["content"]["root"]["files"]
+    ms["source"]["plan"]["properties"]["relations"][0]["data"]["properties"]["update"]["deletedFiles"]["root"]["files"] = \
+        gs["source"]["plan"]["properties"]["relations"][0]["data"]["properties"]["update"]["deletedFiles"]["root"]["files"]
+    assert list(gs.keys()) == list(ms.keys())
+    assert json.dumps(gs) == json.dumps(ms)
+    assert mine["derivedDataset"]["properties"]["schemaString"] == gold["derivedDataset"]["properties"]["schemaString"]
+
+
 def test_log_manager_optimistic_concurrency(tmp_path):
     from hyperspace_1_b200 import log_entry as le
     lm = le.IndexLogManager(str(tmp_path / "idx"))
