@@ -138,39 +138,62 @@ def gen_lineitem_device(torch, n_rows, seed, device):
     return l_orderkey, price, disc, keys
 
 
+def workload_config(n, world, num_buckets):
+    """The `config` object of the line: the same for the native and the reference arm."""
+    return {"workload": "cfg2: TPC-H-shaped lineitem, CoveringIndex on int64 l_orderkey including "
+                        "l_extendedprice,l_discount, 200 buckets per GPU "
+                        "(100 M rows and 200 buckets are added with every GPU: constant bucket size)",
+            "rows_per_gpu": n, "num_buckets": num_buckets, "row_bytes": ROW_BYTES,
+            "l2_policy": "inputs (2.4 GB per step) are larger than L2; no flush needed",
+            "parallelism": f"buckets sharded over {world} GPU(s); rows reach their owners over NVLink peer memory"
+            if world > 1 else "single GPU"}
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
 def reference_arm(args, out):
     """--impl reference: the reference's CPU path for this metric on the host cores. The reference is
     Scala on Spark 2.4.2 and cannot run here (no JVM/Spark in the image), so the timed code is the
-    oracle port of that path (oracle/hs_oracle.c) with every host thread, on a bounded sample."""
+    oracle port of that path (oracle/hs_oracle.c) with every host thread. One step = one build of rank 0's
+    rows of the native arm's workload (rows_per_gpu rows; --ref-rows bounds the sample if a host is too slow)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import numpy as np
-    import pyarrow as pa
     from oracle import oracle
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import fixtures
-    n_orders = max(1, args.ref_rows // 4)
-    cols, _ = fixtures.lineitem(n_orders)
-    n = len(cols[0])
+    cores = oracle.set_threads(host_threads())   # torch.distributed.run exports OMP_NUM_THREADS=1
+    n = args.ref_rows if args.ref_rows > 0 else args.rows
+    cols, _ = fixtures.lineitem(max(1, n // 4), rows=n)
+    assert len(cols[0]) == n
+    arrays = [c.to_numpy(zero_copy_only=False) for c in cols]
+    outs = [np.empty_like(a) for a in arrays]
+
+    def one():
+        perm, off = oracle.build_index(cols, 1, NUM_BUCKETS)
+        for a, o in zip(arrays, outs):   # the build also materialises the index columns in their new order
+            oracle.take_fixed(a, perm, o)
     for _ in range(max(0, min(args.warmup, 1))):
-        oracle.build_index(cols, 1, NUM_BUCKETS)
+        one()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        perm, off = oracle.build_index(cols, 1, NUM_BUCKETS)
-        # the build also materialises the index columns in their new order
-        for c in cols:
-            np.take(c.to_numpy(zero_copy_only=False), perm)
+        one()
     dt = time.perf_counter() - t0
     v = n * args.steps / dt
-    cores = oracle.num_threads()
+    sample = (f"{n} rows per step = " + ("one GPU's share of the workload (rows_per_gpu)" if n == args.rows else
+              f"a bounded sample of the {args.rows} rows_per_gpu") + "; hash, bucket, per-bucket sort, take; "
+              f"{cores} OpenMP threads")
     line = {"metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic", "impl": "reference",
-            "config": {"workload": "cfg2 lineitem shape, int64 key + 2 float64, 200 buckets per GPU", "rows_per_step": n,
-                       "num_buckets": NUM_BUCKETS},
-            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                             "sample": f"{n} rows of the cfg2 workload per step (hash, bucket, per-bucket sort, take)"},
+            "config": workload_config(args.rows, max(1, args.gpus), NUM_BUCKETS),
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "note": "reference Spark local[*]: unavailable on this box (no JVM/Spark); timed = oracle port"}
     print(json.dumps(line), file=out, flush=True)
@@ -193,7 +216,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native")
     ap.add_argument("--rows", type=int, default=100_000_000, help="rows per GPU per step")
-    ap.add_argument("--ref-rows", type=int, default=10_000_000, help="rows per step of the CPU arms")
+    ap.add_argument("--ref-rows", type=int, default=0,
+                    help="rows per step of the CPU arms (0 = the same rows per step as one GPU of the native arm)")
     ap.add_argument("--e2e-steps", type=int, default=3, help="end-to-end steps per host thread")
     ap.add_argument("--e2e-threads", type=int, default=3, help="host threads (contexts) of the end-to-end leg at N=1")
     ap.add_argument("--buckets", type=int, default=0,
@@ -483,14 +507,16 @@ def main():
     if rank == 0 and world == 1 and not args.no_cpu:
         import pyarrow as pa
         from oracle import oracle
-        m = min(args.ref_rows, n)
+        m = min(args.ref_rows, n) if args.ref_rows > 0 else n
+        cores = oracle.set_threads(host_threads())
         sample = [pa.array(key[:m].cpu().numpy()), pa.array(price[:m].cpu().numpy()), pa.array(disc[:m].cpu().numpy())]
+        arrays = [c.to_numpy(zero_copy_only=False) for c in sample]
         t0 = time.perf_counter()
         perm, _ = oracle.build_index(sample, 1, NUM_BUCKETS)
-        for c in sample:
-            np.take(c.to_numpy(zero_copy_only=False), perm)
+        for a in arrays:
+            oracle.take_fixed(a, perm)
         dt = time.perf_counter() - t0
-        cpu = {"value": m / dt, "unit": UNIT, "cores": oracle.num_threads(), "kind": "port",
+        cpu = {"value": m / dt, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": f"first {m} rows of the same workload, one pass (hash, bucket, per-bucket sort, take)",
                "seconds": dt}
 
@@ -498,13 +524,7 @@ def main():
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-                "config": {"workload": "cfg2: TPC-H-shaped lineitem, CoveringIndex on int64 l_orderkey including "
-                                       "l_extendedprice,l_discount, 200 buckets per GPU "
-                                       "(100 M rows and 200 buckets are added with every GPU: constant bucket size)",
-                           "rows_per_gpu": n, "num_buckets": NUM_BUCKETS, "row_bytes": ROW_BYTES,
-                           "l2_policy": "inputs (2.4 GB per step) are larger than L2; no flush needed",
-                           "parallelism": f"buckets sharded over {world} GPU(s); rows reach their owners over NVLink peer memory"
-                           if world > 1 else "single GPU"},
+                "config": workload_config(n, world, NUM_BUCKETS),
                 "roofline": roofline, "build_roofline": build_roofline, "stages": per_stage,
                 "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "join": join,
                 "filter": filt}

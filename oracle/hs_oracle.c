@@ -282,12 +282,33 @@ int32_t hso_build_index(const hs_column* cols, int32_t ncols, int32_t n_indexed,
   if (!b) return HS_ENOMEM;
   int32_t st = hso_bucket_ids(cols, n_indexed, nb, b);
   if (st) { free(b); return st; }
-  memset(out_bucket_offsets, 0, (size_t)(nb + 1) * sizeof(int64_t));
-  for (int64_t i = 0; i < n; i++) out_bucket_offsets[b[i] + 1]++;
-  for (int32_t k = 0; k < nb; k++) out_bucket_offsets[k + 1] += out_bucket_offsets[k];
-  int64_t* cur = (int64_t*)malloc((size_t)nb * sizeof(int64_t));
-  memcpy(cur, out_bucket_offsets, (size_t)nb * sizeof(int64_t));
-  for (int64_t i = 0; i < n; i++) out_perm[cur[b[i]]++] = i;   /* stable partition */
+  /* stable partition by bucket, parallel over contiguous row chunks: chunk t counts its rows per bucket,
+   * the (bucket, chunk) counts are scanned bucket-major, and every chunk then writes its rows in input
+   * order behind the rows of the chunks before it — the same output as the serial loop. */
+  int nt = omp_get_max_threads();
+  if (nt < 1) nt = 1;
+  if (n < (int64_t)nt * 4096) nt = 1;
+  int64_t* cur = (int64_t*)calloc((size_t)nt * (size_t)nb, sizeof(int64_t));
+  if (!cur) { free(b); return HS_ENOMEM; }
+  int64_t chunk = (n + nt - 1) / nt;
+#pragma omp parallel for schedule(static, 1) num_threads(nt)
+  for (int t = 0; t < nt; t++) {
+    int64_t i0 = (int64_t)t * chunk, i1 = i0 + chunk < n ? i0 + chunk : n;
+    int64_t* c = cur + (size_t)t * nb;
+    for (int64_t i = i0; i < i1; i++) c[b[i]]++;
+  }
+  int64_t run = 0;
+  for (int32_t k = 0; k < nb; k++) {
+    out_bucket_offsets[k] = run;
+    for (int t = 0; t < nt; t++) { int64_t c = cur[(size_t)t * nb + k]; cur[(size_t)t * nb + k] = run; run += c; }
+  }
+  out_bucket_offsets[nb] = run;
+#pragma omp parallel for schedule(static, 1) num_threads(nt)
+  for (int t = 0; t < nt; t++) {
+    int64_t i0 = (int64_t)t * chunk, i1 = i0 + chunk < n ? i0 + chunk : n;
+    int64_t* c = cur + (size_t)t * nb;
+    for (int64_t i = i0; i < i1; i++) out_perm[c[b[i]]++] = i;
+  }
   free(cur); free(b);
   return hso_sort_segments(cols, n_indexed, out_bucket_offsets, nb, out_perm, use_radix);
 }
@@ -436,4 +457,34 @@ int32_t hso_num_threads(void) {
 #else
   return 1;
 #endif
+}
+
+/* libgomp reads OMP_NUM_THREADS once, when it is loaded; launchers such as torch.distributed.run export
+ * OMP_NUM_THREADS=1. The timed CPU legs of bench.py call this to use every host core regardless. */
+int32_t hso_set_threads(int32_t n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+  return omp_get_max_threads();
+#else
+  (void)n;
+  return 1;
+#endif
+}
+
+/* dst[i] = src[perm[i]] for a fixed-width column (esize 1, 2, 4 or 8): the materialisation of an index column
+ * in its new order, parallel over the output rows (the timed CPU legs of bench.py use it instead of a
+ * single-threaded numpy take). */
+int32_t hso_take_fixed(const void* src, int32_t esize, const int64_t* perm, int64_t n, void* dst) {
+  if (esize != 1 && esize != 2 && esize != 4 && esize != 8) return HS_EINVAL;
+#pragma omp parallel for schedule(static)
+  for (int64_t i = 0; i < n; i++) {
+    int64_t r = perm[i];
+    switch (esize) {
+      case 8: ((uint64_t*)dst)[i] = ((const uint64_t*)src)[r]; break;
+      case 4: ((uint32_t*)dst)[i] = ((const uint32_t*)src)[r]; break;
+      case 2: ((uint16_t*)dst)[i] = ((const uint16_t*)src)[r]; break;
+      default: ((uint8_t*)dst)[i] = ((const uint8_t*)src)[r]; break;
+    }
+  }
+  return HS_OK;
 }

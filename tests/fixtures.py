@@ -44,12 +44,21 @@ def sample_table():
                      "clicks": pa.array([r[4] for r in SAMPLE_DATA], pa.int32())})
 
 
-def lineitem(n_orders, seed=20240601, null_frac=0.0):
-    """cfg2-shaped rows: sparse TPC-H order keys, each repeated 1..7 times, shuffled."""
+def lineitem(n_orders, seed=20240601, null_frac=0.0, rows=None):
+    """cfg2-shaped rows: sparse TPC-H order keys, each repeated 1..7 times, shuffled.
+    rows: adjust the repeat counts so that exactly that many rows come out (as the survey's 100 M)."""
     rng = np.random.Generator(np.random.PCG64(seed))
     o = np.arange(n_orders, dtype=np.int64)
     keys = (o // 8) * 32 + o % 8 + 1
     reps = rng.integers(1, 8, size=n_orders)
+    if rows is not None:
+        diff = int(rows) - int(reps.sum())
+        step = 1 if diff > 0 else -1
+        while diff != 0:
+            cand = np.nonzero((reps >= (1 if step > 0 else 2)) & (reps <= (6 if step > 0 else 7)))[0][: abs(diff)]
+            assert len(cand), "cannot reach the requested row count with 1..7 repeats per order"
+            reps[cand] += step
+            diff -= step * len(cand)
     l_orderkey = np.repeat(keys, reps)
     rng.shuffle(l_orderkey)
     n = len(l_orderkey)
