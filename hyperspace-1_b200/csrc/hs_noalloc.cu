@@ -95,6 +95,9 @@ extern "C" int32_t hs_bucket_histogram_noalloc(hs_ctx* ctx, const hs_column* key
     HS_THROW(HS_EINVAL, "num_buckets %d is beyond the %d counters of the built-in scratch of "
              "hs_bucket_histogram_noalloc; use hs_hash_bucket or hs_build_index", num_buckets, HS_NOALLOC_MAX_BUCKETS);
   const int64_t n = keys[0].length;
+  // the counters, in shared memory, in the scratch array and in out_counts, are 32 bits wide
+  if (n >= 0xFFFFFFF0ll)
+    HS_THROW(HS_EUNSUPPORTED, "hs_bucket_histogram_noalloc takes fewer than 2^32-16 rows per call (got %lld)", (long long)n);
   KeySpec ks;
   memset(&ks, 0, sizeof ks);
   ks.nkeys = nkeys;

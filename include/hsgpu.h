@@ -189,7 +189,8 @@ int32_t hs_hash_rows(hs_ctx* ctx, const hs_column* keys, int32_t nkeys,
  * RMM-style allocator sized to the GPU), or a thread that may not trigger the device-wide
  * synchronisation cudaMalloc/cudaFree imply. The histogram counters live in a fixed 32 KiB array
  * inside the library image, so num_buckets is limited to HS_NOALLOC_MAX_BUCKETS = 8192 (larger
- * values return HS_EINVAL). Key buffers and out_bucket_ids (int32 per row) must be device memory;
+ * values return HS_EINVAL), and its counters are 32 bits wide, so a call takes fewer than 2^32-16
+ * rows (more returns HS_EUNSUPPORTED). Key buffers and out_bucket_ids (int32 per row) must be device memory;
  * out_counts (num_buckets uint32) may be host or device memory. All calls on a GPU share the
  * array: do not let two of them overlap. The first call on a device resolves the array's device
  * address; make that call outside of stream capture. Same bucket ids as hs_hash_bucket. */
