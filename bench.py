@@ -225,6 +225,7 @@ def main():
                          "stays that of the 1-GPU configuration as rows are added with GPUs)")
     ap.add_argument("--no-join", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-check", action="store_true", help="skip the untimed check of one more build")
     args = ap.parse_args()
     global NUM_BUCKETS
     NUM_BUCKETS = args.buckets if args.buckets > 0 else BUCKETS_PER_GPU * max(1, args.gpus)
@@ -343,6 +344,19 @@ def main():
     build_gbs = ALGO_BYTES_PER_ROW * n / (ms_step * 1e-3) / 1e9
     build_roofline = {"algorithmic_bytes_per_row": ALGO_BYTES_PER_ROW, "achieved": build_gbs, "unit": "GB/s",
                       "frac_of_measured_peak": build_gbs / peak, "frac_of_8TBs": build_gbs / 8000.0}
+
+    # ---- outside the timing: one more build, checked (every rank; results all-reduced)
+    index_check = None
+    if not args.no_check:
+        from oracle import oracle as _oracle   # the checker only
+        from tools import index_check as ic
+        tchk = step()
+        torch.cuda.synchronize()
+        outs = ic.table_tensors(torch, tchk, [torch.int64, torch.float64, torch.float64], dev)
+        index_check = ic.check_index(torch, _oracle, outs, tchk.bucket_offsets(), [key, price, disc], 1, NUM_BUCKETS,
+                                     rank, world, dist)
+        del outs
+        tchk.free()
 
     # ---- e2e: the same build through the C ABI with HOST buffers (pinned in, pinned out)
     e2e = None
@@ -527,7 +541,7 @@ def main():
                 "config": workload_config(n, world, NUM_BUCKETS),
                 "roofline": roofline, "build_roofline": build_roofline, "stages": per_stage,
                 "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "join": join,
-                "filter": filt}
+                "filter": filt, "dist_check" if world > 1 else "index_check": index_check}
         if use_dist and xchg:
             b = sum(x[0] for x in xchg) / len(xchg)
             ms = sum(x[1] for x in xchg) / len(xchg)

@@ -25,7 +25,7 @@ def _dev_tensor(torch, col, dtype, n):
     return torch.as_tensor(a, device="cuda")
 
 
-def test_cfg2_build_and_cfg3_join_properties(hs):
+def test_cfg2_build_and_cfg3_join_properties(hs, oracle):
     import torch
     import bench
     from hyperspace_1_b200 import abi
@@ -56,11 +56,10 @@ def test_cfg2_build_and_cfg3_join_properties(hs):
     desc = (k[1:] < k[:-1]).nonzero().flatten() + 1
     starts = torch.as_tensor(boff[1:-1], device=dev)
     assert bool(torch.isin(desc, starts).all()), "a bucket is not sorted"
-    # (3) every row is in the bucket its key hashes to
-    bid = torch.empty(n, dtype=torch.int32, device=dev)
-    kcs = abi.DeviceColumnSet([{"type": abi.HS_INT64, "length": n, "data": t.column(0).data}])
-    st = ctx._lib.hs_hash_bucket(ctx._h, kcs.ptr(), C.c_int32(1), C.c_int32(200), C.c_void_p(bid.data_ptr()))
-    assert st == 0
+    # (3) every row is in the bucket its key hashes to: bucket ids recomputed by the ORACLE on the host over the
+    # whole key column of the result (the invariant of HT/index/DataFrameWriterExtensionsTest.scala:136-145)
+    import pyarrow as pa
+    bid = torch.from_numpy(oracle.bucket_ids([pa.array(k.cpu().numpy())], 200)).to(dev)
     want = torch.repeat_interleave(torch.arange(200, dtype=torch.int32, device=dev),
                                    torch.as_tensor(np.diff(boff), device=dev))
     assert bool((bid == want).all()), "a row is in the wrong bucket"
@@ -97,7 +96,7 @@ def test_cfg2_build_and_cfg3_join_properties(hs):
     ctx.close()
 
 
-def test_cfg5_shape_composite_key_properties(hs):
+def test_cfg5_shape_composite_key_properties(hs, oracle):
     """cfg5 per-GPU shape at 50 M rows: (k1:int32 < 2^20, k2:int64 < 2^40, v:float64), 8192 buckets —
     lexicographic order inside every bucket, bucket membership, checksums."""
     import torch
@@ -128,10 +127,8 @@ def test_cfg5_shape_composite_key_properties(hs):
     bad = ((o1[1:] < o1[:-1]) | ((o1[1:] == o1[:-1]) & (o2[1:] < o2[:-1]))).nonzero().flatten() + 1
     starts = torch.as_tensor(boff[1:-1], device=dev)
     assert bool(torch.isin(bad, starts).all()), "a bucket is not sorted on (k1, k2)"
-    bid = torch.empty(n, dtype=torch.int32, device=dev)
-    kcs = abi.DeviceColumnSet([{"type": abi.HS_INT32, "length": n, "data": t.column(0).data},
-                               {"type": abi.HS_INT64, "length": n, "data": t.column(1).data}])
-    assert ctx._lib.hs_hash_bucket(ctx._h, kcs.ptr(), C.c_int32(2), C.c_int32(nb), C.c_void_p(bid.data_ptr())) == 0
+    import pyarrow as pa
+    bid = torch.from_numpy(oracle.bucket_ids([pa.array(o1.cpu().numpy()), pa.array(o2.cpu().numpy())], nb)).to(dev)
     want = torch.repeat_interleave(torch.arange(nb, dtype=torch.int32, device=dev), torch.as_tensor(np.diff(boff), device=dev))
     assert bool((bid == want).all()), "a row is in the wrong bucket"
     t.free()

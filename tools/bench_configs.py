@@ -243,8 +243,23 @@ def run_cfg5(args):
     ms_join, tj = timed(lambda: ctx.join_table(vm, vd, [0, 1, 2], [2]), args.steps, 1, True)
     out_rows = total(tj.nrows)
     merged_rows = total(tm.nrows)
-    # sanity: every delta row finds itself in the merged index
+    # every delta row finds itself in the merged index ...
     ok = out_rows >= nd * world and merged_rows == (n + nd) * world and rows_owned == n * world
+    # ... and the three indexes hold what they should (tools/index_check.py: owner ranges, order inside every
+    # bucket, bucket of a 1 M-row sample per rank recomputed by the oracle, row count and checksums over all ranks)
+    from oracle import oracle as _oracle   # the checker only
+    from tools import index_check as ic
+    dts = [torch.int32, torch.int64, torch.float64]
+    dd = dist if world > 1 else None
+    torch.cuda.synchronize()
+    checks = {
+        "base": ic.check_index(torch, _oracle, ic.table_tensors(torch, tb, dts, dev), tb.bucket_offsets(), list(base),
+                               2, nb, rank, world, dd),
+        "refresh_delta": ic.check_index(torch, _oracle, ic.table_tensors(torch, td, dts, dev), td.bucket_offsets(),
+                                        list(delta), 2, nb, rank, world, dd),
+        "merged": ic.check_index(torch, _oracle, ic.table_tensors(torch, tm, dts, dev), tm.bucket_offsets(),
+                                 [torch.cat([a, b]) for a, b in zip(base, delta)], 2, nb, rank, world, dd)}
+    ok = ok and all(c["ok"] for c in checks.values())
     for t in (tj, tm, td, tb):
         t.free()
     if rank == 0:
@@ -256,7 +271,8 @@ def run_cfg5(args):
                 "refresh_incremental_ms": ms_delta, "refresh_rows_per_s": nd * world / (ms_delta * 1e-3),
                 "merge_two_runs_ms": ms_merge, "merge_rows_per_s": (n + nd) * world / (ms_merge * 1e-3),
                 "join_merged_x_delta_ms": ms_join, "join_output_rows": out_rows,
-                "join_output_rows_per_s": out_rows / (ms_join * 1e-3), "checks_ok": bool(ok)}
+                "join_output_rows_per_s": out_rows / (ms_join * 1e-3), "checks_ok": bool(ok),
+                "index_checks": checks}
         line["build_stages_ms_rank0"] = stages
         if xb:
             line["exchange_bytes_ms_rank0"] = xb
