@@ -52,6 +52,12 @@ __device__ __forceinline__ uint64_t load_key(const MoveArgs& mv, const KeySrc& k
   return ((uint64_t)(int64_t)((const int32_t*)p)[row] ^ 0x8000000000000000ull) - ks.min;
 }
 
+__device__ __forceinline__ uint64_t load_key_at(const void* p, const KeySrc& ks, uint32_t row) {
+  if (ks.mode == KS_U64) return ((const uint64_t*)p)[row];
+  if (ks.mode == KS_I64) return (((const uint64_t*)p)[row] ^ 0x8000000000000000ull) - ks.min;
+  return ((uint64_t)(int64_t)((const int32_t*)p)[row] ^ 0x8000000000000000ull) - ks.min;
+}
+
 // ---- TMA (bulk async copy) + mbarrier helpers: contiguous column slices global -> shared memory
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -216,31 +222,14 @@ __device__ __forceinline__ void scatter_column_widen(const unsigned char* stage,
 // per buffer); rows are ranked by digit with shared-memory atomics; one global atomicAdd per (tile, digit)
 // reserves the output run; every column is then read through the tile permutation and written as
 // contiguous runs per digit.
+// The tile body shared by the three launch modes and by the pipelined sort kernel. dst_bias is added (mod 2^32) to
+// every destination row: the pipelined sort writes an MSD level into a small re-used scratch area instead of
+// the rows' own positions.
 template <int MODE>
-__global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_constant__ PartParams p) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
+__device__ __forceinline__ void partition_tile(const PartParams& p, unsigned char* smem_raw, uint32_t tile_start,
+                                               uint32_t tile_len, int bits, uint32_t shift, uint64_t seg_base,
+                                               uint32_t* cursor, uint32_t dst_bias) {
   TileSmem sm = carve(smem_raw, p.radix_pad);
-  uint32_t tile_start, tile_len, shift = 0;
-  uint64_t seg_base = 0;
-  int bits = p.bits;
-  uint32_t* cursor = p.cursor;
-  if (MODE == 0 || MODE == 2) {
-    tile_start = blockIdx.x * (uint32_t)PT_TILE;
-    uint32_t left = p.n - tile_start;
-    tile_len = left < PT_TILE ? left : PT_TILE;
-  } else {
-    uint32_t s = find_segment(p.tile_prefix, p.nseg, blockIdx.x);
-    uint32_t t = blockIdx.x - p.tile_prefix[s];
-    uint32_t slen = p.segs.len[s];
-    tile_start = p.segs.start[s] + t * PT_TILE;
-    uint32_t left = slen - t * PT_TILE;
-    tile_len = left < PT_TILE ? left : PT_TILE;
-    uint32_t sh = p.segs.shift[s];
-    bits = msd_bits(slen, sh);
-    shift = sh - bits;
-    seg_base = p.segs.base[s];
-    cursor = p.cursor + (size_t)s * MSD_RADIX;
-  }
   const int ncols = p.mv.n;
   // column order: in MODE 1 the key column goes first (its slice also feeds the digits)
   const int first = MODE == 1 ? p.key.col : 0;
@@ -294,7 +283,7 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
 #pragma unroll
   for (int k = 0; k < PT_ITEMS; k++) {
     if ((vmask >> k) & 1u) {
-      sm.gdst[pos[k]] = sm.gbase[digit[k]] + pos[k] - sm.cnt[digit[k]];
+      sm.gdst[pos[k]] = sm.gbase[digit[k]] + pos[k] - sm.cnt[digit[k]] + dst_bias;
       uint32_t iv = threadIdx.x + k * PT_THREADS;
       if (MODE == 2)
         iv |= (p.by_owner ? digit[k] : (uint32_t)(((uint64_t)digit[k] * (uint32_t)p.nranks) / (uint32_t)p.radix)) << 12;
@@ -332,7 +321,58 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
   }
 }
 
+template <int MODE>
+__global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_constant__ PartParams p) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  uint32_t tile_start, tile_len, shift = 0;
+  uint64_t seg_base = 0;
+  int bits = p.bits;
+  uint32_t* cursor = p.cursor;
+  if (MODE == 0 || MODE == 2) {
+    tile_start = blockIdx.x * (uint32_t)PT_TILE;
+    uint32_t left = p.n - tile_start;
+    tile_len = left < PT_TILE ? left : PT_TILE;
+  } else {
+    uint32_t s = find_segment(p.tile_prefix, p.nseg, blockIdx.x);
+    uint32_t t = blockIdx.x - p.tile_prefix[s];
+    uint32_t slen = p.segs.len[s];
+    tile_start = p.segs.start[s] + t * PT_TILE;
+    uint32_t left = slen - t * PT_TILE;
+    tile_len = left < PT_TILE ? left : PT_TILE;
+    uint32_t sh = p.segs.shift[s];
+    bits = msd_bits(slen, sh);
+    shift = sh - bits;
+    seg_base = p.segs.base[s];
+    cursor = p.cursor + (size_t)s * MSD_RADIX;
+  }
+  partition_tile<MODE>(p, smem_raw, tile_start, tile_len, bits, shift, seg_base, cursor, 0u);
+}
+
 // per-segment digit histogram of one MSD level
+__device__ __forceinline__ void msd_hist_tile(const MoveArgs& mv, const KeySrc& key, uint32_t tile_start,
+                                              uint32_t tile_len, uint64_t seg_base, uint32_t shift, int bits,
+                                              uint32_t* hist /* shared, MSD_RADIX */, uint32_t* cursor) {
+  if (threadIdx.x < MSD_RADIX) hist[threadIdx.x] = 0;
+  __syncthreads();
+  // all keys of the thread first (independent loads), then the shared-memory updates
+  uint64_t kk[PT_ITEMS];
+#pragma unroll
+  for (int k = 0; k < PT_ITEMS; k++) {
+    const uint32_t j = threadIdx.x + k * PT_THREADS;
+    kk[k] = j < tile_len ? load_key(mv, key, tile_start + j) : 0;
+  }
+#pragma unroll
+  for (int k = 0; k < PT_ITEMS; k++) {
+    const uint32_t j = threadIdx.x + k * PT_THREADS;
+    if (j < tile_len) atomicAdd(&hist[(uint32_t)((kk[k] - seg_base) >> shift) & ((1u << bits) - 1u)], 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x < MSD_RADIX) {
+    uint32_t v = hist[threadIdx.x];
+    if (v) atomicAdd(&cursor[threadIdx.x], v);
+  }
+}
+
 __global__ void __launch_bounds__(PT_THREADS) k_msd_hist(const __grid_constant__ PartParams p) {
   __shared__ uint32_t hist[MSD_RADIX];
   uint32_t s = find_segment(p.tile_prefix, p.nseg, blockIdx.x);
@@ -343,27 +383,8 @@ __global__ void __launch_bounds__(PT_THREADS) k_msd_hist(const __grid_constant__
   uint32_t tile_len = left < PT_TILE ? left : PT_TILE;
   uint32_t sh = p.segs.shift[s];
   int bits = msd_bits(slen, sh);
-  uint32_t shift = sh - bits;
-  const uint64_t seg_base = p.segs.base[s];
-  if (threadIdx.x < MSD_RADIX) hist[threadIdx.x] = 0;
-  __syncthreads();
-  // all keys of the thread first (independent loads), then the shared-memory updates
-  uint64_t kk[PT_ITEMS];
-#pragma unroll
-  for (int k = 0; k < PT_ITEMS; k++) {
-    const uint32_t j = threadIdx.x + k * PT_THREADS;
-    kk[k] = j < tile_len ? load_key(p.mv, p.key, tile_start + j) : 0;
-  }
-#pragma unroll
-  for (int k = 0; k < PT_ITEMS; k++) {
-    const uint32_t j = threadIdx.x + k * PT_THREADS;
-    if (j < tile_len) atomicAdd(&hist[(uint32_t)((kk[k] - seg_base) >> shift) & ((1u << bits) - 1u)], 1u);
-  }
-  __syncthreads();
-  if (threadIdx.x < MSD_RADIX) {
-    uint32_t v = hist[threadIdx.x];
-    if (v) atomicAdd(&p.cursor[(size_t)s * MSD_RADIX + threadIdx.x], v);
-  }
+  msd_hist_tile(p.mv, p.key, tile_start, tile_len, p.segs.base[s], sh - bits, bits, hist,
+                p.cursor + (size_t)s * MSD_RADIX);
 }
 
 #define SMALL_MAX 64   // segments up to this many rows are sorted by one warp each (k_leaf_small)
@@ -490,8 +511,9 @@ struct LeafParams {
 
 // Sort one segment of at most LEAF_MAX rows entirely in shared memory: LSD radix over the bits that
 // vary inside the segment (min/max of its keys), 8 bits per pass, stable; then move every column.
-__global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort(const __grid_constant__ LeafParams p) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
+__device__ __forceinline__ void leaf64_body(unsigned char* smem_raw, const int32_t* esize, int ncols,
+                                            const void* const* src, void* const* dst, const KeySrc& kspec,
+                                            uint32_t start, uint32_t dstart, uint32_t len, bool in_place) {
   uint64_t* skey = (uint64_t*)smem_raw;                 // LEAF_MAX
   uint16_t* sidx = (uint16_t*)(skey + LEAF_MAX);        // LEAF_MAX
   uint32_t* cnt = (uint32_t*)(sidx + LEAF_MAX);         // PT_WARPS * 256
@@ -500,10 +522,6 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort(const __grid_consta
   uint32_t* scratch = loc + MSD_RADIX;                  // PT_SCRATCH
   uint64_t* red = (uint64_t*)(scratch + PT_SCRATCH);    // 2 * PT_WARPS + 2
 
-  const uint32_t s = blockIdx.x;
-  if (s >= *p.count) return;
-  if (p.wide && !p.wide[s]) return;  // already sorted by the packed 32-bit kernel
-  const uint32_t start = p.segs.start[s], len = p.segs.len[s];
   const int w = threadIdx.x >> 5;
   const uint32_t chunk = ((len + PT_THREADS - 1) / PT_THREADS) * 32;  // elements per warp, multiple of 32
   const int items = (int)(chunk >> 5);
@@ -521,7 +539,7 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort(const __grid_consta
     lidx[k] = idx;
     key[k] = 0;
     if (v) {
-      key[k] = load_key(p.mv, p.key, start + idx);
+      key[k] = load_key_at(src[kspec.col], kspec, start + idx);
       mn = key[k] < mn ? key[k] : mn;
       mx = key[k] > mx ? key[k] : mx;
     }
@@ -545,7 +563,7 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort(const __grid_consta
   const int nbits = range ? 64 - __clzll((long long)range) : 0;
 
   if (nbits == 0) {
-    if (p.in_place) return;
+    if (in_place) return;
     for (uint32_t j = threadIdx.x; j < len; j += PT_THREADS) sidx[j] = (uint16_t)j;
   }
   for (int lo = 0; lo < nbits; lo += MSD_BITS) {
@@ -566,18 +584,18 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort(const __grid_consta
   }
   __syncthreads();
   // move every column: read all (registers), then write, so that src == dst is safe
-  for (int c = 0; c < p.mv.n; c++) {
-    const int es = p.mv.esize[c];
+  for (int c = 0; c < ncols; c++) {
+    const int es = esize[c];
     uint64_t v[PT_ITEMS];
 #pragma unroll
     for (int k = 0; k < PT_ITEMS; k++) {
       uint32_t j = threadIdx.x + k * PT_THREADS;
       if (j < len) {
         uint32_t r = start + sidx[j];
-        if (es == 8) v[k] = ((const uint64_t*)p.mv.src[c])[r];
-        else if (es == 4) v[k] = ((const uint32_t*)p.mv.src[c])[r];
-        else if (es == 2) v[k] = ((const uint16_t*)p.mv.src[c])[r];
-        else v[k] = ((const uint8_t*)p.mv.src[c])[r];
+        if (es == 8) v[k] = ((const uint64_t*)src[c])[r];
+        else if (es == 4) v[k] = ((const uint32_t*)src[c])[r];
+        else if (es == 2) v[k] = ((const uint16_t*)src[c])[r];
+        else v[k] = ((const uint8_t*)src[c])[r];
       }
     }
     __syncthreads();
@@ -585,14 +603,23 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort(const __grid_consta
     for (int k = 0; k < PT_ITEMS; k++) {
       uint32_t j = threadIdx.x + k * PT_THREADS;
       if (j < len) {
-        uint32_t r = start + j;
-        if (es == 8) ((uint64_t*)p.mv.dst[c])[r] = v[k];
-        else if (es == 4) ((uint32_t*)p.mv.dst[c])[r] = (uint32_t)v[k];
-        else if (es == 2) ((uint16_t*)p.mv.dst[c])[r] = (uint16_t)v[k];
-        else ((uint8_t*)p.mv.dst[c])[r] = (uint8_t)v[k];
+        uint32_t r = dstart + j;
+        if (es == 8) ((uint64_t*)dst[c])[r] = v[k];
+        else if (es == 4) ((uint32_t*)dst[c])[r] = (uint32_t)v[k];
+        else if (es == 2) ((uint16_t*)dst[c])[r] = (uint16_t)v[k];
+        else ((uint8_t*)dst[c])[r] = (uint8_t)v[k];
       }
     }
   }
+}
+
+__global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort(const __grid_constant__ LeafParams p) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const uint32_t s = blockIdx.x;
+  if (s >= *p.count) return;
+  if (p.wide && !p.wide[s]) return;  // already sorted by the packed 32-bit kernel
+  const uint32_t start = p.segs.start[s], len = p.segs.len[s];
+  leaf64_body(smem_raw, p.mv.esize, p.mv.n, p.mv.src, p.mv.dst, p.key, start, start, len, p.in_place != 0);
 }
 
 #define L32_IDX_BITS 12
@@ -639,9 +666,13 @@ __device__ __forceinline__ void leaf_permute_column(const unsigned char* stage, 
 // written out coalesced. Because a slice is completely in shared memory before the first row of that
 // column is written, sorting in place (src == dst) is safe. Segments with a wider key range are flagged
 // for k_leaf_sort.
+// Returns 0 when the segment has been written sorted to dst, 1 when it holds a run of more than 64 rows with
+// equal 20-bit prefixes (nothing written: the 64-bit kernel has to take it).
 template <int KMODE>
-__global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort32(const __grid_constant__ LeafParams p) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
+__device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_t* esize, int ncols_,
+                                           const void* const* src, void* const* dst, const KeySrc& kspec,
+                                           uint32_t start, uint32_t dstart, uint32_t len, uint32_t seg_bits_,
+                                           uint64_t seg_base_, bool in_place) {
   unsigned char* stage0 = smem_raw;
   unsigned char* stage1 = smem_raw + STAGE_BYTES;
   uint32_t* sdata = (uint32_t*)(smem_raw + 2 * STAGE_BYTES);  // LEAF_MAX packed words
@@ -652,13 +683,10 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort32(const __grid_cons
   uint64_t* red = (uint64_t*)(scratch + PT_SCRATCH);  // 2 * PT_WARPS + 2
   uint64_t* bar = red + 2 * PT_WARPS + 2;           // 2 mbarriers
 
-  const uint32_t s = blockIdx.x;
-  if (s >= *p.count) return;
-  const uint32_t start = p.segs.start[s], len = p.segs.len[s];
   const int w = threadIdx.x >> 5;
   const int items = (int)((len + PT_THREADS - 1) / PT_THREADS);
-  const int ncols = p.mv.n;
-  const int first = p.key.col;
+  const int ncols = ncols_;
+  const int first = kspec.col;
   auto col_at = [&](int i) { return i == 0 ? first : (i <= first ? i - 1 : i); };
 
   if (threadIdx.x == 0) {
@@ -669,20 +697,20 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort32(const __grid_cons
   }
   __syncthreads();
   if (threadIdx.x == 0) {
-    issue_slice(p.mv.src[first], p.mv.esize[first], start, len, stage0, &bar[0]);
+    issue_slice(src[first], esize[first], start, len, stage0, &bar[0]);
     if (ncols > 1) {
       int c1 = col_at(1);
-      issue_slice(p.mv.src[c1], p.mv.esize[c1], start, len, stage1, &bar[1]);
+      issue_slice(src[c1], esize[c1], start, len, stage1, &bar[1]);
     }
   }
   // ---- keys from the staged slice. The segment descriptor says how many low bits of (key - base) can still
   // differ inside the segment; when that fits the packed word no min/max pass is needed at all.
-  const uint32_t seg_bits = p.segs.shift[s];
-  const uint64_t seg_base = p.segs.base[s];
+  const uint32_t seg_bits = seg_bits_;
+  const uint64_t seg_base = seg_base_;
   const bool known = seg_bits <= L32_MAX_KEY_BITS;
   const uint64_t seg_mask = known ? ((1ull << seg_bits) - 1ull) : ~0ull;
   mbar_wait(&bar[0], 0);
-  const unsigned char* ks = stage0 + slice_lead(p.mv.src[first], p.mv.esize[first], start);
+  const unsigned char* ks = stage0 + slice_lead(src[first], esize[first], start);
   uint64_t key[PT_ITEMS];
   uint32_t vmask = 0;
   uint64_t mn = ~0ull, mx = 0;
@@ -694,8 +722,8 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort32(const __grid_cons
     key[k] = 0;
     if (v) {
       if (KMODE == KS_U64) key[k] = ((const uint64_t*)ks)[idx];
-      else if (KMODE == KS_I64) key[k] = (((const uint64_t*)ks)[idx] ^ 0x8000000000000000ull) - p.key.min;
-      else key[k] = ((uint64_t)(int64_t)((const int32_t*)ks)[idx] ^ 0x8000000000000000ull) - p.key.min;
+      else if (KMODE == KS_I64) key[k] = (((const uint64_t*)ks)[idx] ^ 0x8000000000000000ull) - kspec.min;
+      else key[k] = ((uint64_t)(int64_t)((const int32_t*)ks)[idx] ^ 0x8000000000000000ull) - kspec.min;
       key[k] = (key[k] - seg_base) & seg_mask;
       if (!known) {
         mn = key[k] < mn ? key[k] : mn;
@@ -725,11 +753,10 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort32(const __grid_cons
   // A key range wider than the packed field: sort on the top L32_MAX_KEY_BITS bits of (key - kmin) and repair
   // the (rare) runs of equal prefixes afterwards by comparing full keys (see the fix-up below).
   const int drop = nbits > L32_MAX_KEY_BITS ? nbits - L32_MAX_KEY_BITS : 0;
-  if (nbits == 0 && p.in_place) {
+  if (nbits == 0 && in_place) {
     // all keys equal and the rows are in place; a CTA must not retire with a bulk copy in flight
-    if (threadIdx.x == 0) p.wide[s] = 0;
     if (ncols > 1) mbar_wait(&bar[1], 0);
-    return;
+    return 0;
   }
   if (drop) nbits = L32_MAX_KEY_BITS;
 
@@ -824,31 +851,42 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort32(const __grid_cons
       __syncthreads();
     }
   }
-  if (threadIdx.x == 0) {
-    p.wide[s] = too_long ? 1 : 0;
-    if (too_long) atomicAdd(p.n_wide, 1u);
-  }
   if (too_long) {
     if (ncols > 1) mbar_wait(&bar[1], 0);
-    return;
+    return 1;
   }
   // ---- every column: staged slice -> permutation -> coalesced store
   for (int i = 0; i < ncols; i++) {
-    const int c = col_at(i), b = i & 1, es = p.mv.esize[c];
+    const int c = col_at(i), b = i & 1, es = esize[c];
     unsigned char* stage = b ? stage1 : stage0;
     mbar_wait(&bar[b], (uint32_t)(i >> 1) & 1u);
-    const uint32_t lead = slice_lead(p.mv.src[c], es, start);
+    const uint32_t lead = slice_lead(src[c], es, start);
     switch (es) {
-      case 8: leaf_permute_column<uint64_t>(stage, lead, (uint64_t*)p.mv.dst[c], start, len, sdata); break;
-      case 4: leaf_permute_column<uint32_t>(stage, lead, (uint32_t*)p.mv.dst[c], start, len, sdata); break;
-      case 2: leaf_permute_column<uint16_t>(stage, lead, (uint16_t*)p.mv.dst[c], start, len, sdata); break;
-      default: leaf_permute_column<uint8_t>(stage, lead, (uint8_t*)p.mv.dst[c], start, len, sdata); break;
+      case 8: leaf_permute_column<uint64_t>(stage, lead, (uint64_t*)dst[c], dstart, len, sdata); break;
+      case 4: leaf_permute_column<uint32_t>(stage, lead, (uint32_t*)dst[c], dstart, len, sdata); break;
+      case 2: leaf_permute_column<uint16_t>(stage, lead, (uint16_t*)dst[c], dstart, len, sdata); break;
+      default: leaf_permute_column<uint8_t>(stage, lead, (uint8_t*)dst[c], dstart, len, sdata); break;
     }
     __syncthreads();  // stage[b] is free again
     if (threadIdx.x == 0 && i + 2 < ncols) {
       int cn = col_at(i + 2);
-      issue_slice(p.mv.src[cn], p.mv.esize[cn], start, len, stage, &bar[b]);
+      issue_slice(src[cn], esize[cn], start, len, stage, &bar[b]);
     }
+  }
+  return 0;
+}
+
+template <int KMODE>
+__global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort32(const __grid_constant__ LeafParams p) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const uint32_t s = blockIdx.x;
+  if (s >= *p.count) return;
+  const uint32_t start = p.segs.start[s], len = p.segs.len[s];
+  const int r = leaf32_body<KMODE>(smem_raw, p.mv.esize, p.mv.n, p.mv.src, p.mv.dst, p.key, start, start, len,
+                                   p.segs.shift[s], p.segs.base[s], p.in_place != 0);
+  if (threadIdx.x == 0) {
+    p.wide[s] = r ? 1 : 0;
+    if (r) atomicAdd(p.n_wide, 1u);
   }
 }
 static size_t leaf32_smem_bytes() {
@@ -863,14 +901,13 @@ static size_t leaf_smem_bytes() {
 
 // Tiny segments (tie groups of a string sort, buckets of a small table): one warp sorts one segment of at
 // most SMALL_MAX rows by counting, for every row, the rows that precede it (key, then position).
-__global__ void __launch_bounds__(PT_THREADS) k_leaf_small(const __grid_constant__ LeafParams p) {
-  const uint32_t s = blockIdx.x * PT_WARPS + (threadIdx.x >> 5);
-  if (s >= *p.count) return;
-  const uint32_t start = p.segs.start[s], len = p.segs.len[s];
+__device__ __forceinline__ void leaf_small_warp(const int32_t* esize, int ncols, const void* const* src,
+                                                void* const* dst, const KeySrc& kspec, uint32_t start,
+                                                uint32_t dstart, uint32_t len) {
   const uint32_t lane = lane_id();
   const uint32_t i0 = lane, i1 = lane + 32;
-  uint64_t k0 = i0 < len ? load_key(p.mv, p.key, start + i0) : ~0ull;
-  uint64_t k1 = i1 < len ? load_key(p.mv, p.key, start + i1) : ~0ull;
+  uint64_t k0 = i0 < len ? load_key_at(src[kspec.col], kspec, start + i0) : ~0ull;
+  uint64_t k1 = i1 < len ? load_key_at(src[kspec.col], kspec, start + i1) : ~0ull;
   uint32_t r0 = 0, r1 = 0;
   for (uint32_t j = 0; j < len; j++) {
     uint64_t kj = __shfl_sync(0xffffffffu, j < 32 ? k0 : k1, j & 31);
@@ -895,28 +932,35 @@ __global__ void __launch_bounds__(PT_THREADS) k_leaf_small(const __grid_constant
       default: ((uint8_t*)base)[i] = (uint8_t)v; break;
     }
   };
-  for (int c0 = 0; c0 < p.mv.n; c0 += 4) {
+  for (int c0 = 0; c0 < ncols; c0 += 4) {
     uint64_t v0[4], v1[4];
 #pragma unroll
     for (int u = 0; u < 4; u++) {
       const int c = c0 + u;
       v0[u] = v1[u] = 0;
-      if (c < p.mv.n) {
-        if (i0 < len) v0[u] = ld(p.mv.src[c], (size_t)start + i0, p.mv.esize[c]);
-        if (i1 < len) v1[u] = ld(p.mv.src[c], (size_t)start + i1, p.mv.esize[c]);
+      if (c < ncols) {
+        if (i0 < len) v0[u] = ld(src[c], (size_t)start + i0, esize[c]);
+        if (i1 < len) v1[u] = ld(src[c], (size_t)start + i1, esize[c]);
       }
     }
     __syncwarp();
 #pragma unroll
     for (int u = 0; u < 4; u++) {
       const int c = c0 + u;
-      if (c < p.mv.n) {
-        if (i0 < len) st(p.mv.dst[c], (size_t)start + r0, p.mv.esize[c], v0[u]);
-        if (i1 < len) st(p.mv.dst[c], (size_t)start + r1, p.mv.esize[c], v1[u]);
+      if (c < ncols) {
+        if (i0 < len) st(dst[c], (size_t)dstart + r0, esize[c], v0[u]);
+        if (i1 < len) st(dst[c], (size_t)dstart + r1, esize[c], v1[u]);
       }
     }
     __syncwarp();
   }
+}
+
+__global__ void __launch_bounds__(PT_THREADS) k_leaf_small(const __grid_constant__ LeafParams p) {
+  const uint32_t s = blockIdx.x * PT_WARPS + (threadIdx.x >> 5);
+  if (s >= *p.count) return;
+  const uint32_t start = p.segs.start[s], len = p.segs.len[s];
+  leaf_small_warp(p.mv.esize, p.mv.n, p.mv.src, p.mv.dst, p.key, start, start, len);
 }
 
 // segments whose keys are all equal but that are larger than a leaf: plain copy src -> dst. Such a segment can
