@@ -1230,6 +1230,178 @@ static void launch_wide(hs_ctx* c, LeafLaunch& ll, uint32_t* d_counters) {
   run_wide_leaves(c, ll, nw);
 }
 
+// ---------------------------------------------------------------- pipelined sort of the large segments
+// One launch sorts every level-0 segment that is larger than a leaf: per segment a digit histogram of the MSD
+// level (H tiles; the last tile of a segment also turns the histogram into write cursors), the MSD scatter (S
+// tiles) and one leaf sort per child (L items). Work items are handed out through an atomic ticket in an order
+// in which an item only ever waits for items with smaller tickets (those already run or have finished), so the
+// kernel needs no co-residency guarantee:   step k = [ S(group k-1) | H(group k) | L(group k-2) ].
+// The scatter does not write the rows to their own positions in buffer B but into one of PIPE_SLOTS slots at the
+// start of B, re-used group after group: the leaf sort reads a slot shortly after it was written, while its
+// lines are still in L2, and the next group overwrites them there. Memory-bound scatter tiles and issue-bound
+// leaf sorts run side by side on every SM.
+#define PIPE_SLOTS 3
+#define PK_SCATTER 0u
+#define PK_HIST 1u
+#define PK_LEAF 2u
+struct PipePhase { uint32_t first, kind, group, pad; };
+struct PipeParams {
+  PartParams part;              // mv.src: where the rows are (buffer A, or S0), mv.dst: buffer B (the slots), key
+  void* fin[HS_MAX_MOVE];       // buffer A: receives the sorted rows
+  uint32_t key_bits;            // unsorted low key bits of every level-0 segment
+  uint32_t slot_rows;
+  const uint32_t* seg_start;    // [ns]
+  const uint32_t* seg_len;      // [ns]
+  const uint32_t* seg_tile0;    // [ns + 1] tiles before segment s
+  const uint32_t* seg_child0;   // [ns + 1] children before segment s
+  const uint32_t* grp_seg0;     // [ng + 1] first segment of group g
+  const PipePhase* phases;
+  uint32_t nphases, ntickets;
+  uint32_t* ticket;             // state below is zeroed before the launch
+  uint32_t* hist_done;          // [ns] H tiles finished
+  uint32_t* plan_done;          // [ns] cursors ready
+  uint32_t* scat_done;          // [ns] S tiles finished
+  uint32_t* leaf_done;          // [ng] L items finished
+  uint32_t* cursor;             // [ns * MSD_RADIX]
+  uint32_t* child_start;        // [ns * MSD_RADIX]
+  uint32_t* child_len;          // [ns * MSD_RADIX]
+  SegList large;                // children that are still larger than a leaf: left to the level loop
+  uint32_t* counters;           // [1] entries of `large`, [3] their tiles
+};
+
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// the CTA waits until *p >= need (written by CTAs with smaller tickets)
+__device__ __forceinline__ void pipe_wait(const uint32_t* p, uint32_t need) {
+  if (threadIdx.x == 0) {
+    while (ld_acquire_u32(p) < need) __nanosleep(64);
+    asm volatile("fence.proxy.async.global;" ::: "memory");   // what was acquired is read by bulk copies next
+  }
+  __syncthreads();
+}
+// the CTA's global writes are done: publish them and bump a counter; returns the counter's old value to thread 0
+__device__ __forceinline__ uint32_t pipe_signal(uint32_t* p) {
+  __threadfence();
+  __syncthreads();
+  uint32_t old = 0;
+  if (threadIdx.x == 0) old = atomicAdd(p, 1u);
+  return old;
+}
+// largest s in [lo, hi) with pre[s] <= x
+__device__ __forceinline__ uint32_t pipe_find(const uint32_t* pre, uint32_t lo, uint32_t hi, uint32_t x) {
+  while (hi - lo > 1) {
+    uint32_t mid = (lo + hi) >> 1;
+    if (pre[mid] <= x) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+template <int KMODE>
+__global__ void __launch_bounds__(PT_THREADS, 2) k_sort_pipeline(const __grid_constant__ PipeParams p) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ uint32_t s_ticket, s_phase, s_flag;
+  if (threadIdx.x == 0) s_ticket = atomicAdd(p.ticket, 1u);
+  __syncthreads();
+  const uint32_t t = s_ticket;
+  for (uint32_t i = threadIdx.x; i < p.nphases; i += PT_THREADS) {
+    const uint32_t f = p.phases[i].first, e = i + 1 < p.nphases ? p.phases[i + 1].first : p.ntickets;
+    if (f <= t && t < e) s_phase = i;
+  }
+  __syncthreads();
+  const PipePhase ph = p.phases[s_phase];
+  const uint32_t idx = t - ph.first, g = ph.group;
+  const uint32_t s0 = p.grp_seg0[g], s1 = p.grp_seg0[g + 1];
+  const uint32_t bias = (g % PIPE_SLOTS) * p.slot_rows - p.seg_start[s0];   // slot row = row + bias (mod 2^32)
+  const int ncols = p.part.mv.n;
+  if (ph.kind == PK_HIST || ph.kind == PK_SCATTER) {
+    const uint32_t T = p.seg_tile0[s0] + idx;
+    const uint32_t s = pipe_find(p.seg_tile0, s0, s1, T);
+    const uint32_t tt = T - p.seg_tile0[s], ntile = p.seg_tile0[s + 1] - p.seg_tile0[s];
+    const uint32_t slen = p.seg_len[s];
+    const uint32_t tile_start = p.seg_start[s] + tt * PT_TILE;
+    const uint32_t left = slen - tt * PT_TILE;
+    const uint32_t tile_len = left < PT_TILE ? left : PT_TILE;
+    const int bits = msd_bits(slen, p.key_bits);
+    const uint32_t shift = p.key_bits - bits;
+    uint32_t* cursor = p.cursor + (size_t)s * MSD_RADIX;
+    if (ph.kind == PK_HIST) {
+      uint32_t* hist = (uint32_t*)smem_raw;
+      uint32_t* scratch = hist + MSD_RADIX;
+      msd_hist_tile(p.part.mv, p.part.key, tile_start, tile_len, 0, shift, bits, hist, cursor);
+      const uint32_t old = pipe_signal(&p.hist_done[s]);
+      if (threadIdx.x == 0) s_flag = old + 1 == ntile;
+      __syncthreads();
+      if (s_flag) {
+        // the last histogram tile of the segment: counts -> write cursors and the children's extents
+        __threadfence();
+        const uint32_t d = threadIdx.x;
+        const uint32_t hcount = d < MSD_RADIX ? __ldcg(&cursor[d]) : 0;
+        const uint32_t ex = block256_excl_scan_u32(hcount, scratch);
+        if (d < MSD_RADIX) {
+          const uint32_t start = p.seg_start[s] + ex;
+          cursor[d] = start;
+          p.child_start[(size_t)s * MSD_RADIX + d] = start;
+          p.child_len[(size_t)s * MSD_RADIX + d] = hcount;
+        }
+        pipe_signal(&p.plan_done[s]);
+      }
+    } else {
+      if (g >= PIPE_SLOTS) {   // the slot must have been read by every leaf of the group that used it last
+        const uint32_t q0 = p.grp_seg0[g - PIPE_SLOTS], q1 = p.grp_seg0[g - PIPE_SLOTS + 1];
+        pipe_wait(&p.leaf_done[g - PIPE_SLOTS], p.seg_child0[q1] - p.seg_child0[q0]);
+      }
+      pipe_wait(&p.plan_done[s], 1u);
+      partition_tile<1>(p.part, smem_raw, tile_start, tile_len, bits, shift, 0, cursor, bias);
+      pipe_signal(&p.scat_done[s]);
+    }
+    return;
+  }
+  // ---- PK_LEAF: one child of one segment
+  const uint32_t C = p.seg_child0[s0] + idx;
+  const uint32_t s = pipe_find(p.seg_child0, s0, s1, C);
+  const uint32_t ch = C - p.seg_child0[s];
+  pipe_wait(&p.scat_done[s], p.seg_tile0[s + 1] - p.seg_tile0[s]);
+  const uint32_t cs = __ldcg(&p.child_start[(size_t)s * MSD_RADIX + ch]);
+  const uint32_t cl = __ldcg(&p.child_len[(size_t)s * MSD_RADIX + ch]);
+  const uint32_t sh = p.key_bits - (uint32_t)msd_bits(p.seg_len[s], p.key_bits);
+  const void* const* ring = (const void* const*)p.part.mv.dst;
+  if (cl == 0) {
+  } else if (cl <= SMALL_MAX) {
+    if (threadIdx.x < 32) leaf_small_warp(p.part.mv.esize, ncols, ring, p.fin, p.part.key, cs + bias, cs, cl);
+  } else if (cl <= LEAF_MAX) {
+    const int r = leaf32_body<KMODE>(smem_raw, p.part.mv.esize, ncols, ring, p.fin, p.part.key, cs + bias, cs, cl, sh, 0,
+                                     false);
+    if (r) {
+      __syncthreads();
+      leaf64_body(smem_raw, p.part.mv.esize, ncols, ring, p.fin, p.part.key, cs + bias, cs, cl, false);
+    }
+  } else {
+    // still larger than a leaf (skewed keys, or all keys equal): the rows leave the slot for the place they came
+    // from; if key bits are left, the level loop after this kernel splits the child further
+    for (int c = 0; c < ncols; c++) {
+      const int es = p.part.mv.esize[c];
+      const unsigned char* a = (const unsigned char*)ring[c] + (size_t)(uint32_t)(cs + bias) * es;
+      unsigned char* b = (sh ? (unsigned char*)p.part.mv.src[c] : (unsigned char*)p.fin[c]) + (size_t)cs * es;
+      const size_t bytes = (size_t)cl * es;
+      if (((((uintptr_t)a) | ((uintptr_t)b)) & 7) == 0) {
+        for (size_t i = threadIdx.x; i < (bytes >> 3); i += PT_THREADS) ((uint64_t*)b)[i] = ((const uint64_t*)a)[i];
+        for (size_t i = (bytes & ~(size_t)7) + threadIdx.x; i < bytes; i += PT_THREADS) b[i] = a[i];
+      } else {
+        for (size_t i = threadIdx.x; i < bytes; i += PT_THREADS) b[i] = a[i];
+      }
+    }
+    if (sh && threadIdx.x == 0) {
+      const uint32_t i = atomicAdd(&p.counters[1], 1u);
+      p.large.start[i] = cs; p.large.len[i] = cl; p.large.shift[i] = sh; p.large.base[i] = 0;
+      atomicAdd(&p.counters[3], (cl + PT_TILE - 1) / PT_TILE);
+    }
+  }
+  pipe_signal(&p.leaf_done[g]);
+}
+
 // h_seg_off (optional): the segment boundaries on the host. With them level 0 is classified on the host
 // and the sort starts without a device round trip.
 static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_seg_off,
