@@ -1278,6 +1278,7 @@ __device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
 __device__ __forceinline__ void pipe_wait(const uint32_t* p, uint32_t need) {
   if (threadIdx.x == 0) {
     while (ld_acquire_u32(p) < need) __nanosleep(64);
+    __threadfence();   // also drops this SM's L1 lines: a slot may have been read here under its previous contents
     asm volatile("fence.proxy.async.global;" ::: "memory");   // what was acquired is read by bulk copies next
   }
   __syncthreads();
@@ -1402,6 +1403,131 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_sort_pipeline(const __grid_co
   pipe_signal(&p.leaf_done[g]);
 }
 
+static bool pipeline_enabled() {
+  const char* e = getenv("HSGPU_SORT_PIPELINE");
+  return !(e && *e == '0');
+}
+static size_t pipeline_smem_bytes() {
+  size_t a = leaf32_smem_bytes(), b = leaf_smem_bytes(), t = tile_smem_bytes(MSD_RADIX);
+  return std::max(a, std::max(b, t));
+}
+
+// The level-0 large segments (start/len, host-known, ascending) are split into those whose rows fit a slot of the
+// pipelined sort (ps/pl, in groups) and the rest (left to the level loop).
+struct PipePlan {
+  std::vector<uint32_t> ps, pl, grp_seg0, rest_s, rest_l;
+  uint32_t slot_rows = 0;
+};
+static PipePlan plan_sort_pipeline(const MoveSet& ms, int64_t n, const std::vector<uint32_t>& lg_s,
+                                   const std::vector<uint32_t>& lg_l) {
+  PipePlan pl_;
+  size_t row_bytes = 0;
+  for (int i = 0; i < ms.n; i++) row_bytes += (size_t)ms.esize[i];
+  size_t ring_mb = 48;
+  if (const char* e = getenv("HSGPU_RING_MB")) { long v = atol(e); if (v > 0) ring_mb = (size_t)v; }
+  uint64_t slot_target = (uint64_t)ring_mb * 1024 * 1024 / PIPE_SLOTS / row_bytes;
+  if (slot_target > (uint64_t)n / PIPE_SLOTS) slot_target = (uint64_t)n / PIPE_SLOTS;
+  // groups: consecutive segments whose address span fits a slot
+  std::vector<uint32_t>&ps = pl_.ps, &pl = pl_.pl, &grp_seg0 = pl_.grp_seg0;
+  uint64_t g_first = 0;
+  for (size_t i = 0; i < lg_s.size(); i++) {
+    if (lg_l[i] > slot_target) { pl_.rest_s.push_back(lg_s[i]); pl_.rest_l.push_back(lg_l[i]); continue; }
+    const uint64_t end = (uint64_t)lg_s[i] + lg_l[i];
+    if (grp_seg0.empty() || end - g_first > slot_target) {
+      grp_seg0.push_back((uint32_t)ps.size());
+      g_first = lg_s[i];
+    }
+    if (end - g_first > pl_.slot_rows) pl_.slot_rows = (uint32_t)(end - g_first);
+    ps.push_back(lg_s[i]);
+    pl.push_back(lg_l[i]);
+  }
+  if (!ps.empty()) grp_seg0.push_back((uint32_t)ps.size());
+  return pl_;
+}
+
+// Launches k_sort_pipeline over a plan. Children of pipelined segments that are still larger than a leaf are
+// appended on the device to `large` (counters[1] entries, counters[3] tiles).
+static void run_sort_pipeline(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, int src_code,
+                              const PipePlan& plan, const ListBufs& large, uint32_t* d_counters) {
+  const std::vector<uint32_t>&ps = plan.ps, &pl = plan.pl, &grp_seg0 = plan.grp_seg0;
+  const uint32_t slot_rows = plan.slot_rows;
+  const size_t ns = ps.size();
+  if (ns == 0) return;
+  const size_t ng = grp_seg0.size() - 1;
+  std::vector<uint32_t> tile0(ns + 1, 0), child0(ns + 1, 0);
+  for (size_t s = 0; s < ns; s++) {
+    tile0[s + 1] = tile0[s] + (pl[s] + PT_TILE - 1) / PT_TILE;
+    child0[s + 1] = child0[s] + (1u << msd_bits(pl[s], (uint32_t)key_bits));
+  }
+  // ticket order: step k = S(k-1), H(k), L(k-2)
+  std::vector<PipePhase> phases;
+  uint32_t ticket = 0;
+  auto tiles_of = [&](size_t g) { return tile0[grp_seg0[g + 1]] - tile0[grp_seg0[g]]; };
+  auto children_of = [&](size_t g) { return child0[grp_seg0[g + 1]] - child0[grp_seg0[g]]; };
+  for (size_t k = 0; k < ng + 2; k++) {
+    if (k >= 1 && k - 1 < ng) { phases.push_back(PipePhase{ticket, PK_SCATTER, (uint32_t)(k - 1), 0}); ticket += tiles_of(k - 1); }
+    if (k < ng) { phases.push_back(PipePhase{ticket, PK_HIST, (uint32_t)k, 0}); ticket += tiles_of(k); }
+    if (k >= 2 && k - 2 < ng) { phases.push_back(PipePhase{ticket, PK_LEAF, (uint32_t)(k - 2), 0}); ticket += children_of(k - 2); }
+  }
+  // one upload: [seg_start | seg_len | tile0 | child0 | grp_seg0 | phases]
+  std::vector<uint32_t> up;
+  auto put = [&](const std::vector<uint32_t>& v) { size_t o = up.size(); up.insert(up.end(), v.begin(), v.end()); return o; };
+  const size_t o_start = put(ps), o_len = put(pl), o_tile = put(tile0), o_child = put(child0), o_grp = put(grp_seg0);
+  const size_t o_ph = up.size();
+  up.resize(o_ph + phases.size() * 4);
+  memcpy(up.data() + o_ph, phases.data(), phases.size() * sizeof(PipePhase));
+  DBuf d_up(c, up.size() * 4);
+  CK(cudaMemcpyAsync(d_up.p, up.data(), up.size() * 4, cudaMemcpyHostToDevice, c->stream));
+  // state: [ticket(4 words) | hist_done ns | plan_done ns | scat_done ns | leaf_done ng | cursor ns*256], zeroed
+  const size_t n_state = 4 + 3 * ns + ng + ns * MSD_RADIX;
+  DBuf d_state(c, n_state * 4), d_child(c, 2 * ns * MSD_RADIX * 4);
+  d_state.zero();
+  uint32_t* st = d_state.as<uint32_t>();
+  const uint32_t* dup = d_up.as<uint32_t>();
+
+  PipeParams* pp = new PipeParams;
+  memset(pp, 0, sizeof *pp);
+  pp->part.mv = make_move(ms, src_code, BUF_B);
+  pp->part.key = key;
+  pp->part.radix = MSD_RADIX;
+  pp->part.radix_pad = MSD_RADIX;
+  pp->part.bits = MSD_BITS;
+  for (int i = 0; i < ms.n; i++) pp->fin[i] = ms.a[i];
+  pp->key_bits = (uint32_t)key_bits;
+  pp->slot_rows = slot_rows;
+  pp->seg_start = dup + o_start; pp->seg_len = dup + o_len; pp->seg_tile0 = dup + o_tile; pp->seg_child0 = dup + o_child;
+  pp->grp_seg0 = dup + o_grp;
+  pp->phases = (const PipePhase*)(dup + o_ph);
+  pp->nphases = (uint32_t)phases.size();
+  pp->ntickets = ticket;
+  pp->ticket = st;
+  pp->hist_done = st + 4; pp->plan_done = pp->hist_done + ns; pp->scat_done = pp->plan_done + ns;
+  pp->leaf_done = pp->scat_done + ns; pp->cursor = pp->leaf_done + ng;
+  pp->child_start = d_child.as<uint32_t>(); pp->child_len = pp->child_start + ns * MSD_RADIX;
+  pp->large = large.view();
+  pp->counters = d_counters;
+  {
+    static bool attr_dev[64] = {false};
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (!attr_dev[dev & 63]) {
+      const int sm = (int)pipeline_smem_bytes();
+      CK(cudaFuncSetAttribute(k_sort_pipeline<KS_U64>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(k_sort_pipeline<KS_I64>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      CK(cudaFuncSetAttribute(k_sort_pipeline<KS_I32>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
+      attr_dev[dev & 63] = true;
+    }
+  }
+  {
+    Stage stg(c, "sort_pipeline");
+    const size_t sm = pipeline_smem_bytes();
+    if (key.mode == KS_U64) LAUNCH(c, k_sort_pipeline<KS_U64>, ticket, PT_THREADS, sm, *pp);
+    else if (key.mode == KS_I64) LAUNCH(c, k_sort_pipeline<KS_I64>, ticket, PT_THREADS, sm, *pp);
+    else LAUNCH(c, k_sort_pipeline<KS_I32>, ticket, PT_THREADS, sm, *pp);
+  }
+  delete pp;
+}
+
 // h_seg_off (optional): the segment boundaries on the host. With them level 0 is classified on the host
 // and the sort starts without a device round trip.
 static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_seg_off,
@@ -1416,6 +1542,7 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
   const bool ext = ms.s0[0] != nullptr;   // the rows start outside buffer A: every row has to be moved
   int src = ext ? BUF_S0 : BUF_A;
   LeafLaunch ll0;
+  bool pipe_children = false;   // the level loop starts with children of the pipelined level
   if (h_seg_off) {
     // ---- level 0 on the host
     std::vector<uint32_t> tp;
@@ -1430,23 +1557,33 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
       else if (ext) { cp_s.push_back(st); cp_l.push_back(len); }
       // larger than a leaf with no key bits: all keys equal; in place when the rows already are in A
     }
+    PipePlan plan;
+    const bool piped = pipeline_enabled() && !lg_s.empty() && ms.b[0] != nullptr;
+    if (piped) {
+      plan = plan_sort_pipeline(ms, n, lg_s, lg_l);
+      lg_s = plan.rest_s;
+      lg_l = plan.rest_l;
+      tp.assign(1, 0);
+      for (uint32_t len : lg_l) tp.push_back(tp.back() + (len + PT_TILE - 1) / PT_TILE);
+    }
     h[0] = (uint32_t)lf_s.size();
     h[1] = (uint32_t)lg_s.size();
     h[2] = (uint32_t)cp_s.size();
     h[3] = tp.back();
     h[5] = (uint32_t)sm_s.size();
-    auto upload = [&](ListBufs& lb, const std::vector<uint32_t>& st, const std::vector<uint32_t>& ln) {
+    auto upload = [&](ListBufs& lb, const std::vector<uint32_t>& st, const std::vector<uint32_t>& ln, size_t cap = 0) {
       size_t m = st.size();
-      lb.alloc(c, m ? m : 1);
+      lb.alloc(c, std::max(cap, m ? m : 1));
       if (!m) return;
       std::vector<uint32_t> sh(m, (uint32_t)key_bits);
       CK(cudaMemcpyAsync(lb.start.p, st.data(), m * 4, cudaMemcpyHostToDevice, c->stream));
       CK(cudaMemcpyAsync(lb.len.p, ln.data(), m * 4, cudaMemcpyHostToDevice, c->stream));
       CK(cudaMemcpyAsync(lb.shift.p, sh.data(), m * 4, cudaMemcpyHostToDevice, c->stream));
     };
+    const size_t large_cap = !plan.ps.empty() ? cap_large : 0;   // the pipeline may append children
     upload(leaf, lf_s, lf_l);
-    upload(large, lg_s, lg_l);
-    large.base.alloc(c, (lg_s.size() ? lg_s.size() : 1) * 8);
+    upload(large, lg_s, lg_l, large_cap);
+    large.base.alloc(c, std::max(large_cap, lg_s.size() ? lg_s.size() : (size_t)1) * 8);
     large.base.zero();
     leaf.base.alloc(c, (lf_s.size() ? lf_s.size() : 1) * 8);
     leaf.base.zero();
@@ -1456,6 +1593,18 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     CK(cudaMemcpyAsync(tile_prefix.p, tp.data(), tp.size() * 4, cudaMemcpyHostToDevice, c->stream));
     run_leaf_and_copy(c, ms, key, src, leaf, h[0], copy, h[2], counters.as<uint32_t>(), ll0, &small, h[5]);
     launch_wide(c, ll0, counters.as<uint32_t>());
+    if (!plan.ps.empty()) {
+      run_sort_pipeline(c, ms, key, key_bits, src, plan, large, counters.as<uint32_t>());
+      // children that one level could not bring down to a leaf (skewed keys) were appended to `large`
+      uint32_t hh[8];
+      memcpy(hh, hs_read_wait(c, hs_read_begin(c, counters.p, 32)), 32);
+      if (hh[1] != h[1]) {
+        h[1] = hh[1];
+        h[3] = hh[3];
+        LAUNCH(c, k_tile_prefix, 1, 1024, 0, large.view(), counters.as<uint32_t>(), tile_prefix.as<uint32_t>());
+        pipe_children = true;
+      }
+    }
   } else {
     leaf.alloc(c, cap_leaf, true);
     large.alloc(c, cap_large, true);
@@ -1475,7 +1624,7 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     launch_wide(c, ll0, counters.as<uint32_t>());
   }
   uint32_t n_large = h[1], n_tiles = h[3];
-  int level = 0;
+  int level = pipe_children ? 1 : 0;   // children of a level are re-ranged before they are split again
   while (n_large > 0) {
     if (++level > 80) HS_THROW(HS_ECUDA, "segmented sort did not converge");
     // histograms -> cursors + child lists
