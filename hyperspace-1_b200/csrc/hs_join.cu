@@ -11,6 +11,7 @@
 
 #include "hs_keys.cuh"
 #include "hs_kernels.h"
+#include "hs_tma.cuh"
 
 struct JoinSide {
   KeySpec ks;
@@ -155,8 +156,11 @@ __global__ void __launch_bounds__(256) k_full_outer_merge(const uint32_t* __rest
 // Pass 1 counts matches per tile, a scan turns the counts into output offsets, pass 2 repeats the search,
 // expands the pairs in shared memory and writes every output column directly (no index arrays in HBM).
 #define JT 2048          // left rows per tile
-#define JR 6144          // right keys staged per tile (falls back to global probes when the window is larger)
-#define JTHREADS 256
+#define JR 3072          // right rows staged per tile (falls back to global probes when the window is larger)
+#define JTHREADS 512
+#define JPER (JT / JTHREADS)   // consecutive left rows owned by one thread
+#define JOMAX 4096       // outputs of one tile that are expanded through shared memory
+#define JBUF_BYTES (JR * 8 + 128)
 
 struct JoinFast {
   const void* lkey; const void* rkey;     // key columns
@@ -198,8 +202,6 @@ __device__ __forceinline__ uint32_t warp_lower_bound(const K* a, uint32_t lo, ui
   return lo + __popc(__ballot_sync(0xffffffffu, before));
 }
 
-#define JPER (JT / JTHREADS)   // consecutive left rows owned by one thread
-
 // one warp per tile: the window of the right run that can hold matches for the tile's left rows
 template <typename K>
 __global__ void __launch_bounds__(256) k_join_windows(const __grid_constant__ JoinFast p) {
@@ -227,36 +229,58 @@ __device__ __forceinline__ uint32_t window_advance(const K* sR, uint32_t pos, ui
   return pos;
 }
 
+// One tile of left rows against its window of the right run.
 // MODE 0: count matches per tile.  MODE 1: write, offsets from the scanned counts.
 // MODE 2: single pass — the tile's output offset comes from a chained scan over the tiles.
+// The tile's left keys and the window's right keys arrive in shared memory by TMA bulk copies; every thread
+// merges its JPER consecutive left keys against the staged window. For the output, the (left row, right row) of
+// every output position is laid out in shared memory once; each output column is then produced from a staged
+// slice of its source column (bulk copies, double buffered) with coalesced stores — no per-thread strided
+// global loads, no index arrays in HBM. Tiles whose window or output exceeds the staging areas take the
+// global-memory paths below (same results).
 template <typename K, int MODE>
-__global__ void __launch_bounds__(JTHREADS) k_join_tiles(const __grid_constant__ JoinFast p) {
-  extern __shared__ __align__(16) unsigned char jsm[];
-  K* sR = (K*)jsm;                                   // JR staged right keys
-  uint32_t* slb = (uint32_t*)(sR + JR);              // JT  (absolute right row of the first match)
-  uint32_t* scn = slb + JT;                          // JT + 1 (exclusive scan of the match counts)
+__global__ void __launch_bounds__(JTHREADS, 2) k_join_tiles(const __grid_constant__ JoinFast p) {
+  extern __shared__ __align__(128) unsigned char jsm[];
+  unsigned char* buf0 = jsm;
+  unsigned char* buf1 = jsm + JBUF_BYTES;
+  unsigned char* buf2 = jsm + 2 * JBUF_BYTES;
+  uint16_t* omap = (uint16_t*)(jsm + 3 * JBUF_BYTES);   // JOMAX: tile-local left row of every output
+  uint16_t* orel = omap + JOMAX;                        // JOMAX: window-local right row of every output
+  uint32_t* slb = (uint32_t*)omap;                      // expanding path only (aliases the two maps): JT
+  uint32_t* scn = slb + JT;                             // JT + 1
+  uint64_t* bar = (uint64_t*)(jsm + 3 * JBUF_BYTES + 4 * JOMAX + 16);   // 3 mbarriers
   __shared__ uint32_t s_red[JTHREADS / 32 + 1];
   __shared__ uint32_t s_tile, s_obase;
   if (MODE == 2) {
     if (threadIdx.x == 0) s_tile = atomicAdd(p.ticket, 1u);
-    __syncthreads();
   }
+  if (threadIdx.x == 0) {
+    mbar_init(&bar[0], 1);
+    mbar_init(&bar[1], 1);
+    mbar_init(&bar[2], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncthreads();
   const uint32_t t = MODE == 2 ? s_tile : blockIdx.x;
   const uint32_t l0 = p.tile_start[t], ln = p.tile_len[t];
-  const K* lk = (const K*)p.lkey + l0;
   const K* rk = (const K*)p.rkey;
-  // each thread owns JPER consecutive left rows: sorted keys straight from global memory (the warp reads one
-  // contiguous span), merged against the staged window of the right run
+  const uint32_t wlo = p.tile_win[2 * t], whi = p.tile_win[2 * t + 1], wn = whi - wlo;
+  const bool staged = wn <= JR;
+  uint32_t ph0 = 0, ph1 = 0, ph2 = 0;   // phase parity of the three mbarriers
+  if (threadIdx.x == 0) {
+    issue_slice(p.lkey, (int)sizeof(K), l0, ln, buf0, &bar[0]);
+    if (staged && wn) issue_slice(p.rkey, (int)sizeof(K), wlo, wn, buf1, &bar[1]);
+  }
+  const K* sLK = (const K*)(buf0 + slice_lead(p.lkey, (int)sizeof(K), l0));
+  const K* sR = (const K*)(buf1 + slice_lead(p.rkey, (int)sizeof(K), wlo));
+  mbar_wait(&bar[0], ph0); ph0 ^= 1;
+  if (staged && wn) { mbar_wait(&bar[1], ph1); ph1 ^= 1; }
   const uint32_t i0 = threadIdx.x * JPER;
   K key[JPER];
 #pragma unroll
-  for (int j = 0; j < JPER; j++) key[j] = i0 + j < ln ? lk[i0 + j] : (K)0;
-  const uint32_t wlo = p.tile_win[2 * t], whi = p.tile_win[2 * t + 1], wn = whi - wlo;
-  const bool staged = wn <= JR;
-  if (staged)
-    for (uint32_t i = threadIdx.x; i < wn; i += JTHREADS) sR[i] = rk[wlo + i];
-  __syncthreads();
-  uint32_t lb[JPER], cnt[JPER];
+  for (int j = 0; j < JPER; j++) key[j] = i0 + j < ln ? sLK[i0 + j] : (K)0;
+  uint32_t lb[JPER], cnt[JPER];   // first match relative to the window, number of matches
   uint32_t mysum = 0;
   if (staged) {
     uint32_t pos = 0;
@@ -272,7 +296,7 @@ __global__ void __launch_bounds__(JTHREADS) k_join_tiles(const __grid_constant__
         pos = window_advance<K>(sR, pos, wn, key[j]);
         uint32_t e = pos;
         while (e < wn && sR[e] == key[j]) e++;
-        lb[j] = wlo + pos;
+        lb[j] = pos;
         cnt[j] = e - pos;
         mysum += cnt[j];
       }
@@ -287,7 +311,7 @@ __global__ void __launch_bounds__(JTHREADS) k_join_tiles(const __grid_constant__
         uint32_t f = a;
         e = whi;
         while (a < e) { uint32_t m = (a + e) >> 1; if (rk[m] <= key[j]) a = m + 1; else e = m; }
-        lb[j] = f;
+        lb[j] = f - wlo;
         cnt[j] = a - f;
         mysum += cnt[j];
       }
@@ -339,81 +363,87 @@ __global__ void __launch_bounds__(JTHREADS) k_join_tiles(const __grid_constant__
     if ((unsigned long long)s_obase + total > p.capacity) return;   // does not fit: count only
   }
   const uint32_t obase = MODE == 2 ? s_obase : p.tile_cnt[t];   // exclusive offset of this tile in the output
-  // warp-level view of the outputs: a warp whose rows produce at most 256 outputs transposes them through
-  // shared memory (the slb/scn area is free in this mode) so that global stores are fully coalesced
-  uint32_t winc = mysum;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    uint32_t o = __shfl_up_sync(0xffffffffu, winc, d);
-    if (lane_id() >= (uint32_t)d) winc += o;
-  }
-  const uint32_t wtotal = __shfl_sync(0xffffffffu, winc, 31);
-  const uint32_t wex = winc - mysum;                                   // this thread's offset inside the warp
-  const uint32_t wbase = obase + (ex - wex);                           // first output row of the warp
-  const bool all_warps_small = __syncthreads_and(wtotal <= 256);
-  if (total <= 4 * ln && all_warps_small) {
-    uint64_t* wst = (uint64_t*)slb + (threadIdx.x >> 5) * 256;        // 256 x 8 B per warp
-    for (int c = 0; c < p.n_lout + p.n_rout; c++) {
-      const bool left = c < p.n_lout;
-      const int cc = left ? c : c - p.n_lout;
-      const int es = left ? p.les[cc] : p.res[cc];
-      const void* src = left ? p.lsrc[cc] : p.rsrc[cc];
-      void* dst = left ? p.ldst[cc] : p.rdst[cc];
-      uint32_t o = wex;
+  if (total == 0) return;
+  const int ncol = p.n_lout + p.n_rout;
+  if (staged && total <= JOMAX) {
+    // ---- (left row, right row) of every output position of the tile
+    {
+      uint32_t o = ex;
 #pragma unroll
       for (int j = 0; j < JPER; j++) {
         for (uint32_t q = 0; q < cnt[j]; q++) {
-          uint32_t r = left ? l0 + i0 + j : lb[j] + q;
-          wst[o + q] = es == 8 ? ((const uint64_t*)src)[r] : (uint64_t)((const uint32_t*)src)[r];
-        }
-        o += cnt[j];
-      }
-      __syncwarp();
-      for (uint32_t q = lane_id(); q < wtotal; q += 32) {
-        if (es == 8) ((uint64_t*)dst)[wbase + q] = wst[q];
-        else ((uint32_t*)dst)[wbase + q] = (uint32_t)wst[q];
-      }
-      __syncwarp();
-    }
-    return;
-  }
-  if (total <= 4 * ln) {
-    // every thread writes the matches of its own rows (consecutive outputs per thread)
-    for (int c = 0; c < p.n_lout; c++) {
-      uint32_t o = obase + ex;
-      const int es = p.les[c];
-#pragma unroll
-      for (int j = 0; j < JPER; j++) {
-        if (cnt[j]) {
-          if (es == 8) {
-            uint64_t v = ((const uint64_t*)p.lsrc[c])[l0 + i0 + j];
-            for (uint32_t q = 0; q < cnt[j]; q++) ((uint64_t*)p.ldst[c])[o + q] = v;
-          } else {
-            uint32_t v = ((const uint32_t*)p.lsrc[c])[l0 + i0 + j];
-            for (uint32_t q = 0; q < cnt[j]; q++) ((uint32_t*)p.ldst[c])[o + q] = v;
-          }
-          o += cnt[j];
-        }
-      }
-    }
-    for (int c = 0; c < p.n_rout; c++) {
-      uint32_t o = obase + ex;
-      const int es = p.res[c];
-#pragma unroll
-      for (int j = 0; j < JPER; j++) {
-        for (uint32_t q = 0; q < cnt[j]; q++) {
-          if (es == 8) ((uint64_t*)p.rdst[c])[o + q] = ((const uint64_t*)p.rsrc[c])[lb[j] + q];
-          else ((uint32_t*)p.rdst[c])[o + q] = ((const uint32_t*)p.rsrc[c])[lb[j] + q];
+          omap[o + q] = (uint16_t)(i0 + j);
+          orel[o + q] = (uint16_t)(lb[j] + q);
         }
         o += cnt[j];
       }
     }
+    __syncthreads();   // also: every thread is done with the staged right keys (buf1)
+    // ---- columns: a left output that is the key column itself is served from buf0; the others are staged in
+    // buf1 / buf2 alternately, the copy of column k + 2 starting as soon as column k has been written
+    auto col_src = [&](int c, const void*& src, int& es, bool& left) {
+      left = c < p.n_lout;
+      src = left ? p.lsrc[c] : p.rsrc[c - p.n_lout];
+      es = left ? p.les[c] : p.res[c - p.n_lout];
+    };
+    auto start_load = [&](int c, unsigned char* b, uint64_t* br) {
+      const void* src; int es; bool left;
+      col_src(c, src, es, left);
+      if (left) issue_slice(src, es, l0, ln, b, br);
+      else issue_slice(src, es, wlo, wn, b, br);
+    };
+    auto write_col = [&](int c, const unsigned char* b) {
+      const void* src; int es; bool left;
+      col_src(c, src, es, left);
+      const unsigned char* s = b + slice_lead(src, es, left ? l0 : wlo);
+      void* dst = left ? p.ldst[c] : p.rdst[c - p.n_lout];
+      const uint16_t* map = left ? omap : orel;
+      if (es == 8) {
+        for (uint32_t o = threadIdx.x; o < total; o += JTHREADS) ((uint64_t*)dst)[obase + o] = ((const uint64_t*)s)[map[o]];
+      } else {
+        for (uint32_t o = threadIdx.x; o < total; o += JTHREADS) ((uint32_t*)dst)[obase + o] = ((const uint32_t*)s)[map[o]];
+      }
+    };
+    int keycol = -1;
+    for (int c = 0; c < p.n_lout; c++)
+      if (p.lsrc[c] == p.lkey && p.les[c] == (int)sizeof(K)) { keycol = c; break; }
+    // order of the staged columns: all but keycol
+    int nxt = 0;            // next column to load
+    auto next_col = [&]() { while (nxt == keycol) nxt++; return nxt < ncol ? nxt++ : -1; };
+    // every thread follows the same column sequence; thread 0 starts the copies
+    int inb1 = next_col(), inb2 = next_col();
+    if (threadIdx.x == 0) {
+      if (inb1 >= 0) start_load(inb1, buf1, &bar[1]);
+      if (inb2 >= 0) start_load(inb2, buf2, &bar[2]);
+    }
+    if (keycol >= 0) {
+      write_col(keycol, buf0);
+      __syncthreads();
+    }
+    while (inb1 >= 0 || inb2 >= 0) {
+      if (inb1 >= 0) {
+        mbar_wait(&bar[1], ph1); ph1 ^= 1;
+        write_col(inb1, buf1);
+        __syncthreads();
+        inb1 = next_col();
+        if (inb1 >= 0 && threadIdx.x == 0) start_load(inb1, buf1, &bar[1]);
+      }
+      if (inb2 >= 0) {
+        mbar_wait(&bar[2], ph2); ph2 ^= 1;
+        write_col(inb2, buf2);
+        __syncthreads();
+        inb2 = next_col();
+        if (inb2 >= 0 && threadIdx.x == 0) start_load(inb2, buf2, &bar[2]);
+      }
+    }
     return;
   }
-  // expanding case (large cross products): spread the outputs over the whole CTA
+  // ---- large cross products or windows that were not staged: spread the outputs over the whole CTA and read
+  // the sources from global memory
+  __syncthreads();
 #pragma unroll
   for (int j = 0; j < JPER; j++) {
-    if (i0 + j < ln) { slb[i0 + j] = lb[j]; scn[i0 + j] = ex; }
+    if (i0 + j < ln) { slb[i0 + j] = wlo + lb[j]; scn[i0 + j] = ex; }
     ex += cnt[j];
   }
   if (threadIdx.x == 0) scn[ln] = total;
@@ -454,8 +484,7 @@ __global__ void __launch_bounds__(JTHREADS) k_join_tiles(const __grid_constant__
   }
 }
 
-template <typename K>
-static size_t join_smem_bytes() { return (size_t)JR * sizeof(K) + (size_t)(2 * JT + 1) * 4 + 16; }
+static size_t join_smem_bytes() { return (size_t)3 * JBUF_BYTES + (size_t)4 * JOMAX + 16 + 3 * 8 + 16; }
 
 static void check_view(const hs_index_view* v) {
   if (!v || !v->cols || v->ncols <= 0 || v->n_indexed <= 0 || v->n_indexed > v->ncols || v->num_buckets <= 0 ||
@@ -721,7 +750,7 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
     jf.tile_win = d_win.as<uint32_t>();
     // key kind: 0 = int32 column, 1 = int64 column, 2 = packed u64 (built above)
     const int kkind = packed ? 2 : (lc[0].type == HS_INT64 ? 1 : 0);
-    const size_t smem = kkind ? join_smem_bytes<int64_t>() : join_smem_bytes<int32_t>();
+    const size_t smem = join_smem_bytes();
     auto launch_windows = [&]() {
       if (kkind == 2) LAUNCH(ctx, k_join_windows<uint64_t>, (ntiles + 7) / 8, 256, 0, jf);
       else if (kkind == 1) LAUNCH(ctx, k_join_windows<int64_t>, (ntiles + 7) / 8, 256, 0, jf);
@@ -738,15 +767,15 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
     int dev = 0;
     CK(cudaGetDevice(&dev));
     if (!attr_done[dev & 63]) {
-      CK(cudaFuncSetAttribute(k_join_tiles<int64_t, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int64_t>()));
-      CK(cudaFuncSetAttribute(k_join_tiles<int64_t, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int64_t>()));
-      CK(cudaFuncSetAttribute(k_join_tiles<int32_t, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int32_t>()));
-      CK(cudaFuncSetAttribute(k_join_tiles<int32_t, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int32_t>()));
-      CK(cudaFuncSetAttribute(k_join_tiles<int64_t, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int64_t>()));
-      CK(cudaFuncSetAttribute(k_join_tiles<int32_t, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int32_t>()));
-      CK(cudaFuncSetAttribute(k_join_tiles<uint64_t, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int64_t>()));
-      CK(cudaFuncSetAttribute(k_join_tiles<uint64_t, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int64_t>()));
-      CK(cudaFuncSetAttribute(k_join_tiles<uint64_t, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes<int64_t>()));
+      CK(cudaFuncSetAttribute(k_join_tiles<int64_t, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes()));
+      CK(cudaFuncSetAttribute(k_join_tiles<int64_t, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes()));
+      CK(cudaFuncSetAttribute(k_join_tiles<int32_t, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes()));
+      CK(cudaFuncSetAttribute(k_join_tiles<int32_t, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes()));
+      CK(cudaFuncSetAttribute(k_join_tiles<int64_t, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes()));
+      CK(cudaFuncSetAttribute(k_join_tiles<int32_t, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes()));
+      CK(cudaFuncSetAttribute(k_join_tiles<uint64_t, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes()));
+      CK(cudaFuncSetAttribute(k_join_tiles<uint64_t, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes()));
+      CK(cudaFuncSetAttribute(k_join_tiles<uint64_t, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)join_smem_bytes()));
       attr_done[dev & 63] = true;
     }
     uint64_t h_tot = 0;
