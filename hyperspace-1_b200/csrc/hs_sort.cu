@@ -188,20 +188,27 @@ __device__ __forceinline__ void scatter_column_widen(const unsigned char* stage,
 template <int MODE>
 __device__ __forceinline__ void partition_tile(const PartParams& p, unsigned char* smem_raw, uint32_t tile_start,
                                                uint32_t tile_len, int bits, uint32_t shift, uint64_t seg_base,
-                                               uint32_t* cursor, uint32_t dst_bias) {
+                                               uint32_t* cursor, uint32_t dst_bias, uint64_t* ext_bar = nullptr,
+                                               uint32_t* ext_phase = nullptr) {
+  // ext_bar / ext_phase: three mbarriers that live on across calls (persistent kernel) and the parity each one
+  // completes next (bit b of *ext_phase); without them the barriers of the carve-up are initialised here
   TileSmem sm = carve(smem_raw, p.radix_pad);
+  if (ext_bar) sm.bar = ext_bar;
+  const uint32_t ph_in = ext_phase ? *ext_phase : 0u;
   const int ncols = p.mv.n;
   // column order: in MODE 1 the key column goes first (its slice also feeds the digits)
   const int first = MODE == 1 ? p.key.col : 0;
   auto col_at = [&](int i) { return i == 0 ? first : (i <= first ? i - 1 : i); };
-  if (threadIdx.x == 0) {
-    mbar_init(&sm.bar[0], 1);
-    mbar_init(&sm.bar[1], 1);
-    mbar_init(&sm.bar[2], 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  if (!ext_bar) {
+    if (threadIdx.x == 0) {
+      mbar_init(&sm.bar[0], 1);
+      mbar_init(&sm.bar[1], 1);
+      mbar_init(&sm.bar[2], 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
   }
-  __syncthreads();
   if (threadIdx.x == 0) {
     if (MODE != 1) issue_slice(p.bucket, 2, tile_start, tile_len, sm.bstage, &sm.bar[2]);
     int c0 = col_at(0);
@@ -213,8 +220,8 @@ __device__ __forceinline__ void partition_tile(const PartParams& p, unsigned cha
   }
   uint32_t digit[PT_ITEMS], pos[PT_ITEMS];
   uint32_t vmask = 0;
-  if (MODE == 1) mbar_wait(&sm.bar[0], 0);
-  else mbar_wait(&sm.bar[2], 0);
+  if (MODE == 1) mbar_wait(&sm.bar[0], ph_in & 1u);
+  else mbar_wait(&sm.bar[2], (ph_in >> 2) & 1u);
   const uint16_t* sbucket = (const uint16_t*)(sm.bstage + slice_lead(p.bucket, 2, tile_start));
 #pragma unroll
   for (int k = 0; k < PT_ITEMS; k++) {
@@ -253,7 +260,7 @@ __device__ __forceinline__ void partition_tile(const PartParams& p, unsigned cha
   __syncthreads();
   for (int i = 0; i < ncols; i++) {
     const int c = col_at(i), b = i & 1, es = p.mv.esize[c];
-    mbar_wait(&sm.bar[b], (uint32_t)(i >> 1) & 1u);
+    mbar_wait(&sm.bar[b], ((uint32_t)(i >> 1) ^ (ph_in >> b)) & 1u);
     const uint32_t lead = slice_lead(p.mv.src[c], es, tile_start);
     if (MODE == 2 && c + 1 == p.conv_col1) {
       scatter_column_peers_narrow(sm.stage[b], lead, p.pdst, c, tile_len, sm.inv, sm.gdst, p.conv_min);
@@ -279,6 +286,8 @@ __device__ __forceinline__ void partition_tile(const PartParams& p, unsigned cha
       issue_slice(p.mv.src[cn], p.mv.esize[cn], tile_start, tile_len, sm.stage[b], &sm.bar[b]);
     }
   }
+  if (ext_phase)
+    *ext_phase = ph_in ^ (uint32_t)(((ncols + 1) >> 1) & 1) ^ (uint32_t)(((ncols >> 1) & 1) << 1) ^ (MODE != 1 ? 4u : 0u);
 }
 
 template <int MODE>
@@ -632,7 +641,8 @@ template <int KMODE>
 __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_t* esize, int ncols_,
                                            const void* const* src, void* const* dst, const KeySrc& kspec,
                                            uint32_t start, uint32_t dstart, uint32_t len, uint32_t seg_bits_,
-                                           uint64_t seg_base_, bool in_place) {
+                                           uint64_t seg_base_, bool in_place, uint64_t* ext_bar = nullptr,
+                                           uint32_t* ext_phase = nullptr) {
   unsigned char* stage0 = smem_raw;
   unsigned char* stage1 = smem_raw + STAGE_BYTES;
   uint32_t* sdata = (uint32_t*)(smem_raw + 2 * STAGE_BYTES);  // LEAF_MAX packed words
@@ -641,7 +651,10 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
   uint32_t* loc = tot + 256;                        // 256
   uint32_t* scratch = loc + 256;                    // PT_SCRATCH
   uint64_t* red = (uint64_t*)(scratch + PT_SCRATCH);  // 2 * PT_WARPS + 2
-  uint64_t* bar = red + 2 * PT_WARPS + 2;           // 2 mbarriers
+  uint64_t* bar = ext_bar ? ext_bar : red + 2 * PT_WARPS + 2;   // 2 mbarriers (see partition_tile for ext_*)
+  const uint32_t ph_in = ext_phase ? *ext_phase : 0u;
+  // both barriers complete once for the first two slices whatever happens next
+  if (ext_phase) *ext_phase = ph_in ^ 1u ^ (ncols_ > 1 ? 2u : 0u);
 
   const int w = threadIdx.x >> 5;
   const int items = (int)((len + PT_THREADS - 1) / PT_THREADS);
@@ -649,13 +662,15 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
   const int first = kspec.col;
   auto col_at = [&](int i) { return i == 0 ? first : (i <= first ? i - 1 : i); };
 
-  if (threadIdx.x == 0) {
-    mbar_init(&bar[0], 1);
-    mbar_init(&bar[1], 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  if (!ext_bar) {
+    if (threadIdx.x == 0) {
+      mbar_init(&bar[0], 1);
+      mbar_init(&bar[1], 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
   }
-  __syncthreads();
   if (threadIdx.x == 0) {
     issue_slice(src[first], esize[first], start, len, stage0, &bar[0]);
     if (ncols > 1) {
@@ -669,7 +684,7 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
   const uint64_t seg_base = seg_base_;
   const bool known = seg_bits <= L32_MAX_KEY_BITS;
   const uint64_t seg_mask = known ? ((1ull << seg_bits) - 1ull) : ~0ull;
-  mbar_wait(&bar[0], 0);
+  mbar_wait(&bar[0], ph_in & 1u);
   const unsigned char* ks = stage0 + slice_lead(src[first], esize[first], start);
   uint64_t key[PT_ITEMS];
   uint32_t vmask = 0;
@@ -715,7 +730,7 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
   const int drop = nbits > L32_MAX_KEY_BITS ? nbits - L32_MAX_KEY_BITS : 0;
   if (nbits == 0 && in_place) {
     // all keys equal and the rows are in place; a CTA must not retire with a bulk copy in flight
-    if (ncols > 1) mbar_wait(&bar[1], 0);
+    if (ncols > 1) mbar_wait(&bar[1], (ph_in >> 1) & 1u);
     return 0;
   }
   if (drop) nbits = L32_MAX_KEY_BITS;
@@ -812,14 +827,14 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
     }
   }
   if (too_long) {
-    if (ncols > 1) mbar_wait(&bar[1], 0);
+    if (ncols > 1) mbar_wait(&bar[1], (ph_in >> 1) & 1u);
     return 1;
   }
   // ---- every column: staged slice -> permutation -> coalesced store
   for (int i = 0; i < ncols; i++) {
     const int c = col_at(i), b = i & 1, es = esize[c];
     unsigned char* stage = b ? stage1 : stage0;
-    mbar_wait(&bar[b], (uint32_t)(i >> 1) & 1u);
+    mbar_wait(&bar[b], ((uint32_t)(i >> 1) ^ (ph_in >> b)) & 1u);
     const uint32_t lead = slice_lead(src[c], es, start);
     switch (es) {
       case 8: leaf_permute_column<uint64_t>(stage, lead, (uint64_t*)dst[c], dstart, len, sdata); break;
@@ -833,6 +848,8 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
       issue_slice(src[cn], esize[cn], start, len, stage, &bar[b]);
     }
   }
+  if (ext_phase)
+    *ext_phase = ph_in ^ (uint32_t)(((ncols + 1) >> 1) & 1) ^ (uint32_t)(((ncols >> 1) & 1) << 1);
   return 0;
 }
 
@@ -1234,10 +1251,15 @@ __device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-// the CTA waits until *p >= need (written by CTAs with smaller tickets)
-__device__ __forceinline__ void pipe_wait(const uint32_t* p, uint32_t need) {
+// the CTA waits until *p1 >= need1 and *p2 >= need2 (counters bumped by CTAs with smaller tickets); p1 may be null
+__device__ __forceinline__ void pipe_wait2(const uint32_t* p1, uint32_t need1, const uint32_t* p2, uint32_t need2) {
   if (threadIdx.x == 0) {
-    while (ld_acquire_u32(p) < need) __nanosleep(64);
+    uint32_t a = p1 ? ld_acquire_u32(p1) : need1, b = ld_acquire_u32(p2);
+    while (a < need1 || b < need2) {
+      __nanosleep(40);
+      if (a < need1) a = ld_acquire_u32(p1);
+      if (b < need2) b = ld_acquire_u32(p2);
+    }
     __threadfence();   // also drops this SM's L1 lines: a slot may have been read here under its previous contents
     asm volatile("fence.proxy.async.global;" ::: "memory");   // what was acquired is read by bulk copies next
   }
@@ -1245,10 +1267,12 @@ __device__ __forceinline__ void pipe_wait(const uint32_t* p, uint32_t need) {
 }
 // the CTA's global writes are done: publish them and bump a counter; returns the counter's old value to thread 0
 __device__ __forceinline__ uint32_t pipe_signal(uint32_t* p) {
-  __threadfence();
   __syncthreads();
   uint32_t old = 0;
-  if (threadIdx.x == 0) old = atomicAdd(p, 1u);
+  if (threadIdx.x == 0) {
+    __threadfence();
+    old = atomicAdd(p, 1u);
+  }
   return old;
 }
 // largest s in [lo, hi) with pre[s] <= x
@@ -1260,109 +1284,196 @@ __device__ __forceinline__ uint32_t pipe_find(const uint32_t* pre, uint32_t lo, 
   return lo;
 }
 
-template <int KMODE>
-__global__ void __launch_bounds__(PT_THREADS, 2) k_sort_pipeline(const __grid_constant__ PipeParams p) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  __shared__ uint32_t s_ticket, s_phase, s_flag;
-  if (threadIdx.x == 0) s_ticket = atomicAdd(p.ticket, 1u);
-  __syncthreads();
-  const uint32_t t = s_ticket;
-  for (uint32_t i = threadIdx.x; i < p.nphases; i += PT_THREADS) {
-    const uint32_t f = p.phases[i].first, e = i + 1 < p.nphases ? p.phases[i + 1].first : p.ntickets;
-    if (f <= t && t < e) s_phase = i;
-  }
-  __syncthreads();
-  const PipePhase ph = p.phases[s_phase];
-  const uint32_t idx = t - ph.first, g = ph.group;
-  const uint32_t s0 = p.grp_seg0[g], s1 = p.grp_seg0[g + 1];
-  const uint32_t bias = (g % PIPE_SLOTS) * p.slot_rows - p.seg_start[s0];   // slot row = row + bias (mod 2^32)
-  const int ncols = p.part.mv.n;
-  if (ph.kind == PK_HIST || ph.kind == PK_SCATTER) {
-    const uint32_t T = p.seg_tile0[s0] + idx;
-    const uint32_t s = pipe_find(p.seg_tile0, s0, s1, T);
-    const uint32_t tt = T - p.seg_tile0[s], ntile = p.seg_tile0[s + 1] - p.seg_tile0[s];
-    const uint32_t slen = p.seg_len[s];
-    const uint32_t tile_start = p.seg_start[s] + tt * PT_TILE;
-    const uint32_t left = slen - tt * PT_TILE;
-    const uint32_t tile_len = left < PT_TILE ? left : PT_TILE;
-    const int bits = msd_bits(slen, p.key_bits);
-    const uint32_t shift = p.key_bits - bits;
-    uint32_t* cursor = p.cursor + (size_t)s * MSD_RADIX;
-    if (ph.kind == PK_HIST) {
-      uint32_t* hist = (uint32_t*)smem_raw;
-      uint32_t* scratch = hist + MSD_RADIX;
-      msd_hist_tile(p.part.mv, p.part.key, tile_start, tile_len, 0, shift, bits, hist, cursor);
-      const uint32_t old = pipe_signal(&p.hist_done[s]);
-      if (threadIdx.x == 0) s_flag = old + 1 == ntile;
-      __syncthreads();
-      if (s_flag) {
-        // the last histogram tile of the segment: counts -> write cursors and the children's extents
-        __threadfence();
-        const uint32_t d = threadIdx.x;
-        const uint32_t hcount = d < MSD_RADIX ? __ldcg(&cursor[d]) : 0;
-        const uint32_t ex = block256_excl_scan_u32(hcount, scratch);
-        if (d < MSD_RADIX) {
-          const uint32_t start = p.seg_start[s] + ex;
-          cursor[d] = start;
-          p.child_start[(size_t)s * MSD_RADIX + d] = start;
-          p.child_len[(size_t)s * MSD_RADIX + d] = hcount;
-        }
-        pipe_signal(&p.plan_done[s]);
-      }
-    } else {
-      if (g >= PIPE_SLOTS) {   // the slot must have been read by every leaf of the group that used it last
-        const uint32_t q0 = p.grp_seg0[g - PIPE_SLOTS], q1 = p.grp_seg0[g - PIPE_SLOTS + 1];
-        pipe_wait(&p.leaf_done[g - PIPE_SLOTS], p.seg_child0[q1] - p.seg_child0[q0]);
-      }
-      pipe_wait(&p.plan_done[s], 1u);
-      partition_tile<1>(p.part, smem_raw, tile_start, tile_len, bits, shift, 0, cursor, bias);
-      pipe_signal(&p.scat_done[s]);
+// One descriptor per ticket, written by k_pipe_describe before the pipeline starts, so that a CTA learns all about
+// its next work item from one 32-byte load instead of a chain of dependent table look-ups.
+struct PipeItem {
+  uint32_t kind;     // PK_*
+  uint32_t group;
+  uint32_t seg;
+  uint32_t a;        // H/S: first row of the tile; L: index of the child inside the segment
+  uint32_t b;        // H/S: rows of the tile
+  uint32_t bias;     // slot row = row + bias (mod 2^32)
+  uint32_t need;     // H: tiles of the segment; S: leaf items of the group that used the slot last (0: none);
+                     // L: scatter tiles of the segment
+  uint32_t pad;
+};
+__global__ void __launch_bounds__(256) k_pipe_describe(const __grid_constant__ PipeParams p, PipeItem* items,
+                                                       uint32_t n_end) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= p.ntickets) {
+    if (t < p.ntickets + n_end) {     // end markers: one per CTA of the pipeline kernel
+      PipeItem e;
+      e.kind = 0xFFFFFFFFu; e.group = e.seg = e.a = e.b = e.bias = e.need = e.pad = 0;
+      items[t] = e;
     }
     return;
   }
-  // ---- PK_LEAF: one child of one segment
-  const uint32_t C = p.seg_child0[s0] + idx;
-  const uint32_t s = pipe_find(p.seg_child0, s0, s1, C);
-  const uint32_t ch = C - p.seg_child0[s];
-  pipe_wait(&p.scat_done[s], p.seg_tile0[s + 1] - p.seg_tile0[s]);
-  const uint32_t cs = __ldcg(&p.child_start[(size_t)s * MSD_RADIX + ch]);
-  const uint32_t cl = __ldcg(&p.child_len[(size_t)s * MSD_RADIX + ch]);
-  const uint32_t sh = p.key_bits - (uint32_t)msd_bits(p.seg_len[s], p.key_bits);
-  const void* const* ring = (const void* const*)p.part.mv.dst;
-  if (cl == 0) {
-  } else if (cl <= SMALL_MAX) {
-    if (threadIdx.x < 32) leaf_small_warp(p.part.mv.esize, ncols, ring, p.fin, p.part.key, cs + bias, cs, cl);
-  } else if (cl <= LEAF_MAX) {
-    const int r = leaf32_body<KMODE>(smem_raw, p.part.mv.esize, ncols, ring, p.fin, p.part.key, cs + bias, cs, cl, sh, 0,
-                                     false);
-    if (r) {
-      __syncthreads();
-      leaf64_body(smem_raw, p.part.mv.esize, ncols, ring, p.fin, p.part.key, cs + bias, cs, cl, false);
-    }
-  } else {
-    // still larger than a leaf (skewed keys, or all keys equal): the rows leave the slot for the place they came
-    // from; if key bits are left, the level loop after this kernel splits the child further
-    for (int c = 0; c < ncols; c++) {
-      const int es = p.part.mv.esize[c];
-      const unsigned char* a = (const unsigned char*)ring[c] + (size_t)(uint32_t)(cs + bias) * es;
-      unsigned char* b = (sh ? (unsigned char*)p.part.mv.src[c] : (unsigned char*)p.fin[c]) + (size_t)cs * es;
-      const size_t bytes = (size_t)cl * es;
-      if (((((uintptr_t)a) | ((uintptr_t)b)) & 7) == 0) {
-        for (size_t i = threadIdx.x; i < (bytes >> 3); i += PT_THREADS) ((uint64_t*)b)[i] = ((const uint64_t*)a)[i];
-        for (size_t i = (bytes & ~(size_t)7) + threadIdx.x; i < bytes; i += PT_THREADS) b[i] = a[i];
-      } else {
-        for (size_t i = threadIdx.x; i < bytes; i += PT_THREADS) b[i] = a[i];
-      }
-    }
-    if (sh && threadIdx.x == 0) {
-      const uint32_t i = atomicAdd(&p.counters[1], 1u);
-      p.large.start[i] = cs; p.large.len[i] = cl; p.large.shift[i] = sh; p.large.base[i] = 0;
-      atomicAdd(&p.counters[3], (cl + PT_TILE - 1) / PT_TILE);
-    }
+  uint32_t lo = 0, hi = p.nphases;
+  while (hi - lo > 1) {
+    uint32_t mid = (lo + hi) >> 1;
+    if (p.phases[mid].first <= t) lo = mid; else hi = mid;
   }
-  pipe_signal(&p.leaf_done[g]);
+  const PipePhase ph = p.phases[lo];
+  const uint32_t idx = t - ph.first, g = ph.group;
+  const uint32_t s0 = p.grp_seg0[g], s1 = p.grp_seg0[g + 1];
+  PipeItem it;
+  it.kind = ph.kind;
+  it.group = g;
+  it.bias = (g % PIPE_SLOTS) * p.slot_rows - p.seg_start[s0];
+  it.pad = 0;
+  if (ph.kind == PK_LEAF) {
+    const uint32_t C = p.seg_child0[s0] + idx;
+    const uint32_t s = pipe_find(p.seg_child0, s0, s1, C);
+    it.seg = s;
+    it.a = C - p.seg_child0[s];
+    it.b = 0;
+    it.need = p.seg_tile0[s + 1] - p.seg_tile0[s];
+  } else {
+    const uint32_t T = p.seg_tile0[s0] + idx;
+    const uint32_t s = pipe_find(p.seg_tile0, s0, s1, T);
+    const uint32_t tt = T - p.seg_tile0[s];
+    const uint32_t left = p.seg_len[s] - tt * PT_TILE;
+    it.seg = s;
+    it.a = p.seg_start[s] + tt * PT_TILE;
+    it.b = left < PT_TILE ? left : PT_TILE;
+    if (ph.kind == PK_HIST) it.need = p.seg_tile0[s + 1] - p.seg_tile0[s];
+    else if (g >= PIPE_SLOTS) {
+      const uint32_t q0 = p.grp_seg0[g - PIPE_SLOTS], q1 = p.grp_seg0[g - PIPE_SLOTS + 1];
+      it.need = p.seg_child0[q1] - p.seg_child0[q0];
+    } else it.need = 0;
+  }
+  items[t] = it;
 }
 
+// Persistent CTAs (two per SM): each takes tickets until none is left. While an item is being worked on, one
+// lane of warp 1 already fetches the next ticket and its descriptor.
+template <int KMODE>
+__global__ void __launch_bounds__(PT_THREADS, 2) k_sort_pipeline(const __grid_constant__ PipeParams p,
+                                                                 const PipeItem* __restrict__ items,
+                                                                 uint32_t bar_offset) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ __align__(16) PipeItem s_item[2];
+  __shared__ uint32_t s_flag;
+  uint64_t* bar = (uint64_t*)(smem_raw + bar_offset);   // 3 mbarriers behind every body's shared-memory layout
+  uint32_t phase = 0;                                    // parity each of them completes next
+  const int ncols = p.part.mv.n;
+  const void* const* ring = (const void* const*)p.part.mv.dst;
+  // the next item is fetched by lane 0 of warp 1 in three non-blocking steps spread over the current item: take
+  // a ticket (top), load its descriptor (after the item's first wait), park it in shared memory (bottom)
+  // (tickets past the end read one of the end markers that follow the descriptors)
+  uint32_t nt = 0;
+  auto load_desc = [&](int slot) {
+    const PipeItem* q = items + nt;
+    const uint32_t d = smem_u32(&s_item[slot]);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(d), "l"(q) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(d + 16), "l"((const char*)q + 16) : "memory");
+  };
+  auto park = [&]() { asm volatile("cp.async.wait_all;" ::: "memory"); };
+  if (threadIdx.x == 0) {
+    mbar_init(&bar[0], 1);
+    mbar_init(&bar[1], 1);
+    mbar_init(&bar[2], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (threadIdx.x == 32) {
+    nt = atomicAdd(p.ticket, 1u);
+    load_desc(0);
+    park();
+  }
+  __syncthreads();
+  for (int cur = 0;; cur ^= 1) {
+    const PipeItem it = s_item[cur];
+    if (it.kind == 0xFFFFFFFFu) break;
+    if (threadIdx.x == 32) nt = atomicAdd(p.ticket, 1u);
+    const uint32_t s = it.seg, g = it.group, bias = it.bias;
+    if (it.kind == PK_HIST || it.kind == PK_SCATTER) {
+      const uint32_t slen = p.seg_len[s];
+      const int bits = msd_bits(slen, p.key_bits);
+      const uint32_t shift = p.key_bits - bits;
+      uint32_t* cursor = p.cursor + (size_t)s * MSD_RADIX;
+      if (it.kind == PK_HIST) {
+        uint32_t* hist = (uint32_t*)smem_raw;
+        uint32_t* scratch = hist + MSD_RADIX;
+        msd_hist_tile(p.part.mv, p.part.key, it.a, it.b, 0, shift, bits, hist, cursor);
+        if (threadIdx.x == 32) load_desc(cur ^ 1);
+        const uint32_t old = pipe_signal(&p.hist_done[s]);
+        if (threadIdx.x == 0) s_flag = old + 1 == it.need;
+        __syncthreads();
+        if (s_flag) {
+          // the last histogram tile of the segment: counts -> write cursors and the children's extents
+          __threadfence();
+          const uint32_t d = threadIdx.x;
+          const uint32_t hcount = d < MSD_RADIX ? __ldcg(&cursor[d]) : 0;
+          const uint32_t ex = block256_excl_scan_u32(hcount, scratch);
+          if (d < MSD_RADIX) {
+            const uint32_t start = p.seg_start[s] + ex;
+            cursor[d] = start;
+            p.child_start[(size_t)s * MSD_RADIX + d] = start;
+            p.child_len[(size_t)s * MSD_RADIX + d] = hcount;
+          }
+          pipe_signal(&p.plan_done[s]);
+        }
+      } else {
+        // the slot must have been read by every leaf of the group that used it last; the cursors must be ready
+        pipe_wait2(it.need ? &p.leaf_done[g - PIPE_SLOTS] : nullptr, it.need, &p.plan_done[s], 1u);
+        if (threadIdx.x == 32) load_desc(cur ^ 1);
+        partition_tile<1>(p.part, smem_raw, it.a, it.b, bits, shift, 0, cursor, bias, bar, &phase);
+        pipe_signal(&p.scat_done[s]);
+      }
+    } else {
+      // ---- PK_LEAF: one child of one segment
+      pipe_wait2(nullptr, 0, &p.scat_done[s], it.need);
+      if (threadIdx.x == 32) load_desc(cur ^ 1);
+      const uint32_t cs = __ldcg(&p.child_start[(size_t)s * MSD_RADIX + it.a]);
+      const uint32_t cl = __ldcg(&p.child_len[(size_t)s * MSD_RADIX + it.a]);
+      const uint32_t sh = p.key_bits - (uint32_t)msd_bits(p.seg_len[s], p.key_bits);
+      if (cl == 0) {
+      } else if (cl <= SMALL_MAX) {
+        if (threadIdx.x < 32) leaf_small_warp(p.part.mv.esize, ncols, ring, p.fin, p.part.key, cs + bias, cs, cl);
+      } else if (cl <= LEAF_MAX) {
+        const int r = leaf32_body<KMODE>(smem_raw, p.part.mv.esize, ncols, ring, p.fin, p.part.key, cs + bias, cs, cl,
+                                         sh, 0, false, bar, &phase);
+        if (r) {
+          __syncthreads();
+          leaf64_body(smem_raw, p.part.mv.esize, ncols, ring, p.fin, p.part.key, cs + bias, cs, cl, false);
+        }
+      } else {
+        // still larger than a leaf (skewed keys, or all keys equal): the rows leave the slot for the place they
+        // came from; if key bits are left, the level loop after this kernel splits the child further
+        for (int c = 0; c < ncols; c++) {
+          const int es = p.part.mv.esize[c];
+          const unsigned char* a = (const unsigned char*)ring[c] + (size_t)(uint32_t)(cs + bias) * es;
+          unsigned char* b = (sh ? (unsigned char*)p.part.mv.src[c] : (unsigned char*)p.fin[c]) + (size_t)cs * es;
+          const size_t bytes = (size_t)cl * es;
+          if (((((uintptr_t)a) | ((uintptr_t)b)) & 7) == 0) {
+            for (size_t i = threadIdx.x; i < (bytes >> 3); i += PT_THREADS) ((uint64_t*)b)[i] = ((const uint64_t*)a)[i];
+            for (size_t i = (bytes & ~(size_t)7) + threadIdx.x; i < bytes; i += PT_THREADS) b[i] = a[i];
+          } else {
+            for (size_t i = threadIdx.x; i < bytes; i += PT_THREADS) b[i] = a[i];
+          }
+        }
+        if (sh && threadIdx.x == 0) {
+          const uint32_t i = atomicAdd(&p.counters[1], 1u);
+          p.large.start[i] = cs; p.large.len[i] = cl; p.large.shift[i] = sh; p.large.base[i] = 0;
+          atomicAdd(&p.counters[3], (cl + PT_TILE - 1) / PT_TILE);
+        }
+      }
+      pipe_signal(&p.leaf_done[g]);
+    }
+    if (threadIdx.x == 32) park();
+    __syncthreads();   // the item's shared memory is free, s_item[cur ^ 1] is in place
+  }
+}
+
+static int hs_num_sms() {
+  static int n[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  int& v = n[dev & 63];
+  if (!v && cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) v = HS_NUM_SMS;
+  return v;
+}
 static bool pipeline_enabled() {
   const char* e = getenv("HSGPU_SORT_PIPELINE");
   return !(e && *e == '0');
@@ -1471,7 +1582,7 @@ static void run_sort_pipeline(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key
     int dev = 0;
     CK(cudaGetDevice(&dev));
     if (!attr_dev[dev & 63]) {
-      const int sm = (int)pipeline_smem_bytes();
+      const int sm = (int)((pipeline_smem_bytes() + 15) & ~(size_t)15) + 32;
       CK(cudaFuncSetAttribute(k_sort_pipeline<KS_U64>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
       CK(cudaFuncSetAttribute(k_sort_pipeline<KS_I64>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
       CK(cudaFuncSetAttribute(k_sort_pipeline<KS_I32>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
@@ -1480,10 +1591,16 @@ static void run_sort_pipeline(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key
   }
   {
     Stage stg(c, "sort_pipeline");
-    const size_t sm = pipeline_smem_bytes();
-    if (key.mode == KS_U64) LAUNCH(c, k_sort_pipeline<KS_U64>, ticket, PT_THREADS, sm, *pp);
-    else if (key.mode == KS_I64) LAUNCH(c, k_sort_pipeline<KS_I64>, ticket, PT_THREADS, sm, *pp);
-    else LAUNCH(c, k_sort_pipeline<KS_I32>, ticket, PT_THREADS, sm, *pp);
+    unsigned grid = 2 * (unsigned)hs_num_sms();
+    if (grid > ticket) grid = ticket;
+    DBuf d_items(c, ((size_t)ticket + grid) * sizeof(PipeItem));
+    LAUNCH(c, k_pipe_describe, (ticket + grid + 255) / 256, 256, 0, *pp, d_items.as<PipeItem>(), (uint32_t)grid);
+    const size_t bar_off = (pipeline_smem_bytes() + 15) & ~(size_t)15;
+    const size_t sm = bar_off + 32;
+    const PipeItem* di = d_items.as<PipeItem>();
+    if (key.mode == KS_U64) LAUNCH(c, k_sort_pipeline<KS_U64>, grid, PT_THREADS, sm, *pp, di, (uint32_t)bar_off);
+    else if (key.mode == KS_I64) LAUNCH(c, k_sort_pipeline<KS_I64>, grid, PT_THREADS, sm, *pp, di, (uint32_t)bar_off);
+    else LAUNCH(c, k_sort_pipeline<KS_I32>, grid, PT_THREADS, sm, *pp, di, (uint32_t)bar_off);
   }
   delete pp;
 }
