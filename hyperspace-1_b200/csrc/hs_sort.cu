@@ -616,12 +616,12 @@ __device__ __forceinline__ void leaf_move_column(const T* __restrict__ src, T* _
 // key - min and the row's position are packed into one 32-bit word, the first LSD pass (up to 11 bits)
 // ranks with shared-memory atomics (no stability needed), the remaining <= 9 bits take one stable
 // ballot-ranked pass. Segments with a wider key range are flagged for k_leaf_sort.
-template <typename T>
+template <typename T, int ITEMS>
 __device__ __forceinline__ void leaf_permute_column(const unsigned char* stage, uint32_t lead, T* __restrict__ dst,
                                                     uint32_t start, uint32_t len, const uint32_t* sdata) {
   const T* col = (const T*)(stage + lead);
 #pragma unroll 4
-  for (int k = 0; k < PT_ITEMS; k++) {
+  for (int k = 0; k < ITEMS; k++) {
     uint32_t j = threadIdx.x + k * PT_THREADS;
     if (j < len) dst[start + j] = col[sdata[j] & ((1u << L32_IDX_BITS) - 1u)];
   }
@@ -637,7 +637,9 @@ __device__ __forceinline__ void leaf_permute_column(const unsigned char* stage, 
 // for k_leaf_sort.
 // Returns 0 when the segment has been written sorted to dst, 1 when it holds a run of more than 64 rows with
 // equal 20-bit prefixes (nothing written: the 64-bit kernel has to take it).
-template <int KMODE>
+// ITEMS: rows per thread the code is unrolled for (len <= ITEMS * PT_THREADS): a half-full leaf takes the 4-row
+// variant and issues half the instructions.
+template <int KMODE, int ITEMS>
 __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_t* esize, int ncols_,
                                            const void* const* src, void* const* dst, const KeySrc& kspec,
                                            uint32_t start, uint32_t dstart, uint32_t len, uint32_t seg_bits_,
@@ -686,11 +688,11 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
   const uint64_t seg_mask = known ? ((1ull << seg_bits) - 1ull) : ~0ull;
   mbar_wait(&bar[0], ph_in & 1u);
   const unsigned char* ks = stage0 + slice_lead(src[first], esize[first], start);
-  uint64_t key[PT_ITEMS];
+  uint64_t key[ITEMS];
   uint32_t vmask = 0;
   uint64_t mn = ~0ull, mx = 0;
 #pragma unroll
-  for (int k = 0; k < PT_ITEMS; k++) {
+  for (int k = 0; k < ITEMS; k++) {
     uint32_t idx = threadIdx.x + k * PT_THREADS;
     bool v = idx < len;
     vmask |= (uint32_t)v << k;
@@ -735,14 +737,14 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
   }
   if (drop) nbits = L32_MAX_KEY_BITS;
 
-  uint32_t word[PT_ITEMS], pos[PT_ITEMS];
+  uint32_t word[ITEMS], pos[ITEMS];
 #pragma unroll
-  for (int k = 0; k < PT_ITEMS; k++)
+  for (int k = 0; k < ITEMS; k++)
     word[k] = ((uint32_t)((key[k] - kmin) >> drop) << L32_IDX_BITS) | (threadIdx.x + k * PT_THREADS);
 
   if (nbits == 0) {
 #pragma unroll
-    for (int k = 0; k < PT_ITEMS; k++)
+    for (int k = 0; k < ITEMS; k++)
       if ((vmask >> k) & 1u) sdata[threadIdx.x + k * PT_THREADS] = word[k];
     __syncthreads();
   } else {
@@ -750,9 +752,9 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
     int ba = nbits < L32_ATOMIC_BITS ? nbits : L32_ATOMIC_BITS;
     if (nbits - ba > 8) ba = nbits - 8;  // the stable pass handles at most 8 bits
     const int radix_a = 1 << ba;
-    tile_rank_atomic_w<PT_ITEMS>(word, L32_IDX_BITS, (1u << ba) - 1u, vmask, items, radix_a, cnt, scratch, pos);
+    tile_rank_atomic_w<ITEMS>(word, L32_IDX_BITS, (1u << ba) - 1u, vmask, items, radix_a, cnt, scratch, pos);
 #pragma unroll
-    for (int k = 0; k < PT_ITEMS; k++)
+    for (int k = 0; k < ITEMS; k++)
       if ((vmask >> k) & 1u) sdata[pos[k]] = word[k];
     __syncthreads();
     // ---- pass B: the remaining high bits, stable
@@ -762,15 +764,15 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
       const uint32_t base = w * chunk + lane_id();
       uint32_t vm2 = 0;
 #pragma unroll
-      for (int k = 0; k < PT_ITEMS; k++) {
+      for (int k = 0; k < ITEMS; k++) {
         uint32_t idx = base + k * 32;
         bool v = k < items && idx < len;
         vm2 |= (uint32_t)v << k;
         word[k] = v ? sdata[idx] : 0;
       }
-      tile_rank_w<PT_ITEMS>(word, L32_IDX_BITS + ba, vm2, items, bb, 256, cnt, tot, loc, scratch, pos);
+      tile_rank_w<ITEMS>(word, L32_IDX_BITS + ba, vm2, items, bb, 256, cnt, tot, loc, scratch, pos);
 #pragma unroll
-      for (int k = 0; k < PT_ITEMS; k++)
+      for (int k = 0; k < ITEMS; k++)
         if ((vm2 >> k) & 1u) sdata[pos[k]] = word[k];
       __syncthreads();
     }
@@ -781,9 +783,9 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
   // 64-bit kernel instead.
   bool too_long = false;
   if (drop) {
-    uint32_t npos[PT_ITEMS];
+    uint32_t npos[ITEMS];
 #pragma unroll
-    for (int k = 0; k < PT_ITEMS; k++) {
+    for (int k = 0; k < ITEMS; k++) {
       const uint32_t j = threadIdx.x + k * PT_THREADS;
       npos[k] = j;
       if (j < len) {
@@ -811,15 +813,15 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
     }
     too_long = __syncthreads_or(too_long);
     if (!too_long) {
-      uint32_t wv[PT_ITEMS];
+      uint32_t wv[ITEMS];
 #pragma unroll
-      for (int k = 0; k < PT_ITEMS; k++) {
+      for (int k = 0; k < ITEMS; k++) {
         const uint32_t j = threadIdx.x + k * PT_THREADS;
         wv[k] = j < len ? sdata[j] : 0;
       }
       __syncthreads();
 #pragma unroll
-      for (int k = 0; k < PT_ITEMS; k++) {
+      for (int k = 0; k < ITEMS; k++) {
         const uint32_t j = threadIdx.x + k * PT_THREADS;
         if (j < len) sdata[npos[k]] = wv[k];
       }
@@ -837,10 +839,10 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
     mbar_wait(&bar[b], ((uint32_t)(i >> 1) ^ (ph_in >> b)) & 1u);
     const uint32_t lead = slice_lead(src[c], es, start);
     switch (es) {
-      case 8: leaf_permute_column<uint64_t>(stage, lead, (uint64_t*)dst[c], dstart, len, sdata); break;
-      case 4: leaf_permute_column<uint32_t>(stage, lead, (uint32_t*)dst[c], dstart, len, sdata); break;
-      case 2: leaf_permute_column<uint16_t>(stage, lead, (uint16_t*)dst[c], dstart, len, sdata); break;
-      default: leaf_permute_column<uint8_t>(stage, lead, (uint8_t*)dst[c], dstart, len, sdata); break;
+      case 8: leaf_permute_column<uint64_t, ITEMS>(stage, lead, (uint64_t*)dst[c], dstart, len, sdata); break;
+      case 4: leaf_permute_column<uint32_t, ITEMS>(stage, lead, (uint32_t*)dst[c], dstart, len, sdata); break;
+      case 2: leaf_permute_column<uint16_t, ITEMS>(stage, lead, (uint16_t*)dst[c], dstart, len, sdata); break;
+      default: leaf_permute_column<uint8_t, ITEMS>(stage, lead, (uint8_t*)dst[c], dstart, len, sdata); break;
     }
     __syncthreads();  // stage[b] is free again
     if (threadIdx.x == 0 && i + 2 < ncols) {
@@ -859,8 +861,11 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort32(const __grid_cons
   const uint32_t s = blockIdx.x;
   if (s >= *p.count) return;
   const uint32_t start = p.segs.start[s], len = p.segs.len[s];
-  const int r = leaf32_body<KMODE>(smem_raw, p.mv.esize, p.mv.n, p.mv.src, p.mv.dst, p.key, start, start, len,
-                                   p.segs.shift[s], p.segs.base[s], p.in_place != 0);
+  const int r = len <= 4 * PT_THREADS
+      ? leaf32_body<KMODE, 4>(smem_raw, p.mv.esize, p.mv.n, p.mv.src, p.mv.dst, p.key, start, start, len,
+                              p.segs.shift[s], p.segs.base[s], p.in_place != 0)
+      : leaf32_body<KMODE, PT_ITEMS>(smem_raw, p.mv.esize, p.mv.n, p.mv.src, p.mv.dst, p.key, start, start, len,
+                                     p.segs.shift[s], p.segs.base[s], p.in_place != 0);
   if (threadIdx.x == 0) {
     p.wide[s] = r ? 1 : 0;
     if (r) atomicAdd(p.n_wide, 1u);
@@ -1275,6 +1280,11 @@ __device__ __forceinline__ uint32_t pipe_signal(uint32_t* p) {
   }
   return old;
 }
+__device__ __forceinline__ unsigned long long pipe_clock() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 // largest s in [lo, hi) with pre[s] <= x
 __device__ __forceinline__ uint32_t pipe_find(const uint32_t* pre, uint32_t lo, uint32_t hi, uint32_t x) {
   while (hi - lo > 1) {
@@ -1350,7 +1360,8 @@ __global__ void __launch_bounds__(256) k_pipe_describe(const __grid_constant__ P
 template <int KMODE>
 __global__ void __launch_bounds__(PT_THREADS, 2) k_sort_pipeline(const __grid_constant__ PipeParams p,
                                                                  const PipeItem* __restrict__ items,
-                                                                 uint32_t bar_offset) {
+                                                                 uint32_t bar_offset, uint32_t prefetch,
+                                                                 unsigned long long* trace) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(16) PipeItem s_item[2];
   __shared__ uint32_t s_flag;
@@ -1385,7 +1396,9 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_sort_pipeline(const __grid_co
   for (int cur = 0;; cur ^= 1) {
     const PipeItem it = s_item[cur];
     if (it.kind == 0xFFFFFFFFu) break;
-    if (threadIdx.x == 32) nt = atomicAdd(p.ticket, 1u);
+    if (prefetch && threadIdx.x == 32) nt = atomicAdd(p.ticket, 1u);
+    unsigned long long tr0 = 0, tr1 = 0;
+    if (trace && threadIdx.x == 0) tr0 = tr1 = pipe_clock();
     const uint32_t s = it.seg, g = it.group, bias = it.bias;
     if (it.kind == PK_HIST || it.kind == PK_SCATTER) {
       const uint32_t slen = p.seg_len[s];
@@ -1396,7 +1409,7 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_sort_pipeline(const __grid_co
         uint32_t* hist = (uint32_t*)smem_raw;
         uint32_t* scratch = hist + MSD_RADIX;
         msd_hist_tile(p.part.mv, p.part.key, it.a, it.b, 0, shift, bits, hist, cursor);
-        if (threadIdx.x == 32) load_desc(cur ^ 1);
+        if (prefetch && threadIdx.x == 32) load_desc(cur ^ 1);
         const uint32_t old = pipe_signal(&p.hist_done[s]);
         if (threadIdx.x == 0) s_flag = old + 1 == it.need;
         __syncthreads();
@@ -1417,14 +1430,16 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_sort_pipeline(const __grid_co
       } else {
         // the slot must have been read by every leaf of the group that used it last; the cursors must be ready
         pipe_wait2(it.need ? &p.leaf_done[g - PIPE_SLOTS] : nullptr, it.need, &p.plan_done[s], 1u);
-        if (threadIdx.x == 32) load_desc(cur ^ 1);
+        if (trace && threadIdx.x == 0) tr1 = pipe_clock();
+        if (prefetch && threadIdx.x == 32) load_desc(cur ^ 1);
         partition_tile<1>(p.part, smem_raw, it.a, it.b, bits, shift, 0, cursor, bias, bar, &phase);
         pipe_signal(&p.scat_done[s]);
       }
     } else {
       // ---- PK_LEAF: one child of one segment
       pipe_wait2(nullptr, 0, &p.scat_done[s], it.need);
-      if (threadIdx.x == 32) load_desc(cur ^ 1);
+      if (trace && threadIdx.x == 0) tr1 = pipe_clock();
+      if (prefetch && threadIdx.x == 32) load_desc(cur ^ 1);
       const uint32_t cs = __ldcg(&p.child_start[(size_t)s * MSD_RADIX + it.a]);
       const uint32_t cl = __ldcg(&p.child_len[(size_t)s * MSD_RADIX + it.a]);
       const uint32_t sh = p.key_bits - (uint32_t)msd_bits(p.seg_len[s], p.key_bits);
@@ -1432,8 +1447,11 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_sort_pipeline(const __grid_co
       } else if (cl <= SMALL_MAX) {
         if (threadIdx.x < 32) leaf_small_warp(p.part.mv.esize, ncols, ring, p.fin, p.part.key, cs + bias, cs, cl);
       } else if (cl <= LEAF_MAX) {
-        const int r = leaf32_body<KMODE>(smem_raw, p.part.mv.esize, ncols, ring, p.fin, p.part.key, cs + bias, cs, cl,
-                                         sh, 0, false, bar, &phase);
+        const int r = cl <= 4 * PT_THREADS
+            ? leaf32_body<KMODE, 4>(smem_raw, p.part.mv.esize, ncols, ring, p.fin, p.part.key, cs + bias, cs, cl, sh, 0,
+                                    false, bar, &phase)
+            : leaf32_body<KMODE, PT_ITEMS>(smem_raw, p.part.mv.esize, ncols, ring, p.fin, p.part.key, cs + bias, cs, cl,
+                                           sh, 0, false, bar, &phase);
         if (r) {
           __syncthreads();
           leaf64_body(smem_raw, p.part.mv.esize, ncols, ring, p.fin, p.part.key, cs + bias, cs, cl, false);
@@ -1461,7 +1479,23 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_sort_pipeline(const __grid_co
       }
       pipe_signal(&p.leaf_done[g]);
     }
-    if (threadIdx.x == 32) park();
+    if (trace && threadIdx.x == 0) {
+      // one record per item: [kind | segment << 8 | CTA << 32 | SM << 44], start, end of the wait, end (ns)
+      const unsigned long long i = atomicAdd(&trace[0], 1ull);
+      uint32_t smid;
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+      unsigned long long* r = trace + 4 + 4 * i;
+      r[0] = (unsigned long long)it.kind | ((unsigned long long)(s & 0xFFFFFFu) << 8) |
+             ((unsigned long long)(blockIdx.x & 0xFFFu) << 32) | ((unsigned long long)smid << 44);
+      r[1] = tr0; r[2] = tr1; r[3] = pipe_clock();
+    }
+    if (threadIdx.x == 32) {
+      if (!prefetch) {
+        nt = atomicAdd(p.ticket, 1u);
+        load_desc(cur ^ 1);
+      }
+      park();
+    }
     __syncthreads();   // the item's shared memory is free, s_item[cur ^ 1] is in place
   }
 }
@@ -1598,9 +1632,26 @@ static void run_sort_pipeline(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key
     const size_t bar_off = (pipeline_smem_bytes() + 15) & ~(size_t)15;
     const size_t sm = bar_off + 32;
     const PipeItem* di = d_items.as<PipeItem>();
-    if (key.mode == KS_U64) LAUNCH(c, k_sort_pipeline<KS_U64>, grid, PT_THREADS, sm, *pp, di, (uint32_t)bar_off);
-    else if (key.mode == KS_I64) LAUNCH(c, k_sort_pipeline<KS_I64>, grid, PT_THREADS, sm, *pp, di, (uint32_t)bar_off);
-    else LAUNCH(c, k_sort_pipeline<KS_I32>, grid, PT_THREADS, sm, *pp, di, (uint32_t)bar_off);
+    const char* pf = getenv("HSGPU_PIPE_PREFETCH");
+    const uint32_t prefetch = (pf && *pf == '0') ? 0u : 1u;
+    // HSGPU_PIPE_TRACE=<file>: per-item timestamps of this launch (diagnostics; costs a device sync)
+    const char* trace_path = getenv("HSGPU_PIPE_TRACE");
+    DBuf d_trace;
+    unsigned long long* tr = nullptr;
+    if (trace_path && *trace_path) {
+      d_trace.alloc(c, ((size_t)ticket * 4 + 4) * 8);
+      d_trace.zero();
+      tr = d_trace.as<unsigned long long>();
+    }
+    if (key.mode == KS_U64) LAUNCH(c, k_sort_pipeline<KS_U64>, grid, PT_THREADS, sm, *pp, di, (uint32_t)bar_off, prefetch, tr);
+    else if (key.mode == KS_I64) LAUNCH(c, k_sort_pipeline<KS_I64>, grid, PT_THREADS, sm, *pp, di, (uint32_t)bar_off, prefetch, tr);
+    else LAUNCH(c, k_sort_pipeline<KS_I32>, grid, PT_THREADS, sm, *pp, di, (uint32_t)bar_off, prefetch, tr);
+    if (tr) {
+      std::vector<unsigned long long> h((size_t)ticket * 4 + 4);
+      CK(cudaMemcpyAsync(h.data(), tr, h.size() * 8, cudaMemcpyDeviceToHost, c->stream));
+      hs_sync(c);
+      if (FILE* f = fopen(trace_path, "wb")) { fwrite(h.data(), 8, h.size(), f); fclose(f); }
+    }
   }
   delete pp;
 }
