@@ -218,8 +218,9 @@ def main():
     ap.add_argument("--rows", type=int, default=100_000_000, help="rows per GPU per step")
     ap.add_argument("--ref-rows", type=int, default=0,
                     help="rows per step of the CPU arms (0 = the same rows per step as one GPU of the native arm)")
-    ap.add_argument("--e2e-steps", type=int, default=3, help="end-to-end steps per host thread")
-    ap.add_argument("--e2e-threads", type=int, default=3, help="host threads (contexts) of the end-to-end leg at N=1")
+    ap.add_argument("--e2e-steps", type=int, default=8, help="end-to-end steps per host thread")
+    ap.add_argument("--e2e-threads", type=int, default=1, help="host threads (contexts) of the end-to-end leg at N=1")
+    ap.add_argument("--e2e-sync", action="store_true", help="end-to-end leg without deferred results")
     ap.add_argument("--buckets", type=int, default=0,
                     help="bucket count of the index; default 200 per GPU (the bucket size, i.e. the index file size, "
                          "stays that of the 1-GPU configuration as rows are added with GPUs)")
@@ -368,24 +369,35 @@ def main():
             {"type": abi.HS_FLOAT64, "length": n, "data": hd.data_ptr()}])
         ctx.set_output_location(abi.HS_MEM_HOST)
         ctx.build_index_table(hcs, 1, NUM_BUCKETS, dist=use_dist).free()   # warm the pinned pool
-        n_threads = 1
-        if world == 1 and args.e2e_threads > 1:
-            # The ABI's threading model — one context per thread, contexts run concurrently — lets the H2D of one
-            # build overlap the D2H of another (PCIe is full duplex). Every step still copies its own inputs in
-            # and its own result out inside the timed region.
-            n_threads = args.e2e_threads
+        # One caller thread. With deferred results (hs_ctx_set_deferred_results) hs_build_index returns once the
+        # result's download is queued; the thread starts the next build — its upload runs beside that download,
+        # PCIe carries both directions at once — and then collects the previous table (hs_table_wait) and reads
+        # it. Every step still copies its own inputs in and its own result out inside the timed region.
+        n_threads = max(1, args.e2e_threads) if world == 1 else 1
+        deferred = not args.e2e_sync
         extra = [native.Context(local) for _ in range(n_threads - 1)]
-        for cx in extra:
+        for cx in [ctx] + extra:
             cx.set_output_location(abi.HS_MEM_HOST)
-            cx.build_index_table(hcs, 1, NUM_BUCKETS).free()
+            cx.set_deferred_results(deferred)
+            for _ in range(2):      # two results are alive at a time: warm two sets of pinned buffers
+                a = cx.build_index_table(hcs, 1, NUM_BUCKETS, dist=use_dist if cx is ctx else False)
+                b = cx.build_index_table(hcs, 1, NUM_BUCKETS, dist=use_dist if cx is ctx else False)
+                a.free()
+                b.free()
         results = {}
 
         def worker(cx, k):
-            fk = 0
+            fk, prev = 0, None
             for _ in range(args.e2e_steps):
                 t = cx.build_index_table(hcs, 1, NUM_BUCKETS, dist=use_dist)
-                fk = C.c_int64.from_address(t.column(0).data).value if t.nrows else 0  # read the result
-                t.free()
+                if prev is not None:
+                    prev.wait()
+                    fk = C.c_int64.from_address(prev.column(0).data).value if prev.nrows else 0  # read the result
+                    prev.free()
+                prev = t
+            prev.wait()
+            fk = C.c_int64.from_address(prev.column(0).data).value if prev.nrows else 0
+            prev.free()
             results[k] = fk
         barrier()
         t0 = time.perf_counter()
@@ -401,15 +413,16 @@ def main():
         first_key = results[0]
         for cx in extra:
             cx.close()
+        ctx.set_deferred_results(False)
         if dist is not None:
             tt = torch.tensor([dt], dtype=torch.float64, device=dev)
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             dt = float(tt.item())
         e2e = {"value": n * world / dt, "unit": UNIT, "h2d_bytes_per_step": n * ROW_BYTES,
                "d2h_bytes_per_step": n * ROW_BYTES, "ms_per_step": dt * 1e3, "steps": total_steps,
-               "host_threads": n_threads,
-               "note": "pinned host buffers in and out through hs_build_index; with several host threads (one context "
-                       "each) the uploads of some builds overlap the downloads of others",
+               "host_threads": n_threads, "deferred_results": deferred,
+               "note": "pinned host buffers in and out through hs_build_index on one caller thread; the download of "
+                       "build k (hs_ctx_set_deferred_results / hs_table_wait) runs beside the upload of build k+1",
                "first_key": int(first_key)}
         del hk, hp, hd
         ctx.set_output_location(abi.HS_MEM_DEVICE)

@@ -7,7 +7,21 @@ struct TableImpl {
   std::vector<void*> pinned;  // pinned host buffers owned by the table
   std::vector<hs_column> cols;
   std::vector<int64_t> boff;
+  // deferred results: the device -> host copies run on the context's copy stream after the call has returned;
+  // `ready` marks their end, `staged` are the device buffers they read (released once the copies are done)
+  cudaEvent_t ready = nullptr;
+  std::vector<void*> staged;
 };
+
+static void table_settle(hs_ctx* c, TableImpl* ti) {
+  if (!ti || !ti->ready) return;
+  cudaError_t e = cudaEventSynchronize(ti->ready);
+  cudaEventDestroy(ti->ready);
+  ti->ready = nullptr;
+  for (void* p : ti->staged) hs_dev_free(c, p);
+  ti->staged.clear();
+  if (e != cudaSuccess) HS_THROW(HS_ECUDA, "copy of a deferred result failed: %s", cudaGetErrorString(e));
+}
 
 void hs_sync(hs_ctx* c) { CK(cudaStreamSynchronize(c->stream)); }
 
@@ -237,6 +251,19 @@ hs_table* hs_finish_table(hs_ctx* c, std::vector<OutCol>& cols, int64_t nrows, i
   try {
     ti->cols.resize(cols.size());
     bool host = c->out_loc == HS_MEM_HOST;
+    const bool deferred = host && c->deferred;
+    cudaStream_t cs = c->stream;
+    if (deferred) {
+      // the copies wait for everything queued on the compute stream so far and then run beside whatever the
+      // caller starts next (the upload of the next build's input: PCIe carries both directions at once)
+      if (!c->copy_stream) CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+      cudaEvent_t done;
+      CK(cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
+      CK(cudaEventRecord(done, c->stream));
+      CK(cudaStreamWaitEvent(c->copy_stream, done, 0));
+      CK(cudaEventDestroy(done));
+      cs = c->copy_stream;
+    }
     auto place = [&](DBuf& b, size_t bytes) -> void* {
       if (!b.p) return nullptr;
       if (!host) {
@@ -246,7 +273,8 @@ hs_table* hs_finish_table(hs_ctx* c, std::vector<OutCol>& cols, int64_t nrows, i
       }
       void* h = hs_pinned_alloc(c, bytes);
       ti->pinned.push_back(h);
-      if (bytes) CK(cudaMemcpyAsync(h, b.p, bytes, cudaMemcpyDeviceToHost, c->stream));
+      if (bytes) CK(cudaMemcpyAsync(h, b.p, bytes, cudaMemcpyDeviceToHost, cs));
+      if (deferred) ti->staged.push_back(b.detach());
       return h;
     };
     for (size_t i = 0; i < cols.size(); i++) {
@@ -261,7 +289,12 @@ hs_table* hs_finish_table(hs_ctx* c, std::vector<OutCol>& cols, int64_t nrows, i
       hc.data = place(o.data, (size_t)o.data_bytes);
       if (!hc.validity) hc.null_count = 0;
     }
-    hs_sync(c);
+    if (deferred) {
+      CK(cudaEventCreateWithFlags(&ti->ready, cudaEventDisableTiming));
+      CK(cudaEventRecord(ti->ready, cs));
+    } else {
+      hs_sync(c);
+    }
     cols.clear();  // frees the device copies in host mode
     t->ncols = (int32_t)ti->cols.size();
     t->location = host ? HS_MEM_HOST : HS_MEM_DEVICE;
@@ -273,6 +306,9 @@ hs_table* hs_finish_table(hs_ctx* c, std::vector<OutCol>& cols, int64_t nrows, i
       t->bucket_offsets = ti->boff.data();
     }
   } catch (...) {
+    if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
+    if (ti->ready) cudaEventDestroy(ti->ready);
+    for (void* p : ti->staged) hs_dev_free(c, p);
     for (void* p : ti->dev) hs_dev_free(c, p);
     for (void* p : ti->pinned) hs_pinned_free(c, p);
     delete ti;
@@ -328,6 +364,7 @@ int32_t hs_ctx_destroy(hs_ctx* c) {
     cudaFreeHost(c->rd_pin);
     for (int i = 0; i < HS_READ_SLOTS; i++) cudaEventDestroy(c->rd_ev[i]);
   }
+  if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
   cudaStreamDestroy(c->stream);
   delete c;
   return HS_OK;
@@ -384,12 +421,26 @@ int32_t hs_table_free(hs_ctx* c, hs_table* t) {
   cudaSetDevice(c->device);
   TableImpl* ti = (TableImpl*)t->impl;
   if (ti) {
+    try { table_settle(c, ti); } catch (const HsError&) {}
     for (void* p : ti->dev) hs_dev_free(c, p);
     for (void* p : ti->pinned) hs_pinned_free(c, p);
     delete ti;
   }
   delete t;
   return HS_OK;
+}
+
+int32_t hs_ctx_set_deferred_results(hs_ctx* c, int32_t on) {
+  if (!c) return HS_EINVAL;
+  c->deferred = on != 0;
+  return HS_OK;
+}
+
+int32_t hs_table_wait(hs_ctx* c, hs_table* t) {
+  API_BEGIN(c)
+  if (!t) HS_THROW(HS_EINVAL, "null table");
+  table_settle(c, (TableImpl*)t->impl);
+  API_END(c)
 }
 
 }  // extern "C"

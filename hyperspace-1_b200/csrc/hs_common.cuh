@@ -47,6 +47,8 @@ struct hs_ctx {
   cudaStream_t stream = nullptr;
   std::string err;
   int out_loc = HS_MEM_HOST;
+  bool deferred = false;             // host results are copied on copy_stream after the call returns
+  cudaStream_t copy_stream = nullptr;
   bool timing = false;
   std::vector<StageRec> stages;      // of the last call
   std::vector<cudaEvent_t> ev_free;  // recycled events

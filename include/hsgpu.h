@@ -161,6 +161,15 @@ int32_t hs_ctx_destroy(hs_ctx* ctx);
 const char* hs_last_error(hs_ctx* ctx);
 /* HS_MEM_HOST (default, pinned) or HS_MEM_DEVICE for the buffers of later results. */
 int32_t hs_ctx_set_output_location(hs_ctx* ctx, int32_t location);
+/* Deferred host results (off by default). With it on, a call that returns an hs_table in host memory comes
+ * back as soon as the table's device -> host copies are queued on a second stream of the context; the table's
+ * buffers may be read only after hs_table_wait() (hs_table_free() waits by itself). One caller thread can then
+ * start the next build — whose input upload runs beside the previous result's download — and collect the
+ * previous table afterwards. This is the one exception to "calls are synchronous"; it mirrors how the
+ * reference's driver thread hands a finished stage to Spark's writer while the next stage is already running
+ * (CreateActionBase.write, HS/actions/CreateActionBase.scala:122-140, is one call per index but many per job). */
+int32_t hs_ctx_set_deferred_results(hs_ctx* ctx, int32_t on);
+int32_t hs_table_wait(hs_ctx* ctx, hs_table* table);
 /* The cudaStream_t the context launches on (for external event timing). */
 int32_t hs_ctx_get_stream(hs_ctx* ctx, void** stream);
 int32_t hs_ctx_enable_timing(hs_ctx* ctx, int32_t on);
