@@ -339,25 +339,37 @@ __global__ void __launch_bounds__(JTHREADS, 2) k_join_tiles(const __grid_constan
   }
   uint32_t ex = inc - mysum + s_red[threadIdx.x >> 5];
   if (MODE == 2) {
-    if (threadIdx.x == 0) {
+    // chained scan over the tiles (decoupled look-back): warp 0 publishes the tile's total, then looks at 32
+    // predecessors at a time until it meets one that has published its inclusive prefix
+    if (threadIdx.x < 32) {
       const unsigned long long FA = 1ull << 62, FP = 2ull << 62, VM = (1ull << 62) - 1;
       volatile unsigned long long* st = p.tile_state;
       unsigned long long excl = 0;
       if (t > 0) {
-        st[t] = FA | total;
+        if (lane_id() == 0) st[t] = FA | total;
         __threadfence();
-        for (int64_t q = (int64_t)t - 1; q >= 0; q--) {
-          unsigned long long v;
-          do { v = st[q]; } while ((v >> 62) == 0);   // the predecessor has started (ticket order): it will publish
-          excl += v & VM;
-          if ((v >> 62) == 2) break;
+        for (int64_t q = (int64_t)t - 1; q >= 0; q -= 32) {
+          const int64_t idx = q - lane_id();
+          unsigned long long v = FP;               // before the first tile: an inclusive prefix of 0
+          if (idx >= 0) {
+            do { v = st[idx]; } while ((v >> 62) == 0);   // the predecessor has started (ticket order): it will publish
+          }
+          const uint32_t has_prefix = __ballot_sync(0xffffffffu, (v >> 62) == 2);
+          const uint32_t upto = has_prefix ? (uint32_t)__ffs(has_prefix) - 1u : 31u;   // nearest lane with a prefix
+          unsigned long long part = lane_id() <= upto ? (v & VM) : 0ull;
+#pragma unroll
+          for (int d = 16; d; d >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d);
+          excl += part;
+          if (has_prefix) break;
         }
       }
-      __threadfence();
-      st[t] = FP | (excl + total);
-      s_obase = (uint32_t)excl;
-      p.tile_cnt[t] = (uint32_t)excl;
-      if (excl + total > p.capacity) *p.overflow = 1;
+      if (lane_id() == 0) {
+        __threadfence();
+        st[t] = FP | (excl + total);
+        s_obase = (uint32_t)excl;
+        p.tile_cnt[t] = (uint32_t)excl;
+        if (excl + total > p.capacity) *p.overflow = 1;
+      }
     }
     __syncthreads();
     if ((unsigned long long)s_obase + total > p.capacity) return;   // does not fit: count only

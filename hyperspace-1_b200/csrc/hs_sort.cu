@@ -645,18 +645,28 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
                                            uint32_t start, uint32_t dstart, uint32_t len, uint32_t seg_bits_,
                                            uint64_t seg_base_, bool in_place, uint64_t* ext_bar = nullptr,
                                            uint32_t* ext_phase = nullptr) {
+  // landing areas of the column slices: two of a full tile, or — for a leaf of at most half a tile — four of
+  // half a tile, so that up to four columns are requested at once, before the sort starts
+  constexpr int NS = ITEMS * PT_THREADS * 2 <= PT_TILE ? 4 : 2;
+  constexpr uint32_t SLOT_BYTES = 2 * STAGE_BYTES / NS;
+  auto stage_of = [&](int b) { return smem_raw + (size_t)b * SLOT_BYTES; };
   unsigned char* stage0 = smem_raw;
-  unsigned char* stage1 = smem_raw + STAGE_BYTES;
   uint32_t* sdata = (uint32_t*)(smem_raw + 2 * STAGE_BYTES);  // LEAF_MAX packed words
   uint32_t* cnt = sdata + LEAF_MAX;                 // 4096 words: atomic counters or PT_WARPS x 256 warp counters
   uint32_t* tot = cnt + 4096;                       // 256
   uint32_t* loc = tot + 256;                        // 256
   uint32_t* scratch = loc + 256;                    // PT_SCRATCH
   uint64_t* red = (uint64_t*)(scratch + PT_SCRATCH);  // 2 * PT_WARPS + 2
-  uint64_t* bar = ext_bar ? ext_bar : red + 2 * PT_WARPS + 2;   // 2 mbarriers (see partition_tile for ext_*)
+  uint64_t* bar = ext_bar ? ext_bar : red + 2 * PT_WARPS + 2;   // 4 mbarriers (see partition_tile for ext_*)
   const uint32_t ph_in = ext_phase ? *ext_phase : 0u;
-  // both barriers complete once for the first two slices whatever happens next
-  if (ext_phase) *ext_phase = ph_in ^ 1u ^ (ncols_ > 1 ? 2u : 0u);
+  // barrier b completes once for each of the columns b, b + NS, ...; the first min(ncols, NS) slices are
+  // requested whatever happens next
+  auto phase_after = [&](int cols_done) {
+    uint32_t ph = ph_in;
+    for (int b = 0; b < NS; b++) ph ^= (uint32_t)(((cols_done > b ? (cols_done - b + NS - 1) / NS : 0) & 1) << b);
+    return ph;
+  };
+  if (ext_phase) *ext_phase = phase_after(ncols_ < NS ? ncols_ : NS);
 
   const int w = threadIdx.x >> 5;
   const int items = (int)((len + PT_THREADS - 1) / PT_THREADS);
@@ -666,20 +676,23 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
 
   if (!ext_bar) {
     if (threadIdx.x == 0) {
-      mbar_init(&bar[0], 1);
-      mbar_init(&bar[1], 1);
+      for (int b = 0; b < 4; b++) mbar_init(&bar[b], 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
     __syncthreads();
   }
+  const int n_first = ncols < NS ? ncols : NS;   // slices requested up front
   if (threadIdx.x == 0) {
-    issue_slice(src[first], esize[first], start, len, stage0, &bar[0]);
-    if (ncols > 1) {
-      int c1 = col_at(1);
-      issue_slice(src[c1], esize[c1], start, len, stage1, &bar[1]);
+    for (int i = 0; i < n_first; i++) {
+      const int c = col_at(i);
+      issue_slice(src[c], esize[c], start, len, stage_of(i), &bar[i]);
     }
   }
+  // a CTA must not retire (or move on) with a bulk copy in flight
+  auto drain_first = [&]() {
+    for (int b = 1; b < n_first; b++) mbar_wait(&bar[b], (ph_in >> b) & 1u);
+  };
   // ---- keys from the staged slice. The segment descriptor says how many low bits of (key - base) can still
   // differ inside the segment; when that fits the packed word no min/max pass is needed at all.
   const uint32_t seg_bits = seg_bits_;
@@ -732,7 +745,7 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
   const int drop = nbits > L32_MAX_KEY_BITS ? nbits - L32_MAX_KEY_BITS : 0;
   if (nbits == 0 && in_place) {
     // all keys equal and the rows are in place; a CTA must not retire with a bulk copy in flight
-    if (ncols > 1) mbar_wait(&bar[1], (ph_in >> 1) & 1u);
+    drain_first();
     return 0;
   }
   if (drop) nbits = L32_MAX_KEY_BITS;
@@ -829,14 +842,14 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
     }
   }
   if (too_long) {
-    if (ncols > 1) mbar_wait(&bar[1], (ph_in >> 1) & 1u);
+    drain_first();
     return 1;
   }
   // ---- every column: staged slice -> permutation -> coalesced store
   for (int i = 0; i < ncols; i++) {
-    const int c = col_at(i), b = i & 1, es = esize[c];
-    unsigned char* stage = b ? stage1 : stage0;
-    mbar_wait(&bar[b], ((uint32_t)(i >> 1) ^ (ph_in >> b)) & 1u);
+    const int c = col_at(i), b = i % NS, es = esize[c];
+    unsigned char* stage = stage_of(b);
+    mbar_wait(&bar[b], ((uint32_t)(i / NS) ^ (ph_in >> b)) & 1u);
     const uint32_t lead = slice_lead(src[c], es, start);
     switch (es) {
       case 8: leaf_permute_column<uint64_t, ITEMS>(stage, lead, (uint64_t*)dst[c], dstart, len, sdata); break;
@@ -844,14 +857,16 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
       case 2: leaf_permute_column<uint16_t, ITEMS>(stage, lead, (uint16_t*)dst[c], dstart, len, sdata); break;
       default: leaf_permute_column<uint8_t, ITEMS>(stage, lead, (uint8_t*)dst[c], dstart, len, sdata); break;
     }
-    __syncthreads();  // stage[b] is free again
-    if (threadIdx.x == 0 && i + 2 < ncols) {
-      int cn = col_at(i + 2);
-      issue_slice(src[cn], esize[cn], start, len, stage, &bar[b]);
+    if (i + NS < ncols) {
+      __syncthreads();  // the slot is free again
+      if (threadIdx.x == 0) {
+        const int cn = col_at(i + NS);
+        issue_slice(src[cn], esize[cn], start, len, stage, &bar[b]);
+      }
     }
   }
-  if (ext_phase)
-    *ext_phase = ph_in ^ (uint32_t)(((ncols + 1) >> 1) & 1) ^ (uint32_t)(((ncols >> 1) & 1) << 1);
+  __syncthreads();
+  if (ext_phase) *ext_phase = phase_after(ncols);
   return 0;
 }
 
@@ -873,7 +888,7 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort32(const __grid_cons
 }
 static size_t leaf32_smem_bytes() {
   return (size_t)2 * STAGE_BYTES + (size_t)LEAF_MAX * 4 + 4096 * 4 + 512 * 4 + PT_SCRATCH * 4 +
-         (2 * PT_WARPS + 2) * 8 + 16;
+         (2 * PT_WARPS + 2) * 8 + 32;
 }
 
 static size_t leaf_smem_bytes() {
@@ -1365,7 +1380,7 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_sort_pipeline(const __grid_co
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ __align__(16) PipeItem s_item[2];
   __shared__ uint32_t s_flag;
-  uint64_t* bar = (uint64_t*)(smem_raw + bar_offset);   // 3 mbarriers behind every body's shared-memory layout
+  uint64_t* bar = (uint64_t*)(smem_raw + bar_offset);   // 4 mbarriers behind every body's shared-memory layout
   uint32_t phase = 0;                                    // parity each of them completes next
   const int ncols = p.part.mv.n;
   const void* const* ring = (const void* const*)p.part.mv.dst;
@@ -1381,9 +1396,7 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_sort_pipeline(const __grid_co
   };
   auto park = [&]() { asm volatile("cp.async.wait_all;" ::: "memory"); };
   if (threadIdx.x == 0) {
-    mbar_init(&bar[0], 1);
-    mbar_init(&bar[1], 1);
-    mbar_init(&bar[2], 1);
+    for (int b = 0; b < 4; b++) mbar_init(&bar[b], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -1509,8 +1522,10 @@ static int hs_num_sms() {
   return v;
 }
 static bool pipeline_enabled() {
+  // off unless asked for: measured on B200 (profiles/README.md) the single launch does not beat the separate
+  // kernels — co-resident scatter tiles and leaf sorts take as long as they do alone
   const char* e = getenv("HSGPU_SORT_PIPELINE");
-  return !(e && *e == '0');
+  return e && *e == '1';
 }
 static size_t pipeline_smem_bytes() {
   size_t a = leaf32_smem_bytes(), b = leaf_smem_bytes(), t = tile_smem_bytes(MSD_RADIX);
@@ -1616,7 +1631,7 @@ static void run_sort_pipeline(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key
     int dev = 0;
     CK(cudaGetDevice(&dev));
     if (!attr_dev[dev & 63]) {
-      const int sm = (int)((pipeline_smem_bytes() + 15) & ~(size_t)15) + 32;
+      const int sm = (int)((pipeline_smem_bytes() + 15) & ~(size_t)15) + 48;
       CK(cudaFuncSetAttribute(k_sort_pipeline<KS_U64>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
       CK(cudaFuncSetAttribute(k_sort_pipeline<KS_I64>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
       CK(cudaFuncSetAttribute(k_sort_pipeline<KS_I32>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm));
@@ -1630,7 +1645,7 @@ static void run_sort_pipeline(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key
     DBuf d_items(c, ((size_t)ticket + grid) * sizeof(PipeItem));
     LAUNCH(c, k_pipe_describe, (ticket + grid + 255) / 256, 256, 0, *pp, d_items.as<PipeItem>(), (uint32_t)grid);
     const size_t bar_off = (pipeline_smem_bytes() + 15) & ~(size_t)15;
-    const size_t sm = bar_off + 32;
+    const size_t sm = bar_off + 48;
     const PipeItem* di = d_items.as<PipeItem>();
     const char* pf = getenv("HSGPU_PIPE_PREFETCH");
     const uint32_t prefetch = (pf && *pf == '0') ? 0u : 1u;
