@@ -227,6 +227,9 @@ def main():
     ap.add_argument("--no-join", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-check", action="store_true", help="skip the untimed check of one more build")
+    ap.add_argument("--no-extras", action="store_true", help="skip the cfg4 (N=1) / cfg5 (N=8) side measurements")
+    ap.add_argument("--cfg4-rows", type=int, default=80_000_000)
+    ap.add_argument("--cfg5-rows", type=int, default=500_000_000, help="rows per GPU of the cfg5 side measurement")
     args = ap.parse_args()
     global NUM_BUCKETS
     NUM_BUCKETS = args.buckets if args.buckets > 0 else BUCKETS_PER_GPU * max(1, args.gpus)
@@ -547,6 +550,27 @@ def main():
                "sample": f"first {m} rows of the same workload, one pass (hash, bucket, per-bucket sort, take)",
                "seconds": dt}
 
+    # ---- the other BASELINE.json configs, measured beside the headline (tools/bench_configs.py): cfg4 (500 M-row
+    # shape, string keys, 1000 buckets) at 80 M rows on one GPU; cfg5 (composite key, 8192 buckets, 10 % refresh,
+    # merge and join over two runs per bucket) at 8 GPUs x 500 M rows. Each carries its own checks.
+    extra = {}
+    if not args.no_extras:
+        del key, price, disc
+        torch.cuda.empty_cache()
+        from tools import bench_configs as bc
+        try:
+            if world == 1:
+                x = bc.cfg4_measure(torch, native, abi, dev, args.cfg4_rows, 3, 2, ctx=ctx)
+                x["frac_of_measured_peak"] = x["achieved_gbs"] / peak
+                extra["cfg4"] = x
+            elif world == 8:
+                x = bc.cfg5_measure(torch, dist, native, abi, ctx, rank, world, dev, args.cfg5_rows, 2, 1)
+                if x is not None:
+                    x["build_frac_of_measured_peak_per_gpu"] = x["build_achieved_gbs_per_gpu"] / peak
+                    extra["cfg5"] = x
+        except Exception as ex:   # an extra must not cost the headline line
+            extra["error"] = str(ex)[:300]
+
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
@@ -554,7 +578,7 @@ def main():
                 "config": workload_config(n, world, NUM_BUCKETS),
                 "roofline": roofline, "build_roofline": build_roofline, "stages": per_stage,
                 "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "join": join,
-                "filter": filt, "dist_check" if world > 1 else "index_check": index_check}
+                "filter": filt, "dist_check" if world > 1 else "index_check": index_check, "extra": extra}
         if use_dist and xchg:
             b = sum(x[0] for x in xchg) / len(xchg)
             ms = sum(x[1] for x in xchg) / len(xchg)

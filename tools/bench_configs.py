@@ -44,30 +44,31 @@ def gen_cfg4_device(torch, m, seed, dev):
     return off, data, rid, total
 
 
-def run_cfg4(args):
-    import torch
-    from hyperspace_1_b200 import abi, native
-    dev = torch.device("cuda", 0)
-    torch.cuda.set_device(dev)
-    m, nb = args.rows or 80_000_000, 1000
+def cfg4_measure(torch, native, abi, dev, m, steps, warmup, large_offsets=False, check=True, ctx=None):
+    """cfg4 on one GPU: build of m string-keyed rows (device-resident in and out). Returns the result line.
+    check: bucket membership of a sample of output rows recomputed by the oracle, and byte-wise order of
+    sampled neighbours inside buckets, both on the host."""
+    nb = 1000
     off64, data, rid, total = gen_cfg4_device(torch, m, 20240603, dev)
-    wide = total >= (1 << 31) or args.large_offsets
+    wide = total >= (1 << 31) or large_offsets
     off = off64 if wide else off64.to(torch.int32)
     torch.cuda.synchronize()
-    ctx = native.Context(0)
+    own_ctx = ctx is None
+    if own_ctx:
+        ctx = native.Context(dev.index or 0)
     ctx.set_output_location(abi.HS_MEM_DEVICE)
     cs = abi.DeviceColumnSet([
         {"type": getattr(abi, "HS_LARGE_UTF8", -1) if wide else abi.HS_UTF8, "length": m, "offsets": off.data_ptr(),
          "data": data.data_ptr()},
         {"type": abi.HS_INT64, "length": m, "data": rid.data_ptr()}])
     stream = torch.cuda.ExternalStream(ctx.stream(), device=dev)
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         ctx.build_index_table(cs, 1, nb).free()
     ctx.enable_timing(True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     stage_ms = {}
     e0.record(stream)
-    for _ in range(args.steps):
+    for _ in range(steps):
         t = ctx.build_index_table(cs, 1, nb)
         for name, ms, launches in ctx.last_timings():
             a = stage_ms.setdefault(name, [0.0, 0])
@@ -76,17 +77,82 @@ def run_cfg4(args):
         t.free()
     e1.record(stream)
     torch.cuda.synchronize()
-    ms_step = e0.elapsed_time(e1) / args.steps
+    ctx.enable_timing(False)
+    ms_step = e0.elapsed_time(e1) / steps
     row_bytes = total / m + (8 if wide else 4) + 8
     key_bytes = total / m + (8 if wide else 4)
     algo = key_bytes + 4 * row_bytes
     line = {"config": "cfg4", "rows": m, "key_bytes_total": total, "num_buckets": nb, "offsets": "int64" if wide else "int32",
             "ms_per_step": ms_step, "rows_per_s": m / (ms_step * 1e-3), "algorithmic_bytes_per_row": algo,
             "achieved_gbs": algo * m / (ms_step * 1e-3) / 1e9,
-            "stages_ms": {k: round(v[0] / args.steps, 3) for k, v in stage_ms.items()},
-            "launches_per_step": sum(v[1] for v in stage_ms.values()) / args.steps}
+            "stages_ms": {k: round(v[0] / steps, 3) for k, v in stage_ms.items()},
+            "launches_per_step": sum(v[1] for v in stage_ms.values()) / steps}
+    if check:
+        line["check"] = cfg4_check(torch, abi, ctx, cs, nb, m, dev, off64, data)
+    if own_ctx:
+        ctx.close()
+    return line
+
+
+def cfg4_check(torch, abi, ctx, cs, nb, m, dev, in_off, in_data, sample=200_000):
+    """One more build; on a sample of output positions: the row's bucket recomputed by the oracle from the key
+    bytes found in the result, the order against the next row of the same bucket (unsigned byte-wise, shorter
+    first), and the key bytes against the input row the v column (= source row id) names."""
+    import numpy as np
+    import pyarrow as pa
+    from oracle import oracle   # the checker only
+    t = ctx.build_index_table(cs, 1, nb)
+    torch.cuda.synchronize()
+    boff = t.bucket_offsets()
+    kc, vc = t.column(0), t.column(1)
+    large = kc.type in (abi.HS_LARGE_UTF8, abi.HS_LARGE_BINARY)
+
+    def dev_view(addr, n, dt, ts):
+        class _A:
+            pass
+        a = _A()
+        a.__cuda_array_interface__ = {"shape": (n,), "typestr": ts, "data": (addr, False), "version": 2}
+        return torch.as_tensor(a, device=dev)
+    ooff = dev_view(kc.offsets, m + 1, None, "<i8" if large else "<i4").to(torch.int64)
+    nbytes = int(ooff[-1])
+    odata = dev_view(kc.data, nbytes, None, "|u1")
+    orid = dev_view(vc.data, m, None, "<i8")
+    g = torch.Generator(device=dev)
+    g.manual_seed(7)
+    pos = torch.randint(0, m - 1, (min(sample, m - 1),), generator=g, device=dev)
+
+    def strings(offs, dat, idx):
+        s0, s1 = offs[idx].cpu().numpy(), offs[idx + 1].cpu().numpy()
+        # gather the bytes of the sampled rows with one device gather
+        lens = s1 - s0
+        tot = int(lens.sum())
+        starts = torch.as_tensor(np.repeat(s0 - np.concatenate([[0], np.cumsum(lens)[:-1]]), lens), device=dev)
+        flat = dat[starts + torch.arange(tot, device=dev)].cpu().numpy().tobytes()
+        cut = np.concatenate([[0], np.cumsum(lens)])
+        return [flat[cut[i]:cut[i + 1]] for i in range(len(lens))]
+    here, nxt = strings(ooff, odata, pos), strings(ooff, odata, pos + 1)
+    bucket = np.searchsorted(boff, pos.cpu().numpy(), side="right") - 1
+    bucket_next = np.searchsorted(boff, (pos + 1).cpu().numpy(), side="right") - 1
+    got = oracle.bucket_ids([pa.array(here, pa.binary())], nb)
+    member_ok = bool(np.array_equal(got.astype(np.int64), bucket))
+    order_ok = all(a <= b for a, b, x, y in zip(here, nxt, bucket, bucket_next) if x == y)   # bytes compare unsigned
+    src = strings(in_off, in_data, orid[pos])
+    pairing_ok = src == here
+    rows_ok = bool(t.nrows == m and boff[-1] == m and int(orid.sum()) == m * (m - 1) // 2)
+    t.free()
+    return {"ok": bool(member_ok and order_ok and pairing_ok and rows_ok), "bucket_of_sample_by_oracle": member_ok,
+            "sampled_neighbours_in_order": bool(order_ok), "key_matches_source_row": bool(pairing_ok),
+            "row_ids_conserved": rows_ok, "sample_rows": int(len(here))}
+
+
+def run_cfg4(args):
+    import torch
+    from hyperspace_1_b200 import abi, native
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    line = cfg4_measure(torch, native, abi, dev, args.rows or 80_000_000, args.steps, args.warmup, args.large_offsets,
+                        check=not args.no_check)
     print(json.dumps(line), flush=True)
-    ctx.close()
 
 
 def main():
@@ -96,6 +162,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--large-offsets", action="store_true", help="cfg4: int64 offsets even below 2 GiB of key bytes")
+    ap.add_argument("--no-check", action="store_true")
     args = ap.parse_args()
     if args.config == "cfg4":
         run_cfg4(args)
@@ -148,30 +215,12 @@ def run_parquet(args):
     ctx.close()
 
 
-def run_cfg5(args):
-    """cfg5: (k1:int32 < 2^20, k2:int64 < 2^40, v:float64), 8192 buckets, rows generated on the device per rank;
-    distributed build of the base, distributed build of a 10 % append (refresh-incremental builds the delta only),
-    then on every rank, over its own buckets and without communication: merge of the two runs per bucket and a
-    join of the merged index with the delta index on (k1, k2)."""
-    import torch
-    import torch.distributed as dist
-    from hyperspace_1_b200 import abi, native
-    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    dev = torch.device("cuda", local)
-    torch.cuda.set_device(dev)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ.setdefault("MASTER_PORT", "29517")
-        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
-    ctx = native.Context(local)
-    if world > 1:
-        uid = torch.zeros(128, dtype=torch.uint8, device=dev)
-        if rank == 0:
-            uid = torch.frombuffer(bytearray(ctx.comm_unique_id()), dtype=torch.uint8).to(dev)
-        dist.broadcast(uid, 0)
-        ctx.comm_init(rank, world, bytes(uid.cpu().numpy().tobytes()))
-    n, nb = args.rows or 500_000_000, 8192
+def cfg5_measure(torch, dist, native, abi, ctx, rank, world, dev, n, steps, warmup):
+    """cfg5 on `world` GPUs with an initialised context (comm set up when world > 1): n rows per GPU generated on
+    the device, distributed build, build of a 10 % append, merge of the two runs, join; every index checked with
+    tools/index_check.py. Rank 0 gets the result line, the others None."""
+    ROOT = os.path.dirname(HERE)
+    nb = 8192
     nd = n // 10
 
     def gen(m, seed):
@@ -228,19 +277,19 @@ def run_cfg5(args):
         return int(tt.item())
 
     cb, cd = cols(base), cols(delta)
-    ms_base, tb = timed(lambda: ctx.build_index_table(cb, 2, nb, dist=use_dist), args.steps, args.warmup, True)
+    ms_base, tb = timed(lambda: ctx.build_index_table(cb, 2, nb, dist=use_dist), steps, warmup, True)
     xb = ctx.comm_last_exchange() if use_dist else None
     ctx.enable_timing(True)
     for _ in range(2):   # the second call's numbers are reported (the first may still grow the block cache)
         ctx.build_index_table(cb, 2, nb, dist=use_dist).free()
         stages = {name: round(ms, 3) for name, ms, _ in ctx.last_timings()}
     ctx.enable_timing(False)
-    ms_delta, td = timed(lambda: ctx.build_index_table(cd, 2, nb, dist=use_dist), args.steps, args.warmup, True)
+    ms_delta, td = timed(lambda: ctx.build_index_table(cd, 2, nb, dist=use_dist), steps, warmup, True)
     rows_owned = total(tb.nrows)
     vb, vd = tb.view(2), td.view(2)
-    ms_merge, tm = timed(lambda: ctx.merge_tables([vb, vd]), args.steps, 1, True)
+    ms_merge, tm = timed(lambda: ctx.merge_tables([vb, vd]), steps, 1, True)
     vm = tm.view(2)
-    ms_join, tj = timed(lambda: ctx.join_table(vm, vd, [0, 1, 2], [2]), args.steps, 1, True)
+    ms_join, tj = timed(lambda: ctx.join_table(vm, vd, [0, 1, 2], [2]), steps, 1, True)
     out_rows = total(tj.nrows)
     merged_rows = total(tm.nrows)
     # every delta row finds itself in the merged index ...
@@ -262,6 +311,7 @@ def run_cfg5(args):
     ok = ok and all(c["ok"] for c in checks.values())
     for t in (tj, tm, td, tb):
         t.free()
+    line = None
     if rank == 0:
         row_bytes, key_bytes = 20, 12
         line = {"config": "cfg5", "n_gpus": world, "rows_per_gpu": n, "delta_rows_per_gpu": nd, "num_buckets": nb,
@@ -276,6 +326,34 @@ def run_cfg5(args):
         line["build_stages_ms_rank0"] = stages
         if xb:
             line["exchange_bytes_ms_rank0"] = xb
+    return line
+
+
+def run_cfg5(args):
+    """cfg5: (k1:int32 < 2^20, k2:int64 < 2^40, v:float64), 8192 buckets, rows generated on the device per rank;
+    distributed build of the base, distributed build of a 10 % append (refresh-incremental builds the delta only),
+    then on every rank, over its own buckets and without communication: merge of the two runs per bucket and a
+    join of the merged index with the delta index on (k1, k2)."""
+    import torch
+    import torch.distributed as dist
+    from hyperspace_1_b200 import abi, native
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29517")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    ctx = native.Context(local)
+    if world > 1:
+        uid = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            uid = torch.frombuffer(bytearray(ctx.comm_unique_id()), dtype=torch.uint8).to(dev)
+        dist.broadcast(uid, 0)
+        ctx.comm_init(rank, world, bytes(uid.cpu().numpy().tobytes()))
+    line = cfg5_measure(torch, dist, native, abi, ctx, rank, world, dev, args.rows or 500_000_000, args.steps, args.warmup)
+    if rank == 0:
         print(json.dumps(line), flush=True)
     ctx.close()
     if world > 1:
