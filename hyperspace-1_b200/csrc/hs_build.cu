@@ -462,8 +462,10 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
     const char* off = getenv("HSGPU_MOVE_KEY_COLUMNS");
     if (off && *off && *off != '0') packed_keys = false;
   }
-  if (xchg && need_srcrow)
-    HS_THROW(HS_EUNSUPPORTED, "string columns and keys wider than 64 bits are not supported in the multi-GPU build");
+  if (xchg && need_srcrow) {
+    xchg->rows_first = true;
+    return;
+  }
 
   std::vector<MovedCol> mv;
   mv.reserve(HS_MAX_MOVE);

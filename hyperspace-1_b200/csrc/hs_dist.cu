@@ -578,6 +578,290 @@ struct NcclExchange : BuildExchange {
   }
 };
 
+// ------------------------------------------------------------------ rows first, then a local build
+// The general multi-GPU build, for shapes the fused scatter cannot move (string columns travel as a row id and
+// are gathered from the SOURCE column at the end, which lives on the sender; so do keys wider than one 64-bit
+// chunk): every rank groups its rows by the GPU that owns their bucket, the groups change hands in one grouped
+// ncclSend/ncclRecv round (fixed-width values, one byte per row where a column holds NULLs anywhere, string
+// lengths and string bytes as separate arrays), and each GPU then runs the ordinary single-GPU build over the
+// rows it received, restricted to its own bucket range. One more pass over the rows than the fused path.
+static __global__ void __launch_bounds__(256) k_rf_iota(uint32_t* out, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = (uint32_t)i;
+}
+template <typename OFF>
+static __global__ void __launch_bounds__(256) k_rf_lens(const OFF* __restrict__ off, int64_t n, uint32_t* __restrict__ lens) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    lens[i] = (uint32_t)(off[i + 1] - off[i]);
+}
+static __global__ void __launch_bounds__(256) k_rf_bits_to_bytes(const uint8_t* __restrict__ bits, int64_t n, uint8_t* __restrict__ out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = bits ? (bits[i >> 3] >> (i & 7)) & 1 : 1;
+}
+static __global__ void __launch_bounds__(256) k_rf_bytes_to_bits(const uint8_t* __restrict__ in, int64_t n, uint8_t* __restrict__ bits,
+                                                                 unsigned long long* zeros) {
+  const int64_t nb = (n + 7) >> 3;
+  unsigned z = 0;
+  for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < nb; b += (int64_t)gridDim.x * blockDim.x) {
+    unsigned v = 0;
+    for (int k = 0; k < 8; k++) {
+      const int64_t i = b * 8 + k;
+      if (i < n) { if (in[i]) v |= 1u << k; else z++; }
+    }
+    bits[b] = (uint8_t)v;
+  }
+  if (zeros && z) atomicAdd(zeros, (unsigned long long)z);
+}
+static unsigned rf_grid(int64_t n) {
+  int64_t g = (n + 255) / 256;
+  return (unsigned)std::max<int64_t>(1, std::min<int64_t>(g, HS_NUM_SMS * 16));
+}
+
+struct RfPart {           // one array that changes hands
+  const uint8_t* src = nullptr;            // sender side, grouped by owner
+  std::vector<uint64_t> cut;               // N + 1 byte offsets of the owners' pieces inside src
+  DBuf recv;                               // receiver side: the pieces of rank 0, 1, ... one after the other
+  uint64_t recv_bytes = 0;
+};
+
+static void dist_build_rows_first(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int nb,
+                                  std::vector<OutCol>& out, std::vector<int64_t>& boff) {
+  const int N = c->nranks, me = c->rank, ncols = (int)cols.size();
+  nccl_comm comm = (nccl_comm)c->comm;
+  const int64_t n = cols[0].length;
+  if (n >= 0xFFFFFFF0ll) HS_THROW(HS_EUNSUPPORTED, "more than 2^32-16 rows on one GPU");
+  if (nb > 8192 * N) HS_THROW(HS_EUNSUPPORTED, "more than 8192 buckets per GPU");
+  // ---- bucket of every row, rows per bucket; rows grouped by bucket (hence by owner: owners hold bucket ranges)
+  std::vector<uint32_t> h_hist((size_t)nb, 0);
+  DBuf perm(c, (size_t)std::max<int64_t>(n, 1) * 4);
+  {
+    Stage s(c, "group_by_owner");
+    KeySpec ks = hs_make_keyspec(cols, n_indexed);
+    DBuf bucket(c, (size_t)std::max<int64_t>(n, 1) * 2 + 16), hist(c, (size_t)nb * 4), minmax(c, (2 * HS_MAX_KEYS + 1) * 8);
+    hs_hash_bucket_hist(c, ks, cols, n, nb, 0, nb, bucket.as<uint16_t>(), hist.as<uint32_t>(), minmax.as<uint64_t>());
+    CK(cudaMemcpyAsync(h_hist.data(), hist.p, (size_t)nb * 4, cudaMemcpyDeviceToHost, c->stream));
+    hs_sync(c);
+    std::vector<uint32_t> off((size_t)nb + 1, 0);
+    for (int b = 0; b < nb; b++) off[b + 1] = off[b] + h_hist[b];
+    DBuf d_off(c, ((size_t)nb + 1) * 4), iota(c, (size_t)std::max<int64_t>(n, 1) * 4);
+    CK(cudaMemcpyAsync(d_off.p, off.data(), ((size_t)nb + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+    if (n > 0) {
+      LAUNCH(c, k_rf_iota, rf_grid(n), 256, 0, iota.as<uint32_t>(), n);
+      MoveSet ms;
+      memset(&ms, 0, sizeof ms);
+      ms.n = 1;
+      ms.esize[0] = 4;
+      ms.a[0] = perm.p;
+      const void* src0 = iota.p;
+      if (nb <= 8192) {
+        hs_bucket_scatter(c, &src0, ms, bucket.as<uint16_t>(), n, nb, d_off.as<uint32_t>());
+      } else {
+        HS_THROW(HS_EUNSUPPORTED, "the rows-first multi-GPU build takes at most 8192 buckets");
+      }
+    }
+    hs_sync(c);   // off and the scatter's temporaries go out of scope
+  }
+  std::vector<uint64_t> row_cut((size_t)N + 1, 0);    // rows for owner o: [row_cut[o], row_cut[o+1])
+  {
+    uint64_t run = 0;
+    int o = 0;
+    for (int b = 0; b < nb; b++) {
+      while (o < owner_of(b, N, nb)) row_cut[++o] = run;
+      run += h_hist[b];
+    }
+    while (o < N) row_cut[++o] = run;
+  }
+  // ---- which columns hold NULLs on some rank (everyone must send the same arrays)
+  std::vector<uint8_t> nulls_here((size_t)ncols, 0), nulls_any((size_t)ncols * N, 0);
+  for (int i = 0; i < ncols; i++) nulls_here[i] = cols[i].validity && cols[i].null_count != 0;
+  {
+    DBuf d_in(c, (size_t)ncols), d_all(c, (size_t)ncols * N);
+    CK(cudaMemcpyAsync(d_in.p, nulls_here.data(), (size_t)ncols, cudaMemcpyHostToDevice, c->stream));
+    NCK(g_nccl.allgather(d_in.p, d_all.p, (size_t)ncols, NCCL_UINT8, comm, c->stream));
+    CK(cudaMemcpyAsync(nulls_any.data(), d_all.p, (size_t)ncols * N, cudaMemcpyDeviceToHost, c->stream));
+    hs_sync(c);
+  }
+  auto has_nulls = [&](int i) { for (int r = 0; r < N; r++) if (nulls_any[(size_t)r * ncols + i]) return true; return false; };
+
+  // ---- every column gathered into owner order and taken apart into the arrays that travel
+  std::vector<OutCol> grouped((size_t)ncols);
+  std::vector<DBuf> keep;                  // expanded forms (bytes per row, lengths)
+  keep.reserve((size_t)ncols * 3);
+  std::vector<RfPart> parts;
+  struct ColParts { int data = -1, valid = -1, lens = -1; };
+  std::vector<ColParts> cp((size_t)ncols);
+  auto rows_part = [&](const uint8_t* p, int w) {
+    RfPart part;
+    part.src = p;
+    part.cut.resize((size_t)N + 1);
+    for (int o = 0; o <= N; o++) part.cut[o] = row_cut[o] * (uint64_t)w;
+    parts.push_back(std::move(part));
+    return (int)parts.size() - 1;
+  };
+  {
+    Stage s(c, "gather_by_owner");
+    for (int i = 0; i < ncols; i++) {
+      hs_gather_column(c, cols[i], perm.as<uint32_t>(), n, grouped[i]);
+      OutCol& g = grouped[i];
+      if (has_nulls(i)) {
+        keep.emplace_back(c, (size_t)std::max<int64_t>(n, 1));
+        if (n > 0) LAUNCH(c, k_rf_bits_to_bytes, rf_grid(n), 256, 0, g.validity.as<uint8_t>(), n, keep.back().as<uint8_t>());
+        cp[i].valid = rows_part(keep.back().as<uint8_t>(), 1);
+      }
+      if (hs_is_varlen(g.type)) {
+        keep.emplace_back(c, (size_t)std::max<int64_t>(n, 1) * 4);
+        uint32_t* lens = keep.back().as<uint32_t>();
+        std::vector<uint64_t> bcut((size_t)N + 1, 0);
+        const bool large = hs_is_large(g.type);
+        if (n > 0) {
+          if (large) LAUNCH(c, k_rf_lens<int64_t>, rf_grid(n), 256, 0, g.offsets.as<int64_t>(), n, lens);
+          else LAUNCH(c, k_rf_lens<int32_t>, rf_grid(n), 256, 0, g.offsets.as<int32_t>(), n, lens);
+          for (int o = 0; o <= N; o++) {   // byte offset of every owner's first row
+            if (large) {
+              int64_t v = 0;
+              CK(cudaMemcpyAsync(&v, g.offsets.as<int64_t>() + row_cut[o], 8, cudaMemcpyDeviceToHost, c->stream));
+              hs_sync(c);
+              bcut[o] = (uint64_t)v;
+            } else {
+              int32_t v = 0;
+              CK(cudaMemcpyAsync(&v, g.offsets.as<int32_t>() + row_cut[o], 4, cudaMemcpyDeviceToHost, c->stream));
+              hs_sync(c);
+              bcut[o] = (uint64_t)(uint32_t)v;
+            }
+          }
+        }
+        cp[i].lens = rows_part((const uint8_t*)lens, 4);
+        RfPart part;
+        part.src = g.data.as<uint8_t>();
+        part.cut = bcut;
+        parts.push_back(std::move(part));
+        cp[i].data = (int)parts.size() - 1;
+      } else if (g.type == HS_BOOL) {
+        keep.emplace_back(c, (size_t)std::max<int64_t>(n, 1));
+        if (n > 0) LAUNCH(c, k_rf_bits_to_bytes, rf_grid(n), 256, 0, g.data.as<uint8_t>(), n, keep.back().as<uint8_t>());
+        cp[i].data = rows_part(keep.back().as<uint8_t>(), 1);
+      } else {
+        cp[i].data = rows_part(g.data.as<uint8_t>(), hs_fixed_width(g.type));
+      }
+    }
+  }
+  // ---- who sends how much to whom: row [r][o * (P + 1) + p] = bytes of part p from rank r to owner o (p = P: rows)
+  const int P = (int)parts.size();
+  std::vector<uint64_t> mine((size_t)N * (P + 1)), all((size_t)N * N * (P + 1));
+  for (int o = 0; o < N; o++) {
+    for (int p = 0; p < P; p++) mine[(size_t)o * (P + 1) + p] = parts[p].cut[o + 1] - parts[p].cut[o];
+    mine[(size_t)o * (P + 1) + P] = row_cut[o + 1] - row_cut[o];
+  }
+  {
+    DBuf d_in(c, mine.size() * 8), d_all(c, all.size() * 8);
+    CK(cudaMemcpyAsync(d_in.p, mine.data(), mine.size() * 8, cudaMemcpyHostToDevice, c->stream));
+    NCK(g_nccl.allgather(d_in.p, d_all.p, mine.size(), NCCL_UINT64, comm, c->stream));
+    CK(cudaMemcpyAsync(all.data(), d_all.p, all.size() * 8, cudaMemcpyDeviceToHost, c->stream));
+    hs_sync(c);
+  }
+  auto from = [&](int r, int p) { return all[((size_t)r * N + me) * (P + 1) + p]; };   // bytes (rows for p == P) rank r sends here
+  uint64_t m_rows = 0;
+  for (int r = 0; r < N; r++) m_rows += from(r, P);
+  for (int o = 0; o < N; o++) {   // every rank sees the whole matrix: a rank over the limit fails the build on all ranks
+    uint64_t t = 0;
+    for (int r = 0; r < N; r++) t += all[((size_t)r * N + o) * (P + 1) + P];
+    if (t >= 0xFFFFFFF0ull) HS_THROW(HS_EUNSUPPORTED, "more than 2^32-16 rows on GPU %d", o);
+  }
+  // ---- the exchange: one grouped round of sends and receives; this rank's own piece is a local copy
+  int64_t sent = 0;
+  cudaEvent_t x0, x1;
+  CK(cudaEventCreate(&x0));
+  CK(cudaEventCreate(&x1));
+  {
+    Stage s(c, "rows_all_to_all");
+    for (int p = 0; p < P; p++) {
+      uint64_t tot = 0;
+      for (int r = 0; r < N; r++) tot += from(r, p);
+      parts[p].recv_bytes = tot;
+      parts[p].recv.alloc(c, (size_t)std::max<uint64_t>(tot, 16));
+    }
+    CK(cudaEventRecord(x0, c->stream));
+    NCK(g_nccl.group_start());
+    for (int p = 0; p < P; p++) {
+      uint64_t at = 0;
+      for (int r = 0; r < N; r++) {
+        const uint64_t in_bytes = from(r, p);
+        uint8_t* dst = parts[p].recv.as<uint8_t>() + at;
+        at += in_bytes;
+        const uint64_t out_bytes = parts[p].cut[r + 1] - parts[p].cut[r];
+        const uint8_t* src = parts[p].src + parts[p].cut[r];
+        if (r == me) {
+          if (in_bytes) CK(cudaMemcpyAsync(dst, src, (size_t)in_bytes, cudaMemcpyDeviceToDevice, c->stream));
+          continue;
+        }
+        if (out_bytes) { NCK(g_nccl.send((void*)src, (size_t)out_bytes, NCCL_UINT8, r, comm, c->stream)); sent += (int64_t)out_bytes; }
+        if (in_bytes) NCK(g_nccl.recv(dst, (size_t)in_bytes, NCCL_UINT8, r, comm, c->stream));
+      }
+    }
+    NCK(g_nccl.group_end());
+    CK(cudaEventRecord(x1, c->stream));
+  }
+  // ---- the received arrays as columns again
+  const int64_t m = (int64_t)m_rows;
+  std::vector<DevCol> rcv((size_t)ncols);
+  {
+    Stage s(c, "rows_to_columns");
+    for (int i = 0; i < ncols; i++) {
+      DevCol& d = rcv[i];
+      d.type = cols[i].type;
+      d.length = m;
+      if (cp[i].valid >= 0) {
+        DBuf bits(c, (size_t)(m + 7) / 8 + 16), zeros(c, 8);
+        zeros.zero();
+        if (m > 0) LAUNCH(c, k_rf_bytes_to_bits, rf_grid((m + 7) / 8), 256, 0, parts[cp[i].valid].recv.as<uint8_t>(), m,
+                          bits.as<uint8_t>(), zeros.as<unsigned long long>());
+        unsigned long long z = 0;
+        CK(cudaMemcpyAsync(&z, zeros.p, 8, cudaMemcpyDeviceToHost, c->stream));
+        hs_sync(c);
+        d.null_count = (int64_t)z;
+        if (z) d.validity = bits.as<uint8_t>();
+        d.owned.push_back(std::move(bits));
+      }
+      RfPart& dp = parts[cp[i].data];
+      if (hs_is_varlen(d.type)) {
+        OutCol tmp;
+        tmp.type = d.type;
+        const int64_t bytes = hs_offsets_from_lens(c, parts[cp[i].lens].recv.as<uint32_t>(), m, d.type, tmp);
+        if ((uint64_t)bytes != dp.recv_bytes) HS_THROW(HS_ENCCL, "string bytes received do not match their lengths");
+        d.type = tmp.type;                          // the large type when the received bytes pass 2 GiB
+        d.offsets = tmp.offsets.as<int32_t>();
+        d.owned.push_back(std::move(tmp.offsets));
+        d.data = dp.recv.p;
+        d.data_bytes = bytes;
+      } else if (d.type == HS_BOOL) {
+        DBuf bits(c, (size_t)(m + 7) / 8 + 16);
+        if (m > 0) LAUNCH(c, k_rf_bytes_to_bits, rf_grid((m + 7) / 8), 256, 0, dp.recv.as<uint8_t>(), m, bits.as<uint8_t>(),
+                          (unsigned long long*)nullptr);
+        d.data = bits.p;
+        d.data_bytes = (m + 7) / 8;
+        d.owned.push_back(std::move(bits));
+      } else {
+        d.data = dp.recv.p;
+        d.data_bytes = m * hs_fixed_width(d.type);
+      }
+    }
+  }
+  // the source-side copies are no longer needed; the received pieces stay alive inside `parts` until the build is done
+  grouped.clear();
+  keep.clear();
+  perm.release();
+  int blo = 0, bhi = 0;
+  for (int b = 0; b < nb; b++) if (owner_of(b, N, nb) == me) { blo = b; break; }
+  for (bhi = blo; bhi < nb && owner_of(bhi, N, nb) == me; bhi++) {}
+  hs_build_core(c, rcv, n_indexed, nb, blo, bhi - blo, out, boff, nullptr);
+  CK(cudaEventSynchronize(x1));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, x0, x1);
+  cudaEventDestroy(x0);
+  cudaEventDestroy(x1);
+  c->last_xchg_bytes = sent;
+  c->last_xchg_ms = ms;
+}
+
 extern "C" {
 
 int32_t hs_comm_unique_id(hs_ctx* ctx, void* out_id128) {
@@ -657,6 +941,13 @@ int32_t hs_build_index_dist(hs_ctx* ctx, const hs_column* cols, int32_t ncols, i
   }
   NcclExchange xchg(ctx, nb);
   hs_build_core(ctx, dcols, n_indexed, nb, 0, nb, ocols, boff, &xchg);
+  if (xchg.rows_first) {
+    // string columns or a key wider than one 64-bit chunk (every rank decides the same from the shared statistics):
+    // rows change hands first, then every GPU builds its own buckets
+    ocols.clear();
+    boff.clear();
+    dist_build_rows_first(ctx, dcols, n_indexed, nb, ocols, boff);
+  }
   Stage s(ctx, "d2h");
   *out = hs_finish_table(ctx, ocols, boff[nb], nb, &boff);
   API_END(ctx)

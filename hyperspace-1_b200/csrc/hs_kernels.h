@@ -32,6 +32,9 @@ struct BuildExchange {
   // 4 bytes (value - minimum) and be widened again by the receiver's bucket scatter.
   int key_col = -1;
   uint64_t key_min = 0, key_span = ~0ull;
+  // set by the build (on every rank alike, from the shared statistics) when the rows cannot take the fused path:
+  // the build returns without having moved anything and the caller exchanges whole rows first
+  bool rows_first = false;
   virtual bool try_fused(hs_ctx* c, const std::vector<int>& esize) { return false; }
   virtual int64_t scatter_exchange(hs_ctx* c, const void* const* srcs, const std::vector<int>& esize,
                                    const uint16_t* d_bucket, int64_t n_local, std::vector<void*>& recv,

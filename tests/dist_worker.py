@@ -20,11 +20,29 @@ import parity  # noqa: E402
 NB = 64
 
 
-NKEYS = int(os.environ.get("HS_DIST_NKEYS", "2"))   # 1: a single non-null int64 key (the lineitem shape)
+NKEYS = int(os.environ.get("HS_DIST_NKEYS", "2"))
+if os.environ.get("HS_DIST_SHAPE", "") == "strings":
+    NKEYS = 1   # 1: a single non-null int64 key (the lineitem shape)
+
+
+SHAPE = os.environ.get("HS_DIST_SHAPE", "")   # "strings": string key and payload; "wide": a key of two full-range int64
 
 
 def shard(rank, world, n=30000):
     rng = np.random.default_rng(100 + rank)
+    if SHAPE == "strings":
+        # a string key (NULLs on even ranks only, shared prefixes, some multi-byte), an int64, a string payload with
+        # NULLs on odd ranks only, and a boolean: everything the rows-first exchange has to take apart
+        words = ["", "a", "ab", "abc", "prefix-shared-" * 2, "é日本", "zz"]
+        k = [words[int(rng.integers(0, len(words)))] + str(int(rng.integers(0, 5000))) for _ in range(n)]
+        kmask = rng.random(n) < (0.03 if rank % 2 == 0 else 0.0)
+        pay = ["p" * int(rng.integers(0, 30)) for _ in range(n)]
+        pmask = rng.random(n) < (0.05 if rank % 2 == 1 else 0.0)
+        return [pa.array(k, mask=kmask), pa.array(rng.integers(-2**40, 2**40, size=n)), pa.array(pay, mask=pmask),
+                pa.array(rng.random(n) < 0.5)]
+    if SHAPE == "wide":
+        return [pa.array(rng.integers(-2**63, 2**63 - 1, size=n, dtype=np.int64)),
+                pa.array(rng.integers(-2**63, 2**63 - 1, size=n, dtype=np.int64)), pa.array(rng.random(n))]
     if NKEYS == 1:
         # negative and positive keys around a large offset: exercises the sign flip and the subtraction of the
         # minimum when the key crosses NVLink as 4 bytes
@@ -69,7 +87,7 @@ def main():
         pieces = [[c.take(pa.array(np.nonzero(own == r)[0])).to_pylist() for c in cols] for r in range(world)]
         recv = [None] * world
         dist.all_gather_object(recv, pieces)
-        mine = [pa.array(sum((recv[src][rank][i] for src in range(world)), []), type=cols[i].type) for i in range(3)]
+        mine = [pa.array(sum((recv[src][rank][i] for src in range(world)), []), type=cols[i].type) for i in range(len(cols))]
         p2, o2 = oracle.build_index(mine, NKEYS, NB)
         got = oracle.take(mine, p2)
         goff = o2

@@ -41,6 +41,24 @@ def test_sharded_build_world2_gloo():
     _run("gloo", 2)
 
 
+def test_sharded_build_world2_gloo_string_rows(monkeypatch):
+    monkeypatch.setenv("HS_DIST_SHAPE", "strings")
+    _run("gloo", 2)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", ["strings", "wide"])
+def test_rows_first_build_world2_nccl(shape, monkeypatch):
+    """String columns and keys wider than 64 bits cannot ride the fused scatter (their bytes stay with the sender):
+    whole rows change hands first, then every GPU builds its own buckets. Checked against the oracle's index of
+    all ranks' rows."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    monkeypatch.setenv("HS_DIST_SHAPE", shape)
+    _run("nccl", 2)
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("exchange", ["fused", "owner", "copy", "nccl", "owner-int64-key", "fused-int64-key"])
 def test_sharded_build_world2_nccl(exchange, monkeypatch):
