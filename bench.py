@@ -337,12 +337,20 @@ def main():
                 "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})", "unit": "GB/s", "frac": achieved / peak,
                 "algorithmic_bytes_per_row": algo[dom], "rows_per_launch": n, "ms_per_launch": dom_ms,
                 "traffic": None}
+    # DRAM bytes per launch of that kernel from an ncu capture (profiles/dominant_kernel_traffic.json). The file
+    # names the sha256 of the kernel's source file it was taken with: when the source has changed since, the
+    # figure is stale and is left out rather than repeated.
     tr_path = os.path.join(ROOT, "profiles", "dominant_kernel_traffic.json")
     if os.path.exists(tr_path):
         try:
+            import hashlib
             tr = json.load(open(tr_path))
-            if tr.get("kernel") == kernel_of[dom] and tr.get("rows") == n:
+            src = os.path.join(ROOT, tr.get("source_file", ""))
+            sha = hashlib.sha256(open(src, "rb").read()).hexdigest() if os.path.isfile(src) else None
+            if tr.get("kernel") == kernel_of[dom] and tr.get("rows") == n and sha and sha == tr.get("source_sha256"):
                 roofline["traffic"] = tr["dram_bytes_per_launch"]
+            else:
+                roofline["traffic_note"] = "no ncu capture for this kernel at this source revision"
         except Exception:
             pass
     build_gbs = ALGO_BYTES_PER_ROW * n / (ms_step * 1e-3) / 1e9

@@ -174,9 +174,13 @@ KCol hs_kcol(const DevCol& d) {
 
 void hs_dev_cache_flush(hs_ctx* c) {
   for (auto& kv : c->dev_free) cudaFreeAsync(kv.second, c->stream);
-  for (auto& kv : c->dev_free) c->dev_size.erase(kv.second);
+  for (auto& kv : c->dev_free) { c->dev_size.erase(kv.second); c->cache_age.erase(kv.second); }
   c->dev_free.clear();
   c->dev_cached_bytes = 0;
+}
+
+static cudaError_t pool_alloc(hs_ctx* c, void** p, size_t bytes) {
+  return c->pool ? cudaMallocFromPoolAsync(p, bytes, c->pool, c->stream) : cudaMallocAsync(p, bytes, c->stream);
 }
 
 void* hs_dev_alloc(hs_ctx* c, size_t bytes) {
@@ -186,17 +190,18 @@ void* hs_dev_alloc(hs_ctx* c, size_t bytes) {
     if (it != c->dev_free.end() && it->first <= bytes + bytes / 4) {
       void* p = it->second;
       c->dev_cached_bytes -= it->first;
+      c->cache_age.erase(p);
       c->dev_free.erase(it);
       return p;
     }
   }
   void* p = nullptr;
-  cudaError_t e = cudaMallocAsync(&p, bytes, c->stream);
+  cudaError_t e = pool_alloc(c, &p, bytes);
   if (e == cudaErrorMemoryAllocation && !c->dev_free.empty()) {
     cudaGetLastError();
     hs_dev_cache_flush(c);
     cudaStreamSynchronize(c->stream);
-    e = cudaMallocAsync(&p, bytes, c->stream);
+    e = pool_alloc(c, &p, bytes);
   }
   if (e != cudaSuccess) {
     cudaGetLastError();
@@ -216,6 +221,18 @@ void hs_dev_free(hs_ctx* c, void* p) {
   }
   c->dev_free.insert({it->second, p});
   c->dev_cached_bytes += it->second;
+  c->cache_age[p] = ++c->cache_clock;
+  // over the cap: the blocks freed longest ago go back to the pool (the cache holds a few dozen blocks at most)
+  while (c->dev_cached_bytes > c->dev_cache_cap && !c->dev_free.empty()) {
+    auto old = c->dev_free.begin();
+    for (auto j = c->dev_free.begin(); j != c->dev_free.end(); ++j)
+      if (c->cache_age[j->second] < c->cache_age[old->second]) old = j;
+    cudaFreeAsync(old->second, c->stream);
+    c->dev_cached_bytes -= old->first;
+    c->dev_size.erase(old->second);
+    c->cache_age.erase(old->second);
+    c->dev_free.erase(old);
+  }
 }
 
 void* hs_pinned_alloc(hs_ctx* c, size_t bytes) {
@@ -226,6 +243,8 @@ void* hs_pinned_alloc(hs_ctx* c, size_t bytes) {
   auto it = c->pinned_free.lower_bound(cap);
   if (it != c->pinned_free.end() && it->first <= cap * 2) {
     void* p = it->second;
+    c->pinned_cached_bytes -= it->first;
+    c->cache_age.erase(p);
     c->pinned_free.erase(it);
     return p;
   }
@@ -240,6 +259,18 @@ void hs_pinned_free(hs_ctx* c, void* p) {
   auto it = c->pinned_size.find(p);
   if (it == c->pinned_size.end()) return;
   c->pinned_free.insert({it->second, p});
+  c->pinned_cached_bytes += it->second;
+  c->cache_age[p] = ++c->cache_clock;
+  while (c->pinned_cached_bytes > c->pinned_cache_cap && !c->pinned_free.empty()) {
+    auto old = c->pinned_free.begin();
+    for (auto j = c->pinned_free.begin(); j != c->pinned_free.end(); ++j)
+      if (c->cache_age[j->second] < c->cache_age[old->second]) old = j;
+    cudaFreeHost(old->second);
+    c->pinned_cached_bytes -= old->first;
+    c->pinned_size.erase(old->second);
+    c->cache_age.erase(old->second);
+    c->pinned_free.erase(old);
+  }
 }
 
 hs_table* hs_finish_table(hs_ctx* c, std::vector<OutCol>& cols, int64_t nrows, int32_t num_buckets,
@@ -339,12 +370,30 @@ int32_t hs_ctx_create(int32_t device, hs_ctx** out) {
     delete c;
     return HS_ECUDA;
   }
-  // keep freed blocks in the stream-ordered pool: repeated builds reuse them without cudaMalloc
-  cudaMemPool_t pool;
-  if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
-    uint64_t thr = UINT64_MAX;
-    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+  // a stream-ordered pool of the context's own, which keeps freed blocks (repeated builds reuse them without
+  // cudaMalloc); the device's default pool, which belongs to the host application, is left as it is
+  {
+    cudaMemPoolProps props;
+    memset(&props, 0, sizeof props);
+    props.allocType = cudaMemAllocationTypePinned;
+    props.handleTypes = cudaMemHandleTypeNone;
+    props.location.type = cudaMemLocationTypeDevice;
+    props.location.id = device;
+    if (cudaMemPoolCreate(&c->pool, &props) == cudaSuccess) {
+      uint64_t thr = UINT64_MAX;
+      cudaMemPoolSetAttribute(c->pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    } else {
+      cudaGetLastError();
+      c->pool = nullptr;   // allocations fall back to the default pool, untouched
+    }
   }
+  // bounds of the two block caches (oldest blocks are released beyond them)
+  size_t free_b = 0, total_b = 0;
+  if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) { cudaGetLastError(); total_b = size_t(16) << 30; }
+  c->dev_cache_cap = total_b / 2;
+  c->pinned_cache_cap = size_t(16) << 30;
+  if (const char* e = getenv("HSGPU_CACHE_MB")) c->dev_cache_cap = (size_t)atoll(e) << 20;
+  if (const char* e = getenv("HSGPU_PINNED_CACHE_MB")) c->pinned_cache_cap = (size_t)atoll(e) << 20;
   *out = c;
   return HS_OK;
 }
@@ -366,6 +415,7 @@ int32_t hs_ctx_destroy(hs_ctx* c) {
   }
   if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
   cudaStreamDestroy(c->stream);
+  if (c->pool) cudaMemPoolDestroy(c->pool);
   delete c;
   return HS_OK;
 }
@@ -428,6 +478,18 @@ int32_t hs_table_free(hs_ctx* c, hs_table* t) {
   }
   delete t;
   return HS_OK;
+}
+
+int32_t hs_ctx_trim(hs_ctx* c) {
+  API_BEGIN(c)
+  hs_sync(c);
+  hs_dev_cache_flush(c);
+  for (auto& kv : c->pinned_free) { cudaFreeHost(kv.second); c->pinned_size.erase(kv.second); c->cache_age.erase(kv.second); }
+  c->pinned_free.clear();
+  c->pinned_cached_bytes = 0;
+  hs_sync(c);
+  if (c->pool) CK(cudaMemPoolTrimTo(c->pool, 0));
+  API_END(c)
 }
 
 int32_t hs_ctx_set_deferred_results(hs_ctx* c, int32_t on) {

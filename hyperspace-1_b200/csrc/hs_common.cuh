@@ -62,6 +62,12 @@ struct hs_ctx {
   std::multimap<size_t, void*> dev_free;
   std::map<void*, size_t> dev_size;
   size_t dev_cached_bytes = 0;
+  size_t dev_cache_cap = 0;          // bytes the block cache may hold (hs_ctx_create: half of the device memory,
+                                     // HSGPU_CACHE_MB overrides); beyond it the oldest blocks go back to the pool
+  size_t pinned_cached_bytes = 0, pinned_cache_cap = 0;   // same for pinned result buffers (HSGPU_PINNED_CACHE_MB)
+  std::map<void*, uint64_t> cache_age;                    // when a cached block (device or pinned) was freed
+  uint64_t cache_clock = 0;
+  cudaMemPool_t pool = nullptr;      // the context's own stream-ordered pool: the device's default pool is not touched
   // multi-GPU (hs_dist.cu)
   void* nccl_lib = nullptr;
   void* comm = nullptr;

@@ -16,7 +16,7 @@ _lib = None
 EXPORTS = [
     "hs_ctx_create", "hs_ctx_destroy", "hs_last_error", "hs_ctx_set_output_location", "hs_ctx_get_stream",
     "hs_ctx_enable_timing", "hs_ctx_last_timings", "hs_ctx_launch_count", "hs_table_free", "hs_version",
-    "hs_ctx_set_deferred_results", "hs_table_wait",
+    "hs_ctx_set_deferred_results", "hs_table_wait", "hs_ctx_trim",
     "hs_parquet_plain_pages",
     "hs_hash_bucket", "hs_hash_rows", "hs_build_index", "hs_merge_runs", "hs_join_bucketed", "hs_filter_scan",
     "hs_bucket_histogram_noalloc", "hs_comm_unique_id", "hs_comm_init", "hs_comm_destroy", "hs_build_index_dist", "hs_comm_last_exchange",
@@ -174,6 +174,10 @@ class Context:
     def set_deferred_results(self, on=True):
         """hs_ctx_set_deferred_results: host results are downloaded after the call returns; Table.wait() first."""
         self._check(self._lib.hs_ctx_set_deferred_results(self._h, C.c_int32(1 if on else 0)), "set_deferred_results")
+
+    def trim(self):
+        """hs_ctx_trim: give every cached device block and pinned buffer back to the driver."""
+        self._check(self._lib.hs_ctx_trim(self._h), "hs_ctx_trim")
 
     def enable_timing(self, on=True):
         self._check(self._lib.hs_ctx_enable_timing(self._h, C.c_int32(1 if on else 0)), "enable_timing")

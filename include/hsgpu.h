@@ -170,6 +170,12 @@ int32_t hs_ctx_set_output_location(hs_ctx* ctx, int32_t location);
  * (CreateActionBase.write, HS/actions/CreateActionBase.scala:122-140, is one call per index but many per job). */
 int32_t hs_ctx_set_deferred_results(hs_ctx* ctx, int32_t on);
 int32_t hs_table_wait(hs_ctx* ctx, hs_table* table);
+/* Memory kept between calls. A context allocates from a stream-ordered pool of its own (the device's default
+ * pool is not touched) and keeps the large device blocks and the pinned result buffers it has freed for the next
+ * call, up to half of the device memory and 16 GiB of pinned memory (environment: HSGPU_CACHE_MB,
+ * HSGPU_PINNED_CACHE_MB; the blocks freed longest ago are released beyond that). hs_ctx_trim() gives everything
+ * cached back to the driver, for hosts that share the GPU with other libraries. */
+int32_t hs_ctx_trim(hs_ctx* ctx);
 /* The cudaStream_t the context launches on (for external event timing). */
 int32_t hs_ctx_get_stream(hs_ctx* ctx, void** stream);
 int32_t hs_ctx_enable_timing(hs_ctx* ctx, int32_t on);
@@ -277,8 +283,10 @@ int32_t hs_filter_scan(hs_ctx* ctx, const hs_index_view* index,
 /* ---- multi-GPU build (one process per GPU) ----------------------------------
  * Replaces Spark's ShuffleExchangeExec under the same repartition call
  * (HS/actions/CreateActionBase.scala:129-130): rows travel once to the GPU that owns
- * their bucket, owner(b) = b * nranks / num_buckets, through an NCCL all-to-all;
- * every later step is bucket-local. hs_comm_unique_id fills a 128-byte ncclUniqueId
+ * their bucket, owner(b) = b * nranks / num_buckets: the scatter kernel stores them straight into
+ * the owner's peer-mapped memory over NVLink (NCCL sets up, synchronises and is the fallback when peers
+ * cannot be mapped); string columns and keys wider than 64 bits change hands as whole rows in one
+ * grouped ncclSend/ncclRecv round before a local build. Every later step is bucket-local. hs_comm_unique_id fills a 128-byte ncclUniqueId
  * on rank 0 which the host passes to every rank (any transport). */
 int32_t hs_comm_unique_id(hs_ctx* ctx, void* out_id128);
 int32_t hs_comm_init(hs_ctx* ctx, int32_t rank, int32_t nranks, const void* id128);
