@@ -326,6 +326,42 @@ __global__ void __launch_bounds__(JTHREADS, 2) k_join_tiles(const __grid_constan
   }
   if (lane_id() == 31) s_red[threadIdx.x >> 5] = inc;
   __syncthreads();
+  // ---- the output columns' source slices are requested now, so that the copies run beside the scan, the
+  // look-back and the lay-out of the outputs: every thread follows the same column sequence, thread 0 starts
+  // the copies (the staged right keys in buf1 are no longer read: every thread has passed the barrier above)
+  const int ncol = p.n_lout + p.n_rout;
+  auto col_src = [&](int c, const void*& src, int& es, bool& left) {
+    left = c < p.n_lout;
+    src = left ? p.lsrc[c] : p.rsrc[c - p.n_lout];
+    es = left ? p.les[c] : p.res[c - p.n_lout];
+  };
+  auto start_load = [&](int c, unsigned char* b, uint64_t* br) {
+    const void* src; int es; bool left;
+    col_src(c, src, es, left);
+    if (left) issue_slice(src, es, l0, ln, b, br);
+    else issue_slice(src, es, wlo, wn, b, br);
+  };
+  int keycol = -1;
+  for (int c = 0; c < p.n_lout; c++)
+    if (p.lsrc[c] == p.lkey && p.les[c] == (int)sizeof(K)) { keycol = c; break; }
+  // order of the staged columns: all but keycol
+  int nxt = 0;            // next column to load
+  auto next_col = [&]() { while (nxt == keycol) nxt++; return nxt < ncol ? nxt++ : -1; };
+  int inb1 = -1, inb2 = -1;
+  const bool early = MODE != 0 && staged;
+  if (early) {
+    inb1 = next_col();
+    inb2 = next_col();
+    if (threadIdx.x == 0) {
+      if (inb1 >= 0) start_load(inb1, buf1, &bar[1]);
+      if (inb2 >= 0) start_load(inb2, buf2, &bar[2]);
+    }
+  }
+  // a CTA must not retire with a bulk copy in flight
+  auto drain = [&]() {
+    if (inb1 >= 0) mbar_wait(&bar[1], ph1);
+    if (inb2 >= 0) mbar_wait(&bar[2], ph2);
+  };
   if (threadIdx.x == 0) {
     uint32_t run = 0;
     for (int w = 0; w < JTHREADS / 32; w++) { uint32_t v = s_red[w]; s_red[w] = run; run += v; }
@@ -372,11 +408,10 @@ __global__ void __launch_bounds__(JTHREADS, 2) k_join_tiles(const __grid_constan
       }
     }
     __syncthreads();
-    if ((unsigned long long)s_obase + total > p.capacity) return;   // does not fit: count only
+    if ((unsigned long long)s_obase + total > p.capacity) { drain(); return; }   // does not fit: count only
   }
   const uint32_t obase = MODE == 2 ? s_obase : p.tile_cnt[t];   // exclusive offset of this tile in the output
-  if (total == 0) return;
-  const int ncol = p.n_lout + p.n_rout;
+  if (total == 0) { drain(); return; }
   if (staged && total <= JOMAX) {
     // ---- (left row, right row) of every output position of the tile
     {
@@ -393,17 +428,6 @@ __global__ void __launch_bounds__(JTHREADS, 2) k_join_tiles(const __grid_constan
     __syncthreads();   // also: every thread is done with the staged right keys (buf1)
     // ---- columns: a left output that is the key column itself is served from buf0; the others are staged in
     // buf1 / buf2 alternately, the copy of column k + 2 starting as soon as column k has been written
-    auto col_src = [&](int c, const void*& src, int& es, bool& left) {
-      left = c < p.n_lout;
-      src = left ? p.lsrc[c] : p.rsrc[c - p.n_lout];
-      es = left ? p.les[c] : p.res[c - p.n_lout];
-    };
-    auto start_load = [&](int c, unsigned char* b, uint64_t* br) {
-      const void* src; int es; bool left;
-      col_src(c, src, es, left);
-      if (left) issue_slice(src, es, l0, ln, b, br);
-      else issue_slice(src, es, wlo, wn, b, br);
-    };
     auto write_col = [&](int c, const unsigned char* b) {
       const void* src; int es; bool left;
       col_src(c, src, es, left);
@@ -416,18 +440,6 @@ __global__ void __launch_bounds__(JTHREADS, 2) k_join_tiles(const __grid_constan
         for (uint32_t o = threadIdx.x; o < total; o += JTHREADS) ((uint32_t*)dst)[obase + o] = ((const uint32_t*)s)[map[o]];
       }
     };
-    int keycol = -1;
-    for (int c = 0; c < p.n_lout; c++)
-      if (p.lsrc[c] == p.lkey && p.les[c] == (int)sizeof(K)) { keycol = c; break; }
-    // order of the staged columns: all but keycol
-    int nxt = 0;            // next column to load
-    auto next_col = [&]() { while (nxt == keycol) nxt++; return nxt < ncol ? nxt++ : -1; };
-    // every thread follows the same column sequence; thread 0 starts the copies
-    int inb1 = next_col(), inb2 = next_col();
-    if (threadIdx.x == 0) {
-      if (inb1 >= 0) start_load(inb1, buf1, &bar[1]);
-      if (inb2 >= 0) start_load(inb2, buf2, &bar[2]);
-    }
     if (keycol >= 0) {
       write_col(keycol, buf0);
       __syncthreads();
@@ -452,6 +464,7 @@ __global__ void __launch_bounds__(JTHREADS, 2) k_join_tiles(const __grid_constan
   }
   // ---- large cross products or windows that were not staged: spread the outputs over the whole CTA and read
   // the sources from global memory
+  drain();
   __syncthreads();
 #pragma unroll
   for (int j = 0; j < JPER; j++) {
