@@ -158,6 +158,50 @@ __global__ void __launch_bounds__(256) k_filter_mask(const __grid_constant__ KCo
     tile_cnt[blockIdx.x] = t;
   }
 }
+// The common shape of FilterIndexRule's predicate — one comparison, or a range (two comparisons joined by AND), on
+// one NULL-free integer column — needs no interpreter: the tile's values are loaded up front (independent loads)
+// and compared against the literals. Same bits, same counts as k_filter_mask.
+__device__ __forceinline__ bool cmp_op(int op, int64_t x, int64_t lit) {
+  switch (op) {
+    case HS_PRED_EQ: return x == lit;
+    case HS_PRED_NE: return x != lit;
+    case HS_PRED_LT: return x < lit;
+    case HS_PRED_LE: return x <= lit;
+    case HS_PRED_GT: return x > lit;
+    default: return x >= lit;
+  }
+}
+template <typename T>
+__global__ void __launch_bounds__(256) k_filter_mask_int(const T* __restrict__ col, int op1, int64_t lit1, int op2,
+                                                         int64_t lit2, int64_t row0, int64_t n,
+                                                         uint32_t* __restrict__ mask, uint32_t* __restrict__ tile_cnt) {
+  __shared__ uint32_t s_cnt[8];
+  const int64_t base = (int64_t)blockIdx.x * FT_TILE;
+  T v[FT_TILE / 256];
+#pragma unroll
+  for (int k = 0; k < FT_TILE / 256; k++) {
+    const int64_t i = base + k * 256 + threadIdx.x;
+    v[k] = i < n ? col[row0 + i] : (T)0;
+  }
+  uint32_t c = 0;
+#pragma unroll
+  for (int k = 0; k < FT_TILE / 256; k++) {
+    const int64_t i = base + k * 256 + threadIdx.x;
+    const bool f = i < n && cmp_op(op1, (int64_t)v[k], lit1) && (op2 == 0 || cmp_op(op2, (int64_t)v[k], lit2));
+    const uint32_t b = __ballot_sync(0xffffffffu, f);
+    if (lane_id() == 0) {
+      if (base + k * 256 + (threadIdx.x & ~31) < n) mask[(base + k * 256 + threadIdx.x) >> 5] = b;
+      c += __popc(b);
+    }
+  }
+  if (lane_id() == 0) s_cnt[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+    for (int w = 0; w < 8; w++) t += s_cnt[w];
+    tile_cnt[blockIdx.x] = t;
+  }
+}
 struct FilterOut {
   int32_t n;
   int32_t es[HS_MAX_MOVE];
@@ -366,7 +410,26 @@ extern "C" int32_t hs_filter_scan(hs_ctx* ctx, const hs_index_view* index, const
     uint64_t h_total = 0;
     {
       Stage s(ctx, "filter_eval");
-      LAUNCH(ctx, k_filter_mask, ntiles, 256, 0, kc, kp, row0, n, mask.as<uint32_t>(), tcnt.as<uint32_t>());
+      // one comparison or a range on one NULL-free INT32/INT64 column: the specialised kernel
+      auto is_cmp = [&](const KTerm& t) { return t.op >= HS_PRED_EQ && t.op <= HS_PRED_GE; };
+      int fast_col = -1, op2 = 0;
+      int64_t lit2 = 0;
+      if (kp.nterms == 1 && is_cmp(kp.t[0])) fast_col = kp.t[0].col;
+      else if (kp.nterms == 3 && is_cmp(kp.t[0]) && is_cmp(kp.t[1]) && kp.t[2].op == HS_PRED_AND && kp.t[0].col == kp.t[1].col) {
+        fast_col = kp.t[0].col;
+        op2 = kp.t[1].op;
+        lit2 = kp.t[1].lit_i64;
+      }
+      if (fast_col >= 0 && (kc.c[fast_col].has_nulls || (kc.c[fast_col].type != HS_INT64 && kc.c[fast_col].type != HS_INT32)))
+        fast_col = -1;
+      if (fast_col >= 0 && kc.c[fast_col].type == HS_INT64)
+        LAUNCH(ctx, k_filter_mask_int<int64_t>, ntiles, 256, 0, (const int64_t*)kc.c[fast_col].data, kp.t[0].op,
+               kp.t[0].lit_i64, op2, lit2, row0, n, mask.as<uint32_t>(), tcnt.as<uint32_t>());
+      else if (fast_col >= 0)
+        LAUNCH(ctx, k_filter_mask_int<int32_t>, ntiles, 256, 0, (const int32_t*)kc.c[fast_col].data, kp.t[0].op,
+               kp.t[0].lit_i64, op2, lit2, row0, n, mask.as<uint32_t>(), tcnt.as<uint32_t>());
+      else
+        LAUNCH(ctx, k_filter_mask, ntiles, 256, 0, kc, kp, row0, n, mask.as<uint32_t>(), tcnt.as<uint32_t>());
       hs_exclusive_scan_u32(ctx, tcnt.as<uint32_t>(), tcnt.as<uint32_t>(), ntiles, total.as<uint64_t>());
       h_total = *(const uint64_t*)hs_read_wait(ctx, hs_read_begin(ctx, total.p, 8));
     }

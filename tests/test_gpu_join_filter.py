@@ -251,6 +251,9 @@ def test_filter_packed_outputs_keep_row_order(ctx, oracle):
         k = int(keys[len(keys) // 2])
         for p in ([("ge", 0, k)], [("eq", 0, k)], [("lt", 1, 30000.0), ("ge", 2, 0.05), ("and",)],
                   [("lt", 0, -1)], [("ge", 0, -1)], [("eq", 0, k), ("not",)],
+                  # one comparison / a range on the integer key: the specialised mask kernel
+                  [("ne", 0, k)], [("le", 0, k)], [("gt", 0, k)], [("ge", 0, k // 2), ("lt", 0, k), ("and",)],
+                  [("gt", 0, k), ("le", 0, k // 2), ("and",)],
                   [("in", 0, [int(x) for x in keys[::7]])], [("in", 0, [int(x) for x in keys[::3]]), ("not",)],
                   [("gt", 2, 0.02), ("le", 0, k), ("or",), ("ne", 1, 0.0), ("and",)]):
             fg = ctx.filter_scan(got, 1, boff, p, [2, 0, 1])
