@@ -662,6 +662,32 @@ bool hs_pack_key_tuples(hs_ctx* ctx, const KeySpec& a, int64_t na, const KeySpec
   return true;
 }
 
+// (bucket, first left row, rows) of every tile from the left bucket offsets and the tiles before each bucket
+__global__ void __launch_bounds__(256) k_join_make_tiles(const uint32_t* __restrict__ loff, const uint32_t* __restrict__ first_tile,
+                                                         int nb, uint32_t ntiles, uint32_t* __restrict__ tb,
+                                                         uint32_t* __restrict__ ts, uint32_t* __restrict__ tl) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= ntiles) return;
+  int lo = 0, hi = nb;   // last bucket whose first tile is <= t (buckets without rows share their successor's)
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (first_tile[mid] <= t) lo = mid; else hi = mid;
+  }
+  const uint32_t a = loff[lo] + (t - first_tile[lo]) * JT, e = loff[lo + 1];
+  tb[t] = (uint32_t)lo;
+  ts[t] = a;
+  tl[t] = e - a < JT ? e - a : JT;
+}
+// output offset of every bucket = output offset of its first tile (m for buckets after the last tile)
+__global__ void __launch_bounds__(256) k_join_bucket_offsets(const uint32_t* __restrict__ tile_off, const uint32_t* __restrict__ first_tile,
+                                                             int nb, uint32_t ntiles, const unsigned long long* last_state,
+                                                             uint32_t* __restrict__ out) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b > nb) return;
+  const uint32_t m = (uint32_t)(*last_state & ((1ull << 62) - 1));
+  out[b] = first_tile[b] < ntiles ? tile_off[first_tile[b]] : m;
+}
+
 extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, const hs_index_view* right,
                                     int32_t join_type, const int32_t* left_out, int32_t n_left_out,
                                     const int32_t* right_out, int32_t n_right_out, hs_table** out) {
@@ -748,22 +774,22 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
     if (!packed) fast_join = false;
   }
   if (fast_join) {
-    std::vector<uint32_t> tb, ts, tl, first_tile((size_t)nb + 1);
+    // tiles of JT left rows that never cross a bucket: the host only counts them per bucket, a small kernel
+    // writes the (bucket, first row, rows) of every tile
+    std::vector<uint32_t> first_tile((size_t)nb + 1);
+    uint32_t ntiles = 0;
     for (int b = 0; b < nb; b++) {
-      first_tile[b] = (uint32_t)tb.size();
-      for (int64_t a = lboff[b]; a < lboff[b + 1]; a += JT) {
-        tb.push_back((uint32_t)b);
-        ts.push_back((uint32_t)a);
-        tl.push_back((uint32_t)std::min<int64_t>(JT, lboff[b + 1] - a));
-      }
+      first_tile[b] = ntiles;
+      ntiles += (uint32_t)((lboff[b + 1] - lboff[b] + JT - 1) / JT);
     }
-    first_tile[nb] = (uint32_t)tb.size();
-    const uint32_t ntiles = (uint32_t)tb.size();
-    DBuf d_tb(ctx, (size_t)ntiles * 4), d_ts(ctx, (size_t)ntiles * 4), d_tl(ctx, (size_t)ntiles * 4),
-        d_cnt(ctx, (size_t)ntiles * 4 + 4), d_total(ctx, 8), d_win(ctx, (size_t)ntiles * 8);
-    CK(cudaMemcpyAsync(d_tb.p, tb.data(), (size_t)ntiles * 4, cudaMemcpyHostToDevice, ctx->stream));
-    CK(cudaMemcpyAsync(d_ts.p, ts.data(), (size_t)ntiles * 4, cudaMemcpyHostToDevice, ctx->stream));
-    CK(cudaMemcpyAsync(d_tl.p, tl.data(), (size_t)ntiles * 4, cudaMemcpyHostToDevice, ctx->stream));
+    first_tile[nb] = ntiles;
+    DBuf d_tb(ctx, (size_t)ntiles * 4 + 4), d_ts(ctx, (size_t)ntiles * 4 + 4), d_tl(ctx, (size_t)ntiles * 4 + 4),
+        d_cnt(ctx, (size_t)ntiles * 4 + 4), d_total(ctx, 8), d_win(ctx, (size_t)ntiles * 8 + 8),
+        d_first(ctx, ((size_t)nb + 1) * 4), d_boff(ctx, ((size_t)nb + 1) * 4);
+    CK(cudaMemcpyAsync(d_first.p, first_tile.data(), ((size_t)nb + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (ntiles)
+      LAUNCH(ctx, k_join_make_tiles, (ntiles + 255) / 256, 256, 0, loff.as<uint32_t>(), d_first.as<uint32_t>(), nb, ntiles,
+             d_tb.as<uint32_t>(), d_ts.as<uint32_t>(), d_tl.as<uint32_t>());
     JoinFast jf;
     memset(&jf, 0, sizeof jf);
     jf.lkey = packed ? lpk.p : lc[0].data;
@@ -804,7 +830,7 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
       attr_done[dev & 63] = true;
     }
     uint64_t h_tot = 0;
-    std::vector<uint32_t> h_off((size_t)ntiles);
+    std::vector<uint32_t> h_off((size_t)ntiles), h_boff((size_t)nb + 1);
     // ---- single pass first: the output is sized for one match per left row (a key -> unique-key join, the
     // shape JoinIndexRule mostly produces); tiles learn their output offset from a chained scan. If the matches
     // do not fit, the pass has only counted and the two-pass path below runs instead.
@@ -840,9 +866,11 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
         Stage s(ctx, "join_fused");
         launch_windows();
         launch_tiles(2);
+        LAUNCH(ctx, k_join_bucket_offsets, (nb + 256) / 256, 256, 0, d_cnt.as<uint32_t>(), d_first.as<uint32_t>(), nb, ntiles,
+               d_state.as<unsigned long long>() + (ntiles - 1), d_boff.as<uint32_t>());
         CK(cudaMemcpyAsync(h_misc, d_misc.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
         CK(cudaMemcpyAsync(&h_last, d_state.as<unsigned long long>() + (ntiles - 1), 8, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaMemcpyAsync(h_off.data(), d_cnt.p, (size_t)ntiles * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaMemcpyAsync(h_boff.data(), d_boff.p, ((size_t)nb + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
         hs_sync(ctx);
       }
       if (!h_misc[1]) {
@@ -852,7 +880,7 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
           ocols[i].data_bytes = m * hs_fixed_width(ocols[i].type);
         }
         std::vector<int64_t> ooff((size_t)nb + 1, 0);
-        for (int b = 0; b <= nb; b++) ooff[b] = first_tile[b] < ntiles ? (int64_t)h_off[first_tile[b]] : m;
+        for (int b = 0; b <= nb; b++) ooff[b] = (int64_t)h_boff[b];
         Stage s(ctx, "d2h");
         *out = hs_finish_table(ctx, ocols, m, nb, &ooff);
         return HS_OK;
