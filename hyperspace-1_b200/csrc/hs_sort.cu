@@ -476,6 +476,7 @@ struct LeafParams {
   uint8_t* wide;      // per segment: 1 = key range needs the 64-bit kernel (written by k_leaf_sort32)
   const uint32_t* count;  // device: number of segments in the list (the grid is an upper bound)
   uint32_t* n_wide;       // device: how many segments were flagged wide
+  long long* trace;       // diagnostics: 16 clock values per segment, or null
 };
 
 // Sort one segment of at most LEAF_MAX rows entirely in shared memory: LSD radix over the bits that
@@ -644,7 +645,10 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
                                            const void* const* src, void* const* dst, const KeySrc& kspec,
                                            uint32_t start, uint32_t dstart, uint32_t len, uint32_t seg_bits_,
                                            uint64_t seg_base_, bool in_place, uint64_t* ext_bar = nullptr,
-                                           uint32_t* ext_phase = nullptr) {
+                                           uint32_t* ext_phase = nullptr, long long* tr = nullptr) {
+  // tr (diagnostics, HSGPU_LEAF_TRACE): SM clock at the phase boundaries of this segment, written by thread 0
+  auto mark = [&](int i) { if (tr && threadIdx.x == 0) tr[i] = clock64(); };
+  mark(0);
   // landing areas of the column slices: two of a full tile, or — for a leaf of at most half a tile — four of
   // half a tile, so that up to four columns are requested at once, before the sort starts
   constexpr int NS = ITEMS * PT_THREADS * 2 <= PT_TILE ? 4 : 2;
@@ -700,6 +704,7 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
   const bool known = seg_bits <= L32_MAX_KEY_BITS;
   const uint64_t seg_mask = known ? ((1ull << seg_bits) - 1ull) : ~0ull;
   mbar_wait(&bar[0], ph_in & 1u);
+  mark(1);
   const unsigned char* ks = stage0 + slice_lead(src[first], esize[first], start);
   uint64_t key[ITEMS];
   uint32_t vmask = 0;
@@ -770,6 +775,7 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
     for (int k = 0; k < ITEMS; k++)
       if ((vmask >> k) & 1u) sdata[pos[k]] = word[k];
     __syncthreads();
+    mark(2);
     // ---- pass B: the remaining high bits, stable
     const int bb = nbits - ba;
     if (bb > 0) {
@@ -790,6 +796,7 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
       __syncthreads();
     }
   }
+  mark(3);
   // ---- prefix ties: rows whose dropped low bits differ may be out of order inside a run of equal prefixes.
   // Every row of such a run ranks itself inside the run by the full key (the key slice is still staged).
   // Runs are short for keys that are not clustered; a run longer than 64 rows sends the segment to the
@@ -857,6 +864,7 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
       case 2: leaf_permute_column<uint16_t, ITEMS>(stage, lead, (uint16_t*)dst[c], dstart, len, sdata); break;
       default: leaf_permute_column<uint8_t, ITEMS>(stage, lead, (uint8_t*)dst[c], dstart, len, sdata); break;
     }
+    mark(4 + (i < 3 ? i : 3));
     if (i + NS < ncols) {
       __syncthreads();  // the slot is free again
       if (threadIdx.x == 0) {
@@ -866,6 +874,7 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
     }
   }
   __syncthreads();
+  mark(8);
   if (ext_phase) *ext_phase = phase_after(ncols);
   return 0;
 }
@@ -876,11 +885,13 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort32(const __grid_cons
   const uint32_t s = blockIdx.x;
   if (s >= *p.count) return;
   const uint32_t start = p.segs.start[s], len = p.segs.len[s];
+  long long* tr = p.trace ? p.trace + 16 * (size_t)s : nullptr;
+  if (tr && threadIdx.x == 0) { tr[9] = len; uint32_t sm; asm volatile("mov.u32 %0, %%smid;" : "=r"(sm)); tr[10] = sm; }
   const int r = len <= 4 * PT_THREADS
       ? leaf32_body<KMODE, 4>(smem_raw, p.mv.esize, p.mv.n, p.mv.src, p.mv.dst, p.key, start, start, len,
-                              p.segs.shift[s], p.segs.base[s], p.in_place != 0)
+                              p.segs.shift[s], p.segs.base[s], p.in_place != 0, nullptr, nullptr, tr)
       : leaf32_body<KMODE, PT_ITEMS>(smem_raw, p.mv.esize, p.mv.n, p.mv.src, p.mv.dst, p.key, start, start, len,
-                                     p.segs.shift[s], p.segs.base[s], p.in_place != 0);
+                                     p.segs.shift[s], p.segs.base[s], p.in_place != 0, nullptr, nullptr, tr);
   if (threadIdx.x == 0) {
     p.wide[s] = r ? 1 : 0;
     if (r) atomicAdd(p.n_wide, 1u);
@@ -1201,9 +1212,23 @@ static void run_leaf_and_copy(hs_ctx* c, MoveSet& ms, const KeySrc& key, int src
     ll.wide.alloc(c, max_leaf);
     lp.wide = ll.wide.as<uint8_t>();
     Stage st(c, "leaf_sort");
+    const char* trace_path = getenv("HSGPU_LEAF_TRACE");   // diagnostics: per-segment phase clocks of this launch
+    DBuf d_trace;
+    if (trace_path && *trace_path) {
+      d_trace.alloc(c, (size_t)max_leaf * 16 * 8);
+      d_trace.zero();
+      lp.trace = d_trace.as<long long>();
+    }
     if (key.mode == KS_U64) LAUNCH(c, k_leaf_sort32<KS_U64>, max_leaf, PT_THREADS, leaf32_smem_bytes(), lp);
     else if (key.mode == KS_I64) LAUNCH(c, k_leaf_sort32<KS_I64>, max_leaf, PT_THREADS, leaf32_smem_bytes(), lp);
     else LAUNCH(c, k_leaf_sort32<KS_I32>, max_leaf, PT_THREADS, leaf32_smem_bytes(), lp);
+    if (lp.trace) {
+      std::vector<long long> h((size_t)max_leaf * 16);
+      CK(cudaMemcpyAsync(h.data(), lp.trace, h.size() * 8, cudaMemcpyDeviceToHost, c->stream));
+      hs_sync(c);
+      if (FILE* f = fopen(trace_path, "wb")) { fwrite(h.data(), 8, h.size(), f); fclose(f); }
+      lp.trace = nullptr;
+    }
   }
   if (max_copy && src_code != BUF_A) {
     MoveArgs mv = make_move(ms, src_code, BUF_A);
