@@ -1,9 +1,10 @@
 """Host link bandwidth as the end-to-end leg sees it: pinned H2D, pinned D2H, and both at once — on one GPU, or
 on every GPU of the box at the same time (launch with torch.distributed.run: one process per GPU, LOCAL_RANK),
-optionally with the process and its pinned buffers bound to the GPU's NUMA node (--numa).
+optionally with the process and its pinned buffers bound to the GPU's NUMA node (PCIE_BIND_NUMA=1 in the
+environment; torch.distributed.run swallows unknown flags).
 
     python tools/microbench/pcie.py
-    python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 tools/microbench/pcie.py [--numa]
+    python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 tools/microbench/pcie.py
 """
 import os
 import sys
@@ -13,7 +14,7 @@ import torch
 
 local = int(os.environ.get("LOCAL_RANK", "0"))
 world = int(os.environ.get("WORLD_SIZE", "1"))
-numa = "--numa" in sys.argv
+numa = os.environ.get("PCIE_BIND_NUMA", "") == "1"
 node = None
 if numa:
     # the GPU's NUMA node from sysfs; bind this process's CPUs to it BEFORE the pinned buffers are allocated
