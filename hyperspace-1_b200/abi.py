@@ -57,6 +57,11 @@ class hs_predicate(C.Structure):
     _fields_ = [("nterms", C.c_int32), ("reserved", C.c_int32), ("terms", C.POINTER(hs_pred_term))]
 
 
+class hs_parquet_page(C.Structure):
+    _fields_ = [("offset", C.c_int64), ("size", C.c_int64), ("uncompressed_size", C.c_int64), ("num_values", C.c_int64),
+                ("kind", C.c_int32), ("encoding", C.c_int32), ("chunk", C.c_int32), ("reserved", C.c_int32)]
+
+
 class hs_stage_timing(C.Structure):
     _fields_ = [("name", C.c_char * 32), ("ms", C.c_float), ("launches", C.c_int32)]
 

@@ -17,7 +17,7 @@ EXPORTS = [
     "hs_ctx_create", "hs_ctx_destroy", "hs_last_error", "hs_ctx_set_output_location", "hs_ctx_get_stream",
     "hs_ctx_enable_timing", "hs_ctx_last_timings", "hs_ctx_launch_count", "hs_table_free", "hs_version",
     "hs_ctx_set_deferred_results", "hs_table_wait", "hs_ctx_trim",
-    "hs_parquet_plain_pages",
+    "hs_parquet_plain_pages", "hs_parquet_decode_pages",
     "hs_hash_bucket", "hs_hash_rows", "hs_build_index", "hs_merge_runs", "hs_join_bucketed", "hs_filter_scan",
     "hs_bucket_histogram_noalloc", "hs_comm_unique_id", "hs_comm_init", "hs_comm_destroy", "hs_build_index_dist", "hs_comm_last_exchange",
 ]
@@ -273,6 +273,30 @@ class Context:
         try:
             bodies, nulls = t.to_arrow()
             return [b.as_py() for b in bodies], nulls.to_numpy()
+        finally:
+            t.free()
+
+    def parquet_decode_table(self, blob, pages, hs_type, optional, codec):
+        """hs_parquet_decode_pages: `blob` = numpy uint8 array with the page bodies as stored in the files, `pages`
+        = [(offset, size, uncompressed size, num_values, kind, encoding, chunk)] in row order -> Table of one column."""
+        arr = (abi.hs_parquet_page * max(len(pages), 1))()
+        for i, (off, size, usize, nvals, kind, enc, chunk) in enumerate(pages):
+            a = arr[i]
+            a.offset, a.size, a.uncompressed_size, a.num_values = int(off), int(size), int(usize), int(nvals)
+            a.kind, a.encoding, a.chunk = int(kind), int(enc), int(chunk)
+        blob = np.ascontiguousarray(blob, dtype=np.uint8)
+        out = C.POINTER(abi.hs_table)()
+        self._check(self._lib.hs_parquet_decode_pages(self._h, C.c_void_p(blob.ctypes.data if blob.size else None),
+                                                      C.c_int64(blob.size), arr, C.c_int32(len(pages)), C.c_int32(hs_type),
+                                                      C.c_int32(1 if optional else 0), C.c_int32(codec), C.byref(out)),
+                    "hs_parquet_decode_pages")
+        return Table(self, out)
+
+    def parquet_decode_pages(self, blob, pages, hs_type, optional, codec, arrow_type=None):
+        """The same, as one host Arrow array."""
+        t = self.parquet_decode_table(blob, pages, hs_type, optional, codec)
+        try:
+            return t.to_arrow([arrow_type] if arrow_type is not None else None)[0]
         finally:
             t.free()
 

@@ -270,6 +270,29 @@ int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left,
 int32_t hs_parquet_plain_pages(hs_ctx* ctx, const hs_column* col, int32_t optional,
                                const int64_t* page_rows, int32_t npages, hs_table** out);
 
+/* ---- K5: Parquet pages decoded on the device ---------------------------------
+ * The read side of the same files: what Spark's ParquetFileFormat reader does under the bucketed scan the rules
+ * plan (HS/index/rules/RuleUtils.scala:280-286). One call decodes ONE column over all the pages handed in (any
+ * number of files / column chunks, in row order) into one column: codec UNCOMPRESSED (0) or SNAPPY (1); data
+ * pages v1 of flat columns (definition levels: RLE/bit-packed hybrid, bit width 1, only when `optional`); values
+ * PLAIN or dictionary-encoded (PLAIN_DICTIONARY 2 / RLE_DICTIONARY 8, with the chunk's PLAIN dictionary page
+ * among the pages). `bytes` (host or device) holds the page bodies as they sit in the files, framing excluded;
+ * the host parses footers and page headers (hyperspace-1_b200/parquet_read.py). `type`: the hs_type wanted
+ * (HS_INT8 / HS_INT16 are narrowed from Parquet's INT32). Other codecs, encodings and page kinds return
+ * HS_EUNSUPPORTED. */
+typedef struct hs_parquet_page {
+  int64_t offset;             /* of the page body inside `bytes` */
+  int64_t size;               /* bytes of the body as stored (compressed when codec != 0) */
+  int64_t uncompressed_size;
+  int64_t num_values;         /* rows of a data page (NULLs included); entries of a dictionary page */
+  int32_t kind;               /* 0 data page (v1), 2 dictionary page */
+  int32_t encoding;           /* of the values: 0 PLAIN, 2 PLAIN_DICTIONARY, 8 RLE_DICTIONARY */
+  int32_t chunk;              /* column chunk the page belongs to: the scope of its dictionary */
+  int32_t reserved;
+} hs_parquet_page;
+int32_t hs_parquet_decode_pages(hs_ctx* ctx, const uint8_t* bytes, int64_t nbytes, const hs_parquet_page* pages,
+                                int32_t npages, int32_t type, int32_t optional, int32_t codec, hs_table** out);
+
 /* ---- K7: filtered index scan -----------------------------------------------
  * Executes the plan FilterIndexRule.apply produces (HS/index/rules/FilterIndexRule.scala:43-85,
  * useBucketSpec = false at :59-65): rows of the index for which the predicate is TRUE,
