@@ -31,7 +31,7 @@ def _table(n, seed, with_nulls=True):
         "f32": pa.array(rng.standard_normal(n).astype(np.float32)),
         "f64": pa.array(rng.standard_normal(n), mask=m(0.2)),
         "b": pa.array(rng.random(n) < 0.3, mask=m(0.1)),
-        "s": pa.array([words[int(i)] + str(int(j)) for i, j in zip(rng.integers(0, len(words), n), rng.integers(0, 50, n))], mask=m(0.1)),
+        "s": pa.array([words[int(i)] + str(int(j)) for i, j in zip(rng.integers(0, len(words), n), rng.integers(0, 50, n))], type=pa.string(), mask=m(0.1)),
         "bin": pa.array([bytes(rng.integers(0, 256, size=int(k), dtype=np.uint8)) for k in rng.integers(0, 20, n)], type=pa.binary()),
         "d": pa.array(rng.integers(0, 20000, size=n).astype(np.int32), type=pa.date32()),
         "allnull": pa.array([None] * n, type=pa.int64()),
