@@ -227,7 +227,7 @@ class RefreshAction(_CreateBase):
                                          self.out_dir, lineage_ids)
             return
         if self.deleted:
-            runs, names, _ = index_writer.read_index(self.prev)
+            runs, names, _ = index_writer.read_index(self.prev, session=self.session)
             ids = [f["id"] for f in self.deleted_infos]
             for arrays, boff in runs:
                 kept, koff = drop_deleted_rows(self.session, arrays, len(self.indexed), boff, names, ids)
@@ -298,7 +298,7 @@ class OptimizeAction(_CreateBase):
     def op(self):
         props = self.prev["derivedDataset"]["properties"]
         indexed = list(props["columns"]["indexed"])
-        runs, names, _ = index_writer.read_index(self.prev, files=self.to_optimize)
+        runs, names, _ = index_writer.read_index(self.prev, files=self.to_optimize, session=self.session)
         arrays, boff = self.session.ctx.merge_runs([(a, len(indexed), off) for a, off in runs])
         self.new_files, _ = index_writer.write_index_files(self.session, arrays, names, boff, self.out_dir)
 

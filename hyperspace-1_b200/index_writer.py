@@ -69,10 +69,13 @@ def build_and_write(session, table, indexed, included, num_buckets, out_dir):
                    "gpu_stages": session.ctx.last_timings()}
 
 
-def read_index(entry, columns=None, files=None):
+def read_index(entry, columns=None, files=None, session=None):
     """Read the files of an index entry grouped by bucket. Returns (runs, names) where every run is
     (arrays, bucket_offsets): run k holds the k-th file of every bucket, so an index with one file per bucket
-    is one run and an incrementally refreshed index is several."""
+    is one run and an incrementally refreshed index is several.
+    With a session, the pages are decoded on the device (hsgpu.index.fileReader = "gpu", the default there:
+    parquet_read.decode_files — the host only parses footers and page headers); files the device reader does not
+    cover (other codecs, data pages v2) and hsgpu.index.fileReader = "pyarrow" go through pyarrow."""
     props = entry["derivedDataset"]["properties"]
     nb = props["numBuckets"]
     names = index_column_names(entry)
@@ -83,20 +86,34 @@ def read_index(entry, columns=None, files=None):
         b = le.bucket_id_of(fi["name"])
         per_bucket.setdefault(b, []).append(le.from_uri(fi["name"]))
     nruns = max((len(v) for v in per_bucket.values()), default=0)
+    use_gpu = session is not None and session.conf.get("hsgpu.index.fileReader", "gpu") == "gpu"
     runs = []
     t0 = time.perf_counter()
     for k in range(max(nruns, 1)):
-        pieces, off = [], [0]
+        flist, fbucket = [], []
         for b in range(nb):
             fl = per_bucket.get(b, [])
             if k < len(fl):
-                t = pq.ParquetFile(fl[k]).read(columns=want)
-                pieces.append(t)
-                off.append(off[-1] + t.num_rows)
-            else:
-                off.append(off[-1])
-        if not pieces:
+                flist.append(fl[k])
+                fbucket.append(b)
+        if not flist:
             continue
-        t = pa.concat_tables(pieces)
-        runs.append(([t[c].combine_chunks() for c in want], np.asarray(off, dtype=np.int64)))
+        arrays = None
+        if use_gpu:
+            from . import parquet_read
+            from .native import HyperspaceException
+            try:
+                got, gnames, rows = parquet_read.decode_files(session.ctx, flist, want)
+                arrays = [got[gnames.index(c)] for c in want]
+            except HyperspaceException:
+                arrays = None      # not covered by the device reader: the host library reads the files
+        if arrays is None:
+            tables = [pq.ParquetFile(f).read(columns=want) for f in flist]
+            rows = [t.num_rows for t in tables]
+            t = pa.concat_tables(tables)
+            arrays = [t[c].combine_chunks() for c in want]
+        off = np.zeros(nb + 1, dtype=np.int64)
+        for b, r in zip(fbucket, rows):
+            off[b + 1] = r
+        runs.append((arrays, np.cumsum(off)))
     return runs, want, time.perf_counter() - t0

@@ -247,7 +247,7 @@ def _single_run(session, entry, columns=None, hybrid=None):
     from .hyperspace import drop_deleted_rows
     from .index_writer import LINEAGE_COL, read_index
     indexed, included = _index_columns(entry)
-    runs, names, _ = read_index(entry)
+    runs, names, _ = read_index(entry, session=session)
     nb = entry["derivedDataset"]["properties"]["numBuckets"]
     nk = len(indexed)
     hybrid = hybrid or {}

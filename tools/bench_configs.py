@@ -207,8 +207,15 @@ def run_parquet(args):
             rows = sum(pq.ParquetFile(f).read().num_rows for f in files)
             rd = time.perf_counter() - t0
             assert rows == n
+            # the same files decoded on the device (hs_parquet_decode_pages; host parses the framing only)
+            from hyperspace_1_b200 import parquet_read
+            parquet_read.decode_files(ctx, sorted(files))   # warm
+            t0 = time.perf_counter()
+            got, _, rws = parquet_read.decode_files(ctx, sorted(files))
+            gd = time.perf_counter() - t0
+            assert sum(rws) == n and len(got[0]) == n
             out[name] = {"write_s": best, "rows_per_s": n / best, "file_bytes": size, "files": len(files),
-                         "pyarrow_read_back_s": rd}
+                         "pyarrow_read_back_s": rd, "device_decode_read_back_s": gd}
     finally:
         shutil.rmtree(root, ignore_errors=True)
     print(json.dumps(out), flush=True)
