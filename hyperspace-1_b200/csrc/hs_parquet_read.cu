@@ -4,7 +4,7 @@
 // The host parses the few hundred bytes of framing per file (footer, Thrift page headers: parquet_read.py) and
 // hands over the raw bytes of the column chunks with one descriptor per page; everything that touches a value
 // happens here, for the encodings Spark 2.4 / parquet-mr 1.10 and pyarrow write into index files:
-//   * codecs UNCOMPRESSED and SNAPPY (one thread decompresses one page; pages run side by side);
+//   * codecs UNCOMPRESSED and SNAPPY (one warp decompresses one page; pages run side by side);
 //   * data pages v1 with definition levels as RLE/bit-packed hybrid of bit width 1 (flat OPTIONAL columns);
 //   * values PLAIN or dictionary-encoded (PLAIN_DICTIONARY / RLE_DICTIONARY: a PLAIN dictionary page per column
 //     chunk, then hybrid runs of indices), for BOOLEAN, INT32, INT64, FLOAT, DOUBLE and BYTE_ARRAY.
@@ -29,19 +29,23 @@ struct PqPageD {              // device view of one page after decompression
   uint64_t row0;              // data pages: first row of the page in the output column
 };
 
-// ---- snappy: varint length, then literals (tag & 3 == 0) and copies with 1-, 2- or 4-byte offsets
+// ---- snappy: varint length, then literals (tag & 3 == 0) and copies with 1-, 2- or 4-byte offsets.
+// One warp per page: every lane walks the element stream (the same bytes, uniform control flow), the bytes of each
+// element are copied by the 32 lanes together. A copy that overlaps its own output (offset < length: a repeated
+// pattern) reads c[i % offset], which is final before the element starts.
 __global__ void __launch_bounds__(32) k_pq_snappy(const uint8_t* __restrict__ in, const uint64_t* __restrict__ in_off,
                                                   const uint32_t* __restrict__ in_size, uint8_t* __restrict__ out,
                                                   const uint64_t* __restrict__ out_off, const uint32_t* __restrict__ out_size,
                                                   int npages, uint32_t* __restrict__ bad) {
-  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  const int p = blockIdx.x;
   if (p >= npages) return;
+  const uint32_t lane = threadIdx.x;
   const uint8_t* s = in + in_off[p];
   const uint8_t* const se = s + in_size[p];
   uint8_t* d = out + out_off[p];
   uint8_t* const d0 = d;
   uint8_t* const de = d + out_size[p];
-  // preamble: uncompressed length (varint)
+  auto fail = [&]() { if (lane == 0) atomicAdd(bad, 1u); };
   uint64_t ulen = 0;
   int sh = 0;
   while (s < se) {
@@ -50,7 +54,7 @@ __global__ void __launch_bounds__(32) k_pq_snappy(const uint8_t* __restrict__ in
     sh += 7;
     if (!(b & 0x80)) break;
   }
-  if (ulen != out_size[p]) { atomicAdd(bad, 1u); return; }
+  if (ulen != out_size[p]) { fail(); return; }
   while (s < se && d < de) {
     const uint8_t tag = *s++;
     uint32_t len, off = 0;
@@ -63,10 +67,11 @@ __global__ void __launch_bounds__(32) k_pq_snappy(const uint8_t* __restrict__ in
           for (int i = 0; i < nb && s < se; i++) len |= (uint32_t)(*s++) << (8 * i);
           len += 1;
         }
-        if (s + len > se || d + len > de) { atomicAdd(bad, 1u); return; }
-        for (uint32_t i = 0; i < len; i++) d[i] = s[i];
+        if (s + len > se || d + len > de) { fail(); return; }
+        for (uint32_t i = lane; i < len; i += 32) d[i] = s[i];
         s += len;
         d += len;
+        __syncwarp();
         continue;
       }
       case 1:
@@ -84,12 +89,14 @@ __global__ void __launch_bounds__(32) k_pq_snappy(const uint8_t* __restrict__ in
         s += 4;
         break;
     }
-    if (off == 0 || (uint64_t)(d - d0) < off || d + len > de) { atomicAdd(bad, 1u); return; }
+    if (off == 0 || (uint64_t)(d - d0) < off || d + len > de) { fail(); return; }
     const uint8_t* c = d - off;
-    for (uint32_t i = 0; i < len; i++) d[i] = c[i];   // byte by byte: the ranges may overlap (run-length copies)
+    if (off >= len) { for (uint32_t i = lane; i < len; i += 32) d[i] = c[i]; }
+    else { for (uint32_t i = lane; i < len; i += 32) d[i] = c[i % off]; }
     d += len;
+    __syncwarp();
   }
-  if (d != de) atomicAdd(bad, 1u);
+  if (d != de) fail();
 }
 
 // ---- RLE / bit-packed hybrid, read by one warp: calls emit(first index, count, is_rle, value, packed bytes, bit
@@ -385,8 +392,8 @@ extern "C" int32_t hs_parquet_decode_pages(hs_ctx* ctx, const uint8_t* bytes, in
     DBuf sizes(ctx, (size_t)np * 8);
     CK(cudaMemcpyAsync(sizes.p, in_size.data(), (size_t)np * 4, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(sizes.as<uint32_t>() + np, out_size.data(), (size_t)np * 4, cudaMemcpyHostToDevice, ctx->stream));
-    // one thread per page, one page per warp-sized block: a thread walking its page must not wait for its neighbours
-    LAUNCH(ctx, k_pq_snappy, np, 1, 0, d_bytes, a, sizes.as<uint32_t>(), d_un.as<uint8_t>(), a + np, sizes.as<uint32_t>() + np, np,
+    // one warp per page
+    LAUNCH(ctx, k_pq_snappy, np, 32, 0, d_bytes, a, sizes.as<uint32_t>(), d_un.as<uint8_t>(), a + np, sizes.as<uint32_t>() + np, np,
            bad.as<uint32_t>());
     uint32_t h_bad = 0;
     CK(cudaMemcpyAsync(&h_bad, bad.p, 4, cudaMemcpyDeviceToHost, ctx->stream));

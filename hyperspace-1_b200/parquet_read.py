@@ -129,32 +129,45 @@ def decode_files(ctx, files, columns=None):
     schema = metas[0].schema_arrow
     names = [n for n in schema.names if columns is None or n in columns]
     rows_per_file = [m.metadata.num_rows for m in metas]
-    bufs = [np.fromfile(f, dtype=np.uint8) for f in files]
+    handles = [open(f, "rb", buffering=0) for f in files]
     arrays = []
-    for name in names:
-        field = schema.field(name)
-        ci = schema.get_field_index(name)
-        parts, pages, at, chunk, codec = [], [], 0, 0, None
-        for m, buf in zip(metas, bufs):
-            md = m.metadata
-            for rg in range(md.num_row_groups):
-                col = md.row_group(rg).column(ci)
-                c = CODECS.get(col.compression)
-                if c is None:
-                    raise abi_unsupported(f"{col.compression} pages")
-                if codec is not None and c != codec:
-                    raise abi_unsupported("files with different codecs in one call")
-                codec = c
-                start = col.dictionary_page_offset if col.has_dictionary_page and col.dictionary_page_offset else col.data_page_offset
-                start = min(start, col.data_page_offset)
-                for kind, body, csize, usize, nvals, enc in chunk_pages(buf, start, col.total_compressed_size, col.num_values):
-                    pages.append((at, csize, usize, nvals, kind, enc, chunk))
-                    parts.append(buf[body:body + csize])
-                    at += csize
-                chunk += 1
-        blob = np.concatenate(parts) if parts else np.zeros(0, dtype=np.uint8)
-        optional = True   # Spark and pyarrow write every column of an index file as OPTIONAL
-        if metas[0].schema.column(ci).max_definition_level == 0:
-            optional = False
-        arrays.append(ctx.parquet_decode_pages(blob, pages, _hs_type(field.type), optional, codec or 0, field.type))
+    try:
+        for name in names:
+            field = schema.field(name)
+            ci = schema.get_field_index(name)
+            # the column's chunks of all files, read straight into one buffer (page headers stay in between the
+            # bodies; the page descriptors point past them)
+            chunks, total, codec = [], 0, None
+            for fi, m in enumerate(metas):
+                md = m.metadata
+                for rg in range(md.num_row_groups):
+                    col = md.row_group(rg).column(ci)
+                    c = CODECS.get(col.compression)
+                    if c is None:
+                        raise abi_unsupported(f"{col.compression} pages")
+                    if codec is not None and c != codec:
+                        raise abi_unsupported("files with different codecs in one call")
+                    codec = c
+                    start = col.data_page_offset
+                    if col.has_dictionary_page and col.dictionary_page_offset:
+                        start = min(start, col.dictionary_page_offset)
+                    chunks.append((fi, start, col.total_compressed_size, col.num_values))
+                    total += col.total_compressed_size
+            blob = np.empty(total, dtype=np.uint8)
+            view = memoryview(blob)
+            pages, at = [], 0
+            for chunk, (fi, start, size, nvals) in enumerate(chunks):
+                h = handles[fi]
+                h.seek(start)
+                got = h.readinto(view[at:at + size])
+                if got != size:
+                    raise IOError(f"{files[fi]}: short read of a column chunk")
+                for kind, body, csize, usize, nv, enc in chunk_pages(blob, at, size, nvals):
+                    pages.append((body, csize, usize, nv, kind, enc, chunk))
+                at += size
+            optional = metas[0].schema.column(ci).max_definition_level > 0
+            arrays.append(ctx.parquet_decode_pages(blob, pages, _hs_type(field.type), optional, codec or 0, field.type))
+    finally:
+        for h in handles:
+            h.close()
     return arrays, names, rows_per_file
