@@ -36,8 +36,27 @@ __global__ void k(const uint32_t* in, uint32_t* out, int iters) {
       if (r == 0) my[d] = pre + __popc(m);
       __syncwarp();
       acc += pre + r;
-    } else {
+    } else if (MODE == 2) {
       acc += atomicAdd(&cnt[d], 1u);
+    } else if (MODE == 3) {
+      atomicAdd(&cnt[d], 1u);          // result unused: a reduction, no value comes back
+    } else {
+      // MODE 4: two 4-bit ballot passes with the per-digit counts kept in registers (no shared-memory counters):
+      // what a tile ranking by ballots alone would issue per row for an 8-bit digit
+      uint32_t r = 0;
+#pragma unroll
+      for (int half = 0; half < 2; half++) {
+        const uint32_t dd = (d >> (4 * half)) & 15u;
+        uint32_t m = 0xffffffffu;
+#pragma unroll
+        for (int b = 0; b < 4; b++) {
+          const bool bit = (dd >> b) & 1;
+          const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+          m &= bit ? bal : ~bal;
+        }
+        r += __popc(m & lt);
+      }
+      acc += r;
     }
   }
   out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
@@ -65,6 +84,9 @@ int main() {
   run<1, 10>("match_any 10 bits", in, out);
   run<2, 8>("smem atomicAdd 256 bins", in, out);
   run<2, 10>("smem atomicAdd 1024 bins", in, out);
+  run<3, 8>("smem atomicAdd, no return, 256", in, out);
+  run<3, 10>("smem atomicAdd, no return, 1024", in, out);
+  run<4, 8>("2 x 4-bit ballots, registers", in, out);
   printf("%s\n", cudaGetErrorString(cudaGetLastError()));
   return 0;
 }
