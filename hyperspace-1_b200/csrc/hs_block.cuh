@@ -3,11 +3,15 @@
 #pragma once
 #include "hs_common.cuh"
 
+// Threads and rows of a tile. -DPT_THREADS=256 builds the 2048-row-tile variant (4 CTAs per SM) for experiments.
+#ifndef PT_THREADS
 #define PT_THREADS 512
-#define PT_WARPS 16
+#endif
+#define PT_WARPS (PT_THREADS / 32)
 #define PT_ITEMS 8
 #define PT_TILE (PT_THREADS * PT_ITEMS)  // 4096 rows per tile
 #define PT_SCRATCH 32                    // words of scan scratch (>= PT_WARPS + 1)
+#define PT_MIN_CTAS (1024 / PT_THREADS)  // resident CTAs per SM the kernels are compiled for (64 registers per thread)
 
 __device__ __forceinline__ uint32_t warp_incl_scan_u32(uint32_t v) {
 #pragma unroll
@@ -36,20 +40,22 @@ __device__ __forceinline__ uint32_t block_excl_scan_u32(uint32_t v, uint32_t* sc
   return inc - v + scratch[w];
 }
 
-// the same scan for a CTA of exactly 256 threads (k_msd_plan: one thread per digit)
-__device__ __forceinline__ uint32_t block256_excl_scan_u32(uint32_t v, uint32_t* scratch) {
+// the same scan for a CTA of any size up to 1024 threads whose first `nthreads` threads carry a value
+// (k_msd_plan: one thread per digit); scratch: 32 words
+__device__ __forceinline__ uint32_t block256_excl_scan_u32(uint32_t v, uint32_t* scratch, int nthreads = 256) {
   uint32_t inc = warp_incl_scan_u32(v);
   int w = threadIdx.x >> 5;
+  const int nw = (nthreads + 31) >> 5;
   __syncthreads();
-  if (lane_id() == 31) scratch[w] = inc;
+  if (lane_id() == 31 && w < 32) scratch[w] = inc;
   __syncthreads();
   if (w == 0) {
-    uint32_t s = lane_id() < 8 ? scratch[lane_id()] : 0;
+    uint32_t s = (int)lane_id() < nw ? scratch[lane_id()] : 0;
     uint32_t si = warp_incl_scan_u32(s);
-    if (lane_id() < 8) scratch[lane_id()] = si - s;
+    if ((int)lane_id() < nw) scratch[lane_id()] = si - s;
   }
   __syncthreads();
-  return inc - v + scratch[w];
+  return inc - v + (w < nw ? scratch[w] : 0);
 }
 
 // Stable ranking of a tile by digit. Item k of lane l in warp w is tile element

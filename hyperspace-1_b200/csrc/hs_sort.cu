@@ -15,9 +15,11 @@
 #include "hs_tma.cuh"
 
 #define LEAF_MAX PT_TILE
+#ifndef MSD_BITS
 #define MSD_BITS 8
-#define MSD_RADIX 256
-#define MSD_TARGET_ROWS 3300   // aimed-at child size of an MSD level (a leaf holds at most 4096 rows)
+#endif
+#define MSD_RADIX (1 << MSD_BITS)
+#define MSD_TARGET_ROWS (3300 * PT_TILE / 4096)   // aimed-at child size of an MSD level (a leaf holds at most PT_TILE rows)
 
 // Digit width of the MSD level that splits a segment of `len` rows whose keys still differ in their low
 // `r` bits: as many bits (at most 8) as keep the expected child, len / 2^bits, near MSD_TARGET_ROWS. A huge
@@ -291,7 +293,7 @@ __device__ __forceinline__ void partition_tile(const PartParams& p, unsigned cha
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_constant__ PartParams p) {
+__global__ void __launch_bounds__(PT_THREADS, 2 * PT_MIN_CTAS / 2) k_partition(const __grid_constant__ PartParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   uint32_t tile_start, tile_len, shift = 0;
   uint64_t seg_base = 0;
@@ -321,7 +323,7 @@ __global__ void __launch_bounds__(PT_THREADS, 2) k_partition(const __grid_consta
 __device__ __forceinline__ void msd_hist_tile(const MoveArgs& mv, const KeySrc& key, uint32_t tile_start,
                                               uint32_t tile_len, uint64_t seg_base, uint32_t shift, int bits,
                                               uint32_t* hist /* shared, MSD_RADIX */, uint32_t* cursor) {
-  if (threadIdx.x < MSD_RADIX) hist[threadIdx.x] = 0;
+  for (int i = threadIdx.x; i < MSD_RADIX; i += PT_THREADS) hist[i] = 0;
   __syncthreads();
   // all keys of the thread first (independent loads), then the shared-memory updates
   uint64_t kk[PT_ITEMS];
@@ -336,9 +338,9 @@ __device__ __forceinline__ void msd_hist_tile(const MoveArgs& mv, const KeySrc& 
     if (j < tile_len) atomicAdd(&hist[(uint32_t)((kk[k] - seg_base) >> shift) & ((1u << bits) - 1u)], 1u);
   }
   __syncthreads();
-  if (threadIdx.x < MSD_RADIX) {
-    uint32_t v = hist[threadIdx.x];
-    if (v) atomicAdd(&cursor[threadIdx.x], v);
+  for (int i = threadIdx.x; i < MSD_RADIX; i += PT_THREADS) {
+    uint32_t v = hist[i];
+    if (v) atomicAdd(&cursor[i], v);
   }
 }
 
@@ -383,10 +385,10 @@ __device__ __forceinline__ void classify_push(const PlanOut& o, uint32_t start, 
 
 // turn the histograms of one level into write cursors and child segments
 __global__ void __launch_bounds__(MSD_RADIX) k_msd_plan(SegList segs, uint32_t* cursor, PlanOut out) {
-  __shared__ uint32_t scratch[16];
+  __shared__ uint32_t scratch[32];
   uint32_t s = blockIdx.x;
   uint32_t h = cursor[(size_t)s * MSD_RADIX + threadIdx.x];
-  uint32_t ex = block256_excl_scan_u32(h, scratch);
+  uint32_t ex = block256_excl_scan_u32(h, scratch, MSD_RADIX);
   uint32_t start = segs.start[s] + ex;
   cursor[(size_t)s * MSD_RADIX + threadIdx.x] = start;
   uint32_t sh = segs.shift[s];
@@ -583,7 +585,7 @@ __device__ __forceinline__ void leaf64_body(unsigned char* smem_raw, const int32
   }
 }
 
-__global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort(const __grid_constant__ LeafParams p) {
+__global__ void __launch_bounds__(PT_THREADS, 2 * PT_MIN_CTAS / 2) k_leaf_sort(const __grid_constant__ LeafParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const uint32_t s = blockIdx.x;
   if (s >= *p.count) return;
@@ -880,7 +882,7 @@ __device__ __forceinline__ int leaf32_body(unsigned char* smem_raw, const int32_
 }
 
 template <int KMODE>
-__global__ void __launch_bounds__(PT_THREADS, 2) k_leaf_sort32(const __grid_constant__ LeafParams p) {
+__global__ void __launch_bounds__(PT_THREADS, 2 * PT_MIN_CTAS / 2) k_leaf_sort32(const __grid_constant__ LeafParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const uint32_t s = blockIdx.x;
   if (s >= *p.count) return;
@@ -1398,7 +1400,7 @@ __global__ void __launch_bounds__(256) k_pipe_describe(const __grid_constant__ P
 // Persistent CTAs (two per SM): each takes tickets until none is left. While an item is being worked on, one
 // lane of warp 1 already fetches the next ticket and its descriptor.
 template <int KMODE>
-__global__ void __launch_bounds__(PT_THREADS, 2) k_sort_pipeline(const __grid_constant__ PipeParams p,
+__global__ void __launch_bounds__(PT_THREADS, 2 * PT_MIN_CTAS / 2) k_sort_pipeline(const __grid_constant__ PipeParams p,
                                                                  const PipeItem* __restrict__ items,
                                                                  uint32_t bar_offset, uint32_t prefetch,
                                                                  unsigned long long* trace) {
@@ -1550,7 +1552,7 @@ static bool pipeline_enabled() {
   // off unless asked for: measured on B200 (profiles/README.md) the single launch does not beat the separate
   // kernels — co-resident scatter tiles and leaf sorts take as long as they do alone
   const char* e = getenv("HSGPU_SORT_PIPELINE");
-  return e && *e == '1';
+  return MSD_RADIX <= PT_THREADS && MSD_RADIX == 256 && e && *e == '1';
 }
 static size_t pipeline_smem_bytes() {
   size_t a = leaf32_smem_bytes(), b = leaf_smem_bytes(), t = tile_smem_bytes(MSD_RADIX);
