@@ -25,6 +25,15 @@ static void table_settle(hs_ctx* c, TableImpl* ti) {
 
 void hs_sync(hs_ctx* c) { CK(cudaStreamSynchronize(c->stream)); }
 
+int hs_sm_count() {
+  static int n[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  int& v = n[dev & 63];
+  if (!v && cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) v = 148;
+  return v;
+}
+
 int hs_read_begin(hs_ctx* c, const void* d_src, size_t bytes) {
   if (bytes > HS_READ_BYTES) HS_THROW(HS_EINVAL, "hs_read_begin: %zu bytes", bytes);
   if (!c->rd_pin) {

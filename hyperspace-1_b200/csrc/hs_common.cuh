@@ -14,7 +14,9 @@
 
 #define HS_MAX_KEYS 8
 #define HS_MAX_MOVE 40
-#define HS_NUM_SMS 148  // B200: grids are sized in multiples of this
+// SMs of the current device (148 on B200): grids are sized in multiples of this. Queried once per device.
+int hs_sm_count();
+#define HS_NUM_SMS hs_sm_count()
 
 struct HsError {
   int32_t status;

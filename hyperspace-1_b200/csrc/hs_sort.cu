@@ -1540,14 +1540,6 @@ __global__ void __launch_bounds__(PT_THREADS, 2 * PT_MIN_CTAS / 2) k_sort_pipeli
   }
 }
 
-static int hs_num_sms() {
-  static int n[64] = {0};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  int& v = n[dev & 63];
-  if (!v && cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) v = HS_NUM_SMS;
-  return v;
-}
 static bool pipeline_enabled() {
   // off unless asked for: measured on B200 (profiles/README.md) the single launch does not beat the separate
   // kernels — co-resident scatter tiles and leaf sorts take as long as they do alone
@@ -1667,7 +1659,7 @@ static void run_sort_pipeline(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key
   }
   {
     Stage stg(c, "sort_pipeline");
-    unsigned grid = 2 * (unsigned)hs_num_sms();
+    unsigned grid = 2 * (unsigned)hs_sm_count();
     if (grid > ticket) grid = ticket;
     DBuf d_items(c, ((size_t)ticket + grid) * sizeof(PipeItem));
     LAUNCH(c, k_pipe_describe, (ticket + grid + 255) / 256, 256, 0, *pp, d_items.as<PipeItem>(), (uint32_t)grid);

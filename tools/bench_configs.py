@@ -155,9 +155,68 @@ def run_cfg4(args):
     print(json.dumps(line), flush=True)
 
 
+def run_skew(args):
+    """Skewed keys — the case the reference's FAQ warns about (docs/_docs/04-ug-faqs.md:111-125: low-cardinality
+    indexed columns skew the buckets): cfg2-shaped rows whose key column is (a) uniform, (b) half the rows one hot
+    key, (c) ten distinct keys, (d) a heavy-tailed distribution. Build time and the usual index check per shape."""
+    import torch
+    from hyperspace_1_b200 import abi, native
+    from oracle import oracle as _oracle   # the checker only
+    from tools import index_check as ic
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    n, nb = args.rows or 100_000_000, 200
+    g = torch.Generator(device=dev)
+    g.manual_seed(20240606)
+    price = torch.rand(n, generator=g, device=dev, dtype=torch.float64)
+    disc = torch.rand(n, generator=g, device=dev, dtype=torch.float64)
+    uni = torch.randint(0, 1 << 40, (n,), generator=g, device=dev, dtype=torch.int64)
+    shapes = {
+        "uniform": lambda: uni,
+        "half_the_rows_one_key": lambda: torch.where(torch.rand(n, generator=g, device=dev) < 0.5, torch.full_like(uni, 77), uni),
+        "ten_distinct_keys": lambda: torch.randint(0, 10, (n,), generator=g, device=dev, dtype=torch.int64) * 1_000_003,
+        "heavy_tail": lambda: (1.0 / (torch.rand(n, generator=g, device=dev, dtype=torch.float64) + 1e-9)).to(torch.int64),
+    }
+    ctx = native.Context(0)
+    ctx.set_output_location(abi.HS_MEM_DEVICE)
+    stream = torch.cuda.ExternalStream(ctx.stream(), device=dev)
+    out = {"config": "skew", "rows": n, "num_buckets": nb}
+    for name, make in shapes.items():
+        key = make().contiguous()
+        torch.cuda.synchronize()
+        cs = abi.DeviceColumnSet([{"type": abi.HS_INT64, "length": n, "data": key.data_ptr()},
+                                  {"type": abi.HS_FLOAT64, "length": n, "data": price.data_ptr()},
+                                  {"type": abi.HS_FLOAT64, "length": n, "data": disc.data_ptr()}])
+        for _ in range(args.warmup):
+            ctx.build_index_table(cs, 1, nb).free()
+        ctx.enable_timing(True)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(args.steps):
+            t = ctx.build_index_table(cs, 1, nb)
+            stages = {nm: round(ms, 3) for nm, ms, _ in ctx.last_timings() if ms > 0.01}
+            t.free()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ctx.enable_timing(False)
+        ms = e0.elapsed_time(e1) / args.steps
+        t = ctx.build_index_table(cs, 1, nb)
+        torch.cuda.synchronize()
+        boff = t.bucket_offsets()
+        chk = ic.check_index(torch, _oracle, ic.table_tensors(torch, t, [torch.int64, torch.float64, torch.float64], dev),
+                             boff, [key, price, disc], 1, nb)
+        import numpy as np
+        out[name] = {"ms_per_build": ms, "rows_per_s": n / (ms * 1e-3), "largest_bucket_rows": int(np.diff(boff).max()),
+                     "stages_ms": stages, "check_ok": chk["ok"]}
+        t.free()
+        del key
+    print(json.dumps(out), flush=True)
+    ctx.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--config", choices=["cfg4", "cfg5", "parquet"], required=True)
+    ap.add_argument("--config", choices=["cfg4", "cfg5", "parquet", "skew"], required=True)
     ap.add_argument("--rows", type=int, default=0, help="rows (per GPU for cfg5); default = the config's size that fits")
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=2)
@@ -168,6 +227,8 @@ def main():
         run_cfg4(args)
     elif args.config == "parquet":
         run_parquet(args)
+    elif args.config == "skew":
+        run_skew(args)
     else:
         run_cfg5(args)
 
