@@ -233,7 +233,15 @@ struct NcclExchange : BuildExchange {
       send_off[r] = first < nb ? local_off[first] : local_off[nb];
     }
     const uint64_t total = recv_off[N];
-    if (total >= 0xFFFFFFF0ull) HS_THROW(HS_EUNSUPPORTED, "more than 2^32-16 rows on one GPU");
+    // every rank holds every rank's histogram: a rank over the limit fails the build on ALL ranks, so that nobody is
+    // left waiting in the exchange that follows
+    for (int o = 0; o < N; o++) {
+      uint64_t t = 0;
+      for (int b = 0; b < nb; b++)
+        if (owner_of(b, N, nb) == o)
+          for (int r = 0; r < N; r++) t += all_hist[(size_t)r * nb + b];
+      if (t >= 0xFFFFFFF0ull) HS_THROW(HS_EUNSUPPORTED, "more than 2^32-16 rows on GPU %d", o);
+    }
     const int64_t nrecv = (int64_t)total;
     seg_off.assign((size_t)nbl + 1, 0);
     // run table: (src row, dst row, rows) for every (sender, owned bucket)
@@ -354,7 +362,8 @@ struct NcclExchange : BuildExchange {
     rank_rows.assign(N, 0);
     for (int b = 0; b < nb; b++)
       for (int r = 0; r < N; r++) rank_rows[owner_of(b, N, nb)] += all_hist[(size_t)r * nb + b];
-    if (rank_rows[me] >= 0xFFFFFFF0ull) HS_THROW(HS_EUNSUPPORTED, "more than 2^32-16 rows on one GPU");
+    for (int o = 0; o < N; o++)   // decided alike on every rank (see exchange())
+      if (rank_rows[o] >= 0xFFFFFFF0ull) HS_THROW(HS_EUNSUPPORTED, "more than 2^32-16 rows on GPU %d", o);
     // peers have finished with buffers retired one build ago (they passed an all-gather since)
     for (void* p : st->retired) cudaFree(p);
     st->retired.clear();
