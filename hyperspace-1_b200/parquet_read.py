@@ -120,9 +120,10 @@ def _hs_type(t):
     return abi.arrow_type_code(pa.string() if pa.types.is_large_string(t) else pa.binary() if pa.types.is_large_binary(t) else t)
 
 
-def decode_files(ctx, files, columns=None):
+def decode_files(ctx, files, columns=None, device=False):
     """All rows of `files` (in that order) decoded on the device, one call per column.
-    Returns (arrays, names, rows_per_file) with host Arrow arrays (HS_MEM_HOST contexts)."""
+    Returns (arrays, names, rows_per_file): host Arrow arrays, or — device=True — device-resident Tables of one
+    column each (the caller frees them) that can be handed to the join / filter without leaving the GPU."""
     metas = [pq.ParquetFile(f) for f in files]
     if not metas:
         return [], [], []
@@ -166,7 +167,19 @@ def decode_files(ctx, files, columns=None):
                     pages.append((body, csize, usize, nv, kind, enc, chunk))
                 at += size
             optional = metas[0].schema.column(ci).max_definition_level > 0
-            arrays.append(ctx.parquet_decode_pages(blob, pages, _hs_type(field.type), optional, codec or 0, field.type))
+            if device:
+                ctx.set_output_location(abi.HS_MEM_DEVICE)
+                try:
+                    arrays.append(ctx.parquet_decode_table(blob, pages, _hs_type(field.type), optional, codec or 0))
+                finally:
+                    ctx.set_output_location(abi.HS_MEM_HOST)
+            else:
+                arrays.append(ctx.parquet_decode_pages(blob, pages, _hs_type(field.type), optional, codec or 0, field.type))
+    except Exception:
+        if device:
+            for t in arrays:
+                t.free()
+        raise
     finally:
         for h in handles:
             h.close()

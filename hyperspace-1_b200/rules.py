@@ -274,6 +274,61 @@ def _single_run(session, entry, columns=None, hybrid=None):
     return arrays, names, boff
 
 
+class _DeviceRun:
+    """The files of an index decoded into device memory: one Table per column + the bucket offsets."""
+
+    def __init__(self, tables, names, boff, n_indexed):
+        from . import abi
+        from .native import IndexView
+        self.tables, self.names, self.boff = tables, names, boff
+        spec = []
+        for t in tables:
+            c = t.column(0)
+            spec.append({"type": c.type, "length": c.length, "null_count": c.null_count, "validity": c.validity,
+                         "offsets": c.offsets, "data": c.data})
+        self.view = IndexView(abi.DeviceColumnSet(spec), n_indexed, boff)
+
+    def free(self):
+        for t in self.tables:
+            t.free()
+        self.tables = []
+
+
+def _device_run(session, scan):
+    """An index scan whose files can go from disk to the join / filter kernels without a stop in host arrays: one
+    file per bucket, no hybrid-scan work, no lineage column, files the device reader covers. None otherwise (the
+    caller takes the general path through _single_run)."""
+    from . import parquet_read
+    from .index_writer import LINEAGE_COL, index_column_names
+    from .native import HyperspaceException
+    if session.conf.get("hsgpu.index.fileReader", "gpu") != "gpu" or scan.hybrid:
+        return None
+    entry = scan.entry
+    names = index_column_names(entry)
+    if LINEAGE_COL in names:
+        return None
+    nb = entry["derivedDataset"]["properties"]["numBuckets"]
+    per_bucket = {}
+    for fi in le.content_files(entry["content"]):
+        per_bucket.setdefault(le.bucket_id_of(fi["name"]), []).append(le.from_uri(fi["name"]))
+    if not per_bucket or any(len(v) != 1 for v in per_bucket.values()):
+        return None
+    buckets = sorted(per_bucket)
+    try:
+        tables, got_names, rows = parquet_read.decode_files(session.ctx, [per_bucket[b][0] for b in buckets], names, device=True)
+    except HyperspaceException:
+        return None
+    off = np.zeros(nb + 1, dtype=np.int64)
+    for b, r in zip(buckets, rows):
+        off[b + 1] = r
+    tables = [tables[got_names.index(c)] for c in names]
+    import pyarrow.parquet as pq
+    schema = pq.read_schema(per_bucket[buckets[0]][0])
+    run = _DeviceRun(tables, names, np.cumsum(off), len(_index_columns(entry)[0]))
+    run.types = [schema.field(c).type for c in names]
+    return run
+
+
 def execute(session, plan):
     if isinstance(plan, Scan):
         return plan.relation.read()
@@ -295,6 +350,24 @@ def execute(session, plan):
         return t.filter(expr_to_arrow(plan.pred, lambda n: resolve_name(n, t.column_names)))
     if isinstance(plan, Join):
         if isinstance(plan.left, IndexScan):
+            # both indexes straight from their files into device memory, joined there; only the result comes back
+            ld = _device_run(session, plan.left)
+            rd = _device_run(session, plan.right) if ld is not None else None
+            if ld is not None and rd is not None:
+                try:
+                    lout = [ld.names.index(resolve_name(c, ld.names)) for c in plan.left_out]
+                    rout = [rd.names.index(resolve_name(c, rd.names)) for c in plan.right_out]
+                    t = session.ctx.join_table(ld.view, rd.view, lout, rout, how=plan.how)
+                    try:
+                        out = t.to_arrow([ld.types[i] for i in lout] + [rd.types[i] for i in rout])
+                    finally:
+                        t.free()
+                    return pa.table(out, names=_dedupe([ld.names[i] for i in lout] + [rd.names[i] for i in rout]))
+                finally:
+                    ld.free()
+                    rd.free()
+            if ld is not None:
+                ld.free()
             la, ln, lo = _single_run(session, plan.left.entry, hybrid=plan.left.hybrid)
             ra, rn, ro = _single_run(session, plan.right.entry, hybrid=plan.right.hybrid)
             lout = [ln.index(resolve_name(c, ln)) for c in plan.left_out]
