@@ -72,6 +72,7 @@ __global__ void __launch_bounds__(256) k_pq_fixed(const uint8_t* __restrict__ da
   for (; i < n; i += stride) {
     if (!flag[i]) continue;
     const int p = pq_page_of(pg, i);
+    if (pg.val_off[p] == ~0ull) continue;        // dictionary-encoded page
     uint8_t* d = out + pg.val_off[p] + (uint64_t)(vpos[i] - pg.first[2 * p]) * w;
     const uint8_t* s = data + (size_t)i * w;
     // page bodies start at arbitrary byte offsets: copy by bytes unless both ends happen to be aligned
@@ -133,6 +134,223 @@ __global__ void __launch_bounds__(256) k_pq_deflevels(const uint8_t* __restrict_
   }
 }
 
+// ------------------------------------------------------------------ dictionary encoding (PLAIN_DICTIONARY)
+// What parquet-mr does first for every column chunk: values go through a dictionary as long as it stays small.
+// Per chunk (= bucket file) an open-addressing table in global memory collects the distinct values (atomicCAS on
+// the 64-bit slot); a chunk whose table passes max_dict entries falls back to PLAIN. Dictionary-encoded pages hold
+// [definition levels][bit width][one bit-packed run of the indices].
+#define PQD_EMPTY 0xFFFFFFFFFFFFFFFFull
+struct PqDict {
+  int32_t nchunks, slots, max_dict, w;       // slots: power of two >= 2 * max_dict
+  unsigned long long* keys;                  // [nchunks * slots]
+  uint32_t* index;                           // [nchunks * slots]: dictionary index of the slot's value
+  uint32_t* count;                           // [nchunks] distinct values seen
+  uint32_t* overflow;                        // [nchunks] 1 = too many distinct values: PLAIN
+  uint32_t* has_empty;                       // [nchunks] the value whose bits equal PQD_EMPTY occurs (8-byte types)
+  const int32_t* page_chunk;                 // [npages]
+};
+__device__ __forceinline__ uint64_t pqd_load(const uint8_t* data, int w, int64_t i) {
+  return w == 8 ? ((const uint64_t*)data)[i] : (uint64_t)((const uint32_t*)data)[i];
+}
+__device__ __forceinline__ uint32_t pqd_hash(uint64_t v) {
+  v ^= v >> 33; v *= 0xff51afd7ed558ccdull; v ^= v >> 29;
+  return (uint32_t)v;
+}
+__global__ void __launch_bounds__(256) k_pqd_insert(const uint8_t* __restrict__ data, const uint8_t* __restrict__ flag, int64_t n,
+                                                    PqPages pg, PqDict d) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    if (!flag[i]) continue;
+    const int c = d.page_chunk[pq_page_of(pg, i)];
+    if (d.overflow[c]) continue;
+    const uint64_t v = pqd_load(data, d.w, i);
+    if (v == PQD_EMPTY) { d.has_empty[c] = 1; continue; }
+    unsigned long long* tab = d.keys + (size_t)c * d.slots;
+    uint32_t h = pqd_hash(v) & (uint32_t)(d.slots - 1);
+    for (int probe = 0; probe < d.slots; probe++) {
+      const unsigned long long old = atomicCAS(&tab[h], (unsigned long long)PQD_EMPTY, (unsigned long long)v);
+      if (old == PQD_EMPTY) {
+        if (atomicAdd(&d.count[c], 1u) >= (uint32_t)d.max_dict) d.overflow[c] = 1;
+        break;
+      }
+      if (old == v) break;
+      h = (h + 1) & (uint32_t)(d.slots - 1);
+      if (probe == d.slots - 1) d.overflow[c] = 1;
+    }
+  }
+}
+// one CTA per chunk: used slots get consecutive indices (slot order); the dictionary page body is written
+__global__ void __launch_bounds__(256) k_pqd_assign(PqDict d, const uint64_t* __restrict__ dict_off, uint8_t* __restrict__ out) {
+  __shared__ uint32_t s_base, s_warp[8];
+  const int c = blockIdx.x;
+  if (dict_off[c] == ~0ull) return;
+  const unsigned long long* tab = d.keys + (size_t)c * d.slots;
+  uint32_t* idx = d.index + (size_t)c * d.slots;
+  uint8_t* body = out + dict_off[c];
+  if (threadIdx.x == 0) s_base = 0;
+  __syncthreads();
+  for (int s0 = 0; s0 < d.slots; s0 += 256) {
+    const int s = s0 + threadIdx.x;
+    const bool used = s < d.slots && tab[s] != PQD_EMPTY;
+    const uint32_t bal = __ballot_sync(0xffffffffu, used);
+    if (lane_id() == 0) s_warp[threadIdx.x >> 5] = __popc(bal);
+    __syncthreads();
+    uint32_t before = s_base;
+    for (int w = 0; w < (int)(threadIdx.x >> 5); w++) before += s_warp[w];
+    const uint32_t my = before + __popc(bal & ((1u << lane_id()) - 1u));
+    if (used) {
+      idx[s] = my;
+      const uint64_t v = tab[s];
+      for (int b = 0; b < d.w; b++) body[(size_t)my * d.w + b] = (uint8_t)(v >> (8 * b));
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) { uint32_t t = 0; for (int w = 0; w < 8; w++) t += s_warp[w]; s_base += t; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0 && d.has_empty[c]) {   // the all-ones value takes the last index
+    for (int b = 0; b < d.w; b++) body[(size_t)s_base * d.w + b] = 0xFF;
+  }
+}
+// index of every non-NULL value of a dictionary-encoded chunk, in row order
+__global__ void __launch_bounds__(256) k_pqd_lookup(const uint8_t* __restrict__ data, const uint8_t* __restrict__ flag,
+                                                    const uint32_t* __restrict__ vpos, int64_t n, PqPages pg, PqDict d,
+                                                    const uint64_t* __restrict__ dict_off, uint32_t* __restrict__ idxv) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    if (!flag[i]) continue;
+    const int c = d.page_chunk[pq_page_of(pg, i)];
+    if (dict_off[c] == ~0ull) continue;
+    const uint64_t v = pqd_load(data, d.w, i);
+    uint32_t r;
+    if (v == PQD_EMPTY) r = d.count[c];
+    else {
+      const unsigned long long* tab = d.keys + (size_t)c * d.slots;
+      uint32_t h = pqd_hash(v) & (uint32_t)(d.slots - 1);
+      while (tab[h] != v) h = (h + 1) & (uint32_t)(d.slots - 1);
+      r = d.index[(size_t)c * d.slots + h];
+    }
+    idxv[vpos[i]] = r;
+  }
+}
+// bit-packed groups of the dictionary-encoded pages: one thread per output byte
+__global__ void __launch_bounds__(256) k_pqd_pack(const uint32_t* __restrict__ idxv, const uint64_t* __restrict__ pack_off,
+                                                  const uint32_t* __restrict__ pack_bytes, const uint32_t* __restrict__ bw_of,
+                                                  PqPages pg, uint8_t* __restrict__ out) {
+  const int p = blockIdx.y;
+  if (pack_off[p] == ~0ull) return;
+  const uint32_t bw = bw_of[p], nbytes = pack_bytes[p];
+  const uint64_t v0 = pg.first[2 * p], v1 = pg.first[2 * (p + 1)];   // non-NULL values before / through the page
+  for (uint32_t b = blockIdx.x * blockDim.x + threadIdx.x; b < nbytes; b += gridDim.x * blockDim.x) {
+    uint32_t byte = 0;
+    const uint64_t bit0 = (uint64_t)b * 8;
+    for (uint64_t j = bit0 / bw; j * bw < bit0 + 8; j++) {
+      const uint64_t x = v0 + j < v1 ? idxv[v0 + j] : 0;        // padding of the last group: zeros
+      const int64_t sh = (int64_t)(j * bw) - (int64_t)bit0;     // position of the value's bit 0 inside this byte
+      byte |= sh >= 0 ? (uint32_t)(x << sh) : (uint32_t)(x >> (-sh));
+    }
+    out[pack_off[p] + b] = (uint8_t)byte;
+  }
+}
+
+// ------------------------------------------------------------------ snappy (codec 1)
+// Page bodies compressed on the device, in the raw snappy format parquet-mr's SnappyCodec writes. A body is cut
+// into fragments of SN_FRAG bytes, each compressed by one warp on its own (matches never reach back past the
+// fragment start, as in the reference compressor, which also resets its table per block — only the block is
+// 64 KiB there): the fragment sits in shared memory next to a table of the last position of every 4-byte hash;
+// per round the 32 lanes test 32 consecutive positions against the table, the first hit is extended by all lanes
+// together, and literals / copies are written by all lanes. Fragments land in worst-case-sized slots; a second
+// kernel packs them behind the page's length preamble.
+#define SN_FRAG 8192
+#define SN_HT_BITS 11
+#define SN_WARPS 8
+#define SN_SLOT (SN_FRAG + SN_FRAG / 6 + 64)
+struct SnFrag { uint64_t src; uint32_t len; uint32_t pad; };
+struct SnWarp {
+  uint8_t in[SN_FRAG + 32];           // the fragment at in[src & 15] (16-byte loads keep their alignment)
+  uint16_t ht[1 << SN_HT_BITS];
+};
+__device__ __forceinline__ uint32_t sn_ld32(const uint8_t* base, uint32_t a) {   // base is 16-byte aligned
+  const uint32_t* w = (const uint32_t*)base;
+  return __funnelshift_r(w[a >> 2], w[(a >> 2) + 1], (a & 3) * 8);
+}
+__device__ __forceinline__ uint32_t sn_literal(uint8_t* out, uint32_t o, const uint8_t* in, uint32_t start, uint32_t len, int lane) {
+  if (len == 0) return o;
+  const uint32_t n1 = len - 1;
+  uint32_t hdr;
+  if (n1 < 60) { if (lane == 0) out[o] = (uint8_t)(n1 << 2); hdr = 1; }
+  else if (n1 < 256) { if (lane == 0) { out[o] = 60 << 2; out[o + 1] = (uint8_t)n1; } hdr = 2; }
+  else { if (lane == 0) { out[o] = 61 << 2; out[o + 1] = (uint8_t)n1; out[o + 2] = (uint8_t)(n1 >> 8); } hdr = 3; }
+  for (uint32_t i = lane; i < len; i += 32) out[o + hdr + i] = in[start + i];
+  return o + hdr + len;
+}
+__device__ __forceinline__ uint32_t sn_copy(uint8_t* out, uint32_t o, uint32_t off, uint32_t len, int lane) {
+  if (len <= 11 && off < 2048) {      // 2-byte form: length 4..11, 11-bit offset
+    if (lane == 0) { out[o] = (uint8_t)(((off >> 8) << 5) | ((len - 4) << 2) | 1); out[o + 1] = (uint8_t)off; }
+    return o + 2;
+  }
+  const uint32_t nel = (len + 63) >> 6;   // 3-byte form: length 1..64, 16-bit offset
+  for (uint32_t k = lane; k < nel; k += 32) {
+    const uint32_t l = k + 1 < nel ? 64 : len - 64 * (nel - 1);
+    out[o + 3 * k] = (uint8_t)(((l - 1) << 2) | 2);
+    out[o + 3 * k + 1] = (uint8_t)off;
+    out[o + 3 * k + 2] = (uint8_t)(off >> 8);
+  }
+  return o + 3 * nel;
+}
+__global__ void __launch_bounds__(SN_WARPS * 32) k_snappy_frag(const uint8_t* __restrict__ body, const SnFrag* __restrict__ frags,
+                                                               int nfrag, uint8_t* __restrict__ scratch, uint32_t* __restrict__ sizes) {
+  extern __shared__ __align__(16) uint8_t sn_smem[];
+  const int lane = lane_id(), f = blockIdx.x * SN_WARPS + (threadIdx.x >> 5);
+  if (f >= nfrag) return;
+  SnWarp* sw = (SnWarp*)sn_smem + (threadIdx.x >> 5);
+  const SnFrag fr = frags[f];
+  const uint32_t len = fr.len, skew = (uint32_t)(fr.src & 15);
+  const uint4* g = (const uint4*)(body + (fr.src - skew));
+  for (uint32_t i = lane; i * 16 < skew + len; i += 32) ((uint4*)sw->in)[i] = g[i];
+  for (uint32_t i = lane; i < (1u << SN_HT_BITS); i += 32) sw->ht[i] = 0xFFFF;
+  __syncwarp();
+  const uint8_t* base = sw->in;          // 16-byte aligned; fragment byte i is base[skew + i]
+  const uint8_t* in = base + skew;
+  uint8_t* out = scratch + (size_t)f * SN_SLOT;
+  uint32_t pos = 0, lit = 0, o = 0;
+  while (pos + 4 <= len) {
+    const uint32_t p = pos + lane;
+    const bool can = p + 4 <= len;
+    const uint32_t w = can ? sn_ld32(base, skew + p) : 0;
+    const uint32_t h = (w * 0x1e35a7bdu) >> (32 - SN_HT_BITS);
+    const uint32_t cand = can ? sw->ht[h] : 0xFFFFu;
+    __syncwarp();
+    if (can) sw->ht[h] = (uint16_t)p;
+    __syncwarp();
+    const bool hit = can && cand < p && sn_ld32(base, skew + cand) == w;
+    const uint32_t bal = __ballot_sync(0xffffffffu, hit);
+    if (!bal) { pos += 32; continue; }
+    const int first = __ffs(bal) - 1;
+    const uint32_t m = pos + first, c = __shfl_sync(0xffffffffu, cand, first);
+    uint32_t mlen = 4;
+    for (;;) {
+      const uint32_t i = m + mlen + lane;
+      const bool same = i < len && in[i] == in[c + mlen + lane];
+      const uint32_t diff = __ballot_sync(0xffffffffu, !same);
+      if (diff) { mlen += __ffs(diff) - 1; break; }
+      mlen += 32;
+    }
+    o = sn_literal(out, o, in, lit, m - lit, lane);
+    o = sn_copy(out, o, m - c, mlen, lane);
+    pos = m + mlen;
+    lit = pos;
+  }
+  o = sn_literal(out, o, in, lit, len - lit, lane);
+  if (lane == 0) sizes[f] = o;
+}
+// fragment f of the scratch slots -> its place in the packed output
+__global__ void __launch_bounds__(256) k_snappy_pack(const uint8_t* __restrict__ scratch, const uint32_t* __restrict__ sizes,
+                                                     const uint64_t* __restrict__ dst, int nfrag, uint8_t* __restrict__ out) {
+  const int lane = lane_id(), f = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (f >= nfrag) return;
+  const uint8_t* s = scratch + (size_t)f * SN_SLOT;
+  uint8_t* d = out + dst[f];
+  for (uint32_t i = lane; i < sizes[f]; i += 32) d[i] = s[i];
+}
+
 static int varint(uint64_t v, uint8_t* out) {
   int n = 0;
   while (v >= 0x80) { out[n++] = (uint8_t)(v | 0x80); v >>= 7; }
@@ -140,12 +358,19 @@ static int varint(uint64_t v, uint8_t* out) {
   return n;
 }
 
-extern "C" int32_t hs_parquet_plain_pages(hs_ctx* ctx, const hs_column* col, int32_t optional, const int64_t* page_rows,
-                                          int32_t npages, hs_table** out) {
-  API_BEGIN(ctx)
+// page_chunk / nchunks / max_dict: dictionary encoding per column chunk (max_dict = 0: PLAIN only)
+static void pq_encode(hs_ctx* ctx, const hs_column* col, int32_t optional, const int64_t* page_rows, int32_t npages,
+                      const int32_t* page_chunk, int32_t nchunks, int32_t max_dict, hs_table** out) {
   if (!out) HS_THROW(HS_EINVAL, "null out");
   *out = nullptr;
   if (!col || !page_rows || npages <= 0 || npages > 65535) HS_THROW(HS_EINVAL, "bad page list (1..65535 pages per call)");
+  if (max_dict > 0) {
+    if (!page_chunk || nchunks <= 0 || nchunks > npages) HS_THROW(HS_EINVAL, "dictionary encoding needs the chunk of every page");
+    if (max_dict > 32768) HS_THROW(HS_EINVAL, "max_dict is at most 32768 entries");
+    for (int p = 0; p < npages; p++)
+      if (page_chunk[p] < 0 || page_chunk[p] >= nchunks || (p && page_chunk[p] < page_chunk[p - 1]))
+        HS_THROW(HS_EINVAL, "page_chunk must be non-decreasing and inside [0, nchunks)");
+  } else nchunks = 0;
   hs_stages_reset(ctx);
   DevCol dc;
   {
@@ -182,9 +407,43 @@ extern "C" int32_t hs_parquet_plain_pages(hs_ctx* ctx, const hs_column* col, int
     CK(cudaMemcpyAsync(h_first.data(), picks.p, h_first.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
     hs_sync(ctx);
   }
-  // ---- page layout (host): [def levels][values] per page, pages back to back
-  std::vector<int64_t> page_off((size_t)npages + 1, 0), nulls((size_t)npages, 0);
-  std::vector<uint64_t> val_off((size_t)npages), def_off((size_t)npages, ~0ull);
+  // ---- dictionary pass: distinct values per chunk; chunks that stay within max_dict are dictionary-encoded
+  const bool try_dict = max_dict > 0 && !varlen && !is_bool && (w == 4 || w == 8) && n > 0;
+  std::vector<uint32_t> entries((size_t)nchunks, 0);          // dictionary entries per chunk; 0 = PLAIN
+  DBuf d_keys, d_index, d_counts, d_pchunk, d_dictoff, idxv;
+  PqDict pd{};
+  if (try_dict) {
+    Stage s(ctx, "parquet_dict");
+    int slots = 64;
+    while (slots < 2 * max_dict) slots <<= 1;
+    d_keys.alloc(ctx, (size_t)nchunks * slots * 8);
+    d_index.alloc(ctx, (size_t)nchunks * slots * 4);
+    d_counts.alloc(ctx, (size_t)nchunks * 12);
+    d_pchunk.alloc(ctx, (size_t)npages * 4);
+    CK(cudaMemsetAsync(d_keys.p, 0xFF, (size_t)nchunks * slots * 8, ctx->stream));
+    CK(cudaMemsetAsync(d_counts.p, 0, (size_t)nchunks * 12, ctx->stream));
+    CK(cudaMemcpyAsync(d_pchunk.p, page_chunk, (size_t)npages * 4, cudaMemcpyHostToDevice, ctx->stream));
+    pd = PqDict{nchunks, slots, max_dict, w, d_keys.as<unsigned long long>(), d_index.as<uint32_t>(), d_counts.as<uint32_t>(),
+                d_counts.as<uint32_t>() + nchunks, d_counts.as<uint32_t>() + 2 * (size_t)nchunks, d_pchunk.as<int32_t>()};
+    PqPages pg0{npages, d_rows.as<int64_t>(), nullptr, nullptr, picks.as<uint64_t>()};
+    const unsigned g = (unsigned)std::min<int64_t>((n1 + 255) / 256, (int64_t)HS_NUM_SMS * 16);
+    LAUNCH(ctx, k_pqd_insert, g, 256, 0, (const uint8_t*)dc.data, flag.as<uint8_t>(), n, pg0, pd);
+    std::vector<uint32_t> h_counts(3 * (size_t)nchunks);
+    CK(cudaMemcpyAsync(h_counts.data(), d_counts.p, h_counts.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    hs_sync(ctx);
+    for (int c = 0; c < nchunks; c++) {
+      const uint32_t cnt = h_counts[c], over = h_counts[nchunks + c], has_e = h_counts[2 * (size_t)nchunks + c];
+      if (!over && cnt <= (uint32_t)max_dict) entries[c] = cnt + (has_e ? 1u : 0u);
+    }
+  }
+  auto bit_width = [](uint32_t nentries) { int b = 1; while ((1u << b) < nentries) b++; return b; };
+  // ---- page layout (host): [def levels][values] per page, pages back to back; then the dictionary page bodies
+  const int nout = npages + nchunks;
+  std::vector<int64_t> page_off((size_t)nout + 1, 0), nulls((size_t)nout, 0);
+  std::vector<uint64_t> val_off((size_t)npages), def_off((size_t)npages, ~0ull), pack_off((size_t)npages, ~0ull);
+  std::vector<uint64_t> dict_off((size_t)nchunks, ~0ull);
+  std::vector<uint32_t> pack_bytes((size_t)npages, 0), bw_of((size_t)npages, 0);
+  bool any_dict = false;
   std::vector<std::pair<uint64_t, std::vector<uint8_t>>> headers;   // (offset, bytes) written from the host
   uint64_t at = 0;
   for (int p = 0; p < npages; p++) {
@@ -213,23 +472,47 @@ extern "C" int32_t hs_parquet_plain_pages(hs_ctx* ctx, const hs_column* col, int
       at += 4 + body;
     }
     val_off[p] = at;
+    if (nchunks && entries[page_chunk[p]]) {       // [bit width][varint((groups << 1) | 1)][groups * bw bytes]
+      const int bw = bit_width(entries[page_chunk[p]]);
+      std::vector<uint8_t> h(12);
+      h[0] = (uint8_t)bw;
+      int k = 1;
+      if (valid > 0) {
+        const int64_t groups = (valid + 7) >> 3;
+        k += varint(((uint64_t)groups << 1) | 1u, h.data() + 1);
+        pack_off[p] = at + (uint64_t)k;
+        pack_bytes[p] = (uint32_t)(groups * bw);
+        bw_of[p] = (uint32_t)bw;
+      }
+      h.resize((size_t)k);
+      headers.emplace_back(at, std::move(h));
+      at += (uint64_t)k + pack_bytes[p];
+      val_off[p] = ~0ull;                          // no PLAIN values in this page
+      any_dict = true;
+      continue;
+    }
     if (varlen) at += h_first[2 * (p + 1) + 1] - h_first[2 * p + 1];
     else if (is_bool) at += (uint64_t)((valid + 7) >> 3);
     else at += (uint64_t)valid * w;
   }
-  page_off[npages] = (int64_t)at;
+  for (int c = 0; c < nchunks; c++) {
+    page_off[(size_t)npages + c] = (int64_t)at;
+    nulls[(size_t)npages + c] = entries[c];        // second column, rows past the pages: dictionary entries
+    if (entries[c]) { dict_off[c] = at; at += (uint64_t)entries[c] * w; }
+  }
+  page_off[nout] = (int64_t)at;
   if (at >= 0x7FFFFFF0ull) HS_THROW(HS_EUNSUPPORTED, "more than 2 GiB of page data in one call: encode fewer rows at a time");
   std::vector<OutCol> ocols(2);
   OutCol& body = ocols[0];
   body.type = HS_BINARY;
-  body.length = npages;
+  body.length = nout;
   body.data_bytes = (int64_t)at;
   body.data.alloc(ctx, (size_t)at + 8);
-  body.offsets.alloc(ctx, ((size_t)npages + 1) * 4);
+  body.offsets.alloc(ctx, ((size_t)nout + 1) * 4);
   {
     Stage s(ctx, "parquet_encode");
-    std::vector<int32_t> off32((size_t)npages + 1);
-    for (int p = 0; p <= npages; p++) off32[p] = (int32_t)page_off[p];
+    std::vector<int32_t> off32((size_t)nout + 1);
+    for (int p = 0; p <= nout; p++) off32[p] = (int32_t)page_off[p];
     CK(cudaMemcpyAsync(body.offsets.p, off32.data(), off32.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
     if (is_bool) CK(cudaMemsetAsync(body.data.p, 0, (size_t)at + 8, ctx->stream));
     for (auto& h : headers)
@@ -250,6 +533,24 @@ extern "C" int32_t hs_parquet_plain_pages(hs_ctx* ctx, const hs_column* col, int
       } else {
         LAUNCH(ctx, k_pq_fixed, g, 256, 0, (const uint8_t*)dc.data, w, flag.as<uint8_t>(), vpos.as<uint32_t>(), n, pg, o);
       }
+      if (any_dict) {
+        DBuf d_pack(ctx, (size_t)npages * 8), d_pbytes(ctx, (size_t)npages * 4), d_bw(ctx, (size_t)npages * 4);
+        d_dictoff.alloc(ctx, (size_t)nchunks * 8);
+        idxv.alloc(ctx, (size_t)std::max<uint64_t>(h_first[2 * (size_t)npages], 1) * 4);
+        CK(cudaMemcpyAsync(d_pack.p, pack_off.data(), (size_t)npages * 8, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(d_pbytes.p, pack_bytes.data(), (size_t)npages * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(d_bw.p, bw_of.data(), (size_t)npages * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(d_dictoff.p, dict_off.data(), (size_t)nchunks * 8, cudaMemcpyHostToDevice, ctx->stream));
+        LAUNCH(ctx, k_pqd_assign, (unsigned)nchunks, 256, 0, pd, d_dictoff.as<uint64_t>(), o);
+        LAUNCH(ctx, k_pqd_lookup, g, 256, 0, (const uint8_t*)dc.data, flag.as<uint8_t>(), vpos.as<uint32_t>(), n, pg, pd,
+               d_dictoff.as<uint64_t>(), idxv.as<uint32_t>());
+        dim3 grid(64, (unsigned)npages);
+        k_pqd_pack<<<grid, 256, 0, ctx->stream>>>(idxv.as<uint32_t>(), d_pack.as<uint64_t>(), d_pbytes.as<uint32_t>(),
+                                                  d_bw.as<uint32_t>(), pg, o);
+        hs_count_launch(ctx);
+        CK(cudaGetLastError());
+        hs_sync(ctx);   // the small per-page buffers above go out of scope here
+      }
       bool any_def = false;
       for (int p = 0; p < npages; p++) any_def |= def_off[p] != ~0ull;
       if (any_def) {
@@ -263,12 +564,26 @@ extern "C" int32_t hs_parquet_plain_pages(hs_ctx* ctx, const hs_column* col, int
   }
   OutCol& nn = ocols[1];
   nn.type = HS_INT64;
-  nn.length = npages;
-  nn.data_bytes = (int64_t)npages * 8;
-  nn.data.alloc(ctx, (size_t)npages * 8);
-  CK(cudaMemcpyAsync(nn.data.p, nulls.data(), (size_t)npages * 8, cudaMemcpyHostToDevice, ctx->stream));
+  nn.length = nout;
+  nn.data_bytes = (int64_t)nout * 8;
+  nn.data.alloc(ctx, (size_t)nout * 8);
+  CK(cudaMemcpyAsync(nn.data.p, nulls.data(), (size_t)nout * 8, cudaMemcpyHostToDevice, ctx->stream));
   hs_sync(ctx);
   Stage s(ctx, "d2h");
-  *out = hs_finish_table(ctx, ocols, npages, 0, nullptr);
+  *out = hs_finish_table(ctx, ocols, nout, 0, nullptr);
+}
+
+extern "C" int32_t hs_parquet_plain_pages(hs_ctx* ctx, const hs_column* col, int32_t optional, const int64_t* page_rows,
+                                          int32_t npages, hs_table** out) {
+  API_BEGIN(ctx)
+  pq_encode(ctx, col, optional, page_rows, npages, nullptr, 0, 0, out);
+  API_END(ctx)
+}
+
+extern "C" int32_t hs_parquet_encode_pages(hs_ctx* ctx, const hs_column* col, int32_t optional, const int64_t* page_rows,
+                                           int32_t npages, const int32_t* page_chunk, int32_t nchunks, int32_t max_dict,
+                                           hs_table** out) {
+  API_BEGIN(ctx)
+  pq_encode(ctx, col, optional, page_rows, npages, page_chunk, nchunks, max_dict, out);
   API_END(ctx)
 }

@@ -49,12 +49,16 @@ def write_buckets(columns, names, bucket_offsets, out_dir, task_of_bucket=None, 
 
 def write_index_files(session, arrays, names, boff, out_dir):
     """Parquet files of one index version. hsgpu.index.fileWriter = "pyarrow-snappy" (default: the host library
-    encodes, files are named and compressed as Spark's default writer would) or "gpu-plain" (page bodies encoded
-    on the device by hs_parquet_plain_pages, PLAIN + uncompressed; parquet_plain.py)."""
+    encodes, files are named and compressed as Spark's default writer would), "gpu-plain" (page bodies encoded
+    on the device by hs_parquet_plain_pages, PLAIN + uncompressed; parquet_plain.py) or "gpu-dictionary" (the same
+    through hs_parquet_encode_pages: chunks with at most hsgpu.index.dictionaryEntries distinct values — default
+    4096 — are dictionary-encoded, the rest PLAIN)."""
     t0 = time.perf_counter()
-    if session.conf.get("hsgpu.index.fileWriter", "pyarrow-snappy") == "gpu-plain":
+    writer = session.conf.get("hsgpu.index.fileWriter", "pyarrow-snappy")
+    if writer in ("gpu-plain", "gpu-dictionary"):
         from .parquet_plain import write_buckets_plain
-        files = write_buckets_plain(session.ctx, arrays, names, boff, out_dir)
+        max_dict = int(session.conf.get("hsgpu.index.dictionaryEntries", "4096")) if writer == "gpu-dictionary" else 0
+        files = write_buckets_plain(session.ctx, arrays, names, boff, out_dir, max_dict=max_dict)
         return files, time.perf_counter() - t0
     return write_buckets(arrays, names, boff, out_dir)
 

@@ -17,7 +17,7 @@ EXPORTS = [
     "hs_ctx_create", "hs_ctx_destroy", "hs_last_error", "hs_ctx_set_output_location", "hs_ctx_get_stream",
     "hs_ctx_enable_timing", "hs_ctx_last_timings", "hs_ctx_launch_count", "hs_table_free", "hs_version",
     "hs_ctx_set_deferred_results", "hs_table_wait", "hs_ctx_trim",
-    "hs_parquet_plain_pages", "hs_parquet_decode_pages",
+    "hs_parquet_plain_pages", "hs_parquet_encode_pages", "hs_parquet_decode_pages",
     "hs_hash_bucket", "hs_hash_rows", "hs_build_index", "hs_merge_runs", "hs_join_bucketed", "hs_filter_scan",
     "hs_bucket_histogram_noalloc", "hs_comm_unique_id", "hs_comm_init", "hs_comm_destroy", "hs_build_index_dist", "hs_comm_last_exchange",
 ]
@@ -273,6 +273,26 @@ class Context:
         try:
             bodies, nulls = t.to_arrow()
             return [b.as_py() for b in bodies], nulls.to_numpy()
+        finally:
+            t.free()
+
+    def parquet_encode_pages(self, array, optional, page_rows, page_chunk, nchunks, max_dict):
+        """hs_parquet_encode_pages -> (page bodies, NULLs per page, dictionary page bodies, entries per chunk)."""
+        cs = abi.ColumnSet([array])
+        pr = np.ascontiguousarray(page_rows, dtype=np.int64)
+        pc = np.ascontiguousarray(page_chunk, dtype=np.int32)
+        npages = len(pr) - 1
+        out = C.POINTER(abi.hs_table)()
+        self._check(self._lib.hs_parquet_encode_pages(self._h, cs.ptr(), C.c_int32(1 if optional else 0),
+                                                      pr.ctypes.data_as(C.POINTER(C.c_int64)), C.c_int32(npages),
+                                                      pc.ctypes.data_as(C.POINTER(C.c_int32)), C.c_int32(nchunks),
+                                                      C.c_int32(max_dict), C.byref(out)), "hs_parquet_encode_pages")
+        t = Table(self, out)
+        try:
+            bodies, counts = t.to_arrow()
+            bodies = [b.as_py() for b in bodies]
+            counts = counts.to_numpy()
+            return bodies[:npages], counts[:npages], bodies[npages:], counts[npages:]
         finally:
             t.free()
 

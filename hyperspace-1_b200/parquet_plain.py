@@ -1,8 +1,10 @@
 """Parquet files whose page bodies come from the GPU (hs_parquet_plain_pages): the K4 step behind saveWithBuckets
 (HS/index/DataFrameWriterExtensions.scala:58-65, Spark's DynamicPartitionDataWriter + ParquetFileFormat).
 
-Format written: Parquet 1.0, one row group per file, data pages v1, PLAIN encoding, UNCOMPRESSED, every column
-OPTIONAL under a `spark_schema` root — what parquet-mr 1.10 (Spark 2.4.2) and pyarrow read. This module only frames
+Format written: Parquet 1.0, one row group per file, data pages v1, UNCOMPRESSED, every column OPTIONAL under a
+`spark_schema` root — what parquet-mr 1.10 (Spark 2.4.2) and pyarrow read. Values are PLAIN, or — max_dict > 0,
+parquet-mr's default behaviour — PLAIN_DICTIONARY for the column chunks whose distinct values fit a dictionary
+(hs_parquet_encode_pages decides per chunk on the device). This module only frames
 the bytes: Thrift compact-protocol page headers and the footer (a few hundred bytes per file); every value is
 encoded on the device, one call per column for ALL bucket files of an index version. The Spark schema JSON goes
 into the footer under the key Spark looks for, so types come back as Spark wrote them."""
@@ -19,7 +21,7 @@ MAGIC = b"PAR1"
 # parquet.thrift enums
 T_BOOLEAN, T_INT32, T_INT64, T_FLOAT, T_DOUBLE, T_BYTE_ARRAY = 0, 1, 2, 4, 5, 6
 CT_UTF8, CT_DATE, CT_TS_MILLIS, CT_TS_MICROS, CT_INT_8, CT_INT_16 = 0, 6, 9, 10, 15, 16
-ENC_PLAIN, ENC_RLE, ENC_BIT_PACKED = 0, 3, 4
+ENC_PLAIN, ENC_PLAIN_DICTIONARY, ENC_RLE, ENC_BIT_PACKED = 0, 2, 3, 4
 OPTIONAL = 1
 PAGE_ROWS = 1 << 20          # rows per data page at most
 
@@ -121,14 +123,27 @@ def physical_type(t):
     raise TypeError(f"no PLAIN Parquet mapping for {t}")
 
 
-def page_header(num_values, body_len):
+def dictionary_page_header(num_entries, body_len):
+    t = _Thrift()
+    t.i32(1, 2)                       # type = DICTIONARY_PAGE
+    t.i32(2, body_len)
+    t.i32(3, body_len)
+    t.struct_begin(7)                 # dictionary_page_header
+    t.i32(1, num_entries)
+    t.i32(2, ENC_PLAIN_DICTIONARY)    # what parquet-mr 1.10 writes for a v1 dictionary page
+    t.struct_end()
+    t.b.append(0)
+    return bytes(t.b)
+
+
+def page_header(num_values, body_len, encoding=ENC_PLAIN):
     t = _Thrift()
     t.i32(1, 0)                       # type = DATA_PAGE
     t.i32(2, body_len)                # uncompressed_page_size
     t.i32(3, body_len)                # compressed_page_size (codec UNCOMPRESSED)
     t.struct_begin(5)                 # data_page_header
     t.i32(1, num_values)
-    t.i32(2, ENC_PLAIN)
+    t.i32(2, encoding)
     t.i32(3, ENC_RLE)                 # definition levels
     t.i32(4, ENC_BIT_PACKED)          # repetition levels (none: flat schema)
     t.struct_end()
@@ -137,7 +152,8 @@ def page_header(num_values, body_len):
 
 
 def footer(names, types, num_rows, chunks, spark_schema_json):
-    """chunks: per column (first page offset, total bytes, num_values)."""
+    """chunks: per column (chunk start, total bytes, num_values, first data page offset if the chunk starts with a
+    dictionary page else None)."""
     t = _Thrift()
     t.i32(1, 1)                                           # version
     t.list_begin(2, _Thrift.STRUCT, len(names) + 1)       # schema
@@ -159,14 +175,15 @@ def footer(names, types, num_rows, chunks, spark_schema_json):
     t.struct_begin()
     t.list_begin(1, _Thrift.STRUCT, len(names))           # columns
     total = 0
-    for name, ty, (off, nbytes, nvals) in zip(names, types, chunks):
+    for name, ty, (off, nbytes, nvals, data_off) in zip(names, types, chunks):
         phys, _, _ = physical_type(ty)
         t.struct_begin()
         t.i64(2, off)                                     # file_offset
         t.struct_begin(3)                                 # meta_data
         t.i32(1, phys)
+        encs = (ENC_PLAIN, ENC_RLE, ENC_BIT_PACKED) if data_off is None else (ENC_PLAIN_DICTIONARY, ENC_RLE, ENC_BIT_PACKED)
         t.list_begin(2, _Thrift.I32, 3)
-        for e in (ENC_PLAIN, ENC_RLE, ENC_BIT_PACKED):
+        for e in encs:
             t.elem_i32(e)
         t.list_begin(3, _Thrift.BINARY, 1)
         t.elem_string(name)
@@ -174,7 +191,9 @@ def footer(names, types, num_rows, chunks, spark_schema_json):
         t.i64(5, nvals)
         t.i64(6, nbytes)
         t.i64(7, nbytes)
-        t.i64(9, off)                                     # data_page_offset
+        t.i64(9, off if data_off is None else data_off)   # data_page_offset
+        if data_off is not None:
+            t.i64(11, off)                                # dictionary_page_offset
         t.struct_end()
         t.struct_end()
         total += nbytes
@@ -191,30 +210,38 @@ def footer(names, types, num_rows, chunks, spark_schema_json):
     return bytes(t.b)
 
 
-def write_buckets_plain(ctx, columns, names, bucket_offsets, out_dir, task_of_bucket=None):
+def write_buckets_plain(ctx, columns, names, bucket_offsets, out_dir, task_of_bucket=None, max_dict=0):
     """The GPU counterpart of index_writer.write_buckets: rows [off[b], off[b+1]) of every non-empty bucket b go
     to part-<task%05d>-<uuid>_<bucket%05d>.c000.parquet (Spark's name for an uncompressed bucketed file; the
-    bucket id is parsed from it by BucketingUtils.getBucketId either way). Returns the files."""
+    bucket id is parsed from it by BucketingUtils.getBucketId either way). max_dict > 0: column chunks with at most
+    that many distinct values are dictionary-encoded. Returns the files."""
     os.makedirs(out_dir, exist_ok=True)
     job = uuid.uuid4()
     off = np.asarray(bucket_offsets, dtype=np.int64)
     types = [c.type for c in columns]
     # pages never cross a bucket: one call per column encodes the pages of all files
-    page_rows, page_bucket = [0], []
+    page_rows, page_bucket, page_chunk, chunk_of = [0], [], [], {}
     for b in range(len(off) - 1):
         a, e = int(off[b]), int(off[b + 1])
         while a < e:
             a = min(e, a + PAGE_ROWS)
             page_rows.append(a)
             page_bucket.append(b)
+            page_chunk.append(chunk_of.setdefault(b, len(chunk_of)))
     if not page_bucket:
         return []
-    bodies, nvals = [], []
+    bodies, nvals, dicts, dict_entries = [], [], [], []
     for c in columns:
         _, _, feed = physical_type(c.type)
         arr = c if feed == c.type else c.cast(feed)
-        pages, _ = ctx.parquet_plain_pages(arr, True, page_rows)
+        if max_dict > 0:
+            pages, _, dbody, dcount = ctx.parquet_encode_pages(arr, True, page_rows, page_chunk, len(chunk_of), max_dict)
+        else:
+            pages, _ = ctx.parquet_plain_pages(arr, True, page_rows)
+            dbody, dcount = [b""] * len(chunk_of), np.zeros(len(chunk_of), dtype=np.int64)
         bodies.append(pages)
+        dicts.append(dbody)
+        dict_entries.append(dcount)
         nvals.append(np.diff(np.asarray(page_rows, dtype=np.int64)))
     schema_json = le.schema_json(pa.schema([pa.field(n, t) for n, t in zip(names, types)]))
     files = []
@@ -229,15 +256,23 @@ def write_buckets_plain(ctx, columns, names, bucket_offsets, out_dir, task_of_bu
             pos = 4
             chunks = []
             for ci in range(len(columns)):
-                start, nv = pos, 0
+                start, nv, data_off = pos, 0, None
+                entries = int(dict_entries[ci][chunk_of[b]])
+                if entries:
+                    dbody = dicts[ci][chunk_of[b]]
+                    hdr = dictionary_page_header(entries, len(dbody))
+                    f.write(hdr)
+                    f.write(dbody)
+                    pos += len(hdr) + len(dbody)
+                    data_off = pos
                 for p in plist:
                     body = bodies[ci][p]
-                    hdr = page_header(int(nvals[ci][p]), len(body))
+                    hdr = page_header(int(nvals[ci][p]), len(body), ENC_PLAIN_DICTIONARY if entries else ENC_PLAIN)
                     f.write(hdr)
                     f.write(body)
                     pos += len(hdr) + len(body)
                     nv += int(nvals[ci][p])
-                chunks.append((start, pos - start, nv))
+                chunks.append((start, pos - start, nv, data_off))
             foot = footer(names, types, int(off[b + 1] - off[b]), chunks, schema_json)
             f.write(foot)
             f.write(struct.pack("<I", len(foot)))

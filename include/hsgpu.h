@@ -270,6 +270,18 @@ int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left,
 int32_t hs_parquet_plain_pages(hs_ctx* ctx, const hs_column* col, int32_t optional,
                                const int64_t* page_rows, int32_t npages, hs_table** out);
 
+/* The same with parquet-mr's first choice of encoding, the per-chunk dictionary (what Spark 2.4 writes for the
+ * index files: ParquetOutputFormat, dictionary enabled): page_chunk[p] (host, non-decreasing, < nchunks) names
+ * the column chunk — here: the bucket file — of page p. A chunk of a 4- or 8-byte column whose distinct non-NULL
+ * values number at most max_dict (<= 32768) gets a dictionary: its data pages are [definition levels] ++ [bit
+ * width byte] ++ [one bit-packed run of the indices] (encoding PLAIN_DICTIONARY), and its dictionary page body
+ * (PLAIN values in index order) is row npages + chunk of column 0. All other chunks (too many distinct values,
+ * strings, booleans, max_dict = 0) are PLAIN exactly as above and their dictionary row is empty. Column 1: NULLs
+ * per page for rows < npages, dictionary entries (0 = PLAIN chunk) for rows npages .. npages + nchunks - 1. */
+int32_t hs_parquet_encode_pages(hs_ctx* ctx, const hs_column* col, int32_t optional,
+                                const int64_t* page_rows, int32_t npages, const int32_t* page_chunk,
+                                int32_t nchunks, int32_t max_dict, hs_table** out);
+
 /* ---- K5: Parquet pages decoded on the device ---------------------------------
  * The read side of the same files: what Spark's ParquetFileFormat reader does under the bucketed scan the rules
  * plan (HS/index/rules/RuleUtils.scala:280-286). One call decodes ONE column over all the pages handed in (any

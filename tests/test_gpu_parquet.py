@@ -72,13 +72,99 @@ def test_files_read_back_by_pyarrow(ctx, tmp_path, monkeypatch, n, page_rows):
             assert g.equals(want), f"column {names[i]} of bucket {b} differs"
 
 
-def test_index_written_by_the_gpu_encoder_serves_queries(tmp_path, hs):
-    """createIndex with hsgpu.index.fileWriter = gpu-plain: files are named and laid out as Spark expects, and
+def _low_cardinality(n, seed):
+    rng = np.random.default_rng(seed)
+    m = lambda p: rng.random(n) < p
+    few64 = np.array([-1, 0, 1, 2**63 - 1, -2**63, 42, 7_000_000_000], dtype=np.int64)     # -1 = the table's empty marker
+    return [
+        pa.array(few64[rng.integers(0, len(few64), size=n)], mask=m(0.2)),
+        pa.array(rng.integers(0, 300, size=n).astype(np.int32) - 1),                        # int32 -1 as well
+        pa.array(np.array([0.0, -0.0, np.nan, 1.5, -np.inf])[rng.integers(0, 5, size=n)], mask=m(0.1)),
+        pa.array(np.float32([0.25, 0.5])[rng.integers(0, 2, size=n)]),
+        pa.array(rng.integers(-2**62, 2**62, size=n)),                                      # high cardinality: PLAIN (if n is large)
+        pa.array(np.full(n, 5, dtype=np.int64)),                                            # one distinct value
+        pa.array([None] * n, type=pa.int32()),                                              # no values at all: PLAIN
+        pa.array(rng.integers(0, 40, size=n).astype(np.int32), type=pa.int32()).cast(pa.date32()),
+        pa.array([f"s{i % 7}" for i in range(n)]),                                          # strings stay PLAIN
+        pa.array(rng.random(n) < 0.5),
+    ]
+
+
+@pytest.mark.parametrize("n,page_rows,max_dict", [(1, 1 << 20, 16), (3000, 256, 512), (50000, 4096, 256), (50000, 1 << 20, 32768)])
+def test_dictionary_encoded_files_read_back(ctx, tmp_path, monkeypatch, n, page_rows, max_dict):
+    """hs_parquet_encode_pages: chunks with few distinct values carry a dictionary page and bit-packed indices;
+    pyarrow AND the device reader (hs_parquet_decode_pages) return the rows bit for bit (-0.0, NaN payloads and
+    the all-ones value included), and chunks past max_dict fall back to PLAIN."""
+    from hyperspace_1_b200 import parquet_plain, parquet_read
+    monkeypatch.setattr(parquet_plain, "PAGE_ROWS", page_rows)
+    cols = _low_cardinality(n, n + max_dict)
+    names = [f"c{i}" for i in range(len(cols))]
+    cuts = sorted(set([0, n] + [int(x) for x in np.random.default_rng(2).integers(0, n + 1, size=4)]))
+    boff = np.array(cuts[:1] + cuts + [n], dtype=np.int64)
+    files = parquet_plain.write_buckets_plain(ctx, cols, names, boff, str(tmp_path / "out"), max_dict=max_dict)
+    from hyperspace_1_b200 import log_entry as le
+    files = sorted(files, key=le.bucket_id_of)
+    nonempty = [b for b in range(len(boff) - 1) if boff[b + 1] > boff[b]]
+    assert len(files) == len(nonempty)
+    dict_chunks = plain_chunks = 0
+    for f, b in zip(files, nonempty):
+        pf = pq.ParquetFile(f)
+        got = pf.read()
+        rg = pf.metadata.row_group(0)
+        for i, c in enumerate(cols):
+            want = c.slice(int(boff[b]), int(boff[b + 1] - boff[b]))
+            g = got.column(i).combine_chunks()
+            if pa.types.is_floating(want.type):      # compare the bit patterns: NaN != NaN, -0.0 == 0.0 otherwise
+                assert g.is_valid().equals(want.is_valid())
+                gv = np.frombuffer(g.buffers()[1], dtype=f"<u{want.type.bit_width // 8}", count=len(g), offset=g.offset * want.type.bit_width // 8)
+                wv = np.frombuffer(want.buffers()[1], dtype=gv.dtype, count=len(want), offset=want.offset * want.type.bit_width // 8)
+                ok = np.asarray(want.is_valid())
+                assert np.array_equal(gv[ok], wv[ok]), f"column {names[i]} of bucket {b} differs"
+            else:
+                assert g.equals(want), f"column {names[i]} of bucket {b} differs"
+            if rg.column(i).has_dictionary_page:
+                dict_chunks += 1
+                assert "PLAIN_DICTIONARY" in rg.column(i).encodings or "RLE_DICTIONARY" in rg.column(i).encodings
+            else:
+                plain_chunks += 1
+    assert plain_chunks > 0 and dict_chunks > 0
+    # the device reader over the same files
+    arrays, rnames, rows = parquet_read.decode_files(ctx, files)
+    assert rnames == names and rows == [int(boff[b + 1] - boff[b]) for b in nonempty]
+    for i, c in enumerate(cols):
+        g = arrays[i]
+        if pa.types.is_floating(c.type):
+            assert g.is_valid().equals(c.is_valid())
+            ok = np.asarray(c.is_valid())
+            u = f"<u{c.type.bit_width // 8}"
+            assert np.array_equal(np.frombuffer(g.buffers()[1], dtype=u, count=len(c))[ok], np.frombuffer(c.buffers()[1], dtype=u, count=len(c))[ok])
+        else:
+            assert g.cast(c.type).equals(c), f"device reader: column {names[i]} differs"
+
+
+def test_encode_pages_rejects_bad_arguments(ctx):
+    from hyperspace_1_b200 import HyperspaceException
+    a = pa.array(np.arange(10, dtype=np.int64))
+    with pytest.raises(HyperspaceException):
+        ctx.parquet_encode_pages(a, True, [0, 5, 10], [1, 0], 2, 16)          # chunks out of order
+    with pytest.raises(HyperspaceException):
+        ctx.parquet_encode_pages(a, True, [0, 5, 10], [0, 2], 2, 16)          # chunk id past nchunks
+    with pytest.raises(HyperspaceException):
+        ctx.parquet_encode_pages(a, True, [0, 5, 10], [0, 1], 2, 1 << 20)     # max_dict too large
+    pages, nulls, dbody, dcount = ctx.parquet_encode_pages(a, True, [0, 5, 10], [0, 1], 2, 4)
+    assert list(dcount) == [0, 0] and dbody == [b"", b""] and list(nulls) == [0, 0]     # 5 distinct > 4: PLAIN
+    plain, _ = ctx.parquet_plain_pages(a, True, [0, 5, 10])
+    assert pages == plain
+
+
+@pytest.mark.parametrize("writer", ["gpu-plain", "gpu-dictionary"])
+def test_index_written_by_the_gpu_encoder_serves_queries(tmp_path, hs, writer):
+    """createIndex with hsgpu.index.fileWriter = gpu-plain / gpu-dictionary: files are named and laid out as Spark expects, and
     the quick-start style queries over them return what the plain queries return."""
     from hyperspace_1_b200 import Hyperspace, IndexConfig, Session, log_entry as le
     s = Session(system_path=str(tmp_path / "indexes"))
     s.conf["spark.hyperspace.index.numBuckets"] = "8"
-    s.conf["hsgpu.index.fileWriter"] = "gpu-plain"
+    s.conf["hsgpu.index.fileWriter"] = writer
     lcols, keys = lineitem(3000, null_frac=0.02)
     os.makedirs(tmp_path / "lineitem")
     pq.write_table(pa.table(lcols, names=["l_orderkey", "l_extendedprice", "l_discount"]), tmp_path / "lineitem" / "part-0.parquet")

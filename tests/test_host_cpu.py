@@ -359,13 +359,70 @@ def test_parquet_framing_reads_back_with_pyarrow(tmp_path):
                 hdr = pp.page_header(e - a, len(body))
                 f.write(hdr + body)
                 pos += len(hdr) + len(body)
-            chunks.append((start, pos - start, len(arr)))
+            chunks.append((start, pos - start, len(arr), None))
         foot = pp.footer(names, types, 7, chunks, le.schema_json(pa.schema([pa.field(n, t) for n, t in zip(names, types)])))
         f.write(foot + struct.pack("<I", len(foot)) + pp.MAGIC)
     got = pq.ParquetFile(path).read()
     assert got.column_names == names
     for n in names:
         assert got[n].to_pylist() == cols[n].to_pylist()
+
+
+def test_dictionary_page_framing_is_read_by_pyarrow(tmp_path):
+    """The layout hs_parquet_encode_pages produces for a dictionary-encoded chunk, assembled here by hand: a
+    PLAIN dictionary page, then data pages = definition levels ++ bit width ++ ONE bit-packed run of the indices
+    (last group zero-padded). pyarrow must read the rows back; this pins the framing (headers, footer offsets)
+    without a GPU."""
+    import struct
+    import pyarrow.parquet as pq
+    from hyperspace_1_b200 import log_entry as le, parquet_plain as pp
+
+    def varint(v):
+        out = bytearray()
+        while v >= 0x80:
+            out.append((v & 0x7F) | 0x80)
+            v >>= 7
+        out.append(v)
+        return bytes(out)
+
+    def def_levels(valid):
+        groups = (len(valid) + 7) // 8
+        body = varint((groups << 1) | 1) + np.packbits(np.asarray(valid, dtype=np.uint8), bitorder="little").tobytes()
+        return struct.pack("<I", len(body)) + body
+
+    def packed(idx, bw):
+        bits = np.zeros(((len(idx) + 7) // 8) * 8 * bw, dtype=np.uint8)
+        for j, x in enumerate(idx):
+            for k in range(bw):
+                bits[j * bw + k] = (x >> k) & 1
+        return bytes([bw]) + varint((((len(idx) + 7) // 8) << 1) | 1) + np.packbits(bits, bitorder="little").tobytes()
+
+    rng = np.random.default_rng(5)
+    dictionary = np.array([-7, 3, 2**40, 11, 0], dtype="<i8")
+    idx = rng.integers(0, len(dictionary), size=29)
+    valid = rng.random(29) < 0.8
+    values = [int(dictionary[i]) if v else None for i, v in zip(idx, valid)]
+    pages = [(0, 13), (13, 29)]
+    path = tmp_path / "d.parquet"
+    with open(path, "wb") as f:
+        f.write(pp.MAGIC)
+        dbody = dictionary.tobytes()
+        hdr = pp.dictionary_page_header(len(dictionary), len(dbody))
+        f.write(hdr + dbody)
+        pos = 4 + len(hdr) + len(dbody)
+        data_off = pos
+        for a, e in pages:
+            body = def_levels(valid[a:e]) + packed([int(i) for i, v in zip(idx[a:e], valid[a:e]) if v], 3)
+            hdr = pp.page_header(e - a, len(body), pp.ENC_PLAIN_DICTIONARY)
+            f.write(hdr + body)
+            pos += len(hdr) + len(body)
+        names, types = ["k"], [pa.int64()]
+        foot = pp.footer(names, types, 29, [(4, pos - 4, 29, data_off)], le.schema_json(pa.schema([pa.field("k", pa.int64())])))
+        f.write(foot + struct.pack("<I", len(foot)) + pp.MAGIC)
+    pf = pq.ParquetFile(path)
+    col = pf.metadata.row_group(0).column(0)
+    assert col.has_dictionary_page and col.dictionary_page_offset == 4 and col.data_page_offset == data_off
+    assert pf.read()["k"].to_pylist() == values
 
 
 def test_refresh_and_optimize_decisions_without_a_gpu(tmp_path, oracle):
