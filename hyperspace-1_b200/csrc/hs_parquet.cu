@@ -360,17 +360,21 @@ static int varint(uint64_t v, uint8_t* out) {
 
 // page_chunk / nchunks / max_dict: dictionary encoding per column chunk (max_dict = 0: PLAIN only)
 static void pq_encode(hs_ctx* ctx, const hs_column* col, int32_t optional, const int64_t* page_rows, int32_t npages,
-                      const int32_t* page_chunk, int32_t nchunks, int32_t max_dict, hs_table** out) {
+                      const int32_t* page_chunk, int32_t nchunks, int32_t max_dict, int32_t codec, hs_table** out) {
   if (!out) HS_THROW(HS_EINVAL, "null out");
   *out = nullptr;
+  if (codec != 0 && codec != 1) HS_THROW(HS_EUNSUPPORTED, "codec must be 0 (UNCOMPRESSED) or 1 (SNAPPY)");
   if (!col || !page_rows || npages <= 0 || npages > 65535) HS_THROW(HS_EINVAL, "bad page list (1..65535 pages per call)");
-  if (max_dict > 0) {
-    if (!page_chunk || nchunks <= 0 || nchunks > npages) HS_THROW(HS_EINVAL, "dictionary encoding needs the chunk of every page");
-    if (max_dict > 32768) HS_THROW(HS_EINVAL, "max_dict is at most 32768 entries");
+  if (max_dict < 0 || max_dict > 32768) HS_THROW(HS_EINVAL, "max_dict is at most 32768 entries");
+  if (page_chunk) {
+    if (nchunks <= 0 || nchunks > npages) HS_THROW(HS_EINVAL, "nchunks must be in 1..npages");
     for (int p = 0; p < npages; p++)
       if (page_chunk[p] < 0 || page_chunk[p] >= nchunks || (p && page_chunk[p] < page_chunk[p - 1]))
         HS_THROW(HS_EINVAL, "page_chunk must be non-decreasing and inside [0, nchunks)");
-  } else nchunks = 0;
+  } else {
+    if (max_dict > 0) HS_THROW(HS_EINVAL, "dictionary encoding needs the chunk of every page");
+    nchunks = 0;
+  }
   hs_stages_reset(ctx);
   DevCol dc;
   {
@@ -502,19 +506,19 @@ static void pq_encode(hs_ctx* ctx, const hs_column* col, int32_t optional, const
   }
   page_off[nout] = (int64_t)at;
   if (at >= 0x7FFFFFF0ull) HS_THROW(HS_EUNSUPPORTED, "more than 2 GiB of page data in one call: encode fewer rows at a time");
-  std::vector<OutCol> ocols(2);
+  std::vector<OutCol> ocols(codec ? 3 : 2);
   OutCol& body = ocols[0];
   body.type = HS_BINARY;
   body.length = nout;
   body.data_bytes = (int64_t)at;
-  body.data.alloc(ctx, (size_t)at + 8);
+  body.data.alloc(ctx, (size_t)at + 32);   // slack: the compressor reads whole 16-byte words
   body.offsets.alloc(ctx, ((size_t)nout + 1) * 4);
   {
     Stage s(ctx, "parquet_encode");
     std::vector<int32_t> off32((size_t)nout + 1);
     for (int p = 0; p <= nout; p++) off32[p] = (int32_t)page_off[p];
     CK(cudaMemcpyAsync(body.offsets.p, off32.data(), off32.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
-    if (is_bool) CK(cudaMemsetAsync(body.data.p, 0, (size_t)at + 8, ctx->stream));
+    if (is_bool) CK(cudaMemsetAsync(body.data.p, 0, (size_t)at + 32, ctx->stream));
     for (auto& h : headers)
       CK(cudaMemcpyAsync((uint8_t*)body.data.p + h.first, h.second.data(), h.second.size(), cudaMemcpyHostToDevice, ctx->stream));
     DBuf d_val(ctx, (size_t)npages * 8), d_def(ctx, (size_t)npages * 8);
@@ -562,6 +566,66 @@ static void pq_encode(hs_ctx* ctx, const hs_column* col, int32_t optional, const
     }
     hs_sync(ctx);   // headers, val_off, def_off are host vectors: the copies above must have left them
   }
+  if (codec == 1) {
+    // ---- snappy: every row of column 0 (pages and dictionary pages) compressed on its own
+    Stage s(ctx, "parquet_snappy");
+    std::vector<SnFrag> frags;
+    std::vector<int32_t> frag_first((size_t)nout + 1, 0);
+    for (int r = 0; r < nout; r++) {
+      frag_first[r] = (int32_t)frags.size();
+      for (int64_t a = page_off[r]; a < page_off[r + 1]; a += SN_FRAG)
+        frags.push_back(SnFrag{(uint64_t)a, (uint32_t)std::min<int64_t>(SN_FRAG, page_off[r + 1] - a), 0});
+    }
+    const int nfrag = (int)frags.size();
+    frag_first[nout] = nfrag;
+    std::vector<int64_t> usize((size_t)nout), coff((size_t)nout + 1, 0);
+    for (int r = 0; r < nout; r++) usize[r] = page_off[r + 1] - page_off[r];
+    OutCol& us = ocols[2];
+    us.type = HS_INT64;
+    us.length = nout;
+    us.data_bytes = (int64_t)nout * 8;
+    us.data.alloc(ctx, (size_t)nout * 8);
+    CK(cudaMemcpyAsync(us.data.p, usize.data(), (size_t)nout * 8, cudaMemcpyHostToDevice, ctx->stream));
+    DBuf packed;
+    std::vector<std::pair<uint64_t, std::vector<uint8_t>>> pre;
+    if (nfrag > 0) {
+      DBuf d_frags(ctx, (size_t)nfrag * sizeof(SnFrag)), d_sizes(ctx, (size_t)nfrag * 4), d_dst(ctx, (size_t)nfrag * 8);
+      DBuf scratch(ctx, (size_t)nfrag * SN_SLOT);
+      CK(cudaMemcpyAsync(d_frags.p, frags.data(), (size_t)nfrag * sizeof(SnFrag), cudaMemcpyHostToDevice, ctx->stream));
+      const size_t smem = sizeof(SnWarp) * SN_WARPS;
+      CK(cudaFuncSetAttribute(k_snappy_frag, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      LAUNCH(ctx, k_snappy_frag, (unsigned)((nfrag + SN_WARPS - 1) / SN_WARPS), SN_WARPS * 32, smem, body.data.as<uint8_t>(),
+             d_frags.as<SnFrag>(), nfrag, scratch.as<uint8_t>(), d_sizes.as<uint32_t>());
+      std::vector<uint32_t> sizes((size_t)nfrag);
+      CK(cudaMemcpyAsync(sizes.data(), d_sizes.p, (size_t)nfrag * 4, cudaMemcpyDeviceToHost, ctx->stream));
+      hs_sync(ctx);
+      std::vector<uint64_t> dst((size_t)nfrag);
+      uint64_t cat = 0;
+      for (int r = 0; r < nout; r++) {
+        coff[r] = (int64_t)cat;
+        if (usize[r] == 0) continue;               // an empty row stays empty (no dictionary for this chunk)
+        std::vector<uint8_t> v(10);
+        v.resize((size_t)varint((uint64_t)usize[r], v.data()));
+        cat += v.size();
+        pre.emplace_back((uint64_t)coff[r], std::move(v));
+        for (int f = frag_first[r]; f < frag_first[r + 1]; f++) { dst[f] = cat; cat += sizes[f]; }
+      }
+      coff[nout] = (int64_t)cat;
+      if (cat >= 0x7FFFFFF0ull) HS_THROW(HS_EUNSUPPORTED, "more than 2 GiB of compressed page data in one call");
+      packed.alloc(ctx, (size_t)cat + 16);
+      CK(cudaMemcpyAsync(d_dst.p, dst.data(), (size_t)nfrag * 8, cudaMemcpyHostToDevice, ctx->stream));
+      for (auto& h : pre)
+        CK(cudaMemcpyAsync((uint8_t*)packed.p + h.first, h.second.data(), h.second.size(), cudaMemcpyHostToDevice, ctx->stream));
+      LAUNCH(ctx, k_snappy_pack, (unsigned)((nfrag + 7) / 8), 256, 0, scratch.as<uint8_t>(), d_sizes.as<uint32_t>(), d_dst.as<uint64_t>(),
+             nfrag, packed.as<uint8_t>());
+      std::vector<int32_t> off32((size_t)nout + 1);
+      for (int r = 0; r <= nout; r++) off32[r] = (int32_t)coff[r];
+      CK(cudaMemcpyAsync(body.offsets.p, off32.data(), off32.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+      hs_sync(ctx);
+      body.data = std::move(packed);
+      body.data_bytes = (int64_t)cat;
+    }
+  }
   OutCol& nn = ocols[1];
   nn.type = HS_INT64;
   nn.length = nout;
@@ -576,14 +640,14 @@ static void pq_encode(hs_ctx* ctx, const hs_column* col, int32_t optional, const
 extern "C" int32_t hs_parquet_plain_pages(hs_ctx* ctx, const hs_column* col, int32_t optional, const int64_t* page_rows,
                                           int32_t npages, hs_table** out) {
   API_BEGIN(ctx)
-  pq_encode(ctx, col, optional, page_rows, npages, nullptr, 0, 0, out);
+  pq_encode(ctx, col, optional, page_rows, npages, nullptr, 0, 0, 0, out);
   API_END(ctx)
 }
 
 extern "C" int32_t hs_parquet_encode_pages(hs_ctx* ctx, const hs_column* col, int32_t optional, const int64_t* page_rows,
                                            int32_t npages, const int32_t* page_chunk, int32_t nchunks, int32_t max_dict,
-                                           hs_table** out) {
+                                           int32_t codec, hs_table** out) {
   API_BEGIN(ctx)
-  pq_encode(ctx, col, optional, page_rows, npages, page_chunk, nchunks, max_dict, out);
+  pq_encode(ctx, col, optional, page_rows, npages, page_chunk, nchunks, max_dict, codec, out);
   API_END(ctx)
 }

@@ -52,13 +52,15 @@ def write_index_files(session, arrays, names, boff, out_dir):
     encodes, files are named and compressed as Spark's default writer would), "gpu-plain" (page bodies encoded
     on the device by hs_parquet_plain_pages, PLAIN + uncompressed; parquet_plain.py) or "gpu-dictionary" (the same
     through hs_parquet_encode_pages: chunks with at most hsgpu.index.dictionaryEntries distinct values — default
-    4096 — are dictionary-encoded, the rest PLAIN)."""
+    4096 — are dictionary-encoded, the rest PLAIN) or "gpu-snappy" (dictionary as before and every page
+    snappy-compressed on the device: Spark's default file format end to end)."""
     t0 = time.perf_counter()
     writer = session.conf.get("hsgpu.index.fileWriter", "pyarrow-snappy")
-    if writer in ("gpu-plain", "gpu-dictionary"):
+    if writer in ("gpu-plain", "gpu-dictionary", "gpu-snappy"):
         from .parquet_plain import write_buckets_plain
-        max_dict = int(session.conf.get("hsgpu.index.dictionaryEntries", "4096")) if writer == "gpu-dictionary" else 0
-        files = write_buckets_plain(session.ctx, arrays, names, boff, out_dir, max_dict=max_dict)
+        max_dict = int(session.conf.get("hsgpu.index.dictionaryEntries", "4096")) if writer != "gpu-plain" else 0
+        files = write_buckets_plain(session.ctx, arrays, names, boff, out_dir, max_dict=max_dict,
+                                    codec=1 if writer == "gpu-snappy" else 0)
         return files, time.perf_counter() - t0
     return write_buckets(arrays, names, boff, out_dir)
 

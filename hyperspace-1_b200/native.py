@@ -276,8 +276,9 @@ class Context:
         finally:
             t.free()
 
-    def parquet_encode_pages(self, array, optional, page_rows, page_chunk, nchunks, max_dict):
-        """hs_parquet_encode_pages -> (page bodies, NULLs per page, dictionary page bodies, entries per chunk)."""
+    def parquet_encode_pages(self, array, optional, page_rows, page_chunk, nchunks, max_dict, codec=0):
+        """hs_parquet_encode_pages -> (page bodies, NULLs per page, dictionary page bodies, entries per chunk); with
+        codec = 1 (snappy) a fifth element: uncompressed sizes of the pages ++ of the dictionary pages."""
         cs = abi.ColumnSet([array])
         pr = np.ascontiguousarray(page_rows, dtype=np.int64)
         pc = np.ascontiguousarray(page_chunk, dtype=np.int32)
@@ -286,13 +287,15 @@ class Context:
         self._check(self._lib.hs_parquet_encode_pages(self._h, cs.ptr(), C.c_int32(1 if optional else 0),
                                                       pr.ctypes.data_as(C.POINTER(C.c_int64)), C.c_int32(npages),
                                                       pc.ctypes.data_as(C.POINTER(C.c_int32)), C.c_int32(nchunks),
-                                                      C.c_int32(max_dict), C.byref(out)), "hs_parquet_encode_pages")
+                                                      C.c_int32(max_dict), C.c_int32(codec), C.byref(out)),
+                    "hs_parquet_encode_pages")
         t = Table(self, out)
         try:
-            bodies, counts = t.to_arrow()
-            bodies = [b.as_py() for b in bodies]
-            counts = counts.to_numpy()
-            return bodies[:npages], counts[:npages], bodies[npages:], counts[npages:]
+            cols = t.to_arrow()
+            bodies = [b.as_py() for b in cols[0]]
+            counts = cols[1].to_numpy()
+            res = (bodies[:npages], counts[:npages], bodies[npages:], counts[npages:])
+            return res + (cols[2].to_numpy(),) if codec else res
         finally:
             t.free()
 

@@ -123,10 +123,10 @@ def physical_type(t):
     raise TypeError(f"no PLAIN Parquet mapping for {t}")
 
 
-def dictionary_page_header(num_entries, body_len):
+def dictionary_page_header(num_entries, body_len, uncompressed_len=None):
     t = _Thrift()
     t.i32(1, 2)                       # type = DICTIONARY_PAGE
-    t.i32(2, body_len)
+    t.i32(2, body_len if uncompressed_len is None else uncompressed_len)
     t.i32(3, body_len)
     t.struct_begin(7)                 # dictionary_page_header
     t.i32(1, num_entries)
@@ -136,11 +136,11 @@ def dictionary_page_header(num_entries, body_len):
     return bytes(t.b)
 
 
-def page_header(num_values, body_len, encoding=ENC_PLAIN):
+def page_header(num_values, body_len, encoding=ENC_PLAIN, uncompressed_len=None):
     t = _Thrift()
     t.i32(1, 0)                       # type = DATA_PAGE
-    t.i32(2, body_len)                # uncompressed_page_size
-    t.i32(3, body_len)                # compressed_page_size (codec UNCOMPRESSED)
+    t.i32(2, body_len if uncompressed_len is None else uncompressed_len)   # uncompressed_page_size
+    t.i32(3, body_len)                # compressed_page_size (= the body as stored)
     t.struct_begin(5)                 # data_page_header
     t.i32(1, num_values)
     t.i32(2, encoding)
@@ -151,9 +151,9 @@ def page_header(num_values, body_len, encoding=ENC_PLAIN):
     return bytes(t.b)
 
 
-def footer(names, types, num_rows, chunks, spark_schema_json):
+def footer(names, types, num_rows, chunks, spark_schema_json, codec=0):
     """chunks: per column (chunk start, total bytes, num_values, first data page offset if the chunk starts with a
-    dictionary page else None)."""
+    dictionary page else None[, total uncompressed bytes])."""
     t = _Thrift()
     t.i32(1, 1)                                           # version
     t.list_begin(2, _Thrift.STRUCT, len(names) + 1)       # schema
@@ -175,7 +175,9 @@ def footer(names, types, num_rows, chunks, spark_schema_json):
     t.struct_begin()
     t.list_begin(1, _Thrift.STRUCT, len(names))           # columns
     total = 0
-    for name, ty, (off, nbytes, nvals, data_off) in zip(names, types, chunks):
+    for name, ty, chunk in zip(names, types, chunks):
+        off, nbytes, nvals, data_off = chunk[:4]
+        ubytes = chunk[4] if len(chunk) > 4 else nbytes
         phys, _, _ = physical_type(ty)
         t.struct_begin()
         t.i64(2, off)                                     # file_offset
@@ -187,16 +189,16 @@ def footer(names, types, num_rows, chunks, spark_schema_json):
             t.elem_i32(e)
         t.list_begin(3, _Thrift.BINARY, 1)
         t.elem_string(name)
-        t.i32(4, 0)                                       # codec UNCOMPRESSED
+        t.i32(4, codec)                                   # 0 UNCOMPRESSED, 1 SNAPPY
         t.i64(5, nvals)
-        t.i64(6, nbytes)
-        t.i64(7, nbytes)
+        t.i64(6, ubytes)                                  # total_uncompressed_size (page headers included)
+        t.i64(7, nbytes)                                  # total_compressed_size
         t.i64(9, off if data_off is None else data_off)   # data_page_offset
         if data_off is not None:
             t.i64(11, off)                                # dictionary_page_offset
         t.struct_end()
         t.struct_end()
-        total += nbytes
+        total += ubytes
     t.i64(2, total)
     t.i64(3, num_rows)
     t.struct_end()
@@ -210,11 +212,12 @@ def footer(names, types, num_rows, chunks, spark_schema_json):
     return bytes(t.b)
 
 
-def write_buckets_plain(ctx, columns, names, bucket_offsets, out_dir, task_of_bucket=None, max_dict=0):
+def write_buckets_plain(ctx, columns, names, bucket_offsets, out_dir, task_of_bucket=None, max_dict=0, codec=0):
     """The GPU counterpart of index_writer.write_buckets: rows [off[b], off[b+1]) of every non-empty bucket b go
     to part-<task%05d>-<uuid>_<bucket%05d>.c000.parquet (Spark's name for an uncompressed bucketed file; the
     bucket id is parsed from it by BucketingUtils.getBucketId either way). max_dict > 0: column chunks with at most
-    that many distinct values are dictionary-encoded. Returns the files."""
+    that many distinct values are dictionary-encoded. codec = 1: pages snappy-compressed on the device and the
+    files named .c000.snappy.parquet, as Spark's default codec names them. Returns the files."""
     os.makedirs(out_dir, exist_ok=True)
     job = uuid.uuid4()
     off = np.asarray(bucket_offsets, dtype=np.int64)
@@ -230,11 +233,16 @@ def write_buckets_plain(ctx, columns, names, bucket_offsets, out_dir, task_of_bu
             page_chunk.append(chunk_of.setdefault(b, len(chunk_of)))
     if not page_bucket:
         return []
-    bodies, nvals, dicts, dict_entries = [], [], [], []
+    bodies, nvals, dicts, dict_entries, usizes = [], [], [], [], []
+    npages = len(page_bucket)
     for c in columns:
         _, _, feed = physical_type(c.type)
         arr = c if feed == c.type else c.cast(feed)
-        if max_dict > 0:
+        usize = None
+        if codec:
+            pages, _, dbody, dcount, usize = ctx.parquet_encode_pages(arr, True, page_rows, page_chunk, len(chunk_of),
+                                                                       max_dict, codec)
+        elif max_dict > 0:
             pages, _, dbody, dcount = ctx.parquet_encode_pages(arr, True, page_rows, page_chunk, len(chunk_of), max_dict)
         else:
             pages, _ = ctx.parquet_plain_pages(arr, True, page_rows)
@@ -242,6 +250,7 @@ def write_buckets_plain(ctx, columns, names, bucket_offsets, out_dir, task_of_bu
         bodies.append(pages)
         dicts.append(dbody)
         dict_entries.append(dcount)
+        usizes.append(usize)
         nvals.append(np.diff(np.asarray(page_rows, dtype=np.int64)))
     schema_json = le.schema_json(pa.schema([pa.field(n, t) for n, t in zip(names, types)]))
     files = []
@@ -250,30 +259,35 @@ def write_buckets_plain(ctx, columns, names, bucket_offsets, out_dir, task_of_bu
         pages_of.setdefault(b, []).append(p)
     for b, plist in pages_of.items():
         task = b if task_of_bucket is None else task_of_bucket(b)
-        path = os.path.join(out_dir, f"part-{task:05d}-{job}_{b:05d}.c000.parquet")
+        path = os.path.join(out_dir, f"part-{task:05d}-{job}_{b:05d}.c000{'.snappy' if codec else ''}.parquet")
         with open(path, "wb") as f:
             f.write(MAGIC)
             pos = 4
             chunks = []
             for ci in range(len(columns)):
-                start, nv, data_off = pos, 0, None
+                start, nv, data_off, upos = pos, 0, None, 0
+                us = usizes[ci]
                 entries = int(dict_entries[ci][chunk_of[b]])
                 if entries:
                     dbody = dicts[ci][chunk_of[b]]
-                    hdr = dictionary_page_header(entries, len(dbody))
+                    ulen = len(dbody) if us is None else int(us[npages + chunk_of[b]])
+                    hdr = dictionary_page_header(entries, len(dbody), ulen)
                     f.write(hdr)
                     f.write(dbody)
                     pos += len(hdr) + len(dbody)
+                    upos += len(hdr) + ulen
                     data_off = pos
                 for p in plist:
                     body = bodies[ci][p]
-                    hdr = page_header(int(nvals[ci][p]), len(body), ENC_PLAIN_DICTIONARY if entries else ENC_PLAIN)
+                    ulen = len(body) if us is None else int(us[p])
+                    hdr = page_header(int(nvals[ci][p]), len(body), ENC_PLAIN_DICTIONARY if entries else ENC_PLAIN, ulen)
                     f.write(hdr)
                     f.write(body)
                     pos += len(hdr) + len(body)
+                    upos += len(hdr) + ulen
                     nv += int(nvals[ci][p])
-                chunks.append((start, pos - start, nv, data_off))
-            foot = footer(names, types, int(off[b + 1] - off[b]), chunks, schema_json)
+                chunks.append((start, pos - start, nv, data_off, upos))
+            foot = footer(names, types, int(off[b + 1] - off[b]), chunks, schema_json, codec)
             f.write(foot)
             f.write(struct.pack("<I", len(foot)))
             f.write(MAGIC)

@@ -277,10 +277,13 @@ int32_t hs_parquet_plain_pages(hs_ctx* ctx, const hs_column* col, int32_t option
  * width byte] ++ [one bit-packed run of the indices] (encoding PLAIN_DICTIONARY), and its dictionary page body
  * (PLAIN values in index order) is row npages + chunk of column 0. All other chunks (too many distinct values,
  * strings, booleans, max_dict = 0) are PLAIN exactly as above and their dictionary row is empty. Column 1: NULLs
- * per page for rows < npages, dictionary entries (0 = PLAIN chunk) for rows npages .. npages + nchunks - 1. */
+ * per page for rows < npages, dictionary entries (0 = PLAIN chunk) for rows npages .. npages + nchunks - 1.
+ * codec: 0 UNCOMPRESSED, or 1 SNAPPY (Spark's default, spark.sql.parquet.compression.codec): every body of
+ * column 0 is then the raw snappy stream of the page (length preamble, literals and copies; any snappy
+ * decompressor reads it), and a third column (INT64) gives the uncompressed size the page header needs. */
 int32_t hs_parquet_encode_pages(hs_ctx* ctx, const hs_column* col, int32_t optional,
                                 const int64_t* page_rows, int32_t npages, const int32_t* page_chunk,
-                                int32_t nchunks, int32_t max_dict, hs_table** out);
+                                int32_t nchunks, int32_t max_dict, int32_t codec, hs_table** out);
 
 /* ---- K5: Parquet pages decoded on the device ---------------------------------
  * The read side of the same files: what Spark's ParquetFileFormat reader does under the bucketed scan the rules

@@ -90,8 +90,9 @@ def _low_cardinality(n, seed):
     ]
 
 
+@pytest.mark.parametrize("codec", [0, 1])
 @pytest.mark.parametrize("n,page_rows,max_dict", [(1, 1 << 20, 16), (3000, 256, 512), (50000, 4096, 256), (50000, 1 << 20, 32768)])
-def test_dictionary_encoded_files_read_back(ctx, tmp_path, monkeypatch, n, page_rows, max_dict):
+def test_dictionary_encoded_files_read_back(ctx, tmp_path, monkeypatch, n, page_rows, max_dict, codec):
     """hs_parquet_encode_pages: chunks with few distinct values carry a dictionary page and bit-packed indices;
     pyarrow AND the device reader (hs_parquet_decode_pages) return the rows bit for bit (-0.0, NaN payloads and
     the all-ones value included), and chunks past max_dict fall back to PLAIN."""
@@ -101,9 +102,10 @@ def test_dictionary_encoded_files_read_back(ctx, tmp_path, monkeypatch, n, page_
     names = [f"c{i}" for i in range(len(cols))]
     cuts = sorted(set([0, n] + [int(x) for x in np.random.default_rng(2).integers(0, n + 1, size=4)]))
     boff = np.array(cuts[:1] + cuts + [n], dtype=np.int64)
-    files = parquet_plain.write_buckets_plain(ctx, cols, names, boff, str(tmp_path / "out"), max_dict=max_dict)
+    files = parquet_plain.write_buckets_plain(ctx, cols, names, boff, str(tmp_path / "out"), max_dict=max_dict, codec=codec)
     from hyperspace_1_b200 import log_entry as le
     files = sorted(files, key=le.bucket_id_of)
+    assert all(f.endswith(".c000.snappy.parquet" if codec else ".c000.parquet") for f in files)
     nonempty = [b for b in range(len(boff) - 1) if boff[b + 1] > boff[b]]
     assert len(files) == len(nonempty)
     dict_chunks = plain_chunks = 0
@@ -112,6 +114,7 @@ def test_dictionary_encoded_files_read_back(ctx, tmp_path, monkeypatch, n, page_
         got = pf.read()
         rg = pf.metadata.row_group(0)
         for i, c in enumerate(cols):
+            assert rg.column(i).compression == ("SNAPPY" if codec else "UNCOMPRESSED")
             want = c.slice(int(boff[b]), int(boff[b + 1] - boff[b]))
             g = got.column(i).combine_chunks()
             if pa.types.is_floating(want.type):      # compare the bit patterns: NaN != NaN, -0.0 == 0.0 otherwise
@@ -142,6 +145,50 @@ def test_dictionary_encoded_files_read_back(ctx, tmp_path, monkeypatch, n, page_
             assert g.cast(c.type).equals(c), f"device reader: column {names[i]} differs"
 
 
+def _snappy_inputs():
+    rng = np.random.default_rng(9)
+    text = (b"the quick brown fox jumps over the lazy dog; " * 400)
+    return {
+        "random": rng.integers(0, 256, size=40000).astype(np.uint8).tobytes(),          # literals only, 3-byte headers
+        "zeros": bytes(70000),                                                          # one long overlapping copy per fragment
+        "period3": b"abc" * 9000,
+        "period40": bytes(range(40)) * 700,
+        "text": text,
+        "mixed": b"".join(text[i * 37:i * 37 + 90] + rng.integers(0, 256, size=int(rng.integers(0, 70))).astype(np.uint8).tobytes()
+                          for i in range(300)),
+        "tiny": b"ab",
+        "one": b"x",
+        "fragment_edge": b"0123456789abcdef" * 512 + b"Z",                             # 8193 bytes: a 1-byte second fragment
+        "small_ints": np.arange(20000, dtype="<i8").tobytes(),
+    }
+
+
+def test_snappy_pages_are_valid_snappy(ctx):
+    """codec = 1: every body is a raw snappy stream that an independent decompressor (pyarrow's) turns back into
+    exactly the uncompressed body of the codec = 0 call; compressible inputs do get smaller."""
+    inputs = _snappy_inputs()
+    arr = pa.array(list(inputs.values()), type=pa.binary())
+    n = len(arr)
+    rows = list(range(n + 1))                                       # one page per value
+    plain, _ = ctx.parquet_plain_pages(arr, True, rows)
+    pages, nulls, dbody, dcount, usize = ctx.parquet_encode_pages(arr, True, rows, list(range(n)), n, 0, 1)
+    assert list(dcount) == [0] * n and all(d == b"" for d in dbody) and list(usize[n:]) == [0] * n
+    codec = pa.Codec("snappy")
+    for name, p, q, u in zip(inputs, plain, pages, usize[:n]):
+        assert u == len(p), name
+        back = codec.decompress(q, decompressed_size=len(p)).to_pybytes()
+        assert back == p, f"{name}: snappy stream does not decompress to the page body"
+        if name in ("zeros", "period3", "period40", "text"):
+            assert len(q) < len(p) / 10, (name, len(q), len(p))
+        if name == "small_ints":                 # 8-byte values with six zero bytes each
+            assert len(q) < len(p) * 0.6, (name, len(q), len(p))
+        assert len(q) <= 32 + len(p) + len(p) // 6, name
+    # all of it as ONE page: fragments of a page are concatenated behind one length preamble
+    one, _ = ctx.parquet_plain_pages(arr, True, [0, n])
+    page, _, _, _, us = ctx.parquet_encode_pages(arr, True, [0, n], [0], 1, 0, 1)
+    assert codec.decompress(page[0], decompressed_size=len(one[0])).to_pybytes() == one[0] and us[0] == len(one[0])
+
+
 def test_encode_pages_rejects_bad_arguments(ctx):
     from hyperspace_1_b200 import HyperspaceException
     a = pa.array(np.arange(10, dtype=np.int64))
@@ -151,13 +198,15 @@ def test_encode_pages_rejects_bad_arguments(ctx):
         ctx.parquet_encode_pages(a, True, [0, 5, 10], [0, 2], 2, 16)          # chunk id past nchunks
     with pytest.raises(HyperspaceException):
         ctx.parquet_encode_pages(a, True, [0, 5, 10], [0, 1], 2, 1 << 20)     # max_dict too large
+    with pytest.raises(HyperspaceException):
+        ctx.parquet_encode_pages(a, True, [0, 5, 10], [0, 1], 2, 4, 2)        # codec 2 (gzip) is not written
     pages, nulls, dbody, dcount = ctx.parquet_encode_pages(a, True, [0, 5, 10], [0, 1], 2, 4)
     assert list(dcount) == [0, 0] and dbody == [b"", b""] and list(nulls) == [0, 0]     # 5 distinct > 4: PLAIN
     plain, _ = ctx.parquet_plain_pages(a, True, [0, 5, 10])
     assert pages == plain
 
 
-@pytest.mark.parametrize("writer", ["gpu-plain", "gpu-dictionary"])
+@pytest.mark.parametrize("writer", ["gpu-plain", "gpu-dictionary", "gpu-snappy"])
 def test_index_written_by_the_gpu_encoder_serves_queries(tmp_path, hs, writer):
     """createIndex with hsgpu.index.fileWriter = gpu-plain / gpu-dictionary: files are named and laid out as Spark expects, and
     the quick-start style queries over them return what the plain queries return."""
@@ -172,7 +221,7 @@ def test_index_written_by_the_gpu_encoder_serves_queries(tmp_path, hs, writer):
     hx = Hyperspace(s)
     hx.createIndex(li, IndexConfig("liIndex", ["l_orderkey"], ["l_extendedprice"]))
     files = [le.from_uri(f["name"]) for f in le.content_files(hx.index("liIndex")["content"])]
-    assert files and all(f.endswith(".c000.parquet") for f in files)
+    assert files and all(f.endswith(".c000.snappy.parquet" if writer == "gpu-snappy" else ".c000.parquet") for f in files)
     for f in files:
         k = pq.ParquetFile(f).read()["l_orderkey"]
         v = k.drop_null().to_numpy()

@@ -236,7 +236,8 @@ def main():
 def run_parquet(args):
     """K4 beside the kernels (timed separately): the files of a cfg2-shaped index written by the
     host library (pyarrow, snappy, what index_writer does by default) and by the device encoder
-    (hs_parquet_plain_pages + parquet_plain.py framing, PLAIN uncompressed), same rows, to a tmpfs directory."""
+    (hs_parquet_plain_pages / hs_parquet_encode_pages + parquet_plain.py framing: PLAIN uncompressed, with
+    dictionaries, with dictionaries and snappy), same rows, to a tmpfs directory."""
     import shutil
     import tempfile
     import numpy as np
@@ -254,7 +255,9 @@ def run_parquet(args):
     out = {"config": "parquet", "rows": n, "num_buckets": nb, "raw_bytes": n * 24}
     try:
         for name, fn in (("pyarrow_snappy", lambda d: index_writer.write_buckets(arrays, names, boff, d)[0]),
-                         ("gpu_plain", lambda d: parquet_plain.write_buckets_plain(ctx, arrays, names, boff, d))):
+                         ("gpu_plain", lambda d: parquet_plain.write_buckets_plain(ctx, arrays, names, boff, d)),
+                         ("gpu_dictionary", lambda d: parquet_plain.write_buckets_plain(ctx, arrays, names, boff, d, max_dict=4096)),
+                         ("gpu_snappy", lambda d: parquet_plain.write_buckets_plain(ctx, arrays, names, boff, d, max_dict=4096, codec=1))):
             best, files = 1e9, []
             for rep in range(max(1, args.steps)):
                 d = os.path.join(root, f"{name}_{rep}")
