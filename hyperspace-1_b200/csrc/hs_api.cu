@@ -77,7 +77,7 @@ static double host_now_ms() {
 }
 void hs_stage_begin(hs_ctx* c, const char* name) {
   static int trace = getenv("HSGPU_TRACE") ? 1 : 0;
-  if (trace) fprintf(stderr, "[hsgpu] %10.3f ms  %s\n", host_now_ms(), name);
+  if (trace) fprintf(stderr, "[hsgpu r%d] %10.3f ms  %s\n", c->rank, host_now_ms(), name);
   if (!c->timing) return;
   StageRec r;
   memset(&r, 0, sizeof r);
@@ -91,6 +91,8 @@ void hs_stage_begin(hs_ctx* c, const char* name) {
 }
 
 void hs_stage_end(hs_ctx* c) {
+  static int trace = getenv("HSGPU_TRACE") ? 1 : 0;
+  if (trace) fprintf(stderr, "[hsgpu r%d] %10.3f ms    end\n", c->rank, host_now_ms());
   if (!c->timing || c->cur_stage < 0) return;
   cudaEventRecord(c->stages[c->cur_stage].e1, c->stream);
   c->cur_stage = -1;

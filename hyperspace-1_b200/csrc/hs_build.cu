@@ -611,7 +611,16 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
   }
 
   // ---- K3: every bucket sorted on the key
-  hs_segmented_sort(c, ms, key, key_bits, d_off.as<uint32_t>(), nbl, n, off32.data());
+  if (fused && xchg->ngroups > 0) {
+    // grouped spans: the buckets of group g are sorted while the rows of group g + 1 still cross NVLink
+    for (int g = 0; g < xchg->ngroups; g++) {
+      int lb0 = 0, lb1 = 0;
+      xchg->deliver_group(c, g, &lb0, &lb1);
+      if (lb1 > lb0) hs_segmented_sort(c, ms, key, key_bits, nullptr, lb1 - lb0, n, off32.data() + lb0);
+    }
+  } else {
+    hs_segmented_sort(c, ms, key, key_bits, d_off.as<uint32_t>(), nbl, n, off32.data());
+  }
 
   // ---- keys wider than one chunk (strings, wide composites): refine tie groups chunk by chunk
   if (!L.single_chunk) {

@@ -116,6 +116,9 @@ struct P2PState {
   std::map<int, std::string> current;                 // rank * 64 + slot -> handle currently mapped for it
   std::vector<void*> peer_ptr;                        // [rank][slot] for the current build
   bool unusable = false;
+  cudaStream_t xs = nullptr;                          // grouped spans: the stream the copies and barriers run on
+  std::vector<cudaEvent_t> evs;                       // recycled events (no timing) for the groups
+  cudaEvent_t x_e0 = nullptr, x_e1 = nullptr;
 };
 static P2PState* p2p_of(hs_ctx* c) {
   if (!c->p2p) c->p2p = new P2PState();
@@ -125,6 +128,10 @@ static void p2p_destroy(hs_ctx* c) {
   P2PState* st = (P2PState*)c->p2p;
   if (!st) return;
   for (auto& kv : st->opened) cudaIpcCloseMemHandle(kv.second);
+  if (st->xs) cudaStreamDestroy(st->xs);
+  for (cudaEvent_t e : st->evs) cudaEventDestroy(e);
+  if (st->x_e0) cudaEventDestroy(st->x_e0);
+  if (st->x_e1) cudaEventDestroy(st->x_e1);
   for (auto& sl : st->slots) if (sl.ptr) cudaFree(sl.ptr);
   for (void* p : st->retired) cudaFree(p);
   delete st;
@@ -325,7 +332,7 @@ struct NcclExchange : BuildExchange {
 
   // ---- fused path ------------------------------------------------------------------------------------
   std::vector<uint64_t> rank_rows;   // rows every rank receives
-  int xmode = 0;                     // 0 fused, 1 owner, 2 copy (see try_fused)
+  int xmode = 0;                     // 0 fused, 1 owner, 2 copy, 3 grouped spans (see try_fused)
   std::vector<int> xes;              // element sizes of the travelling columns (+ the bucket ids in owner mode)
   std::vector<DBuf> owner_sorted;    // owner mode: the received rows, scattered by bucket (the sort's source)
   bool narrow = false;               // owner mode: the INT64 key travels as u32 (value - minimum)
@@ -344,18 +351,25 @@ struct NcclExchange : BuildExchange {
     //         buckets). The scatter then groups rows by OWNER only (runs of hundreds of rows per destination),
     //         the bucket ids travel as one more column, and the owner scatters what it received by bucket.
     //  copy   scatter by bucket locally, then push whole bucket runs (kept for comparison).
+    //  spans  the sender groups its rows by (owner, bucket group) — a few dozen bins, an HBM-speed pass — and
+    //         the spans travel as plain peer copies on the copy engines, group after group on a second stream;
+    //         the owner scatters a group by bucket and sorts its buckets while the next group is still on the
+    //         wire (spans_exchange / deliver_group). The SMs never wait for NVLink except for the first group.
     const char* mode = getenv("HSGPU_P2P_MODE");
-    xmode = nb <= 256 ? 0 : 1;
+    xmode = nb <= 256 ? 0 : 3;
     if (mode && !strcmp(mode, "fused")) xmode = 0;
     if (mode && !strcmp(mode, "owner")) xmode = 1;
     if (mode && !strcmp(mode, "copy")) xmode = 2;
+    if (mode && !strcmp(mode, "spans")) xmode = 3;
+    if (xmode == 3 && (nb + N - 1) / N > 2048) xmode = 1;   // the owner-side scatter of a group is one-level
+    ngroups = 0;
     xes = esize;
     // owner mode: an INT64 key whose values span less than 2^32 crosses NVLink as 4 bytes (HSGPU_WIDE_KEYS=1: no)
     const char* wide = getenv("HSGPU_WIDE_KEYS");
     narrow = xmode == 1 && key_col >= 0 && key_col < (int)esize.size() && esize[key_col] == 8 &&
              key_span < 0xFFFFFFFFull && nbl <= 2048 && !(wide && *wide && *wide != '0');
     if (narrow) xes[key_col] = 4;
-    if (xmode == 1) xes.push_back(2);       // the bucket-id column
+    if (xmode == 1 || xmode == 3) xes.push_back(2);       // the bucket-id column
     if ((int)xes.size() > HS_MAX_PEER_COLS_HOST) return false;
     const int ncol = (int)xes.size();
     const std::vector<int>& esize_x = xes;
@@ -456,6 +470,10 @@ struct NcclExchange : BuildExchange {
     for (int b = 0; b < nb; b++)
       if (owner_of(b, N, nb) != me)
         for (size_t i = 0; i < xes.size(); i++) bytes_sent += (int64_t)all_hist[(size_t)me * nb + b] * xes[i];
+    if (xmode == 3) {
+      c->last_xchg_bytes = bytes_sent;
+      return spans_exchange(c, st, srcs, esize, d_bucket, n_local, recv, seg_off);
+    }
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
     CK(cudaEventCreate(&e1));
@@ -584,6 +602,167 @@ struct NcclExchange : BuildExchange {
     }
     for (int i = 0; i < ncol; i++) recv[i] = st->slots[i].ptr;
     return (int64_t)rank_rows[me];
+  }
+
+  // ---- grouped spans --------------------------------------------------------------------------------
+  int G = 0;
+  std::vector<uint64_t> grp_off;      // [G + 1] rows of this rank's receive buffers before group g
+  std::vector<uint32_t> own_off;      // [G + 1] where this rank's own rows of group g sit in span_tmp (they do not travel)
+  std::vector<int> grp_lb;            // [G + 1] first local bucket of group g
+  std::vector<cudaEvent_t> grp_ev;    // group g has arrived from every sender
+  std::vector<DBuf> span_tmp;         // the sender's rows grouped by (owner, group); read by the copies
+  DBuf bar_a, bar_b, d_seg;
+  std::vector<int> col_es;            // element sizes of the travelling columns (without the ids)
+
+  int64_t spans_exchange(hs_ctx* c, P2PState* st, const void* const* srcs, const std::vector<int>& esize,
+                         const uint16_t* d_bucket, int64_t n_local, std::vector<void*>& recv,
+                         const std::vector<uint32_t>& seg_off) {
+    const int ncol = (int)esize.size(), ncx = ncol + 1;   // + the bucket ids
+    const char* ge = getenv("HSGPU_XCHG_GROUPS");
+    G = ge && atoi(ge) > 0 ? std::min(atoi(ge), 16) : 4;
+    col_es = esize;
+    // owner o holds buckets [olo[o], olo[o + 1]); its group g the local buckets lb with lb * G / count == g
+    std::vector<int> olo((size_t)N + 1, nb);
+    for (int b = nb - 1; b >= 0; b--) olo[owner_of(b, N, nb)] = b;
+    for (int o = N - 1; o >= 0; o--) if (olo[o] > olo[o + 1]) olo[o] = olo[o + 1];   // owners without buckets
+    // the groups grow (weights 1, 2, 3, 3, ...): the first one is small, so the owners start sorting early, and
+    // the later ones are large, so the sort kernels are not cut into too many short launches
+    std::vector<int> wcum((size_t)G + 1, 0);
+    for (int g = 0; g < G; g++) wcum[g + 1] = wcum[g] + std::min(g + 1, 3);
+    auto group_of = [&](int b, int o) {
+      const int64_t pos = (int64_t)(b - olo[o]) * wcum[G] / (olo[o + 1] - olo[o]);   // in [0, sum of weights)
+      int g = 0;
+      while (wcum[g + 1] <= pos) g++;
+      return g;
+    };
+    const int nbins = N * G;
+    std::vector<uint16_t> lut((size_t)nb);
+    std::vector<uint64_t> cnt((size_t)N * nbins, 0);
+    for (int b = 0; b < nb; b++) {
+      const int o = owner_of(b, N, nb);
+      lut[b] = (uint16_t)(o * G + group_of(b, o));
+      for (int r = 0; r < N; r++) cnt[(size_t)r * nbins + lut[b]] += all_hist[(size_t)r * nb + b];
+    }
+    std::vector<uint32_t> my_off((size_t)nbins + 1, 0);
+    for (int i = 0; i < nbins; i++) my_off[i + 1] = my_off[i] + (uint32_t)cnt[(size_t)me * nbins + i];
+    // owner o's receive buffers are laid out [group][sender]; its own rows stay where its grouping put them
+    auto recv_off = [&](int o, int g, int r) {
+      uint64_t at = 0;
+      for (int gg = 0; gg < g; gg++)
+        for (int q = 0; q < N; q++) if (q != o) at += cnt[(size_t)q * nbins + o * G + gg];
+      for (int q = 0; q < r; q++) if (q != o) at += cnt[(size_t)q * nbins + o * G + g];
+      return at;
+    };
+    own_off.assign((size_t)G + 1, 0);
+    for (int g = 0; g <= G; g++) own_off[g] = my_off[(size_t)me * G + g];
+    grp_off.assign((size_t)G + 1, 0);
+    grp_lb.assign((size_t)G + 1, nbl);
+    for (int g = 0; g <= G; g++) grp_off[g] = recv_off(me, g, 0);
+    for (int lb = nbl - 1; lb >= 0; lb--) grp_lb[group_of(blo + lb, me)] = lb;
+    for (int g = G - 1; g >= 0; g--) if (grp_lb[g] > grp_lb[g + 1]) grp_lb[g] = grp_lb[g + 1];   // empty groups
+    if (!st->xs) {
+      int lo = 0, hi = 0;
+      CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+      CK(cudaStreamCreateWithPriority(&st->xs, cudaStreamNonBlocking, hi));
+      CK(cudaEventCreate(&st->x_e0));
+      CK(cudaEventCreate(&st->x_e1));
+    }
+    while ((int)st->evs.size() < G + 1) {
+      cudaEvent_t e;
+      CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+      st->evs.push_back(e);
+    }
+    grp_ev.assign(st->evs.begin(), st->evs.begin() + G);
+    cudaEvent_t ev_grouped = st->evs[G];
+    span_tmp.clear();
+    span_tmp.resize((size_t)ncx);
+    {
+      Stage s(c, "group_scatter");
+      DBuf d_lut(c, (size_t)nb * 2 + 16), d_boff(c, ((size_t)nbins + 1) * 4);
+      CK(cudaMemcpyAsync(d_lut.p, lut.data(), (size_t)nb * 2, cudaMemcpyHostToDevice, c->stream));
+      CK(cudaMemcpyAsync(d_boff.p, my_off.data(), ((size_t)nbins + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+      std::vector<const void*> xsrc(srcs, srcs + ncol);
+      xsrc.push_back(d_bucket);
+      std::vector<void*> xdst((size_t)ncx);
+      for (int i = 0; i < ncx; i++) {
+        span_tmp[i].alloc(c, (size_t)n_local * xes[i] + 16);
+        xdst[i] = span_tmp[i].p;
+      }
+      hs_scatter_by_bins(c, xsrc.data(), xdst.data(), xes.data(), ncx, d_bucket, n_local, (const uint16_t*)d_lut.p, nbins,
+                         d_boff.as<uint32_t>());
+      CK(cudaEventRecord(ev_grouped, c->stream));
+    }
+    bar_a.alloc(c, 16);
+    bar_b.alloc(c, 16 * (size_t)N);
+    // everything that crosses NVLink is queued now, on the second stream: per group one copy per (owner, column),
+    // then the barrier that tells every owner its group is complete
+    CK(cudaStreamWaitEvent(st->xs, ev_grouped, 0));
+    CK(cudaEventRecord(st->x_e0, st->xs));
+    for (int g = 0; g < G; g++) {
+      for (int k = 1; k < N; k++) {        // every sender starts with a different owner
+        const int o = (me + k) % N, bin = o * G + g;
+        const uint64_t rows = cnt[(size_t)me * nbins + bin];
+        if (!rows) continue;
+        const uint64_t dst_row = recv_off(o, g, me);
+        for (int i = 0; i < ncx; i++)
+          CK(cudaMemcpyAsync((char*)st->peer_ptr[(size_t)o * ncx + i] + dst_row * xes[i],
+                             (const char*)span_tmp[i].p + (uint64_t)my_off[bin] * xes[i], rows * xes[i], cudaMemcpyDefault, st->xs));
+      }
+      if (g == G - 1) CK(cudaEventRecord(st->x_e1, st->xs));
+      NCK(g_nccl.allgather(bar_a.p, bar_b.p, 1, NCCL_UINT8, (nccl_comm)c->comm, st->xs));
+      CK(cudaEventRecord(grp_ev[g], st->xs));
+    }
+    // the owner side: buffers the groups are scattered into by bucket (the sort's source)
+    const int64_t nrecv = (int64_t)rank_rows[me];
+    owner_sorted.clear();
+    owner_sorted.resize((size_t)ncol);
+    recv.resize(ncol);
+    for (int i = 0; i < ncol; i++) {
+      owner_sorted[i].alloc(c, (size_t)nrecv * esize[i] + 16);
+      recv[i] = owner_sorted[i].p;
+    }
+    d_seg.alloc(c, ((size_t)nbl + 1) * 4);
+    CK(cudaMemcpyAsync(d_seg.p, seg_off.data(), ((size_t)nbl + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+    ngroups = G;
+    return nrecv;
+  }
+
+  void deliver_group(hs_ctx* c, int g, int* lb0, int* lb1) override {
+    P2PState* st = p2p_of(c);
+    const int ncol = (int)col_es.size();
+    CK(cudaStreamWaitEvent(c->stream, grp_ev[g], 0));
+    *lb0 = grp_lb[g];
+    *lb1 = grp_lb[g + 1];
+    // two sources fill the group's buckets: what arrived from the peers and this rank's own rows; d_seg holds
+    // the next free row of every bucket across both
+    const int64_t rows = (int64_t)(grp_off[g + 1] - grp_off[g]), own = (int64_t)own_off[g + 1] - (int64_t)own_off[g];
+    if (rows > 0 || own > 0) {
+      Stage s(c, "bucket_scatter");
+      MoveSet ms;
+      memset(&ms, 0, sizeof ms);
+      ms.n = ncol;
+      std::vector<const void*> rsrc((size_t)ncol);
+      for (int i = 0; i < ncol; i++) {
+        ms.esize[i] = col_es[i];
+        ms.a[i] = owner_sorted[i].p;
+        rsrc[i] = (const char*)st->slots[i].ptr + grp_off[g] * col_es[i];
+      }
+      hs_bucket_scatter(c, rsrc.data(), ms, (const uint16_t*)st->slots[ncol].ptr + grp_off[g], rows, nbl, nullptr, blo, -1, 0,
+                        d_seg.as<uint32_t>());
+      for (int i = 0; i < ncol; i++) rsrc[i] = (const char*)span_tmp[i].p + (size_t)own_off[g] * col_es[i];
+      hs_bucket_scatter(c, rsrc.data(), ms, (const uint16_t*)span_tmp[ncol].p + own_off[g], own, nbl, nullptr, blo, -1, 0,
+                        d_seg.as<uint32_t>());
+    }
+    if (g == G - 1) {
+      // the stream has passed the last barrier: the copies are done with the grouped rows
+      span_tmp.clear();
+      bar_a.release();
+      bar_b.release();
+      float ms_x = 0.f;
+      CK(cudaEventSynchronize(st->x_e1));
+      cudaEventElapsedTime(&ms_x, st->x_e0, st->x_e1);
+      c->last_xchg_ms = ms_x;
+    }
   }
 };
 

@@ -39,6 +39,12 @@ struct BuildExchange {
   virtual int64_t scatter_exchange(hs_ctx* c, const void* const* srcs, const std::vector<int>& esize,
                                    const uint16_t* d_bucket, int64_t n_local, std::vector<void*>& recv,
                                    std::vector<uint32_t>& seg_off) { return -1; }
+  // Pipelined delivery (grouped spans): after scatter_exchange the owned buckets become ready group by group
+  // while later groups are still travelling. deliver_group(g) makes the context's stream wait for group g and
+  // puts its rows bucket-contiguously into recv[]; the build then sorts local buckets [lb0, lb1) and asks for
+  // the next group. ngroups = 0: everything was ready when scatter_exchange returned.
+  int ngroups = 0;
+  virtual void deliver_group(hs_ctx* c, int g, int* lb0, int* lb1) {}
 };
 void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t nb, int32_t blo, int32_t nbl,
                    std::vector<OutCol>& out, std::vector<int64_t>& boff, BuildExchange* xchg);
@@ -74,7 +80,9 @@ struct KeySrc {
 // original int64 again
 void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, const uint16_t* d_bucket, int64_t n,
                        int32_t nb, const uint32_t* d_bucket_off, int32_t bucket_base = 0, int widen_col = -1,
-                       uint64_t widen_min = 0);
+                       uint64_t widen_min = 0, uint32_t* d_cursor = nullptr);
+void hs_scatter_by_bins(hs_ctx* c, const void* const* src, void* const* dst, const int32_t* esize, int ncols,
+                        const uint16_t* d_bucket, int64_t n, const uint16_t* d_lut, int32_t nbins, const uint32_t* d_bin_off);
 void hs_bucket_scatter_peers(hs_ctx* c, const void* const* src, const int32_t* esize, int ncols, void* const* pdst,
                              int nranks, const uint16_t* d_bucket, int64_t n, int32_t nb, const uint32_t* d_run_base,
                              bool by_owner = false, int narrow_col = -1, uint64_t narrow_min = 0);

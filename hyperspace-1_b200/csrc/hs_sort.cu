@@ -103,6 +103,7 @@ struct PartParams {
   int32_t bits;             // MODE 0: bits of a bucket id
   int32_t bucket_shift;     // MODE 0: digit = bucket id >> bucket_shift (coarse pass of the two-level scatter)
   int32_t bucket_base;      // MODE 0: subtracted from the bucket id first (ids of a rank's own bucket range)
+  const uint16_t* bin_lut;  // MODE 0: when set, digit = bin_lut[bucket id] (bins that are unions of buckets)
   int32_t by_owner;         // MODE 2: digit = owner of the bucket (nranks bins) instead of the bucket itself
   int32_t nb_total;         // MODE 2, by_owner: number of buckets of the index
   int32_t conv_col1;        // 1 + the column converted on the way (0 = none): MODE 2 writes int64 as u32
@@ -233,7 +234,8 @@ __device__ __forceinline__ void partition_tile(const PartParams& p, unsigned cha
     digit[k] = 0;
     if (v) {
       if (MODE == 0) {
-        digit[k] = ((uint32_t)sbucket[idx] - (uint32_t)p.bucket_base) >> p.bucket_shift;
+        digit[k] = p.bin_lut ? (uint32_t)__ldg(p.bin_lut + sbucket[idx])
+                             : ((uint32_t)sbucket[idx] - (uint32_t)p.bucket_base) >> p.bucket_shift;
       } else if (MODE == 2) {
         digit[k] = p.by_owner ? ((uint32_t)sbucket[idx] * (uint32_t)p.nranks) / (uint32_t)p.nb_total : sbucket[idx];
       } else {
@@ -1054,16 +1056,23 @@ static void launch_bucket_scatter(hs_ctx* c, const PartParams& p, int64_t n) {
 }
 
 void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, const uint16_t* d_bucket, int64_t n,
-                       int32_t nb, const uint32_t* d_bucket_off, int32_t bucket_base, int widen_col, uint64_t widen_min) {
+                       int32_t nb, const uint32_t* d_bucket_off, int32_t bucket_base, int widen_col, uint64_t widen_min,
+                       uint32_t* d_cursor) {
+  // d_cursor: the next free row of every bucket, kept by the caller across several calls that fill the same
+  // buckets from different sources (else the cursors start at d_bucket_off)
   if (n == 0) return;
+  if (d_cursor && nb > 2048) HS_THROW(HS_EINVAL, "a caller-kept cursor cannot pass the two-level scatter");
   if (widen_col >= 0 && nb > 2048) HS_THROW(HS_EINVAL, "a narrowed key cannot pass the two-level scatter");
   if (nb > 8192) HS_THROW(HS_EUNSUPPORTED, "the bucket scatter supports at most 8192 buckets per GPU");
   PartParams p;
   memset(&p, 0, sizeof p);
   p.n = (uint32_t)n;
   p.bucket_base = bucket_base;
-  DBuf cursor(c, (size_t)nb * 4);
-  CK(cudaMemcpyAsync(cursor.p, d_bucket_off, (size_t)nb * 4, cudaMemcpyDeviceToDevice, c->stream));
+  DBuf cursor;
+  if (!d_cursor) {
+    cursor.alloc(c, (size_t)nb * 4);
+    CK(cudaMemcpyAsync(cursor.p, d_bucket_off, (size_t)nb * 4, cudaMemcpyDeviceToDevice, c->stream));
+  }
   const char* one = getenv("HSGPU_ONE_LEVEL_SCATTER");
   if (nb > 2048 && n >= ((int64_t)1 << 22) && ms.n + 1 <= HS_MAX_MOVE && !(one && *one && *one != '0')) {
     // Thousands of buckets: a tile of 4096 rows holds less than two rows per bucket, so a direct scatter writes
@@ -1104,6 +1113,28 @@ void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, con
   p.radix = nb;
   p.radix_pad = ((nb + PT_THREADS - 1) / PT_THREADS) * PT_THREADS;
   p.bits = ilog2_ceil((uint32_t)nb);
+  p.cursor = d_cursor ? d_cursor : cursor.as<uint32_t>();
+  launch_bucket_scatter(c, p, n);
+}
+
+// Rows grouped by bins that are unions of buckets (d_lut[bucket id] = bin; d_bin_off[bin] = first row of the bin
+// in dst): what a sender does before whole spans of rows travel to their owners (hs_dist.cu, grouped spans).
+void hs_scatter_by_bins(hs_ctx* c, const void* const* src, void* const* dst, const int32_t* esize, int ncols,
+                        const uint16_t* d_bucket, int64_t n, const uint16_t* d_lut, int32_t nbins, const uint32_t* d_bin_off) {
+  if (n == 0) return;
+  if (ncols > HS_MAX_MOVE) HS_THROW(HS_EUNSUPPORTED, "too many columns for the grouped scatter");
+  PartParams p;
+  memset(&p, 0, sizeof p);
+  p.n = (uint32_t)n;
+  p.mv.n = ncols;
+  for (int i = 0; i < ncols; i++) { p.mv.esize[i] = esize[i]; p.mv.src[i] = src[i]; p.mv.dst[i] = dst[i]; }
+  p.bucket = d_bucket;
+  p.bin_lut = d_lut;
+  p.radix = nbins;
+  p.radix_pad = ((nbins + PT_THREADS - 1) / PT_THREADS) * PT_THREADS;
+  p.bits = ilog2_ceil((uint32_t)nbins);
+  DBuf cursor(c, (size_t)nbins * 4);
+  CK(cudaMemcpyAsync(cursor.p, d_bin_off, (size_t)nbins * 4, cudaMemcpyDeviceToDevice, c->stream));
   p.cursor = cursor.as<uint32_t>();
   launch_bucket_scatter(c, p, n);
 }

@@ -60,17 +60,23 @@ def test_rows_first_build_world2_nccl(shape, monkeypatch):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("exchange", ["fused", "owner", "copy", "nccl", "owner-int64-key", "fused-int64-key"])
+@pytest.mark.parametrize("exchange", ["fused", "owner", "copy", "spans", "nccl", "owner-int64-key", "fused-int64-key",
+                                      "spans-int64-key", "spans-groups7", "spans-groups1"])
 def test_sharded_build_world2_nccl(exchange, monkeypatch):
     """hs_build_index_dist on two GPUs against the oracle, once per way the rows can travel: straight into the
     owner's buckets (fused), grouped by owner with the bucket ids alongside and a bucket scatter at the receiver
-    (owner), whole bucket runs pushed after a local scatter (copy), and the NCCL send/receive fallback."""
+    (owner), whole bucket runs pushed after a local scatter (copy), spans of rows grouped by (owner, bucket group)
+    copied group after group while the owner sorts the groups that have arrived (spans; with group counts that do
+    not divide the bucket count, and with a single group), and the NCCL send/receive fallback."""
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
     if exchange.endswith("-int64-key"):
         # one non-null int64 key spanning less than 2^32: in owner mode it crosses NVLink as 4 bytes
         monkeypatch.setenv("HS_DIST_NKEYS", "1")
+        exchange = exchange.split("-")[0]
+    if "-groups" in exchange:
+        monkeypatch.setenv("HSGPU_XCHG_GROUPS", exchange.split("-groups")[1])
         exchange = exchange.split("-")[0]
     if exchange == "nccl":
         monkeypatch.setenv("HSGPU_NO_P2P", "1")

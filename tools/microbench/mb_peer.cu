@@ -91,5 +91,37 @@ int main(int argc, char** argv) {
     }
     printf("cudaMemcpyPeerAsync: %.3f ms = %.0f GB/s\n", best, bytes / best / 1e6);
   }
+  if (dpeer) {
+    // both directions at once (what the exchange does: every GPU stores into its peers while they store into it)
+    uint4* src1; unsigned char* d0;
+    CK(cudaSetDevice(1)); CK(cudaMalloc(&src1, bytes)); CK(cudaMemset(src1, 2, bytes));
+    CK(cudaDeviceEnablePeerAccess(0, 0));
+    CK(cudaFuncSetAttribute(k_push<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32768));
+    cudaStream_t s1; CK(cudaStreamCreate(&s1));
+    cudaEvent_t f0, f1; cudaEventCreate(&f0); cudaEventCreate(&f1);
+    CK(cudaDeviceSynchronize());
+    CK(cudaSetDevice(0)); CK(cudaMalloc(&d0, bytes));
+    cudaStream_t s0; CK(cudaStreamCreate(&s0));
+    for (int kind = 0; kind < 2; kind++) {
+      float b0 = 1e9, b1 = 1e9;
+      for (int rep = 0; rep < 5; rep++) {
+        CK(cudaSetDevice(0)); cudaEventRecord(e0, s0);
+        if (kind == 0) k_push<1><<<296, 512, 32768, s0>>>(src, dpeer, nruns, run);
+        else CK(cudaMemcpyPeerAsync(dpeer, 1, src, 0, bytes, s0));
+        cudaEventRecord(e1, s0);
+        CK(cudaSetDevice(1)); cudaEventRecord(f0, s1);
+        if (kind == 0) k_push<1><<<296, 512, 32768, s1>>>(src1, d0, nruns, run);
+        else CK(cudaMemcpyPeerAsync(d0, 0, src1, 1, bytes, s1));
+        cudaEventRecord(f1, s1);
+        CK(cudaSetDevice(0)); CK(cudaDeviceSynchronize());
+        CK(cudaSetDevice(1)); CK(cudaDeviceSynchronize());
+        float m0, m1; cudaEventElapsedTime(&m0, e0, e1); cudaEventElapsedTime(&m1, f0, f1);
+        if (rep && m0 < b0) b0 = m0;
+        if (rep && m1 < b1) b1 = m1;
+      }
+      printf("BOTH DIRECTIONS %s run %u B: 0->1 %.3f ms = %.0f GB/s, 1->0 %.3f ms = %.0f GB/s\n",
+             kind == 0 ? "st.16 grid 296" : "cudaMemcpyPeerAsync", run, b0, bytes / b0 / 1e6, b1, bytes / b1 / 1e6);
+    }
+  }
   return 0;
 }
