@@ -8,10 +8,14 @@
 #define PT_THREADS 512
 #endif
 #define PT_WARPS (PT_THREADS / 32)
+#ifndef PT_ITEMS
 #define PT_ITEMS 8
+#endif
 #define PT_TILE (PT_THREADS * PT_ITEMS)  // 4096 rows per tile
 #define PT_SCRATCH 32                    // words of scan scratch (>= PT_WARPS + 1)
+#ifndef PT_MIN_CTAS
 #define PT_MIN_CTAS (1024 / PT_THREADS)  // resident CTAs per SM the kernels are compiled for (64 registers per thread)
+#endif
 
 __device__ __forceinline__ uint32_t warp_incl_scan_u32(uint32_t v) {
 #pragma unroll

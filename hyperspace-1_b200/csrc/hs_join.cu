@@ -156,8 +156,13 @@ __global__ void __launch_bounds__(256) k_full_outer_merge(const uint32_t* __rest
 // Pass 1 counts matches per tile, a scan turns the counts into output offsets, pass 2 repeats the search,
 // expands the pairs in shared memory and writes every output column directly (no index arrays in HBM).
 #define JT 2048          // left rows per tile
-#define JR 3072          // right rows staged per tile (falls back to global probes when the window is larger)
+#ifndef JR
+#define JR 2048          // right rows staged per tile (falls back to global probes when the window is larger)
+#endif
 #define JTHREADS 512
+#ifndef JCTAS
+#define JCTAS 3          // resident CTAs per SM the tile kernel is compiled for
+#endif
 #define JPER (JT / JTHREADS)   // consecutive left rows owned by one thread
 #define JOMAX 4096       // outputs of one tile that are expanded through shared memory
 #define JBUF_BYTES (JR * 8 + 128)
@@ -239,7 +244,7 @@ __device__ __forceinline__ uint32_t window_advance(const K* sR, uint32_t pos, ui
 // global loads, no index arrays in HBM. Tiles whose window or output exceeds the staging areas take the
 // global-memory paths below (same results).
 template <typename K, int MODE>
-__global__ void __launch_bounds__(JTHREADS, 2) k_join_tiles(const __grid_constant__ JoinFast p) {
+__global__ void __launch_bounds__(JTHREADS, JCTAS) k_join_tiles(const __grid_constant__ JoinFast p) {
   extern __shared__ __align__(128) unsigned char jsm[];
   unsigned char* buf0 = jsm;
   unsigned char* buf1 = jsm + JBUF_BYTES;
@@ -526,8 +531,9 @@ void hs_offsets_to_device(hs_ctx* c, const int64_t* boff, int32_t nb, int64_t nr
   }
   if (boff[0] != 0 || boff[nb] != nrows) HS_THROW(HS_EINVAL, "bucket_offsets do not cover the rows");
   out.alloc(c, ((size_t)nb + 1) * 4);
+  // h is pageable memory: the call returns once the bytes sit in the driver's staging buffer, so h may go out of
+  // scope without waiting for the stream
   CK(cudaMemcpyAsync(out.p, h.data(), ((size_t)nb + 1) * 4, cudaMemcpyHostToDevice, c->stream));
-  hs_sync(c);  // h goes out of scope
 }
 
 // (left row, right row) pairs of a join driven from side A: for every row of A the matching range of B's run in
@@ -681,11 +687,17 @@ __global__ void __launch_bounds__(256) k_join_make_tiles(const uint32_t* __restr
 // output offset of every bucket = output offset of its first tile (m for buckets after the last tile)
 __global__ void __launch_bounds__(256) k_join_bucket_offsets(const uint32_t* __restrict__ tile_off, const uint32_t* __restrict__ first_tile,
                                                              int nb, uint32_t ntiles, const unsigned long long* last_state,
-                                                             uint32_t* __restrict__ out) {
+                                                             const uint32_t* overflow, uint32_t* __restrict__ out) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b > nb) return;
-  const uint32_t m = (uint32_t)(*last_state & ((1ull << 62) - 1));
+  const unsigned long long last = *last_state;
+  const uint32_t m = (uint32_t)(last & ((1ull << 62) - 1));
   out[b] = first_tile[b] < ntiles ? tile_off[first_tile[b]] : m;
+  if (b == 0 && overflow) {   // everything the host wants back, behind the offsets: one read
+    out[nb + 1] = *overflow;
+    out[nb + 2] = (uint32_t)last;
+    out[nb + 3] = (uint32_t)(last >> 32);
+  }
 }
 
 extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, const hs_index_view* right,
@@ -785,7 +797,7 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
     first_tile[nb] = ntiles;
     DBuf d_tb(ctx, (size_t)ntiles * 4 + 4), d_ts(ctx, (size_t)ntiles * 4 + 4), d_tl(ctx, (size_t)ntiles * 4 + 4),
         d_cnt(ctx, (size_t)ntiles * 4 + 4), d_total(ctx, 8), d_win(ctx, (size_t)ntiles * 8 + 8),
-        d_first(ctx, ((size_t)nb + 1) * 4), d_boff(ctx, ((size_t)nb + 1) * 4);
+        d_first(ctx, ((size_t)nb + 1) * 4), d_boff(ctx, ((size_t)nb + 4) * 4);
     CK(cudaMemcpyAsync(d_first.p, first_tile.data(), ((size_t)nb + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
     if (ntiles)
       LAUNCH(ctx, k_join_make_tiles, (ntiles + 255) / 256, 256, 0, loff.as<uint32_t>(), d_first.as<uint32_t>(), nb, ntiles,
@@ -830,7 +842,7 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
       attr_done[dev & 63] = true;
     }
     uint64_t h_tot = 0;
-    std::vector<uint32_t> h_off((size_t)ntiles), h_boff((size_t)nb + 1);
+    std::vector<uint32_t> h_off((size_t)ntiles), h_boff((size_t)nb + 4);
     // ---- single pass first: the output is sized for one match per left row (a key -> unique-key join, the
     // shape JoinIndexRule mostly produces); tiles learn their output offset from a chained scan. If the matches
     // do not fit, the pass has only counted and the two-pass path below runs instead.
@@ -853,27 +865,23 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
         jf.rsrc[i] = sc.data; jf.rdst[i] = ocols[n_left_out + i].data.p; jf.res[i] = hs_fixed_width(sc.type);
       }
       jf.n_lout = n_left_out; jf.n_rout = n_right_out;
-      DBuf d_state(ctx, (size_t)ntiles * 8), d_misc(ctx, 16);
+      DBuf d_state(ctx, (size_t)ntiles * 8 + 16);     // tile states, then the ticket and the overflow flag
       d_state.zero();
-      d_misc.zero();
       jf.tile_state = d_state.as<unsigned long long>();
-      jf.ticket = d_misc.as<uint32_t>();
-      jf.overflow = d_misc.as<uint32_t>() + 1;
+      jf.ticket = (uint32_t*)(d_state.as<unsigned long long>() + ntiles);
+      jf.overflow = jf.ticket + 1;
       jf.capacity = (uint32_t)cap;
-      uint32_t h_misc[4] = {0, 0, 0, 0};
-      unsigned long long h_last = 0;
       {
         Stage s(ctx, "join_fused");
         launch_windows();
         launch_tiles(2);
         LAUNCH(ctx, k_join_bucket_offsets, (nb + 256) / 256, 256, 0, d_cnt.as<uint32_t>(), d_first.as<uint32_t>(), nb, ntiles,
-               d_state.as<unsigned long long>() + (ntiles - 1), d_boff.as<uint32_t>());
-        CK(cudaMemcpyAsync(h_misc, d_misc.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaMemcpyAsync(&h_last, d_state.as<unsigned long long>() + (ntiles - 1), 8, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaMemcpyAsync(h_boff.data(), d_boff.p, ((size_t)nb + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+               d_state.as<unsigned long long>() + (ntiles - 1), (const uint32_t*)jf.overflow, d_boff.as<uint32_t>());
+        CK(cudaMemcpyAsync(h_boff.data(), d_boff.p, ((size_t)nb + 4) * 4, cudaMemcpyDeviceToHost, ctx->stream));
         hs_sync(ctx);
       }
-      if (!h_misc[1]) {
+      if (!h_boff[(size_t)nb + 1]) {
+        const unsigned long long h_last = (unsigned long long)h_boff[(size_t)nb + 2] | ((unsigned long long)h_boff[(size_t)nb + 3] << 32);
         const int64_t m = (int64_t)(h_last & ((1ull << 62) - 1));
         for (size_t i = 0; i < ocols.size(); i++) {
           ocols[i].length = m;

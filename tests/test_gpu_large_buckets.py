@@ -1,7 +1,7 @@
-"""The pipelined sort of the large buckets (k_sort_pipeline: one launch for the MSD level and the leaves, the level
-written into a small re-used scratch area) against the oracle, in the shapes that steer it: many groups per slot
-ring (a tiny ring), buckets that do not fit a slot (left to the level loop), children that stay large (skewed and
-constant keys), and the plain level loop with the pipeline switched off — all must give the oracle's index."""
+"""Buckets well above a leaf against the oracle, in the key shapes that steer the MSD levels and the leaf kernels:
+uniform wide keys, few distinct keys (children of a level stay larger than a leaf and are re-ranged), half of the
+rows on one key, a dense narrow range, and leaves around the sizes where the leaf kernel changes its variant
+(half a tile, a full tile of LEAF_MAX = 3072 rows, one row more)."""
 import numpy as np
 import pyarrow as pa
 import pytest
@@ -32,18 +32,14 @@ def _rows(n, kind, seed):
 
 
 @pytest.mark.parametrize("kind", ["uniform", "dups", "skew", "narrow"])
-@pytest.mark.parametrize("ring_mb,pipeline", [("1", "1"), ("48", "1"), ("48", "0")])
-def test_large_buckets_against_oracle(ctx, oracle, monkeypatch, kind, ring_mb, pipeline):
-    monkeypatch.setenv("HSGPU_RING_MB", ring_mb)
-    monkeypatch.setenv("HSGPU_SORT_PIPELINE", pipeline)
+def test_large_buckets_against_oracle(ctx, oracle, kind):
     n, nb = 400_000, 7          # buckets of ~57 k rows: 14 tiles each, well above a leaf
     cols = _rows(n, kind, 11)
     got, boff = ctx.build_index(cols, 1, nb)
-    parity.check_index(oracle, got, boff, cols, 1, nb, f"{kind} ring={ring_mb} pipeline={pipeline}")
+    parity.check_index(oracle, got, boff, cols, 1, nb, kind)
 
 
-def test_int32_key_and_bucket_larger_than_a_slot(ctx, oracle, monkeypatch):
-    monkeypatch.setenv("HSGPU_RING_MB", "1")     # slots of ~20 k rows: the 150 k-row bucket goes to the level loop
+def test_int32_key(ctx, oracle):
     rng = np.random.default_rng(3)
     n = 300_000
     k = rng.integers(-2**31, 2**31 - 1, size=n).astype(np.int32)
@@ -51,3 +47,16 @@ def test_int32_key_and_bucket_larger_than_a_slot(ctx, oracle, monkeypatch):
     for nb in (2, 40):
         got, boff = ctx.build_index(cols, 1, nb)
         parity.check_index(oracle, got, boff, cols, 1, nb, f"int32 key nb={nb}")
+
+
+@pytest.mark.parametrize("n", [1535, 1536, 1537, 3071, 3072, 3073, 4096, 6145])
+@pytest.mark.parametrize("bits", [10, 19, 20, 33, 63])
+def test_one_bucket_around_the_leaf_sizes(ctx, oracle, n, bits):
+    """One bucket of exactly n rows: the 4-rows-per-thread and 8-rows-per-thread leaf variants, a full leaf, and
+    one row more (an MSD level first); key ranges below, at and above the packed kernel's 19 key bits (wider
+    ranges sort on a prefix and repair ties, or fall to the 64-bit kernel)."""
+    rng = np.random.default_rng(n * 64 + bits)
+    k = rng.integers(0, 2**bits, size=n, dtype=np.uint64).astype(np.int64) - (2**(bits - 1) if bits < 63 else 0)
+    cols = [pa.array(k), pa.array(rng.random(n)), pa.array(rng.integers(0, 9, size=n).astype(np.int16))]
+    got, boff = ctx.build_index(cols, 1, 1)
+    parity.check_index(oracle, got, boff, cols, 1, 1, f"n={n} bits={bits}")
