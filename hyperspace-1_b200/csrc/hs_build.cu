@@ -551,6 +551,7 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
   if (fast_key) {
     key.mode = cols[0].type == HS_INT64 ? KS_I64 : KS_I32;
     key.min = h_minmax[0];
+    key.span = h_minmax[1] - h_minmax[0];
     key_bits = bitlen64(h_minmax[1] - h_minmax[0]);
   } else {
     key.mode = KS_U64;

@@ -116,7 +116,9 @@ struct P2PState {
   std::map<int, std::string> current;                 // rank * 64 + slot -> handle currently mapped for it
   std::vector<void*> peer_ptr;                        // [rank][slot] for the current build
   bool unusable = false;
-  cudaStream_t xs = nullptr;                          // grouped spans: the stream the copies and barriers run on
+  cudaStream_t xs = nullptr;                          // grouped spans: the stream the barriers run on
+  std::vector<cudaStream_t> cs;                       // grouped spans: streams the peer copies are spread over
+  std::vector<cudaEvent_t> cs_ev;
   std::vector<cudaEvent_t> evs;                       // recycled events (no timing) for the groups
   cudaEvent_t x_e0 = nullptr, x_e1 = nullptr;
 };
@@ -129,6 +131,8 @@ static void p2p_destroy(hs_ctx* c) {
   if (!st) return;
   for (auto& kv : st->opened) cudaIpcCloseMemHandle(kv.second);
   if (st->xs) cudaStreamDestroy(st->xs);
+  for (cudaStream_t q : st->cs) cudaStreamDestroy(q);
+  for (cudaEvent_t e : st->cs_ev) cudaEventDestroy(e);
   for (cudaEvent_t e : st->evs) cudaEventDestroy(e);
   if (st->x_e0) cudaEventDestroy(st->x_e0);
   if (st->x_e1) cudaEventDestroy(st->x_e1);
@@ -366,7 +370,7 @@ struct NcclExchange : BuildExchange {
     xes = esize;
     // owner mode: an INT64 key whose values span less than 2^32 crosses NVLink as 4 bytes (HSGPU_WIDE_KEYS=1: no)
     const char* wide = getenv("HSGPU_WIDE_KEYS");
-    narrow = xmode == 1 && key_col >= 0 && key_col < (int)esize.size() && esize[key_col] == 8 &&
+    narrow = (xmode == 1 || xmode == 3) && key_col >= 0 && key_col < (int)esize.size() && esize[key_col] == 8 &&
              key_span < 0xFFFFFFFFull && nbl <= 2048 && !(wide && *wide && *wide != '0');
     if (narrow) xes[key_col] = 4;
     if (xmode == 1 || xmode == 3) xes.push_back(2);       // the bucket-id column
@@ -619,16 +623,17 @@ struct NcclExchange : BuildExchange {
                          const std::vector<uint32_t>& seg_off) {
     const int ncol = (int)esize.size(), ncx = ncol + 1;   // + the bucket ids
     const char* ge = getenv("HSGPU_XCHG_GROUPS");
-    G = ge && atoi(ge) > 0 ? std::min(atoi(ge), 16) : 4;
+    G = ge && atoi(ge) > 0 ? std::min(atoi(ge), 16) : 5;
     col_es = esize;
     // owner o holds buckets [olo[o], olo[o + 1]); its group g the local buckets lb with lb * G / count == g
     std::vector<int> olo((size_t)N + 1, nb);
     for (int b = nb - 1; b >= 0; b--) olo[owner_of(b, N, nb)] = b;
     for (int o = N - 1; o >= 0; o--) if (olo[o] > olo[o + 1]) olo[o] = olo[o + 1];   // owners without buckets
-    // the groups grow (weights 1, 2, 3, 3, ...): the first one is small, so the owners start sorting early, and
-    // the later ones are large, so the sort kernels are not cut into too many short launches
+    // group sizes 1, 2, 3, ..., 3, 2, 1: the first group is small, so the owners start sorting early; the last one
+    // is small, so little is left to sort when the last row has arrived; the middle ones are large, so the sort
+    // kernels are not cut into too many short launches
     std::vector<int> wcum((size_t)G + 1, 0);
-    for (int g = 0; g < G; g++) wcum[g + 1] = wcum[g] + std::min(g + 1, 3);
+    for (int g = 0; g < G; g++) wcum[g + 1] = wcum[g] + std::min(std::min(g + 1, G - g), 3);
     auto group_of = [&](int b, int o) {
       const int64_t pos = (int64_t)(b - olo[o]) * wcum[G] / (olo[o + 1] - olo[o]);   // in [0, sum of weights)
       int g = 0;
@@ -667,6 +672,20 @@ struct NcclExchange : BuildExchange {
       CK(cudaEventCreate(&st->x_e0));
       CK(cudaEventCreate(&st->x_e1));
     }
+    // one copy at a time leaves NVLink idle between copies (measured at N=8: 437 GB/s per GPU with one stream):
+    // the copies of a group are spread over several streams, so that copies to different owners overlap
+    const char* se = getenv("HSGPU_XCHG_STREAMS");
+    const int S = std::max(1, std::min(se && atoi(se) > 0 ? atoi(se) : 2, 8));
+    while ((int)st->cs.size() < S) {
+      int lo = 0, hi = 0;
+      cudaStream_t q;
+      cudaEvent_t e;
+      CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+      CK(cudaStreamCreateWithPriority(&q, cudaStreamNonBlocking, hi));
+      CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+      st->cs.push_back(q);
+      st->cs_ev.push_back(e);
+    }
     while ((int)st->evs.size() < G + 1) {
       cudaEvent_t e;
       CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -689,7 +708,7 @@ struct NcclExchange : BuildExchange {
         xdst[i] = span_tmp[i].p;
       }
       hs_scatter_by_bins(c, xsrc.data(), xdst.data(), xes.data(), ncx, d_bucket, n_local, (const uint16_t*)d_lut.p, nbins,
-                         d_boff.as<uint32_t>());
+                         d_boff.as<uint32_t>(), narrow ? key_col : -1, key_min);
       CK(cudaEventRecord(ev_grouped, c->stream));
     }
     bar_a.alloc(c, 16);
@@ -698,15 +717,22 @@ struct NcclExchange : BuildExchange {
     // then the barrier that tells every owner its group is complete
     CK(cudaStreamWaitEvent(st->xs, ev_grouped, 0));
     CK(cudaEventRecord(st->x_e0, st->xs));
+    for (int q = 0; q < S; q++) CK(cudaStreamWaitEvent(st->cs[q], ev_grouped, 0));
     for (int g = 0; g < G; g++) {
       for (int k = 1; k < N; k++) {        // every sender starts with a different owner
         const int o = (me + k) % N, bin = o * G + g;
         const uint64_t rows = cnt[(size_t)me * nbins + bin];
         if (!rows) continue;
         const uint64_t dst_row = recv_off(o, g, me);
+        cudaStream_t q = st->cs[(size_t)(k - 1) % S];
         for (int i = 0; i < ncx; i++)
           CK(cudaMemcpyAsync((char*)st->peer_ptr[(size_t)o * ncx + i] + dst_row * xes[i],
-                             (const char*)span_tmp[i].p + (uint64_t)my_off[bin] * xes[i], rows * xes[i], cudaMemcpyDefault, st->xs));
+                             (const char*)span_tmp[i].p + (uint64_t)my_off[bin] * xes[i], rows * xes[i], cudaMemcpyDefault, q));
+      }
+      // the barrier stream joins the copy streams (which go straight on with the next group)
+      for (int q = 0; q < S; q++) {
+        CK(cudaEventRecord(st->cs_ev[q], st->cs[q]));
+        CK(cudaStreamWaitEvent(st->xs, st->cs_ev[q], 0));
       }
       if (g == G - 1) CK(cudaEventRecord(st->x_e1, st->xs));
       NCK(g_nccl.allgather(bar_a.p, bar_b.p, 1, NCCL_UINT8, (nccl_comm)c->comm, st->xs));
@@ -745,13 +771,14 @@ struct NcclExchange : BuildExchange {
       for (int i = 0; i < ncol; i++) {
         ms.esize[i] = col_es[i];
         ms.a[i] = owner_sorted[i].p;
-        rsrc[i] = (const char*)st->slots[i].ptr + grp_off[g] * col_es[i];
+        rsrc[i] = (const char*)st->slots[i].ptr + grp_off[g] * xes[i];   // xes: a narrowed key is 4 bytes here
       }
-      hs_bucket_scatter(c, rsrc.data(), ms, (const uint16_t*)st->slots[ncol].ptr + grp_off[g], rows, nbl, nullptr, blo, -1, 0,
-                        d_seg.as<uint32_t>());
-      for (int i = 0; i < ncol; i++) rsrc[i] = (const char*)span_tmp[i].p + (size_t)own_off[g] * col_es[i];
-      hs_bucket_scatter(c, rsrc.data(), ms, (const uint16_t*)span_tmp[ncol].p + own_off[g], own, nbl, nullptr, blo, -1, 0,
-                        d_seg.as<uint32_t>());
+      const int wcol = narrow ? key_col : -1;
+      hs_bucket_scatter(c, rsrc.data(), ms, (const uint16_t*)st->slots[ncol].ptr + grp_off[g], rows, nbl, nullptr, blo, wcol,
+                        key_min, d_seg.as<uint32_t>());
+      for (int i = 0; i < ncol; i++) rsrc[i] = (const char*)span_tmp[i].p + (size_t)own_off[g] * xes[i];
+      hs_bucket_scatter(c, rsrc.data(), ms, (const uint16_t*)span_tmp[ncol].p + own_off[g], own, nbl, nullptr, blo, wcol,
+                        key_min, d_seg.as<uint32_t>());
     }
     if (g == G - 1) {
       // the stream has passed the last barrier: the copies are done with the grouped rows

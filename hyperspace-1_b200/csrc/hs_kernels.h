@@ -69,6 +69,7 @@ struct KeySrc {
   int32_t col;             // index into MoveSet
   int32_t mode;            // 0: u64 as is, 1: int64 (sign flip, minus min), 2: int32 (sign extend, flip, minus min)
   uint64_t min;
+  uint64_t span;           // max - min of the key over all rows when known, else 0 (lets the first MSD level use all its bins)
 };
 #define KS_U64 0
 #define KS_I64 1
@@ -82,7 +83,8 @@ void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, con
                        int32_t nb, const uint32_t* d_bucket_off, int32_t bucket_base = 0, int widen_col = -1,
                        uint64_t widen_min = 0, uint32_t* d_cursor = nullptr);
 void hs_scatter_by_bins(hs_ctx* c, const void* const* src, void* const* dst, const int32_t* esize, int ncols,
-                        const uint16_t* d_bucket, int64_t n, const uint16_t* d_lut, int32_t nbins, const uint32_t* d_bin_off);
+                        const uint16_t* d_bucket, int64_t n, const uint16_t* d_lut, int32_t nbins, const uint32_t* d_bin_off,
+                        int narrow_col = -1, uint64_t narrow_min = 0);
 void hs_bucket_scatter_peers(hs_ctx* c, const void* const* src, const int32_t* esize, int ncols, void* const* pdst,
                              int nranks, const uint16_t* d_bucket, int64_t n, int32_t nb, const uint32_t* d_run_base,
                              bool by_owner = false, int narrow_col = -1, uint64_t narrow_min = 0);

@@ -63,6 +63,7 @@ struct PartParams {
   int32_t nb_total;         // MODE 2, by_owner: number of buckets of the index
   int32_t conv_col1;        // 1 + the column converted on the way (0 = none): MODE 2 writes int64 as u32
                             // ((v ^ sign) - conv_min), MODE 0 reads such u32 and writes the int64 back
+  int32_t conv_narrow;      // MODE 0: narrow like MODE 2 instead of widening (the sender's grouped scatter)
   uint64_t conv_min;
   uint32_t* cursor;         // MODE 0: [radix]; MODE 1: [nseg * 256]
   SegList segs;             // MODE 1: the large segments of this level
@@ -123,6 +124,16 @@ __device__ __forceinline__ void scatter_column_peers_narrow(const unsigned char*
     }
   }
 }
+__device__ __forceinline__ void scatter_column_narrow(const unsigned char* stage, uint32_t lead, uint32_t* __restrict__ dst,
+                                                      uint32_t tile_len, const uint16_t* inv, const uint32_t* gdst,
+                                                      uint64_t mn) {
+  const uint64_t* col = (const uint64_t*)(stage + lead);
+#pragma unroll 4
+  for (int k = 0; k < PT_ITEMS; k++) {
+    uint32_t j = threadIdx.x + k * PT_THREADS;
+    if (j < tile_len) dst[gdst[j]] = (uint32_t)((col[inv[j]] ^ HS_SIGN64) - mn);
+  }
+}
 __device__ __forceinline__ void scatter_column_widen(const unsigned char* stage, uint32_t lead, uint64_t* __restrict__ dst,
                                                      uint32_t tile_len, const uint16_t* inv, const uint32_t* gdst,
                                                      uint64_t mn) {
@@ -147,7 +158,7 @@ template <int MODE>
 __device__ __forceinline__ void partition_tile(const PartParams& p, unsigned char* smem_raw, uint32_t tile_start,
                                                uint32_t tile_len, int bits, uint32_t shift, uint64_t seg_base,
                                                uint32_t* cursor, uint32_t dst_bias, uint64_t* ext_bar = nullptr,
-                                               uint32_t* ext_phase = nullptr) {
+                                               uint32_t* ext_phase = nullptr, uint32_t seg_mul = 0) {
   // ext_bar / ext_phase: three mbarriers that live on across calls (persistent kernel) and the parity each one
   // completes next (bit b of *ext_phase); without them the barriers of the carve-up are initialised here
   TileSmem sm = carve(smem_raw, p.radix_pad);
@@ -199,7 +210,7 @@ __device__ __forceinline__ void partition_tile(const PartParams& p, unsigned cha
         if (p.key.mode == KS_U64) key = ((const uint64_t*)ks)[idx];
         else if (p.key.mode == KS_I64) key = (((const uint64_t*)ks)[idx] ^ 0x8000000000000000ull) - p.key.min;
         else key = ((uint64_t)(int64_t)((const int32_t*)ks)[idx] ^ 0x8000000000000000ull) - p.key.min;
-        digit[k] = (uint32_t)((key - seg_base) >> shift) & ((1u << bits) - 1u);
+        digit[k] = msd_digit(key - seg_base, shift + (uint32_t)bits, bits, seg_mul);
       }
     }
   }
@@ -224,7 +235,8 @@ __device__ __forceinline__ void partition_tile(const PartParams& p, unsigned cha
     if (MODE == 2 && c + 1 == p.conv_col1) {
       scatter_column_peers_narrow(sm.stage[b], lead, p.pdst, c, tile_len, sm.inv, sm.gdst, p.conv_min);
     } else if (MODE == 0 && c + 1 == p.conv_col1) {
-      scatter_column_widen(sm.stage[b], lead, (uint64_t*)p.mv.dst[c], tile_len, sm.inv, sm.gdst, p.conv_min);
+      if (p.conv_narrow) scatter_column_narrow(sm.stage[b], lead, (uint32_t*)p.mv.dst[c], tile_len, sm.inv, sm.gdst, p.conv_min);
+      else scatter_column_widen(sm.stage[b], lead, (uint64_t*)p.mv.dst[c], tile_len, sm.inv, sm.gdst, p.conv_min);
     } else if (MODE == 2) {
       switch (es) {
         case 8: scatter_column_peers<uint64_t>(sm.stage[b], lead, p.pdst, c, tile_len, sm.inv, sm.gdst); break;
@@ -252,7 +264,7 @@ __device__ __forceinline__ void partition_tile(const PartParams& p, unsigned cha
 template <int MODE>
 __global__ void __launch_bounds__(PT_THREADS, 2 * PT_MIN_CTAS / 2) k_partition(const __grid_constant__ PartParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  uint32_t tile_start, tile_len, shift = 0;
+  uint32_t tile_start, tile_len, shift = 0, seg_mul = 0;
   uint64_t seg_base = 0;
   int bits = p.bits;
   uint32_t* cursor = p.cursor;
@@ -271,15 +283,16 @@ __global__ void __launch_bounds__(PT_THREADS, 2 * PT_MIN_CTAS / 2) k_partition(c
     bits = msd_bits(slen, sh);
     shift = sh - bits;
     seg_base = p.segs.base[s];
+    seg_mul = p.segs.mul[s];
     cursor = p.cursor + (size_t)s * MSD_RADIX;
   }
-  partition_tile<MODE>(p, smem_raw, tile_start, tile_len, bits, shift, seg_base, cursor, 0u);
+  partition_tile<MODE>(p, smem_raw, tile_start, tile_len, bits, shift, seg_base, cursor, 0u, nullptr, nullptr, seg_mul);
 }
 
 // per-segment digit histogram of one MSD level
 __device__ __forceinline__ void msd_hist_tile(const MoveArgs& mv, const KeySrc& key, uint32_t tile_start,
                                               uint32_t tile_len, uint64_t seg_base, uint32_t shift, int bits,
-                                              uint32_t* hist /* shared, MSD_RADIX */, uint32_t* cursor) {
+                                              uint32_t* hist /* shared, MSD_RADIX */, uint32_t* cursor, uint32_t seg_mul = 0) {
   for (int i = threadIdx.x; i < MSD_RADIX; i += PT_THREADS) hist[i] = 0;
   __syncthreads();
   // all keys of the thread first (independent loads), then the shared-memory updates
@@ -292,7 +305,7 @@ __device__ __forceinline__ void msd_hist_tile(const MoveArgs& mv, const KeySrc& 
 #pragma unroll
   for (int k = 0; k < PT_ITEMS; k++) {
     const uint32_t j = threadIdx.x + k * PT_THREADS;
-    if (j < tile_len) atomicAdd(&hist[(uint32_t)((kk[k] - seg_base) >> shift) & ((1u << bits) - 1u)], 1u);
+    if (j < tile_len) atomicAdd(&hist[msd_digit(kk[k] - seg_base, shift + (uint32_t)bits, bits, seg_mul)], 1u);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < MSD_RADIX; i += PT_THREADS) {
@@ -312,7 +325,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_msd_hist(const __grid_constant__
   uint32_t sh = p.segs.shift[s];
   int bits = msd_bits(slen, sh);
   msd_hist_tile(p.mv, p.key, tile_start, tile_len, p.segs.base[s], sh - bits, bits, hist,
-                p.cursor + (size_t)s * MSD_RADIX);
+                p.cursor + (size_t)s * MSD_RADIX, p.segs.mul[s]);
 }
 
 struct PlanOut {
@@ -335,6 +348,7 @@ __device__ __forceinline__ void classify_push(const PlanOut& o, uint32_t start, 
   } else {
     uint32_t i = atomicAdd(&o.counters[1], 1u);
     o.large.start[i] = start; o.large.len[i] = len; o.large.shift[i] = shift; o.large.base[i] = base;
+    o.large.mul[i] = 0;
     atomicAdd(&o.counters[3], (len + PT_TILE - 1) / PT_TILE);
   }
 }
@@ -349,7 +363,15 @@ __global__ void __launch_bounds__(MSD_RADIX) k_msd_plan(SegList segs, uint32_t* 
   cursor[(size_t)s * MSD_RADIX + threadIdx.x] = start;
   uint32_t sh = segs.shift[s];
   uint32_t bits = (uint32_t)msd_bits(segs.len[s], sh);
-  classify_push(out, start, h, sh - bits, segs.base[s]);
+  // the keys of child d start at the first cell of digit d (see msd_digit): its base, with sh - bits bits left
+  const int e = msd_extra(sh, (int)bits);
+  const uint32_t mul = segs.mul[s];
+  const uint32_t c0 = msd_cell_lo(threadIdx.x, e, mul), c1 = msd_cell_lo(threadIdx.x + 1, e, mul);
+  const uint64_t child_base = segs.base[s] + ((uint64_t)c0 << (sh - bits - e));
+  // bits still varying inside the child: those below a cell plus what numbers the child's cells
+  const uint32_t ncell = c1 > c0 ? c1 - c0 : 1;
+  const uint32_t child_bits = (sh - bits - e) + (ncell > 1 ? 32 - __clz(ncell - 1) : 0);
+  classify_push(out, start, h, child_bits, child_base);
 }
 
 // level 0: classify the caller's segments
@@ -395,6 +417,7 @@ __global__ void __launch_bounds__(256) k_seg_rerange(SegList segs, uint32_t nseg
   uint64_t range = mx >= mn ? mx - mn : 0;
   segs.base[s] = mn;
   segs.shift[s] = range ? 64 - __clzll((long long)range) : 0;
+  segs.mul[s] = range ? msd_mul_for(range, segs.shift[s], msd_bits(segs.len[s], segs.shift[s]), segs.len[s]) : 0;
 }
 
 // exclusive prefix of tiles over the large list (single CTA; the list is short)
@@ -524,7 +547,10 @@ void hs_bucket_scatter(hs_ctx* c, const void* const* src, const MoveSet& ms, con
 // Rows grouped by bins that are unions of buckets (d_lut[bucket id] = bin; d_bin_off[bin] = first row of the bin
 // in dst): what a sender does before whole spans of rows travel to their owners (hs_dist.cu, grouped spans).
 void hs_scatter_by_bins(hs_ctx* c, const void* const* src, void* const* dst, const int32_t* esize, int ncols,
-                        const uint16_t* d_bucket, int64_t n, const uint16_t* d_lut, int32_t nbins, const uint32_t* d_bin_off) {
+                        const uint16_t* d_bucket, int64_t n, const uint16_t* d_lut, int32_t nbins, const uint32_t* d_bin_off,
+                        int narrow_col, uint64_t narrow_min) {
+  // narrow_col >= 0: that column is an int64 key at the source and is written as u32 (sign-flipped value -
+  // narrow_min); esize[narrow_col] is the 4 bytes of the destination
   if (n == 0) return;
   if (ncols > HS_MAX_MOVE) HS_THROW(HS_EUNSUPPORTED, "too many columns for the grouped scatter");
   PartParams p;
@@ -532,6 +558,12 @@ void hs_scatter_by_bins(hs_ctx* c, const void* const* src, void* const* dst, con
   p.n = (uint32_t)n;
   p.mv.n = ncols;
   for (int i = 0; i < ncols; i++) { p.mv.esize[i] = esize[i]; p.mv.src[i] = src[i]; p.mv.dst[i] = dst[i]; }
+  if (narrow_col >= 0) {
+    p.mv.esize[narrow_col] = 8;           // what the tile stages
+    p.conv_col1 = narrow_col + 1;
+    p.conv_min = narrow_min;
+    p.conv_narrow = 1;
+  }
   p.bucket = d_bucket;
   p.bin_lut = d_lut;
   p.radix = nbins;
@@ -645,6 +677,14 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     upload(large, lg_s, lg_l, large_cap);
     large.base.alloc(c, std::max(large_cap, lg_s.size() ? lg_s.size() : (size_t)1) * 8);
     large.base.zero();
+    {
+      // the key span is known for the whole table: the first level spreads it over all its bins
+      std::vector<uint32_t> mu(std::max<size_t>(lg_s.size(), 1), 0);
+      if (key.span && key_bits > 0)
+        for (size_t i = 0; i < lg_s.size(); i++) mu[i] = msd_mul_for(key.span, (uint32_t)key_bits, msd_bits(lg_l[i], (uint32_t)key_bits), lg_l[i]);
+      large.mul.alloc(c, mu.size() * 4);
+      CK(cudaMemcpyAsync(large.mul.p, mu.data(), mu.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    }
     leaf.base.alloc(c, (lf_s.size() ? lf_s.size() : 1) * 8);
     leaf.base.zero();
     upload(small, sm_s, sm_l);

@@ -15,7 +15,7 @@
 #define MSD_BITS 8
 #endif
 #define MSD_RADIX (1 << MSD_BITS)
-#define MSD_TARGET_ROWS (3300 * LEAF_MAX / 4096)   // aimed-at child size of an MSD level (a leaf holds at most LEAF_MAX rows)
+#define MSD_TARGET_ROWS (3400 * LEAF_MAX / 4096)   // aimed-at child size of an MSD level (a leaf holds at most LEAF_MAX rows)
 
 // Digit width of the MSD level that splits a segment of `len` rows whose keys still differ in their low
 // `r` bits: as many bits (at most 8) as keep the expected child, len / 2^bits, near MSD_TARGET_ROWS. A huge
@@ -31,8 +31,40 @@ struct SegList {           // device arrays
   uint32_t* start;
   uint32_t* len;
   uint32_t* shift;         // unsorted low bits of (key - base) inside the segment
-  uint64_t* base;          // subtracted from the key before digits are taken (0 until a level re-ranges)
+  uint64_t* base;          // subtracted from the key before digits are taken
+  uint32_t* mul;           // large segments: digit multiplier (msd_digit), 0 = plain top bits
 };
+
+// The digit of an MSD level. A key range rarely fills a power of two (cfg2: 100 M keys in 27 bits use 191 of the
+// 256 top-8-bit values, so the children are 34 % larger than len / 256 and many miss the leaf size). A level
+// therefore looks at MSD_EXTRA more bits than its digit has — `cells` — and, when the segment's key span is known,
+// maps the cells that can occur onto all 2^bits digits with one multiplication: digit = cell * mul >> 16. The
+// cells of a digit are contiguous, so a child is still described by (base, bits left): msd_cell_lo gives its base.
+#define MSD_EXTRA 4
+__host__ __device__ __forceinline__ int msd_extra(uint32_t r, int bits) {
+  const int e = (int)r - bits;
+  return e < MSD_EXTRA ? e : MSD_EXTRA;
+}
+__host__ __device__ __forceinline__ uint32_t msd_digit(uint64_t rel, uint32_t r, int bits, uint32_t mul) {   // rel = key - base
+  const int e = msd_extra(r, bits);
+  const uint32_t cell = (uint32_t)(rel >> (r - bits - e)) & ((1u << (bits + e)) - 1u);
+  return mul ? (uint32_t)(((uint64_t)cell * mul) >> 16) : cell >> e;
+}
+__host__ __device__ __forceinline__ uint32_t msd_cell_lo(uint32_t d, int e, uint32_t mul) {   // first cell of digit d
+  return mul ? (uint32_t)((((uint64_t)d << 16) + mul - 1) / mul) : d << e;
+}
+// multiplier for a segment of `len` rows whose keys (minus base) lie in [0, span]: the cells in use are spread over
+// just as many digits as bring the expected child to MSD_TARGET_ROWS (a leaf costs about the same whether it is
+// full or half full, so children should be as large as a leaf allows); 0 when plain top bits do the same
+__host__ __device__ __forceinline__ uint32_t msd_mul_for(uint64_t span, uint32_t r, int bits, uint32_t len) {
+  const int e = msd_extra(r, bits);
+  const uint64_t ncells = (span >> (r - bits - e)) + 1;
+  uint32_t nbins = (len + MSD_TARGET_ROWS - 1) / MSD_TARGET_ROWS;
+  if (nbins > (1u << bits)) nbins = 1u << bits;
+  if (nbins < 2) nbins = 2;
+  if (nbins == (1u << bits) && ncells >= (1ull << (bits + e))) return 0;
+  return (uint32_t)(((uint64_t)nbins << 16) / ncells);
+}
 
 #define HS_MAX_PEERS 8
 #define HS_MAX_PEER_COLS 16
@@ -88,13 +120,13 @@ static inline MoveArgs make_move(const MoveSet& ms, int src_code, int dst_code) 
 }
 
 struct ListBufs {
-  DBuf start, len, shift, base;
+  DBuf start, len, shift, base, mul;
   void alloc(hs_ctx* c, size_t cap, bool with_base = false) {
     start.alloc(c, cap * 4); len.alloc(c, cap * 4); shift.alloc(c, cap * 4);
-    if (with_base) { base.alloc(c, cap * 8); base.zero(); }
+    if (with_base) { base.alloc(c, cap * 8); base.zero(); mul.alloc(c, cap * 4); mul.zero(); }
   }
   SegList view() const {
-    return SegList{start.as<uint32_t>(), len.as<uint32_t>(), shift.as<uint32_t>(), base.as<uint64_t>()};
+    return SegList{start.as<uint32_t>(), len.as<uint32_t>(), shift.as<uint32_t>(), base.as<uint64_t>(), mul.as<uint32_t>()};
   }
 };
 
