@@ -34,6 +34,24 @@ int hs_sm_count() {
   return v;
 }
 
+void hs_upload(hs_ctx* c, void* d_dst, const void* h_src, size_t bytes) {
+  if (!bytes) return;
+  if (bytes > HS_UP_RING / 4) {
+    CK(cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, c->stream));
+    return;
+  }
+  if (!c->up_ring) CK(cudaMallocHost((void**)&c->up_ring, HS_UP_RING));
+  const size_t need = (bytes + 63) & ~(size_t)63;
+  if (c->up_at + need > HS_UP_RING) {
+    CK(cudaStreamSynchronize(c->stream));   // everything staged so far has been copied
+    c->up_at = 0;
+  }
+  unsigned char* slot = c->up_ring + c->up_at;
+  c->up_at += need;
+  memcpy(slot, h_src, bytes);
+  CK(cudaMemcpyAsync(d_dst, slot, bytes, cudaMemcpyHostToDevice, c->stream));
+}
+
 int hs_read_begin(hs_ctx* c, const void* d_src, size_t bytes) {
   if (bytes > HS_READ_BYTES) HS_THROW(HS_EINVAL, "hs_read_begin: %zu bytes", bytes);
   if (!c->rd_pin) {
@@ -420,6 +438,7 @@ int32_t hs_ctx_destroy(hs_ctx* c) {
   for (auto& s : c->stages) { cudaEventDestroy(s.e0); cudaEventDestroy(s.e1); }
   for (auto e : c->ev_free) cudaEventDestroy(e);
   for (auto& kv : c->pinned_size) cudaFreeHost(kv.first);
+  if (c->up_ring) cudaFreeHost(c->up_ring);
   if (c->rd_pin) {
     cudaFreeHost(c->rd_pin);
     for (int i = 0; i < HS_READ_SLOTS; i++) cudaEventDestroy(c->rd_ev[i]);

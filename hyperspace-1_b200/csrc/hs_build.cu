@@ -446,7 +446,7 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
     boff[b + 1] = boff[b] + ((lb >= 0 && lb < nbl) ? (int64_t)h_hist[lb] : 0);
   }
   DBuf d_off(c, ((size_t)nbl + 1) * 4);
-  CK(cudaMemcpyAsync(d_off.p, off32.data(), ((size_t)nbl + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+  hs_upload(c, d_off.p, off32.data(), ((size_t)nbl + 1) * 4);
 
   // ---- key layout and the set of travelling columns
   KeyLayout L = make_layout(cols, n_indexed, h_minmax, has_nulls);
@@ -579,7 +579,7 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
       boff[b + 1] = boff[b] + ((lb >= 0 && lb < nbl) ? (int64_t)(off32[lb + 1] - off32[lb]) : 0);
     }
     d_off.alloc(c, ((size_t)nbl + 1) * 4);
-    CK(cudaMemcpyAsync(d_off.p, off32.data(), ((size_t)nbl + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+    hs_upload(c, d_off.p, off32.data(), ((size_t)nbl + 1) * 4);
   } else {
     Stage s(c, "bucket_scatter");
     hs_bucket_scatter(c, srcs.data(), ms, bucket.as<uint16_t>(), n, nbl, d_off.as<uint32_t>());
@@ -604,7 +604,7 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
       boff[b + 1] = boff[b] + ((lb >= 0 && lb < nbl) ? (int64_t)(off32[lb + 1] - off32[lb]) : 0);
     }
     d_off.alloc(c, ((size_t)nbl + 1) * 4);
-    CK(cudaMemcpyAsync(d_off.p, off32.data(), ((size_t)nbl + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+    hs_upload(c, d_off.p, off32.data(), ((size_t)nbl + 1) * 4);
   }
   for (size_t i = 0; i < mv.size(); i++) {
     mv[i].b.alloc(c, (size_t)n * mv[i].esize + 16);
@@ -614,11 +614,16 @@ void hs_build_core(hs_ctx* c, std::vector<DevCol>& cols, int n_indexed, int32_t 
   // ---- K3: every bucket sorted on the key
   if (fused && xchg->ngroups > 0) {
     // grouped spans: the buckets of group g are sorted while the rows of group g + 1 still cross NVLink
+    struct CarryGuard {
+      SortCarry* k;
+      ~CarryGuard() { hs_sort_carry_free(k); }
+    } carry{hs_sort_carry_new(c, n)};
     for (int g = 0; g < xchg->ngroups; g++) {
       int lb0 = 0, lb1 = 0;
       xchg->deliver_group(c, g, &lb0, &lb1);
-      if (lb1 > lb0) hs_segmented_sort(c, ms, key, key_bits, nullptr, lb1 - lb0, n, off32.data() + lb0);
+      if (lb1 > lb0) hs_segmented_sort(c, ms, key, key_bits, nullptr, lb1 - lb0, n, off32.data() + lb0, carry.k);
     }
+    hs_sort_carry_finish(c, ms, key, carry.k);
   } else {
     hs_segmented_sort(c, ms, key, key_bits, d_off.as<uint32_t>(), nbl, n, off32.data());
   }

@@ -78,6 +78,10 @@ struct hs_ctx {
   int64_t last_xchg_bytes = 0;
   float last_xchg_ms = 0.f;
   // small device->host reads that must not stall the queue behind them (hs_read_begin / hs_read_wait)
+  // small host->device uploads (lists, offsets): a pageable source makes cudaMemcpyAsync wait for the stream
+  // first, which drains the queue at every upload; they go through this pinned ring instead (hs_upload)
+  unsigned char* up_ring = nullptr;
+  size_t up_at = 0;
   void* rd_pin = nullptr;            // pinned, HS_READ_SLOTS x HS_READ_BYTES
   cudaEvent_t rd_ev[4] = {nullptr, nullptr, nullptr, nullptr};
   int rd_next = 0;
@@ -203,6 +207,11 @@ void hs_sync(hs_ctx* c);
 // Copy up to HS_READ_BYTES from the device into a pinned slot and mark the point with an event; work queued
 // afterwards keeps running while the host waits for just that copy. Returns the slot.
 int hs_read_begin(hs_ctx* c, const void* d_src, size_t bytes);
+// Host -> device copy on the context's stream that never waits for the stream: the bytes are staged in a pinned
+// ring (HS_UP_RING bytes; a wrap-around waits for the stream once); h_src may be reused at once. Larger copies
+// fall back to cudaMemcpyAsync from h_src.
+#define HS_UP_RING (4u << 20)
+void hs_upload(hs_ctx* c, void* d_dst, const void* h_src, size_t bytes);
 const void* hs_read_wait(hs_ctx* c, int slot);
 
 #define API_BEGIN(ctx)                      \

@@ -210,7 +210,7 @@ struct NcclExchange : BuildExchange {
     memcpy(mine.data() + nb, minmax, (size_t)2 * HS_MAX_KEYS * 8);
     for (size_t i = 0; i < ncol; i++) mine[nb + 4 * HS_MAX_KEYS + i] = has_nulls[i];
     DBuf d_mine(c, words * 4), d_all(c, words * 4 * N);
-    CK(cudaMemcpyAsync(d_mine.p, mine.data(), words * 4, cudaMemcpyHostToDevice, c->stream));
+    hs_upload(c, d_mine.p, mine.data(), words * 4);
     NCK(g_nccl.allgather(d_mine.p, d_all.p, words * 4, NCCL_UINT8, (nccl_comm)c->comm, c->stream));
     CK(cudaMemcpyAsync(all.data(), d_all.p, words * 4 * N, cudaMemcpyDeviceToHost, c->stream));
     hs_sync(c);
@@ -314,7 +314,7 @@ struct NcclExchange : BuildExchange {
       Stage s(c, "run_transpose");
       DBuf d_runs(c, runs.size() * 4 + 16);
       if (!runs.empty())
-        CK(cudaMemcpyAsync(d_runs.p, runs.data(), runs.size() * 4, cudaMemcpyHostToDevice, c->stream));
+        hs_upload(c, d_runs.p, runs.data(), runs.size() * 4);
       for (size_t i = 0; i < bufs.size(); i++) {
         DBuf dst(c, (size_t)nrecv * esize[i] + 16);
         if (!runs.empty())
@@ -405,7 +405,7 @@ struct NcclExchange : BuildExchange {
     mine[0] = ok ? 1 : 0;
     for (int i = 0; i < ncol && ok; i++) memcpy(&mine[8 + i * sizeof(cudaIpcMemHandle_t)], &st->slots[i].handle, sizeof(cudaIpcMemHandle_t));
     DBuf d_mine(c, rec), d_all(c, rec * N);
-    CK(cudaMemcpyAsync(d_mine.p, mine.data(), rec, cudaMemcpyHostToDevice, c->stream));
+    hs_upload(c, d_mine.p, mine.data(), rec);
     NCK(g_nccl.allgather(d_mine.p, d_all.p, rec, NCCL_UINT8, (nccl_comm)c->comm, c->stream));
     CK(cudaMemcpyAsync(all.data(), d_all.p, rec * N, cudaMemcpyDeviceToHost, c->stream));
     hs_sync(c);
@@ -438,7 +438,7 @@ struct NcclExchange : BuildExchange {
     unsigned char flag = ok ? 1 : 0;
     std::vector<unsigned char> flags(N, 0);
     DBuf d_f(c, 16), d_fa(c, 16 * (size_t)N);
-    CK(cudaMemcpyAsync(d_f.p, &flag, 1, cudaMemcpyHostToDevice, c->stream));
+    hs_upload(c, d_f.p, &flag, 1);
     NCK(g_nccl.allgather(d_f.p, d_fa.p, 1, NCCL_UINT8, (nccl_comm)c->comm, c->stream));
     CK(cudaMemcpyAsync(flags.data(), d_fa.p, N, cudaMemcpyDeviceToHost, c->stream));
     hs_sync(c);
@@ -491,7 +491,7 @@ struct NcclExchange : BuildExchange {
           for (int b = 0; b < nb; b++)
             if (owner_of(b, N, nb) == o) base[o] += all_hist[(size_t)q * nb + b];
       DBuf d_base(c, (size_t)N * 4);
-      CK(cudaMemcpyAsync(d_base.p, base.data(), (size_t)N * 4, cudaMemcpyHostToDevice, c->stream));
+      hs_upload(c, d_base.p, base.data(), (size_t)N * 4);
       std::vector<const void*> xsrc(srcs, srcs + ncol);
       xsrc.push_back(d_bucket);
       CK(cudaEventRecord(e0, c->stream));
@@ -503,7 +503,7 @@ struct NcclExchange : BuildExchange {
       // one kernel: the bucket scatter stores every row at its final place in the owner's memory
       Stage s(c, "scatter_to_owners");
       DBuf d_base(c, (size_t)nb * 4);
-      CK(cudaMemcpyAsync(d_base.p, run_base.data(), (size_t)nb * 4, cudaMemcpyHostToDevice, c->stream));
+      hs_upload(c, d_base.p, run_base.data(), (size_t)nb * 4);
       CK(cudaEventRecord(e0, c->stream));
       hs_bucket_scatter_peers(c, srcs, esize.data(), ncol, st->peer_ptr.data(), N, d_bucket, n_local, nb,
                               d_base.as<uint32_t>());
@@ -526,7 +526,7 @@ struct NcclExchange : BuildExchange {
       {
         Stage s(c, "bucket_scatter");
         DBuf d_loff(c, ((size_t)nb + 1) * 4);
-        CK(cudaMemcpyAsync(d_loff.p, local_off.data(), ((size_t)nb + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+        hs_upload(c, d_loff.p, local_off.data(), ((size_t)nb + 1) * 4);
         hs_bucket_scatter(c, srcs, ms, d_bucket, n_local, nb, d_loff.as<uint32_t>());
       }
       // every sender starts with a different owner (me+1, me+2, ..., me last): if all ranks walked the buckets in
@@ -548,7 +548,7 @@ struct NcclExchange : BuildExchange {
       }
       Stage s(c, "runs_to_owners");
       DBuf d_runs(c, runs.size() * 4 + 16);
-      if (!runs.empty()) CK(cudaMemcpyAsync(d_runs.p, runs.data(), runs.size() * 4, cudaMemcpyHostToDevice, c->stream));
+      if (!runs.empty()) hs_upload(c, d_runs.p, runs.data(), runs.size() * 4);
       CK(cudaEventRecord(e0, c->stream));
       if (!runs.empty()) {
         PeerCols pc;
@@ -598,7 +598,7 @@ struct NcclExchange : BuildExchange {
         recv[i] = owner_sorted[i].p;
       }
       DBuf d_off(c, ((size_t)nbl + 1) * 4);
-      CK(cudaMemcpyAsync(d_off.p, seg_off.data(), ((size_t)nbl + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+      hs_upload(c, d_off.p, seg_off.data(), ((size_t)nbl + 1) * 4);
       hs_bucket_scatter(c, rsrc.data(), ms, (const uint16_t*)st->slots[ncol].ptr, nrecv, nbl, d_off.as<uint32_t>(), blo,
                         narrow ? key_col : -1, key_min);
       hs_sync(c);   // seg_off is the caller's vector, d_off dies here
@@ -698,8 +698,8 @@ struct NcclExchange : BuildExchange {
     {
       Stage s(c, "group_scatter");
       DBuf d_lut(c, (size_t)nb * 2 + 16), d_boff(c, ((size_t)nbins + 1) * 4);
-      CK(cudaMemcpyAsync(d_lut.p, lut.data(), (size_t)nb * 2, cudaMemcpyHostToDevice, c->stream));
-      CK(cudaMemcpyAsync(d_boff.p, my_off.data(), ((size_t)nbins + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+      hs_upload(c, d_lut.p, lut.data(), (size_t)nb * 2);
+      hs_upload(c, d_boff.p, my_off.data(), ((size_t)nbins + 1) * 4);
       std::vector<const void*> xsrc(srcs, srcs + ncol);
       xsrc.push_back(d_bucket);
       std::vector<void*> xdst((size_t)ncx);
@@ -748,7 +748,7 @@ struct NcclExchange : BuildExchange {
       recv[i] = owner_sorted[i].p;
     }
     d_seg.alloc(c, ((size_t)nbl + 1) * 4);
-    CK(cudaMemcpyAsync(d_seg.p, seg_off.data(), ((size_t)nbl + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+    hs_upload(c, d_seg.p, seg_off.data(), ((size_t)nbl + 1) * 4);
     ngroups = G;
     return nrecv;
   }
@@ -858,7 +858,7 @@ static void dist_build_rows_first(hs_ctx* c, std::vector<DevCol>& cols, int n_in
     std::vector<uint32_t> off((size_t)nb + 1, 0);
     for (int b = 0; b < nb; b++) off[b + 1] = off[b] + h_hist[b];
     DBuf d_off(c, ((size_t)nb + 1) * 4), iota(c, (size_t)std::max<int64_t>(n, 1) * 4);
-    CK(cudaMemcpyAsync(d_off.p, off.data(), ((size_t)nb + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+    hs_upload(c, d_off.p, off.data(), ((size_t)nb + 1) * 4);
     if (n > 0) {
       LAUNCH(c, k_rf_iota, rf_grid(n), 256, 0, iota.as<uint32_t>(), n);
       MoveSet ms;
@@ -890,7 +890,7 @@ static void dist_build_rows_first(hs_ctx* c, std::vector<DevCol>& cols, int n_in
   for (int i = 0; i < ncols; i++) nulls_here[i] = cols[i].validity && cols[i].null_count != 0;
   {
     DBuf d_in(c, (size_t)ncols), d_all(c, (size_t)ncols * N);
-    CK(cudaMemcpyAsync(d_in.p, nulls_here.data(), (size_t)ncols, cudaMemcpyHostToDevice, c->stream));
+    hs_upload(c, d_in.p, nulls_here.data(), (size_t)ncols);
     NCK(g_nccl.allgather(d_in.p, d_all.p, (size_t)ncols, NCCL_UINT8, comm, c->stream));
     CK(cudaMemcpyAsync(nulls_any.data(), d_all.p, (size_t)ncols * N, cudaMemcpyDeviceToHost, c->stream));
     hs_sync(c);
@@ -968,7 +968,7 @@ static void dist_build_rows_first(hs_ctx* c, std::vector<DevCol>& cols, int n_in
   }
   {
     DBuf d_in(c, mine.size() * 8), d_all(c, all.size() * 8);
-    CK(cudaMemcpyAsync(d_in.p, mine.data(), mine.size() * 8, cudaMemcpyHostToDevice, c->stream));
+    hs_upload(c, d_in.p, mine.data(), mine.size() * 8);
     NCK(g_nccl.allgather(d_in.p, d_all.p, mine.size(), NCCL_UINT64, comm, c->stream));
     CK(cudaMemcpyAsync(all.data(), d_all.p, all.size() * 8, cudaMemcpyDeviceToHost, c->stream));
     hs_sync(c);

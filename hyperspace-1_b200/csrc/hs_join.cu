@@ -533,7 +533,7 @@ void hs_offsets_to_device(hs_ctx* c, const int64_t* boff, int32_t nb, int64_t nr
   out.alloc(c, ((size_t)nb + 1) * 4);
   // h is pageable memory: the call returns once the bytes sit in the driver's staging buffer, so h may go out of
   // scope without waiting for the stream
-  CK(cudaMemcpyAsync(out.p, h.data(), ((size_t)nb + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+  hs_upload(c, out.p, h.data(), ((size_t)nb + 1) * 4);
 }
 
 // (left row, right row) pairs of a join driven from side A: for every row of A the matching range of B's run in
@@ -644,7 +644,7 @@ bool hs_pack_key_tuples(hs_ctx* ctx, const KeySpec& a, int64_t na, const KeySpec
   DBuf mm(ctx, 2 * HS_MAX_KEYS * 8);
   uint64_t init[2 * HS_MAX_KEYS], h_mm[2 * HS_MAX_KEYS];
   for (int k = 0; k < HS_MAX_KEYS; k++) { init[2 * k] = ~0ull; init[2 * k + 1] = 0; }
-  CK(cudaMemcpyAsync(mm.p, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+  hs_upload(ctx, mm.p, init, sizeof init);
   if (na > 0) LAUNCH(ctx, k_keys_range, HS_NUM_SMS * 8, 256, 0, a, na, mm.as<uint64_t>());
   if (nrows_b > 0) LAUNCH(ctx, k_keys_range, HS_NUM_SMS * 8, 256, 0, b, nrows_b, mm.as<uint64_t>());
   CK(cudaMemcpyAsync(h_mm, mm.p, sizeof h_mm, cudaMemcpyDeviceToHost, ctx->stream));
@@ -798,7 +798,7 @@ extern "C" int32_t hs_join_bucketed(hs_ctx* ctx, const hs_index_view* left, cons
     DBuf d_tb(ctx, (size_t)ntiles * 4 + 4), d_ts(ctx, (size_t)ntiles * 4 + 4), d_tl(ctx, (size_t)ntiles * 4 + 4),
         d_cnt(ctx, (size_t)ntiles * 4 + 4), d_total(ctx, 8), d_win(ctx, (size_t)ntiles * 8 + 8),
         d_first(ctx, ((size_t)nb + 1) * 4), d_boff(ctx, ((size_t)nb + 4) * 4);
-    CK(cudaMemcpyAsync(d_first.p, first_tile.data(), ((size_t)nb + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
+    hs_upload(ctx, d_first.p, first_tile.data(), ((size_t)nb + 1) * 4);
     if (ntiles)
       LAUNCH(ctx, k_join_make_tiles, (ntiles + 255) / 256, 256, 0, loff.as<uint32_t>(), d_first.as<uint32_t>(), nb, ntiles,
              d_tb.as<uint32_t>(), d_ts.as<uint32_t>(), d_tl.as<uint32_t>());

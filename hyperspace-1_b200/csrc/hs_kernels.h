@@ -90,8 +90,15 @@ void hs_bucket_scatter_peers(hs_ctx* c, const void* const* src, const int32_t* e
                              bool by_owner = false, int narrow_col = -1, uint64_t narrow_min = 0);
 // Sort every segment [seg_off[s], seg_off[s+1]) of ms.a by the key; result in ms.a. key_bits = significant
 // low bits of the key. d_seg_off: device u32[nseg+1].
+// carry: several calls over disjoint segments of the same buffers (the grouped multi-GPU build) run only the
+// first MSD level each; children still larger than a leaf collect in the carry and hs_sort_carry_finish takes
+// them through the remaining levels together (a handful of leftovers would otherwise cost every call a level).
+struct SortCarry;
+SortCarry* hs_sort_carry_new(hs_ctx* c, int64_t n);
+void hs_sort_carry_finish(hs_ctx* c, MoveSet& ms, const KeySrc& key, SortCarry* k);
+void hs_sort_carry_free(SortCarry* k);
 void hs_segmented_sort(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_seg_off,
-                       int64_t nseg, int64_t n, const uint32_t* h_seg_off);
+                       int64_t nseg, int64_t n, const uint32_t* h_seg_off, SortCarry* carry = nullptr);
 // Same, for an explicit device list of segments (start,len), all with the same key_bits.
 void hs_segmented_sort_list(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_start,
                             const uint32_t* d_len, int64_t nseg, int64_t n);

@@ -331,6 +331,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_msd_hist(const __grid_constant__
 struct PlanOut {
   SegList leaf, large, copy, small;
   uint32_t* counters;  // [0] leaf, [1] large, [2] copy, [3] tiles of large, [4] wide leaves, [5] small
+  uint32_t* lcounters; // where [1] and [3] are counted: `counters`, or the carry list shared by several sort calls
 };
 
 __device__ __forceinline__ void classify_push(const PlanOut& o, uint32_t start, uint32_t len, uint32_t shift,
@@ -346,10 +347,10 @@ __device__ __forceinline__ void classify_push(const PlanOut& o, uint32_t start, 
     uint32_t i = atomicAdd(&o.counters[2], 1u);
     o.copy.start[i] = start; o.copy.len[i] = len; o.copy.shift[i] = 0;
   } else {
-    uint32_t i = atomicAdd(&o.counters[1], 1u);
+    uint32_t i = atomicAdd(&o.lcounters[1], 1u);
     o.large.start[i] = start; o.large.len[i] = len; o.large.shift[i] = shift; o.large.base[i] = base;
     o.large.mul[i] = 0;
-    atomicAdd(&o.counters[3], (len + PT_TILE - 1) / PT_TILE);
+    atomicAdd(&o.lcounters[3], (len + PT_TILE - 1) / PT_TILE);
   }
 }
 
@@ -632,87 +633,17 @@ static void set_smem_attrs_once() {
   done = true;
 }
 
-static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_seg_off,
-                         const uint32_t* d_start, const uint32_t* d_len, int64_t nseg, int64_t n,
-                         const uint32_t* h_seg_off) {
-  if (n == 0 || nseg == 0) return;
-  set_smem_attrs_once();
-  size_t cap_leaf = (size_t)nseg, cap_large = (size_t)(n / LEAF_MAX + 1);
-  ListBufs leaf, large, copy, small;
-  DBuf counters(c, 8 * 4), tile_prefix(c, (cap_large + 1) * 4);
+struct SortCarry {         // children still larger than a leaf after the first level of several sort calls
+  ListBufs large;
+  DBuf counters;           // [1] segments, [3] their tiles
+  size_t cap_large = 0;
+};
+
+// The MSD levels over `large` until nothing is larger than a leaf (with a carry: exactly one level).
+static void level_loop(hs_ctx* c, MoveSet& ms, const KeySrc& key, ListBufs& large, DBuf& tile_prefix, uint32_t n_large,
+                       uint32_t n_tiles, int src, int level, size_t cap_large, SortCarry* carry) {
   uint32_t h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  const bool ext = ms.s0[0] != nullptr;   // the rows start outside buffer A: every row has to be moved
-  int src = ext ? BUF_S0 : BUF_A;
-  LeafLaunch ll0;
-  if (h_seg_off) {
-    // ---- level 0 on the host
-    std::vector<uint32_t> tp;
-    std::vector<uint32_t> lf_s, lf_l, lg_s, lg_l, sm_s, sm_l, cp_s, cp_l;
-    tp.push_back(0);
-    for (int64_t sidx = 0; sidx < nseg; sidx++) {
-      uint32_t st = h_seg_off[sidx], len = h_seg_off[sidx + 1] - st;
-      if (len == 0 || (len < 2 && !ext)) continue;
-      if (len <= SMALL_MAX) { sm_s.push_back(st); sm_l.push_back(len); }
-      else if (len <= LEAF_MAX) { lf_s.push_back(st); lf_l.push_back(len); }
-      else if (key_bits > 0) { lg_s.push_back(st); lg_l.push_back(len); tp.push_back(tp.back() + (len + PT_TILE - 1) / PT_TILE); }
-      else if (ext) { cp_s.push_back(st); cp_l.push_back(len); }
-      // larger than a leaf with no key bits: all keys equal; in place when the rows already are in A
-    }
-    h[0] = (uint32_t)lf_s.size();
-    h[1] = (uint32_t)lg_s.size();
-    h[2] = (uint32_t)cp_s.size();
-    h[3] = tp.back();
-    h[5] = (uint32_t)sm_s.size();
-    auto upload = [&](ListBufs& lb, const std::vector<uint32_t>& st, const std::vector<uint32_t>& ln, size_t cap = 0) {
-      size_t m = st.size();
-      lb.alloc(c, std::max(cap, m ? m : 1));
-      if (!m) return;
-      std::vector<uint32_t> sh(m, (uint32_t)key_bits);
-      CK(cudaMemcpyAsync(lb.start.p, st.data(), m * 4, cudaMemcpyHostToDevice, c->stream));
-      CK(cudaMemcpyAsync(lb.len.p, ln.data(), m * 4, cudaMemcpyHostToDevice, c->stream));
-      CK(cudaMemcpyAsync(lb.shift.p, sh.data(), m * 4, cudaMemcpyHostToDevice, c->stream));
-    };
-    const size_t large_cap = 0;
-    upload(leaf, lf_s, lf_l);
-    upload(large, lg_s, lg_l, large_cap);
-    large.base.alloc(c, std::max(large_cap, lg_s.size() ? lg_s.size() : (size_t)1) * 8);
-    large.base.zero();
-    {
-      // the key span is known for the whole table: the first level spreads it over all its bins
-      std::vector<uint32_t> mu(std::max<size_t>(lg_s.size(), 1), 0);
-      if (key.span && key_bits > 0)
-        for (size_t i = 0; i < lg_s.size(); i++) mu[i] = msd_mul_for(key.span, (uint32_t)key_bits, msd_bits(lg_l[i], (uint32_t)key_bits), lg_l[i]);
-      large.mul.alloc(c, mu.size() * 4);
-      CK(cudaMemcpyAsync(large.mul.p, mu.data(), mu.size() * 4, cudaMemcpyHostToDevice, c->stream));
-    }
-    leaf.base.alloc(c, (lf_s.size() ? lf_s.size() : 1) * 8);
-    leaf.base.zero();
-    upload(small, sm_s, sm_l);
-    upload(copy, cp_s, cp_l);
-    CK(cudaMemcpyAsync(counters.p, h, 32, cudaMemcpyHostToDevice, c->stream));
-    CK(cudaMemcpyAsync(tile_prefix.p, tp.data(), tp.size() * 4, cudaMemcpyHostToDevice, c->stream));
-    run_leaf_and_copy(c, ms, key, src, leaf, h[0], copy, h[2], counters.as<uint32_t>(), ll0, &small, h[5]);
-    launch_wide(c, ll0, counters.as<uint32_t>());
-  } else {
-    leaf.alloc(c, cap_leaf, true);
-    large.alloc(c, cap_large, true);
-    copy.alloc(c, cap_large);
-    small.alloc(c, cap_leaf);
-    counters.zero();
-    PlanOut po{leaf.view(), large.view(), copy.view(), small.view(), counters.as<uint32_t>()};
-    hs_stage_begin(c, "sort_plan");
-    LAUNCH(c, k_classify, (unsigned)((nseg + 255) / 256), 256, 0, d_seg_off, d_start, d_len, nseg, (uint32_t)key_bits, po);
-    LAUNCH(c, k_tile_prefix, 1, 1024, 0, large.view(), counters.as<uint32_t>(), tile_prefix.as<uint32_t>());
-    hs_stage_end(c);
-    // the list lengths come back first: grids sized by upper bounds (rows / 64 CTAs) cost more in empty CTAs
-    // than the round trip does
-    if (ext) HS_THROW(HS_EINVAL, "external start buffers need host-known segments");
-    memcpy(h, hs_read_wait(c, hs_read_begin(c, counters.p, 32)), 32);
-    run_leaf_and_copy(c, ms, key, BUF_A, leaf, h[0], copy, 0, counters.as<uint32_t>(), ll0, &small, h[5]);
-    launch_wide(c, ll0, counters.as<uint32_t>());
-  }
-  uint32_t n_large = h[1], n_tiles = h[3];
-  int level = 0;   // children of a level are re-ranged before they are split again
+  ListBufs leaf, copy, small;
   while (n_large > 0) {
     if (++level > 80) HS_THROW(HS_ECUDA, "segmented sort did not converge");
     // histograms -> cursors + child lists
@@ -751,11 +682,15 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     nsmall.alloc(c, children);
     DBuf ncounters(c, 8 * 4);
     ncounters.zero();
-    PlanOut npo{nleaf.view(), nlarge.view(), ncopy.view(), nsmall.view(), ncounters.as<uint32_t>()};
+    // with a carry, the children that are still large join the list all calls share: one more level for all of
+    // them at the end (hs_sort_carry_finish) instead of one per call
+    const bool to_carry = carry != nullptr;
+    PlanOut npo{nleaf.view(), to_carry ? carry->large.view() : nlarge.view(), ncopy.view(), nsmall.view(),
+                ncounters.as<uint32_t>(), to_carry ? carry->counters.as<uint32_t>() : ncounters.as<uint32_t>()};
     hs_stage_begin(c, "msd_plan");
     LAUNCH(c, k_msd_plan, n_large, MSD_RADIX, 0, large.view(), cursor.as<uint32_t>(), npo);
     DBuf ntile_prefix(c, (cap_large + 1) * 4);
-    LAUNCH(c, k_tile_prefix, 1, 1024, 0, nlarge.view(), ncounters.as<uint32_t>(), ntile_prefix.as<uint32_t>());
+    if (!to_carry) LAUNCH(c, k_tile_prefix, 1, 1024, 0, nlarge.view(), ncounters.as<uint32_t>(), ntile_prefix.as<uint32_t>());
     hs_stage_end(c);
     // the child counts travel to the host while the scatter runs: the leaf grids below are exact
     const int slot = hs_read_begin(c, ncounters.p, 32);
@@ -767,6 +702,7 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
     LeafLaunch ll;
     run_leaf_and_copy(c, ms, key, src, nleaf, h[0], ncopy, h[2], ncounters.as<uint32_t>(), ll, &nsmall, h[5]);
     launch_wide(c, ll, ncounters.as<uint32_t>());
+    if (to_carry) return;
     large = std::move(nlarge);
     leaf = std::move(nleaf);
     copy = std::move(ncopy);
@@ -777,9 +713,110 @@ static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits
   }
 }
 
+static void segsort_impl(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_seg_off,
+                         const uint32_t* d_start, const uint32_t* d_len, int64_t nseg, int64_t n,
+                         const uint32_t* h_seg_off, SortCarry* carry = nullptr) {
+  if (carry && !h_seg_off) HS_THROW(HS_EINVAL, "a sort carry needs host-known segments");
+  if (n == 0 || nseg == 0) return;
+  set_smem_attrs_once();
+  size_t cap_leaf = (size_t)nseg, cap_large = (size_t)(n / LEAF_MAX + 1);
+  ListBufs leaf, large, copy, small;
+  DBuf counters(c, 8 * 4), tile_prefix(c, (cap_large + 1) * 4);
+  uint32_t h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  const bool ext = ms.s0[0] != nullptr;   // the rows start outside buffer A: every row has to be moved
+  int src = ext ? BUF_S0 : BUF_A;
+  LeafLaunch ll0;
+  if (h_seg_off) {
+    // ---- level 0 on the host
+    std::vector<uint32_t> tp;
+    std::vector<uint32_t> lf_s, lf_l, lg_s, lg_l, sm_s, sm_l, cp_s, cp_l;
+    tp.push_back(0);
+    for (int64_t sidx = 0; sidx < nseg; sidx++) {
+      uint32_t st = h_seg_off[sidx], len = h_seg_off[sidx + 1] - st;
+      if (len == 0 || (len < 2 && !ext)) continue;
+      if (len <= SMALL_MAX) { sm_s.push_back(st); sm_l.push_back(len); }
+      else if (len <= LEAF_MAX) { lf_s.push_back(st); lf_l.push_back(len); }
+      else if (key_bits > 0) { lg_s.push_back(st); lg_l.push_back(len); tp.push_back(tp.back() + (len + PT_TILE - 1) / PT_TILE); }
+      else if (ext) { cp_s.push_back(st); cp_l.push_back(len); }
+      // larger than a leaf with no key bits: all keys equal; in place when the rows already are in A
+    }
+    h[0] = (uint32_t)lf_s.size();
+    h[1] = (uint32_t)lg_s.size();
+    h[2] = (uint32_t)cp_s.size();
+    h[3] = tp.back();
+    h[5] = (uint32_t)sm_s.size();
+    auto upload = [&](ListBufs& lb, const std::vector<uint32_t>& st, const std::vector<uint32_t>& ln, size_t cap = 0) {
+      size_t m = st.size();
+      lb.alloc(c, std::max(cap, m ? m : 1));
+      if (!m) return;
+      std::vector<uint32_t> sh(m, (uint32_t)key_bits);
+      hs_upload(c, lb.start.p, st.data(), m * 4);
+      hs_upload(c, lb.len.p, ln.data(), m * 4);
+      hs_upload(c, lb.shift.p, sh.data(), m * 4);
+    };
+    const size_t large_cap = 0;
+    upload(leaf, lf_s, lf_l);
+    upload(large, lg_s, lg_l, large_cap);
+    large.base.alloc(c, std::max(large_cap, lg_s.size() ? lg_s.size() : (size_t)1) * 8);
+    large.base.zero();
+    {
+      // the key span is known for the whole table: the first level spreads it over all its bins
+      std::vector<uint32_t> mu(std::max<size_t>(lg_s.size(), 1), 0);
+      if (key.span && key_bits > 0)
+        for (size_t i = 0; i < lg_s.size(); i++) mu[i] = msd_mul_for(key.span, (uint32_t)key_bits, msd_bits(lg_l[i], (uint32_t)key_bits), lg_l[i]);
+      large.mul.alloc(c, mu.size() * 4);
+      hs_upload(c, large.mul.p, mu.data(), mu.size() * 4);
+    }
+    leaf.base.alloc(c, (lf_s.size() ? lf_s.size() : 1) * 8);
+    leaf.base.zero();
+    upload(small, sm_s, sm_l);
+    upload(copy, cp_s, cp_l);
+    hs_upload(c, counters.p, h, 32);
+    hs_upload(c, tile_prefix.p, tp.data(), tp.size() * 4);
+    run_leaf_and_copy(c, ms, key, src, leaf, h[0], copy, h[2], counters.as<uint32_t>(), ll0, &small, h[5]);
+    launch_wide(c, ll0, counters.as<uint32_t>());
+  } else {
+    leaf.alloc(c, cap_leaf, true);
+    large.alloc(c, cap_large, true);
+    copy.alloc(c, cap_large);
+    small.alloc(c, cap_leaf);
+    counters.zero();
+    PlanOut po{leaf.view(), large.view(), copy.view(), small.view(), counters.as<uint32_t>(), counters.as<uint32_t>()};
+    hs_stage_begin(c, "sort_plan");
+    LAUNCH(c, k_classify, (unsigned)((nseg + 255) / 256), 256, 0, d_seg_off, d_start, d_len, nseg, (uint32_t)key_bits, po);
+    LAUNCH(c, k_tile_prefix, 1, 1024, 0, large.view(), counters.as<uint32_t>(), tile_prefix.as<uint32_t>());
+    hs_stage_end(c);
+    // the list lengths come back first: grids sized by upper bounds (rows / 64 CTAs) cost more in empty CTAs
+    // than the round trip does
+    if (ext) HS_THROW(HS_EINVAL, "external start buffers need host-known segments");
+    memcpy(h, hs_read_wait(c, hs_read_begin(c, counters.p, 32)), 32);
+    run_leaf_and_copy(c, ms, key, BUF_A, leaf, h[0], copy, 0, counters.as<uint32_t>(), ll0, &small, h[5]);
+    launch_wide(c, ll0, counters.as<uint32_t>());
+  }
+  level_loop(c, ms, key, large, tile_prefix, h[1], h[3], src, 0, cap_large, carry);
+}
+
 void hs_segmented_sort(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_seg_off,
-                       int64_t nseg, int64_t n, const uint32_t* h_seg_off) {
-  segsort_impl(c, ms, key, key_bits, d_seg_off, nullptr, nullptr, nseg, n, h_seg_off);
+                       int64_t nseg, int64_t n, const uint32_t* h_seg_off, SortCarry* carry) {
+  segsort_impl(c, ms, key, key_bits, d_seg_off, nullptr, nullptr, nseg, n, h_seg_off, carry);
+}
+SortCarry* hs_sort_carry_new(hs_ctx* c, int64_t n) {
+  SortCarry* k = new SortCarry();
+  k->cap_large = (size_t)(n / LEAF_MAX + 1);
+  k->large.alloc(c, k->cap_large, true);
+  k->counters.alloc(c, 8 * 4);
+  k->counters.zero();
+  return k;
+}
+void hs_sort_carry_free(SortCarry* k) { delete k; }
+void hs_sort_carry_finish(hs_ctx* c, MoveSet& ms, const KeySrc& key, SortCarry* k) {
+  uint32_t h[8];
+  memcpy(h, hs_read_wait(c, hs_read_begin(c, k->counters.p, 32)), 32);
+  if (!h[1]) return;
+  // the children were written into buffer B by the first level of their call
+  DBuf tile_prefix(c, (k->cap_large + 1) * 4);
+  LAUNCH(c, k_tile_prefix, 1, 1024, 0, k->large.view(), k->counters.as<uint32_t>(), tile_prefix.as<uint32_t>());
+  level_loop(c, ms, key, k->large, tile_prefix, h[1], h[3], BUF_B, 1, k->cap_large, nullptr);
 }
 void hs_segmented_sort_list(hs_ctx* c, MoveSet& ms, const KeySrc& key, int key_bits, const uint32_t* d_start,
                             const uint32_t* d_len, int64_t nseg, int64_t n) {
