@@ -623,7 +623,7 @@ struct NcclExchange : BuildExchange {
                          const std::vector<uint32_t>& seg_off) {
     const int ncol = (int)esize.size(), ncx = ncol + 1;   // + the bucket ids
     const char* ge = getenv("HSGPU_XCHG_GROUPS");
-    G = ge && atoi(ge) > 0 ? std::min(atoi(ge), 16) : 5;
+    G = ge && atoi(ge) > 0 ? std::min(atoi(ge), 16) : 4;   // measured at N=8: 3 groups 8.30 ms, 4 groups 8.02, 5 groups 9.39
     col_es = esize;
     // owner o holds buckets [olo[o], olo[o + 1]); its group g the local buckets lb with lb * G / count == g
     std::vector<int> olo((size_t)N + 1, nb);
@@ -672,10 +672,10 @@ struct NcclExchange : BuildExchange {
       CK(cudaEventCreate(&st->x_e0));
       CK(cudaEventCreate(&st->x_e1));
     }
-    // one copy at a time leaves NVLink idle between copies (measured at N=8: 437 GB/s per GPU with one stream):
-    // the copies of a group are spread over several streams, so that copies to different owners overlap
+    // the copies of a group can be spread over several streams (HSGPU_XCHG_STREAMS); measured at N=8 that does
+    // not help — 437 GB/s per GPU with one stream, 440 with four, 428 with seven — so one is the default
     const char* se = getenv("HSGPU_XCHG_STREAMS");
-    const int S = std::max(1, std::min(se && atoi(se) > 0 ? atoi(se) : 2, 8));
+    const int S = std::max(1, std::min(se && atoi(se) > 0 ? atoi(se) : 1, 8));
     while ((int)st->cs.size() < S) {
       int lo = 0, hi = 0;
       cudaStream_t q;
