@@ -18,8 +18,16 @@
 
 // shared memory carve-up of the partition kernel
 #define STAGE_BYTES (PT_TILE * 8 + 128)   // one column slice of a tile + alignment slack
+// Landing buffers for the column slices of a tile. With two, the next column is already in flight while the
+// current one is scattered, but a tile then needs 104 KB and two tiles fill an SM; with one (64 KB) THREE tiles are
+// resident, each waiting for its next column while the other two work — measured faster (the kernel is a chain
+// of dependent steps per tile and runs at 30 % issue utilisation: a third chain pays more than the prefetch).
+#ifndef PT_STAGES
+#define PT_STAGES 1
+#endif
+#define PT_PART_CTAS (PT_STAGES == 1 ? 3 : 2)   // resident CTAs per SM k_partition is compiled for
 struct TileSmem {
-  unsigned char* stage[2];  // TMA landing buffers (double buffered over the columns)
+  unsigned char* stage[2];  // TMA landing buffers (stage[1] == stage[0] when PT_STAGES == 1)
   uint32_t* gdst;           // PT_TILE: global destination row of every tile-sorted position
   uint16_t* inv;            // PT_TILE: tile row that lands at every tile-sorted position
   uint32_t* cnt;            // radix_pad: counters, then first position of every digit
@@ -27,25 +35,26 @@ struct TileSmem {
   uint32_t* gbase;          // radix_pad: reserved global run start per digit
   uint32_t* scratch;        // PT_SCRATCH
   uint64_t* bar;            // 3 mbarriers
-  unsigned char* bstage;    // TMA landing buffer of the tile's bucket ids (u16)
+  unsigned char* bstage;    // TMA landing buffer of the tile's bucket ids (u16): the ids are in registers before
+                            // the first destination is written, so it shares the bytes of gdst
 };
 __device__ __forceinline__ TileSmem carve(unsigned char* base, int radix_pad) {
   TileSmem s;
   s.stage[0] = base;
-  s.stage[1] = base + STAGE_BYTES;
-  s.gdst = (uint32_t*)(base + 2 * STAGE_BYTES);
+  s.stage[1] = base + (PT_STAGES - 1) * STAGE_BYTES;
+  s.gdst = (uint32_t*)(base + PT_STAGES * STAGE_BYTES);
   s.inv = (uint16_t*)(s.gdst + PT_TILE);
   s.cnt = (uint32_t*)(s.inv + PT_TILE);
   s.tot = s.cnt + radix_pad;
   s.gbase = s.tot + radix_pad;
   s.scratch = s.gbase + radix_pad;
   s.bar = (uint64_t*)(s.scratch + PT_SCRATCH);
-  s.bstage = (unsigned char*)(s.bar + 4);
+  s.bstage = (unsigned char*)s.gdst;
   return s;
 }
 static size_t tile_smem_bytes(int radix_pad) {
-  return (size_t)2 * STAGE_BYTES + (size_t)PT_TILE * 4 + (size_t)PT_TILE * 2 + (size_t)3 * radix_pad * 4 +
-         PT_SCRATCH * 4 + 32 + (size_t)PT_TILE * 2 + 32;
+  return (size_t)PT_STAGES * STAGE_BYTES + (size_t)PT_TILE * 4 + (size_t)PT_TILE * 2 + (size_t)3 * radix_pad * 4 +
+         PT_SCRATCH * 4 + 32;
 }
 
 struct PartParams {
@@ -182,7 +191,7 @@ __device__ __forceinline__ void partition_tile(const PartParams& p, unsigned cha
     if (MODE != 1) issue_slice(p.bucket, 2, tile_start, tile_len, sm.bstage, &sm.bar[2]);
     int c0 = col_at(0);
     issue_slice(p.mv.src[c0], p.mv.esize[c0], tile_start, tile_len, sm.stage[0], &sm.bar[0]);
-    if (ncols > 1) {
+    if (PT_STAGES == 2 && ncols > 1) {
       int c1 = col_at(1);
       issue_slice(p.mv.src[c1], p.mv.esize[c1], tile_start, tile_len, sm.stage[1], &sm.bar[1]);
     }
@@ -229,8 +238,8 @@ __device__ __forceinline__ void partition_tile(const PartParams& p, unsigned cha
   }
   __syncthreads();
   for (int i = 0; i < ncols; i++) {
-    const int c = col_at(i), b = i & 1, es = p.mv.esize[c];
-    mbar_wait(&sm.bar[b], ((uint32_t)(i >> 1) ^ (ph_in >> b)) & 1u);
+    const int c = col_at(i), b = PT_STAGES == 2 ? (i & 1) : 0, es = p.mv.esize[c];
+    mbar_wait(&sm.bar[b], ((uint32_t)(PT_STAGES == 2 ? i >> 1 : i) ^ (ph_in >> b)) & 1u);
     const uint32_t lead = slice_lead(p.mv.src[c], es, tile_start);
     if (MODE == 2 && c + 1 == p.conv_col1) {
       scatter_column_peers_narrow(sm.stage[b], lead, p.pdst, c, tile_len, sm.inv, sm.gdst, p.conv_min);
@@ -252,17 +261,19 @@ __device__ __forceinline__ void partition_tile(const PartParams& p, unsigned cha
       default: scatter_column<uint8_t>(sm.stage[b], lead, (uint8_t*)p.mv.dst[c], tile_len, sm.inv, sm.gdst); break;
     }
     __syncthreads();  // everyone is done with stage[b]: it can be refilled
-    if (threadIdx.x == 0 && i + 2 < ncols) {
-      int cn = col_at(i + 2);
+    if (threadIdx.x == 0 && i + PT_STAGES < ncols) {
+      int cn = col_at(i + PT_STAGES);
       issue_slice(p.mv.src[cn], p.mv.esize[cn], tile_start, tile_len, sm.stage[b], &sm.bar[b]);
     }
   }
   if (ext_phase)
-    *ext_phase = ph_in ^ (uint32_t)(((ncols + 1) >> 1) & 1) ^ (uint32_t)(((ncols >> 1) & 1) << 1) ^ (MODE != 1 ? 4u : 0u);
+    *ext_phase = PT_STAGES == 2
+        ? ph_in ^ (uint32_t)(((ncols + 1) >> 1) & 1) ^ (uint32_t)(((ncols >> 1) & 1) << 1) ^ (MODE != 1 ? 4u : 0u)
+        : ph_in ^ (uint32_t)(ncols & 1) ^ (MODE != 1 ? 4u : 0u);
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(PT_THREADS, 2 * PT_MIN_CTAS / 2) k_partition(const __grid_constant__ PartParams p) {
+__global__ void __launch_bounds__(PT_THREADS, PT_PART_CTAS) k_partition(const __grid_constant__ PartParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   uint32_t tile_start, tile_len, shift = 0, seg_mul = 0;
   uint64_t seg_base = 0;
