@@ -115,13 +115,18 @@ __device__ __forceinline__ void leaf64_body(unsigned char* smem_raw, const int32
   }
 }
 
+// Persistent grid over the leaf list: only the segments the packed kernel flagged are sorted here, and when it
+// flagged none every CTA leaves at once — so the launch needs no answer from the device first.
 __global__ void __launch_bounds__(PT_THREADS, 2 * PT_MIN_CTAS / 2) k_leaf_sort(const __grid_constant__ LeafParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  const uint32_t s = blockIdx.x;
-  if (s >= *p.count) return;
-  if (p.wide && !p.wide[s]) return;  // already sorted by the packed 32-bit kernel
-  const uint32_t start = p.segs.start[s], len = p.segs.len[s];
-  leaf64_body(smem_raw, p.mv.esize, p.mv.n, p.mv.src, p.mv.dst, p.key, start, start, len, p.in_place != 0);
+  if (p.wide && p.n_wide && *p.n_wide == 0) return;
+  const uint32_t n = *p.count;
+  for (uint32_t s = blockIdx.x; s < n; s += gridDim.x) {
+    if (p.wide && !p.wide[s]) continue;  // already sorted by the packed 32-bit kernel
+    const uint32_t start = p.segs.start[s], len = p.segs.len[s];
+    leaf64_body(smem_raw, p.mv.esize, p.mv.n, p.mv.src, p.mv.dst, p.key, start, start, len, p.in_place != 0);
+    __syncthreads();
+  }
 }
 
 #define L32_IDX_BITS 12
@@ -607,19 +612,11 @@ void run_leaf_and_copy(hs_ctx* c, MoveSet& ms, const KeySrc& key, int src_code, 
     LAUNCH(c, k_copy_segments, dim3(max_copy, COPY_SPLIT), 256, 0, mv, copy.view(), counters + 2);
   }
 }
-// after the counters have been read back: the 64-bit kernel, only if some segment needs it
-static void run_wide_leaves(hs_ctx* c, LeafLaunch& ll, uint32_t n_wide) {
-  if (!n_wide || !ll.max_leaf) return;
-  Stage st(c, "leaf_sort_wide");
-  LAUNCH(c, k_leaf_sort, ll.max_leaf, PT_THREADS, leaf_smem_bytes(), ll.lp);
-}
-
-// The 64-bit kernel runs only for segments the packed kernel flagged. With few leaves it is cheaper to launch it
-// blind (unflagged CTAs exit at once) than to ask the device how many were flagged.
+// The 64-bit kernel for the segments the packed kernel flagged (it reads the flags and their count itself).
 void launch_wide(hs_ctx* c, LeafLaunch& ll, uint32_t* d_counters) {
+  (void)d_counters;
   if (!ll.max_leaf) return;
-  uint32_t nw = 1;
-  if (ll.max_leaf > 8192) nw = *(const uint32_t*)hs_read_wait(c, hs_read_begin(c, d_counters + 4, 4));
-  run_wide_leaves(c, ll, nw);
+  Stage st(c, "leaf_sort_wide");
+  const uint32_t grid = std::min<uint32_t>(ll.max_leaf, (uint32_t)HS_NUM_SMS * 4u);
+  LAUNCH(c, k_leaf_sort, grid, PT_THREADS, leaf_smem_bytes(), ll.lp);
 }
-
