@@ -218,6 +218,29 @@ HS_JNI(jlong, filterScan)(JNIEnv* env, jclass cls, jlong ctx, jobject cols, jint
   return (jlong)(intptr_t)out;
 }
 
+/* ---- K4 on the device: the bodies of all Parquet data pages (and dictionary pages) of ONE column of the sorted
+ * result, for all bucket files at once — what Spark's ParquetFileFormat writer does to every value behind
+ * saveWithBuckets (HS/index/DataFrameWriterExtensions.scala:58-65). col: a direct ByteBuffer holding one
+ * hs_column; pageRows: npages + 1 row boundaries; pageChunk: the bucket file of every page. Returns a table:
+ * column 0 the bodies (pages, then one dictionary page per chunk), column 1 NULLs per page / dictionary entries
+ * per chunk, column 2 (codec 1 = snappy only) the uncompressed sizes. GpuPageFileWriter.scala frames them. */
+HS_JNI(jlong, parquetEncodePages)(JNIEnv* env, jclass cls, jlong ctx, jobject col, jboolean optional, jlongArray pageRows,
+                                  jintArray pageChunk, jint nchunks, jint maxDict, jint codec) {
+  (void)cls;
+  hs_table* out = NULL;
+  jlong* pr = (*env)->GetLongArrayElements(env, pageRows, NULL);
+  jint* pc = (*env)->GetIntArrayElements(env, pageChunk, NULL);
+  if (pr && pc) {
+    const jint npages = (*env)->GetArrayLength(env, pageChunk);
+    int32_t st = hs_parquet_encode_pages(as_ctx(ctx), (const hs_column*)buf_addr(env, col), optional ? 1 : 0,
+                                         (const int64_t*)pr, npages, (const int32_t*)pc, nchunks, maxDict, codec, &out);
+    if (st) { throw_hs(env, as_ctx(ctx), st); out = NULL; }
+  }
+  if (pc) (*env)->ReleaseIntArrayElements(env, pageChunk, pc, JNI_ABORT);
+  if (pr) (*env)->ReleaseLongArrayElements(env, pageRows, pr, JNI_ABORT);
+  return (jlong)(intptr_t)out;
+}
+
 /* ---- results: the Scala side wraps the table's buffers as direct ByteBuffers (no copy) and frees the table
  * when the Parquet writer / the Spark ColumnarBatch is done with them */
 HS_JNI(void, tableWait)(JNIEnv* env, jclass cls, jlong ctx, jlong table) {

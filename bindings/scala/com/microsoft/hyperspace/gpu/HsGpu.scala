@@ -38,6 +38,8 @@ object HsGpu {
       leftOut: Array[Int], rightOut: Array[Int]): Long
   @native def filterScan(ctx: Long, cols: ByteBuffer, ncols: Int, off: Array[Long], nIndexed: Int,
       numBuckets: Int, terms: ByteBuffer, nterms: Int, outCols: Array[Int]): Long
+  @native def parquetEncodePages(ctx: Long, col: ByteBuffer, optional: Boolean, pageRows: Array[Long],
+      pageChunk: Array[Int], nchunks: Int, maxDict: Int, codec: Int): Long
   @native def tableWait(ctx: Long, table: Long): Unit
   @native def tableFree(ctx: Long, table: Long): Unit
   @native def tableRows(table: Long): Long
