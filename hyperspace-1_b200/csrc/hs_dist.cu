@@ -199,6 +199,12 @@ struct NcclExchange : BuildExchange {
     nbl = bhi > blo ? bhi - blo : 0;
     if (nbl == 0) blo = 0;
   }
+  // Grouped spans queue copies on a second stream that read span_tmp: if the build unwinds early (an error on
+  // this rank), those copies must have finished before the buffers go back to the cache.
+  cudaStream_t busy_stream = nullptr;
+  ~NcclExchange() override {
+    if (busy_stream) cudaStreamSynchronize(busy_stream);
+  }
   void share_stats(hs_ctx* c, const std::vector<uint32_t>& local_hist, uint64_t* minmax,
                    std::vector<uint8_t>& has_nulls) override {
     Stage s(c, "stats_exchange");
@@ -715,6 +721,7 @@ struct NcclExchange : BuildExchange {
     bar_b.alloc(c, 16 * (size_t)N);
     // everything that crosses NVLink is queued now, on the second stream: per group one copy per (owner, column),
     // then the barrier that tells every owner its group is complete
+    busy_stream = st->xs;
     CK(cudaStreamWaitEvent(st->xs, ev_grouped, 0));
     CK(cudaEventRecord(st->x_e0, st->xs));
     for (int q = 0; q < S; q++) CK(cudaStreamWaitEvent(st->cs[q], ev_grouped, 0));
@@ -782,6 +789,7 @@ struct NcclExchange : BuildExchange {
     }
     if (g == G - 1) {
       // the stream has passed the last barrier: the copies are done with the grouped rows
+      busy_stream = nullptr;
       span_tmp.clear();
       bar_a.release();
       bar_b.release();
