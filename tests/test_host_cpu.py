@@ -368,11 +368,14 @@ def test_parquet_framing_reads_back_with_pyarrow(tmp_path):
         assert got[n].to_pylist() == cols[n].to_pylist()
 
 
-def test_dictionary_page_framing_is_read_by_pyarrow(tmp_path):
+@pytest.mark.parametrize("snappy", [False, True])
+def test_dictionary_page_framing_is_read_by_pyarrow(tmp_path, snappy):
     """The layout hs_parquet_encode_pages produces for a dictionary-encoded chunk, assembled here by hand: a
     PLAIN dictionary page, then data pages = definition levels ++ bit width ++ ONE bit-packed run of the indices
     (last group zero-padded). pyarrow must read the rows back; this pins the framing (headers, footer offsets)
-    without a GPU."""
+    without a GPU. snappy: the same bodies compressed (here by pyarrow's codec, on the GPU by k_snappy_frag), with
+    the uncompressed sizes in the page headers and the codec in the footer, as codec = 1 of
+    hs_parquet_encode_pages is framed."""
     import struct
     import pyarrow.parquet as pq
     from hyperspace_1_b200 import log_entry as le, parquet_plain as pp
@@ -404,23 +407,31 @@ def test_dictionary_page_framing_is_read_by_pyarrow(tmp_path):
     values = [int(dictionary[i]) if v else None for i, v in zip(idx, valid)]
     pages = [(0, 13), (13, 29)]
     path = tmp_path / "d.parquet"
+    squeeze = (lambda b: pa.Codec("snappy").compress(b, asbytes=True)) if snappy else (lambda b: b)
     with open(path, "wb") as f:
         f.write(pp.MAGIC)
         dbody = dictionary.tobytes()
-        hdr = pp.dictionary_page_header(len(dictionary), len(dbody))
-        f.write(hdr + dbody)
-        pos = 4 + len(hdr) + len(dbody)
+        stored = squeeze(dbody)
+        hdr = pp.dictionary_page_header(len(dictionary), len(stored), len(dbody))
+        f.write(hdr + stored)
+        pos = 4 + len(hdr) + len(stored)
+        upos = len(hdr) + len(dbody)
         data_off = pos
         for a, e in pages:
             body = def_levels(valid[a:e]) + packed([int(i) for i, v in zip(idx[a:e], valid[a:e]) if v], 3)
-            hdr = pp.page_header(e - a, len(body), pp.ENC_PLAIN_DICTIONARY)
-            f.write(hdr + body)
-            pos += len(hdr) + len(body)
+            stored = squeeze(body)
+            hdr = pp.page_header(e - a, len(stored), pp.ENC_PLAIN_DICTIONARY, len(body))
+            f.write(hdr + stored)
+            pos += len(hdr) + len(stored)
+            upos += len(hdr) + len(body)
         names, types = ["k"], [pa.int64()]
-        foot = pp.footer(names, types, 29, [(4, pos - 4, 29, data_off)], le.schema_json(pa.schema([pa.field("k", pa.int64())])))
+        foot = pp.footer(names, types, 29, [(4, pos - 4, 29, data_off, upos)],
+                         le.schema_json(pa.schema([pa.field("k", pa.int64())])), 1 if snappy else 0)
         f.write(foot + struct.pack("<I", len(foot)) + pp.MAGIC)
     pf = pq.ParquetFile(path)
     col = pf.metadata.row_group(0).column(0)
+    assert col.compression == ("SNAPPY" if snappy else "UNCOMPRESSED")
+    assert col.total_compressed_size == pos - 4 and col.total_uncompressed_size == upos
     assert col.has_dictionary_page and col.dictionary_page_offset == 4 and col.data_page_offset == data_off
     assert pf.read()["k"].to_pylist() == values
 
